@@ -1,0 +1,372 @@
+/*
+ * amg_oracle.c -- TEST INFRASTRUCTURE ONLY.  CPU restatement ("port") of the reference's
+ * solve-phase V-cycle hot path, fp64 / int32, plain serial C.
+ *
+ * Nothing in the product (pyamg_b200/) may import, link or call this file; it is the
+ * checker used by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg.
+ *
+ * Parity status: PINNED.  tests/test_oracle.py checks every function here against
+ *   (a) the golden vectors of the reference's own tests
+ *       (pyamg/relaxation/tests/test_relaxation.py:139-402) and
+ *   (b) the reference's compiled kernels oracle/_ref/_amg_core.so (built by
+ *       oracle/build_ref.sh from /root/reference/pyamg/amg_core/amg_core_wrap.cxx) and the
+ *       installed scipy 1.18.1 _sparsetools, bit for bit on seeded inputs.
+ *
+ * Each function cites the reference lines it follows (paths relative to /root/reference).
+ * The fp64 operation ORDER of the reference is kept exactly (row-internal storage order,
+ * the b - sum vs (b - t1) - t2 association of the CSR vs BSR smoothers, ...), and the file
+ * is compiled with -ffp-contract=off so no FMA changes roundings.
+ */
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+
+typedef int I;
+typedef double T;
+
+/* ---- scipy _sparsetools csr_matvec: y += A x  (call sites pyamg/multilevel.py:496,498,544) */
+void orc_csr_matvec(I n_row, const I *Ap, const I *Aj, const T *Ax, const T *x, T *y)
+{
+    for (I i = 0; i < n_row; i++) {
+        T s = y[i];
+        for (I p = Ap[i]; p < Ap[i + 1]; p++)
+            s += Ax[p] * x[Aj[p]];
+        y[i] = s;
+    }
+}
+
+/* ---- scipy _sparsetools bsr_matvec: y += A x with R x C row-major blocks.
+ * R == C == 1 goes through csr_matvec exactly as scipy does. */
+void orc_bsr_matvec(I n_brow, I R, I C, const I *Ap, const I *Aj, const T *Ax, const T *x, T *y)
+{
+    if (R == 1 && C == 1) { orc_csr_matvec(n_brow, Ap, Aj, Ax, x, y); return; }
+    const I RC = R * C;
+    for (I i = 0; i < n_brow; i++) {
+        T *yb = y + (size_t)R * i;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            const T *blk = Ax + (size_t)RC * p;
+            const T *xb = x + (size_t)C * Aj[p];
+            for (I r = 0; r < R; r++) {
+                T s = yb[r];
+                for (I c = 0; c < C; c++)
+                    s += blk[r * C + c] * xb[c];
+                yb[r] = s;
+            }
+        }
+    }
+}
+
+/* ---- amg_core.jacobi, pyamg/amg_core/relaxation.h:201-239 */
+void orc_jacobi(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, T *temp,
+                I row_start, I row_stop, I row_step, T omega)
+{
+    for (I i = row_start; i != row_stop; i += row_step)
+        temp[i] = x[i];
+    for (I i = row_start; i != row_stop; i += row_step) {
+        T offd = 0, d = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) d = Ax[p];            /* last stored diagonal wins */
+            else offd += Ax[p] * temp[j];
+        }
+        if (d != 0.0)
+            x[i] = (1.0 - omega) * temp[i] + omega * ((b[i] - offd) / d);
+    }
+}
+
+/* ---- amg_core.gauss_seidel, relaxation.h:33-62 */
+void orc_gauss_seidel(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b,
+                      I row_start, I row_stop, I row_step)
+{
+    for (I i = row_start; i != row_stop; i += row_step) {
+        T offd = 0, d = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) d = Ax[p];
+            else offd += Ax[p] * x[j];
+        }
+        if (d != 0.0)
+            x[i] = (b[i] - offd) / d;
+    }
+}
+
+/* ---- amg_core.gauss_seidel_indexed, relaxation.h:394-426 (positions of Id, repeats allowed) */
+void orc_gauss_seidel_indexed(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b,
+                              const I *Id, I row_start, I row_stop, I row_step)
+{
+    for (I k = row_start; k != row_stop; k += row_step) {
+        I i = Id[k];
+        T offd = 0, d = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) d = Ax[p];
+            else offd += Ax[p] * x[j];
+        }
+        if (d != 0.0)
+            x[i] = (b[i] - offd) / d;
+    }
+}
+
+/* dense row-major block times vector started from zero: linalg.h:359-398 as used by the BSR
+ * smoothers (overwrite='T', Strans='F'): out[r] = ((0 + a_r0 v_0) + a_r1 v_1) + ... */
+static void blk_matvec0(const T *blk, const T *v, T *out, I bs)
+{
+    for (I r = 0; r < bs; r++) {
+        T s = 0;
+        for (I c = 0; c < bs; c++)
+            s += blk[r * bs + c] * v[c];
+        out[r] = s;
+    }
+}
+
+/* ---- amg_core.bsr_gauss_seidel, relaxation.h:89-173 */
+void orc_bsr_gauss_seidel(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b,
+                          I row_start, I row_stop, I row_step, I bs)
+{
+    const I B2 = bs * bs;
+    T *acc = (T *)malloc(sizeof(T) * bs), *loc = (T *)malloc(sizeof(T) * bs);
+    const I k0 = row_step < 0 ? bs - 1 : 0, k1 = row_step < 0 ? -1 : bs, dk = row_step < 0 ? -1 : 1;
+    for (I i = row_start; i != row_stop; i += row_step) {
+        long dptr = -1;
+        for (I k = 0; k < bs; k++) acc[k] = b[(size_t)i * bs + k];
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) { dptr = (long)p * B2; continue; }
+            blk_matvec0(Ax + (size_t)p * B2, x + (size_t)j * bs, loc, bs);
+            for (I m = 0; m < bs; m++) acc[m] -= loc[m];
+        }
+        if (dptr < 0) continue;               /* no stored diagonal block: row untouched */
+        for (I k = k0; k != k1; k += dk) {
+            T d = 1.0;
+            for (I kk = k0; kk != k1; kk += dk) {
+                if (kk == k) d = Ax[dptr + k * bs + kk];
+                else acc[k] -= Ax[dptr + k * bs + kk] * x[(size_t)i * bs + kk];
+            }
+            if (d != 0.0) x[(size_t)i * bs + k] = acc[k] / d;
+        }
+    }
+    free(acc); free(loc);
+}
+
+/* ---- amg_core.bsr_jacobi, relaxation.h:267-360.  The temp copy (:301-303) takes the
+ * |row_stop-row_start|*bs LEADING entries; the reference's loop never terminates for a
+ * negative row_step (i += -1 from 0), and its Python wrapper only ever passes (0, N, 1)
+ * (relaxation.py:403-404), so the copy is restated for the forward case only. */
+void orc_bsr_jacobi(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, T *temp,
+                    I row_start, I row_stop, I row_step, I bs, T omega)
+{
+    const I B2 = bs * bs;
+    T *acc = (T *)malloc(sizeof(T) * bs), *loc = (T *)malloc(sizeof(T) * bs);
+    const I k0 = row_step < 0 ? bs - 1 : 0, k1 = row_step < 0 ? -1 : bs, dk = row_step < 0 ? -1 : 1;
+    for (I i = 0; i < abs(row_stop - row_start) * bs; i++)
+        temp[i] = x[i];
+    for (I i = row_start; i != row_stop; i += row_step) {
+        long dptr = -1;
+        for (I k = 0; k < bs; k++) acc[k] = b[(size_t)i * bs + k];
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) { dptr = (long)p * B2; continue; }
+            blk_matvec0(Ax + (size_t)p * B2, temp + (size_t)j * bs, loc, bs);
+            for (I m = 0; m < bs; m++) acc[m] -= loc[m];
+        }
+        if (dptr < 0) continue;
+        for (I k = k0; k != k1; k += dk) {
+            T d = 1.0;
+            for (I kk = k0; kk != k1; kk += dk) {
+                if (kk == k) d = Ax[dptr + k * bs + kk];
+                else acc[k] -= Ax[dptr + k * bs + kk] * temp[(size_t)i * bs + kk];
+            }
+            if (d != 0.0)
+                x[(size_t)i * bs + k] = (1.0 - omega) * temp[(size_t)i * bs + k] + omega * acc[k] / d;
+        }
+    }
+    free(acc); free(loc);
+}
+
+/* ---- amg_core.vertex_coloring_mis, graph.h:171-188 with the greedy lexicographic MIS of
+ * graph.h:34-61.  State encoding per round K: active = -1-K, in set = K, excluded = -2-K. */
+I orc_vertex_coloring_mis(I n, const I *Ap, const I *Aj, I *color)
+{
+    for (I i = 0; i < n; i++) color[i] = -1;
+    I done = 0, K = 0;
+    while (done < n) {
+        const I active = -1 - K, out = -2 - K;
+        for (I i = 0; i < n; i++) {
+            if (color[i] != active) continue;
+            color[i] = K; done++;
+            for (I p = Ap[i]; p < Ap[i + 1]; p++)
+                if (color[Aj[p]] == active) color[Aj[p]] = out;
+        }
+        K++;
+    }
+    return K;
+}
+
+/* ======================= setup-phase pieces (Galerkin product and its inputs) ============= */
+
+/* ---- scipy _sparsetools csr_matmat_maxnnz: structural nnz of C = A B (upper bound used to
+ * allocate; call sites pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:187) */
+long orc_csr_matmat_maxnnz(I n_row, I n_col, const I *Ap, const I *Aj, const I *Bp, const I *Bj)
+{
+    I *mask = (I *)malloc(sizeof(I) * (n_col > 0 ? n_col : 1));
+    for (I k = 0; k < n_col; k++) mask[k] = -1;
+    long nnz = 0;
+    for (I i = 0; i < n_row; i++)
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            for (I q = Bp[j]; q < Bp[j + 1]; q++)
+                if (mask[Bj[q]] != i) { mask[Bj[q]] = i; nnz++; }
+        }
+    free(mask);
+    return nnz;
+}
+
+/* ---- scipy _sparsetools csr_matmat (Gustavson row-wise product).  Per row: a dense
+ * accumulator + a linked list threaded through the touched columns; columns come out in
+ * REVERSE first-touch order, entries whose accumulated sum is exactly 0.0 are dropped.
+ * Returns nnz written; Cp has n_row+1 entries. */
+long orc_csr_matmat(I n_row, I n_col, const I *Ap, const I *Aj, const T *Ax,
+                    const I *Bp, const I *Bj, const T *Bx, I *Cp, I *Cj, T *Cx)
+{
+    I *link = (I *)malloc(sizeof(I) * (n_col > 0 ? n_col : 1));
+    T *acc = (T *)calloc(n_col > 0 ? n_col : 1, sizeof(T));
+    for (I k = 0; k < n_col; k++) link[k] = -1;
+    long nnz = 0;
+    Cp[0] = 0;
+    for (I i = 0; i < n_row; i++) {
+        I head = -2, len = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            T a = Ax[p];
+            for (I q = Bp[j]; q < Bp[j + 1]; q++) {
+                I k = Bj[q];
+                acc[k] += a * Bx[q];
+                if (link[k] == -1) { link[k] = head; head = k; len++; }
+            }
+        }
+        for (I t = 0; t < len; t++) {
+            if (acc[head] != 0.0) { Cj[nnz] = head; Cx[nnz] = acc[head]; nnz++; }
+            I nxt = link[head];
+            link[head] = -1; acc[head] = 0;
+            head = nxt;
+        }
+        Cp[i + 1] = (I)nnz;
+    }
+    free(link); free(acc);
+    return nnz;
+}
+
+/* ---- scipy _sparsetools csr_tocsc (explicit transpose: P.T.tocsr(), classical.py:174;
+ * P.H for SA, aggregation.py:400-401).  Rows inside each output row stay ascending. */
+void orc_csr_tocsc(I n_row, I n_col, const I *Ap, const I *Aj, const T *Ax, I *Bp, I *Bi, T *Bx)
+{
+    const I nnz = Ap[n_row];
+    for (I k = 0; k <= n_col; k++) Bp[k] = 0;
+    for (I p = 0; p < nnz; p++) Bp[Aj[p] + 1]++;
+    for (I k = 0; k < n_col; k++) Bp[k + 1] += Bp[k];
+    I *fill = (I *)malloc(sizeof(I) * (n_col > 0 ? n_col : 1));
+    memcpy(fill, Bp, sizeof(I) * n_col);
+    for (I i = 0; i < n_row; i++)
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I dst = fill[Aj[p]]++;
+            Bi[dst] = i; Bx[dst] = Ax[p];
+        }
+    free(fill);
+}
+
+/* ---- amg_core.symmetric_strength_of_connection, smoothed_aggregation.h:48-99 (real T):
+ * keep a_ij when i==j or a_ij^2 >= theta^2 |a_ii| |a_jj| ; duplicates on the diagonal summed. */
+void orc_symmetric_strength(I n, T theta, const I *Ap, const I *Aj, const T *Ax, I *Sp, I *Sj, T *Sx)
+{
+    T *dg = (T *)malloc(sizeof(T) * (n > 0 ? n : 1));
+    for (I i = 0; i < n; i++) {
+        T d = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) if (Aj[p] == i) d += Ax[p];
+        dg[i] = fabs(d);
+    }
+    I nnz = 0; Sp[0] = 0;
+    for (I i = 0; i < n; i++) {
+        const T lim = theta * theta * dg[i];
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p]; T a = Ax[p];
+            if (j == i || a * a >= lim * dg[j]) { Sj[nnz] = j; Sx[nnz] = a; nnz++; }
+        }
+        Sp[i + 1] = nnz;
+    }
+    free(dg);
+}
+
+/* ---- amg_core.standard_aggregation, smoothed_aggregation.h:121-221 (three greedy passes).
+ * agg[i] = aggregate of node i (-1: isolated); cpts[] = root nodes.  Returns #aggregates. */
+I orc_standard_aggregation(I n, const I *Ap, const I *Aj, I *agg, I *cpts)
+{
+    for (I i = 0; i < n; i++) agg[i] = 0;
+    I next = 1;
+    for (I i = 0; i < n; i++) {                       /* pass 1: seed where all nbrs are free */
+        if (agg[i]) continue;
+        int nbr = 0, taken = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j != i) { nbr = 1; if (agg[j]) { taken = 1; break; } }
+        }
+        if (!nbr) agg[i] = -n;
+        else if (!taken) {
+            agg[i] = next; cpts[next - 1] = i;
+            for (I p = Ap[i]; p < Ap[i + 1]; p++) agg[Aj[p]] = next;
+            next++;
+        }
+    }
+    for (I i = 0; i < n; i++) {                       /* pass 2: attach to a neighbouring seed aggregate */
+        if (agg[i]) continue;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I a = agg[Aj[p]];
+            if (a > 0) { agg[i] = -a; break; }
+        }
+    }
+    next--;
+    for (I i = 0; i < n; i++) {                       /* pass 3: renumber from 0, sweep up leftovers */
+        I a = agg[i];
+        if (a != 0) {
+            agg[i] = a > 0 ? a - 1 : (a == -n ? -1 : -a - 1);
+            continue;
+        }
+        agg[i] = next; cpts[next] = i;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) if (agg[Aj[p]] == 0) agg[Aj[p]] = next;
+        next++;
+    }
+    return next;
+}
+
+/* ---- amg_core.fit_candidates (real), smoothed_aggregation.h:322-448: per aggregate j
+ * (CSC of AggOp: Ap/Ai) gather the K1 x K2 blocks of B, modified Gram-Schmidt QR of the
+ * stacked block column, Q into Qx (nnz x K1 x K2), R into Rx (n_col x K2 x K2). */
+void orc_fit_candidates(I n_col, I K1, I K2, const I *Ap, const I *Ai, T *Qx, const T *B, T *Rx, T tol)
+{
+    const I BS = K1 * K2;
+    memset(Rx, 0, sizeof(T) * (size_t)n_col * K2 * K2);
+    for (I j = 0; j < n_col; j++)
+        for (I p = Ap[j]; p < Ap[j + 1]; p++)
+            memcpy(Qx + (size_t)BS * p, B + (size_t)BS * Ai[p], sizeof(T) * BS);
+    for (I j = 0; j < n_col; j++) {
+        T *q0 = Qx + (size_t)BS * Ap[j], *q1 = Qx + (size_t)BS * Ap[j + 1];
+        T *Rj = Rx + (size_t)j * K2 * K2;
+        for (I c = 0; c < K2; c++) {
+            T nrm = 0;
+            for (T *q = q0 + c; q < q1; q += K2) nrm += (*q) * (*q);
+            const T thresh = tol * sqrt(nrm);
+            for (I a = 0; a < c; a++) {
+                T d = 0;
+                for (T *qa = q0 + a, *qc = q0 + c; qa < q1; qa += K2, qc += K2) d += (*qa) * (*qc);
+                for (T *qa = q0 + a, *qc = q0 + c; qa < q1; qa += K2, qc += K2) *qc -= d * (*qa);
+                Rj[K2 * a + c] = d;
+            }
+            nrm = 0;
+            for (T *q = q0 + c; q < q1; q += K2) nrm += (*q) * (*q);
+            nrm = sqrt(nrm);
+            T scale;
+            if (nrm > thresh) { scale = 1.0 / nrm; Rj[K2 * c + c] = nrm; }
+            else { scale = 0; Rj[K2 * c + c] = 0; }
+            for (T *q = q0 + c; q < q1; q += K2) *q *= scale;
+        }
+    }
+}
