@@ -1,0 +1,150 @@
+"""Generate tests/golden/*.npz by running the REAL reference (pyamg 3.0.2 fork, imported from
+/root/reference through oracle/refimport.py, native kernels = oracle/_ref/_amg_core.so built
+from the reference sources).  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+Each fixture = the reference-built hierarchy (A/P/R per level, exact formats and column order),
+the resolved smoother parameters (omega/rho for Jacobi, MIS colour orderings for
+gauss_seidel_indexed), b, the reference residual history and the final x.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
+warnings.simplefilter('ignore')
+
+from oracle import refimport  # noqa: E402
+import hier_io  # noqa: E402
+
+pyamg = refimport.import_pyamg()
+from pyamg.gallery import poisson, stencil_grid, linear_elasticity  # noqa: E402
+from pyamg.gallery.diffusion import diffusion_stencil_2d  # noqa: E402
+from pyamg.graph import vertex_coloring  # noqa: E402
+from pyamg.relaxation.relaxation import gauss_seidel_indexed  # noqa: E402
+import pyamg.amg_core as ref_core  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+JAC = ('jacobi', {'omega': 4.0 / 3.0})
+
+
+def run(ml, n, cycles, cycle='V'):
+    b = np.random.rand(n)
+    res = []
+    x = ml.solve(b, tol=1e-30, maxiter=cycles, residuals=res, cycle=cycle)
+    return b, np.array(res), x
+
+
+def jacobi_specs(ml):
+    out = []
+    for lvl in ml.levels[:-1]:
+        om = (4.0 / 3.0) / lvl.A.rho_D_inv
+        out.append((('jacobi', {'omega': float(om), 'iterations': 1}),) * 2)
+    return out
+
+
+def color_order(A):
+    c = vertex_coloring(A.tocsr(), 'MIS')
+    K = int(c.max()) + 1
+    idx = np.concatenate([np.where(c == k)[0] for k in range(K)]).astype('intc')
+    ptr = np.zeros(K + 1, 'intc')
+    ptr[1:] = np.cumsum(np.bincount(c, minlength=K))
+    return c, idx, ptr
+
+
+def install_mcgs(ml):
+    specs = []
+    for lvl in ml.levels[:-1]:
+        _, idx, ptr = color_order(lvl.A)
+
+        def sm(A, x, b, idx=idx):
+            gauss_seidel_indexed(A, x, b, idx, iterations=1, sweep='symmetric')
+        lvl.presmoother = lvl.postsmoother = sm
+        spec = ('gauss_seidel_indexed', {'indices': idx, 'color_ptr': ptr, 'sweep': 'symmetric',
+                                         'iterations': 1})
+        specs.append((spec, spec))
+    return specs
+
+
+def sa_poisson(name, grid, max_coarse, improve):
+    A = poisson(grid, format='csr')
+    np.random.seed(0)
+    kw = {} if improve else {'improve_candidates': None}
+    ml = pyamg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC,
+                                           max_coarse=max_coarse, **kw)
+    b, res, x = run(ml, A.shape[0], 10)
+    rhos = [getattr(l, 'rho_smooth', 0.0) for l in ml.levels[:-1]]
+    hier_io.save(os.path.join(OUT, name), ml.levels, jacobi_specs(ml),
+                 {'b': b, 'residuals': res, 'x': x, 'rho_smooth': rhos})
+    print(name, [l.A.shape[0] for l in ml.levels], res[0], res[-1])
+    # W and F cycles on the same hierarchy
+    for cyc in 'WF':
+        r = []
+        xx = ml.solve(b, tol=1e-30, maxiter=4, residuals=r, cycle=cyc)
+        np.savez_compressed(os.path.join(OUT, name.replace('.npz', '_%s.npz' % cyc)),
+                            residuals=np.array(r), x=xx)
+
+
+def rs_mcgs(name, A, max_coarse):
+    np.random.seed(0)
+    ml = pyamg.ruge_stuben_solver(A, max_coarse=max_coarse)
+    specs = install_mcgs(ml)
+    b, res, x = run(ml, A.shape[0], 10)
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, {'b': b, 'residuals': res, 'x': x})
+    print(name, [l.A.shape[0] for l in ml.levels], [int(s[0][1]['color_ptr'].shape[0]) - 1 for s in specs],
+          [bool(l.A.has_sorted_indices) for l in ml.levels], res[0], res[-1])
+
+
+def sa_elasticity(name, grid):
+    A, B = linear_elasticity(grid, format='bsr')
+    np.random.seed(0)
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    b, res, x = run(ml, A.shape[0], 8)
+    specs = [((('gauss_seidel', {'sweep': 'symmetric', 'iterations': 1}),) * 2) for _ in ml.levels[:-1]]
+    extra = {'b': b, 'residuals': res, 'x': x}
+    # block-multicolour variant: colour the BLOCK graph with the reference MIS colouring and
+    # relax block rows colour by colour through the reference bsr_gauss_seidel kernel, one
+    # block row per call (row_start=i,row_stop=i+-1) -- the sequential definition the GPU
+    # block-colour kernel must reproduce.
+    import scipy.sparse as sp
+    orders = []
+    for lvl in ml.levels[:-1]:
+        Ab = lvl.A.tobsr()
+        G = sp.csr_matrix((np.ones(len(Ab.indices)), Ab.indices, Ab.indptr),
+                          shape=(Ab.shape[0] // Ab.blocksize[0],) * 2)
+        _, idx, ptr = color_order(G)
+        orders.append((idx, ptr))
+
+        def sm(A, x, b, idx=idx):
+            Ab = A.tobsr()
+            bs = Ab.blocksize[0]
+            data = np.ravel(Ab.data)
+            for i in idx:
+                ref_core.bsr_gauss_seidel(Ab.indptr, Ab.indices, data, x, b, int(i), int(i) + 1, 1, bs)
+            for i in idx[::-1]:
+                ref_core.bsr_gauss_seidel(Ab.indptr, Ab.indices, data, x, b, int(i), int(i) - 1, -1, bs)
+        lvl.presmoother = lvl.postsmoother = sm
+    r2 = []
+    x2 = ml.solve(b, tol=1e-30, maxiter=8, residuals=r2)
+    extra.update({'mc_residuals': np.array(r2), 'mc_x': x2})
+    for k, (idx, ptr) in enumerate(orders):
+        extra['mc_idx%d' % k] = idx
+        extra['mc_ptr%d' % k] = ptr
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, extra)
+    print(name, [(l.A.shape[0], l.A.format, getattr(l.A, 'blocksize', None)) for l in ml.levels],
+          res[0], res[-1], r2[-1])
+
+
+if __name__ == '__main__':
+    sa_poisson('sa_poisson3d_12.npz', (12, 12, 12), 20, improve=False)
+    sa_poisson('sa_poisson3d_16_default.npz', (16, 16, 16), 30, improve=True)
+    rs_mcgs('rs_poisson2d_40_mcgs.npz', poisson((40, 40), format='csr'), 20)
+    st = diffusion_stencil_2d(epsilon=0.001, theta=np.pi / 8, type='FE')
+    rs_mcgs('rs_aniso_48_mcgs.npz', stencil_grid(st, (48, 48), format='csr'), 20)
+    sa_elasticity('sa_elasticity2d_14.npz', (14, 14))
