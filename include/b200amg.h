@@ -1,0 +1,183 @@
+/*
+ * b200amg.h -- C-ABI of libb200amg.so: the B200 (sm_100a) drop-in for the solve-phase V-cycle
+ * hot path of PyAMG (reference: rsmedleystevenson/pyamg, paths below relative to its root).
+ *
+ * Conventions
+ *   - every array pointer is a DEVICE pointer (fp64 values, int32 indices) unless the
+ *     parameter name ends in _host; the caller owns all buffers, nothing is retained except
+ *     by the b200amg_vcycle_* handle (which only stores the pointers it is given);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - return value: 0 on success, otherwise a cudaError_t value (>0) or a negative
+ *     B200AMG_E* code; b200amg_last_error() gives the text;
+ *   - kernels mutate x (and temp) in place and return nothing else, exactly like the
+ *     reference's amg_core functions (pyamg/amg_core/amg_core.i:27-92, INPLACE_ARRAY1).
+ *   - fp64 results are BIT-IDENTICAL to the reference's serial loops wherever the parallel
+ *     schedule is order-free (SpMV, residual, prolongation, Jacobi, colour-ordered
+ *     Gauss-Seidel, Galerkin product): every row is accumulated in CSR storage order with
+ *     separately rounded multiply and add, like the reference's non-FMA x86-64 build.
+ */
+#ifndef B200AMG_H
+#define B200AMG_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200AMG_EINVAL  (-1)   /* bad argument (negative size, unsupported blocksize, ...) */
+#define B200AMG_ENOMEM  (-2)   /* caller-provided workspace too small */
+#define B200AMG_ESTATE  (-3)   /* handle used in the wrong state */
+
+const char *b200amg_last_error(void);
+int b200amg_version(void);
+/* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
+long long b200amg_launch_count(void);
+
+/* ---- SpMV family: scipy.sparse `A * x` = _sparsetools csr_matvec / bsr_matvec
+ *      call sites pyamg/multilevel.py:496 (b - A*x), :498 (R*residual), :544 (x += P*coarse_x),
+ *      pyamg/util/linalg.py:109-112 (residual_norm) ---------------------------------------- */
+/* y = A x */
+int b200amg_csr_matvec(int n_row, int n_col, const int *Ap, const int *Aj, const double *Ax,
+                       const double *x, double *y, void *stream);
+/* y = alpha * (A x) + beta * y   (generic helper; not a reference call site) */
+int b200amg_csr_spmv(int n_row, int n_col, const int *Ap, const int *Aj, const double *Ax,
+                     const double *x, double *y, double alpha, double beta, void *stream);
+/* r = b - A x                      (multilevel.py:496 fused with its numpy subtraction) */
+int b200amg_csr_residual(int n_row, const int *Ap, const int *Aj, const double *Ax,
+                         const double *x, const double *b, double *r, void *stream);
+/* x += A xc                        (multilevel.py:544: x += P * coarse_x) */
+int b200amg_csr_matvec_add(int n_row, const int *Ap, const int *Aj, const double *Ax,
+                           const double *xc, double *x, void *stream);
+/* BSR with R x C row-major blocks (scipy bsr_matvec); mode 0: y = A x, 1: y = b - A x,
+ * 2: y += A x.  R, C in 1..8. */
+int b200amg_bsr_matvec(int n_brow, int n_bcol, int R, int C, const int *Ap, const int *Aj,
+                       const double *Ax, const double *x, const double *b, double *y, int mode,
+                       void *stream);
+
+/* ---- smoothers: amg_core signatures (pyamg/amg_core/relaxation.h) --------------------- */
+/* amg_core.jacobi, relaxation.h:201-239.  omega is passed by value (the reference passes a
+ * length-1 array, relaxation.py:412).  temp must hold n doubles. Only the contiguous forward
+ * range the reference's Python wrapper uses (row_step == 1) is accepted. */
+int b200amg_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                   double *temp, int row_start, int row_stop, int row_step, double omega,
+                   void *stream);
+/* amg_core.bsr_jacobi, relaxation.h:267-360 (blocksize 1..8, row_step == 1) */
+int b200amg_bsr_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                       double *temp, int row_start, int row_stop, int row_step, int blocksize,
+                       double omega, void *stream);
+/* amg_core.gauss_seidel_indexed, relaxation.h:394-426.
+ * color_ptr_host (HOST array of K+1 offsets into Id) declares that positions
+ * [color_ptr[c], color_ptr[c+1]) of Id are mutually independent rows: each colour is then
+ * relaxed in parallel, colours in sweep order -- bit-identical to the sequential sweep.
+ * With color_ptr_host == NULL the sweep is executed strictly sequentially on the GPU
+ * (one thread block), so arbitrary index lists with repeats keep reference semantics. */
+int b200amg_gauss_seidel_indexed(const int *Ap, const int *Aj, const double *Ax, double *x,
+                                 const double *b, const int *Id, int row_start, int row_stop,
+                                 int row_step, const int *color_ptr_host, int K, void *stream);
+/* amg_core.gauss_seidel, relaxation.h:33-62: lexicographic sweep, executed sequentially on
+ * the GPU (one thread block; exact, slow) -- the parallel forms are the indexed / level ones. */
+int b200amg_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x,
+                         const double *b, int row_start, int row_stop, int row_step,
+                         void *stream);
+/* amg_core.bsr_gauss_seidel, relaxation.h:89-173 (blocksize 1..8).  Id/color_ptr_host as
+ * above but over BLOCK rows; Id == NULL: the plain (row_start,row_stop,row_step) range,
+ * executed sequentially. */
+int b200amg_bsr_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x,
+                             const double *b, int row_start, int row_stop, int row_step,
+                             int blocksize, const int *Id, const int *color_ptr_host, int K,
+                             void *stream);
+
+/* ---- vector kernels: pyamg/util/linalg.py:17-54 (norm), :109-112 (residual_norm) ------ */
+/* out_dev[0] = sum_i x_i*y_i  (deterministic two-stage reduction; work: >= 1024 doubles) */
+int b200amg_dot(long long n, const double *x, const double *y, double *out_dev, double *work,
+                void *stream);
+/* y = a*x + y ; y = x ; x = 0 */
+int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream);
+/* one Jacobi sweep from a zero initial guess == diagonal scaling (bit-identical):
+ * x = omega*(b/diag) [CSR arithmetic] or (omega*b)/diag [bsr_flavor != 0]; rows with diag==0 -> 0 */
+int b200amg_scale_diag(long long n, double omega, const double *b, const double *diag, double *x,
+                       int bsr_flavor, void *stream);
+/* diag[i*bs+k] = A_ii[k][k] of the LAST stored diagonal block of block row i (0 if absent) */
+int b200amg_extract_diag(int n_brow, int blocksize, const int *Ap, const int *Aj, const double *Ax,
+                         double *diag, void *stream);
+/* y = M x, dense row-major M (n x n): coarse_grid_solver('pinv2'), multilevel.py:608-612 */
+int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, void *stream);
+
+/* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
+ *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */
+/* Row-wise C = A B with SORTED column indices, exact zeros dropped (scipy drops them too);
+ * values bit-identical to scipy's csr_matmat (same accumulation order, no FMA).
+ *  1. b200amg_spgemm_count : ub[i] = number of products of row i;
+ *  2. b200amg_exclusive_scan_i64(ub) -> ubp[n_row+1] (scratch offsets, ubp[n_row] = total);
+ *  3. b200amg_spgemm_numeric: expand-sort-compress every row into the scratch Tj/Tx (both sized
+ *     ubp[n_row]) at offset ubp[i], cnt[i] = kept entries.  Tk (u64[ubp[n_row]]) is only
+ *     needed when some row has more than 8192 products (else NULL).  work: n_row + 128 ints.
+ *     Synchronises the stream once (row binning).
+ *  4. b200amg_exclusive_scan_i32(cnt) -> Cp[n_row+1];
+ *  5. b200amg_spgemm_compact: copy the kept entries to Cj/Cx. */
+int b200amg_spgemm_count(int n_row, const int *Ap, const int *Aj, const int *Bp, long long *ub,
+                         void *stream);
+int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, const double *Ax,
+                           const int *Bp, const int *Bj, const double *Bx, const long long *ub,
+                           const long long *ubp, unsigned long long *Tk, int *Tj, double *Tx,
+                           int *cnt, int *work, void *stream);
+int b200amg_spgemm_compact(int n_row, const long long *ubp, const int *Tj, const double *Tx,
+                           const int *Cp, int *Cj, double *Cx, void *stream);
+/* out[0..n] = exclusive prefix sums of in[0..n) (out[n] = total);
+ * scratch: b200amg_scan_scratch_elems(n) elements of the output type */
+int b200amg_exclusive_scan_i64(long long n, const long long *in, long long *out, long long *scratch,
+                               void *stream);
+int b200amg_exclusive_scan_i32(long long n, const int *in, int *out, int *scratch, void *stream);
+long long b200amg_scan_scratch_elems(long long n);
+/* B = A^T in CSR; every row of B ascending in the original row index (like csr_tocsc).
+ * work: b200amg_csr_transpose_work_bytes(...) bytes.  Synchronises the stream once. */
+long long b200amg_csr_transpose_work_bytes(int n_row, int n_col, long long nnz);
+int b200amg_csr_transpose(int n_row, int n_col, long long nnz, const int *Ap, const int *Aj,
+                          const double *Ax, int *Bp, int *Bi, double *Bx, void *work, void *stream);
+
+/* ---- whole-cycle engine: multilevel_solver.__solve, pyamg/multilevel.py:473-548 ------- */
+typedef struct b200amg_level_desc {
+    /* A: CSR (bs == 1) or BSR with bs x bs blocks; flavor 0: CSR arithmetic
+     * (amg_core.jacobi / gauss_seidel*), 1: BSR arithmetic (amg_core.bsr_*), which differs in
+     * association even for bs == 1 (relaxation.h:216-238 vs :313-350). */
+    int n;            /* scalar unknowns on this level */
+    int bs;           /* block size of A */
+    int flavor;
+    const int *Ap, *Aj; const double *Ax;
+    /* P: (n x nc) and R: (nc x n), stored CSR or BSR(pr x pc) */
+    int nc;
+    int p_br, p_bc;   /* P block shape (R has the transposed shape) */
+    const int *Pp, *Pj; const double *Px;
+    const int *Rp, *Rj; const double *Rx;
+    /* smoothers: kind 0 none, 1 jacobi(omega, iterations), 2 gauss_seidel_indexed over
+     * colour-grouped rows (Id, color_ptr on HOST), sweep 0 fwd / 1 bwd / 2 symmetric */
+    int pre_kind, post_kind;
+    double pre_omega, post_omega;
+    int pre_iters, post_iters;
+    int pre_sweep, post_sweep;
+    const int *Id;              /* device: rows (block rows if bs>1) grouped by colour */
+    const int *color_ptr_host;  /* host: K+1 offsets */
+    int K;
+} b200amg_level_desc;
+
+/* Build a cycle engine over nlev-1 described levels + the dense coarse operator
+ * (coarse_inv: nc_last x nc_last row-major pseudo-inverse on the device, or NULL when the
+ * coarsest matrix has no entries -> zero correction, multilevel.py:699-701).
+ * work: device scratch of b200amg_vcycle_work_bytes(...) bytes. */
+long long b200amg_vcycle_work_bytes(int nlev, const b200amg_level_desc *levels_host);
+int b200amg_vcycle_create(int nlev, const b200amg_level_desc *levels_host, const double *coarse_inv,
+                          void *work, long long work_bytes, void **handle_out);
+/* one cycle: x <- cycle(x, b); cycle_kind 0 = V, 1 = W, 2 = F.  use_graph != 0 replays a CUDA
+ * graph captured on first use for these (x, b) pointers. */
+int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph,
+                       void *stream);
+/* rnorm2_dev[0] = ||b - A0 x||^2 on the finest level (residual_norm of multilevel.py:450,461) */
+int b200amg_vcycle_residual_norm2(void *handle, const double *x, const double *b,
+                                  double *rnorm2_dev, void *stream);
+int b200amg_vcycle_destroy(void *handle);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AMG_H */

@@ -1,0 +1,164 @@
+// extern "C" entry points of libb200amg.so for the stand-alone kernels (include/b200amg.h).
+#include "internal.cuh"
+
+using namespace b200amg;
+
+static inline cudaStream_t S(void *s) { return reinterpret_cast<cudaStream_t>(s); }
+
+extern "C" const char *b200amg_last_error(void) { return g_err; }
+extern "C" int b200amg_version(void) { return 100; }
+extern "C" long long b200amg_launch_count(void) { return g_launches; }
+
+extern "C" int b200amg_csr_matvec(int n_row, int n_col, const int *Ap, const int *Aj, const double *Ax,
+                                  const double *x, double *y, void *stream)
+{
+    if (n_row < 0 || n_col < 0) return set_err(B200AMG_EINVAL, "csr_matvec: negative size");
+    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    return stream_op(OP_MATVEC, a, S(stream));
+}
+
+extern "C" int b200amg_csr_spmv(int n_row, int n_col, const int *Ap, const int *Aj, const double *Ax,
+                                const double *x, double *y, double alpha, double beta, void *stream)
+{
+    if (n_row < 0 || n_col < 0) return set_err(B200AMG_EINVAL, "csr_spmv: negative size");
+    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nullptr, 0, n_row, alpha, beta, 0.0};
+    return stream_op(OP_SPMV_AB, a, S(stream));
+}
+
+extern "C" int b200amg_csr_residual(int n_row, const int *Ap, const int *Aj, const double *Ax, const double *x,
+                                    const double *b, double *r, void *stream)
+{
+    if (n_row < 0) return set_err(B200AMG_EINVAL, "csr_residual: negative size");
+    StreamArgs a{Ap, Aj, Ax, x, b, r, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    return stream_op(OP_RESIDUAL, a, S(stream));
+}
+
+extern "C" int b200amg_csr_matvec_add(int n_row, const int *Ap, const int *Aj, const double *Ax, const double *xc,
+                                      double *x, void *stream)
+{
+    if (n_row < 0) return set_err(B200AMG_EINVAL, "csr_matvec_add: negative size");
+    StreamArgs a{Ap, Aj, Ax, xc, nullptr, x, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    return stream_op(OP_ADD, a, S(stream));
+}
+
+extern "C" int b200amg_bsr_matvec(int n_brow, int n_bcol, int R, int C, const int *Ap, const int *Aj,
+                                  const double *Ax, const double *x, const double *b, double *y, int mode,
+                                  void *stream)
+{
+    if (n_brow < 0 || n_bcol < 0 || mode < 0 || mode > 2) return set_err(B200AMG_EINVAL, "bsr_matvec: bad arguments");
+    if (R == 1 && C == 1) {   // scipy routes 1x1 blocks through csr_matvec
+        StreamArgs a{Ap, Aj, Ax, x, b, y, nullptr, 0, n_brow, 1.0, 0.0, 0.0};
+        return stream_op(mode == 0 ? OP_MATVEC : (mode == 1 ? OP_RESIDUAL : OP_ADD), a, S(stream));
+    }
+    return bsr_matvec(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode, S(stream));
+}
+
+extern "C" int b200amg_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b, double *temp,
+                              int row_start, int row_stop, int row_step, double omega, void *stream)
+{
+    if (row_step != 1 || row_start < 0 || row_stop < row_start)
+        return set_err(B200AMG_EINVAL, "jacobi: only forward contiguous ranges (row_step == 1)");
+    if (row_stop == row_start) return 0;
+    // temp <- x on the swept range (relaxation.h:213-215), then x <- f(temp)
+    B200_CUDA(cudaMemcpyAsync(temp + row_start, x + row_start, sizeof(double) * (row_stop - row_start),
+                              cudaMemcpyDeviceToDevice, S(stream)));
+    StreamArgs a{Ap, Aj, Ax, temp, b, x, nullptr, row_start, row_stop, 1.0, 0.0, omega};
+    return stream_op(OP_JACOBI, a, S(stream));
+}
+
+extern "C" int b200amg_bsr_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                                  double *temp, int row_start, int row_stop, int row_step, int blocksize,
+                                  double omega, void *stream)
+{
+    if (row_step != 1 || row_start < 0 || row_stop < row_start)
+        return set_err(B200AMG_EINVAL, "bsr_jacobi: only forward contiguous ranges (row_step == 1)");
+    if (blocksize < 1 || blocksize > 8) return set_err(B200AMG_EINVAL, "bsr_jacobi: blocksize must be in 1..8");
+    if (row_stop == row_start) return 0;
+    // the reference copies the LEADING |row_stop-row_start|*bs entries (relaxation.h:301-303)
+    const size_t ncopy = (size_t)(row_stop - row_start) * blocksize;
+    B200_CUDA(cudaMemcpyAsync(temp, x, sizeof(double) * ncopy, cudaMemcpyDeviceToDevice, S(stream)));
+    if (blocksize == 1) {
+        StreamArgs a{Ap, Aj, Ax, temp, b, x, nullptr, row_start, row_stop, 1.0, 0.0, omega};
+        return stream_op(OP_JACOBI_BSR1, a, S(stream));
+    }
+    return bsr_jacobi(blocksize, row_start, row_stop, Ap, Aj, Ax, temp, x, b, omega, S(stream));
+}
+
+static int colour_loop(int row_start, int row_stop, int row_step, const int *cp, int K, int *c_first, int *c_last)
+{
+    // the sweep must cover whole colours: positions [cp[0], cp[K]) forward or backward
+    if (row_step == 1 && row_start == cp[0] && row_stop == cp[K]) { *c_first = 0; *c_last = K; return 1; }
+    if (row_step == -1 && row_start == cp[K] - 1 && row_stop == cp[0] - 1) { *c_first = K - 1; *c_last = -1; return -1; }
+    return 0;
+}
+
+extern "C" int b200amg_gauss_seidel_indexed(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                                            const int *Id, int row_start, int row_stop, int row_step,
+                                            const int *color_ptr_host, int K, void *stream)
+{
+    if (row_step == 0) return set_err(B200AMG_EINVAL, "gauss_seidel_indexed: row_step == 0");
+    if (!color_ptr_host) return gs_sequential(false, Ap, Aj, Ax, x, b, Id, row_start, row_stop, row_step, S(stream));
+    int c0, c1;
+    const int dir = colour_loop(row_start, row_stop, row_step, color_ptr_host, K, &c0, &c1);
+    if (!dir) return set_err(B200AMG_EINVAL, "gauss_seidel_indexed: sweep range must cover whole colours");
+    for (int c = c0; c != c1; c += dir)
+        B200_TRY(gs_rows(false, Ap, Aj, Ax, x, b, Id, color_ptr_host[c], color_ptr_host[c + 1], S(stream)));
+    return 0;
+}
+
+extern "C" int b200amg_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                                    int row_start, int row_stop, int row_step, void *stream)
+{
+    if (row_step == 0) return set_err(B200AMG_EINVAL, "gauss_seidel: row_step == 0");
+    return gs_sequential(false, Ap, Aj, Ax, x, b, nullptr, row_start, row_stop, row_step, S(stream));
+}
+
+extern "C" int b200amg_bsr_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                                        int row_start, int row_stop, int row_step, int blocksize, const int *Id,
+                                        const int *color_ptr_host, int K, void *stream)
+{
+    if (row_step == 0) return set_err(B200AMG_EINVAL, "bsr_gauss_seidel: row_step == 0");
+    if (blocksize < 1 || blocksize > 8) return set_err(B200AMG_EINVAL, "bsr_gauss_seidel: blocksize must be in 1..8");
+    if (!color_ptr_host) {
+        if (blocksize == 1) return gs_sequential(true, Ap, Aj, Ax, x, b, Id, row_start, row_stop, row_step, S(stream));
+        return bsr_gs_sequential(blocksize, Ap, Aj, Ax, x, b, Id, row_start, row_stop, row_step, S(stream));
+    }
+    if (!Id) return set_err(B200AMG_EINVAL, "bsr_gauss_seidel: colour pointer without an index list");
+    int c0, c1;
+    const int dir = colour_loop(row_start, row_stop, row_step, color_ptr_host, K, &c0, &c1);
+    if (!dir) return set_err(B200AMG_EINVAL, "bsr_gauss_seidel: sweep range must cover whole colours");
+    for (int c = c0; c != c1; c += dir) {
+        const int p0 = color_ptr_host[c], p1 = color_ptr_host[c + 1];
+        if (blocksize == 1) B200_TRY(gs_rows(true, Ap, Aj, Ax, x, b, Id, p0, p1, S(stream)));
+        else B200_TRY(bsr_gs_color(blocksize, Ap, Aj, Ax, x, b, Id, p0, p1, dir < 0, S(stream)));
+    }
+    return 0;
+}
+
+extern "C" int b200amg_dot(long long n, const double *x, const double *y, double *out_dev, double *work, void *stream)
+{
+    return dot(n, x, y, out_dev, work, S(stream));
+}
+
+extern "C" int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream)
+{
+    return axpy(n, a, x, y, S(stream));
+}
+
+extern "C" int b200amg_scale_diag(long long n, double omega, const double *b, const double *diag, double *x,
+                                  int bsr_flavor, void *stream)
+{
+    return scale_diag(n, omega, b, diag, x, bsr_flavor, S(stream));
+}
+
+extern "C" int b200amg_extract_diag(int n_brow, int blocksize, const int *Ap, const int *Aj, const double *Ax,
+                                    double *diag, void *stream)
+{
+    if (blocksize < 1) return set_err(B200AMG_EINVAL, "extract_diag: blocksize < 1");
+    return extract_diag(n_brow, blocksize, Ap, Aj, Ax, diag, S(stream));
+}
+
+extern "C" int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, void *stream)
+{
+    return dense_matvec(n, M, x, y, S(stream));
+}

@@ -1,0 +1,185 @@
+// BSR kernels (R x C row-major blocks, 1..8): scipy bsr_matvec and the reference's
+// amg_core.bsr_jacobi / bsr_gauss_seidel (pyamg/amg_core/relaxation.h:89-173, :267-360,
+// dense block product = linalg.h:359-398 'gemm' started from zero).
+// Arithmetic order is the reference's: per off-diagonal block loc = ((0+a0 x0)+a1 x1)+...,
+// acc -= loc; then the point sweep inside the diagonal block.
+#include "internal.cuh"
+
+namespace b200amg {
+
+// one thread per scalar output row (i*R + r)
+__global__ void __launch_bounds__(256) bsr_matvec_kernel(int n_brow, int R, int C, const int *__restrict__ Ap,
+                                                         const int *__restrict__ Aj, const double *__restrict__ Ax,
+                                                         const double *__restrict__ x, const double *__restrict__ b,
+                                                         double *y, int mode)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= (long long)n_brow * R) return;
+    const int i = (int)(g / R), r = (int)(g - (long long)i * R);
+    double acc = 0.0;
+    const int hi = Ap[i + 1];
+    for (int p = Ap[i]; p < hi; ++p) {
+        const double *blk = Ax + ((size_t)p * R + r) * C;
+        const double *xb = x + (size_t)Aj[p] * C;
+        for (int c = 0; c < C; ++c) acc = add_rn(acc, mul_rn(blk[c], xb[c]));
+    }
+    if (mode == 0) y[g] = acc;
+    else if (mode == 1) y[g] = sub_rn(b[g], acc);
+    else y[g] = add_rn(y[g], acc);
+}
+
+// amg_core.bsr_jacobi, forward full range: thread per scalar row (i, k); reads xin, writes xout
+template <int BS>
+__global__ void __launch_bounds__(256) bsr_jacobi_kernel(int nb0, int nb1, const int *__restrict__ Ap,
+                                                         const int *__restrict__ Aj, const double *__restrict__ Ax,
+                                                         const double *__restrict__ xin, double *__restrict__ xout,
+                                                         const double *__restrict__ b, double omega)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= (long long)(nb1 - nb0) * BS) return;
+    const int i = nb0 + (int)(g / BS), k = (int)(g % BS);
+    const size_t row = (size_t)i * BS + k;
+    double acc = b[row];
+    long long dptr = -1;
+    const int hi = Ap[i + 1];
+    for (int p = Ap[i]; p < hi; ++p) {
+        const int j = Aj[p];
+        if (j == i) { dptr = p; continue; }
+        const double *blk = Ax + ((size_t)p * BS + k) * BS;
+        const double *xb = xin + (size_t)j * BS;
+        double loc = 0.0;
+#pragma unroll
+        for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[c], xb[c]));
+        acc = sub_rn(acc, loc);
+    }
+    const double xi = xin[row];
+    if (dptr < 0) { xout[row] = xi; return; }
+    const double *D = Ax + ((size_t)dptr * BS + k) * BS;
+    double d = 1.0;
+#pragma unroll
+    for (int kk = 0; kk < BS; ++kk) {
+        if (kk == k) d = D[kk];
+        else acc = sub_rn(acc, mul_rn(D[kk], xin[(size_t)i * BS + kk]));
+    }
+    xout[row] = (d != 0.0) ? add_rn(mul_rn(sub_rn(1.0, omega), xi), div_rn(mul_rn(omega, acc), d)) : xi;
+}
+
+// amg_core.bsr_gauss_seidel for one block row (all of it by one thread: the point sweep inside
+// the diagonal block is sequential in k).
+template <int BS>
+__device__ __forceinline__ void bsr_gs_block_row(int i, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                 const double *__restrict__ Ax, double *x,
+                                                 const double *__restrict__ b, bool backward)
+{
+    double acc[BS];
+#pragma unroll
+    for (int k = 0; k < BS; ++k) acc[k] = b[(size_t)i * BS + k];
+    long long dptr = -1;
+    const int hi = Ap[i + 1];
+    for (int p = Ap[i]; p < hi; ++p) {
+        const int j = Aj[p];
+        if (j == i) { dptr = p; continue; }
+        const double *blk = Ax + (size_t)p * BS * BS;
+        double xv[BS];
+#pragma unroll
+        for (int c = 0; c < BS; ++c) xv[c] = x[(size_t)j * BS + c];
+#pragma unroll
+        for (int k = 0; k < BS; ++k) {
+            double loc = 0.0;
+#pragma unroll
+            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[k * BS + c], xv[c]));
+            acc[k] = sub_rn(acc[k], loc);
+        }
+    }
+    if (dptr < 0) return;
+    const double *D = Ax + (size_t)dptr * BS * BS;
+    double xl[BS];
+#pragma unroll
+    for (int k = 0; k < BS; ++k) xl[k] = x[(size_t)i * BS + k];
+#pragma unroll
+    for (int kq = 0; kq < BS; ++kq) {
+        const int k = backward ? BS - 1 - kq : kq;
+        double d = 1.0, a = acc[k];
+#pragma unroll
+        for (int cq = 0; cq < BS; ++cq) {
+            const int kk = backward ? BS - 1 - cq : cq;
+            if (kk == k) d = D[k * BS + kk];
+            else a = sub_rn(a, mul_rn(D[k * BS + kk], xl[kk]));
+        }
+        if (d != 0.0) { xl[k] = div_rn(a, d); x[(size_t)i * BS + k] = xl[k]; }
+    }
+}
+
+template <int BS>
+__global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                           const double *__restrict__ Ax, double *x,
+                                                           const double *__restrict__ b, const int *__restrict__ Id,
+                                                           int p0, int p1, bool backward)
+{
+    const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= p1) return;
+    bsr_gs_block_row<BS>(Id[p], Ap, Aj, Ax, x, b, backward);
+}
+
+template <int BS>
+__global__ void bsr_gs_sequential_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                         const double *__restrict__ Ax, double *x, const double *__restrict__ b,
+                                         const int *Id, int start, int stop, int step)
+{
+    for (int p = start; p != stop; p += step) {
+        bsr_gs_block_row<BS>(Id ? Id[p] : p, Ap, Aj, Ax, x, b, step < 0);
+        __threadfence_block();
+    }
+}
+
+#define BS_SWITCH(bs, CALL)                                                   \
+    switch (bs) {                                                             \
+    case 1: { constexpr int BS = 1; CALL; } break;                            \
+    case 2: { constexpr int BS = 2; CALL; } break;                            \
+    case 3: { constexpr int BS = 3; CALL; } break;                            \
+    case 4: { constexpr int BS = 4; CALL; } break;                            \
+    case 5: { constexpr int BS = 5; CALL; } break;                            \
+    case 6: { constexpr int BS = 6; CALL; } break;                            \
+    case 7: { constexpr int BS = 7; CALL; } break;                            \
+    case 8: { constexpr int BS = 8; CALL; } break;                            \
+    default: return set_err(B200AMG_EINVAL, "blocksize must be in 1..8");     \
+    }
+
+int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax, const double *x,
+               const double *b, double *y, int mode, cudaStream_t st)
+{
+    if (R < 1 || C < 1 || R > 8 || C > 8) return set_err(B200AMG_EINVAL, "bsr_matvec: block shape must be in 1..8");
+    const long long n = (long long)n_brow * R;
+    if (n <= 0) return 0;
+    bsr_matvec_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
+    return check_launch("bsr_matvec_kernel");
+}
+
+int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const double *Ax, const double *xin,
+               double *xout, const double *b, double omega, cudaStream_t st)
+{
+    const long long n = (long long)(nb1 - nb0) * bs;
+    if (n <= 0) return 0;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    BS_SWITCH(bs, (bsr_jacobi_kernel<BS><<<grid, 256, 0, st>>>(nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega)));
+    return check_launch("bsr_jacobi_kernel");
+}
+
+int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st)
+{
+    if (p1 <= p0) return 0;
+    const unsigned grid = (unsigned)((p1 - p0 + 127) / 128);
+    BS_SWITCH(bs, (bsr_gs_color_kernel<BS><<<grid, 128, 0, st>>>(Ap, Aj, Ax, x, b, Id, p0, p1, backward)));
+    return check_launch("bsr_gs_color_kernel");
+}
+
+int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                      const int *Id, int start, int stop, int step, cudaStream_t st)
+{
+    if (start == stop) return 0;
+    BS_SWITCH(bs, (bsr_gs_sequential_kernel<BS><<<1, 1, 0, st>>>(Ap, Aj, Ax, x, b, Id, start, stop, step)));
+    return check_launch("bsr_gs_sequential_kernel");
+}
+
+}  // namespace b200amg

@@ -1,0 +1,43 @@
+// Cross-file declarations inside libb200amg.
+#pragma once
+#include "common.cuh"
+
+namespace b200amg {
+
+enum : int {
+    OP_MATVEC = 0, OP_SPMV_AB, OP_RESIDUAL, OP_ADD, OP_JACOBI, OP_JACOBI_BSR1, OP_GS, OP_GS_BSR1
+};
+
+struct StreamArgs {
+    const int *Ap, *Aj;
+    const double *Ax;
+    const double *x;
+    const double *b;
+    double *y;
+    const int *map;
+    int row_begin, row_end;
+    double alpha, beta, omega;
+};
+
+int stream_op(int op, const StreamArgs &a, cudaStream_t st);
+int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+            const int *Id, int p0, int p1, cudaStream_t st);
+int gs_sequential(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                  const int *Id, int start, int stop, int step, cudaStream_t st);
+
+int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax, const double *x,
+               const double *b, double *y, int mode, cudaStream_t st);
+int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const double *Ax, const double *xin,
+               double *xout, const double *b, double omega, cudaStream_t st);
+int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st);
+int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                      const int *Id, int start, int stop, int step, cudaStream_t st);
+
+int dot(long long n, const double *x, const double *y, double *out, double *work, cudaStream_t st);
+int axpy(long long n, double a, const double *x, double *y, cudaStream_t st);
+int extract_diag(int nb, int bs, const int *Ap, const int *Aj, const double *Ax, double *diag, cudaStream_t st);
+int scale_diag(long long n, double omega, const double *b, const double *d, double *x, int bsrf, cudaStream_t st);
+int dense_matvec(int n, const double *M, const double *x, double *y, cudaStream_t st);
+
+}  // namespace b200amg

@@ -1,0 +1,251 @@
+// Whole-cycle engine: multilevel_solver.__solve (pyamg/multilevel.py:473-548) as a fixed
+// sequence of kernel launches over caller-owned level arrays, replayed as a CUDA graph.
+//
+//   presmooth -> r = b - A x -> b_c = R r -> recurse / dense coarse solve -> x += P x_c -> postsmooth
+//
+// Level vectors (r, b_c, x_c, Jacobi ping-pong buffer, extracted diagonal) live in one
+// caller-provided work buffer.  Jacobi sweeps ping-pong between x and the spare buffer instead
+// of the reference's temp copy (same values); a pre-smoothing Jacobi sweep from the zero
+// initial guess of a coarse level is the bit-identical diagonal scaling (blas1.cu).
+#include <vector>
+#include "internal.cuh"
+
+namespace b200amg {
+
+struct LevelRt {
+    b200amg_level_desc d;
+    double *r, *bc, *xc, *tmp, *diag;
+    std::vector<int> color_ptr;
+};
+
+struct GraphKey {
+    double *x; const double *b; int kind;
+    cudaGraphExec_t exec;
+    long long launches;   // kernel nodes in the graph (for b200amg_launch_count)
+};
+
+struct Engine {
+    std::vector<LevelRt> lev;
+    const double *coarse_inv;
+    int nc_last;
+    double *dot_work, *r0;
+    std::vector<GraphKey> graphs;
+    bool diag_ready;
+};
+
+static size_t al(size_t n_doubles) { return (n_doubles + 31) & ~(size_t)31; }
+
+long long work_doubles(int nlev, const b200amg_level_desc *L)
+{
+    size_t tot = al(1024) ;
+    for (int k = 0; k < nlev - 1; ++k)
+        tot += al(L[k].n) * 3 /* r, tmp, diag */ + al(L[k].nc) * 2 /* bc, xc */;
+    return (long long)tot;
+}
+
+// ---- level operators ---------------------------------------------------------------------
+static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *x, const double *b, double *y,
+                   cudaStream_t st)
+{
+    const b200amg_level_desc &d = L.d;
+    if (d.bs == 1) {
+        StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, nullptr, 0, d.n, 1.0, 0.0, 0.0};
+        return stream_op(op_scalar, a, st);
+    }
+    return bsr_matvec(d.n / d.bs, d.bs, d.bs, d.Ap, d.Aj, d.Ax, x, b, y, bsr_mode, st);
+}
+
+static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_t st)
+{
+    const b200amg_level_desc &d = L.d;
+    if (d.p_br == 1 && d.p_bc == 1) {
+        StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, nullptr, 0, d.nc, 1.0, 0.0, 0.0};
+        return stream_op(OP_MATVEC, a, st);
+    }
+    return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st);
+}
+
+static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream_t st)
+{
+    const b200amg_level_desc &d = L.d;
+    if (d.p_br == 1 && d.p_bc == 1) {
+        StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, nullptr, 0, d.n, 1.0, 0.0, 0.0};
+        return stream_op(OP_ADD, a, st);
+    }
+    return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, nullptr, x, 2, st);
+}
+
+// one smoothing stage; *cur is the buffer holding the iterate (x or the spare), swapped by Jacobi
+static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep, double **cur, double **spare,
+                  const double *b, bool x_is_zero, cudaStream_t st)
+{
+    const b200amg_level_desc &d = L.d;
+    if (kind == 0) {
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        return 0;
+    }
+    if (kind == 1) {                                   // Jacobi
+        for (int it = 0; it < iters; ++it) {
+            if (it == 0 && x_is_zero && d.bs == 1) {
+                B200_TRY(scale_diag(d.n, omega, b, L.diag, *cur, d.flavor, st));
+                continue;
+            }
+            if (it == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+            if (d.bs == 1) {
+                StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, nullptr, 0, d.n, 1.0, 0.0, omega};
+                B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
+            } else {
+                B200_TRY(bsr_jacobi(d.bs, 0, d.n / d.bs, d.Ap, d.Aj, d.Ax, *cur, *spare, b, omega, st));
+            }
+            double *t = *cur; *cur = *spare; *spare = t;
+        }
+        if (iters == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        return 0;
+    }
+    if (kind == 2) {                                   // colour-ordered Gauss-Seidel (indexed)
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        const int K = d.K;
+        for (int it = 0; it < iters; ++it) {
+            for (int pass = 0; pass < 2; ++pass) {
+                const bool bwd = (pass == 1);
+                if ((sweep == 0 && bwd) || (sweep == 1 && !bwd)) continue;
+                for (int q = 0; q < K; ++q) {
+                    const int c = bwd ? K - 1 - q : q;
+                    const int p0 = L.color_ptr[c], p1 = L.color_ptr[c + 1];
+                    if (d.bs == 1)
+                        B200_TRY(gs_rows(d.flavor != 0, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
+                    else
+                        B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st));
+                }
+            }
+        }
+        return 0;
+    }
+    return set_err(B200AMG_EINVAL, "smooth: unknown smoother kind");
+}
+
+static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_is_zero, cudaStream_t st)
+{
+    LevelRt &L = E.lev[k];
+    const b200amg_level_desc &d = L.d;
+    const int nlev = (int)E.lev.size() + 1;
+    double *cur = x, *spare = L.tmp;
+    B200_TRY(smooth(L, d.pre_kind, d.pre_omega, d.pre_iters, d.pre_sweep, &cur, &spare, b, x_is_zero, st));
+    B200_TRY(apply_A(L, OP_RESIDUAL, 1, cur, b, L.r, st));
+    B200_TRY(restrict_r(L, L.r, L.bc, st));
+    if (k == nlev - 2) {
+        if (E.coarse_inv) B200_TRY(dense_matvec(d.nc, E.coarse_inv, L.bc, L.xc, st));
+        else B200_CUDA(cudaMemsetAsync(L.xc, 0, sizeof(double) * d.nc, st));
+    } else if (kind == 0) {
+        B200_TRY(cycle(E, k + 1, L.xc, L.bc, 0, true, st));
+    } else if (kind == 1) {
+        B200_TRY(cycle(E, k + 1, L.xc, L.bc, 1, true, st));
+        B200_TRY(cycle(E, k + 1, L.xc, L.bc, 1, false, st));
+    } else {
+        B200_TRY(cycle(E, k + 1, L.xc, L.bc, 2, true, st));
+        B200_TRY(cycle(E, k + 1, L.xc, L.bc, 0, false, st));
+    }
+    B200_TRY(prolong_add(L, L.xc, cur, st));
+    B200_TRY(smooth(L, d.post_kind, d.post_omega, d.post_iters, d.post_sweep, &cur, &spare, b, false, st));
+    if (cur != x) B200_CUDA(cudaMemcpyAsync(x, cur, sizeof(double) * d.n, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+static int ensure_diag(Engine &E, cudaStream_t st)
+{
+    if (E.diag_ready) return 0;
+    for (auto &L : E.lev)
+        B200_TRY(extract_diag(L.d.n / L.d.bs, L.d.bs, L.d.Ap, L.d.Aj, L.d.Ax, L.diag, st));
+    E.diag_ready = true;
+    return 0;
+}
+
+}  // namespace b200amg
+
+using namespace b200amg;
+
+extern "C" long long b200amg_vcycle_work_bytes(int nlev, const b200amg_level_desc *levels_host)
+{
+    if (nlev < 1 || !levels_host) return B200AMG_EINVAL;
+    return work_doubles(nlev, levels_host) * (long long)sizeof(double);
+}
+
+extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, const double *coarse_inv, void *work,
+                                     long long work_bytes, void **handle_out)
+{
+    if (nlev < 2 || !Ld || !handle_out) return set_err(B200AMG_EINVAL, "vcycle_create: need >= 2 levels");
+    if (work_bytes < b200amg_vcycle_work_bytes(nlev, Ld)) return set_err(B200AMG_ENOMEM, "vcycle_create: work too small");
+    Engine *E = new Engine();
+    double *w = reinterpret_cast<double *>(work);
+    E->dot_work = w; w += al(1024);
+    E->coarse_inv = coarse_inv;
+    E->diag_ready = false;
+    for (int k = 0; k < nlev - 1; ++k) {
+        LevelRt L;
+        L.d = Ld[k];
+        if (L.d.bs < 1 || L.d.bs > 8 || L.d.n % L.d.bs) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: bad blocksize"); }
+        L.r = w; w += al(L.d.n);
+        L.tmp = w; w += al(L.d.n);
+        L.diag = w; w += al(L.d.n);
+        L.bc = w; w += al(L.d.nc);
+        L.xc = w; w += al(L.d.nc);
+        if (L.d.pre_kind == 2 || L.d.post_kind == 2) {
+            if (!L.d.color_ptr_host || !L.d.Id || L.d.K < 0) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: colour ordering missing"); }
+            L.color_ptr.assign(L.d.color_ptr_host, L.d.color_ptr_host + L.d.K + 1);
+            L.d.color_ptr_host = nullptr;
+        }
+        E->lev.push_back(L);
+    }
+    E->nc_last = Ld[nlev - 2].nc;
+    E->r0 = E->lev[0].r;
+    *handle_out = E;
+    return 0;
+}
+
+extern "C" int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph, void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || cycle_kind < 0 || cycle_kind > 2) return set_err(B200AMG_EINVAL, "vcycle_run: bad arguments");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    B200_TRY(ensure_diag(*E, st));
+    if (!use_graph || st == nullptr) return cycle(*E, 0, x, b, cycle_kind, false, st);
+    for (auto &g : E->graphs)
+        if (g.x == x && g.b == b && g.kind == cycle_kind) {
+            B200_CUDA(cudaGraphLaunch(g.exec, st));
+            g_launches += g.launches;
+            return 0;
+        }
+    cudaGraph_t graph;
+    const long long before = g_launches;
+    B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    int rc = cycle(*E, 0, x, b, cycle_kind, false, st);
+    cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    if (rc) return rc;
+    if (ce != cudaSuccess) return set_err((int)ce, "vcycle_run: stream capture failed");
+    GraphKey key{x, b, cycle_kind, nullptr, g_launches - before};
+    B200_CUDA(cudaGraphInstantiate(&key.exec, graph, 0));
+    B200_CUDA(cudaGraphDestroy(graph));
+    if (E->graphs.size() >= 8) { cudaGraphExecDestroy(E->graphs.front().exec); E->graphs.erase(E->graphs.begin()); }
+    E->graphs.push_back(key);
+    B200_CUDA(cudaGraphLaunch(key.exec, st));
+    return 0;
+}
+
+extern "C" int b200amg_vcycle_residual_norm2(void *handle, const double *x, const double *b, double *out, void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E) return set_err(B200AMG_EINVAL, "vcycle_residual_norm2: null handle");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    LevelRt &L = E->lev[0];
+    B200_TRY(apply_A(L, OP_RESIDUAL, 1, x, b, L.r, st));
+    return dot(L.d.n, L.r, L.r, out, E->dot_work, st);
+}
+
+extern "C" int b200amg_vcycle_destroy(void *handle)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E) return 0;
+    for (auto &g : E->graphs) cudaGraphExecDestroy(g.exec);
+    delete E;
+    return 0;
+}
