@@ -136,6 +136,34 @@ long long b200amg_csr_transpose_work_bytes(int n_row, int n_col, long long nnz);
 int b200amg_csr_transpose(int n_row, int n_col, long long nnz, const int *Ap, const int *Aj,
                           const double *Ax, int *Bp, int *Bi, double *Bx, void *work, void *stream);
 
+/* ---- scalar smoothed-aggregation prolongator pieces (setup; bit-identical op order) ------- */
+/* out[k] = (Ax[k] * v[row]) [* c]: scipy csr_scale_rows (pyamg/util/utils.py:133-200) followed
+ * by the scalar factor of pyamg/aggregation/smooth.py:164 when use_c != 0 */
+int b200amg_csr_scale_rows(int n_row, const int *Ap, const double *Ax, const double *v, double c,
+                           int use_c, double *out, void *stream);
+/* amg_core.fit_candidates for ONE candidate and scalar unknowns (smoothed_aggregation.h:322-448):
+ * (Mp, Mi, Mb) = members of each aggregate (ascending node, candidate value);
+ * Bc[j] = ||b_j||, node_val[i] = b_i / ||b_agg(i)|| */
+int b200amg_tentative_scalar(int n_agg, const int *Mp, const int *Mi, const double *Mb, double tol,
+                             double *Bc, double *node_val, void *stream);
+int b200amg_flag_nonneg(int n, const int *agg, int *flag, void *stream);
+int b200amg_tentative_fill(int n, const int *agg, const double *node_val, const int *Tp, int *Tj,
+                           double *Tx, void *stream);
+/* C = A - B for sorted duplicate-free CSR rows, zero results not stored (scipy csr_binop_csr);
+ * pass 0 writes cnt[i]; pass 1 fills Cj/Cx at Cp[i] */
+int b200amg_csr_sub_sorted(int n_row, const int *Ap, const int *Aj, const double *Ax, const int *Bp,
+                           const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
+                           int *Cj, double *Cx, void *stream);
+
+/* ---- host-side, inherently sequential setup steps whose INTEGER result must be identical
+ *      to the reference (arrays are HOST pointers) ------------------------------------------ */
+/* amg_core.vertex_coloring_mis, pyamg/amg_core/graph.h:171-188: returns K, color[i] in [0,K) */
+int b200amg_vertex_coloring_mis_host(int n, const int *Ap_host, const int *Aj_host, int *color_host);
+/* amg_core.standard_aggregation, pyamg/amg_core/smoothed_aggregation.h:121-221: returns the
+ * number of aggregates; agg[i] = aggregate of node i or -1; roots[k] = seed node of k */
+int b200amg_standard_aggregation_host(int n, const int *Ap_host, const int *Aj_host, int *agg_host,
+                                      int *roots_host);
+
 /* ---- whole-cycle engine: multilevel_solver.__solve, pyamg/multilevel.py:473-548 ------- */
 typedef struct b200amg_level_desc {
     /* A: CSR (bs == 1) or BSR with bs x bs blocks; flavor 0: CSR arithmetic
@@ -151,7 +179,8 @@ typedef struct b200amg_level_desc {
     const int *Pp, *Pj; const double *Px;
     const int *Rp, *Rj; const double *Rx;
     /* smoothers: kind 0 none, 1 jacobi(omega, iterations), 2 gauss_seidel_indexed over
-     * colour-grouped rows (Id, color_ptr on HOST), sweep 0 fwd / 1 bwd / 2 symmetric */
+     * colour-grouped rows (Id, color_ptr on HOST), 3 lexicographic gauss_seidel (sequential on
+     * the device, exact); sweep 0 fwd / 1 bwd / 2 symmetric */
     int pre_kind, post_kind;
     double pre_omega, post_omega;
     int pre_iters, post_iters;

@@ -1,0 +1,186 @@
+"""smoothed_aggregation_solver on the device (pyamg/aggregation/aggregation.py:30-435) for the
+scalar path the BASELINE configs use: symmetric strength (theta = 0), standard aggregation,
+one near-nullspace candidate, Jacobi-smoothed prolongator, R = P^H, Galerkin A_c = R A P.
+
+Per level (extend_hierarchy, aggregation.py:293-435):
+  C      strength pattern; theta = 0 keeps every stored entry (smoothed_aggregation.h:48-99)
+  AggOp  amg_core.standard_aggregation -- sequential greedy, run on the HOST by
+         b200amg_standard_aggregation_host (identical integers), pattern copied D2H once
+  T, Bc  amg_core.fit_candidates, K1 = K2 = 1 (b200amg_tentative_scalar)
+  P      T - (omega/rho(D^-1 A)) D^-1 A T  (csr_scale_rows + SpGEMM + sorted subtract; smooth.py:160-206)
+  R      P^T (b200amg_csr_transpose)        A_c = (R A) P (b200amg_spgemm_*)
+Every floating-point step keeps the reference's operation order, so given the same rho the
+hierarchy equals the reference-built one to the bit; rho itself comes from a device Arnoldi run
+started from the same numpy random vector (agreement ~1e-15 relative).
+"""
+import numpy as np
+import torch
+
+from . import _lib, amg_core
+from .linalg import approximate_spectral_radius
+from .multilevel import multilevel_solver
+from .smoothing import change_smoothers
+from .sparse import DevMat, _dev, _ptr, _scan_i32, _stream, matmat, transpose
+
+
+def _unpack(v):
+    return (v[0], dict(v[1])) if isinstance(v, tuple) else (v, {})
+
+
+def sort_indices(A):
+    """rows ascending in column (scipy sort_indices; get_diagonal sorts level matrices in place,
+    pyamg/util/utils.py:571): a double transpose."""
+    if A.has_sorted_indices:
+        return A
+    S = transpose(transpose(A))
+    return DevMat(S.indptr, S.indices, S.data, A.shape, A.blocksize, A.format, True)
+
+
+def standard_aggregation(A):
+    """-> (agg int32 device tensor [n], n_agg, roots).  Pattern goes to the host once."""
+    n = A.shape[0]
+    Ap, Aj = A.indptr.cpu().numpy(), A.indices.cpu().numpy()
+    agg = np.empty(n, dtype=np.intc)
+    roots = np.empty(n, dtype=np.intc)
+    nagg = amg_core.standard_aggregation(n, Ap, Aj, agg, roots)
+    return torch.from_numpy(agg).to(_dev()), nagg, roots[:nagg]
+
+
+def _one_entry_rows(agg, vals, nagg):
+    """CSR (n x nagg) with entry (agg[i], vals[i]) on every row with agg[i] >= 0"""
+    n = agg.numel()
+    st = _stream()
+    flag = torch.empty(n, dtype=torch.int32, device=agg.device)
+    _lib.call('b200amg_flag_nonneg', n, _ptr(agg), _ptr(flag), st)
+    Tp = _scan_i32(flag)
+    nnz = int(Tp[-1].item())
+    Tj = torch.empty(nnz, dtype=torch.int32, device=agg.device)
+    Tx = torch.empty(nnz, dtype=torch.float64, device=agg.device)
+    _lib.call('b200amg_tentative_fill', n, _ptr(agg), _ptr(vals), _ptr(Tp), _ptr(Tj), _ptr(Tx), st)
+    return DevMat(Tp, Tj, Tx, (n, nagg), (1, 1), 'bsr', True)
+
+
+def fit_candidates_scalar(agg, nagg, B, tol=1e-10):
+    """tentative.py:19-166 for one candidate: -> (T as BSR(1,1) DevMat, coarse candidate Bc)"""
+    n = agg.numel()
+    AggB = _one_entry_rows(agg, B, nagg)
+    M = transpose(AggB)                                   # members of every aggregate, ascending
+    Bc = torch.empty(nagg, dtype=torch.float64, device=B.device)
+    node_val = torch.zeros(n, dtype=torch.float64, device=B.device)
+    _lib.call('b200amg_tentative_scalar', nagg, _ptr(M.indptr), _ptr(M.indices), _ptr(M.data), float(tol),
+              _ptr(Bc), _ptr(node_val), _stream())
+    return _one_entry_rows(agg, node_val, nagg), Bc
+
+
+def _scaled(A, v, c=None):
+    out = torch.empty_like(A.data)
+    _lib.call('b200amg_csr_scale_rows', A.shape[0], _ptr(A.indptr), _ptr(A.data), _ptr(v),
+              0.0 if c is None else float(c), 0 if c is None else 1, _ptr(out), _stream())
+    return DevMat(A.indptr, A.indices, out, A.shape, (1, 1), 'csr', A.has_sorted_indices)
+
+
+def csr_subtract(A, B):
+    """A - B, sorted operands, zero results dropped (scipy csr_binop_csr)"""
+    n = A.shape[0]
+    st = _stream()
+    cnt = torch.empty(max(n, 1), dtype=torch.int32, device=A.data.device)
+    args = (n, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr), _ptr(B.indices), _ptr(B.data))
+    _lib.call('b200amg_csr_sub_sorted', *args, 0, _ptr(cnt), 0, 0, 0, st)
+    Cp = _scan_i32(cnt[:n])
+    nnz = int(Cp[-1].item())
+    Cj = torch.empty(nnz, dtype=torch.int32, device=A.data.device)
+    Cx = torch.empty(nnz, dtype=torch.float64, device=A.data.device)
+    _lib.call('b200amg_csr_sub_sorted', *args, 1, 0, _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
+    return DevMat(Cp, Cj, Cx, A.shape, (1, 1), 'bsr', True)
+
+
+def inverse_diagonal(A):
+    d = A.diagonal()
+    return torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
+
+
+def jacobi_prolongation_smoother(A, T, omega=4.0 / 3.0, degree=1, rho=None):
+    """smooth.py:67-208, weighting='diagonal', filter=False -> (P, rho)"""
+    dinv = inverse_diagonal(A)
+    if rho is None:
+        rho = approximate_spectral_radius(_scaled(A, dinv))
+    S = _scaled(A, dinv, omega / rho)
+    P = T
+    for _ in range(degree):
+        P = csr_subtract(P, matmat(S, P))
+    return P, rho
+
+
+def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', strength='symmetric',
+                                aggregate='standard', smooth=('jacobi', {'omega': 4.0 / 3.0}),
+                                presmoother=('jacobi', {'omega': 4.0 / 3.0}),
+                                postsmoother=('jacobi', {'omega': 4.0 / 3.0}),
+                                improve_candidates=None, max_levels=10, max_coarse=500,
+                                diagonal_dominance=False, keep=False, rho_override=None, **kwargs):
+    """Same call as the reference's smoothed_aggregation_solver for the options that have a
+    device path; unsupported options raise (no CPU fallback).  Deviations from the reference
+    DEFAULTS, both because the reference default is a lexicographic (sequential) block
+    Gauss-Seidel: `presmoother/postsmoother` default to Jacobi(4/3) and `improve_candidates`
+    to None.  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
+    tests feed the reference's spectral-radius estimates."""
+    if symmetry not in ('hermitian', 'symmetric'):
+        raise NotImplementedError('only symmetric / hermitian problems have a device setup path')
+    if improve_candidates is not None and improve_candidates != [None] and improve_candidates != (None, {}):
+        raise NotImplementedError('improve_candidates must be None (the reference default is a sequential '
+                                  'block Gauss-Seidel on B)')
+    if diagonal_dominance:
+        raise NotImplementedError('diagonal_dominance filtering is not available on the device')
+    sname, skw = _unpack(strength)
+    if sname not in ('symmetric', None) or skw.get('theta', 0.0) != 0.0:
+        raise NotImplementedError("strength must be 'symmetric' with theta=0 (or None)")
+    if _unpack(aggregate)[0] != 'standard':
+        raise NotImplementedError("aggregate must be 'standard'")
+    mname, mkw = _unpack(smooth)
+    if mname not in ('jacobi', None) or set(mkw) - {'omega', 'degree'}:
+        raise NotImplementedError("smooth must be ('jacobi', {'omega', 'degree'}) or None")
+    if not isinstance(A, DevMat):
+        A = DevMat.from_scipy(A)
+    if not A.is_scalar:
+        raise NotImplementedError('block (BSR) problems: build the hierarchy with the reference and import it')
+    if A.shape[0] != A.shape[1]:
+        raise ValueError('expected square matrix')
+    dev = A.data.device
+    if B is None:
+        Bv = torch.ones(A.shape[0], dtype=torch.float64, device=dev)
+    else:
+        Bn = np.asarray(B.cpu().numpy() if isinstance(B, torch.Tensor) else B, dtype=np.float64)
+        if Bn.ndim == 2 and Bn.shape[1] != 1:
+            raise NotImplementedError('one near-nullspace candidate only')
+        if Bn.size != A.shape[0]:
+            raise ValueError('The near null-space modes B have incorrect dimensions for matrix A')
+        Bv = torch.from_numpy(np.ascontiguousarray(Bn.ravel())).to(dev)
+
+    levels = [multilevel_solver.level()]
+    levels[-1].A = A
+    levels[-1].B = Bv
+    while len(levels) < max_levels and levels[-1].A.shape[0] > max_coarse:
+        lvl = levels[-1]
+        k = len(levels) - 1
+        A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
+        agg, nagg, roots = standard_aggregation(A)
+        T, Bc = fit_candidates_scalar(agg, nagg, lvl.B)
+        if mname == 'jacobi':
+            rho = rho_override[k][0] if rho_override is not None and k < len(rho_override) else None
+            P, lvl.rho_smooth = jacobi_prolongation_smoother(A, T, mkw.get('omega', 4.0 / 3.0), mkw.get('degree', 1), rho)
+        else:
+            P = T
+        R = transpose(P)
+        if keep:
+            lvl.AggOp, lvl.T, lvl.Cpts = agg, T, roots
+        lvl.P, lvl.R = P, R
+        Ac = matmat(matmat(R, A), P)
+        levels.append(multilevel_solver.level())
+        levels[-1].A = DevMat(Ac.indptr, Ac.indices, Ac.data, Ac.shape, (1, 1), 'bsr', True)
+        levels[-1].B = Bc
+    if rho_override is not None:
+        for k, lvl in enumerate(levels[:-1]):
+            if k < len(rho_override) and rho_override[k][1] is not None:
+                lvl.A.rho_D_inv = rho_override[k][1]
+    ml = multilevel_solver(levels, **kwargs)
+    change_smoothers(ml, presmoother, postsmoother)
+    return ml

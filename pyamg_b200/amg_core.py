@@ -1,0 +1,111 @@
+"""`amg_core`-named entry points with the reference's POSITIONAL signatures
+(pyamg/amg_core/amg_core.i:163-194; C++ in pyamg/amg_core/relaxation.h, graph.h), taking
+device arrays (torch CUDA tensors: int32 indices, float64 values).  Like the SWIG
+INPLACE_ARRAY1 typemaps (amg_core.i:27-92) they refuse wrong dtypes (TypeError) and
+non-contiguous arrays (ValueError) instead of converting, mutate `x` / `temp` in place and
+return None.  Two optional trailing arguments extend gauss_seidel_indexed / bsr_gauss_seidel:
+`color_ptr` (host ints) declares colour groups inside `Id`, enabling the parallel sweep.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from .sparse import _stream
+
+
+def _chk(t, dtype, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError('%s: expected a torch CUDA tensor' % name)
+    if t.dtype != dtype:
+        raise TypeError('%s: expected dtype %s, got %s' % (name, dtype, t.dtype))
+    if t.device.type != 'cuda':
+        raise TypeError('%s: expected a CUDA tensor (no CPU fallback)' % name)
+    if t.dim() != 1:
+        raise ValueError('%s: expected a 1-D array' % name)
+    if not t.is_contiguous():
+        raise ValueError('%s: array must be contiguous' % name)
+    return t.data_ptr()
+
+
+def _csr(Ap, Aj, Ax):
+    return (_chk(Ap, torch.int32, 'Ap'), _chk(Aj, torch.int32, 'Aj'), _chk(Ax, torch.float64, 'Ax'))
+
+
+def _omega(omega):
+    if isinstance(omega, torch.Tensor):
+        return float(omega.reshape(-1)[0].item())
+    return float(np.ravel(omega)[0])
+
+
+def _cptr(color_ptr):
+    if color_ptr is None:
+        return None, 0
+    cp = np.ascontiguousarray(color_ptr, dtype=np.intc)
+    return cp.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), len(cp) - 1
+
+
+def jacobi(Ap, Aj, Ax, x, b, temp, row_start, row_stop, row_step, omega):
+    """relaxation.h:201-239"""
+    p = _csr(Ap, Aj, Ax)
+    _lib.call('b200amg_jacobi', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              _chk(temp, torch.float64, 'temp'), int(row_start), int(row_stop), int(row_step), _omega(omega),
+              _stream())
+
+
+def bsr_jacobi(Ap, Aj, Ax, x, b, temp, row_start, row_stop, row_step, blocksize, omega):
+    """relaxation.h:267-360"""
+    p = _csr(Ap, Aj, Ax)
+    _lib.call('b200amg_bsr_jacobi', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              _chk(temp, torch.float64, 'temp'), int(row_start), int(row_stop), int(row_step), int(blocksize),
+              _omega(omega), _stream())
+
+
+def gauss_seidel(Ap, Aj, Ax, x, b, row_start, row_stop, row_step):
+    """relaxation.h:33-62 (sequential sweep on the device)"""
+    p = _csr(Ap, Aj, Ax)
+    _lib.call('b200amg_gauss_seidel', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              int(row_start), int(row_stop), int(row_step), _stream())
+
+
+def gauss_seidel_indexed(Ap, Aj, Ax, x, b, Id, row_start, row_stop, row_step, color_ptr=None):
+    """relaxation.h:394-426"""
+    p = _csr(Ap, Aj, Ax)
+    cp, K = _cptr(color_ptr)
+    _lib.call('b200amg_gauss_seidel_indexed', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              _chk(Id, torch.int32, 'Id'), int(row_start), int(row_stop), int(row_step), cp, K, _stream())
+
+
+def bsr_gauss_seidel(Ap, Aj, Ax, x, b, row_start, row_stop, row_step, blocksize, Id=None, color_ptr=None):
+    """relaxation.h:89-173"""
+    p = _csr(Ap, Aj, Ax)
+    cp, K = _cptr(color_ptr)
+    _lib.call('b200amg_bsr_gauss_seidel', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              int(row_start), int(row_stop), int(row_step), int(blocksize),
+              0 if Id is None else _chk(Id, torch.int32, 'Id'), cp, K, _stream())
+
+
+def vertex_coloring_mis(num_rows, Ap, Aj, x):
+    """graph.h:171-188.  Setup-time, inherently sequential: HOST int32 numpy arrays; returns K."""
+    Ap = np.ascontiguousarray(Ap, np.intc)
+    Aj = np.ascontiguousarray(Aj, np.intc)
+    if x.dtype != np.intc or not x.flags.c_contiguous:
+        raise TypeError('x must be a contiguous int32 numpy array')
+    lib = _lib.load()
+    K = lib.b200amg_vertex_coloring_mis_host(int(num_rows), Ap.ctypes.data, Aj.ctypes.data, x.ctypes.data)
+    if K < 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+    return K
+
+
+def standard_aggregation(n_row, Ap, Aj, x, y):
+    """smoothed_aggregation.h:121-221 (host arrays); returns the number of aggregates."""
+    Ap = np.ascontiguousarray(Ap, np.intc)
+    Aj = np.ascontiguousarray(Aj, np.intc)
+    lib = _lib.load()
+    n = lib.b200amg_standard_aggregation_host(int(n_row), Ap.ctypes.data, Aj.ctypes.data, x.ctypes.data,
+                                              y.ctypes.data)
+    if n < 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+    return n

@@ -121,6 +121,22 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
         }
         return 0;
     }
+    if (kind == 3) {                                   // lexicographic Gauss-Seidel: exact, sequential
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        const int nb = d.n / d.bs;
+        for (int it = 0; it < iters; ++it) {
+            for (int pass = 0; pass < 2; ++pass) {
+                const bool bwd = (pass == 1);
+                if ((sweep == 0 && bwd) || (sweep == 1 && !bwd)) continue;
+                const int r0 = bwd ? nb - 1 : 0, r1 = bwd ? -1 : nb, dr = bwd ? -1 : 1;
+                if (d.bs == 1)
+                    B200_TRY(gs_sequential(d.flavor != 0, d.Ap, d.Aj, d.Ax, *cur, b, nullptr, r0, r1, dr, st));
+                else
+                    B200_TRY(bsr_gs_sequential(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, nullptr, r0, r1, dr, st));
+            }
+        }
+        return 0;
+    }
     return set_err(B200AMG_EINVAL, "smooth: unknown smoother kind");
 }
 

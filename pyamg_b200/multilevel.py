@@ -1,0 +1,315 @@
+"""multilevel_solver on the B200: same constructor, `solve()`, `aspreconditioner()`,
+complexities and repr as the reference's (pyamg/multilevel.py:14-548); levels hold device
+matrices (pyamg_b200.sparse.DevMat) and the cycle runs inside libb200amg
+(b200amg_vcycle_*: a CUDA-graph replay of the whole V/W/F cycle).
+
+Smoothers are attached with `change_smoothers(ml, presmoother, postsmoother)` like the
+reference (pyamg/relaxation/smoothing.py:24-169) using specs
+    ('jacobi', {'omega': w, 'iterations': k, 'withrho': True})
+    ('gauss_seidel', {'sweep': 'forward'|'backward'|'symmetric', 'iterations': k})      lexicographic (exact, sequential)
+    ('gauss_seidel_indexed', {'indices': Id, 'color_ptr': ptr, 'sweep': ..., 'iterations': k})
+    ('multicolor_gauss_seidel', {'sweep': ..., 'iterations': k})    MIS colouring + indexed sweep
+Anything else raises: there is no CPU fallback.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from .sparse import DevMat, _dev, _ptr
+
+_SWEEP = {'forward': 0, 'backward': 1, 'symmetric': 2}
+_CYCLE = {'V': 0, 'W': 1, 'F': 2}
+
+
+class _Smoother:
+    """resolved smoother of one level: kind, omega, iterations, sweep (+ colour ordering)"""
+
+    def __init__(self, kind=0, omega=1.0, iterations=1, sweep='forward', indices=None, color_ptr=None, name=None):
+        self.kind, self.omega, self.iterations, self.sweep = kind, float(omega), int(iterations), sweep
+        self.indices, self.color_ptr, self.name = indices, color_ptr, name
+
+
+def coarse_grid_solver(solver):
+    """pyamg/multilevel.py:554-720 for the dense pseudo-inverse solvers ('pinv2' default, 'pinv'):
+    the pseudo-inverse of the (<= max_coarse) coarsest matrix is formed ONCE on the host with
+    LAPACK, exactly as the reference does (sp.linalg.pinv2(A.todense())), and applied on the
+    device every cycle (b200amg_dense_matvec)."""
+    name, kwargs = solver if isinstance(solver, tuple) else (solver, {})
+    if name not in ('pinv', 'pinv2'):
+        raise ValueError('coarse solver %r is not available on the device (pinv, pinv2)' % (name,))
+
+    class generic_solver:
+        def __init__(self):
+            self.P = None
+
+        def matrix(self, A):
+            """device pseudo-inverse (n x n row-major) or None when A has no entries"""
+            if A.nnz == 0:
+                return None
+            if self.P is None:
+                import scipy.linalg
+                dense = A.to_scipy().toarray()
+                self.P = torch.from_numpy(np.ascontiguousarray(scipy.linalg.pinv(dense, **kwargs))).to(_dev())
+            return self.P
+
+        def __call__(self, A, b):
+            P = self.matrix(A)
+            x = torch.zeros_like(b)
+            if P is not None:
+                _lib.call('b200amg_dense_matvec', A.shape[0], _ptr(P), _ptr(b), _ptr(x),
+                          torch.cuda.current_stream().cuda_stream)
+            return x
+
+        def __repr__(self):
+            return 'coarse_grid_solver(' + repr(name) + ')'
+
+        def name(self):
+            return repr(name)
+
+    return generic_solver()
+
+
+class multilevel_solver:
+    """Stores the multigrid hierarchy and runs the cycle (pyamg/multilevel.py:14-44)."""
+
+    class level:
+        """struct: A (and P, R, presmoother, postsmoother on all but the coarsest level)"""
+
+        def __init__(self):
+            pass
+
+    def __init__(self, levels, coarse_solver='pinv2'):
+        self.levels = levels
+        self.coarse_solver = coarse_grid_solver(coarse_solver)
+        for lvl in levels:
+            for nm in ('A', 'P', 'R'):
+                M = getattr(lvl, nm, None)
+                if M is not None and not isinstance(M, DevMat):
+                    setattr(lvl, nm, DevMat.from_scipy(M))
+        for lvl in levels[:-1]:
+            if not hasattr(lvl, 'R'):
+                from .sparse import transpose
+                lvl.R = transpose(lvl.P)                  # level.R = level.P.H (multilevel.py:154-156)
+        self._engine = None
+        self._stream = None
+        self._keep = []
+
+    # ---- statistics (multilevel.py:158-269) -----------------------------------------------
+    def __repr__(self):
+        out = 'multilevel_solver\n'
+        out += 'Number of Levels:     %d\n' % len(self.levels)
+        out += 'Operator Complexity: %6.3f\n' % self.operator_complexity()
+        out += 'Grid Complexity:     %6.3f\n' % self.grid_complexity()
+        out += 'Coarse Solver:        %s\n' % self.coarse_solver.name()
+        total = sum(l.A.nnz for l in self.levels)
+        out += '  level   unknowns     nonzeros\n'
+        for n, l in enumerate(self.levels):
+            out += '   %2d   %10d   %10d [%5.2f%%]\n' % (n, l.A.shape[1], l.A.nnz, 100 * float(l.A.nnz) / float(total))
+        return out
+
+    def cycle_complexity(self, cycle='V'):
+        cycle = str(cycle).upper()
+        nnz = [l.A.nnz for l in self.levels]
+        last = len(self.levels) - 2
+
+        def cost(k, kind):
+            if len(self.levels) == 1:
+                return nnz[0]
+            if k == last:
+                return 2 * nnz[k] + nnz[k + 1]
+            if kind == 'V':
+                return 2 * nnz[k] + cost(k + 1, 'V')
+            if kind == 'W':
+                return 2 * nnz[k] + 2 * cost(k + 1, 'W')
+            return 2 * nnz[k] + cost(k + 1, 'F') + cost(k + 1, 'V')
+        if cycle == 'AMLI':
+            cycle = 'W'
+        if cycle not in 'VWF':
+            raise TypeError('Unrecognized cycle type (%s)' % cycle)
+        return float(cost(0, cycle)) / float(nnz[0])
+
+    def operator_complexity(self):
+        return sum(l.A.nnz for l in self.levels) / float(self.levels[0].A.nnz)
+
+    def grid_complexity(self):
+        return sum(l.A.shape[0] for l in self.levels) / float(self.levels[0].A.shape[0])
+
+    # ---- cycle engine ------------------------------------------------------------------------
+    def _destroy_engine(self):
+        if self._engine is not None:
+            _lib.load().b200amg_vcycle_destroy(self._engine)
+            self._engine = None
+            self._keep = []
+
+    def __del__(self):
+        try:
+            self._destroy_engine()
+        except Exception:
+            pass
+
+    def _build_engine(self):
+        lv = self.levels
+        nlev = len(lv)
+        dev = _dev()
+        descs = (_lib.LevelDesc * (nlev - 1))()
+        keep = []
+        for k in range(nlev - 1):
+            L, d = lv[k], descs[k]
+            A, P, R = L.A, L.P, L.R
+            if A.blocksize[0] != A.blocksize[1]:
+                raise ValueError('BSR blocks must be square')
+            if R.blocksize != (P.blocksize[1], P.blocksize[0]) or R.shape != (P.shape[1], P.shape[0]):
+                raise ValueError('R must have the transposed shape / block shape of P')
+            pre = getattr(L, 'presmoother', None) or _Smoother()
+            post = getattr(L, 'postsmoother', None) or _Smoother()
+            if not isinstance(pre, _Smoother) or not isinstance(post, _Smoother):
+                raise TypeError('smoothers must be set with pyamg_b200.change_smoothers (device kernels only)')
+            d.n, d.bs, d.flavor = A.shape[0], A.blocksize[0], 0 if A.format == 'csr' else 1
+            d.Ap, d.Aj, d.Ax = _ptr(A.indptr), _ptr(A.indices), _ptr(A.data)
+            d.nc, d.p_br, d.p_bc = P.shape[1], P.blocksize[0], P.blocksize[1]
+            d.Pp, d.Pj, d.Px = _ptr(P.indptr), _ptr(P.indices), _ptr(P.data)
+            d.Rp, d.Rj, d.Rx = _ptr(R.indptr), _ptr(R.indices), _ptr(R.data)
+            d.pre_kind, d.post_kind = pre.kind, post.kind
+            d.pre_omega, d.post_omega = pre.omega, post.omega
+            d.pre_iters, d.post_iters = pre.iterations, post.iterations
+            d.pre_sweep, d.post_sweep = _SWEEP[pre.sweep], _SWEEP[post.sweep]
+            d.Id, d.K = 0, 0
+            ordered = [s for s in (pre, post) if s.kind == 2]
+            if ordered:
+                s0 = ordered[0]
+                for s in ordered[1:]:
+                    if s.indices is not s0.indices and not np.array_equal(np.asarray(s.color_ptr), np.asarray(s0.color_ptr)):
+                        raise ValueError('pre- and post-smoother must share one colour ordering per level')
+                Id = s0.indices
+                if not isinstance(Id, torch.Tensor):
+                    Id = torch.from_numpy(np.ascontiguousarray(Id, dtype=np.intc)).to(dev)
+                cp = np.ascontiguousarray(s0.color_ptr, dtype=np.intc)
+                keep += [Id, cp]
+                d.Id, d.K = _ptr(Id), len(cp) - 1
+                d.color_ptr_host = cp.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+        lib = _lib.load()
+        nbytes = lib.b200amg_vcycle_work_bytes(nlev, descs)
+        work = torch.empty(nbytes // 8 + 8, dtype=torch.float64, device=dev)
+        cinv = self.coarse_solver.matrix(lv[-1].A)
+        handle = ctypes.c_void_p()
+        _lib.call('b200amg_vcycle_create', nlev, descs, _ptr(cinv), _ptr(work), nbytes, ctypes.byref(handle))
+        n = lv[0].A.shape[0]
+        self._x = torch.zeros(n, dtype=torch.float64, device=dev)
+        self._b = torch.zeros(n, dtype=torch.float64, device=dev)
+        self._nrm = torch.zeros(2, dtype=torch.float64, device=dev)
+        self._keep = keep + [work, cinv, descs]
+        self._engine = handle
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=dev)
+
+    def _residual_norm(self):
+        _lib.call('b200amg_vcycle_residual_norm2', self._engine, _ptr(self._x), _ptr(self._b), _ptr(self._nrm),
+                  self._stream.cuda_stream)
+        return float(np.sqrt(self._nrm[0].item()))
+
+    def cycle_device(self, cycle='V', use_graph=True):
+        """one cycle on the engine's resident (x, b): x <- cycle(x, b).  Asynchronous."""
+        _lib.call('b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], int(use_graph),
+                  self._stream.cuda_stream)
+
+    # ---- public API (multilevel.py:271-471) -------------------------------------------------
+    def psolve(self, b):
+        return self.solve(b, maxiter=1)
+
+    def aspreconditioner(self, cycle='V'):
+        """LinearOperator whose matvec is ONE cycle from a zero guess (multilevel.py:274-314).
+        The reference computes two residual norms around that cycle only to discard them; they
+        are skipped here (same result)."""
+        from scipy.sparse.linalg import LinearOperator
+        shape = self.levels[0].A.shape
+
+        def matvec(b):
+            return self.solve(b, maxiter=1, cycle=cycle, tol=1e-12, _norms=False)
+        return LinearOperator(shape, matvec, dtype=np.float64)
+
+    def solve(self, b, x0=None, tol=1e-5, maxiter=100, cycle='V', accel=None, callback=None, residuals=None,
+              return_residuals=False, _norms=True):
+        """Same contract as the reference's solve (multilevel.py:316-471): relative-residual
+        stopping test `||r_k|| <= tol * ||b||`, residual history appended to `residuals`,
+        `callback(x)` after every cycle.  numpy in -> numpy out, torch CUDA in -> torch CUDA out."""
+        cycle = str(cycle).upper()
+        if cycle not in _CYCLE:
+            if cycle == 'AMLI':
+                raise NotImplementedError('AMLI cycles are not available on the device')
+            raise TypeError('Unrecognized cycle type (%s)' % cycle)
+        if accel is not None:
+            from . import krylov
+            return krylov.accelerated_solve(self, accel, b, x0, tol, maxiter, cycle, callback, residuals)
+        n = self.levels[0].A.shape[0]
+        as_numpy = not isinstance(b, torch.Tensor)
+        if self._engine is None and len(self.levels) > 1:
+            self._build_engine()
+        if len(self.levels) == 1:
+            return self._solve_one_level(b, x0, tol, maxiter, callback, residuals, as_numpy)
+        cur = torch.cuda.current_stream()
+        self._stream.wait_stream(cur)
+        with torch.cuda.stream(self._stream):
+            bt = b if isinstance(b, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.ravel(b), np.float64))
+            if bt.numel() != n:
+                raise ValueError('b has invalid dimensions')
+            self._b.copy_(bt.reshape(-1), non_blocking=True)
+            if x0 is None:
+                self._x.zero_()
+            else:
+                xt = x0 if isinstance(x0, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.ravel(x0), np.float64))
+                self._x.copy_(xt.reshape(-1), non_blocking=True)
+            if residuals is None:
+                residuals = []
+            else:
+                residuals[:] = []
+            if _norms:
+                _lib.call('b200amg_dot', n, _ptr(self._b), _ptr(self._b), _ptr(self._nrm) + 8, self._keep_dotwork(),
+                          self._stream.cuda_stream)
+                normb = float(np.sqrt(self._nrm[1].item()))
+                if normb != 0:
+                    tol = tol * normb
+                residuals.append(self._residual_norm())
+                while len(residuals) <= maxiter and residuals[-1] > tol:
+                    self.cycle_device(cycle)
+                    residuals.append(self._residual_norm())
+                    if callback is not None:
+                        callback(self._x.cpu().numpy() if as_numpy else self._x)
+            else:
+                for _ in range(maxiter):
+                    self.cycle_device(cycle)
+            out = self._x.cpu().numpy() if as_numpy else self._x.clone()
+        cur.wait_stream(self._stream)
+        if as_numpy and isinstance(b, np.ndarray):
+            out = out.reshape(b.shape)
+        if return_residuals:
+            return out, residuals
+        return out
+
+    def _keep_dotwork(self):
+        if not hasattr(self, '_dotwork'):
+            self._dotwork = torch.empty(1024, dtype=torch.float64, device=self._x.device)
+        return _ptr(self._dotwork)
+
+    def _solve_one_level(self, b, x0, tol, maxiter, callback, residuals, as_numpy):
+        A = self.levels[0].A
+        bt = b if isinstance(b, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.ravel(b), np.float64)).to(_dev())
+        bt = bt.reshape(-1)
+        x = torch.zeros_like(bt) if x0 is None else (x0.clone() if isinstance(x0, torch.Tensor) else
+                                                      torch.from_numpy(np.array(np.ravel(x0), np.float64)).to(_dev()))
+        normb = float(torch.linalg.vector_norm(bt).item())
+        if normb != 0:
+            tol = tol * normb
+        if residuals is None:
+            residuals = []
+        else:
+            residuals[:] = []
+        rn = lambda: float(torch.linalg.vector_norm(A.residual(x, bt)).item())
+        residuals.append(rn())
+        while len(residuals) <= maxiter and residuals[-1] > tol:
+            x = self.coarse_solver(A, bt)
+            residuals.append(rn())
+            if callback is not None:
+                callback(x.cpu().numpy() if as_numpy else x)
+        return x.cpu().numpy() if as_numpy else x

@@ -1,0 +1,130 @@
+"""Smoother front-ends with the reference's names, arguments and error behaviour
+(pyamg/relaxation/relaxation.py: make_system :21-105, gauss_seidel :280-354, jacobi :357-427,
+gauss_seidel_indexed :671-741), operating on device data: `A` is a pyamg_b200.sparse.DevMat,
+`x` and `b` are float64 torch CUDA tensors; `x` is updated in place, nothing is returned.
+
+Multicolour Gauss-Seidel = vertex_coloring(A) + color_ordering + gauss_seidel_indexed
+with `color_ptr`; without `color_ptr` the indexed sweep runs strictly sequentially on the GPU.
+"""
+import numpy as np
+import torch
+
+from . import amg_core
+from .sparse import DevMat
+
+
+def make_system(A, x, b, formats=None):
+    """relaxation.py:21-105 on device containers."""
+    if not isinstance(A, DevMat):
+        raise TypeError('expected a pyamg_b200 device matrix (DevMat.from_scipy(A))')
+    if formats == ['csr'] and A.format == 'bsr':
+        if not A.is_scalar:
+            raise NotImplementedError('BSR -> CSR expansion on the device is only done for 1x1 blocks')
+        A = A.tocsr_scalar()
+    if not isinstance(x, torch.Tensor):
+        raise ValueError('expected a torch tensor for argument x')
+    if not isinstance(b, torch.Tensor):
+        raise ValueError('expected a torch tensor for argument b')
+    M, N = A.shape
+    if M != N:
+        raise ValueError('expected square matrix')
+    if tuple(x.shape) not in [(M,), (M, 1)]:
+        raise ValueError('x has invalid dimensions')
+    if tuple(b.shape) not in [(M,), (M, 1)]:
+        raise ValueError('b has invalid dimensions')
+    if x.dtype != torch.float64 or b.dtype != torch.float64:
+        raise TypeError('arguments A, x, and b must have the same dtype')
+    if not x.is_contiguous():
+        raise ValueError('x must be contiguous in memory')
+    return A, x.view(-1), b.reshape(-1).contiguous()
+
+
+def _range(sweep, n):
+    if sweep == 'forward':
+        return 0, n, 1
+    if sweep == 'backward':
+        return n - 1, -1, -1
+    raise ValueError("valid sweep directions are 'forward', 'backward', and 'symmetric'")
+
+
+def jacobi(A, x, b, iterations=1, omega=1.0):
+    A, x, b = make_system(A, x, b, formats=['csr', 'bsr'])
+    n = A.shape[0]
+    if n <= 0:
+        return
+    temp = torch.empty_like(x)
+    for _ in range(iterations):
+        if A.format == 'csr':
+            amg_core.jacobi(A.indptr, A.indices, A.data, x, b, temp, 0, n, 1, [omega])
+        else:
+            R, C = A.blocksize
+            if R != C:
+                raise ValueError('BSR blocks must be square')
+            amg_core.bsr_jacobi(A.indptr, A.indices, A.data, x, b, temp, 0, n // R, 1, R, [omega])
+
+
+def gauss_seidel(A, x, b, iterations=1, sweep='forward', indices=None, color_ptr=None):
+    """Lexicographic sweep (sequential on the device) unless a colour ordering
+    (`indices`, `color_ptr` over rows / block rows) is given."""
+    A, x, b = make_system(A, x, b, formats=['csr', 'bsr'])
+    if A.format == 'csr':
+        bs = 1
+    else:
+        R, C = A.blocksize
+        if R != C:
+            raise ValueError('BSR blocks must be square')
+        bs = R
+    if sweep == 'symmetric':
+        for _ in range(iterations):
+            gauss_seidel(A, x, b, 1, 'forward', indices, color_ptr)
+            gauss_seidel(A, x, b, 1, 'backward', indices, color_ptr)
+        return
+    nrows = len(x) // bs if indices is None else int(indices.numel())
+    r0, r1, dr = _range(sweep, nrows)
+    for _ in range(iterations):
+        if A.format == 'csr' and indices is None:
+            amg_core.gauss_seidel(A.indptr, A.indices, A.data, x, b, r0, r1, dr)
+        elif A.format == 'csr':
+            amg_core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr, color_ptr)
+        else:
+            amg_core.bsr_gauss_seidel(A.indptr, A.indices, A.data, x, b, r0, r1, dr, bs, indices, color_ptr)
+
+
+def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', color_ptr=None):
+    A, x, b = make_system(A, x, b, formats=['csr'])
+    if not isinstance(indices, torch.Tensor):
+        indices = torch.from_numpy(np.ascontiguousarray(indices, dtype='intc')).to(x.device)
+    if sweep == 'symmetric':
+        for _ in range(iterations):
+            gauss_seidel_indexed(A, x, b, indices, 1, 'forward', color_ptr)
+            gauss_seidel_indexed(A, x, b, indices, 1, 'backward', color_ptr)
+        return
+    r0, r1, dr = _range(sweep, int(indices.numel()))
+    for _ in range(iterations):
+        amg_core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr, color_ptr)
+
+
+def vertex_coloring(G, method='MIS'):
+    """pyamg/graph.py:84-125, method 'MIS' only (-> graph.h:171-188); host, setup-time.
+    G: DevMat or scipy matrix (pattern of block rows for BSR)."""
+    if method != 'MIS':
+        raise ValueError('only the MIS colouring is available')
+    if isinstance(G, DevMat):
+        Ap, Aj = G.indptr.cpu().numpy(), G.indices.cpu().numpy()
+        n = G.n_brow
+    else:
+        Ap, Aj = np.asarray(G.indptr, np.intc), np.asarray(G.indices, np.intc)
+        n = len(Ap) - 1
+    colors = np.empty(n, dtype=np.intc)
+    amg_core.vertex_coloring_mis(n, Ap, Aj, colors)
+    return colors
+
+
+def color_ordering(colors):
+    """Rows grouped by colour, ascending inside each colour -> (indices int32[n], color_ptr int32[K+1])."""
+    colors = np.asarray(colors)
+    K = int(colors.max()) + 1 if len(colors) else 0
+    idx = np.argsort(colors, kind='stable').astype(np.intc)
+    ptr = np.zeros(K + 1, dtype=np.intc)
+    np.cumsum(np.bincount(colors, minlength=K), out=ptr[1:])
+    return idx, ptr

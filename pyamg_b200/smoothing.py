@@ -1,0 +1,82 @@
+"""change_smoothers / rho_D_inv_A on the device (pyamg/relaxation/smoothing.py:24-200,320-332).
+
+A smoother spec is `name`, `(name, {opts})`, or a per-level list of those -- the same forms the
+reference accepts (smoothing.py:37-57,126-169).  Names with a device kernel:
+jacobi, gauss_seidel, gauss_seidel_indexed, multicolor_gauss_seidel, None.
+"""
+import numpy as np
+import torch
+
+from .linalg import approximate_spectral_radius
+from .multilevel import _Smoother
+from .sparse import DevMat, _dev
+from . import relaxation
+
+
+def rho_D_inv_A(A):
+    """spectral radius of D^-1 A, cached on the matrix like the reference (smoothing.py:195-200).
+    The estimate draws its start vector from the global numpy RNG exactly like the reference."""
+    if not hasattr(A, 'rho_D_inv'):
+        d = A.diagonal()
+        dinv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
+        A.rho_D_inv = approximate_spectral_radius(A, row_scale=dinv)
+    return A.rho_D_inv
+
+
+def _unpack(spec):
+    if isinstance(spec, tuple):
+        return spec[0], dict(spec[1])
+    return spec, {}
+
+
+def _levelize(spec, nlev):
+    if isinstance(spec, list):
+        out = list(spec)
+        while len(out) < nlev:
+            out.append(out[-1])
+        return out[:nlev]
+    return [spec] * nlev
+
+
+def _resolve(spec, lvl):
+    name, kw = _unpack(spec)
+    A = lvl.A
+    if name is None:
+        return _Smoother(0, name=None)
+    if name == 'jacobi':
+        omega = kw.pop('omega', 1.0)
+        iters = kw.pop('iterations', 1)
+        if kw.pop('withrho', True):
+            omega = omega / rho_D_inv_A(A)
+        if kw:
+            raise TypeError('jacobi: unexpected options %r' % sorted(kw))
+        return _Smoother(1, omega, iters, name='jacobi')
+    if name == 'gauss_seidel':
+        return _Smoother(3, 1.0, kw.pop('iterations', 1), kw.pop('sweep', 'forward'), name='gauss_seidel')
+    if name in ('gauss_seidel_indexed', 'multicolor_gauss_seidel'):
+        iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
+        if name == 'multicolor_gauss_seidel':
+            if not hasattr(lvl, '_mc_order'):
+                idx, ptr = relaxation.color_ordering(relaxation.vertex_coloring(A, 'MIS'))
+                lvl._mc_order = (torch.from_numpy(idx).to(_dev()), ptr)
+            idx, ptr = lvl._mc_order
+        else:
+            idx, ptr = kw.pop('indices'), kw.pop('color_ptr', None)
+            if ptr is None:
+                raise ValueError('gauss_seidel_indexed inside a cycle needs color_ptr (colour groups of `indices`)')
+            if not isinstance(idx, torch.Tensor):
+                idx = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.intc)).to(_dev())
+        return _Smoother(2, 1.0, iters, sweep, idx, np.ascontiguousarray(ptr, dtype=np.intc), name=name)
+    raise ValueError('smoother %r has no device kernel (available: jacobi, gauss_seidel, '
+                     'gauss_seidel_indexed, multicolor_gauss_seidel, None)' % (name,))
+
+
+def change_smoothers(ml, presmoother, postsmoother):
+    """Attach resolved device smoothers to every non-coarsest level (smoothing.py:24-169)."""
+    nlev = len(ml.levels) - 1
+    pre, post = _levelize(presmoother, nlev), _levelize(postsmoother, nlev)
+    for k, lvl in enumerate(ml.levels[:-1]):
+        lvl.presmoother = _resolve(pre[k], lvl)
+    for k, lvl in enumerate(ml.levels[:-1]):
+        lvl.postsmoother = _resolve(post[k], lvl)
+    ml._destroy_engine()

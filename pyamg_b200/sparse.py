@@ -1,0 +1,214 @@
+"""Device-resident CSR/BSR matrices and the sparse products of the hot path.
+
+`DevMat` mirrors the few scipy.sparse members the reference's cycle touches (`shape`, `nnz`,
+`format`, `blocksize`, `indptr/indices/data`, `A * x`), with the arrays living in HBM as torch
+tensors (int32 indices, fp64 values).  All arithmetic is done by libb200amg kernels:
+  A * x          -> b200amg_csr_matvec / b200amg_bsr_matvec   (scipy csr_matvec / bsr_matvec)
+  matmat(A, B)   -> b200amg_spgemm_*                          (scipy csr_matmat, pyamg aggregation.py:429)
+  transpose(A)   -> b200amg_csr_transpose                     (scipy csr_tocsc,  pyamg classical.py:174)
+"""
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        raise _lib.B200AmgError('pyamg_b200 needs a CUDA device (no CPU fallback)')
+    return torch.device('cuda', torch.cuda.current_device())
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def as_dev_vector(v, dtype=torch.float64):
+    """numpy / torch -> contiguous 1-D device tensor (copy only when needed)."""
+    if isinstance(v, torch.Tensor):
+        t = v
+        if t.device.type != 'cuda':
+            t = t.to(_dev())
+        if t.dtype != dtype:
+            raise TypeError('expected dtype %s, got %s' % (dtype, t.dtype))
+        return t.reshape(-1) if t.is_contiguous() else t.contiguous().reshape(-1)
+    a = np.ascontiguousarray(np.ravel(v))
+    return torch.from_numpy(a).to(_dev()).to(dtype)
+
+
+class DevMat:
+    """CSR (blocksize (1,1), format 'csr') or BSR (format 'bsr', R x C row-major blocks) in HBM."""
+
+    def __init__(self, indptr, indices, data, shape, blocksize=(1, 1), fmt=None, sorted_indices=None):
+        self.indptr, self.indices, self.data = indptr, indices, data
+        self.shape = (int(shape[0]), int(shape[1]))
+        self.blocksize = (int(blocksize[0]), int(blocksize[1]))
+        self.format = fmt or ('csr' if self.blocksize == (1, 1) else 'bsr')
+        self.dtype = np.dtype('float64')
+        self.has_sorted_indices = sorted_indices
+        assert indptr.dtype == torch.int32 and indices.dtype == torch.int32 and data.dtype == torch.float64
+        assert indptr.is_contiguous() and indices.is_contiguous() and data.is_contiguous()
+
+    # -- scipy-like surface ------------------------------------------------------------------
+    @property
+    def nnz(self):
+        return int(self.data.numel())
+
+    @property
+    def nblocks(self):
+        return int(self.indices.numel())
+
+    @property
+    def n_brow(self):
+        return self.shape[0] // self.blocksize[0]
+
+    @property
+    def n_bcol(self):
+        return self.shape[1] // self.blocksize[1]
+
+    @property
+    def is_scalar(self):
+        return self.blocksize == (1, 1)
+
+    @classmethod
+    def from_scipy(cls, M):
+        import scipy.sparse as sp
+        if not sp.issparse(M):
+            M = sp.csr_matrix(M)
+        if M.format not in ('csr', 'bsr'):
+            M = M.tocsr()
+        if M.dtype != np.float64:
+            M = M.astype(np.float64)
+        dev = _dev()
+        bs = M.blocksize if M.format == 'bsr' else (1, 1)
+        return cls(torch.from_numpy(np.ascontiguousarray(M.indptr, np.int32)).to(dev),
+                   torch.from_numpy(np.ascontiguousarray(M.indices, np.int32)).to(dev),
+                   torch.from_numpy(np.ascontiguousarray(M.data, np.float64).ravel()).to(dev),
+                   M.shape, bs, M.format, bool(M.has_sorted_indices))
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        ip, ix, dx = self.indptr.cpu().numpy(), self.indices.cpu().numpy(), self.data.cpu().numpy()
+        if self.format == 'bsr':
+            R, C = self.blocksize
+            return sp.bsr_matrix((dx.reshape(-1, R, C), ix, ip), shape=self.shape, blocksize=(R, C))
+        return sp.csr_matrix((dx, ix, ip), shape=self.shape)
+
+    def tocsr_scalar(self):
+        """Same arrays viewed as CSR when the blocks are 1x1 (scipy does the same, bsr_matvec)."""
+        if not self.is_scalar:
+            raise ValueError('only 1x1 blocks can be viewed as CSR')
+        return DevMat(self.indptr, self.indices, self.data, self.shape, (1, 1), 'csr', self.has_sorted_indices)
+
+    # -- products ------------------------------------------------------------------------------
+    def matvec(self, x, out=None):
+        x = as_dev_vector(x)
+        if x.numel() != self.shape[1]:
+            raise ValueError('dimension mismatch')
+        y = torch.empty(self.shape[0], dtype=torch.float64, device=x.device) if out is None else out
+        R, C = self.blocksize
+        _lib.call('b200amg_bsr_matvec', self.n_brow, self.n_bcol, R, C, _ptr(self.indptr), _ptr(self.indices),
+                  _ptr(self.data), _ptr(x), 0, _ptr(y), 0, _stream())
+        return y
+
+    def __mul__(self, other):
+        if isinstance(other, DevMat):
+            return matmat(self, other)
+        return self.matvec(other)
+
+    __matmul__ = __mul__
+
+    def residual(self, x, b, out=None):
+        """b - A x in one pass (pyamg/multilevel.py:496)."""
+        x, b = as_dev_vector(x), as_dev_vector(b)
+        r = torch.empty_like(b) if out is None else out
+        R, C = self.blocksize
+        _lib.call('b200amg_bsr_matvec', self.n_brow, self.n_bcol, R, C, _ptr(self.indptr), _ptr(self.indices),
+                  _ptr(self.data), _ptr(x), _ptr(b), _ptr(r), 1, _stream())
+        return r
+
+    def diagonal(self):
+        if self.blocksize[0] != self.blocksize[1]:
+            raise ValueError('square blocks required')
+        d = torch.empty(self.shape[0], dtype=torch.float64, device=self.data.device)
+        _lib.call('b200amg_extract_diag', self.n_brow, self.blocksize[0], _ptr(self.indptr), _ptr(self.indices),
+                  _ptr(self.data), _ptr(d), _stream())
+        return d
+
+    @property
+    def T(self):
+        return transpose(self)
+
+
+def _scan_i32(v):
+    n = v.numel()
+    out = torch.empty(n + 1, dtype=torch.int32, device=v.device)
+    scr = torch.empty(_lib.load().b200amg_scan_scratch_elems(n), dtype=torch.int32, device=v.device)
+    _lib.call('b200amg_exclusive_scan_i32', n, _ptr(v), _ptr(out), _ptr(scr), _stream())
+    return out
+
+
+def _scan_i64(v):
+    n = v.numel()
+    out = torch.empty(n + 1, dtype=torch.int64, device=v.device)
+    scr = torch.empty(_lib.load().b200amg_scan_scratch_elems(n), dtype=torch.int64, device=v.device)
+    _lib.call('b200amg_exclusive_scan_i64', n, _ptr(v), _ptr(out), _ptr(scr), _stream())
+    return out
+
+
+def matmat(A, B):
+    """C = A B for scalar CSR/BSR(1,1) operands: sorted rows, exact zeros dropped, values
+    bit-identical to scipy's csr_matmat (see csrc/spgemm.cu)."""
+    if not (A.is_scalar and B.is_scalar):
+        raise NotImplementedError('matmat: only scalar (1x1 block) operands')
+    if A.shape[1] != B.shape[0]:
+        raise ValueError('dimension mismatch')
+    n = A.shape[0]
+    dev = A.data.device
+    st = _stream()
+    ub = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    _lib.call('b200amg_spgemm_count', n, _ptr(A.indptr), _ptr(A.indices), _ptr(B.indptr), _ptr(ub), st)
+    ub = ub[:n]
+    ubp = _scan_i64(ub)
+    total = int(ubp[-1].item())
+    big = bool((ub.max() > 8192).item()) if n else False
+    Tj = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+    Tx = torch.empty(max(total, 1), dtype=torch.float64, device=dev)
+    Tk = torch.empty(max(total, 1), dtype=torch.int64, device=dev) if big else None
+    cnt = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    work = torch.empty(n + 256, dtype=torch.int32, device=dev)
+    _lib.call('b200amg_spgemm_numeric', n, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr),
+              _ptr(B.indices), _ptr(B.data), _ptr(ub), _ptr(ubp), _ptr(Tk), _ptr(Tj), _ptr(Tx), _ptr(cnt),
+              _ptr(work), st)
+    Cp = _scan_i32(cnt[:n])
+    nnz = int(Cp[-1].item())
+    Cj = torch.empty(nnz, dtype=torch.int32, device=dev)
+    Cx = torch.empty(nnz, dtype=torch.float64, device=dev)
+    _lib.call('b200amg_spgemm_compact', n, _ptr(ubp), _ptr(Tj), _ptr(Tx), _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
+    return DevMat(Cp, Cj, Cx, (A.shape[0], B.shape[1]), (1, 1), 'csr', True)
+
+
+def transpose(A):
+    """A^T as CSR with rows ascending in the original row index (scipy csr_tocsc order)."""
+    if not A.is_scalar:
+        raise NotImplementedError('transpose: only scalar (1x1 block) matrices')
+    n_row, n_col = A.shape
+    nnz = A.nnz
+    dev = A.data.device
+    Bp = torch.empty(n_col + 1, dtype=torch.int32, device=dev)
+    Bi = torch.empty(nnz, dtype=torch.int32, device=dev)
+    Bx = torch.empty(nnz, dtype=torch.float64, device=dev)
+    nbytes = _lib.load().b200amg_csr_transpose_work_bytes(n_row, n_col, nnz)
+    work = torch.empty(nbytes // 8 + 1, dtype=torch.int64, device=dev)
+    _lib.call('b200amg_csr_transpose', n_row, n_col, nnz, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data),
+              _ptr(Bp), _ptr(Bi), _ptr(Bx), _ptr(work), _stream())
+    return DevMat(Bp, Bi, Bx, (n_col, n_row), (1, 1), A.format, True)
+
+
+def galerkin(R, A, P):
+    """A_c = (R A) P, evaluated left to right like the reference (aggregation.py:429)."""
+    return matmat(matmat(R, A), P)

@@ -1,0 +1,99 @@
+"""CPU tests (-m "not gpu"): the C-ABI library loads and exports exactly what include/b200amg.h
+declares; the host-side (sequential) setup functions equal the oracle; the product refuses to
+run without a CUDA device instead of falling back."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import oracle
+from oracle import relaxation as orx
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, 'include', 'b200amg.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(b200amg_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from pyamg_b200 import _lib
+    lib = _lib.load()
+    names = declared_symbols()
+    assert len(names) >= 35
+    for n in names:
+        assert hasattr(lib, n), 'missing export ' + n
+    assert set(_lib.EXPORTS) <= set(names), set(_lib.EXPORTS) - set(names)
+    assert lib.b200amg_version() >= 100
+    assert ctypes.sizeof(_lib.LevelDesc) > 0
+
+
+def test_no_torch_types_in_header():
+    text = open(os.path.join(ROOT, 'include', 'b200amg.h')).read()
+    assert 'torch' not in text and 'at::' not in text and 'extern "C"' in text
+
+
+def test_host_setup_functions_equal_oracle():
+    from pyamg_b200 import amg_core
+    rng = np.random.RandomState(0)
+    for trial in range(60):
+        n = rng.randint(1, 80)
+        G = sp.random(n, n, rng.uniform(0.01, 0.2), random_state=rng, format='csr')
+        G = sp.csr_matrix(G + G.T + (sp.eye(n) if trial % 2 else 0 * sp.eye(n)))
+        Ap, Aj = G.indptr.astype(np.intc), G.indices.astype(np.intc)
+        c = np.empty(n, np.intc)
+        K = amg_core.vertex_coloring_mis(n, Ap, Aj, c)
+        c2 = np.empty(n, np.intc)
+        K2 = oracle.port.vertex_coloring_mis(n, Ap, Aj, c2)
+        assert K == K2 and np.array_equal(c, c2)
+        a, r = np.empty(n, np.intc), np.empty(n, np.intc)
+        a2, r2 = np.empty(n, np.intc), np.empty(n, np.intc)
+        k = amg_core.standard_aggregation(n, Ap, Aj, a, r)
+        k2 = oracle.port.standard_aggregation(n, Ap, Aj, a2, r2)
+        assert k == k2 and np.array_equal(a, a2) and np.array_equal(r[:k], r2[:k2])
+    # grids: the BASELINE problem class
+    from helpers_mats import poisson3d
+    G = poisson3d(11)
+    Ap, Aj = G.indptr.astype(np.intc), G.indices.astype(np.intc)
+    a, r = np.empty(G.shape[0], np.intc), np.empty(G.shape[0], np.intc)
+    a2, r2 = a.copy(), r.copy()
+    assert amg_core.standard_aggregation(G.shape[0], Ap, Aj, a, r) == oracle.port.standard_aggregation(G.shape[0], Ap, Aj, a2, r2)
+    assert np.array_equal(a, a2)
+
+
+def test_product_never_imports_oracle():
+    bad = []
+    for d, _, files in os.walk(os.path.join(ROOT, 'pyamg_b200')):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h')):
+                src = open(os.path.join(d, f)).read()
+                if re.search(r'^\s*(import|from)\s+oracle\b', src, flags=re.M) or 'oracle/' in src:
+                    bad.append(f)
+    assert not bad, bad
+
+
+def test_no_cpu_fallback_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip('CUDA present')
+    import pyamg_b200
+    with pytest.raises(pyamg_b200._lib.B200AmgError):
+        pyamg_b200.DevMat.from_scipy(sp.eye(4, format='csr'))
+    with pytest.raises(pyamg_b200._lib.B200AmgError):
+        pyamg_b200.gallery.poisson((4, 4))
+
+
+def test_color_ordering_and_stencil_helpers():
+    from pyamg_b200 import relaxation, gallery
+    c = np.array([1, 0, 2, 0, 1], dtype=np.intc)
+    idx, ptr = relaxation.color_ordering(c)
+    assert idx.tolist() == [1, 3, 0, 4, 2] and ptr.tolist() == [0, 2, 4, 5]
+    i2, p2 = orx.color_ordering(c)
+    assert np.array_equal(idx, i2) and np.array_equal(ptr, p2)
+    st = gallery.diffusion_stencil_2d(0.001, np.pi / 8, 'FE')
+    assert st.shape == (3, 3) and abs(st.sum()) < 1e-12

@@ -1,0 +1,217 @@
+"""GPU parity tests (-m gpu): every kernel of libb200amg, called through the C-ABI bindings,
+against the oracle (C port / reference .so / scipy) on the same seeded inputs.
+fp64 results are required to be BIT-IDENTICAL (np.array_equal) unless a tolerance is stated."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+torch = pytest.importorskip('torch')
+pytestmark = pytest.mark.gpu
+
+import oracle
+from oracle import relaxation as orx
+
+
+@pytest.fixture(scope='module')
+def amg():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    import pyamg_b200
+    return pyamg_b200
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def rand_matrix(n, density, rng, diag=3.0, sym=True):
+    A = sp.random(n, n, density, random_state=rng, format='csr')
+    if sym:
+        A = A + A.T
+    A = sp.csr_matrix(A + diag * sp.eye(n))
+    A.sort_indices()
+    return A
+
+
+def lap1d(n):
+    return sp.spdiags([-np.ones(n), 2 * np.ones(n), -np.ones(n)], [-1, 0, 1], n, n, format='csr')
+
+
+def poisson3d(m):
+    I = sp.eye(m); T = lap1d(m)
+    return sp.csr_matrix(sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T))
+
+
+CASES = [('rand300', lambda rng: rand_matrix(300, 0.03, rng)),
+         ('rand5000_long', lambda rng: rand_matrix(5000, 0.02, rng)),      # ~200 nnz/row: multi-chunk CTAs
+         ('poisson3d_17', lambda rng: poisson3d(17)),
+         ('empty_rows', lambda rng: sp.csr_matrix(sp.random(700, 700, 0.002, random_state=rng))),
+         ('one', lambda rng: sp.csr_matrix(np.array([[2.0]])))]
+
+
+@pytest.mark.parametrize('name,make', CASES)
+def test_spmv_family_bit_exact(amg, name, make):
+    rng = np.random.RandomState(0)
+    A = make(rng)
+    n = A.shape[0]
+    x, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    y = dA.matvec(dev(x)).cpu().numpy()
+    assert np.array_equal(y, A * x)
+    r = dA.residual(dev(x), dev(b)).cpu().numpy()
+    assert np.array_equal(r, b - A * x)
+    xx = dev(b.copy())
+    amg._lib.call('b200amg_csr_matvec_add', n, dA.indptr.data_ptr(), dA.indices.data_ptr(), dA.data.data_ptr(),
+                  dev(x).data_ptr(), xx.data_ptr(), 0)
+    torch.cuda.synchronize()
+    assert np.array_equal(xx.cpu().numpy(), b + A * x)
+
+
+def test_spmv_unaligned_and_rectangular(amg):
+    rng = np.random.RandomState(1)
+    A = sp.random(1000, 333, 0.05, random_state=rng, format='csr')
+    x = rng.rand(333)
+    dA = amg.DevMat.from_scipy(A)
+    assert np.array_equal(dA.matvec(dev(x)).cpu().numpy(), A * x)
+    # pointers offset by one element: the scalar (non-128-bit) path
+    pad_j = torch.cat([torch.zeros(1, dtype=torch.int32, device='cuda'), dA.indices])[1:]
+    pad_x = torch.cat([torch.zeros(1, dtype=torch.float64, device='cuda'), dA.data])[1:]
+    y = torch.empty(1000, dtype=torch.float64, device='cuda')
+    amg._lib.call('b200amg_csr_matvec', 1000, 333, dA.indptr.data_ptr(), pad_j.data_ptr(), pad_x.data_ptr(),
+                  dev(x).data_ptr(), y.data_ptr(), 0)
+    assert np.array_equal(y.cpu().numpy(), A * x)
+
+
+@pytest.mark.parametrize('name,make', CASES[:4])
+def test_jacobi_bit_exact(amg, name, make):
+    rng = np.random.RandomState(2)
+    A = make(rng)
+    n = A.shape[0]
+    x0, b = rng.rand(n), rng.rand(n)
+    for omega, iters in ((1.0, 1), (4.0 / 3.0 / 1.9, 3)):
+        xo = x0.copy()
+        orx.jacobi(A, xo, b, iterations=iters, omega=omega, core=oracle.port)
+        xd = dev(x0.copy())
+        amg.relaxation.jacobi(amg.DevMat.from_scipy(A), xd, dev(b), iterations=iters, omega=omega)
+        assert np.array_equal(xd.cpu().numpy(), xo)
+    # BSR(1,1) container -> amg_core.bsr_jacobi arithmetic (different association)
+    Ab = A.tobsr(blocksize=(1, 1))
+    xo = x0.copy(); orx.jacobi(Ab, xo, b, omega=0.7, core=oracle.port)
+    xd = dev(x0.copy()); amg.relaxation.jacobi(amg.DevMat.from_scipy(Ab), xd, dev(b), omega=0.7)
+    assert np.array_equal(xd.cpu().numpy(), xo)
+
+
+@pytest.mark.parametrize('bs', [2, 3, 6])
+def test_bsr_kernels_bit_exact(amg, bs):
+    rng = np.random.RandomState(3)
+    n = 60 * bs
+    A = rand_matrix(n, 0.02, rng).tobsr(blocksize=(bs, bs))
+    x0, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    assert np.array_equal(dA.matvec(dev(x0)).cpu().numpy(), A * x0)
+    assert np.array_equal(dA.residual(dev(x0), dev(b)).cpu().numpy(), b - A * x0)
+    xo = x0.copy(); orx.jacobi(A, xo, b, iterations=2, omega=0.8, core=oracle.port)
+    xd = dev(x0.copy()); amg.relaxation.jacobi(dA, xd, dev(b), iterations=2, omega=0.8)
+    assert np.array_equal(xd.cpu().numpy(), xo)
+    for sweep in ('forward', 'backward', 'symmetric'):
+        xo = x0.copy(); orx.gauss_seidel(A, xo, b, sweep=sweep, core=oracle.port)
+        xd = dev(x0.copy()); amg.relaxation.gauss_seidel(dA, xd, dev(b), sweep=sweep)     # sequential on device
+        assert np.array_equal(xd.cpu().numpy(), xo), sweep
+    # block-multicolour sweep == sequential sweep over the colour-grouped block rows
+    G = sp.csr_matrix((np.ones(len(A.indices)), A.indices, A.indptr), shape=(n // bs, n // bs))
+    colors = amg.relaxation.vertex_coloring(G)
+    assert np.array_equal(colors, orx.vertex_coloring_mis(G, oracle.port))
+    idx, ptr = amg.relaxation.color_ordering(colors)
+    xo = x0.copy()
+    data = np.ravel(A.data)
+    for i in idx:
+        oracle.port.bsr_gauss_seidel(A.indptr, A.indices, data, xo, b, int(i), int(i) + 1, 1, bs)
+    for i in idx[::-1]:
+        oracle.port.bsr_gauss_seidel(A.indptr, A.indices, data, xo, b, int(i), int(i) - 1, -1, bs)
+    xd = dev(x0.copy())
+    amg.relaxation.gauss_seidel(dA, xd, dev(b), sweep='symmetric', indices=dev(idx), color_ptr=ptr)
+    assert np.array_equal(xd.cpu().numpy(), xo)
+    # rectangular blocks (P of an elasticity hierarchy: bs x K)
+    P = sp.random(n, 40 * 3, 0.05, random_state=rng, format='csr').tobsr(blocksize=(bs, 3))
+    xc = rng.rand(P.shape[1])
+    assert np.array_equal(amg.DevMat.from_scipy(P).matvec(dev(xc)).cpu().numpy(), P * xc)
+
+
+@pytest.mark.parametrize('name,make', CASES[:3])
+def test_multicolor_gauss_seidel_bit_exact(amg, name, make):
+    rng = np.random.RandomState(4)
+    A = make(rng)
+    n = A.shape[0]
+    x0, b = rng.rand(n), rng.rand(n)
+    colors = amg.relaxation.vertex_coloring(A)
+    assert np.array_equal(colors, orx.vertex_coloring_mis(A, oracle.port))
+    idx, ptr = amg.relaxation.color_ordering(colors)
+    dA = amg.DevMat.from_scipy(A)
+    for sweep in ('forward', 'backward', 'symmetric'):
+        xo = x0.copy(); orx.gauss_seidel_indexed(A, xo, b, idx, iterations=2, sweep=sweep, core=oracle.port)
+        xd = dev(x0.copy())
+        amg.relaxation.gauss_seidel_indexed(dA, xd, dev(b), dev(idx), iterations=2, sweep=sweep, color_ptr=ptr)
+        assert np.array_equal(xd.cpu().numpy(), xo), sweep
+    # without colour information: strictly sequential on the device, any list (repeats, subsets)
+    lst = rng.randint(0, n, 3 * n // 2).astype('intc')
+    xo = x0.copy(); orx.gauss_seidel_indexed(A, xo, b, lst, sweep='symmetric', core=oracle.port)
+    xd = dev(x0.copy()); amg.relaxation.gauss_seidel_indexed(dA, xd, dev(b), lst, sweep='symmetric')
+    assert np.array_equal(xd.cpu().numpy(), xo)
+    # lexicographic gauss_seidel (sequential on the device)
+    xo = x0.copy(); orx.gauss_seidel(A, xo, b, sweep='symmetric', core=oracle.port)
+    xd = dev(x0.copy()); amg.relaxation.gauss_seidel(dA, xd, dev(b), sweep='symmetric')
+    assert np.array_equal(xd.cpu().numpy(), xo)
+
+
+def test_reference_golden_vectors_on_device(amg):
+    """pyamg/relaxation/tests/test_relaxation.py:139-188, :291-402 through the device path"""
+    rx, D = amg.relaxation, amg.DevMat.from_scipy
+    A = D(lap1d(3))
+    x = dev(np.arange(3, dtype=float)); rx.gauss_seidel(A, x, dev(np.zeros(3)))
+    assert np.allclose(x.cpu().numpy(), [1.0 / 2, 5.0 / 4, 5.0 / 8])
+    x = dev(np.arange(3, dtype=float)); rx.gauss_seidel(A, x, dev(np.zeros(3)), sweep='backward')
+    assert np.allclose(x.cpu().numpy(), [1.0 / 8, 1.0 / 4, 1.0 / 2])
+    x = dev(np.arange(3, dtype=float)); rx.gauss_seidel(A, x, dev(np.array([10., 20, 30])))
+    assert np.allclose(x.cpu().numpy(), [11.0 / 2, 55.0 / 4, 175.0 / 8])
+    x = dev(np.zeros(3)); rx.jacobi(A, x, dev(np.arange(3, dtype=float)))
+    assert np.allclose(x.cpu().numpy(), [0.0, 0.5, 1.0])
+    x = dev(np.arange(3, dtype=float)); rx.jacobi(A, x, dev(np.array([10., 20, 30])), omega=1.0 / 3.0)
+    assert np.allclose(x.cpu().numpy(), 2.0 / 3.0 * np.arange(3) + 1.0 / 3.0 * np.array([5.5, 11.0, 15.5]))
+    x = dev(np.arange(3, dtype=float)); rx.gauss_seidel_indexed(A, x, dev(np.zeros(3)), [2, 1, 0], sweep='backward')
+    assert np.allclose(x.cpu().numpy(), [1.0 / 2, 5.0 / 4, 5.0 / 8])
+    A4 = D(lap1d(4))
+    x = dev(np.ones(4)); rx.gauss_seidel_indexed(A4, x, dev(np.zeros(4)), [0, 3])
+    assert np.allclose(x.cpu().numpy(), [0.5, 1.0, 1.0, 0.5])
+    x = dev(np.ones(4)); rx.gauss_seidel_indexed(A4, x, dev(np.zeros(4)), [0, 0])
+    assert np.allclose(x.cpu().numpy(), [0.5, 1.0, 1.0, 1.0])
+
+
+def test_argument_validation(amg):
+    """TestCommonRelaxation, test_relaxation.py:23-102: TypeError for dtype mismatch, ValueError
+    for bad sizes / non-contiguous x / non-square A"""
+    rx, D = amg.relaxation, amg.DevMat.from_scipy
+    A = D(lap1d(6))
+    b = dev(np.zeros(6))
+    with pytest.raises(TypeError):
+        rx.jacobi(A, torch.zeros(6, dtype=torch.float32, device='cuda'), b)
+    with pytest.raises(ValueError):
+        rx.jacobi(A, dev(np.zeros(5)), b)
+    with pytest.raises(ValueError):
+        rx.gauss_seidel(A, dev(np.zeros(12))[::2], b)
+    with pytest.raises(ValueError):
+        rx.jacobi(D(sp.random(6, 5, 0.5, format='csr')), dev(np.zeros(6)), b)
+    with pytest.raises(ValueError):
+        rx.gauss_seidel(A, dev(np.zeros(6)), b, sweep='sideways')
+    with pytest.raises(TypeError):
+        amg.amg_core.jacobi(A.indptr.long(), A.indices, A.data, dev(np.zeros(6)), b, dev(np.zeros(6)), 0, 6, 1, [1.0])
+
+
+def test_dot_norm_dense(amg):
+    rng = np.random.RandomState(5)
+    for n in (1, 7, 1000, 1 << 20):
+        x, y = rng.rand(n), rng.rand(n)
+        assert abs(amg.linalg.dot(dev(x), dev(y)) - np.dot(x, y)) <= 1e-13 * np.dot(x, y)   # reduction order differs
+    M = rng.rand(37, 37); v = rng.rand(37)
+    out = torch.empty(37, dtype=torch.float64, device='cuda')
+    amg._lib.call('b200amg_dense_matvec', 37, dev(M).data_ptr(), dev(v).data_ptr(), out.data_ptr(), 0)
+    assert np.allclose(out.cpu().numpy(), M @ v, rtol=1e-14)
