@@ -106,8 +106,10 @@ int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, voi
 
 /* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
  *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */
-/* Row-wise C = A B with SORTED column indices, exact zeros dropped (scipy drops them too);
- * values bit-identical to scipy's csr_matmat (same accumulation order, no FMA).
+/* Row-wise C = A B, exact zeros dropped (scipy drops them too); values bit-identical to scipy's
+ * csr_matmat (same accumulation order, no FMA).  scipy_order == 0: rows SORTED by column;
+ * scipy_order != 0: every row in scipy's own output order (reverse first touch), so that a
+ * chained product (R*A)*P accumulates in exactly the reference's order.
  *  1. b200amg_spgemm_count : ub[i] = number of products of row i;
  *  2. b200amg_exclusive_scan_i64(ub) -> ubp[n_row+1] (scratch offsets, ubp[n_row] = total);
  *  3. b200amg_spgemm_numeric: expand-sort-compress every row into the scratch Tj/Tx (both sized
@@ -121,7 +123,7 @@ int b200amg_spgemm_count(int n_row, const int *Ap, const int *Aj, const int *Bp,
 int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, const double *Ax,
                            const int *Bp, const int *Bj, const double *Bx, const long long *ub,
                            const long long *ubp, unsigned long long *Tk, int *Tj, double *Tx,
-                           int *cnt, int *work, void *stream);
+                           int *cnt, int *work, int scipy_order, void *stream);
 int b200amg_spgemm_compact(int n_row, const long long *ubp, const int *Tj, const double *Tx,
                            const int *Cp, int *Cj, double *Cx, void *stream);
 /* out[0..n] = exclusive prefix sums of in[0..n) (out[n] = total);
@@ -154,6 +156,12 @@ int b200amg_tentative_fill(int n, const int *agg, const double *node_val, const 
 int b200amg_csr_sub_sorted(int n_row, const int *Ap, const int *Aj, const double *Ax, const int *Bp,
                            const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
                            int *Cj, double *Cx, void *stream);
+
+/* the same for rows in any order (scipy csr_binop_csr_general): output in reverse first-touch
+ * order over (A's row, then B's row) -- the storage order the reference's P = T - U ends up with */
+int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, const double *Ax, const int *Bp,
+                            const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
+                            int *Cj, double *Cx, void *stream);
 
 /* ---- host-side, inherently sequential setup steps whose INTEGER result must be identical
  *      to the reference (arrays are HOST pointers) ------------------------------------------ */

@@ -46,7 +46,7 @@ _SIGS = {
     'b200amg_extract_diag': (c_int, [c_int, c_int, p, p, p, p, p]),
     'b200amg_dense_matvec': (c_int, [c_int, p, p, p, p]),
     'b200amg_spgemm_count': (c_int, [c_int, p, p, p, p, p]),
-    'b200amg_spgemm_numeric': (c_int, [c_int, p, p, p, p, p, p, p, p, p, p, p, p, p, p]),
+    'b200amg_spgemm_numeric': (c_int, [c_int, p, p, p, p, p, p, p, p, p, p, p, p, p, c_int, p]),
     'b200amg_spgemm_compact': (c_int, [c_int, p, p, p, p, p, p, p]),
     'b200amg_exclusive_scan_i64': (c_int, [c_longlong, p, p, p, p]),
     'b200amg_exclusive_scan_i32': (c_int, [c_longlong, p, p, p, p]),
@@ -58,6 +58,7 @@ _SIGS = {
     'b200amg_flag_nonneg': (c_int, [c_int, p, p, p]),
     'b200amg_tentative_fill': (c_int, [c_int, p, p, p, p, p, p]),
     'b200amg_csr_sub_sorted': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
+    'b200amg_csr_sub_general': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
     'b200amg_vertex_coloring_mis_host': (c_int, [c_int, p, p, p]),
     'b200amg_standard_aggregation_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),

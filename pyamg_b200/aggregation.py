@@ -79,19 +79,22 @@ def _scaled(A, v, c=None):
     return DevMat(A.indptr, A.indices, out, A.shape, (1, 1), 'csr', A.has_sorted_indices)
 
 
-def csr_subtract(A, B):
-    """A - B, sorted operands, zero results dropped (scipy csr_binop_csr)"""
+def csr_subtract(A, B, general=True):
+    """A - B with zero results dropped: scipy csr_binop_csr, canonical (sorted operands, sorted
+    result) or general (any order in, reverse first-touch order out -- what the reference's
+    `T - D_inv_S*T` produces, because csr_matmat returns unsorted rows)"""
+    fn = 'b200amg_csr_sub_general' if general else 'b200amg_csr_sub_sorted'
     n = A.shape[0]
     st = _stream()
     cnt = torch.empty(max(n, 1), dtype=torch.int32, device=A.data.device)
     args = (n, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr), _ptr(B.indices), _ptr(B.data))
-    _lib.call('b200amg_csr_sub_sorted', *args, 0, _ptr(cnt), 0, 0, 0, st)
+    _lib.call(fn, *args, 0, _ptr(cnt), 0, 0, 0, st)
     Cp = _scan_i32(cnt[:n])
     nnz = int(Cp[-1].item())
     Cj = torch.empty(nnz, dtype=torch.int32, device=A.data.device)
     Cx = torch.empty(nnz, dtype=torch.float64, device=A.data.device)
-    _lib.call('b200amg_csr_sub_sorted', *args, 1, 0, _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
-    return DevMat(Cp, Cj, Cx, A.shape, (1, 1), 'bsr', True)
+    _lib.call(fn, *args, 1, 0, _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
+    return DevMat(Cp, Cj, Cx, A.shape, (1, 1), 'bsr', not general)
 
 
 def inverse_diagonal(A):
@@ -107,7 +110,7 @@ def jacobi_prolongation_smoother(A, T, omega=4.0 / 3.0, degree=1, rho=None):
     S = _scaled(A, dinv, omega / rho)
     P = T
     for _ in range(degree):
-        P = csr_subtract(P, matmat(S, P))
+        P = csr_subtract(P, matmat(S, P, scipy_order=True), general=True)
     return P, rho
 
 
@@ -161,9 +164,13 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     while len(levels) < max_levels and levels[-1].A.shape[0] > max_coarse:
         lvl = levels[-1]
         k = len(levels) - 1
-        A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
-        agg, nagg, roots = standard_aggregation(A)
+        # the reference aggregates on the matrix AS STORED at that moment (unsorted rows straight
+        # out of csr_matmat on coarse levels; pass 2 of the aggregation picks the FIRST aggregated
+        # neighbour in storage order) and only afterwards sorts it in place inside
+        # jacobi_prolongation_smoother -> get_diagonal (pyamg/util/utils.py:571)
+        agg, nagg, roots = standard_aggregation(lvl.A)
         T, Bc = fit_candidates_scalar(agg, nagg, lvl.B)
+        A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
         if mname == 'jacobi':
             rho = rho_override[k][0] if rho_override is not None and k < len(rho_override) else None
             P, lvl.rho_smooth = jacobi_prolongation_smoother(A, T, mkw.get('omega', 4.0 / 3.0), mkw.get('degree', 1), rho)
@@ -173,9 +180,9 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         if keep:
             lvl.AggOp, lvl.T, lvl.Cpts = agg, T, roots
         lvl.P, lvl.R = P, R
-        Ac = matmat(matmat(R, A), P)
+        Ac = matmat(matmat(R, A, scipy_order=True), P, scipy_order=True)
         levels.append(multilevel_solver.level())
-        levels[-1].A = DevMat(Ac.indptr, Ac.indices, Ac.data, Ac.shape, (1, 1), 'bsr', True)
+        levels[-1].A = DevMat(Ac.indptr, Ac.indices, Ac.data, Ac.shape, (1, 1), 'bsr', False)
         levels[-1].B = Bc
     if rho_override is not None:
         for k, lvl in enumerate(levels[:-1]):

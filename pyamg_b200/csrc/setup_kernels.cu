@@ -74,6 +74,39 @@ __global__ void __launch_bounds__(256) csr_sub_sorted_kernel(int n, const int *_
     if (!pass) cnt[i] = o;
 }
 
+
+// C = A - B for rows in ANY order without duplicates, restating scipy's csr_binop_csr_general
+// (taken by `T - U` when U comes unsorted out of csr_matmat, pyamg/aggregation/smooth.py:203-206):
+// columns are threaded on a list in first-touch order (A's row, then B's row) and emitted in
+// REVERSE of that order; zero results are not stored.  Rows are short (A: 1 entry, B: a few).
+__global__ void __launch_bounds__(256) csr_sub_general_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                              const double *__restrict__ Ax, const int *__restrict__ Bp,
+                                                              const int *__restrict__ Bj, const double *__restrict__ Bx,
+                                                              int pass, int *__restrict__ cnt, const int *__restrict__ Cp,
+                                                              int *__restrict__ Cj, double *__restrict__ Cx)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const int a0 = Ap[i], a1 = Ap[i + 1], b0 = Bp[i], b1 = Bp[i + 1];
+    int o = pass ? Cp[i] : 0;
+    for (int q = b1 - 1; q >= b0; --q) {                 // B-only columns, last touched first
+        const int col = Bj[q];
+        bool inA = false;
+        for (int p = a0; p < a1; ++p) inA |= (Aj[p] == col);
+        if (inA) continue;
+        const double r = sub_rn(0.0, add_rn(0.0, Bx[q]));
+        if (r != 0.0) { if (pass) { Cj[o] = col; Cx[o] = r; } ++o; }
+    }
+    for (int p = a1 - 1; p >= a0; --p) {                 // A's columns (with B's value if present)
+        const int col = Aj[p];
+        double bv = 0.0;
+        for (int q = b0; q < b1; ++q) if (Bj[q] == col) bv = add_rn(bv, Bx[q]);
+        const double r = sub_rn(add_rn(0.0, Ax[p]), bv);
+        if (r != 0.0) { if (pass) { Cj[o] = col; Cx[o] = r; } ++o; }
+    }
+    if (!pass) cnt[i] = o;
+}
+
 // T (n x nagg, at most one entry per row): row i has (agg[i], node_val[i]) unless agg[i] < 0.
 // Tp must already hold the exclusive scan of (agg >= 0).
 __global__ void __launch_bounds__(256) tentative_fill_kernel(int n, const int *__restrict__ agg, const double *__restrict__ node_val,
@@ -134,4 +167,13 @@ extern "C" int b200amg_csr_sub_sorted(int n_row, const int *Ap, const int *Aj, c
     if (n_row <= 0) return 0;
     csr_sub_sorted_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
     return check_launch("csr_sub_sorted_kernel");
+}
+
+extern "C" int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, const double *Ax, const int *Bp,
+                                       const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp, int *Cj,
+                                       double *Cx, void *stream)
+{
+    if (n_row <= 0) return 0;
+    csr_sub_general_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
+    return check_launch("csr_sub_general_kernel");
 }

@@ -111,7 +111,7 @@ template <class G>
 __device__ __forceinline__ int spgemm_row(int a_lo, int a_hi, const int *__restrict__ Aj, const double *__restrict__ Ax,
                                           const int *__restrict__ Bp, const int *__restrict__ Bj,
                                           const double *__restrict__ Bx, u64 *keys, double *vals, int m,
-                                          int *Tj, double *Tx, int *s_scan)
+                                          int *Tj, double *Tx, int *s_scan, bool scipy_order)
 {
     const int tid = G::tid(), gs = G::size();
     int base = 0;
@@ -133,39 +133,51 @@ __device__ __forceinline__ int spgemm_row(int a_lo, int a_hi, const int *__restr
     }
     G::sync();
     bitonic_sort<G, true>(keys, vals, m);
-    // heads fold their run in sequence order; low word of the key becomes 0 (not a head),
-    // 1 (head, sum == 0: dropped) or 2 (head kept).  Only the high word of a neighbour's key
+    // heads fold their run in sequence order; the low word of a head's key keeps its sequence
+    // number (= scipy's first touch of that column), non-heads get 0xFFFFFFFF and heads whose
+    // sum is exactly 0.0 get 0xFFFFFFFE (dropped).  Only the high word of a neighbour's key
     // is ever read by another thread, and it never changes.
     for (int e = tid; e < m; e += gs) {
-        const unsigned col = (unsigned)(keys[e] >> 32);
-        unsigned tag = 0;
+        const u64 key = keys[e];
+        const unsigned col = (unsigned)(key >> 32);
+        unsigned tag = 0xFFFFFFFFu;
         if (e == 0 || (unsigned)(keys[e - 1] >> 32) != col) {
             double s = 0.0;
             int f = e;
             do { s = add_rn(s, vals[f]); ++f; } while (f < m && (unsigned)(keys[f] >> 32) == col);
             vals[e] = s;
-            tag = (s != 0.0) ? 2u : 1u;
+            tag = (s != 0.0) ? (unsigned)key : 0xFFFFFFFEu;
         }
         keys[e] = ((u64)col << 32) | tag;
     }
     G::sync();
+    // compaction of the kept heads to the front of keys/vals (in place: every element is read
+    // into registers before the scan's barrier and written after it, and kept+ex <= e)
     int kept = 0;
     for (int e0 = 0; e0 < m; e0 += gs) {
         const int e = e0 + tid;
         int flag = 0;
-        unsigned col = 0;
+        u64 key = 0;
         double v = 0.0;
         if (e < m) {
-            const u64 key = keys[e];
-            flag = ((unsigned)key == 2u);
-            col = (unsigned)(key >> 32);
+            key = keys[e];
+            flag = ((unsigned)key < 0xFFFFFFFEu);
             v = vals[e];
         }
         int tot;
         const int ex = G::exscan(flag, &tot, s_scan);
-        if (flag) { Tj[kept + ex] = (int)col; Tx[kept + ex] = v; }
+        G::sync();
+        if (flag) {
+            const unsigned col = (unsigned)(key >> 32), seq = (unsigned)key;
+            // scipy order = reverse first touch: ascending (0xFFFFFFFF - seq)
+            keys[kept + ex] = scipy_order ? (((u64)(0xFFFFFFFFu - seq) << 32) | col) : (u64)col;
+            vals[kept + ex] = v;
+        }
         kept += tot;
     }
+    G::sync();
+    if (scipy_order) bitonic_sort<G, true>(keys, vals, kept);
+    for (int t = tid; t < kept; t += gs) { Tj[t] = (int)(unsigned)keys[t]; Tx[t] = vals[t]; }
     return kept;
 }
 
@@ -176,7 +188,7 @@ __global__ void __launch_bounds__(32 * WPB) spgemm_warp_kernel(const int *__rest
                                                                const double *__restrict__ Ax, const int *__restrict__ Bp,
                                                                const int *__restrict__ Bj, const double *__restrict__ Bx,
                                                                const long long *__restrict__ ubp, int *Tj, double *Tx,
-                                                               int *cnt)
+                                                               int *cnt, bool so)
 {
     __shared__ u64 s_k[WPB][CAP];
     __shared__ double s_v[WPB][CAP];
@@ -186,7 +198,7 @@ __global__ void __launch_bounds__(32 * WPB) spgemm_warp_kernel(const int *__rest
     const int i = rows[r];
     const long long o = ubp[i];
     const int m = (int)(ubp[i + 1] - o);
-    const int kept = spgemm_row<WarpGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, s_k[w], s_v[w], m, Tj + o, Tx + o, nullptr);
+    const int kept = spgemm_row<WarpGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, s_k[w], s_v[w], m, Tj + o, Tx + o, nullptr, so);
     if ((threadIdx.x & 31) == 0) cnt[i] = kept;
 }
 
@@ -195,7 +207,7 @@ template <int CAP>
 __global__ void spgemm_cta_kernel(const int *__restrict__ rows, int nrows, const int *__restrict__ Ap,
                                   const int *__restrict__ Aj, const double *__restrict__ Ax,
                                   const int *__restrict__ Bp, const int *__restrict__ Bj, const double *__restrict__ Bx,
-                                  const long long *__restrict__ ubp, int *Tj, double *Tx, int *cnt)
+                                  const long long *__restrict__ ubp, int *Tj, double *Tx, int *cnt, bool so)
 {
     extern __shared__ __align__(16) unsigned char s_raw[];
     __shared__ int s_scan[33];
@@ -204,7 +216,7 @@ __global__ void spgemm_cta_kernel(const int *__restrict__ rows, int nrows, const
     const int i = rows[blockIdx.x];
     const long long o = ubp[i];
     const int m = (int)(ubp[i + 1] - o);
-    const int kept = spgemm_row<CtaGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, s_k, s_v, m, Tj + o, Tx + o, s_scan);
+    const int kept = spgemm_row<CtaGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, s_k, s_v, m, Tj + o, Tx + o, s_scan, so);
     if (threadIdx.x == 0) cnt[i] = kept;
 }
 
@@ -214,13 +226,13 @@ __global__ void __launch_bounds__(1024) spgemm_big_kernel(const int *__restrict_
                                                           const double *__restrict__ Ax, const int *__restrict__ Bp,
                                                           const int *__restrict__ Bj, const double *__restrict__ Bx,
                                                           const long long *__restrict__ ubp, u64 *Tk, int *Tj, double *Tx,
-                                                          int *cnt)
+                                                          int *cnt, bool so)
 {
     __shared__ int s_scan[33];
     const int i = rows[blockIdx.x];
     const long long o = ubp[i];
     const int m = (int)(ubp[i + 1] - o);
-    const int kept = spgemm_row<CtaGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, Tk + o, Tx + o, m, Tj + o, Tx + o, s_scan);
+    const int kept = spgemm_row<CtaGroup>(Ap[i], Ap[i + 1], Aj, Ax, Bp, Bj, Bx, Tk + o, Tx + o, m, Tj + o, Tx + o, s_scan, so);
     if (threadIdx.x == 0) cnt[i] = kept;
 }
 
@@ -273,32 +285,34 @@ extern "C" long long b200amg_scan_scratch_elems(long long n) { return scan_scrat
 
 extern "C" int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, const double *Ax, const int *Bp,
                                       const int *Bj, const double *Bx, const long long *ub, const long long *ubp,
-                                      unsigned long long *Tk, int *Tj, double *Tx, int *cnt, int *work, void *stream)
+                                      unsigned long long *Tk, int *Tj, double *Tx, int *cnt, int *work, int scipy_order,
+                                      void *stream)
 {
     if (n_row < 0) return set_err(B200AMG_EINVAL, "spgemm_numeric: n_row < 0");
     if (n_row == 0) return 0;
     cudaStream_t st = S(stream);
     B200_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * n_row, st));
     int *perm = work + 64;
+    const bool so = scipy_order != 0;
     int off[NBINS + 1];
     const BinLimits lim{{32, 128, 512, 2048, 8192}};
     B200_TRY(bin_rows(n_row, ub, lim, perm, work, off, st));
 #define ARGS(b) perm + off[b], off[b + 1] - off[b], Ap, Aj, Ax, Bp, Bj, Bx, ubp
     int n;
     if ((n = off[1] - off[0]) > 0) {
-        spgemm_warp_kernel<32, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(0), Tj, Tx, cnt);
+        spgemm_warp_kernel<32, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(0), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_warp_kernel<32>"));
     }
     if ((n = off[2] - off[1]) > 0) {
-        spgemm_warp_kernel<128, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(1), Tj, Tx, cnt);
+        spgemm_warp_kernel<128, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(1), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_warp_kernel<128>"));
     }
     if ((n = off[3] - off[2]) > 0) {
-        spgemm_cta_kernel<512><<<n, 128, 512 * 16, st>>>(ARGS(2), Tj, Tx, cnt);
+        spgemm_cta_kernel<512><<<n, 128, 512 * 16, st>>>(ARGS(2), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<512>"));
     }
     if ((n = off[4] - off[3]) > 0) {
-        spgemm_cta_kernel<2048><<<n, 256, 2048 * 16, st>>>(ARGS(3), Tj, Tx, cnt);
+        spgemm_cta_kernel<2048><<<n, 256, 2048 * 16, st>>>(ARGS(3), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<2048>"));
     }
     if ((n = off[5] - off[4]) > 0) {
@@ -307,12 +321,12 @@ extern "C" int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, c
             B200_CUDA(cudaFuncSetAttribute(spgemm_cta_kernel<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 16));
             attr_set = true;
         }
-        spgemm_cta_kernel<8192><<<n, 512, 8192 * 16, st>>>(ARGS(4), Tj, Tx, cnt);
+        spgemm_cta_kernel<8192><<<n, 512, 8192 * 16, st>>>(ARGS(4), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<8192>"));
     }
     if ((n = off[6] - off[5]) > 0) {
         if (!Tk) return set_err(B200AMG_ENOMEM, "spgemm_numeric: rows with > 8192 products need the Tk scratch");
-        spgemm_big_kernel<<<n, 1024, 0, st>>>(ARGS(5), Tk, Tj, Tx, cnt);
+        spgemm_big_kernel<<<n, 1024, 0, st>>>(ARGS(5), Tk, Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_big_kernel"));
     }
 #undef ARGS

@@ -160,9 +160,10 @@ def _scan_i64(v):
     return out
 
 
-def matmat(A, B):
-    """C = A B for scalar CSR/BSR(1,1) operands: sorted rows, exact zeros dropped, values
-    bit-identical to scipy's csr_matmat (see csrc/spgemm.cu)."""
+def matmat(A, B, scipy_order=False):
+    """C = A B for scalar CSR/BSR(1,1) operands: exact zeros dropped, values bit-identical to
+    scipy's csr_matmat (see csrc/spgemm.cu).  Rows sorted by column, or (scipy_order=True) in
+    scipy's own reverse-first-touch order."""
     if not (A.is_scalar and B.is_scalar):
         raise NotImplementedError('matmat: only scalar (1x1 block) operands')
     if A.shape[1] != B.shape[0]:
@@ -183,13 +184,13 @@ def matmat(A, B):
     work = torch.empty(n + 256, dtype=torch.int32, device=dev)
     _lib.call('b200amg_spgemm_numeric', n, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr),
               _ptr(B.indices), _ptr(B.data), _ptr(ub), _ptr(ubp), _ptr(Tk), _ptr(Tj), _ptr(Tx), _ptr(cnt),
-              _ptr(work), st)
+              _ptr(work), int(bool(scipy_order)), st)
     Cp = _scan_i32(cnt[:n])
     nnz = int(Cp[-1].item())
     Cj = torch.empty(nnz, dtype=torch.int32, device=dev)
     Cx = torch.empty(nnz, dtype=torch.float64, device=dev)
     _lib.call('b200amg_spgemm_compact', n, _ptr(ubp), _ptr(Tj), _ptr(Tx), _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
-    return DevMat(Cp, Cj, Cx, (A.shape[0], B.shape[1]), (1, 1), 'csr', True)
+    return DevMat(Cp, Cj, Cx, (A.shape[0], B.shape[1]), (1, 1), 'csr', not scipy_order)
 
 
 def transpose(A):
@@ -209,6 +210,8 @@ def transpose(A):
     return DevMat(Bp, Bi, Bx, (n_col, n_row), (1, 1), A.format, True)
 
 
-def galerkin(R, A, P):
-    """A_c = (R A) P, evaluated left to right like the reference (aggregation.py:429)."""
-    return matmat(matmat(R, A), P)
+def galerkin(R, A, P, scipy_order=True):
+    """A_c = (R A) P, evaluated left to right like the reference (aggregation.py:429).  With
+    scipy_order (default) the intermediate R A and the result keep scipy's row-internal order, so
+    values AND storage order equal the reference's; otherwise both are column-sorted."""
+    return matmat(matmat(R, A, scipy_order), P, scipy_order)

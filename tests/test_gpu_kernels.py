@@ -60,9 +60,9 @@ def test_spmv_family_bit_exact(amg, name, make):
     assert np.array_equal(y, A * x)
     r = dA.residual(dev(x), dev(b)).cpu().numpy()
     assert np.array_equal(r, b - A * x)
-    xx = dev(b.copy())
+    xx, dx = dev(b.copy()), dev(x)
     amg._lib.call('b200amg_csr_matvec_add', n, dA.indptr.data_ptr(), dA.indices.data_ptr(), dA.data.data_ptr(),
-                  dev(x).data_ptr(), xx.data_ptr(), 0)
+                  dx.data_ptr(), xx.data_ptr(), 0)
     torch.cuda.synchronize()
     assert np.array_equal(xx.cpu().numpy(), b + A * x)
 
@@ -77,8 +77,9 @@ def test_spmv_unaligned_and_rectangular(amg):
     pad_j = torch.cat([torch.zeros(1, dtype=torch.int32, device='cuda'), dA.indices])[1:]
     pad_x = torch.cat([torch.zeros(1, dtype=torch.float64, device='cuda'), dA.data])[1:]
     y = torch.empty(1000, dtype=torch.float64, device='cuda')
+    dx = dev(x)
     amg._lib.call('b200amg_csr_matvec', 1000, 333, dA.indptr.data_ptr(), pad_j.data_ptr(), pad_x.data_ptr(),
-                  dev(x).data_ptr(), y.data_ptr(), 0)
+                  dx.data_ptr(), y.data_ptr(), 0)
     assert np.array_equal(y.cpu().numpy(), A * x)
 
 
@@ -213,5 +214,7 @@ def test_dot_norm_dense(amg):
         assert abs(amg.linalg.dot(dev(x), dev(y)) - np.dot(x, y)) <= 1e-13 * np.dot(x, y)   # reduction order differs
     M = rng.rand(37, 37); v = rng.rand(37)
     out = torch.empty(37, dtype=torch.float64, device='cuda')
-    amg._lib.call('b200amg_dense_matvec', 37, dev(M).data_ptr(), dev(v).data_ptr(), out.data_ptr(), 0)
-    assert np.allclose(out.cpu().numpy(), M @ v, rtol=1e-14)
+    dM, dv = dev(M), dev(v)                       # keep the device copies alive across the call
+    amg._lib.call('b200amg_dense_matvec', 37, dM.data_ptr(), dv.data_ptr(), out.data_ptr(), 0)
+    torch.cuda.synchronize()
+    assert np.allclose(out.cpu().numpy(), M @ v, rtol=1e-13)
