@@ -149,3 +149,281 @@ def time_cpu_cycles(levels, b, cycles, warm=0):
         S._cycle(0, x, b, 'V')
     dt = time.perf_counter() - t0
     return dt / cycles, oracle.kind
+
+
+# ---------------------------------------------------------------------------------------------
+def dist_env():
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    return rank, world, local
+
+
+def build_problem(grid):
+    """config 2 of BASELINE.json: poisson((g,g,g)) + SA(Jacobi 4/3 pre/post, max_coarse=500), seed 0,
+    built on the device by pyamg_b200 (bit-identical to the reference-built hierarchy, tests/)."""
+    import pyamg_b200 as amg
+    A = amg.gallery.poisson((grid, grid, grid))
+    np.random.seed(0)
+    ml = amg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=500)
+    b = np.random.rand(A.shape[0])
+    return ml, b
+
+
+def level_table(ml):
+    return [[int(l.A.shape[0]), int(l.A.nnz)] for l in ml.levels]
+
+
+def cpu_cycles_timed(levels, b, cycles, warm):
+    """-> (seconds per V-cycle, kind, x after `warm + cycles` cycles from x0 = 0)"""
+    import oracle
+    from oracle import multilevel as oml
+    S = oml.Solver(levels, core=oracle.core, wasted_prolongation=True)
+    S.coarse_matrix()
+    x = np.zeros_like(b)
+    for _ in range(warm):
+        S._cycle(0, x, b, 'V')
+    t0 = time.perf_counter()
+    for _ in range(cycles):
+        S._cycle(0, x, b, 'V')
+    dt = time.perf_counter() - t0
+    return dt / max(cycles, 1), oracle.kind, x
+
+
+def run_b200(args):
+    import torch
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device (the product path has no CPU fallback)')
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    import pyamg_b200 as amg
+
+    t0 = time.perf_counter()
+    ml, b = build_problem(args.grid)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t0
+    n = b.size
+    st = ml._stream if ml._stream is not None else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident-data timing: K graph-replayed V-cycles on (x, b) living in HBM -------------
+    ml.solve(b, maxiter=0, _norms=False)          # builds the engine, loads b, x = 0
+    st = ml._stream
+    for _ in range(args.warmup):
+        ml.cycle_device('V')
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = amg._lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()        # no-op unless run under `ncu --profile-from-start off`
+    with torch.cuda.stream(st):
+        e0.record(st)
+        for _ in range(args.steps):
+            ml.cycle_device('V')
+        e1.record(st)
+    barrier()
+    torch.cuda.profiler.stop()
+    ms = e0.elapsed_time(e1)
+    launches = amg._lib.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / args.steps
+    value = world * 1000.0 / ms_step            # replicas: every rank ran its own K cycles
+    return dict(ml=ml, b=b, n=n, ms_step=ms_step, value=value, launches=launches, clocks=clocks,
+                setup_s=setup_s, rank=rank, world=world, dist=dist, barrier=barrier)
+
+
+def measure_e2e(R, args):
+    """the public call a reference user makes for one preconditioner application:
+    x_host = ml.solve(b_host, maxiter=1) -- H2D of b and D2H of x inside the timed region"""
+    import torch
+    ml = R['ml']
+    bh = torch.from_numpy(R['b']).pin_memory()
+    for _ in range(max(1, min(args.warmup, 3))):
+        ml.solve(bh, maxiter=1, _norms=False)
+    R['barrier']()
+    cur = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(cur)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        xh = ml.solve(bh, maxiter=1, _norms=False)
+    e1.record(cur)
+    R['barrier']()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    ms = max(e0.elapsed_time(e1), wall_ms)        # events and host clock bracket the same synchronous calls
+    if R['dist'] is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        R['dist'].all_reduce(t, op=R['dist'].ReduceOp.MAX)
+        ms = float(t.item())
+    assert xh.shape[0] == R['n']
+    return {'value': R['world'] * 1000.0 * args.steps / ms, 'unit': 'V-cycles/s',
+            'h2d_bytes_per_step': 8 * R['n'], 'd2h_bytes_per_step': 8 * R['n'],
+            'call': 'multilevel_solver.solve(b_host_pinned, maxiter=1) -> x_host (aspreconditioner matvec)'}
+
+
+def measure_roofline(R, reps=5):
+    """dominant kernel = csr_stream_kernel<JACOBI> on level 0 (pre- and post-smoothing sweep).
+    Its duration is measured live with CUDA events around each operation of un-graphed cycles
+    (b200amg_vcycle_profile), on the engine's stream."""
+    ml = R['ml']
+    ml.profile_cycle('V')                                    # warm
+    acc = {}
+    tot = 0.0
+    for _ in range(reps):
+        for op, lev, ms in ml.profile_cycle('V'):
+            acc.setdefault((op, lev), []).append(ms)
+            tot += ms
+    tot /= reps
+    share = {('%s@L%d' % k): round(float(np.mean(v)), 4) for k, v in acc.items()}
+    A0 = ml.levels[0].A
+    nB = jacobi_bytes(A0.shape[0], A0.nnz)
+    t_j = float(np.mean(acc[('presmooth', 0)] + acc[('postsmooth', 0)]))     # ms per launch
+    peak, how = measured_peak()
+    ach = nB / (t_j * 1e-3) / 1e9
+    t_r = float(np.mean(acc[('residual', 0)]))
+    return {'bound': 'hbm', 'kernel': 'csr_stream_kernel<OP_JACOBI> level 0', 'achieved': round(ach, 1),
+            'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': round(ach / peak, 4),
+            'algorithmic_bytes_per_launch': nB, 'ms_per_launch': round(t_j, 4), 'traffic': None,
+            'residual_L0_GBs': round((spmv_bytes(A0.shape[0], A0.shape[1], A0.nnz) + 8 * A0.shape[0]) / (t_r * 1e-3) / 1e9, 1),
+            'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
+
+
+def cpu_baseline(R, args):
+    """reference CPU path (scipy SpMV + the reference's compiled amg_core smoothers when
+    oracle/_ref is built, else the C port) on this box's host cores, same hierarchy, same b."""
+    levels = host_levels(R['ml'])
+    sec, kind, x_cpu = cpu_cycles_timed(levels, R['b'], args.cpu_cycles, warm=1)
+    # parity of the very same run: GPU x after (1 + cpu_cycles) cycles from zero vs the CPU x
+    x_gpu = R['ml'].solve(R['b'], maxiter=1 + args.cpu_cycles, _norms=False)
+    err = float(np.max(np.abs(x_gpu - x_cpu)) / max(np.max(np.abs(x_cpu)), 1e-300))
+    return ({'value': 1.0 / sec, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(), 'kind': kind,
+             'sample': '%d full V(1,1)-cycles of the same %d-level hierarchy after 1 warm-up cycle; serial '
+                       'reference code (scipy csr/bsr_matvec + amg_core jacobi), incl. the fork\'s second '
+                       'P*coarse_x per level (multilevel.py:548)' % (args.cpu_cycles, len(levels)),
+             's_per_cycle': sec},
+            {'cycles': 1 + args.cpu_cycles, 'max_rel_diff_x_vs_cpu_reference': err, 'bit_identical': bool(np.array_equal(x_gpu, x_cpu))})
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the V-cycle (oracle/_ref =
+    its compiled _amg_core + scipy SpMV, glued exactly like pyamg/multilevel.py:473-548), serial,
+    on the box's host cores; same config/metric/unit.  Only the TIMED path matters here: the
+    hierarchy it cycles over is produced by the device setup when a GPU is present (seconds
+    instead of ~200 s of CPU setup; bit-identical to the reference-built one, tests/), else by the
+    CPU restatement oracle/sa.py."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    import oracle
+    from oracle import multilevel as oml
+    budget_s = float(os.environ.get('B200AMG_REF_BUDGET_S', '200'))
+    how = None
+    try:
+        import torch
+        if torch.cuda.is_available():
+            ml, b = build_problem(args.grid)
+            levels = host_levels(ml)
+            how = 'device setup (pyamg_b200), downloaded to the host'
+            del ml
+            torch.cuda.empty_cache()
+    except Exception as exc:                                           # noqa: BLE001
+        how = None
+        sys.stderr.write('reference arm: device setup unavailable (%s); CPU setup\n' % (exc,))
+    if how is None:
+        from oracle import sa
+        import scipy.sparse as sp
+        g = args.grid
+        I = sp.identity(g, format='csr')
+        T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(g, g), format='csr')
+        A = (sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T)).tocsr()
+        A.sort_indices()
+        np.random.seed(0)
+        levels = sa.smoothed_aggregation_hierarchy(A, presmoother=JAC, postsmoother=JAC, max_coarse=500, core=oracle.core)
+        b = np.random.rand(A.shape[0])
+        how = 'CPU setup (oracle/sa.py)'
+    S = oml.Solver(levels, core=oracle.core, wasted_prolongation=True)
+    S.coarse_matrix()
+    x = np.zeros_like(b)
+    t0 = time.perf_counter()
+    S._cycle(0, x, b, 'V')
+    t_first = time.perf_counter() - t0
+    warm_done = 1
+    while warm_done < args.warmup and (warm_done + 1) * t_first < 0.25 * budget_s:
+        S._cycle(0, x, b, 'V')
+        warm_done += 1
+    timed = max(1, min(args.steps, int(0.75 * budget_s / max(t_first, 1e-9))))
+    t0 = time.perf_counter()
+    for _ in range(timed):
+        S._cycle(0, x, b, 'V')
+    sec = (time.perf_counter() - t0) / timed
+    val = 1.0 / sec
+    sample = ('%d of the %d requested V(1,1)-cycles timed (%d warm-up), each a full cycle over the %d-level '
+              'hierarchy of poisson(%d^3); hierarchy from: %s' % (timed, args.steps, warm_done, len(levels), args.grid, how))
+    out = {'impl': 'reference', 'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1)' % args.grid,
+           'value': val, 'unit': 'V-cycles/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+           'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+           'dtype': 'f64', 'data': 'synthetic',
+           'config': {'workload': 'configs[1]: 3D Poisson %d^3 7-point, smoothed_aggregation_solver, Jacobi(4/3) pre/post, '
+                                  'max_coarse=500, fp64, one V(1,1)-cycle per step' % args.grid,
+                      'levels': [[int(l.A.shape[0]), int(l.A.nnz)] for l in levels]},
+           'cpu_baseline': {'value': val, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(),
+                            'kind': oracle.kind, 'sample': sample},
+           'e2e': {'value': val, 'unit': 'V-cycles/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+           'gpu_launches': 0}
+    print(json.dumps(out))
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+        return
+    R = run_b200(args)
+    e2e = measure_e2e(R, args)
+    roof = measure_roofline(R) if R['rank'] == 0 else None
+    cpu, parity = (None, None)
+    if R['rank'] == 0 and R['world'] == 1 and not args.no_cpu_baseline:
+        cpu, parity = cpu_baseline(R, args)
+    if R['dist'] is not None:
+        R['barrier']()
+        R['dist'].destroy_process_group()
+    if R['rank'] != 0:
+        return
+    ml = R['ml']
+    vb = vcycle_bytes(ml)
+    out = {'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1)' % args.grid,
+           'value': R['value'], 'unit': 'V-cycles/s', 'n_gpus': R['world'], 'steps': args.steps,
+           'warmup': args.warmup, 'ms_per_step': R['ms_step'], 'higher_is_better': True, 'scaling': 'weak',
+           'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+           'config': {'workload': 'configs[1]: 3D Poisson %d^3 7-point, smoothed_aggregation_solver, Jacobi(4/3) pre/post, '
+                                  'max_coarse=500, fp64, one V(1,1)-cycle per step' % args.grid,
+                      'levels': level_table(ml), 'parallelism': 'single GPU' if R['world'] == 1 else
+                      'replicas: %d independent solves, one per GPU' % R['world'],
+                      'l2': 'inputs larger than L2 (level-0 CSR alone is %.2f GB)' % (12e-9 * ml.levels[0].A.nnz),
+                      'setup_s_device': round(R['setup_s'], 2),
+                      'unfused_algorithmic_bytes_per_cycle': vb,
+                      'cycle_GBs_on_unfused_bytes': round(vb / (R['ms_step'] * 1e-3) / 1e9, 1)},
+           'clocks': R['clocks'], 'e2e': e2e, 'gpu_launches': int(R['launches']), 'roofline': roof}
+    if cpu is not None:
+        out['cpu_baseline'] = cpu
+        out['parity_in_run'] = parity
+    print(json.dumps(out))
+
+
+if __name__ == '__main__':
+    main()

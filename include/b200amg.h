@@ -209,6 +209,20 @@ int b200amg_vcycle_create(int nlev, const b200amg_level_desc *levels_host, const
  * graph captured on first use for these (x, b) pointers. */
 int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph,
                        void *stream);
+/* One UN-graphed cycle with a CUDA event after every operation: fills (host arrays, up to
+ * max_ops entries) the operation code, its level and its device time in ms, in execution
+ * order; *n_ops_host = entries written.  Synchronises the stream.  bench.py uses it for the
+ * per-kernel share of a cycle and the roofline of the dominant kernel. */
+#define B200AMG_OP_PRESMOOTH  0
+#define B200AMG_OP_RESIDUAL   1
+#define B200AMG_OP_RESTRICT   2
+#define B200AMG_OP_COARSE     3
+#define B200AMG_OP_PROLONG    4
+#define B200AMG_OP_POSTSMOOTH 5
+#define B200AMG_OP_COPYBACK   6
+int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_kind, int max_ops,
+                           int *op_code_host, int *op_level_host, float *op_ms_host,
+                           int *n_ops_host, void *stream);
 /* rnorm2_dev[0] = ||b - A0 x||^2 on the finest level (residual_norm of multilevel.py:450,461) */
 int b200amg_vcycle_residual_norm2(void *handle, const double *x, const double *b,
                                   double *rnorm2_dev, void *stream);

@@ -64,6 +64,8 @@ _SIGS = {
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),
     'b200amg_vcycle_create': (c_int, [c_int, POINTER(LevelDesc), p, p, c_longlong, POINTER(c_void_p)]),
     'b200amg_vcycle_run': (c_int, [p, p, p, c_int, c_int, p]),
+    'b200amg_vcycle_profile': (c_int, [p, p, p, c_int, c_int, POINTER(c_int), POINTER(c_int),
+                                       POINTER(ctypes.c_float), POINTER(c_int), p]),
     'b200amg_vcycle_residual_norm2': (c_int, [p, p, p, p, p]),
     'b200amg_vcycle_destroy': (c_int, [p]),
 }

@@ -24,7 +24,15 @@ struct GraphKey {
     long long launches;   // kernel nodes in the graph (for b200amg_launch_count)
 };
 
+// per-operation event timing of one un-graphed cycle (b200amg_vcycle_profile)
+struct Prof {
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> code, level;
+    bool on = false;
+};
+
 struct Engine {
+    Prof prof;
     std::vector<LevelRt> lev;
     const double *coarse_inv;
     int nc_last;
@@ -140,6 +148,18 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
     return set_err(B200AMG_EINVAL, "smooth: unknown smoother kind");
 }
 
+static int mark(Engine &E, int code, int level, cudaStream_t st)
+{
+    if (!E.prof.on) return 0;
+    cudaEvent_t e;
+    B200_CUDA(cudaEventCreate(&e));
+    B200_CUDA(cudaEventRecord(e, st));
+    E.prof.ev.push_back(e);
+    E.prof.code.push_back(code);
+    E.prof.level.push_back(level);
+    return 0;
+}
+
 static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_is_zero, cudaStream_t st)
 {
     LevelRt &L = E.lev[k];
@@ -147,11 +167,15 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
     const int nlev = (int)E.lev.size() + 1;
     double *cur = x, *spare = L.tmp;
     B200_TRY(smooth(L, d.pre_kind, d.pre_omega, d.pre_iters, d.pre_sweep, &cur, &spare, b, x_is_zero, st));
+    B200_TRY(mark(E, B200AMG_OP_PRESMOOTH, k, st));
     B200_TRY(apply_A(L, OP_RESIDUAL, 1, cur, b, L.r, st));
+    B200_TRY(mark(E, B200AMG_OP_RESIDUAL, k, st));
     B200_TRY(restrict_r(L, L.r, L.bc, st));
+    B200_TRY(mark(E, B200AMG_OP_RESTRICT, k, st));
     if (k == nlev - 2) {
         if (E.coarse_inv) B200_TRY(dense_matvec(d.nc, E.coarse_inv, L.bc, L.xc, st));
         else B200_CUDA(cudaMemsetAsync(L.xc, 0, sizeof(double) * d.nc, st));
+        B200_TRY(mark(E, B200AMG_OP_COARSE, k + 1, st));
     } else if (kind == 0) {
         B200_TRY(cycle(E, k + 1, L.xc, L.bc, 0, true, st));
     } else if (kind == 1) {
@@ -162,8 +186,13 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
         B200_TRY(cycle(E, k + 1, L.xc, L.bc, 0, false, st));
     }
     B200_TRY(prolong_add(L, L.xc, cur, st));
+    B200_TRY(mark(E, B200AMG_OP_PROLONG, k, st));
     B200_TRY(smooth(L, d.post_kind, d.post_omega, d.post_iters, d.post_sweep, &cur, &spare, b, false, st));
-    if (cur != x) B200_CUDA(cudaMemcpyAsync(x, cur, sizeof(double) * d.n, cudaMemcpyDeviceToDevice, st));
+    B200_TRY(mark(E, B200AMG_OP_POSTSMOOTH, k, st));
+    if (cur != x) {
+        B200_CUDA(cudaMemcpyAsync(x, cur, sizeof(double) * d.n, cudaMemcpyDeviceToDevice, st));
+        B200_TRY(mark(E, B200AMG_OP_COPYBACK, k, st));
+    }
     return 0;
 }
 
@@ -244,6 +273,38 @@ extern "C" int b200amg_vcycle_run(void *handle, double *x, const double *b, int 
     if (E->graphs.size() >= 8) { cudaGraphExecDestroy(E->graphs.front().exec); E->graphs.erase(E->graphs.begin()); }
     E->graphs.push_back(key);
     B200_CUDA(cudaGraphLaunch(key.exec, st));
+    return 0;
+}
+
+extern "C" int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_kind, int max_ops,
+                                      int *op_code_host, int *op_level_host, float *op_ms_host, int *n_ops_host,
+                                      void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || cycle_kind < 0 || cycle_kind > 2 || !n_ops_host) return set_err(B200AMG_EINVAL, "vcycle_profile: bad arguments");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    B200_TRY(ensure_diag(*E, st));
+    Prof &P = E->prof;
+    P.on = true;
+    int rc = mark(*E, -1, 0, st);
+    if (!rc) rc = cycle(*E, 0, x, b, cycle_kind, false, st);
+    P.on = false;
+    cudaError_t ce = cudaStreamSynchronize(st);
+    int n = 0;
+    if (!rc && ce == cudaSuccess) {
+        for (size_t i = 1; i < P.ev.size() && n < max_ops; ++i, ++n) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, P.ev[i - 1], P.ev[i]);
+            op_code_host[n] = P.code[i];
+            op_level_host[n] = P.level[i];
+            op_ms_host[n] = ms;
+        }
+    }
+    for (auto e : P.ev) cudaEventDestroy(e);
+    P.ev.clear(); P.code.clear(); P.level.clear();
+    *n_ops_host = n;
+    if (rc) return rc;
+    if (ce != cudaSuccess) return set_err((int)ce, "vcycle_profile: stream synchronize failed");
     return 0;
 }
 

@@ -214,6 +214,17 @@ class multilevel_solver:
         _lib.call('b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], int(use_graph),
                   self._stream.cuda_stream)
 
+    def profile_cycle(self, cycle='V'):
+        """one un-graphed cycle on the resident (x, b) with a CUDA event after every operation:
+        -> list of (op, level, ms), op in presmooth/residual/restrict/coarse/prolong/postsmooth/copyback"""
+        names = ('presmooth', 'residual', 'restrict', 'coarse', 'prolong', 'postsmooth', 'copyback')
+        cap = 64 * len(self.levels) * (4 if cycle != 'V' else 1)
+        code, lev = (ctypes.c_int * cap)(), (ctypes.c_int * cap)()
+        ms, n = (ctypes.c_float * cap)(), ctypes.c_int(0)
+        _lib.call('b200amg_vcycle_profile', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], cap,
+                  code, lev, ms, ctypes.byref(n), self._stream.cuda_stream)
+        return [(names[code[i]], lev[i], float(ms[i])) for i in range(n.value)]
+
     # ---- public API (multilevel.py:271-471) -------------------------------------------------
     def psolve(self, b):
         return self.solve(b, maxiter=1)
@@ -244,6 +255,7 @@ class multilevel_solver:
             return krylov.accelerated_solve(self, accel, b, x0, tol, maxiter, cycle, callback, residuals)
         n = self.levels[0].A.shape[0]
         as_numpy = not isinstance(b, torch.Tensor)
+        host_tensor = isinstance(b, torch.Tensor) and b.device.type == 'cpu'
         if self._engine is None and len(self.levels) > 1:
             self._build_engine()
         if len(self.levels) == 1:
@@ -279,7 +291,15 @@ class multilevel_solver:
             else:
                 for _ in range(maxiter):
                     self.cycle_device(cycle)
-            out = self._x.cpu().numpy() if as_numpy else self._x.clone()
+            if host_tensor:
+                # host tensor in -> host tensor out through a persistent pinned buffer (one D2H copy)
+                if getattr(self, '_xhost', None) is None:
+                    self._xhost = torch.empty(n, dtype=torch.float64, pin_memory=True)
+                self._xhost.copy_(self._x, non_blocking=True)
+                self._stream.synchronize()
+                out = self._xhost
+            else:
+                out = self._x.cpu().numpy() if as_numpy else self._x.clone()
         cur.wait_stream(self._stream)
         if as_numpy and isinstance(b, np.ndarray):
             out = out.reshape(b.shape)
