@@ -5,7 +5,7 @@ import os
 from ctypes import POINTER, Structure, c_double, c_int, c_longlong, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libb200amg.so')
+LIB_PATH = os.environ.get('B200AMG_LIB') or os.path.join(_HERE, 'libb200amg.so')   # override: kernel experiments
 
 p = c_void_p          # every device pointer / stream travels as an integer address
 

@@ -13,7 +13,7 @@ extern "C" int b200amg_csr_matvec(int n_row, int n_col, const int *Ap, const int
                                   const double *x, double *y, void *stream)
 {
     if (n_row < 0 || n_col < 0) return set_err(B200AMG_EINVAL, "csr_matvec: negative size");
-    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nnz_lookup(Ap, n_row, S(stream)), 0, n_row, 1.0, 0.0, 0.0};
     return stream_op(OP_MATVEC, a, S(stream));
 }
 
@@ -21,7 +21,7 @@ extern "C" int b200amg_csr_spmv(int n_row, int n_col, const int *Ap, const int *
                                 const double *x, double *y, double alpha, double beta, void *stream)
 {
     if (n_row < 0 || n_col < 0) return set_err(B200AMG_EINVAL, "csr_spmv: negative size");
-    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nullptr, 0, n_row, alpha, beta, 0.0};
+    StreamArgs a{Ap, Aj, Ax, x, nullptr, y, nnz_lookup(Ap, n_row, S(stream)), 0, n_row, alpha, beta, 0.0};
     return stream_op(OP_SPMV_AB, a, S(stream));
 }
 
@@ -29,7 +29,7 @@ extern "C" int b200amg_csr_residual(int n_row, const int *Ap, const int *Aj, con
                                     const double *b, double *r, void *stream)
 {
     if (n_row < 0) return set_err(B200AMG_EINVAL, "csr_residual: negative size");
-    StreamArgs a{Ap, Aj, Ax, x, b, r, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    StreamArgs a{Ap, Aj, Ax, x, b, r, nnz_lookup(Ap, n_row, S(stream)), 0, n_row, 1.0, 0.0, 0.0};
     return stream_op(OP_RESIDUAL, a, S(stream));
 }
 
@@ -37,7 +37,7 @@ extern "C" int b200amg_csr_matvec_add(int n_row, const int *Ap, const int *Aj, c
                                       double *x, void *stream)
 {
     if (n_row < 0) return set_err(B200AMG_EINVAL, "csr_matvec_add: negative size");
-    StreamArgs a{Ap, Aj, Ax, xc, nullptr, x, nullptr, 0, n_row, 1.0, 0.0, 0.0};
+    StreamArgs a{Ap, Aj, Ax, xc, nullptr, x, nnz_lookup(Ap, n_row, S(stream)), 0, n_row, 1.0, 0.0, 0.0};
     return stream_op(OP_ADD, a, S(stream));
 }
 
@@ -47,7 +47,7 @@ extern "C" int b200amg_bsr_matvec(int n_brow, int n_bcol, int R, int C, const in
 {
     if (n_brow < 0 || n_bcol < 0 || mode < 0 || mode > 2) return set_err(B200AMG_EINVAL, "bsr_matvec: bad arguments");
     if (R == 1 && C == 1) {   // scipy routes 1x1 blocks through csr_matvec
-        StreamArgs a{Ap, Aj, Ax, x, b, y, nullptr, 0, n_brow, 1.0, 0.0, 0.0};
+        StreamArgs a{Ap, Aj, Ax, x, b, y, nnz_lookup(Ap, n_brow, S(stream)), 0, n_brow, 1.0, 0.0, 0.0};
         return stream_op(mode == 0 ? OP_MATVEC : (mode == 1 ? OP_RESIDUAL : OP_ADD), a, S(stream));
     }
     return bsr_matvec(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode, S(stream));
@@ -62,7 +62,7 @@ extern "C" int b200amg_jacobi(const int *Ap, const int *Aj, const double *Ax, do
     // temp <- x on the swept range (relaxation.h:213-215), then x <- f(temp)
     B200_CUDA(cudaMemcpyAsync(temp + row_start, x + row_start, sizeof(double) * (row_stop - row_start),
                               cudaMemcpyDeviceToDevice, S(stream)));
-    StreamArgs a{Ap, Aj, Ax, temp, b, x, nullptr, row_start, row_stop, 1.0, 0.0, omega};
+    StreamArgs a{Ap, Aj, Ax, temp, b, x, -1, row_start, row_stop, 1.0, 0.0, omega};
     return stream_op(OP_JACOBI, a, S(stream));
 }
 
@@ -78,7 +78,7 @@ extern "C" int b200amg_bsr_jacobi(const int *Ap, const int *Aj, const double *Ax
     const size_t ncopy = (size_t)(row_stop - row_start) * blocksize;
     B200_CUDA(cudaMemcpyAsync(temp, x, sizeof(double) * ncopy, cudaMemcpyDeviceToDevice, S(stream)));
     if (blocksize == 1) {
-        StreamArgs a{Ap, Aj, Ax, temp, b, x, nullptr, row_start, row_stop, 1.0, 0.0, omega};
+        StreamArgs a{Ap, Aj, Ax, temp, b, x, -1, row_start, row_stop, 1.0, 0.0, omega};
         return stream_op(OP_JACOBI_BSR1, a, S(stream));
     }
     return bsr_jacobi(blocksize, row_start, row_stop, Ap, Aj, Ax, temp, x, b, omega, S(stream));
@@ -110,7 +110,7 @@ extern "C" int b200amg_gauss_seidel(const int *Ap, const int *Aj, const double *
                                     int row_start, int row_stop, int row_step, void *stream)
 {
     if (row_step == 0) return set_err(B200AMG_EINVAL, "gauss_seidel: row_step == 0");
-    return gs_sequential(false, Ap, Aj, Ax, x, b, nullptr, row_start, row_stop, row_step, S(stream));
+    return gs_sequential(false, Ap, Aj, Ax, x, b, 0, row_start, row_stop, row_step, S(stream));
 }
 
 extern "C" int b200amg_bsr_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,

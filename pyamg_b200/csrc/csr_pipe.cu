@@ -1,0 +1,294 @@
+// Persistent, TMA-fed CSR pipeline: the fine-level SpMV / residual / prolongation / Jacobi pass.
+//
+// Same arithmetic contract as csr_stream.cu (storage-order, separately rounded: bit-identical
+// to scipy csr_matvec and amg_core jacobi / bsr_jacobi(bs=1), pyamg/amg_core/relaxation.h:201-239,
+// :267-360), different schedule: csr_stream.cu is latency-bound (ncu: long_scoreboard + barrier
+// stalls, 40-57 % of DRAM peak) because every CTA runs the dependent chain
+// row pointers -> indices/values -> x gather with nothing in flight behind it.  Here
+//   * the grid is persistent (3 CTAs per SM); CTA c owns tiles c, c+grid, c+2*grid, ...;
+//     a tile is `rpt` consecutive rows (256 for short rows, fewer for long ones);
+//   * one thread drives two rings of bulk async copies (cp.async.bulk = TMA engine, mbarrier
+//     completion): row-pointer slices 3 tiles ahead, and -- once a slice has landed and the
+//     tile's nonzero range is known -- its (Aj, Ax) range 1 tile ahead, straight into shared
+//     memory.  The <= 3 ragged tail entries travel as 4/8-byte cp.async on the same mbarrier,
+//     so no load ever reads past the arrays;
+//   * eight consumer warps (thread t = row t of the tile) take tile i from shared memory while
+//     tile i+1 streams in; slots are handed back through "empty" mbarriers, one arrival per
+//     warp, so warps drift apart freely and no CTA-wide barrier sits on the path:
+//       row-parallel (<= 12 nnz/row): thread t walks row t, gathering x[Aj] (neighbouring rows
+//         of a banded operator touch neighbouring x: 2-3 cache lines per warp load);
+//       entry-parallel (long rows): all threads turn values into rounded products in place,
+//         then thread t folds row t in storage order.
+// A tile whose range does not fit a stage (rows much longer than the matrix average) is
+// summed straight from global memory by its row threads: slower, same bits.
+#include "internal.cuh"
+#include "pipe.cuh"
+
+namespace b200amg {
+
+constexpr int P_ROWS = 256;        // consumer threads = max rows per tile
+constexpr int P_TPB = P_ROWS + 32; // + one producer warp
+constexpr int P_CAP = 2816;        // entries per data stage (256 rows x 11)
+constexpr int P_PTRS = 4;          // row-pointer ring
+constexpr int P_DATA = 2;          // (Aj, Ax) ring
+constexpr int P_CTAS_PER_SM = 3;
+constexpr int P_ROWPAR_MAX_AVG = 12;
+constexpr int P_CWARPS = P_ROWS / 32;
+
+struct __align__(16) PipeSmem {
+    double v[P_DATA][P_CAP];
+    int c[P_DATA][P_CAP];
+    int ptr[P_PTRS][P_ROWS + 8];
+    uint64_t ptr_full[P_PTRS], ptr_empty[P_PTRS];
+    uint64_t data_full[P_DATA], data_empty[P_DATA];
+};
+
+__device__ __forceinline__ void consumer_sync()
+{
+    asm volatile("bar.sync 1, %0;" ::"n"(P_ROWS) : "memory");
+}
+
+template <int OP>
+__global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const StreamArgs a, const int rpt,
+                                                                        const int num_tiles)
+{
+    constexpr bool SMOOTH = (OP >= OP_JACOBI);
+    constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
+    constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
+    constexpr bool NEED_XI = SMOOTH;
+    constexpr bool NEED_Y = (OP == OP_ADD);
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    PipeSmem &S = *reinterpret_cast<PipeSmem *>(smem_raw);
+    const int t = threadIdx.x;
+    if (t == 0) {
+        for (int i = 0; i < P_PTRS; ++i) { mbar_init(&S.ptr_full[i], 2); mbar_init(&S.ptr_empty[i], P_CWARPS); }
+        for (int i = 0; i < P_DATA; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int *__restrict__ Ap = a.Ap;
+    const int *__restrict__ Aj = a.Aj;
+    const double *__restrict__ Ax = a.Ax;
+    const double *__restrict__ xg = a.x;
+
+    auto tile_rows = [&](int i, int &r0, int &nr) {
+        const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+        r0 = a.row_begin + tile * rpt;
+        nr = min(rpt, a.row_end - r0);
+    };
+
+    if (t >= P_ROWS) {
+        // ---------------- producer warp: one lane drives both copy rings -----------------------
+        if (t != P_ROWS) return;
+        for (int step = 0; step < my_tiles + P_PTRS - 1; ++step) {
+            const int jd = step - (P_PTRS - 1);
+            if (jd >= 0) {                                 // (Aj, Ax) range of tile jd
+                int r0, nr;
+                tile_rows(jd, r0, nr);
+                mbar_wait(&S.ptr_full[jd % P_PTRS], (jd / P_PTRS) & 1);
+                if (jd >= P_DATA) mbar_wait(&S.data_empty[jd % P_DATA], ((jd / P_DATA) - 1) & 1);
+                const int *sp = S.ptr[jd % P_PTRS];
+                const int s = sp[0], e = sp[nr];
+                const int base = s & ~3;
+                const int st = jd % P_DATA;
+                uint64_t *bar = &S.data_full[st];
+                if (e - base > P_CAP) {                    // does not fit: rows read global memory
+                    mbar_arrive(bar);
+                    mbar_arrive(bar);
+                } else {
+                    const int nb = (e - base) & ~3;
+                    mbar_arrive_expect_tx(bar, (uint32_t)nb * 12u);
+                    if (nb) {
+                        bulk_g2s(S.c[st], Aj + base, (uint32_t)nb * 4u, bar);
+                        bulk_g2s(S.v[st], Ax + base, (uint32_t)nb * 8u, bar);
+                    }
+                    for (int k = base + nb; k < e; ++k) {
+                        cp_async_4(&S.c[st][k - base], Aj + k);
+                        cp_async_8(&S.v[st][k - base], Ax + k);
+                    }
+                    mbar_arrive_after_cp_async(bar);
+                }
+            }
+            const int jp = step;
+            if (jp < my_tiles) {                           // row-pointer slice of tile jp
+                int r0, nr;
+                tile_rows(jp, r0, nr);
+                const int st = jp % P_PTRS;
+                if (jp >= P_PTRS) mbar_wait(&S.ptr_empty[st], ((jp / P_PTRS) - 1) & 1);
+                uint64_t *bar = &S.ptr_full[st];
+                const int cnt = nr + 1, nb = cnt & ~3;
+                mbar_arrive_expect_tx(bar, (uint32_t)nb * 4u);
+                if (nb) bulk_g2s(S.ptr[st], Ap + r0, (uint32_t)nb * 4u, bar);
+                for (int q = nb; q < cnt; ++q) cp_async_4(&S.ptr[st][q], Ap + r0 + q);
+                mbar_arrive_after_cp_async(bar);
+            }
+        }
+        return;
+    }
+
+    // -------------------- consumer warps: thread t owns row t of every tile -----------------------
+    for (int i = 0; i < my_tiles; ++i) {
+        int r0, nr;
+        tile_rows(i, r0, nr);
+        const int row = r0 + t;
+        // vector operands of the epilogue are requested first: their latency hides behind the row sum
+        double bi = 0.0, xi = 0.0, yi = 0.0;
+        if (t < nr) {
+            if (NEED_B) bi = __ldg(a.b + row);
+            if (NEED_XI) xi = __ldg(xg + row);
+            if (NEED_Y) yi = a.y[row];
+        }
+        mbar_wait(&S.ptr_full[i % P_PTRS], (i / P_PTRS) & 1);
+        const int *sp = S.ptr[i % P_PTRS];
+        const int s = sp[0], e = sp[nr];
+        const int base = s & ~3;
+        const int *sc = S.c[i % P_DATA];
+        double *sv = S.v[i % P_DATA];
+        int lo = 0, hi = 0;
+        if (t < nr) {
+            lo = sp[t];
+            hi = sp[t + 1];
+        }
+        double acc = BSRF ? bi : 0.0, diag = 0.0;
+        mbar_wait(&S.data_full[i % P_DATA], (i / P_DATA) & 1);
+        if (e - base > P_CAP) {
+            for (int k = lo; k < hi; ++k) {
+                const int c = Aj[k];
+                const double v = Ax[k];
+                const double pr = mul_rn(v, xg[c]);
+                if (SMOOTH && c == row) diag = v;
+                else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+            }
+        } else if ((e - s) <= P_ROWPAR_MAX_AVG * nr) {
+            const int k0 = lo - base, len = hi - lo;
+#ifndef PIPE_NO_FAST
+            if (len <= 8) {
+#else
+            if (false) {
+#endif
+                // all gathers of the row in flight at once, then the ordered fold
+                int cc[8];
+                double vv[8], xv[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (q < len) {
+                        cc[q] = sc[k0 + q];
+                        vv[q] = sv[k0 + q];
+                        xv[q] = __ldg(xg + cc[q]);
+                    }
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (q < len) {
+                        const double pr = mul_rn(vv[q], xv[q]);
+                        if (SMOOTH && cc[q] == row) diag = vv[q];       // last stored diagonal wins
+                        else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                    }
+            } else {
+#pragma unroll 4
+                for (int k = k0; k < k0 + len; ++k) {
+                    const int c = sc[k];
+                    const double v = sv[k];
+                    const double pr = mul_rn(v, __ldg(xg + c));
+                    if (SMOOTH && c == row) diag = v;
+                    else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                }
+            }
+        } else {
+            for (int k = s - base + t; k < e - base; k += P_ROWS) sv[k] = mul_rn(sv[k], __ldg(xg + sc[k]));
+            consumer_sync();
+            for (int k = lo - base; k < hi - base; ++k) {
+                if (SMOOTH && sc[k] == row) diag = __ldg(Ax + base + k);
+                else acc = BSRF ? sub_rn(acc, sv[k]) : add_rn(acc, sv[k]);
+            }
+        }
+        // this warp is done with both slots
+#ifdef PIPE_SYNC_TILE
+        consumer_sync();
+#endif
+#ifdef PIPE_PROXY_FENCE
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
+        __syncwarp();
+        if ((t & 31) == 0) {
+            mbar_arrive(&S.data_empty[i % P_DATA]);
+            mbar_arrive(&S.ptr_empty[i % P_PTRS]);
+        }
+        if (t < nr) {
+            double *y = a.y;
+            if (OP == OP_MATVEC) {
+                y[row] = acc;
+            } else if (OP == OP_SPMV_AB) {
+                y[row] = (a.beta == 0.0) ? a.alpha * acc : a.alpha * acc + a.beta * y[row];
+            } else if (OP == OP_RESIDUAL) {
+                y[row] = sub_rn(bi, acc);
+            } else if (OP == OP_ADD) {
+                y[row] = add_rn(yi, acc);
+            } else if (OP == OP_JACOBI) {
+                y[row] = (diag != 0.0)
+                             ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi),
+                                      mul_rn(a.omega, div_rn(sub_rn(bi, acc), diag)))
+                             : xi;
+            } else if (OP == OP_JACOBI_BSR1) {
+                y[row] = (diag != 0.0)
+                             ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), div_rn(mul_rn(a.omega, acc), diag))
+                             : xi;
+            }
+        }
+    }
+}
+
+// rows per tile from the average row length: a tile should fill most of one stage
+int pipe_rows_per_tile(long long nnz, int nrows)
+{
+    if (nnz < 0 || nrows <= 0) return 0;                 // unknown: caller uses csr_stream
+    const double avg = (double)nnz / nrows;
+    if (avg <= 11.0) return P_ROWS;
+    int r = P_ROWS;
+    while (r > 4 && r * avg > 0.85 * P_CAP) r >>= 1;
+    return r;
+}
+
+static int g_sms = 0;
+
+template <int OP>
+static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
+{
+    static bool attr_done = false;
+    if (!attr_done) {
+        B200_CUDA(cudaFuncSetAttribute(csr_pipe_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(PipeSmem)));
+        attr_done = true;
+    }
+    if (g_sms == 0) {
+        int dev = 0;
+        B200_CUDA(cudaGetDevice(&dev));
+        B200_CUDA(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int nrows = a.row_end - a.row_begin;
+    const int num_tiles = (nrows + rpt - 1) / rpt;
+    const int grid = min(num_tiles, g_sms * P_CTAS_PER_SM);
+    csr_pipe_kernel<OP><<<grid, P_TPB, sizeof(PipeSmem), st>>>(a, rpt, num_tiles);
+    return check_launch("csr_pipe_kernel");
+}
+
+// -> 1 if launched, 0 if this case is not eligible (caller falls back to csr_stream), <0 / >1 never
+int pipe_op(int op, const StreamArgs &a, long long nnz, cudaStream_t st, int *rc)
+{
+    const int nrows = a.row_end - a.row_begin;
+    const int rpt = pipe_rows_per_tile(nnz, nrows);
+    if (rpt == 0 || nrows <= 0) return 0;
+    if (!aligned16(a.Aj) || !aligned16(a.Ax) || !aligned16(a.Ap + a.row_begin)) return 0;
+    switch (op) {
+    case OP_MATVEC: *rc = launch_pipe<OP_MATVEC>(a, rpt, st); return 1;
+    case OP_SPMV_AB: *rc = launch_pipe<OP_SPMV_AB>(a, rpt, st); return 1;
+    case OP_RESIDUAL: *rc = launch_pipe<OP_RESIDUAL>(a, rpt, st); return 1;
+    case OP_ADD: *rc = launch_pipe<OP_ADD>(a, rpt, st); return 1;
+    case OP_JACOBI: *rc = launch_pipe<OP_JACOBI>(a, rpt, st); return 1;
+    case OP_JACOBI_BSR1: *rc = launch_pipe<OP_JACOBI_BSR1>(a, rpt, st); return 1;
+    }
+    return 0;
+}
+
+}  // namespace b200amg

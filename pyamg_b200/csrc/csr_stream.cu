@@ -1,13 +1,18 @@
 // CSR "stream" kernels: one pass over (Ap, Aj, Ax) at HBM speed, bit-exact row sums.
 //
-// One CTA owns 256 consecutive rows and walks their contiguous nonzero range in chunks of
-// 2048 entries: (1) all threads stream Aj/Ax with 128-bit coalesced loads, gather x[Aj]
-// (L1/L2 hits for banded matrices) and park the rounded products in shared memory;
-// (2) thread t then folds row t's products IN STORAGE ORDER with separately rounded adds.
-// That is the reference's serial arithmetic (scipy csr_matvec; amg_core jacobi /
-// gauss_seidel_indexed, pyamg/amg_core/relaxation.h:201-239, :394-426), so results are
-// identical to the bit while the matrix is read once, fully coalesced, regardless of the
-// row length (7 nnz/row on level 0, 30-70 on the coarse levels).
+// One CTA owns `rows_per_cta` (<= 256) consecutive rows and walks their contiguous nonzero range
+// in chunks of 2048 entries that all threads stage into shared memory with 128-bit coalesced
+// loads.  Every row is then accumulated IN STORAGE ORDER with separately rounded multiply and
+// add -- the reference's serial arithmetic (scipy csr_matvec; amg_core jacobi,
+// pyamg/amg_core/relaxation.h:201-239) -- so results are identical to the bit, while the
+// matrix is read exactly once, fully coalesced, whatever the row length.
+// Two schedules, chosen per CTA from its own rows (uniform branch):
+//   * row-parallel (short rows, <= 12 nnz/row on average: level-0 stencils, prolongators):
+//     raw (Aj, Ax) are staged; thread t then walks row t, gathering x[Aj].  Neighbouring rows of
+//     a banded matrix hit neighbouring x entries, so a warp's gather touches 2-3 cache lines
+//     instead of ~14 and L1TEX stops being the limiter (ncu, profiles/r01).
+//   * entry-parallel (long rows: coarse operators, restriction): all threads gather x and stage
+//     the rounded PRODUCTS; thread t folds row t's products from shared memory.
 #include "internal.cuh"
 
 namespace b200amg {
@@ -17,69 +22,106 @@ long long g_launches = 0;
 
 constexpr int TPB = 256;
 constexpr int CHUNK = 2048;
+constexpr int ROWPAR_MAX_AVG = 12;
 
 template <int OP, bool VEC>
-__global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a)
+__global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a, const int rows_per_cta)
 {
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
-    constexpr bool BSRF = (OP == OP_JACOBI_BSR1 || OP == OP_GS_BSR1);
+    constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
     __shared__ int s_ptr[TPB + 1];
     __shared__ __align__(16) double s_p[CHUNK];
-    __shared__ __align__(16) int s_c[SMOOTH ? CHUNK : 4];
+    __shared__ __align__(16) int s_c[CHUNK];
 
     const int t = threadIdx.x;
-    const int r0 = a.row_begin + blockIdx.x * TPB;
-    const int nr = min(TPB, a.row_end - r0);
+    const int rpb = rows_per_cta;
+    const int r0 = a.row_begin + blockIdx.x * rpb;
+    const int nr = min(rpb, a.row_end - r0);
     for (int q = t; q <= nr; q += TPB) s_ptr[q] = a.Ap[r0 + q];
     __syncthreads();
     const int s = s_ptr[0], e = s_ptr[nr];
-    int lo = 0, hi = 0, row = 0;
+    const bool rowpar = (e - s) <= ROWPAR_MAX_AVG * nr;
+    int lo = 0, hi = 0;
+    const int row = r0 + t;
     double acc = 0.0, diag = 0.0;
     if (t < nr) {
         lo = s_ptr[t];
         hi = s_ptr[t + 1];
-        row = a.map ? a.map[r0 + t] : r0 + t;
         if (BSRF) acc = a.b[row];
     }
     const double *__restrict__ Ax = a.Ax;
     const int *__restrict__ Aj = a.Aj;
-    const double *xg = a.x;
+    const double *__restrict__ xg = a.x;
 
     for (int base = s & ~3; base < e; base += CHUNK) {
+        if (rowpar) {
 #pragma unroll
-        for (int u = 0; u < CHUNK / (4 * TPB); ++u) {
-            const int off = (u * TPB + t) * 4;
-            const int k = base + off;
-            if (VEC && k >= s && k + 4 <= e) {
-                const int4 c = *reinterpret_cast<const int4 *>(Aj + k);
-                const double2 v0 = *reinterpret_cast<const double2 *>(Ax + k);
-                const double2 v1 = *reinterpret_cast<const double2 *>(Ax + k + 2);
-                const double x0 = xg[c.x], x1 = xg[c.y], x2 = xg[c.z], x3 = xg[c.w];
-                *reinterpret_cast<double2 *>(&s_p[off]) = make_double2(mul_rn(v0.x, x0), mul_rn(v0.y, x1));
-                *reinterpret_cast<double2 *>(&s_p[off + 2]) = make_double2(mul_rn(v1.x, x2), mul_rn(v1.y, x3));
-                if (SMOOTH) *reinterpret_cast<int4 *>(&s_c[off]) = c;
-            } else {
+            for (int u = 0; u < CHUNK / (4 * TPB); ++u) {
+                const int off = (u * TPB + t) * 4;
+                const int k = base + off;
+                if (VEC && k + 4 <= e) {
+                    *reinterpret_cast<int4 *>(&s_c[off]) = __ldg(reinterpret_cast<const int4 *>(Aj + k));
+                    *reinterpret_cast<double2 *>(&s_p[off]) = __ldg(reinterpret_cast<const double2 *>(Ax + k));
+                    *reinterpret_cast<double2 *>(&s_p[off + 2]) = __ldg(reinterpret_cast<const double2 *>(Ax + k + 2));
+                } else {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int kk = k + q;
-                    if (kk >= s && kk < e) {
-                        const int c = Aj[kk];
-                        s_p[off + q] = mul_rn(Ax[kk], xg[c]);
-                        if (SMOOTH) s_c[off + q] = c;
+                    for (int q = 0; q < 4; ++q)
+                        if (k + q < e) { s_c[off + q] = Aj[k + q]; s_p[off + q] = Ax[k + q]; }
+                }
+            }
+            __syncthreads();
+            if (t < nr) {
+                const int k0 = max(lo, base) - base;
+                const int k1 = min(hi, base + CHUNK) - base;
+#pragma unroll 4
+                for (int k = k0; k < k1; ++k) {
+                    const int c = s_c[k];
+                    const double v = s_p[k];
+                    const double pr = mul_rn(v, __ldg(xg + c));
+                    if (SMOOTH) {
+                        if (c == row) diag = v;                            // last stored diagonal wins
+                        else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                    } else {
+                        acc = add_rn(acc, pr);
                     }
                 }
             }
-        }
-        __syncthreads();
-        if (t < nr) {
-            const int k0 = max(lo, base) - base;
-            const int k1 = min(hi, base + CHUNK) - base;
-            for (int k = k0; k < k1; ++k) {
-                if (SMOOTH) {
-                    if (s_c[k] == row) diag = Ax[base + k];           // last stored diagonal wins
-                    else acc = BSRF ? sub_rn(acc, s_p[k]) : add_rn(acc, s_p[k]);
+        } else {
+#pragma unroll
+            for (int u = 0; u < CHUNK / (4 * TPB); ++u) {
+                const int off = (u * TPB + t) * 4;
+                const int k = base + off;
+                if (VEC && k >= s && k + 4 <= e) {
+                    const int4 c = __ldg(reinterpret_cast<const int4 *>(Aj + k));
+                    const double2 v0 = __ldg(reinterpret_cast<const double2 *>(Ax + k));
+                    const double2 v1 = __ldg(reinterpret_cast<const double2 *>(Ax + k + 2));
+                    const double x0 = __ldg(xg + c.x), x1 = __ldg(xg + c.y), x2 = __ldg(xg + c.z), x3 = __ldg(xg + c.w);
+                    *reinterpret_cast<double2 *>(&s_p[off]) = make_double2(mul_rn(v0.x, x0), mul_rn(v0.y, x1));
+                    *reinterpret_cast<double2 *>(&s_p[off + 2]) = make_double2(mul_rn(v1.x, x2), mul_rn(v1.y, x3));
+                    if (SMOOTH) *reinterpret_cast<int4 *>(&s_c[off]) = c;
                 } else {
-                    acc = add_rn(acc, s_p[k]);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int kk = k + q;
+                        if (kk >= s && kk < e) {
+                            const int c = Aj[kk];
+                            s_p[off + q] = mul_rn(Ax[kk], xg[c]);
+                            if (SMOOTH) s_c[off + q] = c;
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+            if (t < nr) {
+                const int k0 = max(lo, base) - base;
+                const int k1 = min(hi, base + CHUNK) - base;
+                for (int k = k0; k < k1; ++k) {
+                    if (SMOOTH) {
+                        if (s_c[k] == row) diag = Ax[base + k];           // last stored diagonal wins
+                        else acc = BSRF ? sub_rn(acc, s_p[k]) : add_rn(acc, s_p[k]);
+                    } else {
+                        acc = add_rn(acc, s_p[k]);
+                    }
                 }
             }
         }
@@ -106,28 +148,41 @@ __global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a)
         y[row] = (diag != 0.0)
                      ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), div_rn(mul_rn(a.omega, acc), diag))
                      : xi;
-    } else if (OP == OP_GS) {
-        if (diag != 0.0) y[row] = div_rn(sub_rn(a.b[row], acc), diag);
-    } else if (OP == OP_GS_BSR1) {
-        if (diag != 0.0) y[row] = div_rn(acc, diag);
     }
 }
 
-template <int OP>
-static int launch_stream(const StreamArgs &a, cudaStream_t st)
+// rows per CTA: 256 for short rows; long rows get fewer rows per CTA so that a CTA owns about
+// one chunk of entries and the serial per-row folds of different rows run in different CTAs
+int rows_per_cta_for(long long nnz, int nrows)
 {
+    if (nnz <= 0 || nrows <= 0) return TPB;
+    const double avg = (double)nnz / nrows;
+    if (avg <= ROWPAR_MAX_AVG) return TPB;
+    int r = TPB;
+    if (avg <= 100.0) return TPB;      // measured: splitting 30-nnz rows over more CTAs only adds prologues
+    while (r > 4 && r * avg > 1.25 * CHUNK) r >>= 1;
+    return r;
+}
+
+template <int OP>
+static int launch_stream(const StreamArgs &a0, cudaStream_t st)
+{
+    const StreamArgs &a = a0;
     const int nrows = a.row_end - a.row_begin;
     if (nrows <= 0) return 0;
-    const int grid = (nrows + TPB - 1) / TPB;
+    const int rpb = rows_per_cta_for(a.nnz, nrows);
+    const int grid = (nrows + rpb - 1) / rpb;
     if (aligned16(a.Aj) && aligned16(a.Ax))
-        csr_stream_kernel<OP, true><<<grid, TPB, 0, st>>>(a);
+        csr_stream_kernel<OP, true><<<grid, TPB, 0, st>>>(a, rpb);
     else
-        csr_stream_kernel<OP, false><<<grid, TPB, 0, st>>>(a);
+        csr_stream_kernel<OP, false><<<grid, TPB, 0, st>>>(a, rpb);
     return check_launch("csr_stream_kernel");
 }
 
 int stream_op(int op, const StreamArgs &a, cudaStream_t st)
 {
+    int rc = 0;
+    if (a.nnz >= 0 && pipe_op(op, a, a.nnz, st, &rc)) return rc;
     switch (op) {
     case OP_MATVEC: return launch_stream<OP_MATVEC>(a, st);
     case OP_SPMV_AB: return launch_stream<OP_SPMV_AB>(a, st);
@@ -135,8 +190,6 @@ int stream_op(int op, const StreamArgs &a, cudaStream_t st)
     case OP_ADD: return launch_stream<OP_ADD>(a, st);
     case OP_JACOBI: return launch_stream<OP_JACOBI>(a, st);
     case OP_JACOBI_BSR1: return launch_stream<OP_JACOBI_BSR1>(a, st);
-    case OP_GS: return launch_stream<OP_GS>(a, st);
-    case OP_GS_BSR1: return launch_stream<OP_GS_BSR1>(a, st);
     }
     return set_err(B200AMG_EINVAL, "stream_op: bad op");
 }
@@ -200,6 +253,35 @@ __global__ void __launch_bounds__(32) gs_sequential_kernel(const int *__restrict
             __stcg(x + i, BSRF ? div_rn(acc, diag) : div_rn(sub_rn(b[i], acc), diag));
         __syncwarp();
     }
+}
+
+// ---- nnz of a matrix handed to a stand-alone entry point ------------------------------------
+// The amg_core / scipy signatures carry no nnz; tile sizing needs the average row length.  It is
+// read once per (Ap, n_row) with a 4-byte D2H copy (never while the stream is being captured)
+// and cached.  A stale entry (buffer re-used for another matrix) can only mis-size tiles:
+// results do not depend on it.
+long long nnz_lookup(const int *Ap, int n_row, cudaStream_t st)
+{
+    struct Slot { const int *Ap; int n_row; long long nnz; };
+    static Slot cache[64];
+    static int used = 0, next = 0;
+    if (!Ap || n_row <= 0) return -1;
+    for (int i = 0; i < used; ++i)
+        if (cache[i].Ap == Ap && cache[i].n_row == n_row) return cache[i].nnz;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return -1;
+    int ends[2] = {0, 0};
+    if (cudaMemcpyAsync(&ends[0], Ap, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaMemcpyAsync(&ends[1], Ap + n_row, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    Slot sl{Ap, n_row, (long long)ends[1] - ends[0]};
+    cache[next] = sl;
+    next = (next + 1) % 64;
+    if (used < 64) ++used;
+    return sl.nnz;
 }
 
 int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,

@@ -5,7 +5,7 @@
 namespace b200amg {
 
 enum : int {
-    OP_MATVEC = 0, OP_SPMV_AB, OP_RESIDUAL, OP_ADD, OP_JACOBI, OP_JACOBI_BSR1, OP_GS, OP_GS_BSR1
+    OP_MATVEC = 0, OP_SPMV_AB, OP_RESIDUAL, OP_ADD, OP_JACOBI, OP_JACOBI_BSR1
 };
 
 struct StreamArgs {
@@ -14,10 +14,17 @@ struct StreamArgs {
     const double *x;
     const double *b;
     double *y;
-    const int *map;
+    long long nnz;         // stored entries of the rows in range, or -1 when the caller does not know
     int row_begin, row_end;
     double alpha, beta, omega;
 };
+
+int rows_per_cta_for(long long nnz, int nrows);
+// persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when
+// the case is not eligible (unknown nnz, unaligned arrays) and csr_stream must run instead
+int pipe_op(int op, const StreamArgs &a, long long nnz, cudaStream_t st, int *rc);
+// nnz of rows [0, n_row) for the stand-alone entry points: one 4-byte read per (Ap, n_row), cached
+long long nnz_lookup(const int *Ap, int n_row, cudaStream_t st);
 
 int stream_op(int op, const StreamArgs &a, cudaStream_t st);
 int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,

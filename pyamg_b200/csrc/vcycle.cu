@@ -15,6 +15,7 @@ namespace b200amg {
 struct LevelRt {
     b200amg_level_desc d;
     double *r, *bc, *xc, *tmp, *diag;
+    long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     std::vector<int> color_ptr;
 };
 
@@ -57,7 +58,7 @@ static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *
 {
     const b200amg_level_desc &d = L.d;
     if (d.bs == 1) {
-        StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, nullptr, 0, d.n, 1.0, 0.0, 0.0};
+        StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, L.nzA, 0, d.n, 1.0, 0.0, 0.0};
         return stream_op(op_scalar, a, st);
     }
     return bsr_matvec(d.n / d.bs, d.bs, d.bs, d.Ap, d.Aj, d.Ax, x, b, y, bsr_mode, st);
@@ -67,7 +68,7 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
 {
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
-        StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, nullptr, 0, d.nc, 1.0, 0.0, 0.0};
+        StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, L.nzR, 0, d.nc, 1.0, 0.0, 0.0};
         return stream_op(OP_MATVEC, a, st);
     }
     return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st);
@@ -77,7 +78,7 @@ static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream
 {
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
-        StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, nullptr, 0, d.n, 1.0, 0.0, 0.0};
+        StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
         return stream_op(OP_ADD, a, st);
     }
     return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, nullptr, x, 2, st);
@@ -100,7 +101,7 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
             }
             if (it == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
             if (d.bs == 1) {
-                StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, nullptr, 0, d.n, 1.0, 0.0, omega};
+                StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, L.nzA, 0, d.n, 1.0, 0.0, omega};
                 B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
             } else {
                 B200_TRY(bsr_jacobi(d.bs, 0, d.n / d.bs, d.Ap, d.Aj, d.Ax, *cur, *spare, b, omega, st));
@@ -239,6 +240,17 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             L.color_ptr.assign(L.d.color_ptr_host, L.d.color_ptr_host + L.d.K + 1);
             L.d.color_ptr_host = nullptr;
         }
+        // nonzero counts (one small D2H read per matrix, at create time only) size the CTAs
+        auto last = [](const int *p, int n, int *out) {
+            return p ? cudaMemcpy(out, p + n, sizeof(int), cudaMemcpyDeviceToHost) : cudaSuccess;
+        };
+        int nzA = 0, nzP = 0, nzR = 0;
+        if (last(L.d.Ap, L.d.n / L.d.bs, &nzA) != cudaSuccess || last(L.d.Pp, L.d.n / L.d.p_br, &nzP) != cudaSuccess ||
+            last(L.d.Rp, L.d.nc / L.d.p_bc, &nzR) != cudaSuccess) {
+            delete E;
+            return set_err(B200AMG_EINVAL, "vcycle_create: cannot read row pointers");
+        }
+        L.nzA = nzA; L.nzP = nzP; L.nzR = nzR;
         E->lev.push_back(L);
     }
     E->nc_last = Ld[nlev - 2].nc;
