@@ -163,11 +163,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
             }
         } else if ((e - s) <= P_ROWPAR_MAX_AVG * nr) {
             const int k0 = lo - base, len = hi - lo;
-#ifndef PIPE_NO_FAST
             if (len <= 8) {
-#else
-            if (false) {
-#endif
                 // all gathers of the row in flight at once, then the ordered fold
                 int cc[8];
                 double vv[8], xv[8];
@@ -204,12 +200,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
             }
         }
         // this warp is done with both slots
-#ifdef PIPE_SYNC_TILE
-        consumer_sync();
-#endif
-#ifdef PIPE_PROXY_FENCE
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // in-place products vs the next bulk refill
         __syncwarp();
         if ((t & 31) == 0) {
             mbar_arrive(&S.data_empty[i % P_DATA]);
@@ -244,10 +235,7 @@ int pipe_rows_per_tile(long long nnz, int nrows)
 {
     if (nnz < 0 || nrows <= 0) return 0;                 // unknown: caller uses csr_stream
     const double avg = (double)nnz / nrows;
-    if (avg <= 11.0) return P_ROWS;
-    int r = P_ROWS;
-    while (r > 4 && r * avg > 0.85 * P_CAP) r >>= 1;
-    return r;
+    return avg <= 11.0 ? P_ROWS : 0;                     // long rows: sliced-ELL (engine) or csr_stream
 }
 
 static int g_sms = 0;

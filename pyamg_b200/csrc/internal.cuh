@@ -23,6 +23,23 @@ int rows_per_cta_for(long long nnz, int nrows);
 // persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when
 // the case is not eligible (unknown nnz, unaligned arrays) and csr_stream must run instead
 int pipe_op(int op, const StreamArgs &a, long long nnz, cudaStream_t st, int *rc);
+// ---- sliced-ELL copy of a long-row CSR operator (sell.cu): slices of 32 rows, column-major inside a
+// slice, so that thread-per-row loads of (Aj, Ax) coalesce and neighbouring rows gather neighbouring x
+struct Sell {
+    int n = 0;                       // rows
+    long long padded = 0;            // stored slots (32 * sum of slice widths)
+    long long *slice_off = nullptr;  // [n_slices + 1] slot offset of every slice
+    int *cj = nullptr;               // [padded]
+    double *cv = nullptr;            // [padded]
+    int *row_len = nullptr;          // [n]
+    bool ok() const { return cj != nullptr; }
+};
+int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st);
+void sell_free(Sell *s);
+// same operations / arithmetic as stream_op, on the sliced-ELL copy
+int sell_op(int op, const Sell &s, const StreamArgs &a, cudaStream_t st);
+bool sell_wanted(long long nnz, int nrows);
+
 // nnz of rows [0, n_row) for the stand-alone entry points: one 4-byte read per (Ap, n_row), cached
 long long nnz_lookup(const int *Ap, int n_row, cudaStream_t st);
 

@@ -1,0 +1,210 @@
+// Sliced-ELL (SELL-32) path for CSR operators with 12..400 stored entries per row: the coarse
+// Galerkin operators (31-68 per row) and the level-0 restriction (30 per row).
+//
+// Why a second layout: for these rows the x gather is what limits a CSR kernel, not HBM.  With
+// entries dealt to lanes in CSR order (csr_stream.cu) a warp load of 32 consecutive entries of
+// the level-1 operator touches 0.70 cache lines per entry and L1TEX runs at 88 % while DRAM
+// sits at 40 % (ncu, profiles/r01).  Dealing ROWS to lanes cuts that to 0.28 lines per entry,
+// because neighbouring coarse rows have neighbouring columns -- but then the matrix itself
+// must be readable row-per-lane, which is what a slice of 32 rows stored column-major gives:
+// lane l of a warp reads slot (k, l); 32 lanes read 128 contiguous bytes of indices and 256 of
+// values.  Rows keep their storage order, so every row sum is folded exactly as the reference
+// does it (scipy csr_matvec / amg_core jacobi, pyamg/amg_core/relaxation.h:201-239): the bits
+// are those of the CSR kernels.  Cost: the copy (engine-owned, built once per level) and
+// 19-23 % padding traffic; no shared memory, no barriers, 8 independent loads in flight per lane.
+#include "internal.cuh"
+#include "setup.cuh"
+
+namespace b200amg {
+
+constexpr int SELL_C = 32;
+constexpr int SELL_TPB = 256;
+constexpr int SELL_U = 8;
+
+bool sell_wanted(long long nnz, int nrows)
+{
+    if (nnz <= 0 || nrows < 4 * SELL_C) return false;
+    const double avg = (double)nnz / nrows;
+    return avg > 11.0 && avg <= 400.0;
+}
+
+// ---- build ----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, long long *__restrict__ width,
+                                                         int *__restrict__ row_len)
+{
+    const int row = blockIdx.x * 256 + threadIdx.x;
+    int len = 0;
+    if (row < n) {
+        len = Ap[row + 1] - Ap[row];
+        row_len[row] = len;
+    }
+    int m = len;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && (row >> 5) < (n + SELL_C - 1) / SELL_C) width[row >> 5] = (long long)m * SELL_C;
+}
+
+__global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                        const double *__restrict__ Ax,
+                                                        const long long *__restrict__ slice_off, int *__restrict__ cj,
+                                                        double *__restrict__ cv)
+{
+    const int row = blockIdx.x * 256 + threadIdx.x;
+    const int slice = row >> 5, lane = threadIdx.x & 31;
+    if (slice >= (n + SELL_C - 1) / SELL_C) return;
+    const long long off = slice_off[slice];
+    const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
+    int lo = 0, len = 0;
+    if (row < n) {
+        lo = Ap[row];
+        len = Ap[row + 1] - lo;
+    }
+    for (int k = 0; k < w; ++k) {
+        const bool in = k < len;
+        cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
+        cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
+    }
+}
+
+void sell_free(Sell *s)
+{
+    if (s->slice_off) cudaFree(s->slice_off);
+    if (s->cj) cudaFree(s->cj);
+    if (s->cv) cudaFree(s->cv);
+    if (s->row_len) cudaFree(s->row_len);
+    *s = Sell();
+}
+
+int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st)
+{
+    *out = Sell();
+    if (n <= 0) return 0;
+    const int ns = (n + SELL_C - 1) / SELL_C;
+    long long *width = nullptr, *scratch = nullptr;
+    Sell s;
+    s.n = n;
+    cudaError_t e = cudaMalloc(&width, sizeof(long long) * ns);
+    if (e == cudaSuccess) e = cudaMalloc(&scratch, sizeof(long long) * (size_t)scan_scratch_elems(ns));
+    if (e == cudaSuccess) e = cudaMalloc(&s.slice_off, sizeof(long long) * (ns + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&s.row_len, sizeof(int) * (size_t)n);
+    int rc = 0;
+    if (e == cudaSuccess) {
+        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, width, s.row_len);
+        rc = check_launch("sell_width_kernel");
+        if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
+        if (!rc) {
+            e = cudaMemcpyAsync(&s.padded, s.slice_off + ns, sizeof(long long), cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+    }
+    // refuse pathological padding (one long row per slice): the CSR kernels handle those
+    if (e == cudaSuccess && !rc && s.padded > 0 && s.padded <= 2 * nnz + 64 * SELL_C) {
+        e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
+        if (e == cudaSuccess) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
+        if (e == cudaSuccess) {
+            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, s.slice_off, s.cj, s.cv);
+            rc = check_launch("sell_fill_kernel");
+        }
+    }
+    if (width) cudaFree(width);
+    if (scratch) cudaFree(scratch);
+    if (e != cudaSuccess || rc || !s.cj || !s.cv) {
+        sell_free(&s);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return set_err((int)e, "sell_build: device allocation failed");
+        }
+        return rc;      // rc == 0 with no arrays: layout declined, caller keeps CSR
+    }
+    *out = s;
+    return 0;
+}
+
+// ---- apply ----------------------------------------------------------------------------------
+template <int OP>
+__global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long long *__restrict__ slice_off,
+                                                        const int *__restrict__ cj, const double *__restrict__ cv,
+                                                        const int *__restrict__ row_len, const StreamArgs a)
+{
+    constexpr bool SMOOTH = (OP >= OP_JACOBI);
+    constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
+    constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
+    const int row = blockIdx.x * SELL_TPB + threadIdx.x;
+    const int slice = row >> 5, lane = threadIdx.x & 31;
+    if (slice >= (n + SELL_C - 1) / SELL_C) return;            // whole warp
+    const long long off = slice_off[slice];
+    const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
+    const bool live = row < n;
+    const int len = live ? row_len[row] : 0;
+    const double *__restrict__ xg = a.x;
+    double bi = 0.0, xi = 0.0, yi = 0.0;
+    if (live) {
+        if (NEED_B) bi = __ldg(a.b + row);
+        if (SMOOTH) xi = __ldg(xg + row);
+        if (OP == OP_ADD) yi = a.y[row];
+    }
+    double acc = BSRF ? bi : 0.0, diag = 0.0;
+    const int *pj = cj + off + lane;
+    const double *pv = cv + off + lane;
+    for (int k0 = 0; k0 < w; k0 += SELL_U) {
+        int c[SELL_U];
+        double v[SELL_U], xv[SELL_U];
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            const bool in = k0 + u < len;
+            c[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : -1;
+            v[u] = in ? __ldcs(pv + (long long)(k0 + u) * SELL_C) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            if (c[u] >= 0) {
+                const double pr = mul_rn(v[u], xv[u]);
+                if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
+                else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+            }
+        }
+    }
+    if (!live) return;
+    double *y = a.y;
+    if (OP == OP_MATVEC) {
+        y[row] = acc;
+    } else if (OP == OP_SPMV_AB) {
+        y[row] = (a.beta == 0.0) ? a.alpha * acc : a.alpha * acc + a.beta * y[row];
+    } else if (OP == OP_RESIDUAL) {
+        y[row] = sub_rn(bi, acc);
+    } else if (OP == OP_ADD) {
+        y[row] = add_rn(yi, acc);
+    } else if (OP == OP_JACOBI) {
+        y[row] = (diag != 0.0)
+                     ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), mul_rn(a.omega, div_rn(sub_rn(bi, acc), diag)))
+                     : xi;
+    } else if (OP == OP_JACOBI_BSR1) {
+        y[row] = (diag != 0.0) ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), div_rn(mul_rn(a.omega, acc), diag)) : xi;
+    }
+}
+
+template <int OP>
+static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
+{
+    const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
+    sell_kernel<OP><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
+    return check_launch("sell_kernel");
+}
+
+int sell_op(int op, const Sell &s, const StreamArgs &a, cudaStream_t st)
+{
+    if (a.row_begin != 0 || a.row_end != s.n) return set_err(B200AMG_EINVAL, "sell_op: full row range only");
+    switch (op) {
+    case OP_MATVEC: return launch_sell<OP_MATVEC>(s, a, st);
+    case OP_SPMV_AB: return launch_sell<OP_SPMV_AB>(s, a, st);
+    case OP_RESIDUAL: return launch_sell<OP_RESIDUAL>(s, a, st);
+    case OP_ADD: return launch_sell<OP_ADD>(s, a, st);
+    case OP_JACOBI: return launch_sell<OP_JACOBI>(s, a, st);
+    case OP_JACOBI_BSR1: return launch_sell<OP_JACOBI_BSR1>(s, a, st);
+    }
+    return set_err(B200AMG_EINVAL, "sell_op: bad op");
+}
+
+}  // namespace b200amg

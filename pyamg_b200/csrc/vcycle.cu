@@ -16,6 +16,7 @@ struct LevelRt {
     b200amg_level_desc d;
     double *r, *bc, *xc, *tmp, *diag;
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
+    Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     std::vector<int> color_ptr;
 };
 
@@ -59,6 +60,7 @@ static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *
     const b200amg_level_desc &d = L.d;
     if (d.bs == 1) {
         StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, L.nzA, 0, d.n, 1.0, 0.0, 0.0};
+        if (L.sA.ok()) return sell_op(op_scalar, L.sA, a, st);
         return stream_op(op_scalar, a, st);
     }
     return bsr_matvec(d.n / d.bs, d.bs, d.bs, d.Ap, d.Aj, d.Ax, x, b, y, bsr_mode, st);
@@ -69,6 +71,7 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, L.nzR, 0, d.nc, 1.0, 0.0, 0.0};
+        if (L.sR.ok()) return sell_op(OP_MATVEC, L.sR, a, st);
         return stream_op(OP_MATVEC, a, st);
     }
     return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st);
@@ -79,6 +82,7 @@ static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
+        if (L.sP.ok()) return sell_op(OP_ADD, L.sP, a, st);
         return stream_op(OP_ADD, a, st);
     }
     return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, nullptr, x, 2, st);
@@ -102,7 +106,8 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
             if (it == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
             if (d.bs == 1) {
                 StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, L.nzA, 0, d.n, 1.0, 0.0, omega};
-                B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
+                if (L.sA.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sA, a, st));
+                else B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
             } else {
                 B200_TRY(bsr_jacobi(d.bs, 0, d.n / d.bs, d.Ap, d.Aj, d.Ax, *cur, *spare, b, omega, st));
             }
@@ -251,6 +256,19 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             return set_err(B200AMG_EINVAL, "vcycle_create: cannot read row pointers");
         }
         L.nzA = nzA; L.nzP = nzP; L.nzR = nzR;
+        // long-row scalar operators get a sliced-ELL copy (sell.cu); a declined / failed build keeps CSR
+        int src = 0;
+        if (L.d.bs == 1 && sell_wanted(nzA, L.d.n)) src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sA, nullptr);
+        if (!src && L.d.p_br == 1 && L.d.p_bc == 1) {
+            if (sell_wanted(nzR, L.d.nc)) src = sell_build(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR, nullptr);
+            if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
+        }
+        if (src) {
+            sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP);
+            for (auto &Lp : E->lev) { sell_free(&Lp.sA); sell_free(&Lp.sR); sell_free(&Lp.sP); }
+            delete E;
+            return src;
+        }
         E->lev.push_back(L);
     }
     E->nc_last = Ld[nlev - 2].nc;
@@ -335,6 +353,7 @@ extern "C" int b200amg_vcycle_destroy(void *handle)
     Engine *E = reinterpret_cast<Engine *>(handle);
     if (!E) return 0;
     for (auto &g : E->graphs) cudaGraphExecDestroy(g.exec);
+    for (auto &L : E->lev) { sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); }
     delete E;
     return 0;
 }
