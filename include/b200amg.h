@@ -104,6 +104,12 @@ int b200amg_extract_diag(int n_brow, int blocksize, const int *Ap, const int *Aj
 /* y = M x, dense row-major M (n x n): coarse_grid_solver('pinv2'), multilevel.py:608-612 */
 int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, void *stream);
 
+/* diagnostic (tests): one SpMV-family operation through the engine's sliced-ELL (SELL-32) layout,
+ * which b200amg_vcycle_create builds for operators with 12..400 entries per row.  op: 0 y = A x,
+ * 2 y = b - A x, 3 y += A x, 4 amg_core.jacobi arithmetic (x in, y out), 5 bsr_jacobi(bs=1) arithmetic */
+int b200amg_selftest_sell(int op, int n_row, const int *Ap, const int *Aj, const double *Ax,
+                          const double *x, const double *b, double *y, double omega, void *stream);
+
 /* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
  *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */
 /* Row-wise C = A B, exact zeros dropped (scipy drops them too); values bit-identical to scipy's

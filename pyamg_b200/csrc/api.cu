@@ -62,7 +62,7 @@ extern "C" int b200amg_jacobi(const int *Ap, const int *Aj, const double *Ax, do
     // temp <- x on the swept range (relaxation.h:213-215), then x <- f(temp)
     B200_CUDA(cudaMemcpyAsync(temp + row_start, x + row_start, sizeof(double) * (row_stop - row_start),
                               cudaMemcpyDeviceToDevice, S(stream)));
-    StreamArgs a{Ap, Aj, Ax, temp, b, x, -1, row_start, row_stop, 1.0, 0.0, omega};
+    StreamArgs a{Ap, Aj, Ax, temp, b, x, row_start == 0 ? nnz_lookup(Ap, row_stop, S(stream)) : -1, row_start, row_stop, 1.0, 0.0, omega};
     return stream_op(OP_JACOBI, a, S(stream));
 }
 
@@ -78,7 +78,7 @@ extern "C" int b200amg_bsr_jacobi(const int *Ap, const int *Aj, const double *Ax
     const size_t ncopy = (size_t)(row_stop - row_start) * blocksize;
     B200_CUDA(cudaMemcpyAsync(temp, x, sizeof(double) * ncopy, cudaMemcpyDeviceToDevice, S(stream)));
     if (blocksize == 1) {
-        StreamArgs a{Ap, Aj, Ax, temp, b, x, -1, row_start, row_stop, 1.0, 0.0, omega};
+        StreamArgs a{Ap, Aj, Ax, temp, b, x, row_start == 0 ? nnz_lookup(Ap, row_stop, S(stream)) : -1, row_start, row_stop, 1.0, 0.0, omega};
         return stream_op(OP_JACOBI_BSR1, a, S(stream));
     }
     return bsr_jacobi(blocksize, row_start, row_stop, Ap, Aj, Ax, temp, x, b, omega, S(stream));
@@ -161,4 +161,21 @@ extern "C" int b200amg_extract_diag(int n_brow, int blocksize, const int *Ap, co
 extern "C" int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, void *stream)
 {
     return dense_matvec(n, M, x, y, S(stream));
+}
+
+// diagnostic: run one stream operation through the engine's sliced-ELL layout (built and freed
+// inside the call).  op: 0 y=Ax, 2 y=b-Ax, 3 y+=Ax, 4 jacobi (CSR arithmetic), 5 jacobi (BSR arithmetic)
+extern "C" int b200amg_selftest_sell(int op, int n_row, const int *Ap, const int *Aj, const double *Ax,
+                                     const double *x, const double *b, double *y, double omega, void *stream)
+{
+    if (n_row <= 0 || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "selftest_sell: bad arguments");
+    const long long nnz = nnz_lookup(Ap, n_row, S(stream));
+    Sell s;
+    B200_TRY(sell_build(n_row, nnz, Ap, Aj, Ax, &s, S(stream)));
+    if (!s.ok()) return set_err(B200AMG_ESTATE, "selftest_sell: layout declined (padding too large)");
+    StreamArgs a{Ap, Aj, Ax, x, b, y, nnz, 0, n_row, 1.0, 0.0, omega};
+    int rc = sell_op(op, s, a, S(stream));
+    cudaStreamSynchronize(S(stream));
+    sell_free(&s);
+    return rc;
 }

@@ -121,7 +121,9 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
 }
 
 // ---- apply ----------------------------------------------------------------------------------
-template <int OP>
+// PIPE: prefetch the next round's slots (100 registers, 2 CTAs/SM) -- pays when the matrix has too few
+// rows to fill the SMs with warps anyway; large matrices run the plain form (64 registers, 4 CTAs/SM)
+template <int OP, bool PIPE>
 __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long long *__restrict__ slice_off,
                                                         const int *__restrict__ cj, const double *__restrict__ cv,
                                                         const int *__restrict__ row_len, const StreamArgs a)
@@ -146,6 +148,42 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     double acc = BSRF ? bi : 0.0, diag = 0.0;
     const int *pj = cj + off + lane;
     const double *pv = cv + off + lane;
+    if (PIPE) {
+    // software pipeline: the (index, value) slots of round r+1 are requested before round r's x
+    // gathers are consumed, so a round costs one memory latency, not two
+    int c[SELL_U], cn[SELL_U];
+    double v[SELL_U], vn[SELL_U], xv[SELL_U];
+#pragma unroll
+    for (int u = 0; u < SELL_U; ++u) {
+        const bool in = u < len;
+        c[u] = in ? __ldcs(pj + (long long)u * SELL_C) : -1;
+        v[u] = in ? __ldcs(pv + (long long)u * SELL_C) : 0.0;
+    }
+    for (int k0 = 0; k0 < w; k0 += SELL_U) {
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            const int k = k0 + SELL_U + u;
+            const bool in = k < len;
+            cn[u] = in ? __ldcs(pj + (long long)k * SELL_C) : -1;
+            vn[u] = in ? __ldcs(pv + (long long)k * SELL_C) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            if (c[u] >= 0) {
+                const double pr = mul_rn(v[u], xv[u]);
+                if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
+                else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            c[u] = cn[u];
+            v[u] = vn[u];
+        }
+    }
+    } else {
     for (int k0 = 0; k0 < w; k0 += SELL_U) {
         int c[SELL_U];
         double v[SELL_U], xv[SELL_U];
@@ -165,6 +203,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
             }
         }
+    }
     }
     if (!live) return;
     double *y = a.y;
@@ -189,7 +228,10 @@ template <int OP>
 static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
-    sell_kernel<OP><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
+    if (s.n < 400000)
+        sell_kernel<OP, true><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
+    else
+        sell_kernel<OP, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
     return check_launch("sell_kernel");
 }
 

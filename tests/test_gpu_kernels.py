@@ -218,3 +218,80 @@ def test_dot_norm_dense(amg):
     amg._lib.call('b200amg_dense_matvec', 37, dM.data_ptr(), dv.data_ptr(), out.data_ptr(), 0)
     torch.cuda.synchronize()
     assert np.allclose(out.cpu().numpy(), M @ v, rtol=1e-13)
+
+
+# ---- schedules of the CSR stream family: persistent TMA pipeline (short rows), sliced-ELL (engine
+#      layout for long rows), chunked stream kernel (everything else) -- same bits everywhere -------
+def lap2d(m):
+    I = sp.eye(m); T = lap1d(m)
+    return sp.csr_matrix(sp.kron(T, I) + sp.kron(I, T))
+
+
+def ragged_matrix(rng, n=20000):
+    """tridiagonal + three rows with 5000 entries (tiles larger than a pipeline stage) + a band of
+    300 rows with ~40 entries (entry-parallel tiles inside a short-row matrix) + empty rows"""
+    A = sp.lil_matrix((n, n))
+    A.setdiag(rng.rand(n) + 2.0)
+    A.setdiag(-rng.rand(n - 1), 1)
+    A.setdiag(-rng.rand(n - 1), -1)
+    for r in (17, 9000, n - 1):
+        cols = rng.choice(n, 5000, replace=False)
+        A[r, cols] = rng.rand(5000)
+    for r in range(4000, 4300):
+        cols = rng.choice(n, 40, replace=False)
+        A[r, cols] = rng.rand(40)
+    A = sp.csr_matrix(A)
+    A.sort_indices()
+    keep = np.ones(n, bool); keep[[100, 101, 5000, n - 2]] = False          # empty rows
+    D = sp.diags(keep.astype(float))
+    A = sp.csr_matrix(D @ A); A.eliminate_zeros(); A.sort_indices()
+    return A
+
+
+PIPE_CASES = [('lap2d_800_ring_wrap', lambda rng: lap2d(800)),          # 2500 tiles: >5 per persistent CTA
+              ('lap2d_333_tail_tile', lambda rng: lap2d(333)),          # last tile partial, n % 4 != 0
+              ('ragged', ragged_matrix)]
+
+
+@pytest.mark.parametrize('name,make', PIPE_CASES)
+def test_pipeline_schedule_bit_exact(amg, name, make):
+    rng = np.random.RandomState(7)
+    A = make(rng)
+    n = A.shape[0]
+    x, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    assert np.array_equal(dA.matvec(dev(x)).cpu().numpy(), A * x)
+    assert np.array_equal(dA.residual(dev(x), dev(b)).cpu().numpy(), b - A * x)
+    for it in range(2):                                                  # second call: cached nnz, warm rings
+        xo = x.copy(); orx.jacobi(A, xo, b, iterations=1, omega=0.8, core=oracle.port)
+        xd = dev(x)
+        amg.relaxation.jacobi(dA, xd, dev(b), iterations=1, omega=0.8)
+        assert np.array_equal(xd.cpu().numpy(), xo)
+
+
+@pytest.mark.parametrize('name,n,per_row', [('coarse_like', 40000, 31), ('restriction_like', 9000, 240),
+                                             ('small_pipe_form', 3000, 60)])
+def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
+    """the engine's SELL-32 copy must give the bits of the CSR kernels / the reference loops"""
+    rng = np.random.RandomState(11)
+    rows = np.repeat(np.arange(n), per_row)
+    cols = (rows + rng.randint(-3 * per_row, 3 * per_row, rows.size)) % n
+    A = sp.csr_matrix((rng.rand(rows.size) - 0.3, (rows, cols)), shape=(n, n))      # duplicates summed, ragged
+    A = sp.csr_matrix(A + sp.diags(rng.rand(n) + 1.0)); A.sort_indices()
+    x, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    P = lambda t: t.data_ptr()
+
+    def run(op, y0):
+        y = dev(y0)
+        dx, db = dev(x), dev(b)
+        amg._lib.call('b200amg_selftest_sell', op, n, P(dA.indptr), P(dA.indices), P(dA.data), P(dx), P(db), P(y), 0.7, 0)
+        return y.cpu().numpy()
+    assert np.array_equal(run(0, np.zeros(n)), A * x)
+    assert np.array_equal(run(2, np.zeros(n)), b - A * x)
+    assert np.array_equal(run(3, b), b + A * x)
+    xo = x.copy(); orx.jacobi(A, xo, b, iterations=1, omega=0.7, core=oracle.port)
+    assert np.array_equal(run(4, np.zeros(n)), xo)
+    Ab = sp.bsr_matrix(A, blocksize=(1, 1))
+    xo = x.copy(); orx.jacobi(Ab, xo, b, iterations=1, omega=0.7, core=oracle.port)
+    assert np.array_equal(run(5, np.zeros(n)), xo)
