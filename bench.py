@@ -277,7 +277,8 @@ def measure_e2e(R, args):
 
 
 def measure_roofline(R, reps=5):
-    """dominant kernel = csr_stream_kernel<JACOBI> on level 0 (pre- and post-smoothing sweep).
+    """dominant kernel = csr_pipe_kernel<OP_JACOBI> on level 0 (pre- and post-smoothing sweep: 2 of the
+    5 level-0 passes, ~36 % of a cycle).
     Its duration is measured live with CUDA events around each operation of un-graphed cycles
     (b200amg_vcycle_profile), on the engine's stream."""
     ml = R['ml']
@@ -296,9 +297,17 @@ def measure_roofline(R, reps=5):
     peak, how = measured_peak()
     ach = nB / (t_j * 1e-3) / 1e9
     t_r = float(np.mean(acc[('residual', 0)]))
-    return {'bound': 'hbm', 'kernel': 'csr_stream_kernel<OP_JACOBI> level 0', 'achieved': round(ach, 1),
+    traffic = None
+    try:        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))
+        if int(tj.get('rows', -1)) == int(A0.shape[0]):
+            traffic = tj['dram_bytes_per_launch']
+    except Exception:
+        traffic = None
+    return {'bound': 'hbm', 'kernel': 'csr_pipe_kernel<OP_JACOBI> level 0 (pre- and post-smoothing sweep)',
+            'achieved': round(ach, 1),
             'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': round(ach / peak, 4),
-            'algorithmic_bytes_per_launch': nB, 'ms_per_launch': round(t_j, 4), 'traffic': None,
+            'algorithmic_bytes_per_launch': nB, 'ms_per_launch': round(t_j, 4), 'traffic': traffic,
             'residual_L0_GBs': round((spmv_bytes(A0.shape[0], A0.shape[1], A0.nnz) + 8 * A0.shape[0]) / (t_r * 1e-3) / 1e9, 1),
             'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
 
