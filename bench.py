@@ -37,6 +37,8 @@ def parse():
                     help='grid points per dimension (BASELINE config: 256)')
     ap.add_argument('--cpu-cycles', type=int, default=3, help='V-cycles of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--agglomerate-below', type=int, default=500000,
+                    help='N > 1: levels with fewer global rows than this run on rank 0 only')
     return ap.parse_args()
 
 
@@ -159,11 +161,12 @@ def dist_env():
     return rank, world, local
 
 
-def build_problem(grid):
+def build_problem(grid, slabs=1):
     """config 2 of BASELINE.json: poisson((g,g,g)) + SA(Jacobi 4/3 pre/post, max_coarse=500), seed 0,
-    built on the device by pyamg_b200 (bit-identical to the reference-built hierarchy, tests/)."""
+    built on the device by pyamg_b200 (bit-identical to the reference-built hierarchy, tests/).
+    slabs > 1: poisson((slabs*g, g, g)) -- `slabs` row slabs of g^3 unknowns (config 5 at 8 x 256^3 = 512^3 unknowns)"""
     import pyamg_b200 as amg
-    A = amg.gallery.poisson((grid, grid, grid))
+    A = amg.gallery.poisson((grid * slabs, grid, grid))
     np.random.seed(0)
     ml = amg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=500)
     b = np.random.rand(A.shape[0])
@@ -245,6 +248,131 @@ def run_b200(args):
     value = world * 1000.0 / ms_step            # replicas: every rank ran its own K cycles
     return dict(ml=ml, b=b, n=n, ms_step=ms_step, value=value, launches=launches, clocks=clocks,
                 setup_s=setup_s, rank=rank, world=world, dist=dist, barrier=barrier)
+
+
+def run_distributed(args):
+    """N > 1: one process per GPU; the level-0/1 operators are row-partitioned (one g^3 slab per GPU),
+    halos refreshed by NCCL all-to-all over NVLink, coarse levels agglomerated on rank 0
+    (pyamg_b200/distributed.py).  The hierarchy is built on rank 0 and its slabs shipped to the owners."""
+    import torch
+    import torch.distributed as dist
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    import pyamg_b200 as amg
+    from pyamg_b200.distributed import DistributedSolver, OP_JACOBI
+    t0 = time.perf_counter()
+    ml, b = (None, None)
+    if rank == 0:
+        ml, b = build_problem(args.grid, world)
+    S = DistributedSolver.from_ml(ml, agglomerate_below=args.agglomerate_below)
+    torch.cuda.synchronize()
+    dist.barrier()
+    setup_s = time.perf_counter() - t0
+
+    def barrier():
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_max(ms):
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    bh = torch.from_numpy(b).pin_memory() if rank == 0 else None
+    S.load(bh)
+    for _ in range(args.warmup):
+        S.cycle()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = amg._lib.launch_count()
+    cur = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()
+    e0.record(cur)
+    for _ in range(args.steps):
+        S.cycle()
+    e1.record(cur)
+    barrier()
+    torch.cuda.profiler.stop()
+    ms_step = reduce_max(e0.elapsed_time(e1)) / args.steps
+    launches = amg._lib.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end to end: global b from pinned host memory on rank 0 -> slabs; one cycle; x gathered to the host
+    for _ in range(2):
+        S.load(bh); S.cycle(); xg = S.gather_x()
+    barrier()
+    t1 = time.perf_counter()
+    e0.record(cur)
+    for _ in range(args.steps):
+        S.load(bh)
+        S.cycle()
+        xg = S.gather_x()
+        if rank == 0:
+            xh = xg.cpu()
+    e1.record(cur)
+    barrier()
+    e2e_ms = reduce_max(max(e0.elapsed_time(e1), (time.perf_counter() - t1) * 1e3)) / args.steps
+
+    # level-0 Jacobi sweep on this rank's slab, timed alone (roofline)
+    L = S.levels[0]
+    for _ in range(3):
+        L.A.apply(OP_JACOBI, L.x, L.b, L.xs, L.info['pre'][1])
+    e0.record(cur)
+    for _ in range(10):
+        L.A.apply(OP_JACOBI, L.x, L.b, L.xs, L.info['pre'][1])
+    e1.record(cur)
+    barrier()
+    t_j = reduce_max(e0.elapsed_time(e1)) / 10
+
+    # parity inside the run: 2 distributed cycles vs 2 single-GPU engine cycles of the same global problem
+    parity = None
+    S.load(bh)
+    S.cycle(); S.cycle()
+    xd = S.gather_x()
+    if rank == 0:
+        xs = ml.solve(torch.from_numpy(b).cuda(), maxiter=2, _norms=False)
+        parity = {'cycles': 2, 'bit_identical_to_single_gpu_engine': bool(torch.equal(xd, xs)),
+                  'max_abs_diff': float((xd - xs).abs().max().item())}
+    barrier()
+    out = None
+    if rank == 0:
+        n_loc, nnz_loc = L.n_own, int(L.A.dx.numel())
+        nB = jacobi_bytes(n_loc, nnz_loc)
+        peak, how = measured_peak()
+        ach = nB / (t_j * 1e-3) / 1e9
+        val = world * 1000.0 / ms_step
+        out = {'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1)' % args.grid,
+               'value': val, 'unit': 'V-cycles/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+               'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+               'dtype': 'f64', 'data': 'synthetic',
+               'config': {'workload': 'configs[1] per GPU / configs[4] in total: 3D Poisson %dx%dx%d 7-point (%d slabs of %d^3, one per GPU), '
+                                      'smoothed_aggregation_solver, Jacobi(4/3) pre/post, max_coarse=500, fp64, one distributed '
+                                      'V(1,1)-cycle per step' % (args.grid * world, args.grid, args.grid, world, args.grid),
+                          'value_definition': 'n_gpus x distributed V-cycles/s (every distributed cycle sweeps n_gpus slabs of %d^3 '
+                                              'unknowns; the same unit as the 1-GPU line)' % args.grid,
+                          'distributed_cycles_per_s': 1000.0 / ms_step,
+                          'levels': level_table(ml), 'partitioned_levels': len(S.levels),
+                          'parallelism': 'row slabs over %d GPUs, NCCL all-to-all halo refresh (%d per cycle), levels >= %d agglomerated on rank 0'
+                                         % (world, S.exchanges // max(1, (args.warmup + 3 * args.steps + 6)), S.ka),
+                          'l2': 'inputs larger than L2', 'setup_s_rank0_build_and_distribute': round(setup_s, 2)},
+               'clocks': clocks,
+               'e2e': {'value': world * 1000.0 / e2e_ms, 'unit': 'V-cycles/s', 'h2d_bytes_per_step': 8 * b.size,
+                       'd2h_bytes_per_step': 8 * b.size,
+                       'call': 'DistributedSolver.load(b_host_pinned) + cycle() + gather_x().cpu() on rank 0'},
+               'gpu_launches': int(launches) * world,
+               'roofline': {'bound': 'hbm', 'kernel': 'csr_pipe_kernel<OP_JACOBI> on one rank\'s level-0 slab, timed alone',
+                            'achieved': round(ach, 1), 'peak': peak, 'peak_source': how, 'unit': 'GB/s',
+                            'frac': round(ach / peak, 4), 'algorithmic_bytes_per_launch': nB, 'ms_per_launch': round(t_j, 4),
+                            'traffic': None},
+               'parity_in_run': parity}
+    dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out))
 
 
 def measure_e2e(R, args):
@@ -401,6 +529,9 @@ def main():
     args = parse()
     if args.impl == 'reference':
         run_reference(args)
+        return
+    if dist_env()[1] > 1:
+        run_distributed(args)
         return
     R = run_b200(args)
     e2e = measure_e2e(R, args)

@@ -104,11 +104,22 @@ int b200amg_extract_diag(int n_brow, int blocksize, const int *Ap, const int *Aj
 /* y = M x, dense row-major M (n x n): coarse_grid_solver('pinv2'), multilevel.py:608-612 */
 int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, void *stream);
 
-/* diagnostic (tests): one SpMV-family operation through the engine's sliced-ELL (SELL-32) layout,
- * which b200amg_vcycle_create builds for operators with 12..400 entries per row.  op: 0 y = A x,
- * 2 y = b - A x, 3 y += A x, 4 amg_core.jacobi arithmetic (x in, y out), 5 bsr_jacobi(bs=1) arithmetic */
-int b200amg_selftest_sell(int op, int n_row, const int *Ap, const int *Aj, const double *Ax,
-                          const double *x, const double *b, double *y, double omega, void *stream);
+/* ---- operator handles: a level operator bound once to its best device layout ---------------
+ * layout 0: automatic (sliced-ELL SELL-32 copy for 12..400 entries per row, else the caller's CSR),
+ * 1: CSR kernels only, 2: force the sliced-ELL copy.  The handle keeps the caller's pointers
+ * (not the arrays) and owns only its SELL copy.  op: 0  y = A x          (scipy csr_matvec)
+ *                                                    2  y = b - A x      (multilevel.py:496)
+ *                                                    3  y += A x         (multilevel.py:544)
+ *                                                    4  y = jacobi(x)    out of place, amg_core.jacobi arithmetic
+ *                                                    5  y = jacobi(x)    out of place, amg_core.bsr_jacobi(bs=1) arithmetic
+ * Results are bit-identical across layouts.  Used by the row-partitioned multi-GPU cycle
+ * (pyamg_b200/distributed.py), where every rank applies LOCAL operators to [owned | halo] vectors. */
+int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
+                      void **handle_out, void *stream);
+int b200amg_op_apply(void *handle, int op, const double *x, const double *b, double *y, double omega,
+                     void *stream);
+int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL */
+int b200amg_op_destroy(void *handle);
 
 /* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
  *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */

@@ -40,7 +40,10 @@ _SIGS = {
     'b200amg_gauss_seidel_indexed': (c_int, [p, p, p, p, p, p, c_int, c_int, c_int, POINTER(c_int), c_int, p]),
     'b200amg_gauss_seidel': (c_int, [p, p, p, p, p, c_int, c_int, c_int, p]),
     'b200amg_bsr_gauss_seidel': (c_int, [p, p, p, p, p, c_int, c_int, c_int, c_int, p, POINTER(c_int), c_int, p]),
-    'b200amg_selftest_sell': (c_int, [c_int, c_int, p, p, p, p, p, p, c_double, p]),
+    'b200amg_op_create': (c_int, [c_int, p, p, p, c_int, POINTER(c_void_p), p]),
+    'b200amg_op_apply': (c_int, [p, c_int, p, p, p, c_double, p]),
+    'b200amg_op_layout': (c_int, [p]),
+    'b200amg_op_destroy': (c_int, [p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
     'b200amg_axpy': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scale_diag': (c_int, [c_longlong, c_double, p, p, p, c_int, p]),

@@ -20,7 +20,7 @@ from . import _lib, amg_core
 from .linalg import approximate_spectral_radius
 from .multilevel import multilevel_solver
 from .smoothing import change_smoothers
-from .sparse import DevMat, _dev, _ptr, _scan_i32, _stream, matmat, transpose
+from .sparse import DevMat, _dev, _ptr, _scan_i32, _stream, galerkin, matmat, transpose
 
 
 def _unpack(v):
@@ -180,7 +180,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         if keep:
             lvl.AggOp, lvl.T, lvl.Cpts = agg, T, roots
         lvl.P, lvl.R = P, R
-        Ac = matmat(matmat(R, A, scipy_order=True), P, scipy_order=True)
+        Ac = galerkin(R, A, P, scipy_order=True)
         levels.append(multilevel_solver.level())
         levels[-1].A = DevMat(Ac.indptr, Ac.indices, Ac.data, Ac.shape, (1, 1), 'bsr', False)
         levels[-1].B = Bc

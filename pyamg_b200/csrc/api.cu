@@ -163,19 +163,59 @@ extern "C" int b200amg_dense_matvec(int n, const double *M, const double *x, dou
     return dense_matvec(n, M, x, y, S(stream));
 }
 
-// diagnostic: run one stream operation through the engine's sliced-ELL layout (built and freed
-// inside the call).  op: 0 y=Ax, 2 y=b-Ax, 3 y+=Ax, 4 jacobi (CSR arithmetic), 5 jacobi (BSR arithmetic)
-extern "C" int b200amg_selftest_sell(int op, int n_row, const int *Ap, const int *Aj, const double *Ax,
-                                     const double *x, const double *b, double *y, double omega, void *stream)
+// ---- operator handles: one level operator bound to its best layout ---------------------------
+struct OpHandle {
+    int n_row;
+    long long nnz;
+    const int *Ap, *Aj;
+    const double *Ax;
+    Sell sell;
+};
+
+extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
+                                 void **handle_out, void *stream)
 {
-    if (n_row <= 0 || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "selftest_sell: bad arguments");
-    const long long nnz = nnz_lookup(Ap, n_row, S(stream));
-    Sell s;
-    B200_TRY(sell_build(n_row, nnz, Ap, Aj, Ax, &s, S(stream)));
-    if (!s.ok()) return set_err(B200AMG_ESTATE, "selftest_sell: layout declined (padding too large)");
-    StreamArgs a{Ap, Aj, Ax, x, b, y, nnz, 0, n_row, 1.0, 0.0, omega};
-    int rc = sell_op(op, s, a, S(stream));
-    cudaStreamSynchronize(S(stream));
-    sell_free(&s);
-    return rc;
+    if (n_row < 0 || !handle_out || layout < 0 || layout > 2) return set_err(B200AMG_EINVAL, "op_create: bad arguments");
+    OpHandle *h = new OpHandle{n_row, -1, Ap, Aj, Ax, Sell()};
+    if (n_row > 0) {
+        int ends[2] = {0, 0};
+        cudaError_t e = cudaMemcpyAsync(&ends[0], Ap, sizeof(int), cudaMemcpyDeviceToHost, S(stream));
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&ends[1], Ap + n_row, sizeof(int), cudaMemcpyDeviceToHost, S(stream));
+        if (e == cudaSuccess) e = cudaStreamSynchronize(S(stream));
+        if (e != cudaSuccess) { delete h; return set_err((int)e, "op_create: cannot read row pointers"); }
+        h->nnz = (long long)ends[1] - ends[0];
+        if (layout == 2 || (layout == 0 && sell_wanted(h->nnz, n_row))) {
+            int rc = sell_build(n_row, h->nnz, Ap, Aj, Ax, &h->sell, S(stream));
+            if (rc) { delete h; return rc; }
+            if (layout == 2 && !h->sell.ok()) { delete h; return set_err(B200AMG_ESTATE, "op_create: sliced-ELL layout declined (padding too large)"); }
+        }
+    }
+    *handle_out = h;
+    return 0;
+}
+
+extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const double *b, double *y, double omega,
+                                void *stream)
+{
+    OpHandle *h = reinterpret_cast<OpHandle *>(handle);
+    if (!h || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "op_apply: bad arguments");
+    if (h->n_row == 0) return 0;
+    StreamArgs a{h->Ap, h->Aj, h->Ax, x, b, y, h->nnz, 0, h->n_row, 1.0, 0.0, omega};
+    if (h->sell.ok()) return sell_op(op, h->sell, a, S(stream));
+    return stream_op(op, a, S(stream));
+}
+
+extern "C" int b200amg_op_layout(void *handle)
+{
+    OpHandle *h = reinterpret_cast<OpHandle *>(handle);
+    return h ? (h->sell.ok() ? 2 : 1) : 0;
+}
+
+extern "C" int b200amg_op_destroy(void *handle)
+{
+    OpHandle *h = reinterpret_cast<OpHandle *>(handle);
+    if (!h) return 0;
+    sell_free(&h->sell);
+    delete h;
+    return 0;
 }

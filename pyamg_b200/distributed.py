@@ -1,0 +1,340 @@
+"""Row-partitioned V-cycle over G GPUs of one node (one process per GPU, torch.distributed).
+
+* Levels with at least `agglomerate_below` rows are cut into contiguous row slabs (partition.py);
+  every rank applies its LOCAL operators (same rows, same storage order -> same bits as the
+  single-GPU kernels) to `[owned | halo]` vectors; the halo is refreshed by ONE all-to-all
+  (grouped NCCL send/recv over NVLink) before each operator application:
+      x before the pre-smoothing sweep, x before the residual, r before the restriction,
+      x_c before the prolongation, x before the post-smoothing sweep.
+* Levels below the threshold are agglomerated on rank 0: b_c is gathered there, the lower part of the
+  cycle runs in the ordinary single-GPU engine (multilevel_solver over levels[ka:], one CUDA-graph
+  replay), x_c is scattered back.
+* Norms: local dot + all-reduce.
+Jacobi parity across ranks is exact (row arithmetic is rank-independent); norms differ in summation
+order only.  The hierarchy is built on rank 0 (setup across GPUs is out of the first milestone)
+and its slabs are shipped to their owners.
+
+`backend` supplies the per-rank compute (default: libb200amg through the C-ABI; there is no CPU
+fallback -- the CPU/gloo tests inject a checker backend from tests/).
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import partition as part
+
+OP_MATVEC, OP_RESIDUAL, OP_ADD, OP_JACOBI, OP_JACOBI_BSR1 = 0, 2, 3, 4, 5
+
+
+class DeviceBackend:
+    """per-rank compute through libb200amg (operator handles: pipeline / sliced-ELL / stream kernels)"""
+
+    def __init__(self):
+        from . import _lib
+        from .sparse import _dev
+        self._lib, self.device = _lib, _dev()
+
+    def stream(self):
+        return torch.cuda.current_stream().cuda_stream
+
+    class Op:
+        def __init__(self, be, ip, ix, dx, n_row):
+            self.be, self.ip, self.ix, self.dx, self.n_row = be, ip, ix, dx, int(n_row)
+            self.h = ctypes.c_void_p()
+            be._lib.call('b200amg_op_create', self.n_row, ip.data_ptr(), ix.data_ptr(), dx.data_ptr(), 0,
+                         ctypes.byref(self.h), be.stream())
+
+        def apply(self, op, x, b, y, omega=0.0):
+            self.be._lib.call('b200amg_op_apply', self.h, op, x.data_ptr(), 0 if b is None else b.data_ptr(),
+                              y.data_ptr(), float(omega), self.be.stream())
+
+        def diagonal(self):
+            d = torch.empty(self.n_row, dtype=torch.float64, device=self.dx.device)
+            self.be._lib.call('b200amg_extract_diag', self.n_row, 1, self.ip.data_ptr(), self.ix.data_ptr(),
+                              self.dx.data_ptr(), d.data_ptr(), self.be.stream())
+            return d
+
+        def __del__(self):
+            try:
+                self.be._lib.load().b200amg_op_destroy(self.h)
+            except Exception:
+                pass
+
+    def make_op(self, ip, ix, dx, n_row):
+        return DeviceBackend.Op(self, ip, ix, dx, n_row)
+
+    def scale_diag(self, omega, b, diag, x, flavor):
+        self._lib.call('b200amg_scale_diag', diag.numel(), float(omega), b.data_ptr(), diag.data_ptr(), x.data_ptr(),
+                       int(flavor), self.stream())
+
+    def dot(self, x, y, n):
+        if not hasattr(self, '_dw'):
+            self._dw = torch.empty(1024, dtype=torch.float64, device=self.device)
+        out = torch.empty(1, dtype=torch.float64, device=self.device)
+        self._lib.call('b200amg_dot', int(n), x.data_ptr(), y.data_ptr(), out.data_ptr(), self._dw.data_ptr(), self.stream())
+        return out
+
+
+class _Level:
+    pass
+
+
+def _send_tensors(tensors, dst, group):
+    for t in tensors:
+        dist.send(t.contiguous(), dst, group=group)
+
+
+def _recv_tensors(specs, src, device, group):
+    out = []
+    for n, dt in specs:
+        t = torch.empty(n, dtype=dt, device=device)
+        dist.recv(t, src, group=group)
+        out.append(t)
+    return out
+
+
+def describe(ml):
+    """rank-0 description of a device multilevel_solver for DistributedSolver: per non-coarsest level
+    the raw CSR arrays of A, P, R (torch tensors), sizes, arithmetic flavor and resolved smoothers"""
+    out = []
+    for L in ml.levels[:-1]:
+        for nm in ('A', 'P', 'R'):
+            if not getattr(L, nm).is_scalar:
+                raise NotImplementedError('distributed cycle: scalar (1x1 block) levels only')
+        pre, post = L.presmoother, L.postsmoother
+        for sm in (pre, post):
+            if sm.kind not in (0, 1):
+                raise NotImplementedError('distributed cycle: Jacobi / None smoothers only')
+        d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
+             'pre': (pre.kind, pre.omega, pre.iterations), 'post': (post.kind, post.omega, post.iterations)}
+        for nm in ('A', 'P', 'R'):
+            M = getattr(L, nm)
+            d[nm] = (M.indptr, M.indices, M.data)
+        out.append(d)
+    return out
+
+
+class DistributedSolver:
+    """Collective constructor.  On rank 0: `levels` = describe(ml) (or an equivalent list) and
+    `coarse_factory(ka)` -> object with cycle_from_zero(b_c) -> x_c running levels[ka:] on rank 0;
+    both None on the other ranks."""
+
+    @classmethod
+    def from_ml(cls, ml, **kw):
+        """ml: device multilevel_solver on rank 0, None elsewhere"""
+        if ml is None:
+            return cls(None, None, **kw)
+        from .multilevel import multilevel_solver
+
+        def coarse(ka):
+            sub = multilevel_solver(ml.levels[ka:], coarse_solver=ml.coarse_solver_spec)
+            return sub
+        return cls(describe(ml), coarse, **kw)
+
+    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=500000, backend=None, device=None):
+        self.group = group
+        self.rank, self.G = dist.get_rank(group), dist.get_world_size(group)
+        self.be = backend if backend is not None else DeviceBackend()
+        self.device = device if device is not None else self.be.device
+        self.exchanges = 0
+        meta = [None]
+        if self.rank == 0:
+            nlev = len(levels) + 1
+            ka = nlev - 1
+            for k in range(1, nlev - 1):
+                if levels[k]['n'] < agglomerate_below:
+                    ka = k
+                    break
+            info = [{q: levels[k][q] for q in ('n', 'nc', 'flavor', 'pre', 'post')} for k in range(ka)]
+            meta[0] = {'ka': ka, 'nlev': nlev, 'levels': info}
+        dist.broadcast_object_list(meta, src=0, group=group)
+        meta = meta[0]
+        self.ka, self.nlev = meta['ka'], meta['nlev']
+        self.levels = []
+        for k in range(self.ka):
+            self.levels.append(self._distribute_level(k, meta['levels'][k], levels[k] if self.rank == 0 else None))
+        # agglomerated lower part of the cycle: ordinary single-GPU engine on rank 0
+        self.coarse = None
+        if self.rank == 0:
+            self.coarse = coarse_factory(self.ka)
+            self.nc_global = meta['levels'][-1]['nc']
+        self._alloc()
+
+    # ---- setup ---------------------------------------------------------------------------------
+    def _distribute_level(self, k, info, src):
+        G, rank, dev = self.G, self.rank, self.device
+        n, nc = info['n'], info['nc']
+        sp, spc = part.split_points(n, G), part.split_points(nc, G)
+        L = _Level()
+        L.info, L.split, L.csplit = info, sp, spc
+        L.n_own, L.nc_own = sp[rank + 1] - sp[rank], spc[rank + 1] - spc[rank]
+        shapes = {'A': (sp, sp), 'P': (sp, spc), 'R': (spc, sp)}
+        for nm in ('A', 'P', 'R'):
+            rs, cs = shapes[nm]
+            header = [None]
+            if rank == 0:
+                Mp, Mj, Mx = src[nm]
+                halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1])[3] for p in range(G)]
+                plans = part.build_plans(halos, cs)
+                header[0] = [pl.pack() for pl in plans]
+            dist.broadcast_object_list(header, src=0, group=self.group)
+            plan = part.HaloPlan.unpack(header[0][rank]).to(dev)
+            if rank == 0:
+                mine = None
+                for p in range(G):
+                    ip, ix, dx, _ = part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1])
+                    if p == 0:
+                        mine = (ip, ix, dx)
+                    else:
+                        sizes = torch.tensor([ip.numel(), ix.numel()], dtype=torch.int64, device=dev)
+                        dist.send(sizes, p, group=self.group)
+                        _send_tensors((ip, ix, dx), p, self.group)
+                    del ip, ix, dx
+                ip, ix, dx = mine
+            else:
+                sizes = torch.empty(2, dtype=torch.int64, device=dev)
+                dist.recv(sizes, 0, group=self.group)
+                n_ip, n_ix = [int(v) for v in sizes.tolist()]
+                ip, ix, dx = _recv_tensors([(n_ip, torch.int32), (n_ix, torch.int32), (n_ix, torch.float64)], 0, dev, self.group)
+            setattr(L, nm, self.be.make_op(ip, ix, dx, ip.numel() - 1))
+            setattr(L, 'plan' + nm, plan)
+        L.diag = L.A.diagonal()
+        return L
+
+    def _alloc(self):
+        dev, f64 = self.device, torch.float64
+        for k, L in enumerate(self.levels):
+            halo_x = max(L.planA.n_halo, self.levels[k - 1].planP.n_halo if k > 0 else 0)
+            L.x = torch.zeros(L.n_own + halo_x, dtype=f64, device=dev) if k == 0 else self.levels[k - 1].xc
+            L.xs = torch.zeros(L.n_own + halo_x, dtype=f64, device=dev)
+            L.r = torch.zeros(L.n_own + L.planR.n_halo, dtype=f64, device=dev)
+            L.bc = torch.zeros(max(L.nc_own, 1), dtype=f64, device=dev)
+            nxt_halo = self.levels[k + 1].planA.n_halo if k + 1 < len(self.levels) else 0
+            L.xc = torch.zeros(L.nc_own + max(L.planP.n_halo, nxt_halo), dtype=f64, device=dev)
+            L.b = torch.zeros(max(L.n_own, 1), dtype=f64, device=dev) if k == 0 else self.levels[k - 1].bc
+        if self.rank == 0:
+            self.cb = torch.zeros(self.nc_global, dtype=f64, device=dev)
+        self._sbuf = {}
+
+    # ---- communication -------------------------------------------------------------------------
+    def exchange(self, plan, v):
+        """refresh v[n_own : n_own + n_halo] from the owners (v = [owned | halo])"""
+        if self.G == 1 or (plan.n_halo == 0 and plan.send_idx.numel() == 0):
+            return
+        send = v[:plan.n_own].index_select(0, plan.send_idx)
+        recv = v[plan.n_own:plan.n_own + plan.n_halo]
+        dist.all_to_all_single(recv, send, output_split_sizes=plan.recv_counts, input_split_sizes=plan.send_counts,
+                               group=self.group)
+        self.exchanges += 1
+
+    def _gather_coarse(self, L):
+        spc = L.csplit
+        sizes = [spc[p + 1] - spc[p] for p in range(self.G)]
+        out = self.cb if self.rank == 0 else torch.empty(0, dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(out, L.bc[:L.nc_own], output_split_sizes=sizes if self.rank == 0 else [0] * self.G,
+                               input_split_sizes=[L.nc_own] + [0] * (self.G - 1), group=self.group)
+
+    def _scatter_coarse(self, L, xc_global):
+        spc = L.csplit
+        sizes = [spc[p + 1] - spc[p] for p in range(self.G)]
+        src = xc_global if self.rank == 0 else torch.empty(0, dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(L.xc[:L.nc_own], src, output_split_sizes=[L.nc_own] + [0] * (self.G - 1),
+                               input_split_sizes=sizes if self.rank == 0 else [0] * self.G, group=self.group)
+
+    # ---- the cycle (multilevel.py:473-548 on slabs) ----------------------------------------------
+    def _smooth(self, L, spec, x, xs, b, x_is_zero):
+        kind, omega, iters = spec
+        if kind == 0 or iters == 0:
+            if x_is_zero:
+                x[:L.n_own].zero_()
+            return x, xs
+        op = OP_JACOBI_BSR1 if L.info['flavor'] else OP_JACOBI
+        for it in range(iters):
+            if it == 0 and x_is_zero:
+                self.be.scale_diag(omega, b, L.diag, x, L.info['flavor'])     # bit-identical zero-guess sweep
+                continue
+            self.exchange(L.planA, x)
+            L.A.apply(op, x, b, xs, omega)
+            x, xs = xs, x
+        return x, xs
+
+    def _cycle(self, k, x, b, x_is_zero):
+        L = self.levels[k]
+        xs = L.xs if L.xs is not x else L.x
+        x, xs = self._smooth(L, L.info['pre'], x, xs, b, x_is_zero)
+        self.exchange(L.planA, x)
+        L.A.apply(OP_RESIDUAL, x, b, L.r)
+        self.exchange(L.planR, L.r)
+        L.R.apply(OP_MATVEC, L.r, None, L.bc)
+        xc = L.xc
+        if k + 1 < len(self.levels):
+            xc, _ = self._cycle(k + 1, L.xc, L.bc, True)          # the iterate may end in the child's spare buffer
+        else:
+            self._gather_coarse(L)
+            xg = self.coarse.cycle_from_zero(self.cb) if self.rank == 0 else None
+            self._scatter_coarse(L, xg)
+        self.exchange(L.planP, xc)
+        L.P.apply(OP_ADD, xc, None, x)
+        x, xs = self._smooth(L, L.info['post'], x, xs, b, False)
+        return x, xs
+
+    def cycle(self):
+        """one V-cycle on the resident (x, b) slabs"""
+        L = self.levels[0]
+        L.x, L.xs = self._cycle(0, L.x, L.b, False)        # ping-pong: no copy back
+
+    # ---- data movement / norms ---------------------------------------------------------------------
+    def load(self, b_global=None, x0_global=None):
+        """scatter b (and x0, default 0) from rank 0 to the slabs"""
+        L = self.levels[0]
+        sp = L.split
+        sizes = [sp[p + 1] - sp[p] for p in range(self.G)]
+        for dst, src in ((L.b, b_global), (L.x, x0_global)):
+            if src is None and dst is L.x:
+                L.x.zero_()
+                continue
+            s = torch.as_tensor(src, dtype=torch.float64).to(self.device).reshape(-1) if self.rank == 0 else \
+                torch.empty(0, dtype=torch.float64, device=self.device)
+            dist.all_to_all_single(dst[:L.n_own], s, output_split_sizes=[L.n_own] + [0] * (self.G - 1),
+                                   input_split_sizes=sizes if self.rank == 0 else [0] * self.G, group=self.group)
+
+    def gather_x(self):
+        L = self.levels[0]
+        sp = L.split
+        sizes = [sp[p + 1] - sp[p] for p in range(self.G)]
+        out = torch.empty(sp[-1] if self.rank == 0 else 0, dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(out, L.x[:L.n_own], output_split_sizes=sizes if self.rank == 0 else [0] * self.G,
+                               input_split_sizes=[L.n_own] + [0] * (self.G - 1), group=self.group)
+        return out if self.rank == 0 else None
+
+    def residual_norm(self):
+        L = self.levels[0]
+        self.exchange(L.planA, L.x)
+        L.A.apply(OP_RESIDUAL, L.x, L.b, L.r)
+        s = self.be.dot(L.r, L.r, L.n_own)
+        dist.all_reduce(s, group=self.group)
+        return float(np.sqrt(s.item()))
+
+    def norm_b(self):
+        L = self.levels[0]
+        s = self.be.dot(L.b, L.b, L.n_own)
+        dist.all_reduce(s, group=self.group)
+        return float(np.sqrt(s.item()))
+
+    def solve(self, b=None, x0=None, tol=1e-5, maxiter=100, residuals=None):
+        """multilevel_solver.solve semantics (multilevel.py:316-471) on the partitioned problem.
+        b / x0 are global arrays on rank 0 (ignored elsewhere); returns global x on rank 0, None elsewhere."""
+        self.load(b, x0)
+        normb = self.norm_b()
+        if normb != 0:
+            tol = tol * normb
+        res = [self.residual_norm()]
+        while len(res) <= maxiter and res[-1] > tol:
+            self.cycle()
+            res.append(self.residual_norm())
+        if residuals is not None:
+            residuals[:] = res
+        x = self.gather_x()
+        return x

@@ -82,6 +82,7 @@ class multilevel_solver:
 
     def __init__(self, levels, coarse_solver='pinv2'):
         self.levels = levels
+        self.coarse_solver_spec = coarse_solver
         self.coarse_solver = coarse_grid_solver(coarse_solver)
         for lvl in levels:
             for nm in ('A', 'P', 'R'):
@@ -224,6 +225,23 @@ class multilevel_solver:
         _lib.call('b200amg_vcycle_profile', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], cap,
                   code, lev, ms, ctypes.byref(n), self._stream.cuda_stream)
         return [(names[code[i]], lev[i], float(ms[i])) for i in range(n.value)]
+
+    def cycle_from_zero(self, b_dev, cycle='V'):
+        """x = one cycle from a zero guess for a DEVICE right-hand side: no norms, no host sync, the
+        result stays in the engine's x buffer (valid until the next call).  Used for the agglomerated
+        coarse levels of the row-partitioned cycle (distributed.py)."""
+        if len(self.levels) == 1:
+            return self.coarse_solver(self.levels[0].A, b_dev)
+        if self._engine is None:
+            self._build_engine()
+        cur = torch.cuda.current_stream()
+        self._stream.wait_stream(cur)
+        with torch.cuda.stream(self._stream):
+            self._b.copy_(b_dev, non_blocking=True)
+            self._x.zero_()
+            self.cycle_device(cycle)
+        cur.wait_stream(self._stream)
+        return self._x
 
     # ---- public API (multilevel.py:271-471) -------------------------------------------------
     def psolve(self, b):

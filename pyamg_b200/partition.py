@@ -1,0 +1,97 @@
+"""Row-slab partition of a multigrid hierarchy over G ranks: index plumbing only.
+
+Every partitioned level is cut into G contiguous row slabs (rank p owns rows
+[split[p], split[p+1]) of A_l and P_l, and the rows of R_l of its coarse slab).  A local operator
+keeps its rows exactly as stored (same entries, same order: the fp summation order of the reference
+is untouched) with columns renumbered into the rank's local vector layout
+
+        [ owned entries (global - split[p]) | halo entries, ascending global index ]
+
+so the single-GPU kernels run unchanged on `[owned | halo]` vectors.  Because ownership ranges are
+contiguous and the halo is sorted, the halo region is the concatenation, by owner rank, of what each
+peer must send: one all-to-all (grouped NCCL send/recv over NVLink) with precomputed counts refreshes it.
+
+Everything here is torch tensor arithmetic and therefore device-agnostic: rank 0 runs it on its GPU
+for the real thing, the CPU tests run the same code on gloo.  No floating-point arithmetic happens here.
+"""
+import torch
+
+
+def split_points(n, G):
+    """contiguous, near-equal slabs: split[p] = floor(n p / G)"""
+    return [(n * p) // G for p in range(G + 1)]
+
+
+def owner_counts(sorted_cols, split):
+    """how many entries of an ascending global index list fall into each owner's range"""
+    bounds = torch.tensor(split, dtype=sorted_cols.dtype, device=sorted_cols.device)
+    pos = torch.searchsorted(sorted_cols, bounds)
+    return (pos[1:] - pos[:-1]).tolist()
+
+
+def localize(indptr, indices, data, row0, row1, col0, col1):
+    """Rows [row0, row1) of a CSR/BSR(1x1) matrix with columns renumbered for the rank owning the
+    column range [col0, col1).  -> (indptr int32, indices int32, data, halo_cols int64 ascending)"""
+    s, e = int(indptr[row0]), int(indptr[row1])
+    ip = (indptr[row0:row1 + 1] - indptr[row0]).to(torch.int32).contiguous()
+    cols = indices[s:e].to(torch.int64)
+    own = (cols >= col0) & (cols < col1)
+    halo_cols = torch.unique(cols[~own])                       # sorted ascending
+    loc = torch.empty_like(cols)
+    loc[own] = cols[own] - col0
+    if halo_cols.numel():
+        loc[~own] = (col1 - col0) + torch.searchsorted(halo_cols, cols[~own])
+    return ip, loc.to(torch.int32).contiguous(), data[s:e].contiguous().clone(), halo_cols
+
+
+class HaloPlan:
+    """what one rank sends / receives to refresh the halo of one vector space"""
+
+    def __init__(self, n_own, n_halo, send_idx, send_counts, recv_counts):
+        self.n_own, self.n_halo = int(n_own), int(n_halo)
+        self.send_idx = send_idx                  # int64 local indices into the owned part, grouped by peer
+        self.send_counts = [int(c) for c in send_counts]
+        self.recv_counts = [int(c) for c in recv_counts]
+
+    def to(self, device):
+        self.send_idx = self.send_idx.to(device)
+        return self
+
+    def pack(self):
+        return {'n_own': self.n_own, 'n_halo': self.n_halo, 'send_idx': self.send_idx.cpu(),
+                'send_counts': self.send_counts, 'recv_counts': self.recv_counts}
+
+    @classmethod
+    def unpack(cls, d):
+        return cls(d['n_own'], d['n_halo'], d['send_idx'], d['send_counts'], d['recv_counts'])
+
+
+def build_plans(halo_lists, split):
+    """halo_lists[p] = ascending global indices rank p needs (none inside its own range).
+    -> [HaloPlan for every rank]"""
+    G = len(split) - 1
+    recv = [owner_counts(h, split) for h in halo_lists]                     # recv[p][q]: p gets from q
+    plans = []
+    for q in range(G):
+        parts, counts = [], []
+        for p in range(G):
+            h = halo_lists[p]
+            lo = sum(recv[p][:q])
+            seg = h[lo:lo + recv[p][q]] - split[q]                         # q's local indices p wants
+            parts.append(seg)
+            counts.append(recv[p][q])
+        send_idx = torch.cat(parts) if parts else torch.empty(0, dtype=torch.int64)
+        plans.append(HaloPlan(split[q + 1] - split[q], halo_lists[q].numel(), send_idx.to(torch.int64),
+                              counts, recv[q]))
+    return plans
+
+
+def partition_operator(indptr, indices, data, row_split, col_split):
+    """-> per rank (ip, ix, dx) and the HaloPlans of the operator's COLUMN space"""
+    G = len(row_split) - 1
+    locs, halos = [], []
+    for p in range(G):
+        ip, ix, dx, h = localize(indptr, indices, data, row_split[p], row_split[p + 1], col_split[p], col_split[p + 1])
+        locs.append((ip, ix, dx))
+        halos.append(h)
+    return locs, build_plans(halos, col_split)

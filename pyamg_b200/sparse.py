@@ -160,10 +160,14 @@ def _scan_i64(v):
     return out
 
 
-def matmat(A, B, scipy_order=False):
+MATMAT_BATCH_PRODUCTS = 400_000_000      # scratch bound of one SpGEMM pass: 12 bytes per product -> 4.8 GB
+
+
+def matmat(A, B, scipy_order=False, batch_products=None):
     """C = A B for scalar CSR/BSR(1,1) operands: exact zeros dropped, values bit-identical to
     scipy's csr_matmat (see csrc/spgemm.cu).  Rows sorted by column, or (scipy_order=True) in
-    scipy's own reverse-first-touch order."""
+    scipy's own reverse-first-touch order.  Rows are independent, so large products run in row
+    batches whose expand-sort-compress scratch stays below `batch_products` entries (same result)."""
     if not (A.is_scalar and B.is_scalar):
         raise NotImplementedError('matmat: only scalar (1x1 block) operands')
     if A.shape[1] != B.shape[0]:
@@ -171,25 +175,56 @@ def matmat(A, B, scipy_order=False):
     n = A.shape[0]
     dev = A.data.device
     st = _stream()
+    limit = int(batch_products or MATMAT_BATCH_PRODUCTS)
     ub = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     _lib.call('b200amg_spgemm_count', n, _ptr(A.indptr), _ptr(A.indices), _ptr(B.indptr), _ptr(ub), st)
     ub = ub[:n]
     ubp = _scan_i64(ub)
     total = int(ubp[-1].item())
-    big = bool((ub.max() > 8192).item()) if n else False
-    Tj = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
-    Tx = torch.empty(max(total, 1), dtype=torch.float64, device=dev)
-    Tk = torch.empty(max(total, 1), dtype=torch.int64, device=dev) if big else None
     cnt = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
-    work = torch.empty(n + 256, dtype=torch.int32, device=dev)
-    _lib.call('b200amg_spgemm_numeric', n, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr),
-              _ptr(B.indices), _ptr(B.data), _ptr(ub), _ptr(ubp), _ptr(Tk), _ptr(Tj), _ptr(Tx), _ptr(cnt),
-              _ptr(work), int(bool(scipy_order)), st)
-    Cp = _scan_i32(cnt[:n])
-    nnz = int(Cp[-1].item())
-    Cj = torch.empty(nnz, dtype=torch.int32, device=dev)
-    Cx = torch.empty(nnz, dtype=torch.float64, device=dev)
-    _lib.call('b200amg_spgemm_compact', n, _ptr(ubp), _ptr(Tj), _ptr(Tx), _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
+    # row batches [r0, r1) with at most `limit` products each (a single row may exceed it)
+    cuts = [0]
+    if total > limit:
+        targets = torch.arange(limit, total, limit, dtype=torch.int64, device=dev)
+        for c in torch.searchsorted(ubp, targets, right=True).tolist():
+            c = min(max(int(c) - 1, cuts[-1] + 1), n)
+            if c > cuts[-1]:
+                cuts.append(c)
+    if cuts[-1] != n:
+        cuts.append(n)
+    pieces = []
+    for r0, r1 in zip(cuts[:-1], cuts[1:]):
+        m = r1 - r0
+        if len(cuts) == 2:
+            ubp_b, tot_b = ubp, total
+        else:
+            ubp_b = (ubp[r0:r1 + 1] - ubp[r0]).contiguous()
+            tot_b = int(ubp_b[-1].item())
+        ub_b = ub[r0:r1]
+        big = bool((ub_b.max() > 8192).item()) if m else False
+        Tj = torch.empty(max(tot_b, 1), dtype=torch.int32, device=dev)
+        Tx = torch.empty(max(tot_b, 1), dtype=torch.float64, device=dev)
+        Tk = torch.empty(max(tot_b, 1), dtype=torch.int64, device=dev) if big else None
+        work = torch.empty(m + 256, dtype=torch.int32, device=dev)
+        cnt_b = cnt[r0:r1]
+        _lib.call('b200amg_spgemm_numeric', m, _ptr(A.indptr) + 4 * r0, _ptr(A.indices), _ptr(A.data), _ptr(B.indptr),
+                  _ptr(B.indices), _ptr(B.data), _ptr(ub_b), _ptr(ubp_b), _ptr(Tk), _ptr(Tj), _ptr(Tx), _ptr(cnt_b),
+                  _ptr(work), int(bool(scipy_order)), st)
+        Cp_b = _scan_i32(cnt_b)
+        nnz_b = int(Cp_b[-1].item())
+        Cj = torch.empty(nnz_b, dtype=torch.int32, device=dev)
+        Cx = torch.empty(nnz_b, dtype=torch.float64, device=dev)
+        _lib.call('b200amg_spgemm_compact', m, _ptr(ubp_b), _ptr(Tj), _ptr(Tx), _ptr(Cp_b), _ptr(Cj), _ptr(Cx), st)
+        pieces.append((Cp_b, Cj, Cx))
+        del Tj, Tx, Tk, work
+    if len(pieces) == 1:
+        Cp, Cj, Cx = pieces[0]
+    else:
+        Cp = _scan_i32(cnt[:n])
+        if int(Cp[-1].item()) != sum(int(pc[1].numel()) for pc in pieces):
+            raise _lib.B200AmgError('matmat: result exceeds int32 indexing')
+        Cj = torch.cat([pc[1] for pc in pieces])
+        Cx = torch.cat([pc[2] for pc in pieces])
     return DevMat(Cp, Cj, Cx, (A.shape[0], B.shape[1]), (1, 1), 'csr', not scipy_order)
 
 
@@ -210,8 +245,44 @@ def transpose(A):
     return DevMat(Bp, Bi, Bx, (n_col, n_row), (1, 1), A.format, True)
 
 
-def galerkin(R, A, P, scipy_order=True):
+GALERKIN_BATCH_NNZ = 48_000_000          # entries of R per pass of the triple product
+
+
+def row_slice(M, r0, r1):
+    """rows [r0, r1) of a scalar CSR matrix as a DevMat over views of the same arrays"""
+    s, e = int(M.indptr[r0].item()), int(M.indptr[r1].item())
+    ip = (M.indptr[r0:r1 + 1] - M.indptr[r0]).contiguous()
+    return DevMat(ip, M.indices[s:e], M.data[s:e], (r1 - r0, M.shape[1]), (1, 1), M.format, M.has_sorted_indices)
+
+
+def galerkin(R, A, P, scipy_order=True, batch_nnz=None):
     """A_c = (R A) P, evaluated left to right like the reference (aggregation.py:429).  With
     scipy_order (default) the intermediate R A and the result keep scipy's row-internal order, so
-    values AND storage order equal the reference's; otherwise both are column-sorted."""
-    return matmat(matmat(R, A, scipy_order), P, scipy_order)
+    values AND storage order equal the reference's; otherwise both are column-sorted.
+    Output rows depend on the matching rows of R only, so the product runs in batches of rows of R
+    (about `batch_nnz` entries each): the intermediate R A never exists as a whole (at 512^3 it would
+    not fit int32 indexing), the result is identical."""
+    limit = int(batch_nnz or GALERKIN_BATCH_NNZ)
+    n = R.shape[0]
+    if R.nnz <= limit or n <= 1:
+        return matmat(matmat(R, A, scipy_order), P, scipy_order)
+    targets = torch.arange(limit, R.nnz, limit, dtype=torch.int64, device=R.indptr.device)
+    cuts = [0]
+    for c in torch.searchsorted(R.indptr.to(torch.int64), targets, right=True).tolist():
+        c = min(max(int(c) - 1, cuts[-1] + 1), n)
+        if c > cuts[-1]:
+            cuts.append(c)
+    if cuts[-1] != n:
+        cuts.append(n)
+    cps, cjs, cxs, base = [], [], [], 0
+    for r0, r1 in zip(cuts[:-1], cuts[1:]):
+        C = matmat(matmat(row_slice(R, r0, r1), A, scipy_order), P, scipy_order)
+        cps.append(C.indptr[:-1].to(torch.int64) + base)
+        base += C.nnz
+        cjs.append(C.indices)
+        cxs.append(C.data)
+        del C
+    if base >= 2 ** 31:
+        raise _lib.B200AmgError('galerkin: result exceeds int32 indexing')
+    Cp = torch.cat(cps + [torch.tensor([base], dtype=torch.int64, device=R.indptr.device)]).to(torch.int32)
+    return DevMat(Cp, torch.cat(cjs), torch.cat(cxs), (R.shape[0], P.shape[1]), (1, 1), 'csr', not scipy_order)

@@ -1,0 +1,136 @@
+"""worker of tests/test_distributed_cpu.py: world_size-2 gloo run of the row-partitioned cycle with a
+CPU checker backend (oracle kernels on numpy views).  TEST INFRASTRUCTURE: exercises the host logic of
+pyamg_b200/partition.py + distributed.py (slab cutting, column renumbering, halo plans, all-to-all
+refresh, agglomeration gather/scatter); the product backend is the CUDA one."""
+import os
+import sys
+
+import numpy as np
+import scipy.sparse as sp
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
+
+import oracle                                       # noqa: E402
+from oracle import multilevel as oml, sa as osa     # noqa: E402
+from helpers_mats import poisson3d                  # noqa: E402
+import importlib.util                               # noqa: E402
+
+
+def _load(name):
+    """import pyamg_b200.<name> WITHOUT importing the package (which needs the CUDA library loaded lazily only)"""
+    import pyamg_b200.partition  # noqa: F401  (pure torch)
+    return importlib.import_module('pyamg_b200.' + name)
+
+
+class CpuOp:
+    def __init__(self, ip, ix, dx, n_row):
+        self.ip, self.ix, self.dx, self.n = ip.numpy(), ix.numpy(), dx.numpy(), int(n_row)
+        self.ncol = int(self.ix.max()) + 1 if self.ix.size else 0
+
+    def apply(self, op, x, b, y, omega=0.0):
+        xn, yn = x.numpy(), y.numpy()
+        n = self.n
+        if op in (0, 2, 3):
+            t = np.zeros(n)
+            oracle.port.csr_matvec(n, self.ncol, self.ip, self.ix, self.dx, np.ascontiguousarray(xn), t)
+            if op == 0:
+                yn[:n] = t
+            elif op == 2:
+                yn[:n] = b.numpy()[:n] - t
+            else:
+                yn[:n] = yn[:n] + t
+        else:
+            xc, temp = xn.copy(), xn.copy()
+            bb = np.ascontiguousarray(b.numpy()[:n])
+            if op == 4:
+                oracle.port.jacobi(self.ip, self.ix, self.dx, xc, bb, temp, 0, n, 1, np.array([omega]))
+            else:
+                oracle.port.bsr_jacobi(self.ip, self.ix, self.dx, xc, bb, temp, 0, n, 1, 1, np.array([omega]))
+            yn[:n] = xc[:n]
+
+    def diagonal(self):
+        d = np.zeros(self.n)
+        for i in range(self.n):
+            for k in range(self.ip[i], self.ip[i + 1]):
+                if self.ix[k] == i:
+                    d[i] = self.dx[k]
+        return torch.from_numpy(d)
+
+
+class CpuBackend:
+    device = torch.device('cpu')
+
+    def make_op(self, ip, ix, dx, n_row):
+        return CpuOp(ip, ix, dx, n_row)
+
+    def scale_diag(self, omega, b, diag, x, flavor):
+        n = diag.numel()
+        bn, dn = b.numpy()[:n], diag.numpy()
+        with np.errstate(divide='ignore', invalid='ignore'):
+            v = (omega * bn) / dn if flavor else omega * (bn / dn)
+        x.numpy()[:n] = np.where(dn != 0, v, 0.0)
+
+    def dot(self, x, y, n):
+        return torch.tensor([float(np.dot(x.numpy()[:n], y.numpy()[:n]))], dtype=torch.float64)
+
+
+class CoarseOracle:
+    def __init__(self, levels):
+        self.S = oml.Solver(levels, core=oracle.port, wasted_prolongation=False)
+
+    def cycle_from_zero(self, b):
+        bn = b.numpy()
+        if len(self.S.levels) == 1:
+            return torch.from_numpy(np.asarray(self.S.coarse_solve(self.S.levels[0].A, bn)).copy())
+        x = np.zeros_like(bn)
+        self.S._cycle(0, x, bn, 'V')
+        return torch.from_numpy(x)
+
+
+def t3(M):
+    M = sp.csr_matrix(M) if M.format != 'bsr' else M
+    return (torch.from_numpy(np.ascontiguousarray(M.indptr, np.int32)), torch.from_numpy(np.ascontiguousarray(M.indices, np.int32)),
+            torch.from_numpy(np.ascontiguousarray(np.ravel(M.data), np.float64)))
+
+
+def main():
+    grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    dist.init_process_group('gloo')
+    rank = dist.get_rank()
+    D = _load('distributed')
+    levels_desc, coarse, host, b = None, None, None, None
+    if rank == 0:
+        A = poisson3d(grid); A.sort_indices()
+        np.random.seed(5)
+        jac = ('jacobi', {'omega': 4.0 / 3.0})
+        host = osa.smoothed_aggregation_hierarchy(A, presmoother=jac, postsmoother=jac, max_coarse=12, core=oracle.port)
+        b = np.random.rand(A.shape[0])
+        levels_desc = []
+        for L in host[:-1]:
+            d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
+                 'pre': (1, L.pre[1]['omega'], 1), 'post': (1, L.post[1]['omega'], 1),
+                 'A': t3(L.A), 'P': t3(L.P), 'R': t3(L.R)}
+            levels_desc.append(d)
+        coarse = lambda ka: CoarseOracle(host[ka:])
+    S = D.DistributedSolver(levels_desc, coarse, agglomerate_below=thresh, backend=CpuBackend())
+    res = []
+    x = S.solve(b, tol=1e-30, maxiter=cycles, residuals=res)
+    ok = True
+    if rank == 0:
+        ref_res = []
+        xr = oml.Solver(host, core=oracle.port, wasted_prolongation=False).solve(b, tol=1e-30, maxiter=cycles, residuals=ref_res)
+        ok = bool(np.array_equal(x.numpy(), xr)) and np.allclose(res, ref_res, rtol=1e-12, atol=0)
+        print('partitioned levels', len(S.levels), 'of', S.nlev, 'exchanges', S.exchanges, 'bit-identical x', np.array_equal(x.numpy(), xr),
+              'res', res[-1], ref_res[-1], flush=True)
+    flag = torch.tensor([1 if ok else 0])
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == '__main__':
+    main()

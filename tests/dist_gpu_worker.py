@@ -1,0 +1,47 @@
+"""worker of tests/test_gpu_distributed.py: one process per GPU (NCCL), row-partitioned cycle through
+libb200amg vs the single-GPU engine on rank 0."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    import pyamg_b200 as amg
+    from pyamg_b200.distributed import DistributedSolver
+    ml, b = None, None
+    if rank == 0:
+        A = amg.gallery.poisson((grid * world, grid, grid))
+        np.random.seed(2)
+        jac = ('jacobi', {'omega': 4.0 / 3.0})
+        ml = amg.smoothed_aggregation_solver(A, presmoother=jac, postsmoother=jac, max_coarse=40)
+        b = np.random.rand(A.shape[0])
+    S = DistributedSolver.from_ml(ml, agglomerate_below=thresh)
+    res = []
+    x = S.solve(b, tol=1e-30, maxiter=cycles, residuals=res)
+    ok = True
+    if rank == 0:
+        ref = []
+        xr = ml.solve(torch.from_numpy(b).cuda(), tol=1e-30, maxiter=cycles, residuals=ref)
+        same = bool(torch.equal(x, xr))
+        ok = same and np.allclose(res, ref, rtol=1e-12, atol=0)
+        print('world', world, 'partitioned levels', len(S.levels), 'of', S.nlev, 'exchanges', S.exchanges,
+              'bit-identical x', same, 'res', res[-1], ref[-1], flush=True)
+    flag = torch.tensor([1 if ok else 0], device='cuda')
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == '__main__':
+    main()

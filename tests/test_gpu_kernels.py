@@ -282,10 +282,16 @@ def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
     dA = amg.DevMat.from_scipy(A)
     P = lambda t: t.data_ptr()
 
+    import ctypes
+    h = ctypes.c_void_p()
+    amg._lib.call('b200amg_op_create', n, P(dA.indptr), P(dA.indices), P(dA.data), 2, ctypes.byref(h), 0)
+    assert amg._lib.load().b200amg_op_layout(h) == 2
+
     def run(op, y0):
         y = dev(y0)
         dx, db = dev(x), dev(b)
-        amg._lib.call('b200amg_selftest_sell', op, n, P(dA.indptr), P(dA.indices), P(dA.data), P(dx), P(db), P(y), 0.7, 0)
+        amg._lib.call('b200amg_op_apply', h, op, P(dx), P(db), P(y), 0.7, 0)
+        torch.cuda.synchronize()
         return y.cpu().numpy()
     assert np.array_equal(run(0, np.zeros(n)), A * x)
     assert np.array_equal(run(2, np.zeros(n)), b - A * x)
@@ -295,3 +301,4 @@ def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
     Ab = sp.bsr_matrix(A, blocksize=(1, 1))
     xo = x.copy(); orx.jacobi(Ab, xo, b, iterations=1, omega=0.7, core=oracle.port)
     assert np.array_equal(run(5, np.zeros(n)), xo)
+    amg._lib.load().b200amg_op_destroy(h)
