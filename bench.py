@@ -37,6 +37,7 @@ def parse():
                     help='grid points per dimension (BASELINE config: 256)')
     ap.add_argument('--cpu-cycles', type=int, default=3, help='V-cycles of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='N > 1: drive the distributed cycle from Python instead of one CUDA graph per rank')
     ap.add_argument('--agglomerate-below', type=int, default=500000,
                     help='N > 1: levels with fewer global rows than this run on rank 0 only')
     return ap.parse_args()
@@ -281,7 +282,13 @@ def run_distributed(args):
         return float(t.item())
 
     bh = torch.from_numpy(b).pin_memory() if rank == 0 else None
+    xh = torch.empty(b.size, dtype=torch.float64).pin_memory() if rank == 0 else None
     S.load(bh)
+    ex0, lc0 = S.exchanges, amg._lib.launch_count()
+    S.cycle()
+    ex_per_cycle, launches_per_cycle = S.exchanges - ex0, amg._lib.launch_count() - lc0
+    if not args.no_graph:
+        S.capture()
     for _ in range(args.warmup):
         S.cycle()
     barrier()
@@ -299,7 +306,7 @@ def run_distributed(args):
     barrier()
     torch.cuda.profiler.stop()
     ms_step = reduce_max(e0.elapsed_time(e1)) / args.steps
-    launches = amg._lib.launch_count() - l0
+    launches = launches_per_cycle * args.steps
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end: global b from pinned host memory on rank 0 -> slabs; one cycle; x gathered to the host
@@ -313,7 +320,8 @@ def run_distributed(args):
         S.cycle()
         xg = S.gather_x()
         if rank == 0:
-            xh = xg.cpu()
+            xh.copy_(xg, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
     e1.record(cur)
     barrier()
     e2e_ms = reduce_max(max(e0.elapsed_time(e1), (time.perf_counter() - t1) * 1e3)) / args.steps
@@ -358,8 +366,9 @@ def run_distributed(args):
                           'distributed_cycles_per_s': 1000.0 / ms_step,
                           'levels': level_table(ml), 'partitioned_levels': len(S.levels),
                           'parallelism': 'row slabs over %d GPUs, NCCL all-to-all halo refresh (%d per cycle), levels >= %d agglomerated on rank 0'
-                                         % (world, S.exchanges // max(1, (args.warmup + 3 * args.steps + 6)), S.ka),
-                          'l2': 'inputs larger than L2', 'setup_s_rank0_build_and_distribute': round(setup_s, 2)},
+                                         % (world, ex_per_cycle, S.ka),
+                          'l2': 'inputs larger than L2', 'setup_s_rank0_build_and_distribute': round(setup_s, 2),
+                          'cuda_graph': not args.no_graph},
                'clocks': clocks,
                'e2e': {'value': world * 1000.0 / e2e_ms, 'unit': 'V-cycles/s', 'h2d_bytes_per_step': 8 * b.size,
                        'd2h_bytes_per_step': 8 * b.size,
@@ -370,9 +379,25 @@ def run_distributed(args):
                             'frac': round(ach / peak, 4), 'algorithmic_bytes_per_launch': nB, 'ms_per_launch': round(t_j, 4),
                             'traffic': None},
                'parity_in_run': parity}
-    dist.destroy_process_group()
     if out is not None:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
+    # a CUDA graph that holds captured NCCL kernels must be gone before the communicator is torn
+    # down (destroy_process_group otherwise blocks forever: seen on 2 x B200, NCCL 2.28.9)
+    S.release_graph()
+    del S
+    torch.cuda.synchronize()
+    dist.barrier()
+    finish_process_group(dist)
+
+
+def finish_process_group(dist):
+    """destroy_process_group with a 20 s escape hatch (the JSON line is already out)"""
+    import threading
+    t = threading.Timer(20.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    dist.destroy_process_group()
+    t.cancel()
 
 
 def measure_e2e(R, args):
@@ -527,6 +552,10 @@ def run_reference(args):
 
 def main():
     args = parse()
+    wd = float(os.environ.get('B200AMG_BENCH_WATCHDOG', '0'))
+    if wd > 0:                       # dump every thread's stack if the run is still alive after `wd` seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(wd, exit=True)
     if args.impl == 'reference':
         run_reference(args)
         return

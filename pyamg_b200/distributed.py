@@ -139,6 +139,7 @@ class DistributedSolver:
         self.be = backend if backend is not None else DeviceBackend()
         self.device = device if device is not None else self.be.device
         self.exchanges = 0
+        self._graph = None
         meta = [None]
         if self.rank == 0:
             nlev = len(levels) + 1
@@ -280,10 +281,45 @@ class DistributedSolver:
         x, xs = self._smooth(L, L.info['post'], x, xs, b, False)
         return x, xs
 
-    def cycle(self):
-        """one V-cycle on the resident (x, b) slabs"""
+    def _cycle_eager(self):
         L = self.levels[0]
         L.x, L.xs = self._cycle(0, L.x, L.b, False)        # ping-pong: no copy back
+
+    def cycle(self):
+        """one V-cycle on the resident (x, b) slabs (a CUDA-graph replay after capture())"""
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self._cycle_eager()
+
+    def release_graph(self):
+        """drop the captured cycle (required before the process group is destroyed)"""
+        if self._graph is not None:
+            torch.cuda.synchronize()
+            self._graph.reset()
+            self._graph = None
+
+    def capture(self, warmup=2):
+        """Capture one whole distributed cycle -- slab kernels, halo all-to-alls (NCCL), the rank-0 coarse
+        engine -- into ONE CUDA graph per rank: replays cost one launch instead of ~60 Python-driven
+        ones.  Collective (every rank must call it); device backend only."""
+        L = self.levels[0]
+        x0 = L.x.clone()
+        for _ in range(warmup):                             # engines / communicators / allocator warm
+            self._cycle_eager()
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        home = L.x
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._cycle_eager()
+            if L.x is not home:                             # odd number of sweeps: keep the iterate in place
+                home[:L.n_own].copy_(L.x[:L.n_own])
+                L.x, L.xs = home, L.x
+        self._graph = g
+        L.x.copy_(x0)
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
 
     # ---- data movement / norms ---------------------------------------------------------------------
     def load(self, b_global=None, x0_global=None):
@@ -295,8 +331,13 @@ class DistributedSolver:
             if src is None and dst is L.x:
                 L.x.zero_()
                 continue
-            s = torch.as_tensor(src, dtype=torch.float64).to(self.device).reshape(-1) if self.rank == 0 else \
-                torch.empty(0, dtype=torch.float64, device=self.device)
+            if self.rank == 0:
+                if getattr(self, '_stage', None) is None:
+                    self._stage = torch.empty(sp[-1], dtype=torch.float64, device=self.device)
+                self._stage.copy_(torch.as_tensor(src, dtype=torch.float64).reshape(-1), non_blocking=True)
+                s = self._stage
+            else:
+                s = torch.empty(0, dtype=torch.float64, device=self.device)
             dist.all_to_all_single(dst[:L.n_own], s, output_split_sizes=[L.n_own] + [0] * (self.G - 1),
                                    input_split_sizes=sizes if self.rank == 0 else [0] * self.G, group=self.group)
 
@@ -304,7 +345,9 @@ class DistributedSolver:
         L = self.levels[0]
         sp = L.split
         sizes = [sp[p + 1] - sp[p] for p in range(self.G)]
-        out = torch.empty(sp[-1] if self.rank == 0 else 0, dtype=torch.float64, device=self.device)
+        if getattr(self, '_xg', None) is None:
+            self._xg = torch.empty(sp[-1] if self.rank == 0 else 0, dtype=torch.float64, device=self.device)
+        out = self._xg
         dist.all_to_all_single(out, L.x[:L.n_own], output_split_sizes=sizes if self.rank == 0 else [0] * self.G,
                                input_split_sizes=[L.n_own] + [0] * (self.G - 1), group=self.group)
         return out if self.rank == 0 else None

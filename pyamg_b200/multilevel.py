@@ -234,6 +234,14 @@ class multilevel_solver:
             return self.coarse_solver(self.levels[0].A, b_dev)
         if self._engine is None:
             self._build_engine()
+        if torch.cuda.is_current_stream_capturing():
+            # inside an outer CUDA-graph capture (distributed cycle): launch the level kernels directly
+            # into the capturing stream instead of replaying the engine's own graph
+            self._b.copy_(b_dev, non_blocking=True)
+            self._x.zero_()
+            _lib.call('b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], 0,
+                      torch.cuda.current_stream().cuda_stream)
+            return self._x
         cur = torch.cuda.current_stream()
         self._stream.wait_stream(cur)
         with torch.cuda.stream(self._stream):
