@@ -287,6 +287,11 @@ def run_distributed(args):
     ex0, lc0 = S.exchanges, amg._lib.launch_count()
     S.cycle()
     ex_per_cycle, launches_per_cycle = S.exchanges - ex0, amg._lib.launch_count() - lc0
+    S.profile_cycle()
+    prof = {}
+    for _ in range(3):
+        for lab, ms in S.profile_cycle():
+            prof[lab] = prof.get(lab, 0.0) + ms / 3
     if not args.no_graph:
         S.capture()
     for _ in range(args.warmup):
@@ -368,7 +373,8 @@ def run_distributed(args):
                           'parallelism': 'row slabs over %d GPUs, NCCL all-to-all halo refresh (%d per cycle), levels >= %d agglomerated on rank 0'
                                          % (world, ex_per_cycle, S.ka),
                           'l2': 'inputs larger than L2', 'setup_s_rank0_build_and_distribute': round(setup_s, 2),
-                          'cuda_graph': not args.no_graph},
+                          'cuda_graph': not args.no_graph,
+                          'eager_cycle_breakdown_ms_rank0': {k: round(v, 4) for k, v in prof.items()}},
                'clocks': clocks,
                'e2e': {'value': world * 1000.0 / e2e_ms, 'unit': 'V-cycles/s', 'h2d_bytes_per_step': 8 * b.size,
                        'd2h_bytes_per_step': 8 * b.size,

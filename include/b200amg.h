@@ -121,6 +121,20 @@ int b200amg_op_apply(void *handle, int op, const double *x, const double *b, dou
 int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL */
 int b200amg_op_destroy(void *handle);
 
+/* ---- multi-GPU halo refresh over NVLink peer memory (pyamg_b200/distributed.py) -------
+ * Level vectors live in a symmetric allocation (the same buffer mapped on every GPU of the node).
+ * push: scatter v[send_idx[j]] to (double*)bases[dst_rank[j]] + dst_off[j] on the peers, then raise this
+ *       rank's epoch in the flag cell sig_ptrs[i] of each of the n_nbr neighbours (system-scope release);
+ * wait: spin (bounded by max_spins polls per neighbour; state[1] != 0 afterwards = timed out) until every
+ *       neighbour's flag cell flag_ptrs[i] reached the next epoch.
+ * state: 2 device uint32 per call site, zero-initialised (epoch, scratch) -- epochs live in memory so the
+ * pair is CUDA-graph replay safe.  No reference counterpart: the reference is single-process. */
+int b200amg_halo_push(const double *v, int n_send, const int *send_idx, const int *dst_rank,
+                      const long long *dst_off, const unsigned long long *bases,
+                      const unsigned long long *sig_ptrs, int n_nbr, unsigned *state, void *stream);
+int b200amg_halo_wait(const unsigned long long *flag_ptrs, int n_nbr, unsigned *state,
+                      long long max_spins, void *stream);
+
 /* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
  *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */
 /* Row-wise C = A B, exact zeros dropped (scipy drops them too); values bit-identical to scipy's

@@ -44,6 +44,8 @@ _SIGS = {
     'b200amg_op_apply': (c_int, [p, c_int, p, p, p, c_double, p]),
     'b200amg_op_layout': (c_int, [p]),
     'b200amg_op_destroy': (c_int, [p]),
+    'b200amg_halo_push': (c_int, [p, c_int, p, p, p, p, p, c_int, p, p]),
+    'b200amg_halo_wait': (c_int, [p, c_int, p, c_longlong, p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
     'b200amg_axpy': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scale_diag': (c_int, [c_longlong, c_double, p, p, p, c_int, p]),

@@ -133,13 +133,17 @@ class DistributedSolver:
             return sub
         return cls(describe(ml), coarse, **kw)
 
-    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=500000, backend=None, device=None):
+    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=500000, backend=None, device=None,
+                 halo='auto'):
         self.group = group
         self.rank, self.G = dist.get_rank(group), dist.get_world_size(group)
         self.be = backend if backend is not None else DeviceBackend()
         self.device = device if device is not None else self.be.device
         self.exchanges = 0
+        self.halo_mode = halo
+        self._p2p = None
         self._graph = None
+        self._prof = None
         meta = [None]
         if self.rank == 0:
             nlev = len(levels) + 1
@@ -206,29 +210,162 @@ class DistributedSolver:
 
     def _alloc(self):
         dev, f64 = self.device, torch.float64
+        K = len(self.levels)
+        # vectors that receive halos: X_k / XS_k (iterate + Jacobi spare), R_k, and X_K (coarse vector of
+        # the last partitioned level).  X_{k+1} doubles as x_c of level k.
+        sizes = {}
         for k, L in enumerate(self.levels):
             halo_x = max(L.planA.n_halo, self.levels[k - 1].planP.n_halo if k > 0 else 0)
-            L.x = torch.zeros(L.n_own + halo_x, dtype=f64, device=dev) if k == 0 else self.levels[k - 1].xc
-            L.xs = torch.zeros(L.n_own + halo_x, dtype=f64, device=dev)
-            L.r = torch.zeros(L.n_own + L.planR.n_halo, dtype=f64, device=dev)
+            sizes[('x', k)] = sizes[('xs', k)] = L.n_own + halo_x
+            sizes[('r', k)] = L.n_own + L.planR.n_halo
+        Ll = self.levels[-1]
+        sizes[('x', K)] = Ll.nc_own + Ll.planP.n_halo
+        self._buf_sizes = sizes
+        use_p2p = self.halo_mode in ('auto', 'p2p') and self.G > 1 and isinstance(self.be, DeviceBackend)
+        bufs = None
+        if use_p2p:
+            try:
+                bufs = self._alloc_symmetric(sizes)
+            except Exception as exc:                      # noqa: BLE001
+                if self.halo_mode == 'p2p':
+                    raise
+                import warnings
+                warnings.warn('symmetric memory unavailable (%s): halo refresh falls back to NCCL all-to-all' % (exc,))
+                bufs = None
+        if bufs is None:
+            bufs = {key: torch.zeros(max(n, 1), dtype=f64, device=dev) for key, n in sizes.items()}
+        self._bufs = bufs
+        for k, L in enumerate(self.levels):
+            L.x, L.xs, L.r = bufs[('x', k)], bufs[('xs', k)], bufs[('r', k)]
+            L.xc = bufs[('x', k + 1)]
             L.bc = torch.zeros(max(L.nc_own, 1), dtype=f64, device=dev)
-            nxt_halo = self.levels[k + 1].planA.n_halo if k + 1 < len(self.levels) else 0
-            L.xc = torch.zeros(L.nc_own + max(L.planP.n_halo, nxt_halo), dtype=f64, device=dev)
             L.b = torch.zeros(max(L.n_own, 1), dtype=f64, device=dev) if k == 0 else self.levels[k - 1].bc
         if self.rank == 0:
             self.cb = torch.zeros(self.nc_global, dtype=f64, device=dev)
-        self._sbuf = {}
+        if self._p2p is not None:
+            self._build_p2p_tables()
+
+    # ---- NVLink peer-memory halo refresh (csrc/halo.cu) ---------------------------------------------
+    def _alloc_symmetric(self, sizes):
+        import torch.distributed._symmetric_memory as symm
+        grp = self.group if self.group is not None else dist.group.WORLD
+        al = lambda n: (max(n, 1) + 31) & ~31
+        offs, tot = {}, 0
+        for key in sorted(sizes):
+            offs[key] = tot
+            tot += al(sizes[key])
+        t = torch.tensor([tot], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        arena = symm.empty(int(t.item()), dtype=torch.float64, device=self.device)
+        arena.zero_()
+        nslots = 3 * len(self.levels)
+        flags = symm.empty(nslots * self.G + 32, dtype=torch.int32, device=self.device)
+        flags.zero_()
+        torch.cuda.synchronize()
+        ha = symm.rendezvous(arena, grp)
+        hf = symm.rendezvous(flags, grp)
+        self._p2p = {'arena': arena, 'flags': flags, 'ha': ha, 'hf': hf, 'offs': offs,
+                     'arena_ptrs': [int(p) for p in ha.buffer_ptrs], 'flag_ptrs': [int(p) for p in hf.buffer_ptrs]}
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        return {key: arena[offs[key]:offs[key] + max(sizes[key], 1)] for key in sizes}
+
+    def _build_p2p_tables(self):
+        """per plan: element-wise destinations on the peers; per (plan, target buffer): peer base table"""
+        P, G, me, dev = self._p2p, self.G, self.rank, self.device
+        K = len(self.levels)
+        mine = {'offs': {'%s%d' % key: v for key, v in P['offs'].items()},
+                'n_own': [L.n_own for L in self.levels] + [self.levels[-1].nc_own],
+                'recv': {}}
+        plans = {}
+        for k, L in enumerate(self.levels):
+            plans[('A', k)] = (L.planA, k, [('x', k), ('xs', k)])
+            plans[('R', k)] = (L.planR, k, [('r', k)])
+            plans[('P', k)] = (L.planP, k + 1, [('x', k + 1)] + ([('xs', k + 1)] if k + 1 < K else []))
+        for (kind, k), (pl, _, _) in plans.items():
+            mine['recv']['%s%d' % (kind, k)] = pl.recv_counts
+        allmeta = [None] * G
+        dist.all_gather_object(allmeta, mine, group=self.group)
+        nbr = set()
+        for (kind, k), (pl, _, _) in plans.items():
+            for q in range(G):
+                if q != me and (pl.send_counts[q] > 0 or pl.recv_counts[q] > 0):
+                    nbr.add(q)
+        nbr = sorted(nbr)
+        P['nbr'] = nbr
+        u64 = lambda v: torch.tensor(v, dtype=torch.int64, device=dev)
+        P['plans'] = {}
+        for slot, ((kind, k), (pl, vec_level, targets)) in enumerate(sorted(plans.items())):
+            name = '%s%d' % (kind, k)
+            dst_rank, dst_off = [], []
+            for p in range(G):
+                cnt = pl.send_counts[p]
+                if cnt == 0:
+                    continue
+                rc = allmeta[p]['recv'][name]                       # what p receives, by source rank
+                base = allmeta[p]['n_own'][vec_level] + sum(rc[:me])
+                dst_rank.append(torch.full((cnt,), p, dtype=torch.int32))
+                dst_off.append(torch.arange(base, base + cnt, dtype=torch.int64))
+            n_send = int(pl.send_idx.numel())
+            ent = {'n_send': n_send,
+                   'send_idx': pl.send_idx.to(torch.int32).contiguous(),
+                   'dst_rank': (torch.cat(dst_rank) if dst_rank else torch.zeros(0, dtype=torch.int32)).to(dev),
+                   'dst_off': (torch.cat(dst_off) if dst_off else torch.zeros(0, dtype=torch.int64)).to(dev),
+                   'sig': u64([P['flag_ptrs'][q] + 4 * (slot * G + me) for q in nbr] or [0]),
+                   'flg': u64([P['flag_ptrs'][me] + 4 * (slot * G + q) for q in nbr] or [0]),
+                   'push_state': torch.zeros(2, dtype=torch.int32, device=dev),
+                   'wait_state': torch.zeros(2, dtype=torch.int32, device=dev),
+                   'bases': {}}
+            for tkey in targets:
+                tname = '%s%d' % tkey
+                ent['bases'][self._bufs[tkey].data_ptr()] = u64([P['arena_ptrs'][p] + 8 * allmeta[p]['offs'][tname] for p in range(G)])
+            P['plans'][id(pl)] = ent
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+
+    def halo_errors(self):
+        """number of halo waits that timed out (0 on a healthy run)"""
+        if self._p2p is None:
+            return 0
+        return int(sum(int(e['wait_state'][1].item()) for e in self._p2p['plans'].values()))
 
     # ---- communication -------------------------------------------------------------------------
+    def _mark(self, label):
+        if self._prof is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(torch.cuda.current_stream())
+            self._prof.append((label, e))
+
+    def profile_cycle(self):
+        """one eager cycle with a CUDA event after every step -> [(label, ms)] on this rank"""
+        self._prof = []
+        self._mark('start')
+        self._cycle_eager()
+        torch.cuda.synchronize()
+        ev, self._prof = self._prof, None
+        return [(ev[i][0], ev[i - 1][1].elapsed_time(ev[i][1])) for i in range(1, len(ev))]
+
     def exchange(self, plan, v):
         """refresh v[n_own : n_own + n_halo] from the owners (v = [owned | halo])"""
-        if self.G == 1 or (plan.n_halo == 0 and plan.send_idx.numel() == 0):
+        if self.G == 1 or (self._p2p is None and plan.n_halo == 0 and plan.send_idx.numel() == 0):
+            return
+        self._mark('compute')
+        if self._p2p is not None:
+            ent = self._p2p['plans'][id(plan)]
+            lib, st, nn = self.be._lib, self.be.stream(), len(self._p2p['nbr'])
+            lib.call('b200amg_halo_push', v.data_ptr(), ent['n_send'], ent['send_idx'].data_ptr(), ent['dst_rank'].data_ptr(),
+                     ent['dst_off'].data_ptr(), ent['bases'][v.data_ptr()].data_ptr(), ent['sig'].data_ptr(), nn,
+                     ent['push_state'].data_ptr(), st)
+            lib.call('b200amg_halo_wait', ent['flg'].data_ptr(), nn, ent['wait_state'].data_ptr(), 1 << 24, st)
+            self.exchanges += 1
+            self._mark('exchange')
             return
         send = v[:plan.n_own].index_select(0, plan.send_idx)
         recv = v[plan.n_own:plan.n_own + plan.n_halo]
         dist.all_to_all_single(recv, send, output_split_sizes=plan.recv_counts, input_split_sizes=plan.send_counts,
                                group=self.group)
         self.exchanges += 1
+        self._mark('exchange')
 
     def _gather_coarse(self, L):
         spc = L.csplit
@@ -273,9 +410,13 @@ class DistributedSolver:
         if k + 1 < len(self.levels):
             xc, _ = self._cycle(k + 1, L.xc, L.bc, True)          # the iterate may end in the child's spare buffer
         else:
+            self._mark('compute')
             self._gather_coarse(L)
+            self._mark('gather')
             xg = self.coarse.cycle_from_zero(self.cb) if self.rank == 0 else None
+            self._mark('coarse_rank0')
             self._scatter_coarse(L, xg)
+            self._mark('scatter')
         self.exchange(L.planP, xc)
         L.P.apply(OP_ADD, xc, None, x)
         x, xs = self._smooth(L, L.info['post'], x, xs, b, False)
@@ -284,6 +425,7 @@ class DistributedSolver:
     def _cycle_eager(self):
         L = self.levels[0]
         L.x, L.xs = self._cycle(0, L.x, L.b, False)        # ping-pong: no copy back
+        self._mark('compute')
 
     def cycle(self):
         """one V-cycle on the resident (x, b) slabs (a CUDA-graph replay after capture())"""
