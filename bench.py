@@ -162,12 +162,25 @@ def dist_env():
     return rank, world, local
 
 
+def grid_dims(grid, slabs):
+    """g^3 unknowns per GPU: the factors of two of `slabs` go round-robin over the three axes, so
+    2 GPUs -> (2g, g, g), 4 -> (2g, 2g, g), 8 -> (2g, 2g, 2g) = BASELINE config 5 (512^3) at g = 256.
+    Row slabs are cut along the first (slowest) axis."""
+    dims, ax, s = [grid, grid, grid], 0, int(slabs)
+    while s % 2 == 0 and s > 1:
+        dims[ax % 3] *= 2
+        s //= 2
+        ax += 1
+    dims[0] *= s
+    return tuple(dims)
+
+
 def build_problem(grid, slabs=1):
     """config 2 of BASELINE.json: poisson((g,g,g)) + SA(Jacobi 4/3 pre/post, max_coarse=500), seed 0,
     built on the device by pyamg_b200 (bit-identical to the reference-built hierarchy, tests/).
-    slabs > 1: poisson((slabs*g, g, g)) -- `slabs` row slabs of g^3 unknowns (config 5 at 8 x 256^3 = 512^3 unknowns)"""
+    slabs > 1: poisson(grid_dims(g, slabs)) -- `slabs` row slabs of g^3 unknowns each (8 x 256^3 = the 512^3 of config 5)"""
     import pyamg_b200 as amg
-    A = amg.gallery.poisson((grid * slabs, grid, grid))
+    A = amg.gallery.poisson(grid_dims(grid, slabs))
     np.random.seed(0)
     ml = amg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=500)
     b = np.random.rand(A.shape[0])
@@ -363,15 +376,17 @@ def run_distributed(args):
                'value': val, 'unit': 'V-cycles/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
                'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
                'dtype': 'f64', 'data': 'synthetic',
-               'config': {'workload': 'configs[1] per GPU / configs[4] in total: 3D Poisson %dx%dx%d 7-point (%d slabs of %d^3, one per GPU), '
-                                      'smoothed_aggregation_solver, Jacobi(4/3) pre/post, max_coarse=500, fp64, one distributed '
-                                      'V(1,1)-cycle per step' % (args.grid * world, args.grid, args.grid, world, args.grid),
+               'config': {'workload': 'configs[1] per GPU (configs[4] = 512^3 in total at 8 GPUs): 3D Poisson %dx%dx%d 7-point (%d row slabs of %d^3 '
+                                      'unknowns, one per GPU), smoothed_aggregation_solver, Jacobi(4/3) pre/post, max_coarse=500, fp64, one '
+                                      'distributed V(1,1)-cycle per step' % (grid_dims(args.grid, world) + (world, args.grid)),
                           'value_definition': 'n_gpus x distributed V-cycles/s (every distributed cycle sweeps n_gpus slabs of %d^3 '
                                               'unknowns; the same unit as the 1-GPU line)' % args.grid,
                           'distributed_cycles_per_s': 1000.0 / ms_step,
                           'levels': level_table(ml), 'partitioned_levels': len(S.levels),
-                          'parallelism': 'row slabs over %d GPUs, NCCL all-to-all halo refresh (%d per cycle), levels >= %d agglomerated on rank 0'
-                                         % (world, ex_per_cycle, S.ka),
+                          'parallelism': 'row slabs over %d GPUs; halo refresh by %s (%d per cycle); levels >= %d agglomerated on rank 0'
+                                         % (world, 'peer-memory push/wait kernels over NVLink' if S._p2p is not None else 'NCCL all-to-all',
+                                            ex_per_cycle, S.ka),
+                          'halo_wait_timeouts': S.halo_errors(),
                           'l2': 'inputs larger than L2', 'setup_s_rank0_build_and_distribute': round(setup_s, 2),
                           'cuda_graph': not args.no_graph,
                           'eager_cycle_breakdown_ms_rank0': {k: round(v, 4) for k, v in prof.items()}},

@@ -9,7 +9,7 @@ from .multilevel import multilevel_solver, coarse_grid_solver
 from .smoothing import change_smoothers, rho_D_inv_A
 from .aggregation import smoothed_aggregation_solver
 from .hierarchy import import_hierarchy
-from . import amg_core, relaxation, gallery, linalg, krylov
+from . import amg_core, relaxation, gallery, linalg, krylov, partition, distributed
 
 __all__ = ['DevMat', 'matmat', 'transpose', 'galerkin', 'multilevel_solver', 'coarse_grid_solver',
            'change_smoothers', 'rho_D_inv_A', 'smoothed_aggregation_solver', 'import_hierarchy',
