@@ -34,7 +34,10 @@ struct Sell {
     int *row_len = nullptr;          // [n]
     bool ok() const { return cj != nullptr; }
 };
-int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st);
+int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
+               const int *perm = nullptr);
+// one colour [p0, p1) of a colour-grouped copy (slot row r = matrix row Id[r]); x updated in place
+int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st);
 void sell_free(Sell *s);
 // same operations / arithmetic as stream_op, on the sliced-ELL copy
 int sell_op(int op, const Sell &s, const StreamArgs &a, cudaStream_t st);

@@ -29,13 +29,15 @@ bool sell_wanted(long long nnz, int nrows)
 }
 
 // ---- build ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, long long *__restrict__ width,
-                                                         int *__restrict__ row_len)
+// perm (nullable): slot row r holds the matrix row perm[r] (colour-grouped copies for Gauss-Seidel)
+__global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ perm,
+                                                         long long *__restrict__ width, int *__restrict__ row_len)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     int len = 0;
     if (row < n) {
-        len = Ap[row + 1] - Ap[row];
+        const int src = perm ? perm[row] : row;
+        len = Ap[src + 1] - Ap[src];
         row_len[row] = len;
     }
     int m = len;
@@ -45,7 +47,7 @@ __global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__res
 }
 
 __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
-                                                        const double *__restrict__ Ax,
+                                                        const double *__restrict__ Ax, const int *__restrict__ perm,
                                                         const long long *__restrict__ slice_off, int *__restrict__ cj,
                                                         double *__restrict__ cv)
 {
@@ -56,8 +58,9 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__rest
     const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
     int lo = 0, len = 0;
     if (row < n) {
-        lo = Ap[row];
-        len = Ap[row + 1] - lo;
+        const int src = perm ? perm[row] : row;
+        lo = Ap[src];
+        len = Ap[src + 1] - lo;
     }
     for (int k = 0; k < w; ++k) {
         const bool in = k < len;
@@ -75,7 +78,8 @@ void sell_free(Sell *s)
     *s = Sell();
 }
 
-int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st)
+int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
+               const int *perm)
 {
     *out = Sell();
     if (n <= 0) return 0;
@@ -89,7 +93,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
     if (e == cudaSuccess) e = cudaMalloc(&s.row_len, sizeof(int) * (size_t)n);
     int rc = 0;
     if (e == cudaSuccess) {
-        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, width, s.row_len);
+        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, perm, width, s.row_len);
         rc = check_launch("sell_width_kernel");
         if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
         if (!rc) {
@@ -102,7 +106,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
         if (e == cudaSuccess) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
         if (e == cudaSuccess) {
-            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, s.slice_off, s.cj, s.cv);
+            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv);
             rc = check_launch("sell_fill_kernel");
         }
     }
@@ -222,6 +226,64 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     } else if (OP == OP_JACOBI_BSR1) {
         y[row] = (diag != 0.0) ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), div_rn(mul_rn(a.omega, acc), diag)) : xi;
     }
+}
+
+// ---- colour-ordered Gauss-Seidel on a colour-grouped SELL copy -----------------------------------
+// amg_core.gauss_seidel_indexed (relaxation.h:394-426) / bsr_gauss_seidel with bs = 1 (:89-173) for the
+// positions [p0, p1) of the index list `Id` = ONE colour: rows of a colour never read each other, so the
+// parallel update equals the sequential sweep bit for bit.  Slot row r of the copy holds matrix row Id[r]
+// (columns keep the original numbering); x is updated in place.
+template <bool BSRF>
+__global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const int p1, const long long *__restrict__ slice_off,
+                                                           const int *__restrict__ cj, const double *__restrict__ cv,
+                                                           const int *__restrict__ row_len, const int *__restrict__ Id,
+                                                           double *x, const double *__restrict__ b)
+{
+    const int r = (p0 & ~31) + blockIdx.x * SELL_TPB + threadIdx.x;          // slot row (slices may straddle colours)
+    const int slice = r >> 5, lane = threadIdx.x & 31;
+    if ((slice << 5) >= p1) return;                                         // whole warp
+    const bool live = r >= p0 && r < p1;
+    const long long off = slice_off[slice];
+    const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
+    const int len = live ? row_len[r] : 0;
+    const int row = live ? Id[r] : -1;
+    const double bi = live ? b[row] : 0.0;
+    double acc = BSRF ? bi : 0.0, diag = 0.0;
+    const int *pj = cj + off + lane;
+    const double *pv = cv + off + lane;
+    for (int k0 = 0; k0 < w; k0 += SELL_U) {
+        int c[SELL_U];
+        double v[SELL_U], xv[SELL_U];
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            const bool in = k0 + u < len;
+            c[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : -1;
+            v[u] = in ? __ldcs(pv + (long long)(k0 + u) * SELL_C) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? x[c[u]] : 0.0;
+#pragma unroll
+        for (int u = 0; u < SELL_U; ++u) {
+            if (c[u] >= 0) {
+                if (c[u] == row) diag = v[u];
+                else {
+                    const double pr = mul_rn(v[u], xv[u]);
+                    acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                }
+            }
+        }
+    }
+    if (live && diag != 0.0) x[row] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(bi, acc), diag);
+}
+
+int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st)
+{
+    if (p1 <= p0) return 0;
+    const int first = p0 & ~31;
+    const int grid = (p1 - first + SELL_TPB - 1) / SELL_TPB;
+    if (bsrf) sell_gs_kernel<true><<<grid, SELL_TPB, 0, st>>>(p0, p1, s.slice_off, s.cj, s.cv, s.row_len, Id, x, b);
+    else sell_gs_kernel<false><<<grid, SELL_TPB, 0, st>>>(p0, p1, s.slice_off, s.cj, s.cv, s.row_len, Id, x, b);
+    return check_launch("sell_gs_kernel");
 }
 
 template <int OP>

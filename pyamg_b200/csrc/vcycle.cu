@@ -17,6 +17,7 @@ struct LevelRt {
     double *r, *bc, *xc, *tmp, *diag;
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
+    Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
     std::vector<int> color_ptr;
 };
 
@@ -126,7 +127,9 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
                 for (int q = 0; q < K; ++q) {
                     const int c = bwd ? K - 1 - q : q;
                     const int p0 = L.color_ptr[c], p1 = L.color_ptr[c + 1];
-                    if (d.bs == 1)
+                    if (d.bs == 1 && L.sGS.ok())
+                        B200_TRY(sell_gs_color(d.flavor != 0, L.sGS, d.Id, p0, p1, *cur, b, st));
+                    else if (d.bs == 1)
                         B200_TRY(gs_rows(d.flavor != 0, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
                     else
                         B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st));
@@ -263,9 +266,13 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             if (sell_wanted(nzR, L.d.nc)) src = sell_build(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR, nullptr);
             if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
         }
+        // colour-ordered Gauss-Seidel: colour-grouped SELL copy of A when the index list is a permutation
+        if (!src && L.d.bs == 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 &&
+            L.color_ptr[0] == 0 && L.color_ptr[L.d.K] == L.d.n && L.d.n >= 128)
+            src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sGS, nullptr, L.d.Id);
         if (src) {
-            sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP);
-            for (auto &Lp : E->lev) { sell_free(&Lp.sA); sell_free(&Lp.sR); sell_free(&Lp.sP); }
+            sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
+            for (auto &Lp : E->lev) { sell_free(&Lp.sA); sell_free(&Lp.sR); sell_free(&Lp.sP); sell_free(&Lp.sGS); }
             delete E;
             return src;
         }
@@ -353,7 +360,7 @@ extern "C" int b200amg_vcycle_destroy(void *handle)
     Engine *E = reinterpret_cast<Engine *>(handle);
     if (!E) return 0;
     for (auto &g : E->graphs) cudaGraphExecDestroy(g.exec);
-    for (auto &L : E->lev) { sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); }
+    for (auto &L : E->lev) { sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS); }
     delete E;
     return 0;
 }
