@@ -1,4 +1,5 @@
 // extern "C" entry points of libb200amg.so for the stand-alone kernels (include/b200amg.h).
+#include <stdlib.h>
 #include "internal.cuh"
 
 using namespace b200amg;
@@ -170,13 +171,14 @@ struct OpHandle {
     const int *Ap, *Aj;
     const double *Ax;
     Sell sell;
+    ValueDict vd;
 };
 
 extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
                                  void **handle_out, void *stream)
 {
     if (n_row < 0 || !handle_out || layout < 0 || layout > 2) return set_err(B200AMG_EINVAL, "op_create: bad arguments");
-    OpHandle *h = new OpHandle{n_row, -1, Ap, Aj, Ax, Sell()};
+    OpHandle *h = new OpHandle{n_row, -1, Ap, Aj, Ax, Sell(), ValueDict()};
     if (n_row > 0) {
         int ends[2] = {0, 0};
         cudaError_t e = cudaMemcpyAsync(&ends[0], Ap, sizeof(int), cudaMemcpyDeviceToHost, S(stream));
@@ -188,6 +190,11 @@ extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const 
             int rc = sell_build(n_row, h->nnz, Ap, Aj, Ax, &h->sell, S(stream));
             if (rc) { delete h; return rc; }
             if (layout == 2 && !h->sell.ok()) { delete h; return set_err(B200AMG_ESTATE, "op_create: sliced-ELL layout declined (padding too large)"); }
+        }
+        const char *env = getenv("B200AMG_VALUE_DICT");
+        if (layout == 0 && !h->sell.ok() && (double)h->nnz / n_row <= 11.0 && !(env && env[0] == '0')) {
+            int rc = dict_build(h->nnz, Ax, &h->vd, S(stream));       // declined silently when > 256 distinct values
+            if (rc) { delete h; return rc; }
         }
     }
     *handle_out = h;
@@ -201,6 +208,7 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
     if (!h || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "op_apply: bad arguments");
     if (h->n_row == 0) return 0;
     StreamArgs a{h->Ap, h->Aj, h->Ax, x, b, y, h->nnz, 0, h->n_row, 1.0, 0.0, omega};
+    a.codes = h->vd.codes; a.dict = h->vd.dict;
     if (h->sell.ok()) return sell_op(op, h->sell, a, S(stream));
     return stream_op(op, a, S(stream));
 }
@@ -216,6 +224,7 @@ extern "C" int b200amg_op_destroy(void *handle)
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
     if (!h) return 0;
     sell_free(&h->sell);
+    dict_free(&h->vd);
     delete h;
     return 0;
 }

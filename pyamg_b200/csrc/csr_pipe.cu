@@ -21,6 +21,7 @@
 //         then thread t folds row t in storage order.
 // A tile whose range does not fit a stage (rows much longer than the matrix average) is
 // summed straight from global memory by its row threads: slower, same bits.
+#include <type_traits>
 #include "internal.cuh"
 #include "pipe.cuh"
 
@@ -35,12 +36,19 @@ constexpr int P_CTAS_PER_SM = 3;
 constexpr int P_ROWPAR_MAX_AVG = 12;
 constexpr int P_CWARPS = P_ROWS / 32;
 
-struct __align__(16) PipeSmem {
-    double v[P_DATA][P_CAP];
-    int c[P_DATA][P_CAP];
+// DICT: the operator's values are 8-bit codes into a table of <= 256 distinct doubles (stencil matrices:
+// 2 values for Poisson) -- 5 bytes per entry instead of 12 cross HBM; the decoded value is the same double,
+// so the arithmetic and its bits are unchanged.  The smaller stages pay for a deeper (4-slot) data ring.
+template <bool DICT>
+struct __align__(16) PipeSmemT {
+    static constexpr int ND = DICT ? 4 : P_DATA;
+    using V = typename std::conditional<DICT, unsigned char, double>::type;
+    V v[ND][P_CAP];
+    int c[ND][P_CAP];
     int ptr[P_PTRS][P_ROWS + 8];
+    double dict[DICT ? 256 : 2];
     uint64_t ptr_full[P_PTRS], ptr_empty[P_PTRS];
-    uint64_t data_full[P_DATA], data_empty[P_DATA];
+    uint64_t data_full[ND], data_empty[ND];
 };
 
 __device__ __forceinline__ void consumer_sync()
@@ -48,29 +56,35 @@ __device__ __forceinline__ void consumer_sync()
     asm volatile("bar.sync 1, %0;" ::"n"(P_ROWS) : "memory");
 }
 
-template <int OP>
+template <int OP, bool DICT>
 __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const StreamArgs a, const int rpt,
                                                                         const int num_tiles)
 {
+    using Smem = PipeSmemT<DICT>;
+    using V = typename Smem::V;
+    constexpr int ND = Smem::ND;
+    constexpr int ALIGN = DICT ? 16 : 4;                 // entries per 16 bytes of the narrowest staged array
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
     constexpr bool NEED_XI = SMOOTH;
     constexpr bool NEED_Y = (OP == OP_ADD);
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    PipeSmem &S = *reinterpret_cast<PipeSmem *>(smem_raw);
+    Smem &S = *reinterpret_cast<Smem *>(smem_raw);
     const int t = threadIdx.x;
     if (t == 0) {
         for (int i = 0; i < P_PTRS; ++i) { mbar_init(&S.ptr_full[i], 2); mbar_init(&S.ptr_empty[i], P_CWARPS); }
-        for (int i = 0; i < P_DATA; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
+        for (int i = 0; i < ND; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
         mbar_fence_init();
     }
+    if (DICT && t < 256) S.dict[t] = a.dict[t];
     __syncthreads();
 
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int *__restrict__ Ap = a.Ap;
     const int *__restrict__ Aj = a.Aj;
     const double *__restrict__ Ax = a.Ax;
+    const V *__restrict__ Av = DICT ? reinterpret_cast<const V *>(a.codes) : reinterpret_cast<const V *>(a.Ax);
     const double *__restrict__ xg = a.x;
 
     auto tile_rows = [&](int i, int &r0, int &nr) {
@@ -88,25 +102,27 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                 int r0, nr;
                 tile_rows(jd, r0, nr);
                 mbar_wait(&S.ptr_full[jd % P_PTRS], (jd / P_PTRS) & 1);
-                if (jd >= P_DATA) mbar_wait(&S.data_empty[jd % P_DATA], ((jd / P_DATA) - 1) & 1);
+                if (jd >= ND) mbar_wait(&S.data_empty[jd % ND], ((jd / ND) - 1) & 1);
                 const int *sp = S.ptr[jd % P_PTRS];
                 const int s = sp[0], e = sp[nr];
-                const int base = s & ~3;
-                const int st = jd % P_DATA;
+                const int base = s & ~(ALIGN - 1);
+                const int st = jd % ND;
                 uint64_t *bar = &S.data_full[st];
                 if (e - base > P_CAP) {                    // does not fit: rows read global memory
                     mbar_arrive(bar);
                     mbar_arrive(bar);
                 } else {
-                    const int nb = (e - base) & ~3;
-                    mbar_arrive_expect_tx(bar, (uint32_t)nb * 12u);
+                    const int nb = (e - base) & ~(ALIGN - 1);
+                    mbar_arrive_expect_tx(bar, (uint32_t)nb * (4u + (uint32_t)sizeof(V)));
                     if (nb) {
                         bulk_g2s(S.c[st], Aj + base, (uint32_t)nb * 4u, bar);
-                        bulk_g2s(S.v[st], Ax + base, (uint32_t)nb * 8u, bar);
+                        bulk_g2s(S.v[st], Av + base, (uint32_t)nb * (uint32_t)sizeof(V), bar);
                     }
-                    for (int k = base + nb; k < e; ++k) {
-                        cp_async_4(&S.c[st][k - base], Aj + k);
-                        cp_async_8(&S.v[st][k - base], Ax + k);
+                    for (int k = base + nb; k < e; ++k) cp_async_4(&S.c[st][k - base], Aj + k);
+                    if (DICT) {                            // codes travel in 4-byte groups (the code array is padded)
+                        for (int k = base + nb; k < e; k += 4) cp_async_4(&S.v[st][k - base], Av + k);
+                    } else {
+                        for (int k = base + nb; k < e; ++k) cp_async_8(&S.v[st][k - base], Av + k);
                     }
                     mbar_arrive_after_cp_async(bar);
                 }
@@ -143,17 +159,22 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         mbar_wait(&S.ptr_full[i % P_PTRS], (i / P_PTRS) & 1);
         const int *sp = S.ptr[i % P_PTRS];
         const int s = sp[0], e = sp[nr];
-        const int base = s & ~3;
-        const int *sc = S.c[i % P_DATA];
-        double *sv = S.v[i % P_DATA];
+        const int base = s & ~(ALIGN - 1);
+        const int *sc = S.c[i % ND];
+        V *sv = S.v[i % ND];
+        auto val = [&](int k) -> double {
+            if constexpr (DICT) return S.dict[sv[k]];
+            else return sv[k];
+        };
+        const bool rowpar = (e - s) <= P_ROWPAR_MAX_AVG * nr;
         int lo = 0, hi = 0;
         if (t < nr) {
             lo = sp[t];
             hi = sp[t + 1];
         }
         double acc = BSRF ? bi : 0.0, diag = 0.0;
-        mbar_wait(&S.data_full[i % P_DATA], (i / P_DATA) & 1);
-        if (e - base > P_CAP) {
+        mbar_wait(&S.data_full[i % ND], (i / ND) & 1);
+        if (e - base > P_CAP || (DICT && !rowpar)) {
             for (int k = lo; k < hi; ++k) {
                 const int c = Aj[k];
                 const double v = Ax[k];
@@ -161,7 +182,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                 if (SMOOTH && c == row) diag = v;
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
             }
-        } else if ((e - s) <= P_ROWPAR_MAX_AVG * nr) {
+        } else if (rowpar) {
             const int k0 = lo - base, len = hi - lo;
             if (len <= 8) {
                 // all gathers of the row in flight at once, then the ordered fold
@@ -171,7 +192,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                 for (int q = 0; q < 8; ++q)
                     if (q < len) {
                         cc[q] = sc[k0 + q];
-                        vv[q] = sv[k0 + q];
+                        vv[q] = val(k0 + q);
                         xv[q] = __ldg(xg + cc[q]);
                     }
 #pragma unroll
@@ -185,25 +206,27 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
 #pragma unroll 4
                 for (int k = k0; k < k0 + len; ++k) {
                     const int c = sc[k];
-                    const double v = sv[k];
+                    const double v = val(k);
                     const double pr = mul_rn(v, __ldg(xg + c));
                     if (SMOOTH && c == row) diag = v;
                     else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                 }
             }
         } else {
-            for (int k = s - base + t; k < e - base; k += P_ROWS) sv[k] = mul_rn(sv[k], __ldg(xg + sc[k]));
-            consumer_sync();
-            for (int k = lo - base; k < hi - base; ++k) {
-                if (SMOOTH && sc[k] == row) diag = __ldg(Ax + base + k);
-                else acc = BSRF ? sub_rn(acc, sv[k]) : add_rn(acc, sv[k]);
+            if constexpr (!DICT) {
+                for (int k = s - base + t; k < e - base; k += P_ROWS) sv[k] = mul_rn(sv[k], __ldg(xg + sc[k]));
+                consumer_sync();
+                for (int k = lo - base; k < hi - base; ++k) {
+                    if (SMOOTH && sc[k] == row) diag = __ldg(Ax + base + k);
+                    else acc = BSRF ? sub_rn(acc, sv[k]) : add_rn(acc, sv[k]);
+                }
             }
         }
         // this warp is done with both slots
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // in-place products vs the next bulk refill
         __syncwarp();
         if ((t & 31) == 0) {
-            mbar_arrive(&S.data_empty[i % P_DATA]);
+            mbar_arrive(&S.data_empty[i % ND]);
             mbar_arrive(&S.ptr_empty[i % P_PTRS]);
         }
         if (t < nr) {
@@ -240,13 +263,14 @@ int pipe_rows_per_tile(long long nnz, int nrows)
 
 static int g_sms = 0;
 
-template <int OP>
+template <int OP, bool DICT>
 static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
 {
+    using Smem = PipeSmemT<DICT>;
     static bool attr_done = false;
     if (!attr_done) {
-        B200_CUDA(cudaFuncSetAttribute(csr_pipe_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(PipeSmem)));
+        B200_CUDA(cudaFuncSetAttribute(csr_pipe_kernel<OP, DICT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(Smem)));
         attr_done = true;
     }
     if (g_sms == 0) {
@@ -257,7 +281,7 @@ static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
     const int nrows = a.row_end - a.row_begin;
     const int num_tiles = (nrows + rpt - 1) / rpt;
     const int grid = min(num_tiles, g_sms * P_CTAS_PER_SM);
-    csr_pipe_kernel<OP><<<grid, P_TPB, sizeof(PipeSmem), st>>>(a, rpt, num_tiles);
+    csr_pipe_kernel<OP, DICT><<<grid, P_TPB, sizeof(Smem), st>>>(a, rpt, num_tiles);
     return check_launch("csr_pipe_kernel");
 }
 
@@ -268,13 +292,14 @@ int pipe_op(int op, const StreamArgs &a, long long nnz, cudaStream_t st, int *rc
     const int rpt = pipe_rows_per_tile(nnz, nrows);
     if (rpt == 0 || nrows <= 0) return 0;
     if (!aligned16(a.Aj) || !aligned16(a.Ax) || !aligned16(a.Ap + a.row_begin)) return 0;
+    const bool dict = a.codes != nullptr && a.dict != nullptr && aligned16(a.codes);
     switch (op) {
-    case OP_MATVEC: *rc = launch_pipe<OP_MATVEC>(a, rpt, st); return 1;
-    case OP_SPMV_AB: *rc = launch_pipe<OP_SPMV_AB>(a, rpt, st); return 1;
-    case OP_RESIDUAL: *rc = launch_pipe<OP_RESIDUAL>(a, rpt, st); return 1;
-    case OP_ADD: *rc = launch_pipe<OP_ADD>(a, rpt, st); return 1;
-    case OP_JACOBI: *rc = launch_pipe<OP_JACOBI>(a, rpt, st); return 1;
-    case OP_JACOBI_BSR1: *rc = launch_pipe<OP_JACOBI_BSR1>(a, rpt, st); return 1;
+    case OP_MATVEC: *rc = dict ? launch_pipe<OP_MATVEC, true>(a, rpt, st) : launch_pipe<OP_MATVEC, false>(a, rpt, st); return 1;
+    case OP_SPMV_AB: *rc = dict ? launch_pipe<OP_SPMV_AB, true>(a, rpt, st) : launch_pipe<OP_SPMV_AB, false>(a, rpt, st); return 1;
+    case OP_RESIDUAL: *rc = dict ? launch_pipe<OP_RESIDUAL, true>(a, rpt, st) : launch_pipe<OP_RESIDUAL, false>(a, rpt, st); return 1;
+    case OP_ADD: *rc = dict ? launch_pipe<OP_ADD, true>(a, rpt, st) : launch_pipe<OP_ADD, false>(a, rpt, st); return 1;
+    case OP_JACOBI: *rc = dict ? launch_pipe<OP_JACOBI, true>(a, rpt, st) : launch_pipe<OP_JACOBI, false>(a, rpt, st); return 1;
+    case OP_JACOBI_BSR1: *rc = dict ? launch_pipe<OP_JACOBI_BSR1, true>(a, rpt, st) : launch_pipe<OP_JACOBI_BSR1, false>(a, rpt, st); return 1;
     }
     return 0;
 }

@@ -17,7 +17,18 @@ struct StreamArgs {
     long long nnz;         // stored entries of the rows in range, or -1 when the caller does not know
     int row_begin, row_end;
     double alpha, beta, omega;
+    const unsigned char *codes = nullptr;   // optional value dictionary (engine-built): Ax[k] == dict[codes[k]]
+    const double *dict = nullptr;           // 256 doubles
 };
+
+// value dictionary of an operator with <= 256 distinct values (csr_pipe.cu DICT path); codes == nullptr: declined
+struct ValueDict {
+    unsigned char *codes = nullptr;
+    double *dict = nullptr;
+    bool ok() const { return codes != nullptr; }
+};
+int dict_build(long long nnz, const double *Ax, ValueDict *out, cudaStream_t st);
+void dict_free(ValueDict *d);
 
 int rows_per_cta_for(long long nnz, int nrows);
 // persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when

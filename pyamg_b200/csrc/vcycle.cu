@@ -7,6 +7,7 @@
 // caller-provided work buffer.  Jacobi sweeps ping-pong between x and the spare buffer instead
 // of the reference's temp copy (same values); a pre-smoothing Jacobi sweep from the zero
 // initial guess of a coarse level is the bit-identical diagonal scaling (blas1.cu).
+#include <stdlib.h>
 #include <vector>
 #include "internal.cuh"
 
@@ -18,6 +19,7 @@ struct LevelRt {
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
+    ValueDict dA, dP, dR;                     // 8-bit value codes of operators with <= 256 distinct values
     std::vector<int> color_ptr;
 };
 
@@ -44,6 +46,19 @@ struct Engine {
     bool diag_ready;
 };
 
+static void free_level(LevelRt &L)
+{
+    sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
+    dict_free(&L.dA); dict_free(&L.dP); dict_free(&L.dR);
+}
+
+// B200AMG_VALUE_DICT=0 switches the value dictionary off (A/B measurements)
+static bool use_value_dict()
+{
+    const char *e = getenv("B200AMG_VALUE_DICT");
+    return !(e && e[0] == '0');
+}
+
 static size_t al(size_t n_doubles) { return (n_doubles + 31) & ~(size_t)31; }
 
 long long work_doubles(int nlev, const b200amg_level_desc *L)
@@ -61,6 +76,7 @@ static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *
     const b200amg_level_desc &d = L.d;
     if (d.bs == 1) {
         StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, L.nzA, 0, d.n, 1.0, 0.0, 0.0};
+        a.codes = L.dA.codes; a.dict = L.dA.dict;
         if (L.sA.ok()) return sell_op(op_scalar, L.sA, a, st);
         return stream_op(op_scalar, a, st);
     }
@@ -72,6 +88,7 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, L.nzR, 0, d.nc, 1.0, 0.0, 0.0};
+        a.codes = L.dR.codes; a.dict = L.dR.dict;
         if (L.sR.ok()) return sell_op(OP_MATVEC, L.sR, a, st);
         return stream_op(OP_MATVEC, a, st);
     }
@@ -83,6 +100,7 @@ static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
+        a.codes = L.dP.codes; a.dict = L.dP.dict;
         if (L.sP.ok()) return sell_op(OP_ADD, L.sP, a, st);
         return stream_op(OP_ADD, a, st);
     }
@@ -107,6 +125,7 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
             if (it == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
             if (d.bs == 1) {
                 StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, L.nzA, 0, d.n, 1.0, 0.0, omega};
+                a.codes = L.dA.codes; a.dict = L.dA.dict;
                 if (L.sA.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sA, a, st));
                 else B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
             } else {
@@ -266,13 +285,20 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             if (sell_wanted(nzR, L.d.nc)) src = sell_build(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR, nullptr);
             if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
         }
+        // short-row operators streamed by the TMA pipeline: try an 8-bit value dictionary (dict.cu)
+        if (!src && L.d.bs == 1 && !L.sA.ok() && nzA > 0 && (double)nzA / L.d.n <= 11.0 && use_value_dict())
+            src = dict_build(nzA, L.d.Ax, &L.dA, nullptr);
+        if (!src && L.d.p_br == 1 && L.d.p_bc == 1 && use_value_dict()) {
+            if (!L.sP.ok() && nzP > 0 && (double)nzP / L.d.n <= 11.0) src = dict_build(nzP, L.d.Px, &L.dP, nullptr);
+            if (!src && !L.sR.ok() && nzR > 0 && (double)nzR / L.d.nc <= 11.0) src = dict_build(nzR, L.d.Rx, &L.dR, nullptr);
+        }
         // colour-ordered Gauss-Seidel: colour-grouped SELL copy of A when the index list is a permutation
         if (!src && L.d.bs == 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 &&
             L.color_ptr[0] == 0 && L.color_ptr[L.d.K] == L.d.n && L.d.n >= 128)
             src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sGS, nullptr, L.d.Id);
         if (src) {
-            sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
-            for (auto &Lp : E->lev) { sell_free(&Lp.sA); sell_free(&Lp.sR); sell_free(&Lp.sP); sell_free(&Lp.sGS); }
+            free_level(L);
+            for (auto &Lp : E->lev) free_level(Lp);
             delete E;
             return src;
         }
@@ -360,7 +386,7 @@ extern "C" int b200amg_vcycle_destroy(void *handle)
     Engine *E = reinterpret_cast<Engine *>(handle);
     if (!E) return 0;
     for (auto &g : E->graphs) cudaGraphExecDestroy(g.exec);
-    for (auto &L : E->lev) { sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS); }
+    for (auto &L : E->lev) free_level(L);
     delete E;
     return 0;
 }
