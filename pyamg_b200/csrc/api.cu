@@ -192,7 +192,7 @@ extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const 
             if (layout == 2 && !h->sell.ok()) { delete h; return set_err(B200AMG_ESTATE, "op_create: sliced-ELL layout declined (padding too large)"); }
         }
         const char *env = getenv("B200AMG_VALUE_DICT");
-        if (layout == 0 && !h->sell.ok() && (double)h->nnz / n_row <= 11.0 && !(env && env[0] == '0')) {
+        if (layout == 0 && !h->sell.ok() && (double)h->nnz / n_row <= 8.0 && !(env && env[0] == '0')) {
             int rc = dict_build(h->nnz, Ax, &h->vd, S(stream));       // declined silently when > 256 distinct values
             if (rc) { delete h; return rc; }
         }

@@ -41,13 +41,18 @@ constexpr int P_CWARPS = P_ROWS / 32;
 // so the arithmetic and its bits are unchanged.  The smaller stages pay for a deeper (4-slot) data ring.
 template <bool DICT>
 struct __align__(16) PipeSmemT {
-    static constexpr int ND = DICT ? 4 : P_DATA;
+#ifndef PIPE_DICT_ND
+#define PIPE_DICT_ND 4
+#endif
+    static constexpr int ND = DICT ? PIPE_DICT_ND : P_DATA;  // data ring slots
+    static constexpr int NP = DICT ? PIPE_DICT_ND + 2 : P_PTRS;   // row-pointer ring slots
+    static constexpr int CAP = DICT ? 2064 : P_CAP;          // entries per slot (DICT: 256 rows x 8 + alignment)
     using V = typename std::conditional<DICT, unsigned char, double>::type;
-    V v[ND][P_CAP];
-    int c[ND][P_CAP];
-    int ptr[P_PTRS][P_ROWS + 8];
+    V v[ND][CAP];
+    int c[ND][CAP];
+    int ptr[NP][P_ROWS + 8];
     double dict[DICT ? 256 : 2];
-    uint64_t ptr_full[P_PTRS], ptr_empty[P_PTRS];
+    uint64_t ptr_full[NP], ptr_empty[NP];
     uint64_t data_full[ND], data_empty[ND];
 };
 
@@ -62,7 +67,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
 {
     using Smem = PipeSmemT<DICT>;
     using V = typename Smem::V;
-    constexpr int ND = Smem::ND;
+    constexpr int ND = Smem::ND, NP = Smem::NP, CAP = Smem::CAP;
     constexpr int ALIGN = DICT ? 16 : 4;                 // entries per 16 bytes of the narrowest staged array
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
@@ -73,7 +78,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
     const int t = threadIdx.x;
     if (t == 0) {
-        for (int i = 0; i < P_PTRS; ++i) { mbar_init(&S.ptr_full[i], 2); mbar_init(&S.ptr_empty[i], P_CWARPS); }
+        for (int i = 0; i < NP; ++i) { mbar_init(&S.ptr_full[i], 2); mbar_init(&S.ptr_empty[i], P_CWARPS); }
         for (int i = 0; i < ND; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
         mbar_fence_init();
     }
@@ -86,6 +91,8 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
     const double *__restrict__ Ax = a.Ax;
     const V *__restrict__ Av = DICT ? reinterpret_cast<const V *>(a.codes) : reinterpret_cast<const V *>(a.Ax);
     const double *__restrict__ xg = a.x;
+    // entries [0, arr_end) of Aj / Ax exist (known when the row range starts at row 0)
+    const long long arr_end = (a.row_begin == 0) ? a.nnz : -1;
 
     auto tile_rows = [&](int i, int &r0, int &nr) {
         const int tile = (int)blockIdx.x + i * (int)gridDim.x;
@@ -96,33 +103,43 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
     if (t >= P_ROWS) {
         // ---------------- producer warp: one lane drives both copy rings -----------------------
         if (t != P_ROWS) return;
-        for (int step = 0; step < my_tiles + P_PTRS - 1; ++step) {
-            const int jd = step - (P_PTRS - 1);
+        // row pointers run LA tiles ahead of the data copies; LA = NP - ND keeps the pointer ring from
+        // being the binding constraint (slot of tile j+LA is free once tile j+LA-NP = j-ND is consumed,
+        // which the data slot of tile j needs anyway)
+        constexpr int LA = NP - ND;
+        for (int step = 0; step < my_tiles + LA; ++step) {
+            const int jd = step - LA;
             if (jd >= 0) {                                 // (Aj, Ax) range of tile jd
                 int r0, nr;
                 tile_rows(jd, r0, nr);
-                mbar_wait(&S.ptr_full[jd % P_PTRS], (jd / P_PTRS) & 1);
+                mbar_wait(&S.ptr_full[jd % NP], (jd / NP) & 1);
                 if (jd >= ND) mbar_wait(&S.data_empty[jd % ND], ((jd / ND) - 1) & 1);
-                const int *sp = S.ptr[jd % P_PTRS];
+                const int *sp = S.ptr[jd % NP];
                 const int s = sp[0], e = sp[nr];
                 const int base = s & ~(ALIGN - 1);
                 const int st = jd % ND;
                 uint64_t *bar = &S.data_full[st];
-                if (e - base > P_CAP) {                    // does not fit: rows read global memory
+                if (e - base > CAP) {                    // does not fit: rows read global memory
                     mbar_arrive(bar);
                     mbar_arrive(bar);
                 } else {
-                    const int nb = (e - base) & ~(ALIGN - 1);
+                    // whole 16-byte groups travel as bulk copies; when the rounded-up range still lies inside
+                    // the arrays (every tile but the matrix' last) there is no tail at all
+                    const int e_pad = (e + ALIGN - 1) & ~(ALIGN - 1);
+                    const bool over = (long long)e_pad <= arr_end;
+                    const int nb = over ? e_pad - base : (e - base) & ~(ALIGN - 1);
                     mbar_arrive_expect_tx(bar, (uint32_t)nb * (4u + (uint32_t)sizeof(V)));
                     if (nb) {
                         bulk_g2s(S.c[st], Aj + base, (uint32_t)nb * 4u, bar);
                         bulk_g2s(S.v[st], Av + base, (uint32_t)nb * (uint32_t)sizeof(V), bar);
                     }
-                    for (int k = base + nb; k < e; ++k) cp_async_4(&S.c[st][k - base], Aj + k);
-                    if (DICT) {                            // codes travel in 4-byte groups (the code array is padded)
-                        for (int k = base + nb; k < e; k += 4) cp_async_4(&S.v[st][k - base], Av + k);
-                    } else {
-                        for (int k = base + nb; k < e; ++k) cp_async_8(&S.v[st][k - base], Av + k);
+                    if (!over) {
+                        for (int k = base + nb; k < e; ++k) cp_async_4(&S.c[st][k - base], Aj + k);
+                        if (DICT) {                        // codes travel in 4-byte groups (the code array is padded)
+                            for (int k = base + nb; k < e; k += 4) cp_async_4(&S.v[st][k - base], Av + k);
+                        } else {
+                            for (int k = base + nb; k < e; ++k) cp_async_8(&S.v[st][k - base], Av + k);
+                        }
                     }
                     mbar_arrive_after_cp_async(bar);
                 }
@@ -131,8 +148,8 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
             if (jp < my_tiles) {                           // row-pointer slice of tile jp
                 int r0, nr;
                 tile_rows(jp, r0, nr);
-                const int st = jp % P_PTRS;
-                if (jp >= P_PTRS) mbar_wait(&S.ptr_empty[st], ((jp / P_PTRS) - 1) & 1);
+                const int st = jp % NP;
+                if (jp >= NP) mbar_wait(&S.ptr_empty[st], ((jp / NP) - 1) & 1);
                 uint64_t *bar = &S.ptr_full[st];
                 const int cnt = nr + 1, nb = cnt & ~3;
                 mbar_arrive_expect_tx(bar, (uint32_t)nb * 4u);
@@ -151,13 +168,13 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         const int row = r0 + t;
         // vector operands of the epilogue are requested first: their latency hides behind the row sum
         double bi = 0.0, xi = 0.0, yi = 0.0;
+        bool have_xi = false;                   // Jacobi: x[row] arrives with the gathered diagonal entry
         if (t < nr) {
             if (NEED_B) bi = __ldg(a.b + row);
-            if (NEED_XI) xi = __ldg(xg + row);
             if (NEED_Y) yi = a.y[row];
         }
-        mbar_wait(&S.ptr_full[i % P_PTRS], (i / P_PTRS) & 1);
-        const int *sp = S.ptr[i % P_PTRS];
+        mbar_wait(&S.ptr_full[i % NP], (i / NP) & 1);
+        const int *sp = S.ptr[i % NP];
         const int s = sp[0], e = sp[nr];
         const int base = s & ~(ALIGN - 1);
         const int *sc = S.c[i % ND];
@@ -174,7 +191,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         }
         double acc = BSRF ? bi : 0.0, diag = 0.0;
         mbar_wait(&S.data_full[i % ND], (i / ND) & 1);
-        if (e - base > P_CAP || (DICT && !rowpar)) {
+        if (e - base > CAP || (DICT && !rowpar)) {
             for (int k = lo; k < hi; ++k) {
                 const int c = Aj[k];
                 const double v = Ax[k];
@@ -199,7 +216,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                 for (int q = 0; q < 8; ++q)
                     if (q < len) {
                         const double pr = mul_rn(vv[q], xv[q]);
-                        if (SMOOTH && cc[q] == row) diag = vv[q];       // last stored diagonal wins
+                        if (SMOOTH && cc[q] == row) { diag = vv[q]; xi = xv[q]; have_xi = true; }   // last stored diagonal wins
                         else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                     }
             } else {
@@ -227,10 +244,11 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         __syncwarp();
         if ((t & 31) == 0) {
             mbar_arrive(&S.data_empty[i % ND]);
-            mbar_arrive(&S.ptr_empty[i % P_PTRS]);
+            mbar_arrive(&S.ptr_empty[i % NP]);
         }
         if (t < nr) {
             double *y = a.y;
+            if (NEED_XI && !have_xi) xi = xg[row];
             if (OP == OP_MATVEC) {
                 y[row] = acc;
             } else if (OP == OP_SPMV_AB) {

@@ -59,7 +59,9 @@ static bool use_value_dict()
     return !(e && e[0] == '0');
 }
 
-static size_t al(size_t n_doubles) { return (n_doubles + 31) & ~(size_t)31; }
+// level vectors are padded by an odd number of 2 KB pages so that same-index entries of different
+// vectors (all 2^k-sized on structured grids) do not land on the same DRAM channel / L2 slice
+static size_t al(size_t n_doubles) { return ((n_doubles + 31) & ~(size_t)31) + 9 * 256; }
 
 long long work_doubles(int nlev, const b200amg_level_desc *L)
 {
@@ -286,11 +288,11 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
         }
         // short-row operators streamed by the TMA pipeline: try an 8-bit value dictionary (dict.cu)
-        if (!src && L.d.bs == 1 && !L.sA.ok() && nzA > 0 && (double)nzA / L.d.n <= 11.0 && use_value_dict())
+        if (!src && L.d.bs == 1 && !L.sA.ok() && nzA > 0 && (double)nzA / L.d.n <= 8.0 && use_value_dict())
             src = dict_build(nzA, L.d.Ax, &L.dA, nullptr);
         if (!src && L.d.p_br == 1 && L.d.p_bc == 1 && use_value_dict()) {
-            if (!L.sP.ok() && nzP > 0 && (double)nzP / L.d.n <= 11.0) src = dict_build(nzP, L.d.Px, &L.dP, nullptr);
-            if (!src && !L.sR.ok() && nzR > 0 && (double)nzR / L.d.nc <= 11.0) src = dict_build(nzR, L.d.Rx, &L.dR, nullptr);
+            if (!L.sP.ok() && nzP > 0 && (double)nzP / L.d.n <= 8.0) src = dict_build(nzP, L.d.Px, &L.dP, nullptr);
+            if (!src && !L.sR.ok() && nzR > 0 && (double)nzR / L.d.nc <= 8.0) src = dict_build(nzR, L.d.Rx, &L.dR, nullptr);
         }
         // colour-ordered Gauss-Seidel: colour-grouped SELL copy of A when the index list is a permutation
         if (!src && L.d.bs == 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 &&
