@@ -168,9 +168,9 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         const int row = r0 + t;
         // vector operands of the epilogue are requested first: their latency hides behind the row sum
         double bi = 0.0, xi = 0.0, yi = 0.0;
-        bool have_xi = false;                   // Jacobi: x[row] arrives with the gathered diagonal entry
         if (t < nr) {
             if (NEED_B) bi = __ldg(a.b + row);
+            if (NEED_XI) xi = __ldg(xg + row);
             if (NEED_Y) yi = a.y[row];
         }
         mbar_wait(&S.ptr_full[i % NP], (i / NP) & 1);
@@ -202,23 +202,25 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         } else if (rowpar) {
             const int k0 = lo - base, len = hi - lo;
             if (len <= 8) {
-                // all gathers of the row in flight at once, then the ordered fold
-                int cc[8];
+                // all gathers of the row in flight at once, then the ordered fold.  Jacobi only records WHICH
+                // slots hold the diagonal (bit mask): they are skipped by the fold, the last one is the divisor.
                 double vv[8], xv[8];
+                unsigned dm = 0;
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     if (q < len) {
-                        cc[q] = sc[k0 + q];
+                        const int c = sc[k0 + q];
+                        if (SMOOTH && c == row) dm |= 1u << q;
                         vv[q] = val(k0 + q);
-                        xv[q] = __ldg(xg + cc[q]);
+                        xv[q] = __ldg(xg + c);
                     }
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     if (q < len) {
                         const double pr = mul_rn(vv[q], xv[q]);
-                        if (SMOOTH && cc[q] == row) { diag = vv[q]; xi = xv[q]; have_xi = true; }   // last stored diagonal wins
-                        else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                        if (!SMOOTH || !((dm >> q) & 1u)) acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                     }
+                if (SMOOTH && dm) diag = val(k0 + 31 - __clz(dm));   // last stored diagonal wins
             } else {
 #pragma unroll 4
                 for (int k = k0; k < k0 + len; ++k) {
@@ -237,10 +239,11 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                     if (SMOOTH && sc[k] == row) diag = __ldg(Ax + base + k);
                     else acc = BSRF ? sub_rn(acc, sv[k]) : add_rn(acc, sv[k]);
                 }
+                // the in-place products were generic-proxy writes: order them before the next bulk refill
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             }
         }
-        // this warp is done with both slots
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // in-place products vs the next bulk refill
+        // this warp is done with both slots (reads only on the other paths: the mbarrier orders them)
         __syncwarp();
         if ((t & 31) == 0) {
             mbar_arrive(&S.data_empty[i % ND]);
@@ -248,7 +251,6 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         }
         if (t < nr) {
             double *y = a.y;
-            if (NEED_XI && !have_xi) xi = xg[row];
             if (OP == OP_MATVEC) {
                 y[row] = acc;
             } else if (OP == OP_SPMV_AB) {

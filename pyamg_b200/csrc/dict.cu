@@ -13,7 +13,7 @@ namespace b200amg {
 constexpr int DICT_MAX = 256;
 constexpr int MISS_CAP = 512;
 
-// miss[0] = number of values not in the table (capped report in miss_vals)
+// miss[0] = number of entries whose value is not in the table; miss_vals[512]: hashed report of such values
 __global__ void __launch_bounds__(256) dict_encode_kernel(long long nnz, const double *__restrict__ Ax,
                                                           const unsigned long long *__restrict__ keys, int nkeys,
                                                           unsigned char *__restrict__ codes, int *miss,
@@ -33,8 +33,10 @@ __global__ void __launch_bounds__(256) dict_encode_kernel(long long nnz, const d
         if (lo < nkeys && s_k[lo] == key) {
             codes[k] = (unsigned char)lo;
         } else {
-            const int slot = atomicAdd(miss, 1);
-            if (slot < MISS_CAP) miss_vals[slot] = key;
+            // report the value in a hashed slot: the same missing value always lands in the same slot, so a
+            // value that occurs millions of times cannot crowd out the others
+            atomicAdd(miss, 1);
+            miss_vals[(key * 0x9E3779B97F4A7C15ull) >> 55] = key;
         }
     }
 }
@@ -76,9 +78,10 @@ int dict_build(long long nnz, const double *Ax, ValueDict *out, cudaStream_t st)
     if (e == cudaSuccess) e = cudaMalloc(&d_miss, sizeof(int));
     int rc = 0;
     bool done = false;
-    for (int round = 0; e == cudaSuccess && !rc && !done && round < 4; ++round) {
+    for (int round = 0; e == cudaSuccess && !rc && !done && round < 8; ++round) {
         e = cudaMemcpyAsync(d_keys, keys.data(), sizeof(unsigned long long) * keys.size(), cudaMemcpyHostToDevice, st);
         if (e == cudaSuccess) e = cudaMemsetAsync(d_miss, 0, sizeof(int), st);
+        if (e == cudaSuccess) e = cudaMemsetAsync(d_missv, 0xFF, sizeof(unsigned long long) * MISS_CAP, st);
         if (e != cudaSuccess) break;
         const int grid = (int)std::min<long long>((nnz + 255) / 256, 148 * 16);
         dict_encode_kernel<<<grid, 256, 0, st>>>(nnz, Ax, d_keys, (int)keys.size(), codes, d_miss, d_missv);
@@ -88,10 +91,10 @@ int dict_build(long long nnz, const double *Ax, ValueDict *out, cudaStream_t st)
         if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(st);
         if (rc || e != cudaSuccess) break;
         if (miss == 0) { done = true; break; }
-        if (miss > MISS_CAP) break;                                      // far too many distinct values
-        std::vector<unsigned long long> mv(miss);
-        e = cudaMemcpy(mv.data(), d_missv, sizeof(unsigned long long) * miss, cudaMemcpyDeviceToHost);
-        keys.insert(keys.end(), mv.begin(), mv.end());
+        std::vector<unsigned long long> mv(MISS_CAP);
+        e = cudaMemcpy(mv.data(), d_missv, sizeof(unsigned long long) * MISS_CAP, cudaMemcpyDeviceToHost);
+        for (unsigned long long k : mv)
+            if (k != ~0ull) keys.push_back(k);
         std::sort(keys.begin(), keys.end());
         keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
         if ((int)keys.size() > DICT_MAX) break;
