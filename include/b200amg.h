@@ -118,7 +118,9 @@ int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax,
                       void **handle_out, void *stream);
 int b200amg_op_apply(void *handle, int op, const double *x, const double *b, double *y, double omega,
                      void *stream);
-int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL */
+int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL, 3 CSR + 8-bit value codes, 4 CSR rows + 8-bit
+                                           * (column offset, value) pattern codes, 5 one row-pattern
+                                           * byte per row (stencil operators) */
 int b200amg_op_destroy(void *handle);
 
 /* ---- multi-GPU halo refresh over NVLink peer memory (pyamg_b200/distributed.py) -------
@@ -254,6 +256,9 @@ int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind,
 int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_kind, int max_ops,
                            int *op_code_host, int *op_level_host, float *op_ms_host,
                            int *n_ops_host, void *stream);
+/* layout the engine streams an operator of `level` in (which: 0 A, 1 P, 2 R): the b200amg_op_layout codes,
+ * 0 for block operators.  Informational: every layout gives the same bits. */
+int b200amg_vcycle_layout(void *handle, int level, int which);
 /* rnorm2_dev[0] = ||b - A0 x||^2 on the finest level (residual_norm of multilevel.py:450,461) */
 int b200amg_vcycle_residual_norm2(void *handle, const double *x, const double *b,
                                   double *rnorm2_dev, void *stream);

@@ -172,13 +172,14 @@ struct OpHandle {
     const double *Ax;
     Sell sell;
     ValueDict vd;
+    RowPat rp;
 };
 
 extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
                                  void **handle_out, void *stream)
 {
     if (n_row < 0 || !handle_out || layout < 0 || layout > 2) return set_err(B200AMG_EINVAL, "op_create: bad arguments");
-    OpHandle *h = new OpHandle{n_row, -1, Ap, Aj, Ax, Sell(), ValueDict()};
+    OpHandle *h = new OpHandle{n_row, -1, Ap, Aj, Ax, Sell(), ValueDict(), RowPat()};
     if (n_row > 0) {
         int ends[2] = {0, 0};
         cudaError_t e = cudaMemcpyAsync(&ends[0], Ap, sizeof(int), cudaMemcpyDeviceToHost, S(stream));
@@ -192,8 +193,13 @@ extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const 
             if (layout == 2 && !h->sell.ok()) { delete h; return set_err(B200AMG_ESTATE, "op_create: sliced-ELL layout declined (padding too large)"); }
         }
         const char *env = getenv("B200AMG_VALUE_DICT");
-        if (layout == 0 && !h->sell.ok() && (double)h->nnz / n_row <= 8.0 && !(env && env[0] == '0')) {
-            int rc = dict_build(h->nnz, Ax, &h->vd, S(stream));       // declined silently when > 256 distinct values
+        const int dict_level = (env && env[0] >= '0' && env[0] <= '3') ? env[0] - '0' : 3;
+        if (layout == 0 && !h->sell.ok() && (double)h->nnz / n_row <= 8.0 && dict_level) {
+            // each layout is declined silently when the operator does not qualify (too many distinct row
+            // patterns / (offset, value) pairs / values); the next one down is tried
+            int rc = dict_level >= 3 ? rowpat_build(n_row, h->nnz, Ap, Aj, Ax, &h->rp, S(stream)) : 0;
+            if (!rc && !h->rp.ok() && dict_level >= 2) rc = pattern_build(n_row, h->nnz, Ap, Aj, Ax, &h->vd, S(stream));
+            if (!rc && !h->rp.ok() && !h->vd.ok()) rc = dict_build(h->nnz, Ax, &h->vd, S(stream));
             if (rc) { delete h; return rc; }
         }
     }
@@ -208,7 +214,8 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
     if (!h || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "op_apply: bad arguments");
     if (h->n_row == 0) return 0;
     StreamArgs a{h->Ap, h->Aj, h->Ax, x, b, y, h->nnz, 0, h->n_row, 1.0, 0.0, omega};
-    a.codes = h->vd.codes; a.dict = h->vd.dict;
+    h->vd.apply(a);
+    if (h->rp.ok()) return rowpat_op(op, h->rp, a, S(stream));
     if (h->sell.ok()) return sell_op(op, h->sell, a, S(stream));
     return stream_op(op, a, S(stream));
 }
@@ -216,7 +223,10 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
 extern "C" int b200amg_op_layout(void *handle)
 {
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
-    return h ? (h->sell.ok() ? 2 : 1) : 0;
+    if (!h) return 0;
+    if (h->rp.ok()) return 5;
+    if (h->sell.ok()) return 2;
+    return h->vd.ok() ? (h->vd.offs ? 4 : 3) : 1;
 }
 
 extern "C" int b200amg_op_destroy(void *handle)
@@ -225,6 +235,7 @@ extern "C" int b200amg_op_destroy(void *handle)
     if (!h) return 0;
     sell_free(&h->sell);
     dict_free(&h->vd);
+    rowpat_free(&h->rp);
     delete h;
     return 0;
 }

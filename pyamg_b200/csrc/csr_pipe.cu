@@ -36,22 +36,32 @@ constexpr int P_CTAS_PER_SM = 3;
 constexpr int P_ROWPAR_MAX_AVG = 12;
 constexpr int P_CWARPS = P_ROWS / 32;
 
-// DICT: the operator's values are 8-bit codes into a table of <= 256 distinct doubles (stencil matrices:
-// 2 values for Poisson) -- 5 bytes per entry instead of 12 cross HBM; the decoded value is the same double,
-// so the arithmetic and its bits are unchanged.  The smaller stages pay for a deeper (4-slot) data ring.
-template <bool DICT>
+// MODE 0: (Aj, Ax) as stored.
+// MODE 1: the operator's values are 8-bit codes into a table of <= 256 distinct doubles -- 5 bytes per entry
+//         instead of 12 cross HBM; the decoded value is the same double, so the arithmetic and its bits are
+//         unchanged.  The smaller stages pay for a deeper (4-slot) data ring.
+// MODE 2: 8-bit codes into a table of (column offset, value) pairs (constant-coefficient stencils): 1 byte per
+//         entry; the column is row + offset.
+struct __align__(16) PatEntry {
+    double v;
+    int off, pad;
+};
+
+template <int MODE>
 struct __align__(16) PipeSmemT {
 #ifndef PIPE_DICT_ND
 #define PIPE_DICT_ND 4
 #endif
-    static constexpr int ND = DICT ? PIPE_DICT_ND : P_DATA;  // data ring slots
-    static constexpr int NP = DICT ? PIPE_DICT_ND + 2 : P_PTRS;   // row-pointer ring slots
-    static constexpr int CAP = DICT ? 2064 : P_CAP;          // entries per slot (DICT: 256 rows x 8 + alignment)
-    using V = typename std::conditional<DICT, unsigned char, double>::type;
+    static constexpr bool CODED = MODE != 0;
+    static constexpr int ND = CODED ? PIPE_DICT_ND : P_DATA;     // data ring slots
+    static constexpr int NP = CODED ? PIPE_DICT_ND + 2 : P_PTRS; // row-pointer ring slots
+    static constexpr int CAP = CODED ? 2064 : P_CAP;             // entries per slot (coded: 256 rows x 8 + alignment)
+    using V = typename std::conditional<CODED, unsigned char, double>::type;
     V v[ND][CAP];
-    int c[ND][CAP];
+    int c[MODE == 2 ? 1 : ND][MODE == 2 ? 4 : CAP];
     int ptr[NP][P_ROWS + 8];
-    double dict[DICT ? 256 : 2];
+    PatEntry pat[MODE == 2 ? 256 : 1];
+    double dict[MODE == 1 ? 256 : 2];
     uint64_t ptr_full[NP], ptr_empty[NP];
     uint64_t data_full[ND], data_empty[ND];
 };
@@ -61,13 +71,15 @@ __device__ __forceinline__ void consumer_sync()
     asm volatile("bar.sync 1, %0;" ::"n"(P_ROWS) : "memory");
 }
 
-template <int OP, bool DICT>
+template <int OP, int MODE>
 __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const StreamArgs a, const int rpt,
                                                                         const int num_tiles)
 {
-    using Smem = PipeSmemT<DICT>;
+    using Smem = PipeSmemT<MODE>;
     using V = typename Smem::V;
     constexpr int ND = Smem::ND, NP = Smem::NP, CAP = Smem::CAP;
+    constexpr bool DICT = MODE != 0;                     // coded entries
+    constexpr bool HAVE_C = MODE != 2;                   // column indices travel with the entries
     constexpr int ALIGN = DICT ? 16 : 4;                 // entries per 16 bytes of the narrowest staged array
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
@@ -82,7 +94,8 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         for (int i = 0; i < ND; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
         mbar_fence_init();
     }
-    if (DICT && t < 256) S.dict[t] = a.dict[t];
+    if (MODE == 1 && t < 256) S.dict[t] = a.dict[t];
+    if (MODE == 2 && t < 256) S.pat[t] = PatEntry{a.dict[t], a.offs[t], 0};
     __syncthreads();
 
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
@@ -128,13 +141,14 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                     const int e_pad = (e + ALIGN - 1) & ~(ALIGN - 1);
                     const bool over = (long long)e_pad <= arr_end;
                     const int nb = over ? e_pad - base : (e - base) & ~(ALIGN - 1);
-                    mbar_arrive_expect_tx(bar, (uint32_t)nb * (4u + (uint32_t)sizeof(V)));
+                    mbar_arrive_expect_tx(bar, (uint32_t)nb * ((HAVE_C ? 4u : 0u) + (uint32_t)sizeof(V)));
                     if (nb) {
-                        bulk_g2s(S.c[st], Aj + base, (uint32_t)nb * 4u, bar);
+                        if (HAVE_C) bulk_g2s(S.c[st], Aj + base, (uint32_t)nb * 4u, bar);
                         bulk_g2s(S.v[st], Av + base, (uint32_t)nb * (uint32_t)sizeof(V), bar);
                     }
                     if (!over) {
-                        for (int k = base + nb; k < e; ++k) cp_async_4(&S.c[st][k - base], Aj + k);
+                        if (HAVE_C)
+                            for (int k = base + nb; k < e; ++k) cp_async_4(&S.c[st][k - base], Aj + k);
                         if (DICT) {                        // codes travel in 4-byte groups (the code array is padded)
                             for (int k = base + nb; k < e; k += 4) cp_async_4(&S.v[st][k - base], Av + k);
                         } else {
@@ -177,11 +191,20 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         const int *sp = S.ptr[i % NP];
         const int s = sp[0], e = sp[nr];
         const int base = s & ~(ALIGN - 1);
-        const int *sc = S.c[i % ND];
+        const int *sc = S.c[HAVE_C ? i % ND : 0];
         V *sv = S.v[i % ND];
-        auto val = [&](int k) -> double {
-            if constexpr (DICT) return S.dict[sv[k]];
-            else return sv[k];
+        auto fetch = [&](int k, int &c, double &v) {     // entry k of the staged range: column and value
+            if constexpr (MODE == 2) {
+                const PatEntry pe = S.pat[sv[k]];
+                c = row + pe.off;
+                v = pe.v;
+            } else if constexpr (MODE == 1) {
+                c = sc[k];
+                v = S.dict[sv[k]];
+            } else {
+                c = sc[k];
+                v = sv[k];
+            }
         };
         const bool rowpar = (e - s) <= P_ROWPAR_MAX_AVG * nr;
         int lo = 0, hi = 0;
@@ -209,9 +232,9 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     if (q < len) {
-                        const int c = sc[k0 + q];
+                        int c;
+                        fetch(k0 + q, c, vv[q]);
                         if (SMOOTH && c == row) dm |= 1u << q;
-                        vv[q] = val(k0 + q);
                         xv[q] = __ldg(xg + c);
                     }
 #pragma unroll
@@ -220,19 +243,23 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
                         const double pr = mul_rn(vv[q], xv[q]);
                         if (!SMOOTH || !((dm >> q) & 1u)) acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                     }
-                if (SMOOTH && dm) diag = val(k0 + 31 - __clz(dm));   // last stored diagonal wins
+                if (SMOOTH && dm) {                                  // last stored diagonal wins
+                    int c;
+                    fetch(k0 + 31 - __clz(dm), c, diag);
+                }
             } else {
 #pragma unroll 4
                 for (int k = k0; k < k0 + len; ++k) {
-                    const int c = sc[k];
-                    const double v = val(k);
+                    int c;
+                    double v;
+                    fetch(k, c, v);
                     const double pr = mul_rn(v, __ldg(xg + c));
                     if (SMOOTH && c == row) diag = v;
                     else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                 }
             }
         } else {
-            if constexpr (!DICT) {
+            if constexpr (MODE == 0) {
                 for (int k = s - base + t; k < e - base; k += P_ROWS) sv[k] = mul_rn(sv[k], __ldg(xg + sc[k]));
                 consumer_sync();
                 for (int k = lo - base; k < hi - base; ++k) {
@@ -283,13 +310,13 @@ int pipe_rows_per_tile(long long nnz, int nrows)
 
 static int g_sms = 0;
 
-template <int OP, bool DICT>
+template <int OP, int MODE>
 static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
 {
-    using Smem = PipeSmemT<DICT>;
+    using Smem = PipeSmemT<MODE>;
     static bool attr_done = false;
     if (!attr_done) {
-        B200_CUDA(cudaFuncSetAttribute(csr_pipe_kernel<OP, DICT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200_CUDA(cudaFuncSetAttribute(csr_pipe_kernel<OP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(Smem)));
         attr_done = true;
     }
@@ -301,7 +328,7 @@ static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
     const int nrows = a.row_end - a.row_begin;
     const int num_tiles = (nrows + rpt - 1) / rpt;
     const int grid = min(num_tiles, g_sms * P_CTAS_PER_SM);
-    csr_pipe_kernel<OP, DICT><<<grid, P_TPB, sizeof(Smem), st>>>(a, rpt, num_tiles);
+    csr_pipe_kernel<OP, MODE><<<grid, P_TPB, sizeof(Smem), st>>>(a, rpt, num_tiles);
     return check_launch("csr_pipe_kernel");
 }
 
@@ -312,15 +339,22 @@ int pipe_op(int op, const StreamArgs &a, long long nnz, cudaStream_t st, int *rc
     const int rpt = pipe_rows_per_tile(nnz, nrows);
     if (rpt == 0 || nrows <= 0) return 0;
     if (!aligned16(a.Aj) || !aligned16(a.Ax) || !aligned16(a.Ap + a.row_begin)) return 0;
-    const bool dict = a.codes != nullptr && a.dict != nullptr && aligned16(a.codes);
+    const bool coded = a.codes != nullptr && a.dict != nullptr && aligned16(a.codes);
+    const int mode = !coded ? 0 : (a.offs != nullptr ? 2 : 1);
+#define PIPE_CASE(OPC)                                                              \
+    case OPC:                                                                       \
+        *rc = mode == 2 ? launch_pipe<OPC, 2>(a, rpt, st)                           \
+              : mode == 1 ? launch_pipe<OPC, 1>(a, rpt, st) : launch_pipe<OPC, 0>(a, rpt, st); \
+        return 1;
     switch (op) {
-    case OP_MATVEC: *rc = dict ? launch_pipe<OP_MATVEC, true>(a, rpt, st) : launch_pipe<OP_MATVEC, false>(a, rpt, st); return 1;
-    case OP_SPMV_AB: *rc = dict ? launch_pipe<OP_SPMV_AB, true>(a, rpt, st) : launch_pipe<OP_SPMV_AB, false>(a, rpt, st); return 1;
-    case OP_RESIDUAL: *rc = dict ? launch_pipe<OP_RESIDUAL, true>(a, rpt, st) : launch_pipe<OP_RESIDUAL, false>(a, rpt, st); return 1;
-    case OP_ADD: *rc = dict ? launch_pipe<OP_ADD, true>(a, rpt, st) : launch_pipe<OP_ADD, false>(a, rpt, st); return 1;
-    case OP_JACOBI: *rc = dict ? launch_pipe<OP_JACOBI, true>(a, rpt, st) : launch_pipe<OP_JACOBI, false>(a, rpt, st); return 1;
-    case OP_JACOBI_BSR1: *rc = dict ? launch_pipe<OP_JACOBI_BSR1, true>(a, rpt, st) : launch_pipe<OP_JACOBI_BSR1, false>(a, rpt, st); return 1;
+        PIPE_CASE(OP_MATVEC)
+        PIPE_CASE(OP_SPMV_AB)
+        PIPE_CASE(OP_RESIDUAL)
+        PIPE_CASE(OP_ADD)
+        PIPE_CASE(OP_JACOBI)
+        PIPE_CASE(OP_JACOBI_BSR1)
     }
+#undef PIPE_CASE
     return 0;
 }
 

@@ -19,16 +19,40 @@ struct StreamArgs {
     double alpha, beta, omega;
     const unsigned char *codes = nullptr;   // optional value dictionary (engine-built): Ax[k] == dict[codes[k]]
     const double *dict = nullptr;           // 256 doubles
+    // optional pattern dictionary (square operators): codes index (column offset, value) pairs,
+    // Aj[k] == row + offs[codes[k]] as well -- a constant-coefficient stencil then costs 1 byte per entry
+    const int *offs = nullptr;
 };
 
 // value dictionary of an operator with <= 256 distinct values (csr_pipe.cu DICT path); codes == nullptr: declined
 struct ValueDict {
     unsigned char *codes = nullptr;
     double *dict = nullptr;
+    int *offs = nullptr;             // pattern dictionary only: column offset (Aj - row) per code
     bool ok() const { return codes != nullptr; }
+    void apply(StreamArgs &a) const { a.codes = codes; a.dict = dict; a.offs = offs; }
 };
 int dict_build(long long nnz, const double *Ax, ValueDict *out, cudaStream_t st);
+// (column offset, value) pairs of a square operator; declined when there are more than 256 distinct pairs
+int pattern_build(int n_row, long long nnz, const int *Ap, const int *Aj, const double *Ax, ValueDict *out,
+                  cudaStream_t st);
 void dict_free(ValueDict *d);
+
+// ---- row-pattern layout (rowpat.cu): one byte per row = number of the row's (offset, value) sequence in a
+// table of <= 255 patterns of <= 8 entries (constant-coefficient stencils); codes == nullptr: declined
+struct __align__(16) RowPatEntry {
+    double v;
+    int off, len;                    // column offset (Aj - row); len = entries of the whole pattern
+};
+struct RowPat {
+    unsigned char *codes = nullptr;  // [n]
+    RowPatEntry *table = nullptr;    // [npat * 8]
+    int npat = 0, n = 0;
+    bool ok() const { return codes != nullptr; }
+};
+int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const double *Ax, RowPat *out, cudaStream_t st);
+void rowpat_free(RowPat *r);
+int rowpat_op(int op, const RowPat &r, const StreamArgs &a, cudaStream_t st);
 
 int rows_per_cta_for(long long nnz, int nrows);
 // persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when

@@ -19,6 +19,7 @@ struct LevelRt {
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
+    RowPat rpA;                               // one byte per row of a stencil operator (rowpat.cu)
     ValueDict dA, dP, dR;                     // 8-bit value codes of operators with <= 256 distinct values
     std::vector<int> color_ptr;
 };
@@ -50,13 +51,17 @@ static void free_level(LevelRt &L)
 {
     sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
     dict_free(&L.dA); dict_free(&L.dP); dict_free(&L.dR);
+    rowpat_free(&L.rpA);
 }
 
 // B200AMG_VALUE_DICT=0 switches the value dictionary off (A/B measurements)
-static bool use_value_dict()
+// B200AMG_VALUE_DICT: 0 = operators are streamed as stored, 1 = value dictionary only,
+// 2 = (offset, value) pattern dictionary for A where it applies, 3 / unset = row-pattern layout for A where
+// it applies; each level falls back to the one below when the operator does not qualify
+static int use_value_dict()
 {
     const char *e = getenv("B200AMG_VALUE_DICT");
-    return !(e && e[0] == '0');
+    return (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 3;
 }
 
 // level vectors are padded by an odd number of 2 KB pages so that same-index entries of different
@@ -78,7 +83,8 @@ static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *
     const b200amg_level_desc &d = L.d;
     if (d.bs == 1) {
         StreamArgs a{d.Ap, d.Aj, d.Ax, x, b, y, L.nzA, 0, d.n, 1.0, 0.0, 0.0};
-        a.codes = L.dA.codes; a.dict = L.dA.dict;
+        L.dA.apply(a);
+        if (L.rpA.ok()) return rowpat_op(op_scalar, L.rpA, a, st);
         if (L.sA.ok()) return sell_op(op_scalar, L.sA, a, st);
         return stream_op(op_scalar, a, st);
     }
@@ -90,7 +96,7 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Rp, d.Rj, d.Rx, r, nullptr, bc, L.nzR, 0, d.nc, 1.0, 0.0, 0.0};
-        a.codes = L.dR.codes; a.dict = L.dR.dict;
+        L.dR.apply(a);
         if (L.sR.ok()) return sell_op(OP_MATVEC, L.sR, a, st);
         return stream_op(OP_MATVEC, a, st);
     }
@@ -102,7 +108,7 @@ static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
         StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
-        a.codes = L.dP.codes; a.dict = L.dP.dict;
+        L.dP.apply(a);
         if (L.sP.ok()) return sell_op(OP_ADD, L.sP, a, st);
         return stream_op(OP_ADD, a, st);
     }
@@ -127,8 +133,9 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
             if (it == 0 && x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
             if (d.bs == 1) {
                 StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, L.nzA, 0, d.n, 1.0, 0.0, omega};
-                a.codes = L.dA.codes; a.dict = L.dA.dict;
-                if (L.sA.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sA, a, st));
+                L.dA.apply(a);
+                if (L.rpA.ok()) B200_TRY(rowpat_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.rpA, a, st));
+                else if (L.sA.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sA, a, st));
                 else B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
             } else {
                 B200_TRY(bsr_jacobi(d.bs, 0, d.n / d.bs, d.Ap, d.Aj, d.Ax, *cur, *spare, b, omega, st));
@@ -288,8 +295,13 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
         }
         // short-row operators streamed by the TMA pipeline: try an 8-bit value dictionary (dict.cu)
-        if (!src && L.d.bs == 1 && !L.sA.ok() && nzA > 0 && (double)nzA / L.d.n <= 8.0 && use_value_dict())
-            src = dict_build(nzA, L.d.Ax, &L.dA, nullptr);
+        // (A first as a pattern dictionary -- offset and value in one code -- then values only)
+        if (!src && L.d.bs == 1 && !L.sA.ok() && nzA > 0 && (double)nzA / L.d.n <= 8.0 && use_value_dict()) {
+            if (use_value_dict() >= 3) src = rowpat_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.rpA, nullptr);
+            if (!src && !L.rpA.ok() && use_value_dict() >= 2)
+                src = pattern_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.dA, nullptr);
+            if (!src && !L.rpA.ok() && !L.dA.ok()) src = dict_build(nzA, L.d.Ax, &L.dA, nullptr);
+        }
         if (!src && L.d.p_br == 1 && L.d.p_bc == 1 && use_value_dict()) {
             if (!L.sP.ok() && nzP > 0 && (double)nzP / L.d.n <= 8.0) src = dict_build(nzP, L.d.Px, &L.dP, nullptr);
             if (!src && !L.sR.ok() && nzR > 0 && (double)nzR / L.d.nc <= 8.0) src = dict_build(nzR, L.d.Rx, &L.dR, nullptr);
@@ -381,6 +393,22 @@ extern "C" int b200amg_vcycle_residual_norm2(void *handle, const double *x, cons
     LevelRt &L = E->lev[0];
     B200_TRY(apply_A(L, OP_RESIDUAL, 1, x, b, L.r, st));
     return dot(L.d.n, L.r, L.r, out, E->dot_work, st);
+}
+
+// layout the engine streams an operator in: 1 CSR as given, 2 sliced-ELL copy, 3 CSR + 8-bit value codes,
+// 4 CSR row pointers + 8-bit (offset, value) pattern codes, 5 one row-pattern byte per row;
+// 0 = block operator / no such level
+extern "C" int b200amg_vcycle_layout(void *handle, int level, int which)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || level < 0 || level >= (int)E->lev.size() || which < 0 || which > 2) return 0;
+    const LevelRt &L = E->lev[level];
+    if (which == 0 ? L.d.bs != 1 : (L.d.p_br != 1 || L.d.p_bc != 1)) return 0;
+    const Sell &s = which == 0 ? L.sA : which == 1 ? L.sP : L.sR;
+    const ValueDict &d = which == 0 ? L.dA : which == 1 ? L.dP : L.dR;
+    if (which == 0 && L.rpA.ok()) return 5;
+    if (s.ok()) return 2;
+    return d.ok() ? (d.offs ? 4 : 3) : 1;
 }
 
 extern "C" int b200amg_vcycle_destroy(void *handle)

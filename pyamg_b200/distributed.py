@@ -50,6 +50,10 @@ class DeviceBackend:
             self.be._lib.call('b200amg_op_apply', self.h, op, x.data_ptr(), 0 if b is None else b.data_ptr(),
                               y.data_ptr(), float(omega), self.be.stream())
 
+        def layout(self):
+            """b200amg_op_layout code: 1 CSR, 2 sliced-ELL, 3 value codes, 4 pattern codes"""
+            return int(self.be._lib.load().b200amg_op_layout(self.h))
+
         def diagonal(self):
             d = torch.empty(self.n_row, dtype=torch.float64, device=self.dx.device)
             self.be._lib.call('b200amg_extract_diag', self.n_row, 1, self.ip.data_ptr(), self.ix.data_ptr(),

@@ -269,6 +269,84 @@ def test_pipeline_schedule_bit_exact(amg, name, make):
         assert np.array_equal(xd.cpu().numpy(), xo)
 
 
+def few_valued_irregular(rng):
+    """short rows, 6 distinct values, irregular columns: the value dictionary applies, the pattern one does not"""
+    n = 70000
+    rows = np.repeat(np.arange(n), 4)
+    cols = (rows + rng.randint(-40, 40, rows.size)) % n
+    vals = rng.choice(np.array([-1.0, 0.5, 2.0, -0.0, 1e-300, 3.25]), rows.size)
+    A = sp.coo_matrix((vals, (rows, cols)), shape=(n, n)).tocsr()        # duplicates summed: a few more values
+    A = sp.csr_matrix(A + sp.diags(np.full(n, 4.0))); A.sort_indices()
+    return A
+
+
+def stencil_with_oddities(rng):
+    """5-point stencil with an empty row, a row without a diagonal and a stored zero on a diagonal"""
+    A = lap2d(400)
+    A.sort_indices()
+    A.data[A.indptr[5000]:A.indptr[5001]] = 0.0                          # becomes an empty row
+    k = A.indptr[123] + int(np.where(A.indices[A.indptr[123]:A.indptr[124]] == 123)[0][0])
+    A.data[k] = 0.0                                                      # row 123 loses its diagonal entry
+    A.eliminate_zeros()
+    k = A.indptr[17] + int(np.where(A.indices[A.indptr[17]:A.indptr[18]] == 17)[0][0])
+    A.data[k] = 0.0                                                      # explicit zero stays stored
+    return A
+
+
+def stencil_many_row_patterns(rng):
+    """5-point stencil whose diagonal takes 400 different values: few (offset, value) pairs per offset would
+    still fit... but not 255 row patterns -> the row-pattern layout declines, so does the pattern dictionary"""
+    A = lap2d(300)
+    A.sort_indices()
+    A = sp.csr_matrix(A + sp.diags((np.arange(A.shape[0]) % 400).astype(float)))
+    A.sort_indices()
+    return A
+
+
+DICT_CASES = [('lap2d_800', lambda rng: lap2d(800), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('few_valued_irregular', few_valued_irregular, {'0': 1, '1': 3, '2': 3, '3': 3}),
+              ('stencil_with_oddities', stencil_with_oddities, {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('stencil_many_row_patterns', stencil_many_row_patterns, {'0': 1, '1': 1, '2': 1, '3': 1}),
+              ('ragged_many_values', ragged_matrix, {'0': 1, '1': 1, '2': 1, '3': 1})]
+
+
+@pytest.mark.parametrize('level', ['0', '1', '2', '3'])
+@pytest.mark.parametrize('name,make,layouts', DICT_CASES)
+def test_dictionary_layouts_bit_exact(amg, monkeypatch, name, make, layouts, level):
+    """B200AMG_VALUE_DICT = 0 / 1 / 2 / 3: as stored, 8-bit value codes, 8-bit (offset, value) pattern codes,
+    one row-pattern byte per row -- the operator handle must pick the expected layout (falling back when the
+    operator does not qualify) and give the same bits in every one"""
+    import ctypes
+    monkeypatch.setenv('B200AMG_VALUE_DICT', level)
+    rng = np.random.RandomState(5)
+    A = make(rng)
+    n = A.shape[0]
+    x, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    P = lambda t: t.data_ptr()
+    h = ctypes.c_void_p()
+    amg._lib.call('b200amg_op_create', n, P(dA.indptr), P(dA.indices), P(dA.data), 0, ctypes.byref(h), 0)
+    try:
+        assert amg._lib.load().b200amg_op_layout(h) == layouts[level]
+
+        def run(op, y0):
+            y = dev(y0)
+            dx, db = dev(x), dev(b)
+            amg._lib.call('b200amg_op_apply', h, op, P(dx), P(db), P(y), 0.7, 0)
+            torch.cuda.synchronize()
+            return y.cpu().numpy()
+        assert np.array_equal(run(0, np.zeros(n)), A * x)
+        assert np.array_equal(run(2, np.zeros(n)), b - A * x)
+        assert np.array_equal(run(3, b), b + A * x)
+        xo = x.copy(); orx.jacobi(A, xo, b, iterations=1, omega=0.7, core=oracle.port)
+        assert np.array_equal(run(4, np.zeros(n)), xo)
+        Ab = sp.bsr_matrix(A, blocksize=(1, 1))
+        xo = x.copy(); orx.jacobi(Ab, xo, b, iterations=1, omega=0.7, core=oracle.port)
+        assert np.array_equal(run(5, np.zeros(n)), xo)
+    finally:
+        amg._lib.call('b200amg_op_destroy', h)
+
+
 @pytest.mark.parametrize('name,n,per_row', [('coarse_like', 40000, 31), ('restriction_like', 9000, 240),
                                              ('small_pipe_form', 3000, 60)])
 def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
