@@ -47,7 +47,7 @@ struct __align__(16) RowPatEntry {
 struct RowPat {
     unsigned char *codes = nullptr;  // [n]
     RowPatEntry *table = nullptr;    // [npat * 8]
-    int npat = 0, n = 0;
+    int npat = 0, n = 0, far = 0;    // far = largest column offset in the table
     bool ok() const { return codes != nullptr; }
 };
 int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const double *Ax, RowPat *out, cudaStream_t st);

@@ -12,6 +12,7 @@
 // jacobi loops (pyamg/amg_core/relaxation.h:201-239, :267-360): results are bit-identical to the CSR kernels.
 // Detection is exact: rows are grouped by a 64-bit hash first, then EVERY row is compared entry by entry with
 // its pattern's table entry; any mismatch (hash collision) declines the layout.
+#include <string.h>
 #include <algorithm>
 #include <vector>
 #include "internal.cuh"
@@ -195,6 +196,12 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
         if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(st);
         good = e == cudaSuccess && !rc && flags[2] == 0;
         if (good) {
+            std::vector<RowPatEntry> ht((size_t)RP_LEN * npat);
+            e = cudaMemcpy(ht.data(), table, sizeof(RowPatEntry) * ht.size(), cudaMemcpyDeviceToHost);
+            good = e == cudaSuccess;
+            for (const RowPatEntry &en : ht) out->far = std::max(out->far, en.off);
+        }
+        if (good) {
             out->codes = codes;
             out->table = table;
             out->npat = npat;
@@ -221,12 +228,21 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
 // thread = row.  A CTA walks chunks of RP_CHUNK consecutive rows (round-robin over the grid): inside a chunk
 // the +-1 and +-nx neighbours are re-read from L1, and because all CTAs advance through the matrix together
 // the +-nx*ny neighbours (a few MB away) are still in L2 -- x crosses HBM once.
+#ifndef RP_CHUNK_ROWS
+#define RP_CHUNK_ROWS 1024
+#endif
+#ifndef RP_AHEAD
+#define RP_AHEAD 1
+#endif
+#ifndef RP_RESIDENT
+#define RP_RESIDENT 4
+#endif
 constexpr int RP_TPB = 256;
-constexpr int RP_CHUNK = 1024;
-constexpr int RP_CTAS_PER_SM = 4;
+constexpr int RP_CHUNK = RP_CHUNK_ROWS;
+constexpr int RP_CTAS_PER_SM = RP_RESIDENT;
 
 struct RowPatArgs {
-    int n, npat;
+    int n, npat, far;                // far = largest column offset of any pattern (prefetch distance in x)
     const unsigned char *codes;
     const RowPatEntry *table;
     const double *x, *b;
@@ -296,19 +312,48 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
     __syncthreads();
     const double *__restrict__ xg = a.x;
     const int n_chunks = (a.n + RP_CHUNK - 1) / RP_CHUNK;
-    for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
-        const int r_end = min(a.n, (ch + 1) * RP_CHUNK);
+    // A CTA's steps: step k covers rows [r0, r0 + 256) of chunk blockIdx.x + (k / SPC) * gridDim.x.
+    constexpr int SPC = RP_CHUNK / RP_TPB;                       // steps per chunk
+    auto step_row = [&](int k) -> int {                          // this thread's row at step k, -1 past the end
+        const int ch = (int)blockIdx.x + (k / SPC) * (int)gridDim.x;
+        const int row = ch * RP_CHUNK + (k % SPC) * RP_TPB + (int)threadIdx.x;
+        return (ch < n_chunks && row < a.n) ? row : -1;
+    };
+    // Latency hiding.  (1) The pattern number of a row is needed before its gathers can start: it is loaded
+    // one step ahead.  (2) What a step pulls from DRAM -- its slice of b and the x entries of its farthest
+    // neighbours (first touch of x; every other gather finds x in L1/L2) -- is requested RP_AHEAD steps ahead
+    // with prefetch.global.L2, one lane per 128-byte line: the 32 resident warps of an SM cannot keep enough
+    // demand loads in flight to cover HBM latency, the prefetches cost no registers.
+    const int far = a.far;
+    const int my_steps = ((n_chunks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x) * SPC;
+    int code_next = step_row(0) >= 0 ? (int)a.codes[step_row(0)] : -1;
 #pragma unroll 1
-        for (int r0 = ch * RP_CHUNK; r0 < r_end; r0 += RP_TPB) {        // warp-uniform trip count
-            const int row = r0 + (int)threadIdx.x;
-            const bool live = row < r_end;
+    for (int k = 0; k < my_steps; ++k) {
+        {
+            const int row = step_row(k);
+            const int code = code_next;
+            const bool live = row >= 0;
+            {
+                const int rn = step_row(k + 1);
+                code_next = rn >= 0 ? (int)a.codes[rn] : -1;
+            }
+#if RP_AHEAD > 0
+            if ((threadIdx.x & 15) == 0) {
+                const int rp = step_row(k + RP_AHEAD);
+                if (rp >= 0) {
+                    if (NEED_B) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.b + rp));
+                    if (NEED_Y) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.y + rp));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + min(rp + far, a.n - 1)));
+                }
+            }
+#endif
             const RowPatEntry *p = tab;
             double bi = 0.0, xi = 0.0, yi = 0.0;
             int len = 0;
             unsigned dm = 0;
             const double *xr = xg + row;
             if (live) {
-                p = tab + (int)a.codes[row] * RP_LEN;
+                p = tab + code * RP_LEN;
                 if (NEED_B) bi = __ldg(a.b + row);
                 if (SMOOTH) xi = __ldg(xr);
                 if (NEED_Y) yi = a.y[row];
@@ -318,6 +363,7 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
             }
             double acc = BSRF ? bi : 0.0;
             // interior warps: every lane has the same row length -> straight-line code without predicates
+            // (a table copy in the constant bank or in registers for warps with ONE pattern was tried: both slower)
             const int l0 = __shfl_sync(0xffffffffu, len, 0);
             if (__all_sync(0xffffffffu, len == l0)) {
                 switch (l0) {
@@ -367,9 +413,9 @@ static int launch_rowpat(const RowPat &r, const StreamArgs &s, cudaStream_t st)
         B200_CUDA(cudaGetDevice(&dev));
         B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     }
-    RowPatArgs a{r.n, r.npat, r.codes, r.table, s.x, s.b, s.y, s.alpha, s.beta, s.omega};
     const int n_chunks = (r.n + RP_CHUNK - 1) / RP_CHUNK;
     const int grid = std::min(n_chunks, sms * RP_CTAS_PER_SM);
+    RowPatArgs a{r.n, r.npat, r.far, r.codes, r.table, s.x, s.b, s.y, s.alpha, s.beta, s.omega};
     rowpat_kernel<OP><<<grid, RP_TPB, sizeof(RowPatEntry) * RP_LEN * r.npat, st>>>(a);
     return check_launch("rowpat_kernel");
 }
