@@ -102,9 +102,9 @@ def measured_peak():
     return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-ENTRY_BYTES = {1: 12, 2: 12, 3: 5, 4: 1, 5: 0}   # bytes per stored entry by engine layout (b200amg_vcycle_layout)
+ENTRY_BYTES = {1: 12, 2: 12, 3: 5, 4: 1, 5: 0, 6: 5}   # bytes per stored entry by engine layout (b200amg_vcycle_layout)
 LAYOUT_NAME = {1: 'CSR (int32 column + fp64 value)', 2: 'sliced-ELL copy', 3: 'CSR + 8-bit value codes',
-               4: 'CSR rows + 8-bit (offset, value) pattern codes', 5: 'one row-pattern byte per row'}
+               4: 'CSR rows + 8-bit (offset, value) pattern codes', 5: 'one row-pattern byte per row', 6: 'sliced-ELL copy with 8-bit value codes'}
 
 
 def matrix_bytes(n, nnz, layout=1):

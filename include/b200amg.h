@@ -120,7 +120,8 @@ int b200amg_op_apply(void *handle, int op, const double *x, const double *b, dou
                      void *stream);
 int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL, 3 CSR + 8-bit value codes, 4 CSR rows + 8-bit
                                            * (column offset, value) pattern codes, 5 one row-pattern
-                                           * byte per row (stencil operators) */
+                                           * byte per row (stencil operators), 6 sliced-ELL with
+                                           * 8-bit value codes */
 int b200amg_op_destroy(void *handle);
 
 /* ---- multi-GPU halo refresh over NVLink peer memory (pyamg_b200/distributed.py) -------

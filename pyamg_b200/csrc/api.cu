@@ -188,7 +188,12 @@ extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const 
         if (e != cudaSuccess) { delete h; return set_err((int)e, "op_create: cannot read row pointers"); }
         h->nnz = (long long)ends[1] - ends[0];
         if (layout == 2 || (layout == 0 && sell_wanted(h->nnz, n_row))) {
-            int rc = sell_build(n_row, h->nnz, Ap, Aj, Ax, &h->sell, S(stream));
+            // value slots as 8-bit codes when the operator has <= 256 distinct values (B200AMG_VALUE_DICT=0: never)
+            const char *ev = getenv("B200AMG_VALUE_DICT");
+            ValueDict vd;
+            int rc = (ev && ev[0] == '0') ? 0 : dict_build(h->nnz, Ax, &vd, S(stream));
+            if (!rc) rc = sell_build(n_row, h->nnz, Ap, Aj, Ax, &h->sell, S(stream), nullptr, vd.codes, vd.dict);
+            dict_free(&vd);
             if (rc) { delete h; return rc; }
             if (layout == 2 && !h->sell.ok()) { delete h; return set_err(B200AMG_ESTATE, "op_create: sliced-ELL layout declined (padding too large)"); }
         }
@@ -225,7 +230,7 @@ extern "C" int b200amg_op_layout(void *handle)
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
     if (!h) return 0;
     if (h->rp.ok()) return 5;
-    if (h->sell.ok()) return 2;
+    if (h->sell.ok()) return h->sell.cc ? 6 : 2;
     return h->vd.ok() ? (h->vd.offs ? 4 : 3) : 1;
 }
 

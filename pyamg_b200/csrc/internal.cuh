@@ -65,12 +65,14 @@ struct Sell {
     long long padded = 0;            // stored slots (32 * sum of slice widths)
     long long *slice_off = nullptr;  // [n_slices + 1] slot offset of every slice
     int *cj = nullptr;               // [padded]
-    double *cv = nullptr;            // [padded]
+    double *cv = nullptr;            // [padded]   (fp64 values) or
+    unsigned char *cc = nullptr;     // [padded]   8-bit value codes into dict[256]
+    double *dict = nullptr;
     int *row_len = nullptr;          // [n]
     bool ok() const { return cj != nullptr; }
 };
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
-               const int *perm = nullptr);
+               const int *perm = nullptr, const unsigned char *codes = nullptr, const double *dict = nullptr);
 // one colour [p0, p1) of a colour-grouped copy (slot row r = matrix row Id[r]); x updated in place
 int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st);
 void sell_free(Sell *s);

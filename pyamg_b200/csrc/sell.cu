@@ -12,6 +12,7 @@
 // does it (scipy csr_matvec / amg_core jacobi, pyamg/amg_core/relaxation.h:201-239): the bits
 // are those of the CSR kernels.  Cost: the copy (engine-owned, built once per level) and
 // 19-23 % padding traffic; no shared memory, no barriers, 8 independent loads in flight per lane.
+#include <type_traits>
 #include "internal.cuh"
 #include "setup.cuh"
 
@@ -49,7 +50,8 @@ __global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__res
 __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                         const double *__restrict__ Ax, const int *__restrict__ perm,
                                                         const long long *__restrict__ slice_off, int *__restrict__ cj,
-                                                        double *__restrict__ cv)
+                                                        double *__restrict__ cv, const unsigned char *__restrict__ codes,
+                                                        unsigned char *__restrict__ cc)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     const int slice = row >> 5, lane = threadIdx.x & 31;
@@ -65,7 +67,8 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__rest
     for (int k = 0; k < w; ++k) {
         const bool in = k < len;
         cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
-        cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
+        if (cc) cc[off + (long long)k * SELL_C + lane] = in ? codes[lo + k] : (unsigned char)0;
+        else cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
     }
 }
 
@@ -74,13 +77,16 @@ void sell_free(Sell *s)
     if (s->slice_off) cudaFree(s->slice_off);
     if (s->cj) cudaFree(s->cj);
     if (s->cv) cudaFree(s->cv);
+    if (s->cc) cudaFree(s->cc);
+    if (s->dict) cudaFree(s->dict);
     if (s->row_len) cudaFree(s->row_len);
     *s = Sell();
 }
 
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
-               const int *perm)
+               const int *perm, const unsigned char *codes, const double *dict)
 {
+    const bool coded = codes != nullptr && dict != nullptr;     // 8-bit value codes instead of fp64 values
     *out = Sell();
     if (n <= 0) return 0;
     const int ns = (n + SELL_C - 1) / SELL_C;
@@ -104,15 +110,18 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
     // refuse pathological padding (one long row per slice): the CSR kernels handle those
     if (e == cudaSuccess && !rc && s.padded > 0 && s.padded <= 2 * nnz + 64 * SELL_C) {
         e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
-        if (e == cudaSuccess) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
+        if (e == cudaSuccess && !coded) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
+        if (e == cudaSuccess && coded) e = cudaMalloc(&s.cc, (size_t)s.padded + 64);
+        if (e == cudaSuccess && coded) e = cudaMalloc(&s.dict, sizeof(double) * 256);
+        if (e == cudaSuccess && coded) e = cudaMemcpyAsync(s.dict, dict, sizeof(double) * 256, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess) {
-            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv);
+            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc);
             rc = check_launch("sell_fill_kernel");
         }
     }
     if (width) cudaFree(width);
     if (scratch) cudaFree(scratch);
-    if (e != cudaSuccess || rc || !s.cj || !s.cv) {
+    if (e != cudaSuccess || rc || !s.cj || !(s.cv || s.cc)) {
         sell_free(&s);
         if (e != cudaSuccess) {
             cudaGetLastError();
@@ -127,11 +136,24 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
 // ---- apply ----------------------------------------------------------------------------------
 // PIPE: prefetch the next round's slots (100 registers, 2 CTAs/SM) -- pays when the matrix has too few
 // rows to fill the SMs with warps anyway; large matrices run the plain form (64 registers, 4 CTAs/SM)
-template <int OP, bool PIPE>
+// CODED: the value slots hold 8-bit codes into a table of <= 256 doubles (dict.cu) -- 5 bytes per slot instead of 12
+template <int OP, bool PIPE, bool CODED>
 __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long long *__restrict__ slice_off,
-                                                        const int *__restrict__ cj, const double *__restrict__ cv,
+                                                        const int *__restrict__ cj, const void *__restrict__ cvals,
+                                                        const double *__restrict__ dict,
                                                         const int *__restrict__ row_len, const StreamArgs a)
 {
+    using V = typename std::conditional<CODED, unsigned char, double>::type;
+    const V *__restrict__ cv = reinterpret_cast<const V *>(cvals);
+    __shared__ double s_dict[CODED ? 256 : 1];
+    if (CODED) {
+        s_dict[threadIdx.x] = dict[threadIdx.x];               // SELL_TPB == 256
+        __syncthreads();
+    }
+    auto value = [&](V raw) -> double {
+        if constexpr (CODED) return s_dict[raw];
+        else return raw;
+    };
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
@@ -151,7 +173,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     }
     double acc = BSRF ? bi : 0.0, diag = 0.0;
     const int *pj = cj + off + lane;
-    const double *pv = cv + off + lane;
+    const V *pv = cv + off + lane;
     if (PIPE) {
     // software pipeline: the (index, value) slots of round r+1 are requested before round r's x
     // gathers are consumed, so a round costs one memory latency, not two
@@ -161,7 +183,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     for (int u = 0; u < SELL_U; ++u) {
         const bool in = u < len;
         c[u] = in ? __ldcs(pj + (long long)u * SELL_C) : -1;
-        v[u] = in ? __ldcs(pv + (long long)u * SELL_C) : 0.0;
+        v[u] = in ? value(__ldcs(pv + (long long)u * SELL_C)) : 0.0;
     }
     for (int k0 = 0; k0 < w; k0 += SELL_U) {
 #pragma unroll
@@ -171,7 +193,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
             const int k = k0 + SELL_U + u;
             const bool in = k < len;
             cn[u] = in ? __ldcs(pj + (long long)k * SELL_C) : -1;
-            vn[u] = in ? __ldcs(pv + (long long)k * SELL_C) : 0.0;
+            vn[u] = in ? value(__ldcs(pv + (long long)k * SELL_C)) : 0.0;
         }
 #pragma unroll
         for (int u = 0; u < SELL_U; ++u) {
@@ -195,7 +217,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
         for (int u = 0; u < SELL_U; ++u) {
             const bool in = k0 + u < len;
             c[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : -1;
-            v[u] = in ? __ldcs(pv + (long long)(k0 + u) * SELL_C) : 0.0;
+            v[u] = in ? value(__ldcs(pv + (long long)(k0 + u) * SELL_C)) : 0.0;
         }
 #pragma unroll
         for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
@@ -290,10 +312,12 @@ template <int OP>
 static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
-    if (s.n < 400000)
-        sell_kernel<OP, true><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
+    if (s.cc)
+        sell_kernel<OP, false, true><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cc, s.dict, s.row_len, a);
+    else if (s.n < 400000)
+        sell_kernel<OP, true, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, s.row_len, a);
     else
-        sell_kernel<OP, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
+        sell_kernel<OP, false, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, s.row_len, a);
     return check_launch("sell_kernel");
 }
 

@@ -289,10 +289,19 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
         L.nzA = nzA; L.nzP = nzP; L.nzR = nzR;
         // long-row scalar operators get a sliced-ELL copy (sell.cu); a declined / failed build keeps CSR
         int src = 0;
-        if (L.d.bs == 1 && sell_wanted(nzA, L.d.n)) src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sA, nullptr);
+        // (with 8-bit value codes in the value slots when the operator has <= 256 distinct values: R_0 of a
+        // stencil problem has ~85)
+        auto sell_with_codes = [&](int n, long long nz, const int *Xp, const int *Xj, const double *Xx, Sell *out) -> int {
+            ValueDict vd;
+            int rc = use_value_dict() ? dict_build(nz, Xx, &vd, nullptr) : 0;
+            if (!rc) rc = sell_build(n, nz, Xp, Xj, Xx, out, nullptr, nullptr, vd.codes, vd.dict);
+            dict_free(&vd);
+            return rc;
+        };
+        if (L.d.bs == 1 && sell_wanted(nzA, L.d.n)) src = sell_with_codes(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sA);
         if (!src && L.d.p_br == 1 && L.d.p_bc == 1) {
-            if (sell_wanted(nzR, L.d.nc)) src = sell_build(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR, nullptr);
-            if (!src && sell_wanted(nzP, L.d.n)) src = sell_build(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP, nullptr);
+            if (sell_wanted(nzR, L.d.nc)) src = sell_with_codes(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR);
+            if (!src && sell_wanted(nzP, L.d.n)) src = sell_with_codes(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP);
         }
         // short-row operators streamed by the TMA pipeline: try an 8-bit value dictionary (dict.cu)
         // (A first as a pattern dictionary -- offset and value in one code -- then values only)
@@ -396,7 +405,8 @@ extern "C" int b200amg_vcycle_residual_norm2(void *handle, const double *x, cons
 }
 
 // layout the engine streams an operator in: 1 CSR as given, 2 sliced-ELL copy, 3 CSR + 8-bit value codes,
-// 4 CSR row pointers + 8-bit (offset, value) pattern codes, 5 one row-pattern byte per row;
+// 4 CSR row pointers + 8-bit (offset, value) pattern codes, 5 one row-pattern byte per row,
+// 6 sliced-ELL copy with 8-bit value codes;
 // 0 = block operator / no such level
 extern "C" int b200amg_vcycle_layout(void *handle, int level, int which)
 {
@@ -407,7 +417,7 @@ extern "C" int b200amg_vcycle_layout(void *handle, int level, int which)
     const Sell &s = which == 0 ? L.sA : which == 1 ? L.sP : L.sR;
     const ValueDict &d = which == 0 ? L.dA : which == 1 ? L.dP : L.dR;
     if (which == 0 && L.rpA.ok()) return 5;
-    if (s.ok()) return 2;
+    if (s.ok()) return s.cc ? 6 : 2;
     return d.ok() ? (d.offs ? 4 : 3) : 1;
 }
 

@@ -347,15 +347,21 @@ def test_dictionary_layouts_bit_exact(amg, monkeypatch, name, make, layouts, lev
         amg._lib.call('b200amg_op_destroy', h)
 
 
-@pytest.mark.parametrize('name,n,per_row', [('coarse_like', 40000, 31), ('restriction_like', 9000, 240),
-                                             ('small_pipe_form', 3000, 60)])
-def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
+@pytest.mark.parametrize('name,n,per_row,few_values', [('coarse_like', 40000, 31, False), ('restriction_like', 9000, 240, False),
+                                                        ('small_pipe_form', 3000, 60, False),
+                                                        ('coded_values', 40000, 30, True)])
+def test_sliced_ell_layout_bit_exact(amg, name, n, per_row, few_values):
     """the engine's SELL-32 copy must give the bits of the CSR kernels / the reference loops"""
     rng = np.random.RandomState(11)
     rows = np.repeat(np.arange(n), per_row)
     cols = (rows + rng.randint(-3 * per_row, 3 * per_row, rows.size)) % n
-    A = sp.csr_matrix((rng.rand(rows.size) - 0.3, (rows, cols)), shape=(n, n))      # duplicates summed, ragged
-    A = sp.csr_matrix(A + sp.diags(rng.rand(n) + 1.0)); A.sort_indices()
+    if few_values:      # restriction-like: a handful of distinct values -> 8-bit codes in the value slots
+        vals = rng.choice(np.array([0.25, -0.125, 1.0, 3.5, -0.0, 1e-310]), rows.size)
+        A = sp.coo_matrix((vals, (rows, cols)), shape=(n, n)).tocsr()
+        A = sp.csr_matrix(A + sp.diags(np.full(n, 2.0))); A.sort_indices()
+    else:
+        A = sp.csr_matrix((rng.rand(rows.size) - 0.3, (rows, cols)), shape=(n, n))  # duplicates summed, ragged
+        A = sp.csr_matrix(A + sp.diags(rng.rand(n) + 1.0)); A.sort_indices()
     x, b = rng.rand(n), rng.rand(n)
     dA = amg.DevMat.from_scipy(A)
     P = lambda t: t.data_ptr()
@@ -363,7 +369,7 @@ def test_sliced_ell_layout_bit_exact(amg, name, n, per_row):
     import ctypes
     h = ctypes.c_void_p()
     amg._lib.call('b200amg_op_create', n, P(dA.indptr), P(dA.indices), P(dA.data), 2, ctypes.byref(h), 0)
-    assert amg._lib.load().b200amg_op_layout(h) == 2
+    assert amg._lib.load().b200amg_op_layout(h) == (6 if few_values else 2)
 
     def run(op, y0):
         y = dev(y0)
