@@ -370,3 +370,137 @@ void orc_fit_candidates(I n_col, I K1, I K2, const I *Ap, const I *Ai, T *Qx, co
         }
     }
 }
+
+/* ==== Ruge-Stuben setup pieces, restated from pyamg/amg_core/ruge_stuben.h ======== */
+
+/* ---- amg_core.classical_strength_of_connection, ruge_stuben.h:45-93 (real T): off-diagonal a_ij is
+ * strong when |a_ij| >= theta * max_{k != i} |a_ik| (the running maximum starts at DBL_MIN, the smallest
+ * positive normal, :57); stored diagonal entries are always kept; order inside a row unchanged. */
+void orc_classical_strength(I n, T theta, const I *Ap, const I *Aj, const T *Ax, I *Sp, I *Sj, T *Sx)
+{
+    I out = 0;
+    Sp[0] = 0;
+    for (I i = 0; i < n; i++) {
+        T big = 2.2250738585072014e-308;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++)
+            if (Aj[p] != i && fabs(Ax[p]) > big) big = fabs(Ax[p]);
+        const T lim = theta * big;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++)
+            if (Aj[p] == i || fabs(Ax[p]) >= lim) { Sj[out] = Aj[p]; Sx[out] = Ax[p]; out++; }
+        Sp[i + 1] = out;
+    }
+}
+
+/* ---- amg_core.rs_cf_splitting, ruge_stuben.h:157-297.  First-pass Ruge-Stuben coarsening: nodes
+ * are kept in an array ordered by their measure lambda (= column count of S, i.e. row length of
+ * T = S^T), one contiguous bucket per measure value; the last node of the array is taken as the next
+ * C point, its undecided dependants become F points, and measures of their / its undecided
+ * neighbours go up / down by one, which moves the node to the far / near end of its bucket and
+ * shifts the bucket boundary.  The tie-breaking between equal measures IS the bucket mechanics, so
+ * they are reproduced exactly, including: bucket starts are only initialised for measures < n
+ * (:180-184), nodes with measure >= n-1 are never raised (:241), measure 0 is never lowered (:270).
+ * split[i]: 1 = C, 0 = F. */
+static void rs_swap(I *seq, I *where, I a, I b)
+{
+    const I na = seq[a], nb = seq[b];
+    seq[a] = nb; seq[b] = na;
+    where[nb] = a; where[na] = b;
+}
+
+void orc_rs_cf_splitting(I n, const I *Sp, const I *Sj, const I *Tp, const I *Tj, I *split)
+{
+    I *meas = (I *)calloc((size_t)n + 1, sizeof(I));
+    I *first = (I *)calloc((size_t)n + 1, sizeof(I));
+    I *fill = (I *)calloc((size_t)n + 1, sizeof(I));
+    I *seq = (I *)malloc(sizeof(I) * ((size_t)n + 1));
+    I *where = (I *)malloc(sizeof(I) * ((size_t)n + 1));
+    for (I i = 0; i < n; i++) { meas[i] = Tp[i + 1] - Tp[i]; fill[meas[i]]++; }
+    for (I v = 0, run = 0; v < n; v++) { first[v] = run; run += fill[v]; fill[v] = 0; }
+    for (I i = 0; i < n; i++) {
+        const I at = first[meas[i]] + fill[meas[i]]++;
+        seq[at] = i; where[i] = at;
+    }
+    for (I i = 0; i < n; i++)
+        split[i] = (meas[i] == 0 || (meas[i] == 1 && Tj[Tp[i]] == i)) ? 0 : 2;
+    for (I top = n - 1; top >= 0; top--) {
+        const I c = seq[top];
+        fill[meas[c]]--;
+        if (split[c] == 0) continue;
+        split[c] = 1;
+        for (I p = Tp[c]; p < Tp[c + 1]; p++) {
+            const I f = Tj[p];
+            if (split[f] != 2) continue;
+            split[f] = 0;
+            for (I q = Sp[f]; q < Sp[f + 1]; q++) {
+                const I k = Sj[q];
+                if (split[k] != 2 || meas[k] >= n - 1) continue;
+                const I m = meas[k], to = first[m] + fill[m] - 1;
+                rs_swap(seq, where, where[k], to);
+                fill[m]--; fill[m + 1]++;
+                first[m + 1] = to;
+                meas[k] = m + 1;
+            }
+        }
+        for (I p = Sp[c]; p < Sp[c + 1]; p++) {
+            const I j = Sj[p];
+            if (split[j] != 2 || meas[j] == 0) continue;
+            const I m = meas[j], to = first[m];
+            rs_swap(seq, where, where[j], to);
+            fill[m]--; fill[m - 1]++;
+            first[m]++;
+            first[m - 1] = first[m] - fill[m - 1];
+            meas[j] = m - 1;
+        }
+    }
+    free(meas); free(first); free(fill); free(seq); free(where);
+}
+
+/* ---- amg_core.rs_direct_interpolation_pass1, ruge_stuben.h:496-515: row pointer of P.  A C row has
+ * one entry; an F row one entry per strong C neighbour other than itself. */
+void orc_rs_direct_interpolation_pass1(I n, const I *Sp, const I *Sj, const I *split, I *Pp)
+{
+    I run = 0;
+    Pp[0] = 0;
+    for (I i = 0; i < n; i++) {
+        if (split[i] == 1) run++;
+        else
+            for (I p = Sp[i]; p < Sp[i + 1]; p++) run += (split[Sj[p]] == 1 && Sj[p] != i);
+        Pp[i + 1] = run;
+    }
+}
+
+/* ---- amg_core.rs_direct_interpolation_pass2, ruge_stuben.h:518-595: direct interpolation weights
+ * w_ij = -(sum of all negative a_ik / sum of strong-C negative a_ik) a_ij / a_ii for negative a_ij, the
+ * same with the positive sums for positive a_ij; without positive strong C neighbours the positive
+ * off-diagonals are lumped into the diagonal (:569-572).  Sums run in storage order; columns are
+ * renumbered to coarse indices at the end (:589-595). */
+void orc_rs_direct_interpolation_pass2(I n, const I *Ap, const I *Aj, const T *Ax, const I *Sp, const I *Sj,
+                                       const T *Sx, const I *split, const I *Pp, I *Pj, T *Px)
+{
+    for (I i = 0; i < n; i++) {
+        if (split[i] == 1) { Pj[Pp[i]] = i; Px[Pp[i]] = 1; continue; }
+        T sneg = 0, spos = 0, aneg = 0, apos = 0, d = 0;
+        for (I p = Sp[i]; p < Sp[i + 1]; p++)
+            if (split[Sj[p]] == 1 && Sj[p] != i) { if (Sx[p] < 0) sneg += Sx[p]; else spos += Sx[p]; }
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            if (Aj[p] == i) d += Ax[p];
+            else if (Ax[p] < 0) aneg += Ax[p];
+            else apos += Ax[p];
+        }
+        const T alpha = aneg / sneg;
+        T beta = apos / spos;
+        if (spos == 0) { d += apos; beta = 0; }
+        const T cn = -alpha / d, cp = -beta / d;
+        I at = Pp[i];
+        for (I p = Sp[i]; p < Sp[i + 1]; p++)
+            if (split[Sj[p]] == 1 && Sj[p] != i) {
+                Pj[at] = Sj[p];
+                Px[at] = (Sx[p] < 0 ? cn : cp) * Sx[p];
+                at++;
+            }
+    }
+    I *renum = (I *)malloc(sizeof(I) * ((size_t)n + 1));
+    for (I i = 0, run = 0; i < n; i++) { renum[i] = run; run += split[i]; }
+    for (I p = 0; p < Pp[n]; p++) Pj[p] = renum[Pj[p]];
+    free(renum);
+}
