@@ -197,6 +197,25 @@ int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, const doubl
                             const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
                             int *Cj, double *Cx, void *stream);
 
+/* ---- Ruge-Stuben setup (csrc/rs_setup.cu): pyamg/amg_core/ruge_stuben.h:45-93, :496-595 -------- */
+/* amg_core.classical_strength_of_connection fused with the two things the reference's glue does to S:
+ * flags & 1: drop the diagonal (the graph of the C/F splitting, pyamg/util/utils.py:1815-1827);
+ * flags & 2: do not store exact zeros, flags & 4: rows in reverse storage order -- C = pattern(S) .* A as
+ * scipy's csr_elmul_csr returns it for canonical (2) / non-canonical (2|4) A (classical/interpolate.py:55-57).
+ * pass 0 writes cnt[i]; pass 1 fills Cj/Cx at Cp[i] (Cx = entries of A). */
+int b200amg_rs_strength(int n_row, double theta, const int *Ap, const int *Aj, const double *Ax, int flags,
+                        int pass, int *cnt, const int *Cp, int *Cj, double *Cx, void *stream);
+/* flag_dev[0] = 1 when some row is not strictly increasing in column (scipy csr_has_canonical_format) */
+int b200amg_csr_not_canonical(int n_row, const int *Ap, const int *Aj, int *flag_dev, void *stream);
+/* amg_core.rs_direct_interpolation_pass1: entries per row of P (the caller scans them into Pp) */
+int b200amg_rs_direct_interpolation_pass1(int n_nodes, const int *Sp, const int *Sj, const int *splitting,
+                                          int *cnt, void *stream);
+/* amg_core.rs_direct_interpolation_pass2; cmap = exclusive scan of splitting (coarse index of a C point,
+ * the reference's `map`, ruge_stuben.h:589-595) */
+int b200amg_rs_direct_interpolation_pass2(int n_nodes, const int *Ap, const int *Aj, const double *Ax,
+                                          const int *Sp, const int *Sj, const double *Sx, const int *splitting,
+                                          const int *cmap, const int *Pp, int *Pj, double *Px, void *stream);
+
 /* ---- host-side, inherently sequential setup steps whose INTEGER result must be identical
  *      to the reference (arrays are HOST pointers) ------------------------------------------ */
 /* amg_core.vertex_coloring_mis, pyamg/amg_core/graph.h:171-188: returns K, color[i] in [0,K) */
@@ -205,6 +224,10 @@ int b200amg_vertex_coloring_mis_host(int n, const int *Ap_host, const int *Aj_ho
  * number of aggregates; agg[i] = aggregate of node i or -1; roots[k] = seed node of k */
 int b200amg_standard_aggregation_host(int n, const int *Ap_host, const int *Aj_host, int *agg_host,
                                       int *roots_host);
+/* amg_core.rs_cf_splitting, pyamg/amg_core/ruge_stuben.h:157-297: S (no diagonal) and T = S^T as host CSR;
+ * splitting[i] = 1 (C point) or 0 (F point) */
+int b200amg_rs_cf_splitting_host(int n_nodes, const int *Sp_host, const int *Sj_host, const int *Tp_host,
+                                 const int *Tj_host, int *splitting_host);
 
 /* ---- whole-cycle engine: multilevel_solver.__solve, pyamg/multilevel.py:473-548 ------- */
 typedef struct b200amg_level_desc {

@@ -8,9 +8,10 @@ from .sparse import DevMat, matmat, transpose, galerkin
 from .multilevel import multilevel_solver, coarse_grid_solver
 from .smoothing import change_smoothers, rho_D_inv_A
 from .aggregation import smoothed_aggregation_solver
+from .classical import ruge_stuben_solver
 from .hierarchy import import_hierarchy
-from . import amg_core, relaxation, gallery, linalg, krylov, partition, distributed
+from . import amg_core, relaxation, gallery, linalg, krylov, partition, distributed, classical
 
 __all__ = ['DevMat', 'matmat', 'transpose', 'galerkin', 'multilevel_solver', 'coarse_grid_solver',
-           'change_smoothers', 'rho_D_inv_A', 'smoothed_aggregation_solver', 'import_hierarchy',
-           'amg_core', 'relaxation', 'gallery', 'linalg', 'krylov']
+           'change_smoothers', 'rho_D_inv_A', 'smoothed_aggregation_solver', 'ruge_stuben_solver', 'import_hierarchy',
+           'amg_core', 'relaxation', 'gallery', 'linalg', 'krylov', 'classical']

@@ -66,6 +66,11 @@ _SIGS = {
     'b200amg_tentative_fill': (c_int, [c_int, p, p, p, p, p, p]),
     'b200amg_csr_sub_sorted': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
     'b200amg_csr_sub_general': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
+    'b200amg_rs_strength': (c_int, [c_int, c_double, p, p, p, c_int, c_int, p, p, p, p, p]),
+    'b200amg_csr_not_canonical': (c_int, [c_int, p, p, p, p]),
+    'b200amg_rs_direct_interpolation_pass1': (c_int, [c_int, p, p, p, p, p]),
+    'b200amg_rs_direct_interpolation_pass2': (c_int, [c_int, p, p, p, p, p, p, p, p, p, p, p, p]),
+    'b200amg_rs_cf_splitting_host': (c_int, [c_int, p, p, p, p, p]),
     'b200amg_vertex_coloring_mis_host': (c_int, [c_int, p, p, p]),
     'b200amg_standard_aggregation_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),

@@ -109,3 +109,15 @@ def standard_aggregation(n_row, Ap, Aj, x, y):
     if n < 0:
         raise _lib.B200AmgError(lib.b200amg_last_error().decode())
     return n
+
+
+def rs_cf_splitting(n_nodes, Sp, Sj, Tp, Tj, splitting):
+    """ruge_stuben.h:157-297 (host int32 numpy arrays; sequential by definition): splitting[i] = 1 C / 0 F."""
+    Sp, Sj, Tp, Tj = (np.ascontiguousarray(v, np.intc) for v in (Sp, Sj, Tp, Tj))
+    if splitting.dtype != np.intc or not splitting.flags.c_contiguous:
+        raise TypeError('splitting must be a contiguous int32 numpy array')
+    lib = _lib.load()
+    rc = lib.b200amg_rs_cf_splitting_host(int(n_nodes), Sp.ctypes.data, Sj.ctypes.data, Tp.ctypes.data, Tj.ctypes.data,
+                                          splitting.ctypes.data)
+    if rc != 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())

@@ -81,3 +81,79 @@ extern "C" int b200amg_standard_aggregation_host(int n, const int *Ap, const int
     }
     return nagg;
 }
+
+// Ruge-Stuben first-pass C/F splitting (amg_core.rs_cf_splitting, pyamg/amg_core/ruge_stuben.h:157-297).
+// S = strength graph without diagonal, T = S^T, both CSR on the HOST; split[i] = 1 (C) or 0 (F).
+//
+// The selection order between nodes of equal measure is defined by the reference's bucket array (nodes
+// ordered by measure; raising a node moves it to the far end of its bucket and hands that slot to the
+// next bucket, lowering moves it to the near end), so the same mechanics are kept -- including that
+// bucket starts exist only for measures < n, that a measure >= n-1 is never raised and 0 never lowered.
+namespace {
+struct MeasureBuckets {
+    std::vector<int> measure, start, size, node_at, slot_of;
+    explicit MeasureBuckets(int n) : measure(n + 1, 0), start(n + 1, 0), size(n + 1, 0), node_at(n + 1, 0), slot_of(n + 1, 0) {}
+    void exchange(int a, int b)
+    {
+        const int na = node_at[a], nb = node_at[b];
+        node_at[a] = nb; slot_of[nb] = a;
+        node_at[b] = na; slot_of[na] = b;
+    }
+    void raise(int k)
+    {
+        const int m = measure[k], last = start[m] + size[m] - 1;
+        exchange(slot_of[k], last);
+        --size[m]; ++size[m + 1];
+        start[m + 1] = last;
+        measure[k] = m + 1;
+    }
+    void lower(int k)
+    {
+        const int m = measure[k];
+        exchange(slot_of[k], start[m]);
+        --size[m]; ++size[m - 1];
+        ++start[m];
+        start[m - 1] = start[m] - size[m - 1];
+        measure[k] = m - 1;
+    }
+};
+}  // namespace
+
+extern "C" int b200amg_rs_cf_splitting_host(int n, const int *Sp, const int *Sj, const int *Tp, const int *Tj, int *split)
+{
+    if (n < 0) return set_err(B200AMG_EINVAL, "rs_cf_splitting: n < 0");
+    enum : int { F_PT = 0, C_PT = 1, OPEN = 2 };
+    MeasureBuckets B(n);
+    for (int i = 0; i < n; ++i) ++B.size[B.measure[i] = Tp[i + 1] - Tp[i]];
+    for (int v = 0, run = 0; v < n; ++v) { B.start[v] = run; run += B.size[v]; B.size[v] = 0; }
+    for (int i = 0; i < n; ++i) {
+        const int m = B.measure[i], at = B.start[m] + B.size[m]++;
+        B.node_at[at] = i;
+        B.slot_of[i] = at;
+    }
+    // nobody depends on the node (or only itself): F point from the start
+    for (int i = 0; i < n; ++i) {
+        const int m = B.measure[i];
+        split[i] = (m == 0 || (m == 1 && Tj[Tp[i]] == i)) ? F_PT : OPEN;
+    }
+    for (int top = n - 1; top >= 0; --top) {
+        const int c = B.node_at[top];
+        --B.size[B.measure[c]];
+        if (split[c] == F_PT) continue;
+        split[c] = C_PT;
+        for (int p = Tp[c]; p < Tp[c + 1]; ++p) {           // undecided nodes that depend on c become F ...
+            const int f = Tj[p];
+            if (split[f] != OPEN) continue;
+            split[f] = F_PT;
+            for (int q = Sp[f]; q < Sp[f + 1]; ++q) {       // ... and what they depend on gets more attractive
+                const int k = Sj[q];
+                if (split[k] == OPEN && B.measure[k] < n - 1) B.raise(k);
+            }
+        }
+        for (int p = Sp[c]; p < Sp[c + 1]; ++p) {           // what c depends on loses one potential dependant
+            const int j = Sj[p];
+            if (split[j] == OPEN && B.measure[j] != 0) B.lower(j);
+        }
+    }
+    return 0;
+}

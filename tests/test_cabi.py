@@ -66,6 +66,33 @@ def test_host_setup_functions_equal_oracle():
     assert np.array_equal(a, a2)
 
 
+def test_host_rs_splitting_equals_oracle():
+    """b200amg_rs_cf_splitting_host == the C restatement (itself pinned against the reference .so) on random
+    graphs, grids and directed (non-symmetric) strength graphs"""
+    from pyamg_b200 import amg_core
+    from oracle import rs as ors
+    rng = np.random.RandomState(4)
+    mats = []
+    for trial in range(50):
+        n = rng.randint(1, 120)
+        G = sp.random(n, n, rng.uniform(0.01, 0.25), random_state=rng, format='csr')
+        mats.append(sp.csr_matrix(G + G.T) if trial % 3 else sp.csr_matrix(G))
+    from helpers_mats import poisson3d
+    mats.append(poisson3d(9))
+    g = 31
+    T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(g, g))
+    mats.append(sp.csr_matrix(sp.kron(T, sp.eye(g)) + sp.kron(sp.eye(g), T)))
+    for G in mats:
+        S = ors.remove_diagonal(sp.csr_matrix(G))
+        Tt = S.T.tocsr()
+        n = S.shape[0]
+        a, b = np.empty(n, np.intc), np.empty(n, np.intc)
+        args = [np.ascontiguousarray(v, np.intc) for v in (S.indptr, S.indices, Tt.indptr, Tt.indices)]
+        amg_core.rs_cf_splitting(n, *args, a)
+        oracle.port.rs_cf_splitting(n, *args, b)
+        assert np.array_equal(a, b)
+
+
 def test_product_never_imports_oracle():
     bad = []
     for d, _, files in os.walk(os.path.join(ROOT, 'pyamg_b200')):
