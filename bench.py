@@ -33,8 +33,12 @@ def parse():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--grid', type=int, default=int(os.environ.get('B200AMG_GRID', '256')),
-                    help='grid points per dimension (BASELINE config: 256)')
+    ap.add_argument('--config', type=int, default=2, choices=[2, 3],
+                    help='BASELINE.json configs[] entry (1-based as in SURVEY 8d): 2 = 3D Poisson 256^3 SA + Jacobi (the headline, '
+                         'default); 3 = 2D rotated anisotropic diffusion 4000^2, classical RS + symmetric multicolour Gauss-Seidel '
+                         '(an extra measurement, single GPU)')
+    ap.add_argument('--grid', type=int, default=int(os.environ.get('B200AMG_GRID', '0')),
+                    help='grid points per dimension (default: 256 for config 2, 4000 for config 3)')
     ap.add_argument('--cpu-cycles', type=int, default=3, help='V-cycles of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--smoother', default='jacobi', choices=['jacobi', 'mcgs'],
@@ -43,7 +47,12 @@ def parse():
     ap.add_argument('--no-graph', action='store_true', help='N > 1: drive the distributed cycle from Python instead of one CUDA graph per rank')
     ap.add_argument('--agglomerate-below', type=int, default=500000,
                     help='N > 1: levels with fewer global rows than this run on rank 0 only')
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.grid <= 0:
+        args.grid = 256 if args.config == 2 else 4000
+    if args.config == 3:
+        args.smoother = 'mcgs'
+    return args
 
 
 # ---------------------------------------------------------------------------------------------
@@ -121,17 +130,27 @@ def jacobi_bytes(n, nnz, layout=1):
     return matrix_bytes(n, nnz, layout) + 24 * n
 
 
+def gs_sweep_bytes(n, nnz):
+    """algorithmic bytes of ONE colour-ordered Gauss-Seidel sweep over all colours: B_spmv (A once, x gathered
+    once, x written) + b (8n) + the index list Id (4n)"""
+    return 12 * nnz + 4 * (n + 1) + 8 * n + 8 * n + 8 * n + 4 * n
+
+
 def spmv_bytes(n_row, n_col, nnz):
     return 12 * nnz + 4 * (n_row + 1) + 8 * n_col + 8 * n_row
 
 
-def vcycle_bytes(ml):
-    """unfused algorithmic bytes of one V(1,1)-cycle (SURVEY 8d formula) over the hierarchy"""
+def vcycle_bytes(ml, gs_sweeps=0):
+    """unfused algorithmic bytes of one V(1,1)-cycle (SURVEY 8d formula) over the hierarchy; gs_sweeps > 0: the
+    smoothers are colour-ordered Gauss-Seidel with that many sweeps per smoothing step (2 = symmetric)"""
     tot = 0
     for lvl in ml.levels[:-1]:
         n, nnz = lvl.A.shape[0], lvl.A.nnz
         nc = lvl.P.shape[1]
-        tot += 3 * (12 * nnz + 4 * n + 24 * n)
+        if gs_sweeps:
+            tot += 2 * gs_sweeps * gs_sweep_bytes(n, nnz) + (12 * nnz + 4 * n + 24 * n)
+        else:
+            tot += 3 * (12 * nnz + 4 * n + 24 * n)
         tot += 12 * lvl.R.nnz + 4 * nc + 8 * n + 8 * nc
         tot += 12 * lvl.P.nnz + 4 * n + 8 * nc + 16 * n
     tot += 8 * ml.levels[-1].A.shape[0] ** 2
@@ -147,10 +166,18 @@ def host_levels(ml):
         h.A = lvl.A.to_scipy()
         if hasattr(lvl, 'P'):
             h.P, h.R = lvl.P.to_scipy(), lvl.R.to_scipy()
-            h.pre = ('jacobi', {'omega': lvl.presmoother.omega, 'iterations': lvl.presmoother.iterations})
-            h.post = ('jacobi', {'omega': lvl.postsmoother.omega, 'iterations': lvl.postsmoother.iterations})
+            h.pre, h.post = host_spec(lvl.presmoother), host_spec(lvl.postsmoother)
         out.append(h)
     return out
+
+
+def host_spec(sm):
+    """resolved device smoother -> the oracle's spec for the same sweep"""
+    if sm.kind == 1:
+        return ('jacobi', {'omega': sm.omega, 'iterations': sm.iterations})
+    if sm.kind == 2:
+        return ('gauss_seidel_indexed', {'indices': sm.indices.cpu().numpy(), 'sweep': sm.sweep, 'iterations': sm.iterations})
+    raise SystemExit('bench: smoother kind %r has no CPU-baseline spec' % (sm.kind,))
 
 
 def time_cpu_cycles(levels, b, cycles, warm=0):
@@ -203,6 +230,38 @@ def build_problem(grid, slabs=1):
     return ml, b
 
 
+def build_problem_rs(grid):
+    """config 3 of BASELINE.json: stencil_grid(diffusion_stencil_2d(epsilon=0.001, theta=pi/8, 'FE'), (g,g)) +
+    ruge_stuben_solver(max_coarse=500) with symmetric multicolour Gauss-Seidel (gauss_seidel_indexed over the MIS colour
+    ordering) on every level, all built on the device / its host helpers by pyamg_b200"""
+    import pyamg_b200 as amg
+    st = amg.gallery.diffusion_stencil_2d(epsilon=0.001, theta=np.pi / 8, type='FE')
+    A = amg.gallery.stencil_grid(st, (grid, grid))
+    np.random.seed(0)
+    mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+    ml = amg.ruge_stuben_solver(A, max_coarse=500, presmoother=mc, postsmoother=mc)
+    b = np.random.rand(A.shape[0])
+    return ml, b
+
+
+def workload_name(args):
+    if args.config == 3:
+        return ('configs[2]: 2D rotated anisotropic diffusion %dx%d (eps=0.001, theta=pi/8, FE 9-point), ruge_stuben_solver '
+                '(classical strength 0.25, RS splitting, direct interpolation, max_coarse=500), symmetric multicolour '
+                'Gauss-Seidel pre/post (gauss_seidel_indexed over MIS colours), fp64, one V(1,1)-cycle per step'
+                % (args.grid, args.grid))
+    return ('configs[1]: 3D Poisson %d^3 7-point, smoothed_aggregation_solver, %s pre/post, max_coarse=500, fp64, one '
+            'V(1,1)-cycle per step' % (args.grid, 'Jacobi(4/3)' if args.smoother == 'jacobi' else
+                                       'symmetric multicolour Gauss-Seidel'))
+
+
+def metric_name(args):
+    if args.config == 3:
+        return 'V-cycles/sec, 2D rotated anisotropic diffusion %d^2 RS (symmetric multicolour Gauss-Seidel), V(1,1)' % args.grid
+    return 'V-cycles/sec, 3D Poisson %d^3 SA (%s), V(1,1)' % (args.grid, 'Jacobi 4/3' if args.smoother == 'jacobi' else
+                                                               'symmetric multicolour Gauss-Seidel')
+
+
 def level_table(ml):
     return [[int(l.A.shape[0]), int(l.A.nnz)] for l in ml.levels]
 
@@ -236,10 +295,13 @@ def run_b200(args):
     import pyamg_b200 as amg
 
     t0 = time.perf_counter()
-    ml, b = build_problem(args.grid)
-    if args.smoother == 'mcgs':
-        mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
-        amg.change_smoothers(ml, mc, mc)
+    if args.config == 3:
+        ml, b = build_problem_rs(args.grid)
+    else:
+        ml, b = build_problem(args.grid)
+        if args.smoother == 'mcgs':
+            mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+            amg.change_smoothers(ml, mc, mc)
     torch.cuda.synchronize()
     setup_s = time.perf_counter() - t0
     n = b.size
@@ -489,12 +551,30 @@ def measure_roofline(R, reps=5):
     share = {('%s@L%d' % k): round(float(np.mean(v)), 4) for k, v in acc.items()}
     A0 = ml.levels[0].A
     lay = ml.layouts()[0]['A']
+    peak, how = measured_peak()
+    t_r = float(np.mean(acc[('residual', 0)]))
+    res_bytes = jacobi_bytes(A0.shape[0], A0.nnz, lay)
+    sm0 = ml.levels[0].presmoother
+    if sm0.kind == 2:
+        # colour-ordered Gauss-Seidel: the unit is ONE sweep over all K colours (K launches of sell_gs_kernel on the
+        # colour-grouped sliced-ELL copy of A); a symmetric smoothing step is two sweeps
+        sweeps = 2 if sm0.sweep == 'symmetric' else 1
+        K = int(len(sm0.color_ptr) - 1)
+        t_s = float(np.mean(acc[('presmooth', 0)] + acc[('postsmooth', 0)])) / (sweeps * sm0.iterations)
+        nB = gs_sweep_bytes(A0.shape[0], A0.nnz)
+        ach = nB / (t_s * 1e-3) / 1e9
+        return {'bound': 'hbm', 'kernel': 'sell_gs_kernel level 0: one colour-ordered Gauss-Seidel sweep = %d launches '
+                                          '(one per MIS colour) over the colour-grouped sliced-ELL copy of A' % K,
+                'achieved': round(ach, 1), 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': round(ach / peak, 4),
+                'algorithmic_bytes_per_launch': nB // K, 'algorithmic_bytes_per_sweep': nB, 'launches_per_sweep': K,
+                'ms_per_launch': round(t_s / K, 4), 'ms_per_sweep': round(t_s, 4), 'traffic': None,
+                'residual_L0_layout': LAYOUT_NAME.get(lay, str(lay)),
+                'residual_L0_GBs': round(res_bytes / (t_r * 1e-3) / 1e9, 1),
+                'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
     nB = jacobi_bytes(A0.shape[0], A0.nnz, lay)
     nB_csr = jacobi_bytes(A0.shape[0], A0.nnz)
     t_j = float(np.mean(acc[('presmooth', 0)] + acc[('postsmooth', 0)]))     # ms per launch
-    peak, how = measured_peak()
     ach = nB / (t_j * 1e-3) / 1e9
-    t_r = float(np.mean(acc[('residual', 0)]))
     traffic = None
     try:        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
         tj = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))
@@ -502,7 +582,6 @@ def measure_roofline(R, reps=5):
             traffic = tj['dram_bytes_per_launch']
     except Exception:
         traffic = None
-    res_bytes = jacobi_bytes(A0.shape[0], A0.nnz, lay)
     kname = {5: 'rowpat_kernel<OP_JACOBI>', 2: 'sell_kernel<OP_JACOBI>'}.get(lay, 'csr_pipe_kernel<OP_JACOBI>')
     return {'bound': 'hbm', 'kernel': kname + ' level 0 (pre- and post-smoothing sweep)',
             'layout': LAYOUT_NAME.get(lay, str(lay)),
@@ -524,10 +603,45 @@ def cpu_baseline(R, args):
     err = float(np.max(np.abs(x_gpu - x_cpu)) / max(np.max(np.abs(x_cpu)), 1e-300))
     return ({'value': 1.0 / sec, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(), 'kind': kind,
              'sample': '%d full V(1,1)-cycles of the same %d-level hierarchy after 1 warm-up cycle; serial '
-                       'reference code (scipy csr/bsr_matvec + amg_core jacobi), incl. the fork\'s second '
-                       'P*coarse_x per level (multilevel.py:548)' % (args.cpu_cycles, len(levels)),
+                       'reference code (scipy csr/bsr_matvec + amg_core %s), incl. the fork\'s second '
+                       'P*coarse_x per level (multilevel.py:548)'
+                       % (args.cpu_cycles, len(levels), 'jacobi' if args.smoother == 'jacobi' else 'gauss_seidel_indexed'),
              's_per_cycle': sec},
             {'cycles': 1 + args.cpu_cycles, 'max_rel_diff_x_vs_cpu_reference': err, 'bit_identical': bool(np.array_equal(x_gpu, x_cpu))})
+
+
+def cpu_problem_rs(grid):
+    """config 3 without a GPU: the anisotropic FE stencil matrix, oracle/rs.py hierarchy, MIS colour orderings"""
+    import oracle
+    from oracle import rs as ors, relaxation as orx
+    import scipy.sparse as sp
+    eps, th = 0.001, np.pi / 8                                # pyamg/gallery/diffusion.py FE stencil
+    C, S = np.cos(th), np.sin(th)
+    CS, CC, SS = C * S, C * C, S * S
+    a = (-1 * eps - 1) * CC + (-1 * eps - 1) * SS + (3 * eps - 3) * CS
+    b_ = (2 * eps - 4) * CC + (-4 * eps + 2) * SS
+    c = (-1 * eps - 1) * CC + (-1 * eps - 1) * SS + (-3 * eps + 3) * CS
+    d = (-4 * eps + 2) * CC + (2 * eps - 4) * SS
+    e = (8 * eps + 8) * CC + (8 * eps + 8) * SS
+    st = np.array([[a, b_, c], [d, e, d], [c, b_, a]]) / 6.0
+    g = grid
+    diags, offs = [], []
+    for di in (-1, 0, 1):
+        for dj in (-1, 0, 1):
+            v = np.full(g * g, st[di + 1, dj + 1])
+            jj = np.arange(g * g) % g
+            v[(jj + dj < 0) | (jj + dj >= g)] = 0.0
+            off = di * g + dj
+            diags.append(v[max(0, -off):g * g - max(0, off)])
+            offs.append(off)
+    A = sp.diags(diags, offs, shape=(g * g, g * g), format='csr')
+    A.eliminate_zeros(); A.sort_indices()
+    np.random.seed(0)
+    levels = ors.ruge_stuben_hierarchy(A, max_coarse=500, core=oracle.core)
+    for lvl in levels[:-1]:
+        idx, _ = orx.color_ordering(orx.vertex_coloring_mis(lvl.A, oracle.core))
+        lvl.pre = lvl.post = ('gauss_seidel_indexed', {'indices': idx, 'sweep': 'symmetric', 'iterations': 1})
+    return levels, np.random.rand(A.shape[0])
 
 
 def run_reference(args):
@@ -547,7 +661,7 @@ def run_reference(args):
     try:
         import torch
         if torch.cuda.is_available():
-            ml, b = build_problem(args.grid)
+            ml, b = build_problem_rs(args.grid) if args.config == 3 else build_problem(args.grid)
             levels = host_levels(ml)
             how = 'device setup (pyamg_b200), downloaded to the host'
             del ml
@@ -555,6 +669,9 @@ def run_reference(args):
     except Exception as exc:                                           # noqa: BLE001
         how = None
         sys.stderr.write('reference arm: device setup unavailable (%s); CPU setup\n' % (exc,))
+    if how is None and args.config == 3:
+        levels, b = cpu_problem_rs(args.grid)
+        how = 'CPU setup (oracle/rs.py)'
     if how is None:
         from oracle import sa
         import scipy.sparse as sp
@@ -585,12 +702,11 @@ def run_reference(args):
     val = 1.0 / sec
     sample = ('%d of the %d requested V(1,1)-cycles timed (%d warm-up), each a full cycle over the %d-level '
               'hierarchy of poisson(%d^3); hierarchy from: %s' % (timed, args.steps, warm_done, len(levels), args.grid, how))
-    out = {'impl': 'reference', 'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1)' % args.grid,
+    out = {'impl': 'reference', 'metric': metric_name(args),
            'value': val, 'unit': 'V-cycles/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
            'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
            'dtype': 'f64', 'data': 'synthetic',
-           'config': {'workload': 'configs[1]: 3D Poisson %d^3 7-point, smoothed_aggregation_solver, Jacobi(4/3) pre/post, '
-                                  'max_coarse=500, fp64, one V(1,1)-cycle per step' % args.grid,
+           'config': {'workload': workload_name(args),
                       'levels': [[int(l.A.shape[0]), int(l.A.nnz)] for l in levels]},
            'cpu_baseline': {'value': val, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(),
                             'kind': oracle.kind, 'sample': sample},
@@ -612,7 +728,7 @@ def main():
         run_distributed(args)
         return
     R = run_b200(args)
-    if args.smoother != 'jacobi':
+    if args.smoother != 'jacobi' and args.config == 2:
         args.no_cpu_baseline = True
     e2e = measure_e2e(R, args)
     roof = measure_roofline(R) if R['rank'] == 0 else None
@@ -625,17 +741,17 @@ def main():
     if R['rank'] != 0:
         return
     ml = R['ml']
-    vb = vcycle_bytes(ml)
-    out = {'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (%s), V(1,1)' % (args.grid, 'Jacobi 4/3' if args.smoother == 'jacobi' else
-                                                                       'symmetric multicolour Gauss-Seidel'),
+    vb = vcycle_bytes(ml, 2 if args.smoother == 'mcgs' else 0)
+    out = {'metric': metric_name(args),
            'value': R['value'], 'unit': 'V-cycles/s', 'n_gpus': R['world'], 'steps': args.steps,
            'warmup': args.warmup, 'ms_per_step': R['ms_step'], 'higher_is_better': True, 'scaling': 'weak',
            'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-           'config': {'workload': 'configs[1]: 3D Poisson %d^3 7-point, smoothed_aggregation_solver, Jacobi(4/3) pre/post, '
-                                  'max_coarse=500, fp64, one V(1,1)-cycle per step' % args.grid,
+           'config': {'workload': workload_name(args),
                       'levels': level_table(ml), 'parallelism': 'single GPU' if R['world'] == 1 else
                       'replicas: %d independent solves, one per GPU' % R['world'],
                       'l2': 'inputs larger than L2 (level-0 CSR alone is %.2f GB)' % (12e-9 * ml.levels[0].A.nnz),
+                      'colours_per_level': ([int(len(l.presmoother.color_ptr) - 1) for l in ml.levels[:-1]]
+                                            if args.smoother == 'mcgs' else None),
                       'setup_s_device': round(R['setup_s'], 2),
                       'unfused_algorithmic_bytes_per_cycle': vb,
                       'cycle_GBs_on_unfused_bytes': round(vb / (R['ms_step'] * 1e-3) / 1e9, 1)},

@@ -250,19 +250,51 @@ struct RowPatArgs {
     double alpha, beta, omega;
 };
 
+// The table sits in shared memory as structure of arrays -- 8 column offsets (32 B), 8 values (64 B) and one
+// meta word per pattern -- so a row's offsets come with two 128-bit loads and its values with four, instead of
+// two loads per entry; gather addresses are formed from the 32-bit column number (one add + one wide
+// multiply-add per entry).  Padding slots hold offset 0 / value 0.
+struct RowPatSmem {
+    const int *off;        // [npat * 8]
+    const double *val;     // [npat * 8]
+    const int *meta;       // [npat]: len | diagonal mask << 8
+};
+
+template <int LEN>
+__device__ __forceinline__ void rp_load_offsets(const int *po, int (&off)[RP_LEN])
+{
+    const int4 a = *reinterpret_cast<const int4 *>(po);
+    off[0] = a.x; off[1] = a.y; off[2] = a.z; off[3] = a.w;
+    if (LEN > 4) {
+        const int4 c = *reinterpret_cast<const int4 *>(po + 4);
+        off[4] = c.x; off[5] = c.y; off[6] = c.z; off[7] = c.w;
+    }
+}
+
+template <int LEN>
+__device__ __forceinline__ void rp_load_values(const double *pv, double (&vv)[RP_LEN])
+{
+#pragma unroll
+    for (int q = 0; q < LEN; q += 2) {
+        const double2 t = *reinterpret_cast<const double2 *>(pv + q);
+        vv[q] = t.x;
+        vv[q + 1] = t.y;
+    }
+}
+
 // ordered fold of a row of exactly LEN entries: all gathers in flight first, then the storage-order sum
 template <int OP, int LEN>
-__device__ __forceinline__ double rp_fold_fixed(const RowPatEntry *p, const double *__restrict__ xr, unsigned dm, double acc)
+__device__ __forceinline__ double rp_fold_fixed(const int *po, const double *pv, const double *__restrict__ xg, int row,
+                                                unsigned dm, double acc)
 {
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
-    double vv[LEN], xv[LEN];
+    int off[RP_LEN];
+    double vv[RP_LEN], xv[RP_LEN];
+    rp_load_offsets<LEN>(po, off);
 #pragma unroll
-    for (int q = 0; q < LEN; ++q) {
-        const RowPatEntry en = p[q];
-        vv[q] = en.v;
-        xv[q] = __ldg(xr + en.off);
-    }
+    for (int q = 0; q < LEN; ++q) xv[q] = __ldg(xg + (row + off[q]));
+    rp_load_values<LEN>(pv, vv);
 #pragma unroll
     for (int q = 0; q < LEN; ++q) {
         // a diagonal slot contributes +0.0 instead of being skipped: acc + 0.0 == acc bit for bit (acc is never
@@ -277,19 +309,18 @@ __device__ __forceinline__ double rp_fold_fixed(const RowPatEntry *p, const doub
 
 // rows of different lengths in one warp (grid boundaries): every slot predicated on q < len
 template <int OP>
-__device__ __forceinline__ double rp_fold_mixed(const RowPatEntry *p, const double *__restrict__ xr, unsigned dm, int len,
-                                                double acc)
+__device__ __forceinline__ double rp_fold_mixed(const int *po, const double *pv, const double *__restrict__ xg, int row,
+                                                unsigned dm, int len, double acc)
 {
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
+    int off[RP_LEN];
     double vv[RP_LEN], xv[RP_LEN];
+    rp_load_offsets<RP_LEN>(po, off);
 #pragma unroll
     for (int q = 0; q < RP_LEN; ++q)
-        if (q < len) {
-            const RowPatEntry en = p[q];
-            vv[q] = en.v;
-            xv[q] = __ldg(xr + en.off);
-        }
+        if (q < len) xv[q] = __ldg(xg + (row + off[q]));
+    rp_load_values<RP_LEN>(pv, vv);
 #pragma unroll
     for (int q = 0; q < RP_LEN; ++q)
         if (q < len) {
@@ -307,8 +338,15 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
     constexpr bool NEED_Y = (OP == OP_ADD);
     extern __shared__ __align__(16) unsigned char rp_smem[];
-    RowPatEntry *tab = reinterpret_cast<RowPatEntry *>(rp_smem);
-    for (int i = threadIdx.x; i < a.npat * RP_LEN; i += RP_TPB) tab[i] = a.table[i];
+    int *s_off = reinterpret_cast<int *>(rp_smem);
+    double *s_val = reinterpret_cast<double *>(rp_smem + (size_t)a.npat * RP_LEN * sizeof(int));
+    int *s_meta = reinterpret_cast<int *>(rp_smem + (size_t)a.npat * RP_LEN * (sizeof(int) + sizeof(double)));
+    for (int i = threadIdx.x; i < a.npat * RP_LEN; i += RP_TPB) {
+        const RowPatEntry en = a.table[i];
+        s_off[i] = en.off;
+        s_val[i] = en.v;
+        if ((i & (RP_LEN - 1)) == 0) s_meta[i / RP_LEN] = en.len;
+    }
     __syncthreads();
     const double *__restrict__ xg = a.x;
     const int n_chunks = (a.n + RP_CHUNK - 1) / RP_CHUNK;
@@ -347,17 +385,18 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
                 }
             }
 #endif
-            const RowPatEntry *p = tab;
+            const int *po = s_off;
+            const double *pv = s_val;
             double bi = 0.0, xi = 0.0, yi = 0.0;
             int len = 0;
             unsigned dm = 0;
-            const double *xr = xg + row;
             if (live) {
-                p = tab + code * RP_LEN;
+                po = s_off + code * RP_LEN;
+                pv = s_val + code * RP_LEN;
                 if (NEED_B) bi = __ldg(a.b + row);
-                if (SMOOTH) xi = __ldg(xr);
+                if (SMOOTH) xi = __ldg(xg + row);
                 if (NEED_Y) yi = a.y[row];
-                const int meta = p[0].len;
+                const int meta = s_meta[code];
                 len = meta & 0xff;
                 dm = (unsigned)meta >> 8;
             }
@@ -367,22 +406,22 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
             const int l0 = __shfl_sync(0xffffffffu, len, 0);
             if (__all_sync(0xffffffffu, len == l0)) {
                 switch (l0) {
-                case 1: acc = rp_fold_fixed<OP, 1>(p, xr, dm, acc); break;
-                case 2: acc = rp_fold_fixed<OP, 2>(p, xr, dm, acc); break;
-                case 3: acc = rp_fold_fixed<OP, 3>(p, xr, dm, acc); break;
-                case 4: acc = rp_fold_fixed<OP, 4>(p, xr, dm, acc); break;
-                case 5: acc = rp_fold_fixed<OP, 5>(p, xr, dm, acc); break;
-                case 6: acc = rp_fold_fixed<OP, 6>(p, xr, dm, acc); break;
-                case 7: acc = rp_fold_fixed<OP, 7>(p, xr, dm, acc); break;
-                case 8: acc = rp_fold_fixed<OP, 8>(p, xr, dm, acc); break;
+                case 1: acc = rp_fold_fixed<OP, 1>(po, pv, xg, row, dm, acc); break;
+                case 2: acc = rp_fold_fixed<OP, 2>(po, pv, xg, row, dm, acc); break;
+                case 3: acc = rp_fold_fixed<OP, 3>(po, pv, xg, row, dm, acc); break;
+                case 4: acc = rp_fold_fixed<OP, 4>(po, pv, xg, row, dm, acc); break;
+                case 5: acc = rp_fold_fixed<OP, 5>(po, pv, xg, row, dm, acc); break;
+                case 6: acc = rp_fold_fixed<OP, 6>(po, pv, xg, row, dm, acc); break;
+                case 7: acc = rp_fold_fixed<OP, 7>(po, pv, xg, row, dm, acc); break;
+                case 8: acc = rp_fold_fixed<OP, 8>(po, pv, xg, row, dm, acc); break;
                 default: break;
                 }
             } else {
-                acc = rp_fold_mixed<OP>(p, xr, dm, len, acc);
+                acc = rp_fold_mixed<OP>(po, pv, xg, row, dm, len, acc);
             }
             if (!live) continue;
             double diag = 0.0;
-            if (SMOOTH && dm) diag = p[31 - __clz(dm)].v;            // last stored diagonal wins
+            if (SMOOTH && dm) diag = pv[31 - __clz(dm)];            // last stored diagonal wins
             double *y = a.y;
             if (OP == OP_MATVEC) {
                 y[row] = acc;
@@ -416,7 +455,7 @@ static int launch_rowpat(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     const int n_chunks = (r.n + RP_CHUNK - 1) / RP_CHUNK;
     const int grid = std::min(n_chunks, sms * RP_CTAS_PER_SM);
     RowPatArgs a{r.n, r.npat, r.far, r.codes, r.table, s.x, s.b, s.y, s.alpha, s.beta, s.omega};
-    rowpat_kernel<OP><<<grid, RP_TPB, sizeof(RowPatEntry) * RP_LEN * r.npat, st>>>(a);
+    rowpat_kernel<OP><<<grid, RP_TPB, ((sizeof(int) + sizeof(double)) * RP_LEN + sizeof(int)) * r.npat + 16, st>>>(a);
     return check_launch("rowpat_kernel");
 }
 
