@@ -199,7 +199,13 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
             std::vector<RowPatEntry> ht((size_t)RP_LEN * npat);
             e = cudaMemcpy(ht.data(), table, sizeof(RowPatEntry) * ht.size(), cudaMemcpyDeviceToHost);
             good = e == cudaSuccess;
-            for (const RowPatEntry &en : ht) out->far = std::max(out->far, en.off);
+            // prefetch distance = farthest neighbour of a TYPICAL row (the row in the middle of the matrix), not of
+            // any row: on a row slab of a partitioned operator the boundary planes reach into the halo region
+            // (offset ~ n), and prefetching "row + n" from every row hammers one clamped address
+            unsigned char mid = 0;
+            if (good) good = cudaMemcpy(&mid, codes + n_row / 2, 1, cudaMemcpyDeviceToHost) == cudaSuccess;
+            if (good && mid < npat)
+                for (int q = 0; q < RP_LEN; ++q) out->far = std::max(out->far, ht[(size_t)mid * RP_LEN + q].off);
         }
         if (good) {
             out->codes = codes;
@@ -381,7 +387,7 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
                 if (rp >= 0) {
                     if (NEED_B) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.b + rp));
                     if (NEED_Y) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.y + rp));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + min(rp + far, a.n - 1)));
+                    if (rp + far < a.n) asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + (rp + far)));
                 }
             }
 #endif
