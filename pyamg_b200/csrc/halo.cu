@@ -45,9 +45,12 @@ __global__ void __launch_bounds__(256) halo_push_kernel(const double *__restrict
         double *dst = reinterpret_cast<double *>(bases[dst_rank[j]]) + dst_off[j];
         *dst = v[send_idx[j]];
     }
-    __threadfence_system();
+    // one system-scope fence per CTA, by the thread that goes on to signal: the barrier orders the CTA's peer stores
+    // before it and the fence is cumulative (the grid-sync pattern) -- a fence per thread made every thread wait for
+    // its own NVLink round trip
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence_system();
         const unsigned prev = atomicAdd(&state[1], 1u);
         if (prev == gridDim.x - 1) {                    // last CTA: every CTA's stores are fenced
             state[1] = 0;
