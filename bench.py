@@ -45,7 +45,7 @@ def parse():
                     help='jacobi: the BASELINE headline config; mcgs: same hierarchy with symmetric multicolour Gauss-Seidel '
                          '(gauss_seidel_indexed over MIS colours) pre/post -- an extra, non-headline measurement')
     ap.add_argument('--no-graph', action='store_true', help='N > 1: drive the distributed cycle from Python instead of one CUDA graph per rank')
-    ap.add_argument('--agglomerate-below', type=int, default=500000,
+    ap.add_argument('--agglomerate-below', type=int, default=100000,
                     help='N > 1: levels with fewer global rows than this run on rank 0 only')
     args = ap.parse_args()
     if args.grid <= 0:

@@ -137,7 +137,7 @@ class DistributedSolver:
             return sub
         return cls(describe(ml), coarse, **kw)
 
-    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=500000, backend=None, device=None,
+    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=100000, backend=None, device=None,
                  halo='auto'):
         self.group = group
         self.rank, self.G = dist.get_rank(group), dist.get_world_size(group)
