@@ -110,15 +110,72 @@ __device__ __forceinline__ void bsr_gs_block_row(int i, const int *__restrict__ 
     }
 }
 
+// One colour of block rows, BS lanes per block row (lane k owns scalar row k of the block row; 32 / BS block rows
+// per warp).  Off-diagonal blocks: lane k folds row k of every block exactly like the one-thread form above (the
+// BS lanes of a group read the BS*BS doubles of a block as one contiguous piece).  Diagonal block: the point
+// sweep is sequential in k, so step kq is done by the lane that owns row k and its result is handed to the
+// group by a shuffle before the next step -- the order and the bits of bsr_gs_block_row, with BS times the
+// threads in flight (thread-per-block-row reached 0.41-0.53 of HBM peak, profiles/r01b/kernels_roofline.json).
 template <int BS>
 __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                            const double *__restrict__ Ax, double *x,
                                                            const double *__restrict__ b, const int *__restrict__ Id,
                                                            int p0, int p1, bool backward)
 {
-    const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= p1) return;
-    bsr_gs_block_row<BS>(Id[p], Ap, Aj, Ax, x, b, backward);
+    constexpr int RPW = 32 / BS;                        // block rows per warp
+    const int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int g = lane / BS, k = lane - g * BS;
+    const int p = p0 + warp * RPW + g;
+    const bool active = g < RPW && p < p1;
+    const int i = active ? Id[p] : 0;
+    double acc = 0.0;
+    long long dptr = -1;
+    if (active) {
+        acc = b[(size_t)i * BS + k];
+        const int hi = Ap[i + 1];
+        for (int q = Ap[i]; q < hi; ++q) {
+            const int j = Aj[q];
+            if (j == i) { dptr = q; continue; }
+            const double *blk = Ax + ((size_t)q * BS + k) * BS;
+            const double *xb = x + (size_t)j * BS;
+            double loc = 0.0;
+#pragma unroll
+            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[c], xb[c]));
+            acc = sub_rn(acc, loc);
+        }
+    }
+    const bool has_diag = active && dptr >= 0;
+    double xl[BS], Dk[BS];
+#pragma unroll
+    for (int c = 0; c < BS; ++c) {
+        xl[c] = has_diag ? x[(size_t)i * BS + c] : 0.0;
+        Dk[c] = has_diag ? Ax[((size_t)dptr * BS + k) * BS + c] : 0.0;
+    }
+#pragma unroll
+    for (int kq = 0; kq < BS; ++kq) {
+        const int kk0 = backward ? BS - 1 - kq : kq;     // the scalar row relaxed in this step
+        double nv = 0.0;
+        bool wrote = false;
+        if (has_diag && k == kk0) {
+            double d = 1.0, a = acc;
+#pragma unroll
+            for (int cq = 0; cq < BS; ++cq) {
+                const int kk = backward ? BS - 1 - cq : cq;
+                if (kk == kk0) d = Dk[kk];
+                else a = sub_rn(a, mul_rn(Dk[kk], xl[kk]));
+            }
+            if (d != 0.0) {
+                nv = div_rn(a, d);
+                wrote = true;
+                x[(size_t)i * BS + kk0] = nv;
+            }
+        }
+        // hand the new value (or the unchanged one) to the other lanes of the group
+        const int src = g * BS + kk0;
+        const double cur = wrote ? nv : xl[kk0];
+        const double got = __shfl_sync(0xffffffffu, cur, src < 32 ? src : 0);
+        if (has_diag) xl[kk0] = got;
+    }
 }
 
 template <int BS>
@@ -169,7 +226,8 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
                  const int *Id, int p0, int p1, bool backward, cudaStream_t st)
 {
     if (p1 <= p0) return 0;
-    const unsigned grid = (unsigned)((p1 - p0 + 127) / 128);
+    const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
+    const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
     BS_SWITCH(bs, (bsr_gs_color_kernel<BS><<<grid, 128, 0, st>>>(Ap, Aj, Ax, x, b, Id, p0, p1, backward)));
     return check_launch("bsr_gs_color_kernel");
 }
