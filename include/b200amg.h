@@ -94,6 +94,8 @@ int b200amg_dot(long long n, const double *x, const double *y, double *out_dev, 
                 void *stream);
 /* y = a*x + y ; y = x ; x = 0 */
 int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream);
+/* y = a*x */
+int b200amg_scal(long long n, double a, const double *x, double *y, void *stream);
 /* one Jacobi sweep from a zero initial guess == diagonal scaling (bit-identical):
  * x = omega*(b/diag) [CSR arithmetic] or (omega*b)/diag [bsr_flavor != 0]; rows with diag==0 -> 0 */
 int b200amg_scale_diag(long long n, double omega, const double *b, const double *diag, double *x,
@@ -245,7 +247,7 @@ typedef struct b200amg_level_desc {
     const int *Rp, *Rj; const double *Rx;
     /* smoothers: kind 0 none, 1 jacobi(omega, iterations), 2 gauss_seidel_indexed over
      * colour-grouped rows (Id, color_ptr on HOST), 3 lexicographic gauss_seidel (sequential on
-     * the device, exact); sweep 0 fwd / 1 bwd / 2 symmetric */
+     * the device, exact), 4 polynomial (coefficients below); sweep 0 fwd / 1 bwd / 2 symmetric */
     int pre_kind, post_kind;
     double pre_omega, post_omega;
     int pre_iters, post_iters;
@@ -253,6 +255,10 @@ typedef struct b200amg_level_desc {
     const int *Id;              /* device: rows (block rows if bs>1) grouped by colour */
     const int *color_ptr_host;  /* host: K+1 offsets */
     int K;
+    /* kind 4: polynomial smoother (pyamg/relaxation/relaxation.py:593-668; what 'chebyshev' resolves to,
+     * smoothing.py:438-449): per iteration r = b - A x, h = c[0] r, h = c[k] r + A h (k = 1..ncoef-1), x += h */
+    int pre_ncoef, post_ncoef;  /* 1..8 */
+    double pre_coef[8], post_coef[8];
 } b200amg_level_desc;
 
 /* Build a cycle engine over nlev-1 described levels + the dense coarse operator

@@ -104,6 +104,21 @@ def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', core=N
         core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr)
 
 
+def polynomial(A, x, b, coefficients, iterations=1, core=None):
+    """pyamg/relaxation/relaxation.py:593-668 (what 'chebyshev' resolves to, smoothing.py:438-449): numpy / scipy
+    expressions exactly as the reference writes them."""
+    A, x, b = make_system(A, x, b, formats=None)
+    for _ in range(iterations):
+        if np.sqrt(np.inner(x.conj(), x).real) == 0:
+            residual = b
+        else:
+            residual = (b - A * x)
+        h = coefficients[0] * residual
+        for c in coefficients[1:]:
+            h = c * residual + A * h
+        x += h
+
+
 def vertex_coloring_mis(G, core=None):
     """pyamg/graph.py:84-125 with method='MIS' (-> graph.h:171-188)."""
     core = core or _o.core

@@ -23,6 +23,8 @@ class LevelDesc(Structure):
         ('pre_iters', c_int), ('post_iters', c_int),
         ('pre_sweep', c_int), ('post_sweep', c_int),
         ('Id', p), ('color_ptr_host', POINTER(c_int)), ('K', c_int),
+        ('pre_ncoef', c_int), ('post_ncoef', c_int),
+        ('pre_coef', c_double * 8), ('post_coef', c_double * 8),
     ]
 
 
@@ -49,6 +51,7 @@ _SIGS = {
     'b200amg_halo_wait': (c_int, [p, c_int, p, c_longlong, p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
     'b200amg_axpy': (c_int, [c_longlong, c_double, p, p, p]),
+    'b200amg_scal': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scale_diag': (c_int, [c_longlong, c_double, p, p, p, c_int, p]),
     'b200amg_extract_diag': (c_int, [c_int, c_int, p, p, p, p, p]),
     'b200amg_dense_matvec': (c_int, [c_int, p, p, p, p]),

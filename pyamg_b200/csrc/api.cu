@@ -146,6 +146,11 @@ extern "C" int b200amg_axpy(long long n, double a, const double *x, double *y, v
     return axpy(n, a, x, y, S(stream));
 }
 
+extern "C" int b200amg_scal(long long n, double a, const double *x, double *y, void *stream)
+{
+    return scal(n, a, x, y, S(stream));
+}
+
 extern "C" int b200amg_scale_diag(long long n, double omega, const double *b, const double *diag, double *x,
                                   int bsr_flavor, void *stream)
 {

@@ -77,6 +77,20 @@ int axpy(long long n, double a, const double *x, double *y, cudaStream_t st)
     return check_launch("axpy_kernel");
 }
 
+// y = a * x (the polynomial smoother's h = c * residual, pyamg/relaxation/relaxation.py:663-666)
+__global__ void __launch_bounds__(256) scal_kernel(long long n, double a, const double *__restrict__ x, double *__restrict__ y)
+{
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) y[i] = mul_rn(a, x[i]);
+}
+
+int scal(long long n, double a, const double *x, double *y, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    scal_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, a, x, y);
+    return check_launch("scal_kernel");
+}
+
 // diag[i] = last stored a_ii of row i (0 when absent): relaxation.h:228-229 semantics
 __global__ void __launch_bounds__(256) extract_diag_kernel(int nb, int bs, const int *__restrict__ Ap,
                                                            const int *__restrict__ Aj, const double *__restrict__ Ax,

@@ -100,6 +100,7 @@ int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, do
 
 int dot(long long n, const double *x, const double *y, double *out, double *work, cudaStream_t st);
 int axpy(long long n, double a, const double *x, double *y, cudaStream_t st);
+int scal(long long n, double a, const double *x, double *y, cudaStream_t st);
 int extract_diag(int nb, int bs, const int *Ap, const int *Aj, const double *Ax, double *diag, cudaStream_t st);
 int scale_diag(long long n, double omega, const double *b, const double *d, double *x, int bsrf, cudaStream_t st);
 int dense_matvec(int n, const double *M, const double *x, double *y, cudaStream_t st);

@@ -16,6 +16,7 @@ namespace b200amg {
 struct LevelRt {
     b200amg_level_desc d;
     double *r, *bc, *xc, *tmp, *diag;
+    double *poly = nullptr;                   // third work vector of the polynomial smoother
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
@@ -72,7 +73,8 @@ long long work_doubles(int nlev, const b200amg_level_desc *L)
 {
     size_t tot = al(1024) ;
     for (int k = 0; k < nlev - 1; ++k)
-        tot += al(L[k].n) * 3 /* r, tmp, diag */ + al(L[k].nc) * 2 /* bc, xc */;
+        tot += al(L[k].n) * (3 + (L[k].pre_kind == 4 || L[k].post_kind == 4)) /* r, tmp, diag [, poly] */ +
+               al(L[k].nc) * 2 /* bc, xc */;
     return (long long)tot;
 }
 
@@ -116,7 +118,7 @@ static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream
 }
 
 // one smoothing stage; *cur is the buffer holding the iterate (x or the spare), swapped by Jacobi
-static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep, double **cur, double **spare,
+static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters, int sweep, double **cur, double **spare,
                   const double *b, bool x_is_zero, cudaStream_t st)
 {
     const b200amg_level_desc &d = L.d;
@@ -182,6 +184,25 @@ static int smooth(const LevelRt &L, int kind, double omega, int iters, int sweep
         }
         return 0;
     }
+    if (kind == 4) {                                   // polynomial (Chebyshev): relaxation.py:593-668
+        const double *coef = post ? d.post_coef : d.pre_coef;
+        const int ncoef = post ? d.post_ncoef : d.pre_ncoef;
+        double *r = L.r, *h = *spare, *t = L.poly;
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        for (int it = 0; it < iters; ++it) {
+            // "norm(x) == 0 -> residual = b" of the reference is the same bits as b - A*0
+            if (it == 0 && x_is_zero) B200_CUDA(cudaMemcpyAsync(r, b, sizeof(double) * d.n, cudaMemcpyDeviceToDevice, st));
+            else B200_TRY(apply_A(L, OP_RESIDUAL, 1, *cur, b, r, st));
+            B200_TRY(scal(d.n, coef[0], r, h, st));
+            for (int c = 1; c < ncoef; ++c) {          // h = c*residual + A*h
+                B200_TRY(scal(d.n, coef[c], r, t, st));
+                B200_TRY(apply_A(L, OP_ADD, 2, h, nullptr, t, st));
+                double *sw = h; h = t; t = sw;
+            }
+            B200_TRY(axpy(d.n, 1.0, h, *cur, st));     // x += h
+        }
+        return 0;
+    }
     return set_err(B200AMG_EINVAL, "smooth: unknown smoother kind");
 }
 
@@ -203,7 +224,7 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
     const b200amg_level_desc &d = L.d;
     const int nlev = (int)E.lev.size() + 1;
     double *cur = x, *spare = L.tmp;
-    B200_TRY(smooth(L, d.pre_kind, d.pre_omega, d.pre_iters, d.pre_sweep, &cur, &spare, b, x_is_zero, st));
+    B200_TRY(smooth(L, false, d.pre_kind, d.pre_omega, d.pre_iters, d.pre_sweep, &cur, &spare, b, x_is_zero, st));
     B200_TRY(mark(E, B200AMG_OP_PRESMOOTH, k, st));
     B200_TRY(apply_A(L, OP_RESIDUAL, 1, cur, b, L.r, st));
     B200_TRY(mark(E, B200AMG_OP_RESIDUAL, k, st));
@@ -224,7 +245,7 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
     }
     B200_TRY(prolong_add(L, L.xc, cur, st));
     B200_TRY(mark(E, B200AMG_OP_PROLONG, k, st));
-    B200_TRY(smooth(L, d.post_kind, d.post_omega, d.post_iters, d.post_sweep, &cur, &spare, b, false, st));
+    B200_TRY(smooth(L, true, d.post_kind, d.post_omega, d.post_iters, d.post_sweep, &cur, &spare, b, false, st));
     B200_TRY(mark(E, B200AMG_OP_POSTSMOOTH, k, st));
     if (cur != x) {
         B200_CUDA(cudaMemcpyAsync(x, cur, sizeof(double) * d.n, cudaMemcpyDeviceToDevice, st));
@@ -269,6 +290,11 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
         L.r = w; w += al(L.d.n);
         L.tmp = w; w += al(L.d.n);
         L.diag = w; w += al(L.d.n);
+        if (L.d.pre_kind == 4 || L.d.post_kind == 4) { L.poly = w; w += al(L.d.n); }
+        for (int side = 0; side < 2; ++side) {
+            const int kind = side ? L.d.post_kind : L.d.pre_kind, nc = side ? L.d.post_ncoef : L.d.pre_ncoef;
+            if (kind == 4 && (nc < 1 || nc > 8)) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: polynomial smoother needs 1..8 coefficients"); }
+        }
         L.bc = w; w += al(L.d.nc);
         L.xc = w; w += al(L.d.nc);
         if (L.d.pre_kind == 2 || L.d.post_kind == 2) {

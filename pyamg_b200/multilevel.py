@@ -26,9 +26,11 @@ _CYCLE = {'V': 0, 'W': 1, 'F': 2}
 class _Smoother:
     """resolved smoother of one level: kind, omega, iterations, sweep (+ colour ordering)"""
 
-    def __init__(self, kind=0, omega=1.0, iterations=1, sweep='forward', indices=None, color_ptr=None, name=None):
+    def __init__(self, kind=0, omega=1.0, iterations=1, sweep='forward', indices=None, color_ptr=None, name=None,
+                 coefficients=None):
         self.kind, self.omega, self.iterations, self.sweep = kind, float(omega), int(iterations), sweep
         self.indices, self.color_ptr, self.name = indices, color_ptr, name
+        self.coefficients = None if coefficients is None else [float(c) for c in coefficients]   # kind 4: polynomial
 
 
 def coarse_grid_solver(solver):
@@ -177,6 +179,13 @@ class multilevel_solver:
             d.pre_iters, d.post_iters = pre.iterations, post.iterations
             d.pre_sweep, d.post_sweep = _SWEEP[pre.sweep], _SWEEP[post.sweep]
             d.Id, d.K = 0, 0
+            for side, sm in (('pre', pre), ('post', post)):
+                if sm.kind == 4:
+                    if not 1 <= len(sm.coefficients) <= 8:
+                        raise ValueError('polynomial smoother: 1..8 coefficients')
+                    setattr(d, side + '_ncoef', len(sm.coefficients))
+                    for q, c in enumerate(sm.coefficients):
+                        getattr(d, side + '_coef')[q] = c
             ordered = [s for s in (pre, post) if s.kind == 2]
             if ordered:
                 s0 = ordered[0]

@@ -9,7 +9,7 @@ with `color_ptr`; without `color_ptr` the indexed sweep runs strictly sequential
 import numpy as np
 import torch
 
-from . import amg_core
+from . import _lib, amg_core
 from .sparse import DevMat
 
 
@@ -102,6 +102,26 @@ def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', color_
     r0, r1, dr = _range(sweep, int(indices.numel()))
     for _ in range(iterations):
         amg_core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr, color_ptr)
+
+
+def polynomial(A, x, b, coefficients, iterations=1):
+    """pyamg/relaxation/relaxation.py:593-668: x += p(A)(b - A x) with p given by its coefficients (highest power
+    first), Horner form: h = c0 r; h = c_k r + A h.  The reference's "norm(x) == 0 -> residual = b" shortcut gives
+    the bits of b - A*0, so the residual is always formed."""
+    A, x, b = make_system(A, x, b, formats=None)
+    n = A.shape[0]
+    st = torch.cuda.current_stream().cuda_stream
+    h, t = torch.empty_like(x), torch.empty_like(x)
+    for _ in range(iterations):
+        r = A.residual(x, b)
+        _lib.call('b200amg_scal', n, float(coefficients[0]), r.data_ptr(), h.data_ptr(), st)
+        for c in coefficients[1:]:
+            _lib.call('b200amg_scal', n, float(c), r.data_ptr(), t.data_ptr(), st)
+            R, C = A.blocksize
+            _lib.call('b200amg_bsr_matvec', A.n_brow, A.n_bcol, R, C, A.indptr.data_ptr(), A.indices.data_ptr(),
+                      A.data.data_ptr(), h.data_ptr(), 0, t.data_ptr(), 2, st)              # t += A h
+            h, t = t, h
+        _lib.call('b200amg_axpy', n, 1.0, h.data_ptr(), x.data_ptr(), st)
 
 
 def vertex_coloring(G, method='MIS'):

@@ -2,7 +2,7 @@
 
 A smoother spec is `name`, `(name, {opts})`, or a per-level list of those -- the same forms the
 reference accepts (smoothing.py:37-57,126-169).  Names with a device kernel:
-jacobi, gauss_seidel, gauss_seidel_indexed, multicolor_gauss_seidel, None.
+jacobi, gauss_seidel, gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev / polynomial, None.
 """
 import numpy as np
 import torch
@@ -21,6 +21,18 @@ def rho_D_inv_A(A):
         dinv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
         A.rho_D_inv = approximate_spectral_radius(A, row_scale=dinv)
     return A.rho_D_inv
+
+
+def chebyshev_polynomial_coefficients(a, b, degree):
+    """pyamg/relaxation/chebyshev.py:9-56: coefficients (highest power first) of the polynomial with the Chebyshev
+    roots of [a, b], scaled so that C(0) = 1.  A handful of host flops at setup time."""
+    if a >= b or a <= 0:
+        raise ValueError('invalid interval [%s,%s]' % (a, b))
+    std_roots = np.cos(np.pi * (np.arange(degree) + 0.5) / degree)
+    scaled_roots = 0.5 * (b - a) * (1 + std_roots) + a
+    scaled_poly = np.poly(scaled_roots)
+    scaled_poly /= np.polyval(scaled_poly, 0)
+    return scaled_poly
 
 
 def _unpack(spec):
@@ -67,8 +79,21 @@ def _resolve(spec, lvl):
             if not isinstance(idx, torch.Tensor):
                 idx = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.intc)).to(_dev())
         return _Smoother(2, 1.0, iters, sweep, idx, np.ascontiguousarray(ptr, dtype=np.intc), name=name)
+    if name in ('polynomial', 'chebyshev'):
+        iters = kw.pop('iterations', 1)
+        if name == 'polynomial':
+            coef = kw.pop('coefficients')
+        else:                       # setup_chebyshev, smoothing.py:438-449
+            lower, upper, degree = kw.pop('lower_bound', 1.0 / 30.0), kw.pop('upper_bound', 1.1), kw.pop('degree', 3)
+            rho = kw.pop('rho', None)
+            if rho is None:
+                rho = approximate_spectral_radius(A)
+            coef = -chebyshev_polynomial_coefficients(rho * lower, rho * upper, degree)[:-1]
+        if kw:
+            raise TypeError('%s: unexpected options %r' % (name, sorted(kw)))
+        return _Smoother(4, 1.0, iters, name=name, coefficients=np.asarray(coef, dtype=np.float64))
     raise ValueError('smoother %r has no device kernel (available: jacobi, gauss_seidel, '
-                     'gauss_seidel_indexed, multicolor_gauss_seidel, None)' % (name,))
+                     'gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev, polynomial, None)' % (name,))
 
 
 def change_smoothers(ml, presmoother, postsmoother):

@@ -100,6 +100,28 @@ def rs_mcgs(name, A, max_coarse):
           [bool(l.A.has_sorted_indices) for l in ml.levels], res[0], res[-1])
 
 
+def sa_chebyshev(name, grid, max_coarse):
+    """SA hierarchy with the reference's 'chebyshev' smoother (smoothing.py:438-449 -> relaxation.polynomial).  The
+    coefficients the reference resolved (from its own random-start spectral-radius estimate) are read back out of the
+    smoother closures and stored, so a cycle can be replayed with exactly those numbers."""
+    A = poisson(grid, format='csr')
+    np.random.seed(0)
+    ch = ('chebyshev', {'degree': 3, 'iterations': 1})
+    ml = pyamg.smoothed_aggregation_solver(A, presmoother=ch, postsmoother=ch, max_coarse=max_coarse,
+                                           improve_candidates=None)
+    specs = []
+    for lvl in ml.levels[:-1]:
+        pair = []
+        for fn in (lvl.presmoother, lvl.postsmoother):
+            cells = dict(zip(fn.__code__.co_freevars, [c.cell_contents for c in fn.__closure__]))
+            pair.append(('polynomial', {'coefficients': np.asarray(cells['coefficients'], dtype=np.float64),
+                                        'iterations': int(cells['iterations'])}))
+        specs.append(tuple(pair))
+    b, res, x = run(ml, A.shape[0], 8)
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, {'b': b, 'residuals': res, 'x': x})
+    print(name, [l.A.shape[0] for l in ml.levels], res[0], res[-1])
+
+
 def sa_elasticity(name, grid):
     A, B = linear_elasticity(grid, format='bsr')
     np.random.seed(0)
@@ -148,3 +170,4 @@ if __name__ == '__main__':
     st = diffusion_stencil_2d(epsilon=0.001, theta=np.pi / 8, type='FE')
     rs_mcgs('rs_aniso_48_mcgs.npz', stencil_grid(st, (48, 48), format='csr'), 20)
     sa_elasticity('sa_elasticity2d_14.npz', (14, 14))
+    sa_chebyshev('sa_poisson3d_12_chebyshev.npz', (12, 12, 12), 20)
