@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) bsr_matvec_kernel(int n_brow, int R, int 
     }
     if (mode == 0) y[g] = acc;
     else if (mode == 1) y[g] = sub_rn(b[g], acc);
-    else y[g] = add_rn(y[g], acc);
+    else y[g] = add_rn(b ? b[g] : y[g], acc);        // mode 2: y = (b or y) + A x
 }
 
 // amg_core.bsr_jacobi, forward full range: thread per scalar row (i, k); reads xin, writes xout

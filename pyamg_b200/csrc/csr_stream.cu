@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a, con
     } else if (OP == OP_RESIDUAL) {
         y[row] = sub_rn(a.b[row], acc);
     } else if (OP == OP_ADD) {
-        y[row] = add_rn(y[row], acc);
+        y[row] = add_rn((a.b ? a.b : y)[row], acc);                // addend from b when given (out-of-place add)
     } else if (OP == OP_JACOBI) {
         const double xi = xg[row];
         y[row] = (diag != 0.0)

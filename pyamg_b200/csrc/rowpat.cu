@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
                 const int rp = step_row(k + RP_AHEAD);
                 if (rp >= 0) {
                     if (NEED_B) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.b + rp));
-                    if (NEED_Y) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.y + rp));
+                    if (NEED_Y) asm volatile("prefetch.global.L2 [%0];" ::"l"((a.b ? a.b : a.y) + rp));
                     if (rp + far < a.n) asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + (rp + far)));
                 }
             }
@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
                 pv = s_val + code * RP_LEN;
                 if (NEED_B) bi = __ldg(a.b + row);
                 if (SMOOTH) xi = __ldg(xg + row);
-                if (NEED_Y) yi = a.y[row];
+                if (NEED_Y) yi = (a.b ? a.b : a.y)[row];
                 const int meta = s_meta[code];
                 len = meta & 0xff;
                 dm = (unsigned)meta >> 8;

@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     if (live) {
         if (NEED_B) bi = __ldg(a.b + row);
         if (SMOOTH) xi = __ldg(xg + row);
-        if (OP == OP_ADD) yi = a.y[row];
+        if (OP == OP_ADD) yi = (a.b ? a.b : a.y)[row];
     }
     double acc = BSRF ? bi : 0.0, diag = 0.0;
     const int *pj = cj + off + lane;

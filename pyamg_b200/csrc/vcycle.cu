@@ -105,16 +105,17 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
     return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st);
 }
 
-static int prolong_add(const LevelRt &L, const double *xc, double *x, cudaStream_t st)
+// x_out = x_in + P x_c (x_in == nullptr: in place)
+static int prolong_add(const LevelRt &L, const double *xc, const double *x_in, double *x, cudaStream_t st)
 {
     const b200amg_level_desc &d = L.d;
     if (d.p_br == 1 && d.p_bc == 1) {
-        StreamArgs a{d.Pp, d.Pj, d.Px, xc, nullptr, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
+        StreamArgs a{d.Pp, d.Pj, d.Px, xc, x_in, x, L.nzP, 0, d.n, 1.0, 0.0, 0.0};
         L.dP.apply(a);
         if (L.sP.ok()) return sell_op(OP_ADD, L.sP, a, st);
         return stream_op(OP_ADD, a, st);
     }
-    return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, nullptr, x, 2, st);
+    return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, x_in, x, 2, st);
 }
 
 // one smoothing stage; *cur is the buffer holding the iterate (x or the spare), swapped by Jacobi
@@ -243,7 +244,16 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
         B200_TRY(cycle(E, k + 1, L.xc, L.bc, 2, true, st));
         B200_TRY(cycle(E, k + 1, L.xc, L.bc, 0, false, st));
     }
-    B200_TRY(prolong_add(L, L.xc, cur, st));
+    // The iterate must end in x.  Jacobi sweeps ping-pong between x and the spare buffer; when the sweeps still to
+    // come would leave the result in the spare buffer, the correction is written OUT OF PLACE (other buffer =
+    // iterate + P x_c, same bits) -- one more swap, and the D2D copy back to x disappears.
+    const int swaps_to_come = d.post_kind == 1 ? d.post_iters : 0;
+    if (((cur == x) ? 0 : 1) != (swaps_to_come & 1)) {
+        B200_TRY(prolong_add(L, L.xc, cur, spare, st));
+        double *t = cur; cur = spare; spare = t;
+    } else {
+        B200_TRY(prolong_add(L, L.xc, nullptr, cur, st));
+    }
     B200_TRY(mark(E, B200AMG_OP_PROLONG, k, st));
     B200_TRY(smooth(L, true, d.post_kind, d.post_omega, d.post_iters, d.post_sweep, &cur, &spare, b, false, st));
     B200_TRY(mark(E, B200AMG_OP_POSTSMOOTH, k, st));
