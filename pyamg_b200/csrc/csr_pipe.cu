@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
         if (t < nr) {
             if (NEED_B) bi = __ldg(a.b + row);
             if (NEED_XI) xi = __ldg(xg + row);
-            if (NEED_Y) yi = (a.b ? a.b : a.y)[row];            // OP_ADD: y = (b or y) + A x
+            if (NEED_Y) yi = a.b[row];                         // OP_ADD: y = b + A x (b == y: in place)
         }
         mbar_wait(&S.ptr_full[i % NP], (i / NP) & 1);
         const int *sp = S.ptr[i % NP];

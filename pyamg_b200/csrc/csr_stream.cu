@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a, con
     } else if (OP == OP_RESIDUAL) {
         y[row] = sub_rn(a.b[row], acc);
     } else if (OP == OP_ADD) {
-        y[row] = add_rn((a.b ? a.b : y)[row], acc);                // addend from b when given (out-of-place add)
+        y[row] = add_rn(a.b[row], acc);                            // b == y: in place
     } else if (OP == OP_JACOBI) {
         const double xi = xg[row];
         y[row] = (diag != 0.0)
@@ -179,8 +179,10 @@ static int launch_stream(const StreamArgs &a0, cudaStream_t st)
     return check_launch("csr_stream_kernel");
 }
 
-int stream_op(int op, const StreamArgs &a, cudaStream_t st)
+int stream_op(int op, const StreamArgs &a0, cudaStream_t st)
 {
+    StreamArgs a = a0;
+    if (op == OP_ADD && !a.b) a.b = a.y;              // y += A x: the kernels read the addend through b
     int rc = 0;
     if (a.nnz >= 0 && pipe_op(op, a, a.nnz, st, &rc)) return rc;
     switch (op) {

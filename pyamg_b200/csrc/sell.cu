@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     if (live) {
         if (NEED_B) bi = __ldg(a.b + row);
         if (SMOOTH) xi = __ldg(xg + row);
-        if (OP == OP_ADD) yi = (a.b ? a.b : a.y)[row];
+        if (OP == OP_ADD) yi = a.b[row];
     }
     double acc = BSRF ? bi : 0.0, diag = 0.0;
     const int *pj = cj + off + lane;
@@ -321,8 +321,10 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
     return check_launch("sell_kernel");
 }
 
-int sell_op(int op, const Sell &s, const StreamArgs &a, cudaStream_t st)
+int sell_op(int op, const Sell &s, const StreamArgs &a0, cudaStream_t st)
 {
+    StreamArgs a = a0;
+    if (op == OP_ADD && !a.b) a.b = a.y;              // y += A x: the kernels read the addend through b
     if (a.row_begin != 0 || a.row_end != s.n) return set_err(B200AMG_EINVAL, "sell_op: full row range only");
     switch (op) {
     case OP_MATVEC: return launch_sell<OP_MATVEC>(s, a, st);
