@@ -20,8 +20,13 @@ def run(world, grid, thresh, cycles, port):
 
 @pytest.mark.parametrize('world,grid,thresh', [(2, 10, 50),       # levels 0 and 1 partitioned, rest agglomerated
                                                (2, 9, 100000),    # only level 0 partitioned
-                                               (3, 8, 30)])       # uneven slabs
+                                               (3, 8, 30),        # uneven slabs
+                                               (2, 14, 5)])       # every level but the coarsest partitioned (3 of 4):
+                                                                  # the shape of the 8-GPU 512^3 run, only the dense
+                                                                  # coarse solve stays on rank 0
 def test_partitioned_cycle_equals_global(world, grid, thresh):
     r = run(world, grid, thresh, 4, 29500 + world * 10 + grid)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert 'bit-identical x True' in r.stdout
+    if (grid, thresh) == (14, 5):
+        assert 'partitioned levels 3 of 4' in r.stdout
