@@ -1,0 +1,45 @@
+"""CPU tests (-m "not gpu") of the bench.py contract pieces that run without a GPU: the reference arm (the
+reference's CPU path = oracle/_ref or the C port, hierarchy from the CPU setup restatements) for both benchable
+configs, and the byte models the roofline numbers are computed from."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize('extra', [['--grid', '14'], ['--config', '3', '--grid', '60']])
+def test_reference_arm_line(extra):
+    env = dict(os.environ, B200AMG_REF_BUDGET_S='5', CUDA_VISIBLE_DEVICES='')
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference', '--steps', '2', '--warmup', '1'] + extra,
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d['impl'] == 'reference' and d['unit'] == 'V-cycles/s' and d['higher_is_better'] is True
+    assert d['value'] > 0 and abs(d['value'] - 1000.0 / d['ms_per_step']) <= 1e-6 * d['value']
+    assert d['cpu_baseline']['kind'] in ('reference', 'port') and d['cpu_baseline']['cores'] == 1
+    assert d['cpu_baseline']['value'] == d['value'] and d['e2e']['value'] == d['value']
+    assert d['e2e']['h2d_bytes_per_step'] == 0 and d['e2e']['d2h_bytes_per_step'] == 0 and d['gpu_launches'] == 0
+    assert d['vs_baseline'] is None and len(d['config']['levels']) >= 2 and 'workload' in d['config']
+
+
+def test_reference_arm_other_ranks_exit_quietly():
+    env = dict(os.environ, RANK='1', WORLD_SIZE='2', LOCAL_RANK='1', CUDA_VISIBLE_DEVICES='')
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference', '--gpus', '2'],
+                       env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip() == ''
+
+
+def test_byte_models():
+    sys.path.insert(0, ROOT)
+    import bench
+    n, nnz = 16777216, 117047296
+    # CSR SpMV of the 256^3 operator = 1.740 GB; Jacobi adds b (8n)
+    assert bench.spmv_bytes(n, n, nnz) == 12 * nnz + 4 * (n + 1) + 16 * n == 1740111876
+    assert bench.jacobi_bytes(n, nnz) == bench.spmv_bytes(n, n, nnz) + 8 * n
+    assert bench.jacobi_bytes(n, nnz, 5) == 25 * n                       # row-pattern layout: 1 B/row + b, x, x_new
+    assert bench.gs_sweep_bytes(n, nnz) == bench.spmv_bytes(n, n, nnz) + 8 * n + 4 * n
+    assert bench.grid_dims(256, 8) == (512, 512, 512) and bench.grid_dims(256, 2) == (512, 256, 256)
