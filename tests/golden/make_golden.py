@@ -100,6 +100,43 @@ def rs_mcgs(name, A, max_coarse):
           [bool(l.A.has_sorted_indices) for l in ml.levels], res[0], res[-1])
 
 
+def tet_grid(nv):
+    """nv^3 vertices of the unit cube, every cube cut into 6 tetrahedra around its main diagonal (fixed orientation)"""
+    g = np.arange(nv) / float(nv - 1)
+    V = np.array([[x, y, z] for z in g for y in g for x in g])
+    vid = lambda i, j, k: i + nv * (j + nv * k)
+    E = []
+    for k in range(nv - 1):
+        for j in range(nv - 1):
+            for i in range(nv - 1):
+                c = [vid(i + a, j + b, k + d) for d in (0, 1) for b in (0, 1) for a in (0, 1)]   # c[a + 2b + 4d]
+                for p, q in ((1, 3), (3, 2), (2, 6), (6, 4), (4, 5), (5, 1)):                   # ring around c0-c7
+                    E.append([c[0], c[p], c[q], c[7]])
+    return V, np.array(E)
+
+
+def sa_elasticity3d(name, nv):
+    """BASELINE config 4 in miniature: P1 tetrahedral elasticity (linear_elasticity_p1, E = 1e5, nu = 0.3), the face
+    x = 0 clamped by eliminating its block rows / columns, SA with the 6 rigid-body modes and symmetric Gauss-Seidel:
+    level 0 is BSR 3x3, the coarse levels BSR 6x6, P is 3x6 / 6x6 -- the block shapes of the full-size problem."""
+    from pyamg.gallery import linear_elasticity_p1
+    import scipy.sparse as sp
+    V, E = tet_grid(nv)
+    A, B = linear_elasticity_p1(V, E, format='bsr')
+    free = np.where(V[:, 0] > 0)[0]
+    dof = (3 * free[:, None] + np.arange(3)[None, :]).ravel()
+    A = sp.csr_matrix(A)[dof][:, dof].tobsr(blocksize=(3, 3))
+    B = B[dof]
+    np.random.seed(0)
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    b, res, x = run(ml, A.shape[0], 8)
+    specs = [((('gauss_seidel', {'sweep': 'symmetric', 'iterations': 1}),) * 2) for _ in ml.levels[:-1]]
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, {'b': b, 'residuals': res, 'x': x})
+    print(name, [(l.A.shape[0], l.A.format, getattr(l.A, 'blocksize', None)) for l in ml.levels],
+          [getattr(l, 'P', None) is not None and l.P.blocksize for l in ml.levels], res[0], res[-1])
+
+
 def sa_chebyshev(name, grid, max_coarse):
     """SA hierarchy with the reference's 'chebyshev' smoother (smoothing.py:438-449 -> relaxation.polynomial).  The
     coefficients the reference resolved (from its own random-start spectral-radius estimate) are read back out of the
@@ -171,3 +208,4 @@ if __name__ == '__main__':
     rs_mcgs('rs_aniso_48_mcgs.npz', stencil_grid(st, (48, 48), format='csr'), 20)
     sa_elasticity('sa_elasticity2d_14.npz', (14, 14))
     sa_chebyshev('sa_poisson3d_12_chebyshev.npz', (12, 12, 12), 20)
+    sa_elasticity3d('sa_elasticity3d_tets_7.npz', 7)
