@@ -124,3 +124,17 @@ def test_color_ordering_and_stencil_helpers():
     assert np.array_equal(idx, i2) and np.array_equal(ptr, p2)
     st = gallery.diffusion_stencil_2d(0.001, np.pi / 8, 'FE')
     assert st.shape == (3, 3) and abs(st.sum()) < 1e-12
+
+
+def test_chebyshev_coefficients_host_formula():
+    """pyamg/relaxation/chebyshev.py:9-56 (docstring example :37-38) and the sign / truncation setup_chebyshev applies
+    (smoothing.py:438-449); pure host arithmetic, no GPU needed"""
+    from pyamg_b200.smoothing import chebyshev_polynomial_coefficients
+    c = chebyshev_polynomial_coefficients(1.0, 2.0, 3)
+    assert np.allclose(c, [-0.32323232, 1.45454545, -2.12121212, 1.0], atol=5e-9)
+    assert abs(np.polyval(c, 0.0) - 1.0) < 1e-15
+    roots = np.sort(np.roots(c).real)
+    assert np.all(roots > 1.0) and np.all(roots < 2.0)
+    import pytest
+    with pytest.raises(ValueError):
+        chebyshev_polynomial_coefficients(2.0, 1.0, 3)
