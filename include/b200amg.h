@@ -199,6 +199,43 @@ int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, const doubl
                             const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
                             int *Cj, double *Cx, void *stream);
 
+/* ---- block (BSR) smoothed-aggregation setup (csrc/bsr_setup.cu) -- BASELINE config 4 -------------- */
+/* scipy bsr_scale_rows (pyamg/util/utils.py:133-200): out[blk][r][c] = Ax[blk][r][c] * v[R*i + r], then
+ * times the scalar c of pyamg/aggregation/smooth.py:164 when use_c != 0 */
+int b200amg_bsr_scale_rows(int n_brow, int R, int C, const int *Ap, const double *Ax, const double *v,
+                           double c, int use_c, double *out, void *stream);
+/* out block q = in block perm[q] (R x C, row-major), transposed to C x R when transpose_blocks != 0.
+ * perm = the VALUE array of b200amg_csr_transpose run over block numbers 0..n_blocks-1 stored as doubles:
+ * scipy bsr_transpose (P.H, pyamg/aggregation/aggregation.py:400-401) and bsr sort_indices
+ * (pyamg/util/utils.py:571) */
+int b200amg_bsr_gather_blocks(long long n_blocks, int R, int C, const double *perm, const double *in,
+                              double *out, int transpose_blocks, void *stream);
+/* amg_core.fit_candidates (pyamg/amg_core/smoothed_aggregation.h:322-448) for K1 unknowns per node and K2
+ * candidates: (Mp, Mi) = members of each aggregate, ascending (AggOp in CSC form); B[node][K1][K2];
+ * Qx[member][K1][K2] (CSC member order) receives the orthonormalised candidates, Rx[agg][K2][K2] the
+ * coarse candidates */
+int b200amg_fit_candidates(int n_agg, int K1, int K2, const int *Mp, const int *Mi, const double *B,
+                           double tol, double *Qx, double *Rx, void *stream);
+/* Q.T.tobsr() of pyamg/aggregation/tentative.py:158-161: block of member p goes to block Tp[Mi[p]] of T */
+int b200amg_tentative_scatter(long long n_members, int K1, int K2, const int *Mi, const int *Tp,
+                              const double *Qx, double *Tx, void *stream);
+/* C = A - B on R x C blocks, all-zero result blocks not stored (scipy bsr_binop_bsr): general != 0 =
+ * rows in any order, output in reverse first-touch order; general == 0 = canonical merge of sorted rows.
+ * pass 0 writes cnt[i]; pass 1 fills Cj/Cx at Cp[i] */
+int b200amg_bsr_sub(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax,
+                    const int *Bp, const int *Bj, const double *Bx, int general, int pass, int *cnt,
+                    const int *Cp, int *Cj, double *Cx, void *stream);
+/* scipy bsr_matmat (the block R*A*P of pyamg/aggregation/aggregation.py:429): the block pattern is the
+ * scalar SpGEMM of the block patterns, column-sorted (Sj) and in csr_matmat order (Lj) over one row
+ * pointer Cp; slot_map turns the pair into scipy's first-touch block order (Cj) + the slot of every
+ * sorted entry; numeric accumulates every block in visiting order (Cx is cleared inside) */
+int b200amg_bsr_slot_map(int n_brow, const int *Cp, const int *Sj, const int *Lj, int *slot, int *Cj,
+                         void *stream);
+int b200amg_bsr_matmat_numeric(int n_brow, int R, int N, int C, const int *Ap, const int *Aj,
+                               const double *Ax, const int *Bp, const int *Bj, const double *Bx,
+                               const int *Cp, const int *Sj, const int *slot, long long n_out_blocks,
+                               double *Cx, void *stream);
+
 /* ---- Ruge-Stuben setup (csrc/rs_setup.cu): pyamg/amg_core/ruge_stuben.h:45-93, :496-595 -------- */
 /* amg_core.classical_strength_of_connection fused with the two things the reference's glue does to S:
  * flags & 1: drop the diagonal (the graph of the C/F splitting, pyamg/util/utils.py:1815-1827);

@@ -69,6 +69,13 @@ _SIGS = {
     'b200amg_tentative_fill': (c_int, [c_int, p, p, p, p, p, p]),
     'b200amg_csr_sub_sorted': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
     'b200amg_csr_sub_general': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
+    'b200amg_bsr_scale_rows': (c_int, [c_int, c_int, c_int, p, p, p, c_double, c_int, p, p]),
+    'b200amg_bsr_gather_blocks': (c_int, [c_longlong, c_int, c_int, p, p, p, c_int, p]),
+    'b200amg_fit_candidates': (c_int, [c_int, c_int, c_int, p, p, p, c_double, p, p, p]),
+    'b200amg_tentative_scatter': (c_int, [c_longlong, c_int, c_int, p, p, p, p, p]),
+    'b200amg_bsr_sub': (c_int, [c_int, c_int, c_int, p, p, p, p, p, p, c_int, c_int, p, p, p, p, p]),
+    'b200amg_bsr_slot_map': (c_int, [c_int, p, p, p, p, p, p]),
+    'b200amg_bsr_matmat_numeric': (c_int, [c_int, c_int, c_int, c_int, p, p, p, p, p, p, p, p, p, c_longlong, p, p]),
     'b200amg_rs_strength': (c_int, [c_int, c_double, p, p, p, c_int, c_int, p, p, p, p, p]),
     'b200amg_csr_not_canonical': (c_int, [c_int, p, p, p, p]),
     'b200amg_rs_direct_interpolation_pass1': (c_int, [c_int, p, p, p, p, p]),

@@ -1,6 +1,8 @@
 """smoothed_aggregation_solver on the device (pyamg/aggregation/aggregation.py:30-435) for the
-scalar path the BASELINE configs use: symmetric strength (theta = 0), standard aggregation,
-one near-nullspace candidate, Jacobi-smoothed prolongator, R = P^H, Galerkin A_c = R A P.
+paths the BASELINE configs use: symmetric strength (theta = 0), standard aggregation, Jacobi-smoothed
+prolongator, R = P^H, Galerkin A_c = R A P -- scalar CSR with one near-nullspace candidate (configs 2, 5)
+and BSR with K1 x K1 blocks and K2 candidates (config 4: 3 x 3 elasticity blocks, 6 rigid-body modes;
+the `_block` functions below, kernels in csrc/bsr_setup.cu).
 
 Per level (extend_hierarchy, aggregation.py:293-435):
   C      strength pattern; theta = 0 keeps every stored entry (smoothed_aggregation.h:48-99)
@@ -20,7 +22,8 @@ from . import _lib, amg_core
 from .linalg import approximate_spectral_radius
 from .multilevel import multilevel_solver
 from .smoothing import change_smoothers
-from .sparse import DevMat, _dev, _ptr, _scan_i32, _stream, galerkin, matmat, transpose
+from .sparse import (DevMat, _dev, _ptr, _scan_i32, _stream, block_pattern, bsr_matmat, bsr_sort_indices, galerkin,
+                     is_canonical_pattern, matmat, transpose)
 
 
 def _unpack(v):
@@ -32,6 +35,8 @@ def sort_indices(A):
     pyamg/util/utils.py:571): a double transpose."""
     if A.has_sorted_indices:
         return A
+    if not A.is_scalar:
+        return bsr_sort_indices(A)
     S = transpose(transpose(A))
     return DevMat(S.indptr, S.indices, S.data, A.shape, A.blocksize, A.format, True)
 
@@ -70,6 +75,66 @@ def fit_candidates_scalar(agg, nagg, B, tol=1e-10):
     _lib.call('b200amg_tentative_scalar', nagg, _ptr(M.indptr), _ptr(M.indices), _ptr(M.data), float(tol),
               _ptr(Bc), _ptr(node_val), _stream())
     return _one_entry_rows(agg, node_val, nagg), Bc
+
+
+def fit_candidates_block(agg, nagg, B, K1, K2, tol=1e-10):
+    """tentative.py:19-166 for K1 unknowns per node and K2 candidates: B is the (n K1) x K2 candidate array, row-major
+    on the device.  -> (T as BSR with K1 x K2 blocks, one per aggregated node; coarse candidates (nagg K2) x K2)"""
+    n = agg.numel()
+    dev = B.device
+    AggM = _one_entry_rows(agg, torch.zeros(n, dtype=torch.float64, device=dev), nagg)     # pattern of AggOp
+    M = transpose(AggM)                                   # AggOp in CSC form: members of every aggregate, ascending
+    nmem = M.nnz
+    Qx = torch.empty(nmem * K1 * K2, dtype=torch.float64, device=dev)
+    Bc = torch.empty(nagg * K2 * K2, dtype=torch.float64, device=dev)
+    _lib.call('b200amg_fit_candidates', nagg, K1, K2, _ptr(M.indptr), _ptr(M.indices), _ptr(B), float(tol), _ptr(Qx),
+              _ptr(Bc), _stream())
+    Tx = torch.empty_like(Qx)
+    _lib.call('b200amg_tentative_scatter', nmem, K1, K2, _ptr(M.indices), _ptr(AggM.indptr), _ptr(Qx), _ptr(Tx), _stream())
+    return DevMat(AggM.indptr, AggM.indices, Tx, (n * K1, nagg * K2), (K1, K2), 'bsr', True), Bc
+
+
+def _scaled_block(A, v, c=None):
+    out = torch.empty_like(A.data)
+    R, C = A.blocksize
+    _lib.call('b200amg_bsr_scale_rows', A.n_brow, R, C, _ptr(A.indptr), _ptr(A.data), _ptr(v),
+              0.0 if c is None else float(c), 0 if c is None else 1, _ptr(out), _stream())
+    return DevMat(A.indptr, A.indices, out, A.shape, A.blocksize, 'bsr', A.has_sorted_indices)
+
+
+def bsr_subtract(A, B):
+    """A - B on blocks with all-zero result blocks dropped: scipy bsr_binop_bsr, which merges when both operands are
+    canonical (rows strictly ascending) and otherwise emits in reverse first-touch order -- what `T - D_inv_S*T` gets,
+    because bsr_matmat returns its blocks in first-touch order"""
+    general = not (is_canonical_pattern(A) and is_canonical_pattern(B))
+    n = A.n_brow
+    R, C = A.blocksize
+    if B.blocksize != (R, C) or B.shape != A.shape:
+        raise ValueError('inconsistent shapes')
+    st = _stream()
+    dev = A.data.device
+    cnt = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    args = (n, R, C, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data), _ptr(B.indptr), _ptr(B.indices), _ptr(B.data),
+            int(general))
+    _lib.call('b200amg_bsr_sub', *args, 0, _ptr(cnt), 0, 0, 0, st)
+    Cp = _scan_i32(cnt[:n])
+    nb = int(Cp[-1].item())
+    Cj = torch.empty(nb, dtype=torch.int32, device=dev)
+    Cx = torch.empty(nb * R * C, dtype=torch.float64, device=dev)
+    _lib.call('b200amg_bsr_sub', *args, 1, 0, _ptr(Cp), _ptr(Cj), _ptr(Cx), st)
+    return DevMat(Cp, Cj, Cx, A.shape, (R, C), 'bsr', not general)
+
+
+def jacobi_prolongation_smoother_block(A, T, omega=4.0 / 3.0, degree=1, rho=None):
+    """smooth.py:67-208 for BSR operands, weighting='diagonal', filter=False -> (P, rho)"""
+    dinv = inverse_diagonal(A)
+    if rho is None:
+        rho = approximate_spectral_radius(_scaled_block(A, dinv))
+    S = _scaled_block(A, dinv, omega / rho)
+    P = T
+    for _ in range(degree):
+        P = bsr_subtract(P, bsr_matmat(S, P))
+    return P, rho
 
 
 def _scaled(A, v, c=None):
@@ -143,27 +208,55 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         raise NotImplementedError("smooth must be ('jacobi', {'omega', 'degree'}) or None")
     if not isinstance(A, DevMat):
         A = DevMat.from_scipy(A)
-    if not A.is_scalar:
-        raise NotImplementedError('block (BSR) problems: build the hierarchy with the reference and import it')
     if A.shape[0] != A.shape[1]:
         raise ValueError('expected square matrix')
+    if A.blocksize[0] != A.blocksize[1]:
+        raise ValueError('expected square blocks')
     dev = A.data.device
-    if B is None:
-        Bv = torch.ones(A.shape[0], dtype=torch.float64, device=dev)
+    bs = A.blocksize[0]
+    if B is None:                       # one constant per unknown of a node (aggregation.py:234-236)
+        Bn = np.kron(np.ones((A.shape[0] // bs, 1)), np.eye(bs))
     else:
         Bn = np.asarray(B.cpu().numpy() if isinstance(B, torch.Tensor) else B, dtype=np.float64)
-        if Bn.ndim == 2 and Bn.shape[1] != 1:
-            raise NotImplementedError('one near-nullspace candidate only')
-        if Bn.size != A.shape[0]:
+        if Bn.ndim == 1:
+            Bn = Bn.reshape(-1, 1)
+        if Bn.shape[0] != A.shape[0]:
             raise ValueError('The near null-space modes B have incorrect dimensions for matrix A')
-        Bv = torch.from_numpy(np.ascontiguousarray(Bn.ravel())).to(dev)
+    K2 = Bn.shape[1]
+    block = not A.is_scalar
+    if block and sname is None:
+        raise NotImplementedError("strength=None on a BSR matrix aggregates scalar unknowns in the reference; use 'symmetric'")
+    if not block and K2 != 1:
+        raise NotImplementedError('several candidates need a BSR matrix (the reference mixes CSR and BSR operands there)')
+    Bv = torch.from_numpy(np.ascontiguousarray(Bn.ravel())).to(dev)
 
     levels = [multilevel_solver.level()]
     levels[-1].A = A
     levels[-1].B = Bv
-    while len(levels) < max_levels and levels[-1].A.shape[0] > max_coarse:
+    while len(levels) < max_levels and levels[-1].A.n_brow > max_coarse:
         lvl = levels[-1]
         k = len(levels) - 1
+        if block:
+            # the same steps on blocks: aggregation on the block graph AS STORED (first-touch order out of bsr_matmat
+            # on coarse levels), then the in-place block sort of get_diagonal
+            K1 = lvl.A.blocksize[0]
+            agg, nagg, roots = standard_aggregation(block_pattern(lvl.A))
+            T, Bc = fit_candidates_block(agg, nagg, lvl.B, K1, K2)
+            A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
+            if mname == 'jacobi':
+                rho = rho_override[k][0] if rho_override is not None and k < len(rho_override) else None
+                P, lvl.rho_smooth = jacobi_prolongation_smoother_block(A, T, mkw.get('omega', 4.0 / 3.0),
+                                                                       mkw.get('degree', 1), rho)
+            else:
+                P = T
+            R = transpose(P)
+            if keep:
+                lvl.AggOp, lvl.T, lvl.Cpts = agg, T, roots
+            lvl.P, lvl.R = P, R
+            levels.append(multilevel_solver.level())
+            levels[-1].A = galerkin(R, A, P)
+            levels[-1].B = Bc
+            continue
         # the reference aggregates on the matrix AS STORED at that moment (unsorted rows straight
         # out of csr_matmat on coarse levels; pass 2 of the aggregation picks the FIRST aggregated
         # neighbour in storage order) and only afterwards sorts it in place inside

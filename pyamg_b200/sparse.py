@@ -6,6 +6,9 @@ tensors (int32 indices, fp64 values).  All arithmetic is done by libb200amg kern
   A * x          -> b200amg_csr_matvec / b200amg_bsr_matvec   (scipy csr_matvec / bsr_matvec)
   matmat(A, B)   -> b200amg_spgemm_*                          (scipy csr_matmat, pyamg aggregation.py:429)
   transpose(A)   -> b200amg_csr_transpose                     (scipy csr_tocsc,  pyamg classical.py:174)
+Block operands (BSR with R x C blocks, BASELINE config 4) take the same two calls: the block PATTERN goes through
+the scalar kernels, the blocks follow through b200amg_bsr_slot_map / _bsr_matmat_numeric / _bsr_gather_blocks
+(scipy bsr_matmat / bsr_transpose).
 """
 import numpy as np
 import torch
@@ -169,7 +172,7 @@ def matmat(A, B, scipy_order=False, batch_products=None):
     scipy's own reverse-first-touch order.  Rows are independent, so large products run in row
     batches whose expand-sort-compress scratch stays below `batch_products` entries (same result)."""
     if not (A.is_scalar and B.is_scalar):
-        raise NotImplementedError('matmat: only scalar (1x1 block) operands')
+        return bsr_matmat(A, B)
     if A.shape[1] != B.shape[0]:
         raise ValueError('dimension mismatch')
     n = A.shape[0]
@@ -231,7 +234,7 @@ def matmat(A, B, scipy_order=False, batch_products=None):
 def transpose(A):
     """A^T as CSR with rows ascending in the original row index (scipy csr_tocsc order)."""
     if not A.is_scalar:
-        raise NotImplementedError('transpose: only scalar (1x1 block) matrices')
+        return bsr_transpose(A)
     n_row, n_col = A.shape
     nnz = A.nnz
     dev = A.data.device
@@ -262,6 +265,8 @@ def galerkin(R, A, P, scipy_order=True, batch_nnz=None):
     Output rows depend on the matching rows of R only, so the product runs in batches of rows of R
     (about `batch_nnz` entries each): the intermediate R A never exists as a whole (at 512^3 it would
     not fit int32 indexing), the result is identical."""
+    if not (R.is_scalar and A.is_scalar and P.is_scalar):
+        return bsr_matmat(bsr_matmat(R, A), P)
     limit = int(batch_nnz or GALERKIN_BATCH_NNZ)
     n = R.shape[0]
     if R.nnz <= limit or n <= 1:
@@ -286,3 +291,70 @@ def galerkin(R, A, P, scipy_order=True, batch_nnz=None):
         raise _lib.B200AmgError('galerkin: result exceeds int32 indexing')
     Cp = torch.cat(cps + [torch.tensor([base], dtype=torch.int64, device=R.indptr.device)]).to(torch.int32)
     return DevMat(Cp, torch.cat(cjs), torch.cat(cxs), (R.shape[0], P.shape[1]), (1, 1), 'csr', not scipy_order)
+
+
+# ---- block (BSR) operands ------------------------------------------------------------------------------------
+def block_pattern(A, values=None):
+    """the block graph of a BSR matrix as a scalar CSR DevMat over the SAME index arrays (unit values, or `values`
+    per block)"""
+    v = torch.ones(A.nblocks, dtype=torch.float64, device=A.data.device) if values is None else values
+    return DevMat(A.indptr, A.indices, v, (A.n_brow, A.n_bcol), (1, 1), 'csr', A.has_sorted_indices)
+
+
+def is_canonical_pattern(A):
+    """scipy's csr_has_canonical_format on the (block) index arrays: every row strictly increasing in column"""
+    flag = torch.zeros(1, dtype=torch.int32, device=A.data.device)
+    _lib.call('b200amg_csr_not_canonical', A.n_brow, _ptr(A.indptr), _ptr(A.indices), _ptr(flag), _stream())
+    return int(flag.item()) == 0
+
+
+def bsr_matmat(A, B):
+    """C = A B on blocks (R x N) (N x C) with scipy bsr_matmat's result: blocks of a row in FIRST-TOUCH order, zero
+    blocks kept, every block summed in visiting order with separately rounded multiplies and adds.  The block pattern
+    is the scalar SpGEMM of the two block patterns (sorted for the lookups, csr_matmat order for the slots)."""
+    R, N = A.blocksize
+    N2, C = B.blocksize
+    if N != N2 or A.shape[1] != B.shape[0]:
+        raise ValueError('dimension mismatch')
+    pa, pb = block_pattern(A), block_pattern(B)
+    Ssorted = matmat(pa, pb, scipy_order=False)
+    Lorder = matmat(pa, pb, scipy_order=True)
+    if not torch.equal(Ssorted.indptr, Lorder.indptr):
+        raise _lib.B200AmgError('bsr_matmat: the two pattern products disagree')
+    nb = Ssorted.nnz
+    dev = A.data.device
+    st = _stream()
+    slot = torch.empty(max(nb, 1), dtype=torch.int32, device=dev)
+    Cj = torch.empty(nb, dtype=torch.int32, device=dev)
+    Cx = torch.empty(nb * R * C, dtype=torch.float64, device=dev)
+    _lib.call('b200amg_bsr_slot_map', A.n_brow, _ptr(Ssorted.indptr), _ptr(Ssorted.indices), _ptr(Lorder.indices),
+              _ptr(slot), _ptr(Cj), st)
+    _lib.call('b200amg_bsr_matmat_numeric', A.n_brow, R, N, C, _ptr(A.indptr), _ptr(A.indices), _ptr(A.data),
+              _ptr(B.indptr), _ptr(B.indices), _ptr(B.data), _ptr(Ssorted.indptr), _ptr(Ssorted.indices), _ptr(slot),
+              nb, _ptr(Cx), st)
+    return DevMat(Ssorted.indptr, Cj, Cx, (A.shape[0], B.shape[1]), (R, C), 'bsr', False)
+
+
+def _gather_blocks(A, perm, transpose_blocks):
+    out = torch.empty_like(A.data)
+    R, C = A.blocksize
+    _lib.call('b200amg_bsr_gather_blocks', A.nblocks, R, C, _ptr(perm), _ptr(A.data), _ptr(out),
+              int(bool(transpose_blocks)), _stream())
+    return out
+
+
+def bsr_transpose(A):
+    """scipy bsr_transpose: csr_tocsc on the block numbers, every block transposed"""
+    ids = torch.arange(A.nblocks, dtype=torch.float64, device=A.data.device)
+    T = transpose(block_pattern(A, ids))
+    R, C = A.blocksize
+    return DevMat(T.indptr, T.indices, _gather_blocks(A, T.data, True), (A.shape[1], A.shape[0]), (C, R), 'bsr', True)
+
+
+def bsr_sort_indices(A):
+    """blocks of every row ascending in column (scipy bsr sort_indices; stable, rows hold no duplicates)"""
+    if A.has_sorted_indices:
+        return A
+    ids = torch.arange(A.nblocks, dtype=torch.float64, device=A.data.device)
+    S = transpose(transpose(block_pattern(A, ids)))
+    return DevMat(S.indptr, S.indices, _gather_blocks(A, S.data, False), A.shape, A.blocksize, 'bsr', True)

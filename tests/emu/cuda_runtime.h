@@ -1,0 +1,81 @@
+// TEST INFRASTRUCTURE ONLY -- a stand-in for <cuda_runtime.h> that lets g++ compile a libb200amg kernel source
+// (pyamg_b200/csrc/*.cu, unchanged) for the HOST, so that thread-per-row / warp-per-row kernels can be checked
+// against scipy in this GPU-less container before they ever see hardware (tests/test_emulated_kernels.py).
+// Every CUDA thread of a block is a real OS thread; __syncthreads / __syncwarp are barriers; blocks run one after
+// the other.  Supports what the setup kernels use: no shuffles, no shared memory, no atomics.  The product never
+// loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
+#pragma once
+#include <barrier>
+#include <cmath>
+#include <cstddef>
+#include <cstring>
+#include <memory>
+#include <thread>
+#include <vector>
+
+struct dim3 { unsigned x = 1, y = 1, z = 1; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
+struct uint3emu { unsigned x, y, z; };
+inline thread_local uint3emu threadIdx, blockIdx;
+inline thread_local dim3 blockDim, gridDim;
+
+typedef int cudaError_t;
+typedef void *cudaStream_t;
+enum { cudaSuccess = 0 };
+inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
+inline cudaError_t cudaMemsetAsync(void *p, int v, size_t n, cudaStream_t) { memset(p, v, n); return cudaSuccess; }
+
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __launch_bounds__(...)
+#define __align__(n) alignas(n)
+
+// separately rounded arithmetic: the volatile keeps the compiler from contracting or reassociating
+inline double __dmul_rn(double a, double b) { volatile double r = a * b; return r; }
+inline double __dadd_rn(double a, double b) { volatile double r = a + b; return r; }
+inline double __dsub_rn(double a, double b) { volatile double r = a - b; return r; }
+inline double __ddiv_rn(double a, double b) { volatile double r = a / b; return r; }
+
+namespace cuda_emu {
+struct BlockSync {
+    std::barrier<> block;
+    std::vector<std::unique_ptr<std::barrier<>>> warp;
+    explicit BlockSync(int nthreads) : block(nthreads) {
+        for (int w = 0; w < (nthreads + 31) / 32; ++w)
+            warp.emplace_back(new std::barrier<>(std::min(32, nthreads - 32 * w)));
+    }
+};
+inline thread_local BlockSync *cur = nullptr;
+
+template <class F>
+void launch(dim3 grid, dim3 block, F body)
+{
+    const int nt = (int)block.x;
+    for (unsigned b = 0; b < grid.x; ++b) {
+        BlockSync sync(nt);
+        std::vector<std::thread> ts;
+        ts.reserve(nt);
+        for (int t = 0; t < nt; ++t)
+            ts.emplace_back([&, t] {
+                threadIdx = {(unsigned)t, 0, 0};
+                blockIdx = {b, 0, 0};
+                blockDim = block;
+                gridDim = grid;
+                cur = &sync;
+                body();
+                // a thread that has left the kernel no longer takes part in barriers
+                sync.warp[t / 32]->arrive_and_drop();
+                sync.block.arrive_and_drop();
+            });
+        for (auto &th : ts) th.join();
+    }
+}
+}  // namespace cuda_emu
+
+inline void __syncthreads() { cuda_emu::cur->block.arrive_and_wait(); }
+inline void __syncwarp(unsigned = 0xffffffffu) { cuda_emu::cur->warp[threadIdx.x / 32]->arrive_and_wait(); }
+
+#define B200_LAUNCH(kernel, grid, block, smem, stream, ...) \
+    cuda_emu::launch(dim3(grid), dim3(block), [&] { kernel(__VA_ARGS__); })

@@ -115,7 +115,7 @@ def tet_grid(nv):
     return V, np.array(E)
 
 
-def sa_elasticity3d(name, nv):
+def sa_elasticity3d(name, nv, improve=True):
     """BASELINE config 4 in miniature: P1 tetrahedral elasticity (linear_elasticity_p1, E = 1e5, nu = 0.3), the face
     x = 0 clamped by eliminating its block rows / columns, SA with the 6 rigid-body modes and symmetric Gauss-Seidel:
     level 0 is BSR 3x3, the coarse levels BSR 6x6, P is 3x6 / 6x6 -- the block shapes of the full-size problem."""
@@ -129,10 +129,17 @@ def sa_elasticity3d(name, nv):
     B = B[dof]
     np.random.seed(0)
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
-    ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    extra = {}
+    if improve:
+        ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    else:
+        # the SETUP fixture: candidates as given (improve_candidates=None, the option the device setup has), B kept
+        ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10,
+                                               improve_candidates=None)
+        extra['B'] = B
     b, res, x = run(ml, A.shape[0], 8)
     specs = [((('gauss_seidel', {'sweep': 'symmetric', 'iterations': 1}),) * 2) for _ in ml.levels[:-1]]
-    hier_io.save(os.path.join(OUT, name), ml.levels, specs, {'b': b, 'residuals': res, 'x': x})
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, dict(extra, b=b, residuals=res, x=x))
     print(name, [(l.A.shape[0], l.A.format, getattr(l.A, 'blocksize', None)) for l in ml.levels],
           [getattr(l, 'P', None) is not None and l.P.blocksize for l in ml.levels], res[0], res[-1])
 
@@ -201,6 +208,9 @@ def sa_elasticity(name, grid):
 
 
 if __name__ == '__main__':
+    if sys.argv[1:] == ['elasticity3d_setup']:           # only the fixture added last (the others are unchanged)
+        sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
+        sys.exit(0)
     sa_poisson('sa_poisson3d_12.npz', (12, 12, 12), 20, improve=False)
     sa_poisson('sa_poisson3d_16_default.npz', (16, 16, 16), 30, improve=True)
     rs_mcgs('rs_poisson2d_40_mcgs.npz', poisson((40, 40), format='csr'), 20)
@@ -209,3 +219,4 @@ if __name__ == '__main__':
     sa_elasticity('sa_elasticity2d_14.npz', (14, 14))
     sa_chebyshev('sa_poisson3d_12_chebyshev.npz', (12, 12, 12), 20)
     sa_elasticity3d('sa_elasticity3d_tets_7.npz', 7)
+    sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)

@@ -1,0 +1,153 @@
+"""pyamg_b200.smoothed_aggregation_solver's BLOCK path run end to end in this GPU-less container, to check the Python
+orchestration (argument order of every new C-ABI call, shapes, level loop) before hardware sees it:
+
+  * the new entry points (csrc/bsr_setup.cu) are served by that source compiled for the host (tests/emu);
+  * the scalar building blocks already pinned on the GPU (SpGEMM, transpose, scan, diagonal, ...) are replaced by
+    scipy / numpy doubles;
+  * tensors are torch CPU tensors, so every `data_ptr()` is a host pointer.
+
+All of this is monkeypatching inside the test: the product itself still raises without a CUDA device
+(tests/test_cabi.py::test_no_cpu_fallback_without_cuda)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+import hier_io
+from oracle import sa as osa
+from test_emulated_kernels import emu, same  # noqa: F401  (the host-compiled kernel source)
+
+
+def _arr(ptr, n, ctype):
+    return np.ctypeslib.as_array((ctype * n).from_address(ptr)) if n else np.zeros(0, dtype=ctype)
+
+
+@pytest.fixture()
+def host_amg(emu, monkeypatch):  # noqa: F811
+    import pyamg_b200 as amg
+    from pyamg_b200 import _lib, aggregation, linalg, multilevel, smoothing, sparse
+    DevMat = sparse.DevMat
+    cpu = torch.device('cpu')
+    for mod in (sparse, aggregation, linalg, multilevel, smoothing):
+        if hasattr(mod, '_dev'):
+            monkeypatch.setattr(mod, '_dev', lambda: cpu)
+        if hasattr(mod, '_stream'):
+            monkeypatch.setattr(mod, '_stream', lambda: 0)
+    emu_names = ('b200amg_bsr_scale_rows', 'b200amg_bsr_gather_blocks', 'b200amg_fit_candidates', 'b200amg_tentative_scatter',
+                 'b200amg_bsr_sub', 'b200amg_bsr_slot_map', 'b200amg_bsr_matmat_numeric')
+    for name in emu_names:                                  # bind exactly the product's signature table
+        f = getattr(emu, name)
+        f.restype, f.argtypes = _lib._SIGS[name]
+    real_call = _lib.call
+    seen = set()
+
+    def call(name, *args):
+        seen.add(name)
+        if name in emu_names:
+            rc = getattr(emu, name)(*args)
+            assert rc == 0, name
+        elif name == 'b200amg_flag_nonneg':
+            n, agg, flag, _ = args
+            _arr(flag, n, ctypes.c_int)[:] = _arr(agg, n, ctypes.c_int) >= 0
+        elif name == 'b200amg_tentative_fill':
+            n, agg, val, Tp, Tj, Tx, _ = args
+            a, tp = _arr(agg, n, ctypes.c_int), _arr(Tp, n + 1, ctypes.c_int)
+            keep = a >= 0
+            _arr(Tj, int(tp[-1]), ctypes.c_int)[:] = a[keep]
+            _arr(Tx, int(tp[-1]), ctypes.c_double)[:] = _arr(val, n, ctypes.c_double)[keep]
+        elif name == 'b200amg_extract_diag':
+            nb, bs, Ap, Aj, Ax, d, _ = args
+            ap = _arr(Ap, nb + 1, ctypes.c_int)
+            M = sp.bsr_matrix((_arr(Ax, int(ap[-1]) * bs * bs, ctypes.c_double).reshape(-1, bs, bs),
+                               _arr(Aj, int(ap[-1]), ctypes.c_int), ap), shape=(nb * bs, nb * bs))
+            _arr(d, nb * bs, ctypes.c_double)[:] = M.diagonal()
+        elif name == 'b200amg_csr_not_canonical':
+            n, Ap, Aj, flag, _ = args
+            ap = _arr(Ap, n + 1, ctypes.c_int)
+            aj = _arr(Aj, int(ap[-1]), ctypes.c_int)
+            bad = any(np.any(np.diff(aj[ap[i]:ap[i + 1]]) <= 0) for i in range(n))
+            _arr(flag, 1, ctypes.c_int)[0] = int(bad)
+        else:
+            real_call(name, *args)                          # host entry points of the real library (aggregation, colouring)
+
+    monkeypatch.setattr(_lib, 'call', call)
+
+    def scan(v):
+        out = torch.zeros(v.numel() + 1, dtype=torch.int32)
+        out[1:] = torch.cumsum(v.to(torch.int64), 0).to(torch.int32)
+        return out
+    monkeypatch.setattr(sparse, '_scan_i32', scan)
+    monkeypatch.setattr(aggregation, '_scan_i32', scan)
+
+    def from_sp(M, fmt, sorted_flag):
+        return DevMat(torch.from_numpy(np.ascontiguousarray(M.indptr, np.int32)), torch.from_numpy(np.ascontiguousarray(M.indices, np.int32)),
+                      torch.from_numpy(np.ascontiguousarray(M.data, np.float64)), M.shape, (1, 1), fmt, sorted_flag)
+
+    real_bsr_matmat, real_bsr_transpose = sparse.bsr_matmat, sparse.bsr_transpose
+
+    def matmat(A, B, scipy_order=False, batch_products=None):
+        if not (A.is_scalar and B.is_scalar):
+            return real_bsr_matmat(A, B)
+        C = sp.csr_matrix(A.to_scipy()) * sp.csr_matrix(B.to_scipy())        # csr_matmat: reverse first-touch rows
+        if not scipy_order:
+            C.sort_indices()
+        return from_sp(C, 'csr', not scipy_order)
+
+    def transpose(A):
+        if not A.is_scalar:
+            return real_bsr_transpose(A)
+        T = sp.csr_matrix(A.to_scipy()).tocsc()
+        return DevMat(torch.from_numpy(np.ascontiguousarray(T.indptr, np.int32)), torch.from_numpy(np.ascontiguousarray(T.indices, np.int32)),
+                      torch.from_numpy(np.ascontiguousarray(T.data, np.float64)), (A.shape[1], A.shape[0]), (1, 1), A.format, True)
+
+    for mod in (sparse, aggregation):
+        monkeypatch.setattr(mod, 'matmat', matmat)
+        monkeypatch.setattr(mod, 'transpose', transpose)
+    amg._seen_calls = seen
+    return amg
+
+
+def test_block_path_builds_the_reference_hierarchy(host_amg, golden_dir):
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))
+    A, B = levels[0].A, ex['B']
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    rhos = [(l.rho_smooth, None) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    assert len(ml.levels) == len(levels) == 3
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    assert [l.A.blocksize for l in ml.levels] == [(3, 3), (6, 6), (6, 6)]
+    assert {'b200amg_fit_candidates', 'b200amg_tentative_scatter', 'b200amg_bsr_scale_rows', 'b200amg_bsr_sub',
+            'b200amg_bsr_slot_map', 'b200amg_bsr_matmat_numeric', 'b200amg_bsr_gather_blocks'} <= amg._seen_calls
+
+
+def test_block_path_default_candidates_and_argument_checks(host_amg, golden_dir):
+    """B=None -> one constant per unknown of a node (K2 = blocksize); the options without a device path raise"""
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity2d_14.npz'))
+    A = levels[0].A
+    assert A.format == 'bsr' and A.blocksize == (2, 2)
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10)
+    rhos = [(l.rho_smooth, None) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    assert len(ml.levels) == len(ref)
+    for k, (m, r) in enumerate(zip(ml.levels, ref)):
+        for nm in ('A', 'P', 'R'):
+            if getattr(r, nm, None) is not None:
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    with pytest.raises(NotImplementedError):
+        amg.smoothed_aggregation_solver(A, strength=None)
+    with pytest.raises(NotImplementedError):
+        amg.smoothed_aggregation_solver(sp.csr_matrix(A), np.ones((A.shape[0], 2)))
+    with pytest.raises(ValueError):
+        amg.smoothed_aggregation_solver(A, np.ones((A.shape[0] + 2, 3)))

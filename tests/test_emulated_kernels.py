@@ -1,0 +1,312 @@
+"""Pre-hardware check of the block (BSR) setup kernels: pyamg_b200/csrc/bsr_setup.cu is compiled UNCHANGED for the host
+with tests/emu/cuda_runtime.h (every CUDA thread an OS thread, __syncwarp a barrier) and every entry point is compared
+bit for bit with scipy / the reference's amg_core on small block matrices, then a whole block smoothed-aggregation
+hierarchy is assembled from the emulated kernels and compared with the fixture the REAL reference produced
+(tests/golden/sa_elasticity3d_tets_7_setup.npz).
+
+This is test infrastructure: the emulated library takes host pointers and is never loaded by pyamg_b200.  It checks the
+kernel SOURCE (indexing, operation order, storage order) -- launch geometry and device behaviour are what the
+`-m gpu` tests check on hardware."""
+import ctypes
+import os
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import hier_io
+import oracle
+from oracle import sa as osa
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+EMU = os.path.join(HERE, 'emu')
+c_int, c_ll, c_dbl, vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_double, ctypes.c_void_p
+
+
+@pytest.fixture(scope='module')
+def emu():
+    if shutil.which('g++') is None:
+        pytest.skip('g++ not available')
+    out = os.path.join(EMU, '_build', 'libemu_bsr_setup.so')
+    src = os.path.join(ROOT, 'pyamg_b200', 'csrc', 'bsr_setup.cu')
+    deps = [src, os.path.join(EMU, 'cuda_runtime.h'), os.path.join(EMU, 'emu_globals.cpp'),
+            os.path.join(ROOT, 'pyamg_b200', 'csrc', 'common.cuh'), os.path.join(ROOT, 'include', 'b200amg.h')]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU,
+                        '-x', 'c++', src, os.path.join(EMU, 'emu_globals.cpp'), '-o', out], check=True)
+    lib = ctypes.CDLL(out)
+    sigs = {
+        'b200amg_bsr_scale_rows': [c_int, c_int, c_int, vp, vp, vp, c_dbl, c_int, vp, vp],
+        'b200amg_bsr_gather_blocks': [c_ll, c_int, c_int, vp, vp, vp, c_int, vp],
+        'b200amg_fit_candidates': [c_int, c_int, c_int, vp, vp, vp, c_dbl, vp, vp, vp],
+        'b200amg_tentative_scatter': [c_ll, c_int, c_int, vp, vp, vp, vp, vp],
+        'b200amg_bsr_sub': [c_int, c_int, c_int, vp, vp, vp, vp, vp, vp, c_int, c_int, vp, vp, vp, vp, vp],
+        'b200amg_bsr_slot_map': [c_int, vp, vp, vp, vp, vp, vp],
+        'b200amg_bsr_matmat_numeric': [c_int, c_int, c_int, c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_ll, vp, vp],
+    }
+    for name, args in sigs.items():
+        f = getattr(lib, name)
+        f.restype, f.argtypes = c_int, args
+    # the signatures used here are the ones the product binds (pyamg_b200/_lib.py)
+    from pyamg_b200 import _lib
+    for name, args in sigs.items():
+        assert len(_lib._SIGS[name][1]) == len(args), name
+    return lib
+
+
+def P(a):
+    return a.ctypes.data if a is not None else 0
+
+
+def i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+# ---- host mirrors of the product's Python orchestration (pyamg_b200/sparse.py, aggregation.py) -----------------
+def pattern(M):
+    return sp.csr_matrix((np.ones(len(M.indices)), M.indices, M.indptr), shape=(M.shape[0] // M.blocksize[0],
+                                                                                 M.shape[1] // M.blocksize[1]))
+
+
+def emu_bsr_matmat(lib, A, B):
+    """sparse.bsr_matmat: pattern = scalar SpGEMM of the block patterns (scipy's csr_matmat here; the device's own
+    SpGEMM is pinned to it bit for bit by tests/test_gpu_kernels.py), blocks by slot_map + numeric"""
+    R, N = A.blocksize
+    _, C = B.blocksize
+    L = pattern(A) * pattern(B)                          # csr_matmat order = reverse first touch
+    Ssorted = L.copy()
+    Ssorted.sort_indices()
+    Cp, Sj, Lj = i32(L.indptr), i32(Ssorted.indices), i32(L.indices)
+    nb = len(Lj)
+    slot, Cj = np.full(nb, -1, np.int32), np.full(nb, -1, np.int32)
+    Cx = np.full(nb * R * C, np.nan)
+    nbrow = A.shape[0] // R
+    assert lib.b200amg_bsr_slot_map(nbrow, P(Cp), P(Sj), P(Lj), P(slot), P(Cj), None) == 0
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ascontiguousarray(A.data).ravel()
+    Bp, Bj, Bx = i32(B.indptr), i32(B.indices), np.ascontiguousarray(B.data).ravel()
+    assert lib.b200amg_bsr_matmat_numeric(nbrow, R, N, C, P(Ap), P(Aj), P(Ax), P(Bp), P(Bj), P(Bx), P(Cp), P(Sj), P(slot),
+                                          nb, P(Cx), None) == 0
+    return sp.bsr_matrix((Cx.reshape(-1, R, C), Cj, Cp), shape=(A.shape[0], B.shape[1]), blocksize=(R, C))
+
+
+def canonical(M):
+    return all(np.all(np.diff(M.indices[M.indptr[i]:M.indptr[i + 1]]) > 0) for i in range(len(M.indptr) - 1))
+
+
+def emu_bsr_sub(lib, A, B):
+    R, C = A.blocksize
+    n = A.shape[0] // R
+    general = int(not (canonical(A) and canonical(B)))
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ascontiguousarray(A.data).ravel()
+    Bp, Bj, Bx = i32(B.indptr), i32(B.indices), np.ascontiguousarray(B.data).ravel()
+    cnt = np.zeros(n, np.int32)
+    assert lib.b200amg_bsr_sub(n, R, C, P(Ap), P(Aj), P(Ax), P(Bp), P(Bj), P(Bx), general, 0, P(cnt), None, None, None, None) == 0
+    Cp = i32(np.concatenate([[0], np.cumsum(cnt)]))
+    Cj = np.full(Cp[-1], -1, np.int32)
+    Cx = np.full(Cp[-1] * R * C, np.nan)
+    assert lib.b200amg_bsr_sub(n, R, C, P(Ap), P(Aj), P(Ax), P(Bp), P(Bj), P(Bx), general, 1, None, P(Cp), P(Cj), P(Cx), None) == 0
+    return sp.bsr_matrix((Cx.reshape(-1, R, C), Cj, Cp), shape=A.shape, blocksize=(R, C))
+
+
+def emu_gather(lib, A, perm, tr):
+    R, C = A.blocksize
+    data = np.ascontiguousarray(A.data).ravel()
+    out = np.full_like(data, np.nan)
+    permd = np.ascontiguousarray(perm, dtype=np.float64)
+    assert lib.b200amg_bsr_gather_blocks(len(perm), R, C, P(permd), P(data), P(out), int(tr), None) == 0
+    return out
+
+
+def emu_bsr_transpose(lib, A):
+    """sparse.bsr_transpose: csr_tocsc over block numbers (scipy here), then the block gather + transpose"""
+    R, C = A.blocksize
+    ids = sp.csr_matrix((np.arange(len(A.indices), dtype=np.float64), A.indices, A.indptr),
+                        shape=(A.shape[0] // R, A.shape[1] // C))
+    T = ids.tocsc()                                      # (indptr, indices, data) of the CSC = CSR of the transpose
+    out = emu_gather(lib, A, T.data, True)
+    return sp.bsr_matrix((out.reshape(-1, C, R), i32(T.indices), i32(T.indptr)), shape=(A.shape[1], A.shape[0]), blocksize=(C, R))
+
+
+def emu_bsr_sort(lib, A):
+    R, C = A.blocksize
+    ids = sp.csr_matrix((np.arange(len(A.indices), dtype=np.float64), A.indices.copy(), A.indptr.copy()),
+                        shape=(A.shape[0] // R, A.shape[1] // C))
+    ids.sort_indices()
+    out = emu_gather(lib, A, ids.data, False)
+    return sp.bsr_matrix((out.reshape(-1, R, C), i32(ids.indices), i32(ids.indptr)), shape=A.shape, blocksize=(R, C))
+
+
+def emu_scale_rows(lib, A, v, c=None):
+    R, C = A.blocksize
+    data = np.ascontiguousarray(A.data).ravel()
+    out = np.full_like(data, np.nan)
+    Ap = i32(A.indptr)
+    v = np.ascontiguousarray(v, dtype=np.float64)
+    assert lib.b200amg_bsr_scale_rows(A.shape[0] // R, R, C, P(Ap), P(data), P(v), 0.0 if c is None else float(c),
+                                      0 if c is None else 1, P(out), None) == 0
+    return sp.bsr_matrix((out.reshape(-1, R, C), A.indices, A.indptr), shape=A.shape, blocksize=(R, C))
+
+
+def emu_fit_candidates(lib, agg, nagg, B, K1, K2, tol=1e-10):
+    """aggregation.fit_candidates_block"""
+    n = len(agg)
+    keep = agg >= 0
+    AggOp = sp.csr_matrix((np.ones(keep.sum()), agg[keep], np.concatenate([[0], np.cumsum(keep)])), shape=(n, nagg))
+    M = AggOp.tocsc()
+    Mp, Mi = i32(M.indptr), i32(M.indices)
+    nmem = len(Mi)
+    Bf = np.ascontiguousarray(B, dtype=np.float64).ravel()
+    Qx = np.full(nmem * K1 * K2, np.nan)
+    Rx = np.full(nagg * K2 * K2, np.nan)
+    assert lib.b200amg_fit_candidates(nagg, K1, K2, P(Mp), P(Mi), P(Bf), tol, P(Qx), P(Rx), None) == 0
+    Tp = i32(AggOp.indptr)
+    Tx = np.full(nmem * K1 * K2, np.nan)
+    assert lib.b200amg_tentative_scatter(nmem, K1, K2, P(Mi), P(Tp), P(Qx), P(Tx), None) == 0
+    T = sp.bsr_matrix((Tx.reshape(-1, K1, K2), i32(AggOp.indices), Tp), shape=(n * K1, nagg * K2), blocksize=(K1, K2))
+    return T, Rx.reshape(-1, K2)
+
+
+def same(M, Rf):
+    return (M.format == Rf.format and M.blocksize == Rf.blocksize and M.shape == Rf.shape
+            and np.array_equal(M.indptr, Rf.indptr) and np.array_equal(M.indices, Rf.indices)
+            and np.array_equal(np.ravel(M.data), np.ravel(Rf.data)))
+
+
+def random_bsr(nbr, nbc, R, C, density, seed, unsorted=False):
+    rng = np.random.RandomState(seed)
+    pat = sp.random(nbr, nbc, density=density, format='csr', random_state=rng)
+    pat.sort_indices()
+    indptr, indices = pat.indptr.astype(np.int32), pat.indices.astype(np.int32)
+    if unsorted:
+        for i in range(nbr):
+            seg = indices[indptr[i]:indptr[i + 1]]
+            indices[indptr[i]:indptr[i + 1]] = seg[rng.permutation(len(seg))]
+    data = rng.randn(len(indices), R, C)
+    data[rng.rand(*data.shape) < 0.2] = 0.0                 # exact zeros inside blocks
+    return sp.bsr_matrix((data, indices, indptr), shape=(nbr * R, nbc * C), blocksize=(R, C))
+
+
+# ---- entry points against scipy ----------------------------------------------------------------------------------
+@pytest.mark.parametrize('R,N,C', [(3, 3, 6), (6, 3, 3), (6, 3, 6), (2, 2, 3), (6, 6, 6), (1, 2, 1)])
+def test_bsr_matmat_equals_scipy(emu, R, N, C):
+    """first-touch block order, zero blocks kept, visiting-order sums: identical arrays to scipy's bsr_matmat, for
+    sorted and unsorted operands"""
+    for seed, unsorted in ((1, False), (2, True)):
+        A = random_bsr(37, 29, R, N, 0.2, seed, unsorted)
+        B = random_bsr(29, 41, N, C, 0.15, seed + 10, unsorted)
+        ref = A * B
+        assert ref.format == 'bsr' and ref.blocksize == (R, C)
+        assert same(emu_bsr_matmat(emu, A, B), ref)
+
+
+def test_bsr_matmat_keeps_zero_blocks_and_empty_rows(emu):
+    A = random_bsr(12, 9, 2, 2, 0.3, 5)
+    B = random_bsr(9, 7, 2, 2, 0.3, 6)
+    B.data[:] = 0.0                                         # every product block is exactly zero: scipy keeps them
+    A.data[A.indptr[3]:A.indptr[4]] = 0.0
+    ref = A * B
+    got = emu_bsr_matmat(emu, A, B)
+    assert same(got, ref) and len(ref.indices) > 0
+    E = sp.bsr_matrix((12 * 2, 9 * 2), blocksize=(2, 2))
+    assert same(emu_bsr_matmat(emu, E, B), E * B)
+
+
+@pytest.mark.parametrize('R,C', [(3, 6), (6, 6), (2, 3)])
+def test_bsr_sub_equals_scipy(emu, R, C):
+    """general (reverse first-touch) and canonical (merge) forms of scipy's bsr_binop_bsr, dropped zero blocks included"""
+    for seed, unsorted in ((3, True), (4, False)):
+        A = random_bsr(40, 23, R, C, 0.08, seed, False)
+        B = random_bsr(40, 23, R, C, 0.2, seed + 20, unsorted)
+        # make some blocks cancel exactly (same column, same values) and some rows empty
+        Bl = B.tolil() if False else B
+        for i in range(0, 40, 5):
+            a0, a1 = A.indptr[i], A.indptr[i + 1]
+            b0, b1 = B.indptr[i], B.indptr[i + 1]
+            common = np.intersect1d(A.indices[a0:a1], B.indices[b0:b1])
+            for col in common:
+                pa = a0 + int(np.where(A.indices[a0:a1] == col)[0][0])
+                pb = b0 + int(np.where(B.indices[b0:b1] == col)[0][0])
+                B.data[pb] = A.data[pa]
+        ref = A - B
+        assert same(emu_bsr_sub(emu, A, B), ref), (seed, unsorted)
+    assert canonical(random_bsr(40, 23, R, C, 0.2, 24, False)) and not canonical(random_bsr(40, 23, R, C, 0.2, 23, True))
+
+
+def test_bsr_transpose_sort_scale_equal_scipy(emu):
+    A = random_bsr(31, 17, 3, 6, 0.25, 7, unsorted=True)
+    T = A.T
+    assert T.format == 'bsr' and same(emu_bsr_transpose(emu, A), T)
+    Ssrt = A.copy()
+    Ssrt.sort_indices()
+    assert same(emu_bsr_sort(emu, A), Ssrt)
+    Sq = random_bsr(20, 20, 3, 3, 0.3, 8)
+    v = np.random.RandomState(0).rand(60)
+    assert same(emu_scale_rows(emu, Sq, v), osa.scale_rows(Sq, v))
+    ref = 0.37 * osa.scale_rows(Sq, v)
+    assert same(emu_scale_rows(emu, Sq, v, 0.37), ref)
+
+
+@pytest.mark.parametrize('K1,K2', [(3, 6), (6, 6), (2, 3), (1, 1), (1, 2)])
+def test_fit_candidates_equals_reference_kernel(emu, K1, K2):
+    """amg_core.fit_candidates (the reference's compiled kernel when built, else the C port) incl. unaggregated nodes,
+    dependent candidates (dropped by the tolerance) and single-node aggregates"""
+    rng = np.random.RandomState(K1 * 10 + K2)
+    n, nagg = 57, 9
+    agg = rng.randint(0, nagg, n).astype(np.int32)
+    agg[[4, 19]] = -1                                       # not aggregated
+    agg[agg == 8] = 7
+    agg[5] = 8                                              # aggregate 8 = one node
+    B = rng.randn(n * K1, K2)
+    if K2 > 1:
+        B[:, 1] = 2.0 * B[:, 0]                             # numerically dependent second candidate
+    keep = agg >= 0
+    AggOp = sp.csr_matrix((np.ones(keep.sum(), 'int8'), agg[keep], np.concatenate([[0], np.cumsum(keep)]).astype(np.int32)),
+                          shape=(n, nagg))
+    for core in ([oracle.ref] if oracle.ref is not None else []) + [oracle.port]:
+        Tref, Rref = osa.fit_candidates(AggOp, B, core=core)
+        T, Rc = emu_fit_candidates(emu, agg, nagg, B, K1, K2)
+        assert same(T, Tref)
+        assert np.array_equal(Rc, Rref)
+
+
+# ---- the whole block hierarchy from the emulated kernels ------------------------------------------------------------
+def test_block_sa_hierarchy_equals_reference_fixture(emu, golden_dir):
+    """pyamg_b200.aggregation's block path, step for step, on the kernels' source: A, P, R of every level equal the arrays
+    the REAL reference built for P1 tetrahedral elasticity (BSR 3x3 -> 6x6, six rigid-body modes), given the reference's
+    spectral-radius estimates (an unconverged Krylov number, fed like in test_sa_setup_matches_reference)."""
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))
+    A, B = levels[0].A, ex['B']
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    assert len(ref) == len(levels) == 3
+    K2 = B.shape[1]
+    cur_A, cur_B = A.copy(), B
+    omega = 4.0 / 3.0
+    for k in range(len(levels) - 1):
+        K1 = cur_A.blocksize[0]
+        nb = cur_A.shape[0] // K1
+        agg = np.empty(nb, np.int32)
+        roots = np.empty(nb, np.int32)
+        nagg = oracle.core.standard_aggregation(nb, i32(cur_A.indptr), i32(cur_A.indices), agg, roots)   # host in the product too
+        T, Bc = emu_fit_candidates(emu, agg, nagg, cur_B, K1, K2)
+        assert same(T, ref[k].T)
+        cur_A = emu_bsr_sort(emu, cur_A)                   # get_diagonal's in-place sort: what the reference keeps as A
+        assert same(cur_A, levels[k].A), k
+        d = cur_A.diagonal()
+        dinv = np.where(d != 0, 1.0 / np.where(d != 0, d, 1.0), 0.0)
+        S = emu_scale_rows(emu, cur_A, dinv, omega / ref[k].rho_smooth)
+        U = emu_bsr_matmat(emu, S, T)
+        Pk = emu_bsr_sub(emu, T, U)
+        Rk = emu_bsr_transpose(emu, Pk)
+        Ac = emu_bsr_matmat(emu, emu_bsr_matmat(emu, Rk, cur_A), Pk)
+        for got, name in ((Pk, 'P'), (Rk, 'R')):
+            assert same(got, getattr(levels[k], name)), (k, name)
+        assert np.array_equal(Bc, ref[k + 1].B)
+        cur_A, cur_B = Ac, Bc
+    assert same(cur_A, levels[-1].A)                       # the coarsest operator stays in bsr_matmat's first-touch order

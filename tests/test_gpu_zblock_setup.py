@@ -1,0 +1,130 @@
+"""GPU parity tests (-m gpu) of the block (BSR) smoothed-aggregation setup -- BASELINE config 4's setup path:
+csrc/bsr_setup.cu through pyamg_b200.sparse / pyamg_b200.aggregation against scipy's bsr kernels, the reference's
+amg_core.fit_candidates and the hierarchy the REAL reference built (tests/golden/sa_elasticity3d_tets_7_setup.npz).
+
+These tests were written after round 1's GPU minutes were spent.  Until their first hardware run the same kernel
+source is checked on the host (tests/test_emulated_kernels.py: bit-identical to scipy / the reference fixture) and the
+Python orchestration with it (tests/test_block_setup_host_logic.py); hence the non-strict xfail marker: a pass shows up
+as XPASS, a device-only defect does not hide the rest of the suite.  Remove the marker after the first green run."""
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+torch = pytest.importorskip('torch')
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.xfail(strict=False, reason='first hardware run pending (written after the round-1 GPU budget '
+                                                     'was spent); host emulation of the same kernel source is green')]
+
+import oracle
+from oracle import multilevel as oml, sa as osa
+import hier_io
+from test_emulated_kernels import random_bsr, same
+
+RTOL = 1e-12
+
+
+@pytest.fixture(scope='module')
+def amg():
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    import pyamg_b200
+    return pyamg_b200
+
+
+def D(amg, M):
+    return amg.sparse.DevMat.from_scipy(M)
+
+
+@pytest.mark.parametrize('R,N,C', [(3, 3, 6), (6, 3, 3), (6, 3, 6), (2, 2, 3), (6, 6, 6), (1, 2, 1)])
+def test_bsr_matmat_equals_scipy(amg, R, N, C):
+    for seed, unsorted in ((1, False), (2, True)):
+        A = random_bsr(370, 290, R, N, 0.03, seed, unsorted)
+        B = random_bsr(290, 410, N, C, 0.03, seed + 10, unsorted)
+        assert same(amg.sparse.bsr_matmat(D(amg, A), D(amg, B)).to_scipy(), A * B)
+    # long rows: more output blocks per row than a warp has lanes, several visits per output block
+    A = random_bsr(40, 60, R, N, 0.6, 3, True)
+    B = random_bsr(60, 90, N, C, 0.5, 4, True)
+    assert same(amg.sparse.bsr_matmat(D(amg, A), D(amg, B)).to_scipy(), A * B)
+    Z = B.copy()
+    Z.data[:] = 0.0                                         # zero blocks are kept
+    assert same(amg.sparse.bsr_matmat(D(amg, A), D(amg, Z)).to_scipy(), A * Z)
+
+
+def test_bsr_transpose_sort_subtract_equal_scipy(amg):
+    A = random_bsr(310, 170, 3, 6, 0.05, 7, unsorted=True)
+    assert same(amg.sparse.transpose(D(amg, A)).to_scipy(), A.T)
+    S = A.copy()
+    S.sort_indices()
+    assert same(amg.sparse.bsr_sort_indices(D(amg, A)).to_scipy(), S)
+    for seed, unsorted in ((3, True), (4, False)):
+        T = random_bsr(400, 230, 3, 6, 0.01, seed, False)
+        U = random_bsr(400, 230, 3, 6, 0.03, seed + 20, unsorted)
+        for i in range(0, 400, 5):                          # blocks that cancel exactly are dropped
+            a0, a1, b0, b1 = T.indptr[i], T.indptr[i + 1], U.indptr[i], U.indptr[i + 1]
+            for col in np.intersect1d(T.indices[a0:a1], U.indices[b0:b1]):
+                U.data[b0 + int(np.where(U.indices[b0:b1] == col)[0][0])] = T.data[a0 + int(np.where(T.indices[a0:a1] == col)[0][0])]
+        assert same(amg.aggregation.bsr_subtract(D(amg, T), D(amg, U)).to_scipy(), T - U), (seed, unsorted)
+
+
+@pytest.mark.parametrize('K1,K2', [(3, 6), (6, 6), (2, 3), (1, 2)])
+def test_fit_candidates_equals_reference_kernel(amg, K1, K2):
+    rng = np.random.RandomState(K1 * 10 + K2)
+    n, nagg = 5700, 900
+    agg = rng.randint(0, nagg, n).astype(np.int32)
+    agg[[4, 19]] = -1
+    B = rng.randn(n * K1, K2)
+    B[:, 1] = 2.0 * B[:, 0]
+    keep = agg >= 0
+    AggOp = sp.csr_matrix((np.ones(keep.sum(), 'int8'), agg[keep], np.concatenate([[0], np.cumsum(keep)]).astype(np.int32)),
+                          shape=(n, nagg))
+    Tref, Rref = osa.fit_candidates(AggOp, B)
+    T, Bc = amg.aggregation.fit_candidates_block(torch.from_numpy(agg).cuda(), nagg,
+                                                 torch.from_numpy(np.ascontiguousarray(B).ravel()).cuda(), K1, K2)
+    assert same(T.to_scipy(), Tref)
+    assert np.array_equal(Bc.cpu().numpy().reshape(-1, K2), Rref)
+
+
+def test_block_sa_setup_matches_reference(amg, golden_dir):
+    """every array of the block hierarchy (A, P, R per level: pattern, storage order, values) equals the REAL reference's,
+    given its spectral-radius estimates; then symmetric block-multicolour Gauss-Seidel cycles on the device-built
+    hierarchy against the oracle's cycle on the reference-built one"""
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))
+    A, B = levels[0].A, ex['B']
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    rhos = [(l.rho_smooth, None) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    # lexicographic bsr_gauss_seidel cycles: the history the real reference recorded for this hierarchy
+    res = []
+    x = ml.solve(ex['b'], tol=1e-30, maxiter=len(ex['residuals']) - 1, residuals=res)
+    assert np.all(np.abs(np.array(res) - ex['residuals']) <= RTOL * ex['residuals'][0])
+    assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
+    # own spectral-radius estimate from the same seeded stream: an unconverged Krylov number, 1e-7
+    np.random.seed(0)
+    ml2 = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    for m, r in zip(ml2.levels[:-1], ref[:-1]):
+        assert abs(m.rho_smooth - r.rho_smooth) <= 1e-7 * r.rho_smooth
+
+
+def test_block_sa_default_candidates_2d(amg, golden_dir):
+    """B=None on a BSR 2x2 operator (K2 = 2 constants per node) against the oracle's setup (scipy + reference kernels)"""
+    levels, _ = hier_io.load(os.path.join(golden_dir, 'sa_elasticity2d_14.npz'))
+    A = levels[0].A
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10)
+    rhos = [(l.rho_smooth, None) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    assert len(ml.levels) == len(ref)
+    for k, (m, r) in enumerate(zip(ml.levels, ref)):
+        for nm in ('A', 'P', 'R'):
+            if getattr(r, nm, None) is not None:
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
