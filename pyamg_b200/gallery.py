@@ -91,3 +91,86 @@ def diffusion_stencil_2d(epsilon=1.0, theta=0.0, type='FE'):
                    [west, centre, west],
                    [corner_m, north, corner_p]]) / scale
     return st
+
+
+# ---- BASELINE config 4: P1 tetrahedral linear elasticity on a structured grid -------------------------------------
+_TET_RING = ((1, 3), (3, 2), (2, 6), (6, 4), (4, 5), (5, 1))     # the 6 tetrahedra (c0, cp, cq, c7) around the diagonal c0-c7
+
+
+def _p13d_local(verts, lame, mu):
+    """local stiffness matrix of a P1 tetrahedron (pyamg/gallery/elasticity.py:340-357)"""
+    A = np.vstack((np.ones((1, 4)), verts.T))
+    grad = np.linalg.inv(A)[:, 1:]
+    R = np.zeros((6, 12))
+    R[[0, 3, 4], 0::3] = grad.T
+    R[[3, 1, 5], 1::3] = grad.T
+    R[[4, 5, 2], 2::3] = grad.T
+    C = np.zeros((6, 6))
+    C[0:3, 0:3] = lame + 2 * mu * np.eye(3)
+    C[3:6, 3:6] = mu * np.eye(3)
+    return np.linalg.det(A) / 6 * np.dot(np.dot(R.T, C), R)
+
+
+def linear_elasticity_tets(nv, E=1e5, nu=0.3, device=None):
+    """P1 linear elasticity (pyamg/gallery/elasticity.py:215-322, `linear_elasticity_p1`) on nv^3 vertices of the unit
+    cube, every cube cut into 6 tetrahedra around its main diagonal, the face x = 0 clamped by leaving its vertices out:
+    -> (A as BSR with 3 x 3 blocks, B = the 6 rigid-body modes as an (n, 6) tensor).
+
+    All cubes are congruent, so the operator is a 15-point block stencil whose blocks are sums of the local stiffness
+    blocks of the tetrahedra that exist around a vertex; it is assembled per stencil offset instead of per element
+    (12.3 M elements at nv = 128).  Same pattern as the reference generator on the same mesh, values equal up to the
+    rounding of the duplicate sums (checked against a reference-built fixture in tests/test_cabi.py)."""
+    dev = device or _dev()
+    nv = int(nv)
+    if nv < 3:
+        raise ValueError('need at least 3 vertices per side')
+    lame = E * nu / ((1 + nu) * (1 - 2 * nu))
+    mu = E / (2 + 2 * nu)
+    h = 1.0 / (nv - 1)
+    corner = [np.array([a, b, d]) for d in (0, 1) for b in (0, 1) for a in (0, 1)]        # c[a + 2b + 4d] -> (x, y, z)
+    # contrib[d] = list of (offset of the row vertex inside its cube, 3x3 block) for the stencil offset d
+    contrib = {}
+    for p, q in _TET_RING:
+        loc = [corner[0], corner[p], corner[q], corner[7]]
+        K = _p13d_local(np.array(loc, dtype=np.float64) * h, lame, mu)
+        for a in range(4):
+            for b in range(4):
+                d = tuple(int(v) for v in (loc[b] - loc[a]))
+                contrib.setdefault(d, []).append((tuple(int(v) for v in loc[a]), K[3 * a:3 * a + 3, 3 * b:3 * b + 3]))
+    nx, ny, nz = nv - 1, nv, nv                       # free vertices: original x index 1..nv-1
+    N = nx * ny * nz
+    stride = (1, nx, nx * ny)
+    offs = sorted(contrib, key=lambda d: d[0] * stride[0] + d[1] * stride[1] + d[2] * stride[2])
+    lin = torch.arange(N, device=dev, dtype=torch.int64)
+    ck = torch.div(lin, nx * ny, rounding_mode='floor')
+    cj = torch.div(lin - ck * nx * ny, nx, rounding_mode='floor')
+    ci = lin - ck * nx * ny - cj * nx
+    co = (ci + 1, cj, ck)                             # original vertex coordinates
+    valid = torch.zeros((N, len(offs)), dtype=torch.bool, device=dev)
+    data = torch.zeros((N, len(offs), 9), dtype=torch.float64, device=dev)
+    for q, d in enumerate(offs):
+        for oa, blk in contrib[d]:
+            ok = torch.ones(N, dtype=torch.bool, device=dev)
+            for dim in range(3):                      # the cube (vertex - oa) must exist: 0 <= c <= nv - 2
+                c = co[dim] - oa[dim]
+                ok &= (c >= 0) & (c <= nv - 2)
+            ok &= (co[0] + d[0] >= 1)                 # neighbour not on the clamped face
+            valid[:, q] |= ok
+            data[:, q, :] += ok[:, None].to(torch.float64) * torch.from_numpy(np.ascontiguousarray(blk).ravel()).to(dev)[None, :]
+    counts = valid.sum(dim=1, dtype=torch.int32)
+    indptr = torch.zeros(N + 1, dtype=torch.int32, device=dev)
+    indptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+    off_t = torch.tensor([d[0] * stride[0] + d[1] * stride[1] + d[2] * stride[2] for d in offs], dtype=torch.int64, device=dev)
+    mask = valid.reshape(-1)
+    cols = (lin[:, None] + off_t[None, :]).reshape(-1)[mask].to(torch.int32).contiguous()
+    vals = data.reshape(-1, 9)[mask].reshape(-1).contiguous()
+    A = DevMat(indptr, cols, vals, (3 * N, 3 * N), (3, 3), 'bsr', True)
+    x, y, z = (c.to(torch.float64) / float(nv - 1) for c in co)
+    B = torch.zeros((N, 3, 6), dtype=torch.float64, device=dev)
+    B[:, 0, 0] = 1
+    B[:, 1, 1] = 1
+    B[:, 2, 2] = 1
+    B[:, 0, 3], B[:, 1, 3] = -y, x                    # rotations (-y, x, 0), (-z, 0, x), (0, -z, y)
+    B[:, 0, 4], B[:, 2, 4] = -z, x
+    B[:, 1, 5], B[:, 2, 5] = -z, y
+    return A, B.reshape(3 * N, 6)

@@ -138,3 +138,24 @@ def test_chebyshev_coefficients_host_formula():
     import pytest
     with pytest.raises(ValueError):
         chebyshev_polynomial_coefficients(2.0, 1.0, 3)
+
+
+def test_tet_elasticity_generator_equals_reference_gallery(golden_dir):
+    """pyamg_b200.gallery.linear_elasticity_tets (stencil-wise assembly, BASELINE config 4's workload) against the
+    matrix the REAL reference's linear_elasticity_p1 assembled element by element on the same mesh: identical block
+    pattern, values to the rounding of the duplicate sums, rigid-body modes identical.  Index arithmetic only (torch on
+    the CPU device passed explicitly): no kernel of the product runs here."""
+    import torch
+    import hier_io
+    from pyamg_b200 import gallery
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))
+    Aref = levels[0].A
+    A, B = gallery.linear_elasticity_tets(7, device=torch.device('cpu'))
+    As = A.to_scipy()
+    assert As.blocksize == (3, 3) and As.shape == Aref.shape
+    assert np.array_equal(As.indptr, Aref.indptr) and np.array_equal(As.indices, Aref.indices)
+    assert np.abs(As.data - Aref.data).max() <= 1e-13 * np.abs(Aref.data).max()
+    assert np.array_equal(B.numpy(), ex['B'])
+    # the operator is symmetric and annihilates the rigid-body modes away from the clamped face
+    D = (As - As.T)
+    assert abs(D).max() <= 1e-10 * np.abs(Aref.data).max()
