@@ -33,12 +33,13 @@ def parse():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--config', type=int, default=2, choices=[2, 3],
+    ap.add_argument('--config', type=int, default=2, choices=[2, 3, 4],
                     help='BASELINE.json configs[] entry (1-based as in SURVEY 8d): 2 = 3D Poisson 256^3 SA + Jacobi (the headline, '
-                         'default); 3 = 2D rotated anisotropic diffusion 4000^2, classical RS + symmetric multicolour Gauss-Seidel '
-                         '(an extra measurement, single GPU)')
+                         'default); 3 = 2D rotated anisotropic diffusion 4000^2, classical RS + symmetric multicolour Gauss-Seidel; '
+                         '4 = 3D P1 elasticity on 128^3 vertices (BSR 3x3), SA with the 6 rigid-body modes + symmetric '
+                         'block-multicolour bsr_gauss_seidel (3 and 4: extra measurements, single GPU)')
     ap.add_argument('--grid', type=int, default=int(os.environ.get('B200AMG_GRID', '0')),
-                    help='grid points per dimension (default: 256 for config 2, 4000 for config 3)')
+                    help='grid points per dimension (default: 256 for config 2, 4000 for config 3, 128 for config 4)')
     ap.add_argument('--cpu-cycles', type=int, default=3, help='V-cycles of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--smoother', default='jacobi', choices=['jacobi', 'mcgs'],
@@ -49,8 +50,8 @@ def parse():
                     help='N > 1: levels with fewer global rows than this run on rank 0 only')
     args = ap.parse_args()
     if args.grid <= 0:
-        args.grid = 256 if args.config == 2 else 4000
-    if args.config == 3:
+        args.grid = {2: 256, 3: 4000, 4: 128}[args.config]
+    if args.config in (3, 4):
         args.smoother = 'mcgs'
     return args
 
@@ -140,19 +141,35 @@ def spmv_bytes(n_row, n_col, nnz):
     return 12 * nnz + 4 * (n_row + 1) + 8 * n_col + 8 * n_row
 
 
+def block_bytes(nblocks, R, C):
+    """stored bytes of the blocks of a BSR operator: fp64 R x C block + int32 block column"""
+    return nblocks * (8 * R * C + 4)
+
+
+def bsr_gs_sweep_bytes(n_brow, nblocks, bs):
+    """one colour-ordered block Gauss-Seidel sweep: blocks once, block row pointer, x gathered once, x written, b, and the
+    block-row index list Id"""
+    n = n_brow * bs
+    return block_bytes(nblocks, bs, bs) + 4 * (n_brow + 1) + 8 * n + 8 * n + 8 * n + 4 * n_brow
+
+
 def vcycle_bytes(ml, gs_sweeps=0):
     """unfused algorithmic bytes of one V(1,1)-cycle (SURVEY 8d formula) over the hierarchy; gs_sweeps > 0: the
-    smoothers are colour-ordered Gauss-Seidel with that many sweeps per smoothing step (2 = symmetric)"""
+    smoothers are colour-ordered Gauss-Seidel with that many sweeps per smoothing step (2 = symmetric).  Block (BSR)
+    levels count 8 R C + 4 bytes per block and 4 bytes per BLOCK row of row pointer (the scalar formula at R = C = 1)"""
     tot = 0
     for lvl in ml.levels[:-1]:
-        n, nnz = lvl.A.shape[0], lvl.A.nnz
-        nc = lvl.P.shape[1]
+        A, P, R = lvl.A, lvl.P, lvl.R
+        n, nb = A.shape[0], A.n_brow
+        mA = block_bytes(A.nblocks, *A.blocksize)
+        nc = P.shape[1]
         if gs_sweeps:
-            tot += 2 * gs_sweeps * gs_sweep_bytes(n, nnz) + (12 * nnz + 4 * n + 24 * n)
+            sweep = gs_sweep_bytes(n, A.nnz) if A.is_scalar else bsr_gs_sweep_bytes(nb, A.nblocks, A.blocksize[0])
+            tot += 2 * gs_sweeps * sweep + (mA + 4 * nb + 24 * n)
         else:
-            tot += 3 * (12 * nnz + 4 * n + 24 * n)
-        tot += 12 * lvl.R.nnz + 4 * nc + 8 * n + 8 * nc
-        tot += 12 * lvl.P.nnz + 4 * n + 8 * nc + 16 * n
+            tot += 3 * (mA + 4 * nb + 24 * n)
+        tot += block_bytes(R.nblocks, *R.blocksize) + 4 * R.n_brow + 8 * n + 8 * nc
+        tot += block_bytes(P.nblocks, *P.blocksize) + 4 * P.n_brow + 8 * nc + 16 * n
     tot += 8 * ml.levels[-1].A.shape[0] ** 2
     return tot
 
@@ -166,15 +183,18 @@ def host_levels(ml):
         h.A = lvl.A.to_scipy()
         if hasattr(lvl, 'P'):
             h.P, h.R = lvl.P.to_scipy(), lvl.R.to_scipy()
-            h.pre, h.post = host_spec(lvl.presmoother), host_spec(lvl.postsmoother)
+            blk = not lvl.A.is_scalar
+            h.pre, h.post = host_spec(lvl.presmoother, blk), host_spec(lvl.postsmoother, blk)
         out.append(h)
     return out
 
 
-def host_spec(sm):
-    """resolved device smoother -> the oracle's spec for the same sweep"""
+def host_spec(sm, block=False):
+    """resolved device smoother -> the oracle's spec for the same sweep (block levels: the index list holds block rows)"""
     if sm.kind == 1:
         return ('jacobi', {'omega': sm.omega, 'iterations': sm.iterations})
+    if sm.kind == 2 and block:
+        return ('bsr_gauss_seidel_indexed', {'indices': sm.indices.cpu().numpy(), 'sweep': sm.sweep, 'iterations': sm.iterations})
     if sm.kind == 2:
         return ('gauss_seidel_indexed', {'indices': sm.indices.cpu().numpy(), 'sweep': sm.sweep, 'iterations': sm.iterations})
     raise SystemExit('bench: smoother kind %r has no CPU-baseline spec' % (sm.kind,))
@@ -244,7 +264,33 @@ def build_problem_rs(grid):
     return ml, b
 
 
+def build_problem_elasticity(nv):
+    """config 4 of BASELINE.json: P1 tetrahedral linear elasticity on nv^3 vertices (E = 1e5, nu = 0.3, face x = 0
+    clamped; pyamg_b200.gallery.linear_elasticity_tets = the reference's linear_elasticity_p1 on the structured mesh),
+    BSR 3x3, smoothed_aggregation_solver with the 6 rigid-body modes (max_coarse=500 block rows, candidates as given),
+    symmetric block-multicolour Gauss-Seidel = bsr_gauss_seidel over the MIS colouring of the block graph"""
+    import pyamg_b200 as amg
+    A, B = amg.gallery.linear_elasticity_tets(nv)
+    np.random.seed(0)
+    mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=500)
+    b = np.random.rand(A.shape[0])
+    return ml, b
+
+
+def build_for(args):
+    if args.config == 3:
+        return build_problem_rs(args.grid)
+    if args.config == 4:
+        return build_problem_elasticity(args.grid)
+    return build_problem(args.grid)
+
+
 def workload_name(args):
+    if args.config == 4:
+        return ('configs[3]: 3D linear elasticity, P1 tetrahedra on %d^3 vertices (E=1e5, nu=0.3, one face clamped), BSR 3x3, '
+                'smoothed_aggregation_solver with the 6 rigid-body modes (max_coarse=500), symmetric block-multicolour '
+                'bsr_gauss_seidel pre/post (MIS colours of the block graph), fp64, one V(1,1)-cycle per step' % args.grid)
     if args.config == 3:
         return ('configs[2]: 2D rotated anisotropic diffusion %dx%d (eps=0.001, theta=pi/8, FE 9-point), ruge_stuben_solver '
                 '(classical strength 0.25, RS splitting, direct interpolation, max_coarse=500), symmetric multicolour '
@@ -256,6 +302,8 @@ def workload_name(args):
 
 
 def metric_name(args):
+    if args.config == 4:
+        return 'V-cycles/sec, 3D elasticity %d^3 BSR 3x3 SA (symmetric block-multicolour bsr_gauss_seidel), V(1,1)' % args.grid
     if args.config == 3:
         return 'V-cycles/sec, 2D rotated anisotropic diffusion %d^2 RS (symmetric multicolour Gauss-Seidel), V(1,1)' % args.grid
     return 'V-cycles/sec, 3D Poisson %d^3 SA (%s), V(1,1)' % (args.grid, 'Jacobi 4/3' if args.smoother == 'jacobi' else
@@ -266,11 +314,18 @@ def level_table(ml):
     return [[int(l.A.shape[0]), int(l.A.nnz)] for l in ml.levels]
 
 
-def cpu_cycles_timed(levels, b, cycles, warm):
+def block_table(ml):
+    """[block rows, blocks, block size] per level (block hierarchies only)"""
+    if all(l.A.is_scalar for l in ml.levels):
+        return None
+    return [[int(l.A.n_brow), int(l.A.nblocks), int(l.A.blocksize[0])] for l in ml.levels]
+
+
+def cpu_cycles_timed(levels, b, cycles, warm, core=None):
     """-> (seconds per V-cycle, kind, x after `warm + cycles` cycles from x0 = 0)"""
     import oracle
     from oracle import multilevel as oml
-    S = oml.Solver(levels, core=oracle.core, wasted_prolongation=True)
+    S = oml.Solver(levels, core=core or oracle.core, wasted_prolongation=True)
     S.coarse_matrix()
     x = np.zeros_like(b)
     for _ in range(warm):
@@ -295,8 +350,8 @@ def run_b200(args):
     import pyamg_b200 as amg
 
     t0 = time.perf_counter()
-    if args.config == 3:
-        ml, b = build_problem_rs(args.grid)
+    if args.config in (3, 4):
+        ml, b = build_for(args)
     else:
         ml, b = build_problem(args.grid)
         if args.smoother == 'mcgs':
@@ -555,6 +610,23 @@ def measure_roofline(R, reps=5):
     t_r = float(np.mean(acc[('residual', 0)]))
     res_bytes = jacobi_bytes(A0.shape[0], A0.nnz, lay)
     sm0 = ml.levels[0].presmoother
+    if sm0.kind == 2 and not A0.is_scalar:
+        # block rows by MIS colour of the block graph: one sweep = K launches of bsr_gs_color_kernel<bs> on the BSR arrays
+        bs = A0.blocksize[0]
+        sweeps = 2 if sm0.sweep == 'symmetric' else 1
+        K = int(len(sm0.color_ptr) - 1)
+        t_s = float(np.mean(acc[('presmooth', 0)] + acc[('postsmooth', 0)])) / (sweeps * sm0.iterations)
+        nB = bsr_gs_sweep_bytes(A0.n_brow, A0.nblocks, bs)
+        ach = nB / (t_s * 1e-3) / 1e9
+        rB = block_bytes(A0.nblocks, bs, bs) + 4 * (A0.n_brow + 1) + 24 * A0.shape[0]
+        return {'bound': 'hbm', 'kernel': 'bsr_gs_color_kernel<%d> level 0: one colour-ordered block Gauss-Seidel sweep = %d '
+                                          'launches (one per MIS colour of the block graph)' % (bs, K),
+                'achieved': round(ach, 1), 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': round(ach / peak, 4),
+                'algorithmic_bytes_per_launch': nB // K, 'algorithmic_bytes_per_sweep': nB, 'launches_per_sweep': K,
+                'ms_per_launch': round(t_s / K, 4), 'ms_per_sweep': round(t_s, 4), 'traffic': None,
+                'residual_L0_layout': 'BSR %dx%d (fp64 blocks + int32 block column)' % (bs, bs),
+                'residual_L0_GBs': round(rB / (t_r * 1e-3) / 1e9, 1),
+                'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
     if sm0.kind == 2:
         # colour-ordered Gauss-Seidel: the unit is ONE sweep over all K colours (K launches of sell_gs_kernel on the
         # colour-grouped sliced-ELL copy of A); a symmetric smoothing step is two sweeps
@@ -597,6 +669,8 @@ def cpu_baseline(R, args):
     """reference CPU path (scipy SpMV + the reference's compiled amg_core smoothers when
     oracle/_ref is built, else the C port) on this box's host cores, same hierarchy, same b."""
     levels = host_levels(R['ml'])
+    if args.config == 4:
+        return cpu_baseline_block(R, args, levels)
     sec, kind, x_cpu = cpu_cycles_timed(levels, R['b'], args.cpu_cycles, warm=1)
     # parity of the very same run: GPU x after (1 + cpu_cycles) cycles from zero vs the CPU x
     x_gpu = R['ml'].solve(R['b'], maxiter=1 + args.cpu_cycles, _norms=False)
@@ -608,6 +682,56 @@ def cpu_baseline(R, args):
                        % (args.cpu_cycles, len(levels), 'jacobi' if args.smoother == 'jacobi' else 'gauss_seidel_indexed'),
              's_per_cycle': sec},
             {'cycles': 1 + args.cpu_cycles, 'max_rel_diff_x_vs_cpu_reference': err, 'bit_identical': bool(np.array_equal(x_gpu, x_cpu))})
+
+
+def lexicographic(levels):
+    """the reference's own smoother for config 4: symmetric lexicographic bsr_gauss_seidel on every level"""
+    from oracle import multilevel as oml
+    out = []
+    for src in levels:
+        h = oml.Level()
+        h.A = src.A
+        if hasattr(src, 'P'):
+            h.P, h.R = src.P, src.R
+            h.pre = h.post = ('gauss_seidel', {'sweep': 'symmetric', 'iterations': 1})
+        out.append(h)
+    return out
+
+
+def cpu_baseline_block(R, args, levels):
+    """config 4.  TIMED: the reference's CPU cycle with ITS smoother for this config -- symmetric lexicographic
+    amg_core.bsr_gauss_seidel (the block-multicolour order only exists on the device; same operators, same bytes per
+    sweep).  PARITY: the device's block-multicolour cycles against the same block rows relaxed one by one in the same
+    order by the reference row update (oracle.relaxation.bsr_gauss_seidel_indexed), untimed."""
+    import oracle
+    sec, kind, _ = cpu_cycles_timed(lexicographic(levels), R['b'], args.cpu_cycles, warm=1)
+    _, _, x_cpu = cpu_cycles_timed(levels, R['b'], 2, warm=0, core=oracle.port)
+    x_gpu = R['ml'].solve(R['b'], maxiter=2, _norms=False)
+    err = float(np.max(np.abs(x_gpu - x_cpu)) / max(np.max(np.abs(x_cpu)), 1e-300))
+    return ({'value': 1.0 / sec, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(), 'kind': kind,
+             'sample': '%d full V(1,1)-cycles of the same %d-level block hierarchy after 1 warm-up cycle; serial reference '
+                       'code (scipy bsr_matvec + amg_core bsr_gauss_seidel, symmetric LEXICOGRAPHIC sweeps: the reference '
+                       'has no block-multicolour order), incl. the fork\'s second P*coarse_x per level (multilevel.py:548)'
+                       % (args.cpu_cycles, len(levels)),
+             's_per_cycle': sec},
+            {'cycles': 2, 'against': 'block rows relaxed one at a time in the same colour order by the reference row update '
+                                     '(oracle C port)',
+             'max_rel_diff_x_vs_cpu_reference': err, 'bit_identical': bool(np.array_equal(x_gpu, x_cpu))})
+
+
+def cpu_problem_elasticity(nv):
+    """config 4 without a GPU: the generator's index arithmetic on the CPU device, oracle/sa.py block hierarchy, the
+    reference's lexicographic symmetric bsr_gauss_seidel"""
+    import torch
+    import oracle
+    from oracle import sa
+    from pyamg_b200 import gallery
+    A, B = gallery.linear_elasticity_tets(nv, device=torch.device('cpu'))
+    A, B = A.to_scipy(), B.numpy()
+    np.random.seed(0)
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    levels = sa.smoothed_aggregation_hierarchy(A, B, presmoother=gs, postsmoother=gs, max_coarse=500, core=oracle.core)
+    return levels, np.random.rand(A.shape[0])
 
 
 def cpu_problem_rs(grid):
@@ -661,8 +785,10 @@ def run_reference(args):
     try:
         import torch
         if torch.cuda.is_available():
-            ml, b = build_problem_rs(args.grid) if args.config == 3 else build_problem(args.grid)
+            ml, b = build_for(args)
             levels = host_levels(ml)
+            if args.config == 4:
+                levels = lexicographic(levels)
             how = 'device setup (pyamg_b200), downloaded to the host'
             del ml
             torch.cuda.empty_cache()
@@ -672,6 +798,9 @@ def run_reference(args):
     if how is None and args.config == 3:
         levels, b = cpu_problem_rs(args.grid)
         how = 'CPU setup (oracle/rs.py)'
+    if how is None and args.config == 4:
+        levels, b = cpu_problem_elasticity(args.grid)
+        how = 'CPU setup (oracle/sa.py on blocks)'
     if how is None:
         from oracle import sa
         import scipy.sparse as sp
@@ -701,7 +830,7 @@ def run_reference(args):
     sec = (time.perf_counter() - t0) / timed
     val = 1.0 / sec
     sample = ('%d of the %d requested V(1,1)-cycles timed (%d warm-up), each a full cycle over the %d-level '
-              'hierarchy of poisson(%d^3); hierarchy from: %s' % (timed, args.steps, warm_done, len(levels), args.grid, how))
+              'hierarchy of the workload (grid %d); hierarchy from: %s' % (timed, args.steps, warm_done, len(levels), args.grid, how))
     out = {'impl': 'reference', 'metric': metric_name(args),
            'value': val, 'unit': 'V-cycles/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
            'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -724,7 +853,7 @@ def main():
     if args.impl == 'reference':
         run_reference(args)
         return
-    if dist_env()[1] > 1:
+    if dist_env()[1] > 1 and args.config == 2:
         run_distributed(args)
         return
     R = run_b200(args)
@@ -749,7 +878,9 @@ def main():
            'config': {'workload': workload_name(args),
                       'levels': level_table(ml), 'parallelism': 'single GPU' if R['world'] == 1 else
                       'replicas: %d independent solves, one per GPU' % R['world'],
-                      'l2': 'inputs larger than L2 (level-0 CSR alone is %.2f GB)' % (12e-9 * ml.levels[0].A.nnz),
+                      'l2': 'inputs larger than L2 (the level-0 operator alone is %.2f GB)'
+                            % (1e-9 * block_bytes(ml.levels[0].A.nblocks, *ml.levels[0].A.blocksize)),
+                      'block_levels': block_table(ml),
                       'colours_per_level': ([int(len(l.presmoother.color_ptr) - 1) for l in ml.levels[:-1]]
                                             if args.smoother == 'mcgs' else None),
                       'setup_s_device': round(R['setup_s'], 2),

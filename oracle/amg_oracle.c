@@ -148,6 +148,18 @@ void orc_bsr_gauss_seidel(const I *Ap, const I *Aj, const T *Ax, T *x, const T *
     free(acc); free(loc);
 }
 
+/* ---- block rows relaxed in the order of an index list: bsr_gauss_seidel (relaxation.h:89-173) called for ONE block
+ * row at a time, (i, i+1, +1) going forward through Id and (i, i-1, -1) going backward -- the sequential definition of
+ * the block-multicolour sweep (the reference has no such entry point; its gauss_seidel_indexed is CSR-only,
+ * relaxation.py:671-741).  Same arithmetic per row as orc_bsr_gauss_seidel. */
+void orc_bsr_gauss_seidel_indexed(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, const I *Id,
+                                  I start, I stop, I step, I bs)
+{
+    const I dir = step < 0 ? -1 : 1;
+    for (I p = start; p != stop; p += step)
+        orc_bsr_gauss_seidel(Ap, Aj, Ax, x, b, Id[p], Id[p] + dir, dir, bs);
+}
+
 /* ---- amg_core.bsr_jacobi, relaxation.h:267-360.  The temp copy (:301-303) takes the
  * |row_stop-row_start|*bs LEADING entries; the reference's loop never terminates for a
  * negative row_step (i += -1 from 0), and its Python wrapper only ever passes (0, N, 1)

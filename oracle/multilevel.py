@@ -24,7 +24,8 @@ def _smoother(spec, core=None):
     if name is None:
         return lambda A, x, b: None
     fn = {'jacobi': _rx.jacobi, 'gauss_seidel': _rx.gauss_seidel,
-          'gauss_seidel_indexed': _rx.gauss_seidel_indexed, 'polynomial': _rx.polynomial}[name]
+          'gauss_seidel_indexed': _rx.gauss_seidel_indexed, 'bsr_gauss_seidel_indexed': _rx.bsr_gauss_seidel_indexed,
+          'polynomial': _rx.polynomial}[name]
     return lambda A, x, b: fn(A, x, b, core=core, **kw)
 
 

@@ -104,6 +104,30 @@ def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', core=N
         core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr)
 
 
+def bsr_gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', core=None):
+    """Block rows of a BSR matrix relaxed in the order of `indices` (block-row numbers), each through the reference's
+    bsr_gauss_seidel restricted to that one row -- the sequential definition of the block-multicolour sweep
+    (tests/golden/make_golden.py::sa_elasticity).  A core without the fused loop (the reference's own _amg_core) is
+    driven one row per call."""
+    core = core or _o.core
+    A, x, b = make_system(A, x, b, formats=['bsr'])
+    bs = A.blocksize[0]
+    if A.blocksize[0] != A.blocksize[1]:
+        raise ValueError('BSR blocks must be square')
+    indices = np.asarray(indices, dtype='intc')
+    data = np.ravel(A.data)
+    fused = getattr(core, 'bsr_gauss_seidel_indexed', None)
+    for _ in range(iterations):
+        for direction in (('forward', 'backward') if sweep == 'symmetric' else (sweep,)):
+            r0, r1, dr = _sweep_range(direction, len(indices))
+            if fused is not None:
+                fused(A.indptr, A.indices, data, x, b, indices, r0, r1, dr, bs)
+            else:
+                for p in range(r0, r1, dr):
+                    i = int(indices[p])
+                    core.bsr_gauss_seidel(A.indptr, A.indices, data, x, b, i, i + dr, dr, bs)
+
+
 def polynomial(A, x, b, coefficients, iterations=1, core=None):
     """pyamg/relaxation/relaxation.py:593-668 (what 'chebyshev' resolves to, smoothing.py:438-449): numpy / scipy
     expressions exactly as the reference writes them."""

@@ -11,7 +11,7 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize('extra', [['--grid', '14'], ['--config', '3', '--grid', '60']])
+@pytest.mark.parametrize('extra', [['--grid', '14'], ['--config', '3', '--grid', '60'], ['--config', '4', '--grid', '10']])
 def test_reference_arm_line(extra):
     env = dict(os.environ, B200AMG_REF_BUDGET_S='5', CUDA_VISIBLE_DEVICES='')
     r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference', '--steps', '2', '--warmup', '1'] + extra,
@@ -43,3 +43,32 @@ def test_byte_models():
     assert bench.jacobi_bytes(n, nnz, 5) == 25 * n                       # row-pattern layout: 1 B/row + b, x, x_new
     assert bench.gs_sweep_bytes(n, nnz) == bench.spmv_bytes(n, n, nnz) + 8 * n + 4 * n
     assert bench.grid_dims(256, 8) == (512, 512, 512) and bench.grid_dims(256, 2) == (512, 256, 256)
+
+
+def test_block_byte_model_reduces_to_the_scalar_one():
+    """vcycle_bytes on a hierarchy of 1x1 blocks is SURVEY 8d's scalar formula; 3x3 blocks cost 76 bytes each"""
+    sys.path.insert(0, ROOT)
+    import bench
+
+    class M:
+        def __init__(self, nbr, nbc, nblk, R, C):
+            self.n_brow, self.nblocks, self.blocksize = nbr, nblk, (R, C)
+            self.shape, self.nnz, self.is_scalar = (nbr * R, nbc * C), nblk * R * C, (R, C) == (1, 1)
+
+    class L:
+        pass
+
+    class H:
+        pass
+    n, nnz, nc, pn = 1000, 6800, 120, 3600
+    l0, l1 = L(), L()
+    l0.A, l0.P, l0.R = M(n, n, nnz, 1, 1), M(n, nc, pn, 1, 1), M(nc, n, pn, 1, 1)
+    l1.A = M(nc, nc, 900, 1, 1)
+    ml = H()
+    ml.levels = [l0, l1]
+    want = 3 * (12 * nnz + 4 * n + 24 * n) + (12 * pn + 4 * nc + 8 * n + 8 * nc) + (12 * pn + 4 * n + 8 * nc + 16 * n) + 8 * nc ** 2
+    assert bench.vcycle_bytes(ml) == want
+    want_gs = 4 * bench.gs_sweep_bytes(n, nnz) + (12 * nnz + 28 * n) + (12 * pn + 4 * nc + 8 * n + 8 * nc) + (12 * pn + 4 * n + 8 * nc + 16 * n) + 8 * nc ** 2
+    assert bench.vcycle_bytes(ml, 2) == want_gs
+    assert bench.block_bytes(10, 3, 3) == 760 and bench.block_bytes(10, 1, 1) == 120
+    assert bench.bsr_gs_sweep_bytes(100, 1500, 3) == 1500 * 76 + 4 * 101 + 3 * 8 * 300 + 400

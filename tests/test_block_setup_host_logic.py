@@ -151,3 +151,36 @@ def test_block_path_default_candidates_and_argument_checks(host_amg, golden_dir)
         amg.smoothed_aggregation_solver(sp.csr_matrix(A), np.ones((A.shape[0], 2)))
     with pytest.raises(ValueError):
         amg.smoothed_aggregation_solver(A, np.ones((A.shape[0] + 2, 3)))
+
+
+def test_bench_config4_host_pieces(host_amg, golden_dir):
+    """bench.py's config-4 plumbing on a block hierarchy: the generator, block-multicolour smoother specs (MIS colouring
+    of the BLOCK graph), their oracle mirror (block rows relaxed in colour order) and the block byte model"""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import oracle
+    from oracle import multilevel as oml
+    amg = host_amg
+    A, B = amg.gallery.linear_elasticity_tets(7, device=torch.device('cpu'))
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)             # spectral radii from the oracle's setup: the device Arnoldi needs the GPU's dot / axpy
+    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10)
+    mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=10,
+                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+    assert [l.A.blocksize for l in ml.levels] == [(3, 3), (6, 6), (6, 6)]
+    sm = ml.levels[0].presmoother
+    assert sm.kind == 2 and sm.indices.numel() == ml.levels[0].A.n_brow          # block rows, not scalar rows
+    levels = bench.host_levels(ml)
+    assert levels[0].pre[0] == 'bsr_gauss_seidel_indexed' and levels[0].A.blocksize == (3, 3)
+    b = np.random.rand(A.shape[0])
+    res = []
+    oml.Solver(levels, core=oracle.port).solve(b, tol=1e-30, maxiter=6, residuals=res)
+    assert res[-1] < 0.1 * res[0]
+    lex = bench.lexicographic(levels)
+    assert lex[0].pre == ('gauss_seidel', {'sweep': 'symmetric', 'iterations': 1}) and lex[0].A is levels[0].A
+    A0 = ml.levels[0].A
+    assert bench.block_table(ml)[0] == [A0.n_brow, A0.nblocks, 3]
+    vb = bench.vcycle_bytes(ml, 2)
+    assert vb > 4 * bench.bsr_gs_sweep_bytes(A0.n_brow, A0.nblocks, 3) + bench.block_bytes(A0.nblocks, 3, 3)
