@@ -197,6 +197,12 @@ def host_spec(sm, block=False):
         return ('bsr_gauss_seidel_indexed', {'indices': sm.indices.cpu().numpy(), 'sweep': sm.sweep, 'iterations': sm.iterations})
     if sm.kind == 2:
         return ('gauss_seidel_indexed', {'indices': sm.indices.cpu().numpy(), 'sweep': sm.sweep, 'iterations': sm.iterations})
+    if sm.kind in (5, 6, 7):
+        Dinv = sm.Dinv.cpu().numpy()
+        if sm.kind == 5:
+            return ('block_jacobi', {'Dinv': Dinv, 'blocksize': int(Dinv.shape[1]), 'omega': sm.omega, 'iterations': sm.iterations})
+        return ('block_gauss_seidel', {'Dinv': Dinv, 'blocksize': int(Dinv.shape[1]), 'sweep': sm.sweep, 'iterations': sm.iterations,
+                                       'indices': sm.indices.cpu().numpy() if sm.kind == 6 else None})
     raise SystemExit('bench: smoother kind %r has no CPU-baseline spec' % (sm.kind,))
 
 

@@ -236,6 +236,34 @@ int b200amg_bsr_matmat_numeric(int n_brow, int R, int N, int C, const int *Ap, c
                                const int *Cp, const int *Sj, const int *slot, long long n_out_blocks,
                                double *Cx, void *stream);
 
+/* ---- block relaxation with stored diagonal-block inverses (csrc/block_relax.cu) --------------------- */
+/* amg_core.block_jacobi (pyamg/amg_core/relaxation.h:661-727): temp <- x on the block rows of the sweep, then
+ * x_i = (1 - omega) temp_i + omega Dinv_i (b_i - sum_{j != i} A_ij temp_j).  Dinv[n_brow][bs][bs] as the
+ * reference's Tx.  omega by value (the reference passes a length-1 array, relaxation.py:894). */
+int b200amg_block_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                         const double *Dinv, double *temp, int row_start, int row_stop, int row_step,
+                         double omega, int blocksize, void *stream);
+/* amg_core.block_gauss_seidel (relaxation.h:753-806): x_i = Dinv_i (b_i - sum_{j != i} A_ij x_j) in place.
+ * color_ptr_host == NULL: block rows row_start, row_start + row_step, ... (positions of Id when Id != NULL)
+ * one after the other -- the reference's order, sequential on the device.  With (Id, color_ptr_host, K):
+ * Id holds the block rows grouped by colour and the sweep covers whole colours, forward or backward, one
+ * launch per colour (same contract as b200amg_bsr_gauss_seidel). */
+int b200amg_block_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                               const double *Dinv, int row_start, int row_stop, int row_step, int blocksize,
+                               const int *Id, const int *color_ptr_host, int K, void *stream);
+/* amg_core.pinv_array (pyamg/amg_core/linalg.h:888-954 over svd_jacobi :455-780): every n x n block of AA
+ * (m blocks; row-major when transA != 0) is replaced by its Moore-Penrose pseudo-inverse, operation for operation
+ * as the reference computes it (n <= 6: above that the reference's Python layer switches to LAPACK). */
+int b200amg_pinv_array(double *AA, int m, int n, int transA, void *stream);
+/* inverses of the diagonal blocks, Dinv[n_brow][bs][bs] (pyamg/util/utils.py:601-690 get_block_diag(inv_flag=True)):
+ * the stored diagonal block (zeros when absent) through pinv_array for bs < 7 -- the bits of the reference.  For
+ * bs = 7, 8 the reference calls LAPACK gelss (no bit contract): Gauss-Jordan with partial pivoting, equal to
+ * rounding, a numerically singular block giving a zero block instead of its pseudo-inverse. */
+int b200amg_block_diag_inverse(int n_brow, int blocksize, const int *Ap, const int *Aj, const double *Ax,
+                               double *Dinv, void *stream);
+int b200amg_block_diag_inverse_gj(int n_brow, int blocksize, const int *Ap, const int *Aj, const double *Ax,
+                                  double *Dinv, void *stream);   /* the Gauss-Jordan path at any block size */
+
 /* ---- Ruge-Stuben setup (csrc/rs_setup.cu): pyamg/amg_core/ruge_stuben.h:45-93, :496-595 -------- */
 /* amg_core.classical_strength_of_connection fused with the two things the reference's glue does to S:
  * flags & 1: drop the diagonal (the graph of the C/F splitting, pyamg/util/utils.py:1815-1827);
@@ -284,7 +312,8 @@ typedef struct b200amg_level_desc {
     const int *Rp, *Rj; const double *Rx;
     /* smoothers: kind 0 none, 1 jacobi(omega, iterations), 2 gauss_seidel_indexed over
      * colour-grouped rows (Id, color_ptr on HOST), 3 lexicographic gauss_seidel (sequential on
-     * the device, exact), 4 polynomial (coefficients below); sweep 0 fwd / 1 bwd / 2 symmetric */
+     * the device, exact), 4 polynomial (coefficients below), 5-7 block smoothers (Dinv below);
+     * sweep 0 fwd / 1 bwd / 2 symmetric */
     int pre_kind, post_kind;
     double pre_omega, post_omega;
     int pre_iters, post_iters;
@@ -296,7 +325,13 @@ typedef struct b200amg_level_desc {
      * smoothing.py:438-449): per iteration r = b - A x, h = c[0] r, h = c[k] r + A h (k = 1..ncoef-1), x += h */
     int pre_ncoef, post_ncoef;  /* 1..8 */
     double pre_coef[8], post_coef[8];
+    /* kinds 5 block_jacobi(omega, iterations), 6 block_gauss_seidel over colour-grouped block rows (Id,
+     * color_ptr as for kind 2), 7 lexicographic block_gauss_seidel (sequential on the device, exact):
+     * pyamg/amg_core/relaxation.h:661-806 with the inverses of the diagonal blocks, [n / bs][bs][bs] */
+    const double *Dinv;
 } b200amg_level_desc;
+/* sizeof(b200amg_level_desc) as compiled: lets a binding check its mirror of the struct */
+int b200amg_level_desc_size(void);
 
 /* Build a cycle engine over nlev-1 described levels + the dense coarse operator
  * (coarse_inv: nc_last x nc_last row-major pseudo-inverse on the device, or NULL when the

@@ -160,6 +160,59 @@ void orc_bsr_gauss_seidel_indexed(const I *Ap, const I *Aj, const T *Ax, T *x, c
         orc_bsr_gauss_seidel(Ap, Aj, Ax, x, b, Id[p], Id[p] + dir, dir, bs);
 }
 
+/* ---- amg_core.block_gauss_seidel, relaxation.h:753-806: Tx = inverses of the diagonal blocks */
+void orc_block_gauss_seidel(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, const T *Tx,
+                            I row_start, I row_stop, I row_step, I bs)
+{
+    const I B2 = bs * bs;
+    T *rsum = (T *)malloc(sizeof(T) * bs), *v = (T *)malloc(sizeof(T) * bs);
+    for (I i = row_start; i != row_stop; i += row_step) {
+        for (I k = 0; k < bs; k++) rsum[k] = 0.0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) continue;
+            blk_matvec0(Ax + (size_t)p * B2, x + (size_t)j * bs, v, bs);
+            for (I k = 0; k < bs; k++) rsum[k] += v[k];
+        }
+        for (I k = 0; k < bs; k++) rsum[k] = b[(size_t)i * bs + k] - rsum[k];
+        blk_matvec0(Tx + (size_t)i * B2, rsum, x + (size_t)i * bs, bs);
+    }
+    free(rsum); free(v);
+}
+
+/* block rows in the order of an index list, one block_gauss_seidel call per row (cf. orc_bsr_gauss_seidel_indexed) */
+void orc_block_gauss_seidel_indexed(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, const T *Tx, const I *Id,
+                                    I start, I stop, I step, I bs)
+{
+    const I dir = step < 0 ? -1 : 1;
+    for (I p = start; p != stop; p += step)
+        orc_block_gauss_seidel(Ap, Aj, Ax, x, b, Tx, Id[p], Id[p] + dir, dir, bs);
+}
+
+/* ---- amg_core.block_jacobi, relaxation.h:661-727 */
+void orc_block_jacobi(const I *Ap, const I *Aj, const T *Ax, T *x, const T *b, const T *Tx, T *temp,
+                      I row_start, I row_stop, I row_step, T omega, I bs)
+{
+    const I B2 = bs * bs;
+    T *rsum = (T *)malloc(sizeof(T) * bs), *v = (T *)malloc(sizeof(T) * bs);
+    for (I i = row_start * bs; i != row_stop * bs; i += row_step * bs)
+        for (I k = 0; k < bs; k++) temp[i + k] = x[i + k];
+    for (I i = row_start; i != row_stop; i += row_step) {
+        for (I k = 0; k < bs; k++) rsum[k] = 0.0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            I j = Aj[p];
+            if (j == i) continue;
+            blk_matvec0(Ax + (size_t)p * B2, temp + (size_t)j * bs, v, bs);
+            for (I k = 0; k < bs; k++) rsum[k] += v[k];
+        }
+        for (I k = 0; k < bs; k++) rsum[k] = b[(size_t)i * bs + k] - rsum[k];
+        blk_matvec0(Tx + (size_t)i * B2, rsum, v, bs);
+        for (I k = 0; k < bs; k++)
+            x[(size_t)i * bs + k] = (1.0 - omega) * temp[(size_t)i * bs + k] + omega * v[k];
+    }
+    free(rsum); free(v);
+}
+
 /* ---- amg_core.bsr_jacobi, relaxation.h:267-360.  The temp copy (:301-303) takes the
  * |row_stop-row_start|*bs LEADING entries; the reference's loop never terminates for a
  * negative row_step (i += -1 from 0), and its Python wrapper only ever passes (0, N, 1)
@@ -515,4 +568,125 @@ void orc_rs_direct_interpolation_pass2(I n, const I *Ap, const I *Aj, const T *A
     for (I i = 0, run = 0; i < n; i++) { renum[i] = run; run += split[i]; }
     for (I p = 0; p < Pp[n]; p++) Pj[p] = renum[Pj[p]];
     free(renum);
+}
+
+/* ---- amg_core.pinv_array, linalg.h:888-954, on top of svd_jacobi, linalg.h:455-780 (one-sided Jacobi SVD of a
+ * column-major m x n matrix, real case).  get_block_diag(inv_flag=True) calls it with TransA = 'T' for blocks smaller
+ * than 7 (pyamg/util/utils.py:670-677): the inverses of the diagonal blocks the block smoothers use. */
+static T vec_dot(const T *x, const T *y, I n) { T s = 0.0; for (I i = 0; i < n; i++) s += x[i] * y[i]; return s; }
+static T vec_norm(const T *x, I n) { return sqrt(vec_dot(x, x, n)); }
+
+static I svd_jacobi(const T *A, T *U, T *V, T *S, I m, I n)
+{
+    const T eps = 2.220446049250313e-16;
+    if (m < n) return -1;
+    if (n == 1 && m == 1) {
+        T normA = fabs(A[0]);
+        V[0] = 1.0; S[0] = normA;
+        U[0] = (normA == 0.0) ? 1.0 : A[0] / normA;
+        return 0;
+    }
+    I i, j, k, nsq = n * n, count = 1, sweep = 0;
+    const I sweepmax = 15 * n > 30 ? 15 * n : 30;
+    const T tolerance = sqrt((T)m) * eps;
+    for (i = 0; i < nsq; i++) V[i] = 0.0;
+    for (i = 0; i < nsq; i += n + 1) V[i] = 1.0;
+    for (i = 0; i < m * n; i++) U[i] = A[i];
+    for (j = 0; j < n; j++) S[j] = eps * vec_norm(U + j * m, m);
+    while (count > 0 && sweep <= sweepmax) {
+        count = n * (n - 1) / 2;
+        I jm = 0, jn = 0;
+        for (j = 0; j < n - 1; j++) {
+            I km = (j + 1) * m, kn = (j + 1) * n;
+            for (k = j + 1; k < n; k++) {
+                T a = vec_norm(U + jm, m), b = vec_norm(U + km, m);
+                T d = vec_dot(U + jm, U + km, m);
+                T norm_d = fabs(d);
+                T abserr_a = S[j], abserr_b = S[k];
+                int sorted = (a >= b), orthog = (norm_d <= tolerance * a * b);
+                int noisya = (a < abserr_a), noisyb = (b < abserr_b);
+                if (sorted && (orthog || noisya || noisyb)) {
+                    count--;
+                } else if (!sorted || (norm_d == 0.0 && a == b)) {
+                    S[j] = abserr_b; S[k] = abserr_a;
+                    for (i = 0; i < m; i++) { T uj = U[jm + i], uk = U[km + i]; U[jm + i] = -uk; U[km + i] = uj; }
+                    for (i = 0; i < n; i++) { T vj = V[jn + i], vk = V[kn + i]; V[jn + i] = -vk; V[kn + i] = vj; }
+                } else {
+                    T tau = (b * b - a * a) / (2.0 * norm_d);
+                    T t = (tau < 0.0 ? -1.0 : 1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
+                    T c = 1.0 / (sqrt(1.0 + t * t));
+                    T sn = d * (t * c / norm_d);
+                    T nsn = -sn;
+                    T norm_sin = fabs(sn);
+                    S[j] = fabs(c) * abserr_a + norm_sin * abserr_b;
+                    S[k] = norm_sin * abserr_a + fabs(c) * abserr_b;
+                    for (i = 0; i < m; i++) {
+                        T uj = U[jm + i], uk = U[km + i];
+                        U[jm + i] = uj * c + nsn * uk;
+                        U[km + i] = sn * uj + uk * c;
+                    }
+                    for (i = 0; i < n; i++) {
+                        T vj = V[jn + i], vk = V[kn + i];
+                        V[jn + i] = vj * c + nsn * vk;
+                        V[kn + i] = sn * vj + vk * c;
+                    }
+                }
+                km += m; kn += n;
+            }
+            jm += m; jn += n;
+        }
+        sweep++;
+    }
+    T sigma_tol = 0.0;
+    I iszero = n;
+    for (j = 0; j < n; j++) {
+        T cur = vec_norm(U + j * m, m);
+        if (j == 0) { T alpha = 50.0 / sqrt(sqrt(eps)); sigma_tol = alpha * cur * eps; }
+        if (cur <= sigma_tol) {
+            iszero--;
+            S[j] = 0.0;
+            for (i = 0; i < m; i++) U[j * m + i] = 0.0;
+        } else {
+            S[j] = cur;
+            for (i = 0; i < m; i++) U[j * m + i] = U[j * m + i] / cur;
+        }
+    }
+    if (iszero == 0) {
+        for (i = 0; i < nsq; i++) V[i] = 0.0;
+        for (i = 0; i < nsq; i += n + 1) V[i] = 1.0;
+        for (i = 0; i < n * m; i += m + 1) U[i] = 1.0;
+        return 0;
+    }
+    return count > 0 ? 1 : 0;
+}
+
+void orc_pinv_array(T *AA, I m, I n, I transA)
+{
+    const I nsq = n * n;
+    T *Tran = (T *)malloc(sizeof(T) * nsq), *U = (T *)malloc(sizeof(T) * nsq), *V = (T *)malloc(sizeof(T) * nsq);
+    T *SinvUh = (T *)malloc(sizeof(T) * nsq), *S = (T *)malloc(sizeof(T) * n);
+    for (I blk = 0; blk < m; blk++) {
+        T *A = AA + (size_t)blk * nsq;
+        if (transA) {
+            for (I r = 0; r < n; r++) for (I c = 0; c < n; c++) Tran[c * n + r] = A[r * n + c];
+            svd_jacobi(Tran, U, V, S, n, n);
+        } else {
+            svd_jacobi(A, U, V, S, n, n);
+        }
+        for (I j = 0; j < n; j++) if (S[j] != 0.0) S[j] = 1.0 / S[j];
+        I counter = 0;
+        for (I j = 0; j < n; j++) {                 /* Sinv(k) * U(j,k) -> SinvUh(k,j), column major */
+            I uo = j;
+            for (I k = 0; k < n; k++) { SinvUh[counter] = U[uo] * S[k]; counter++; uo += n; }
+        }
+        for (I r = 0; r < n; r++) for (I c = 0; c < n; c++) Tran[c * n + r] = V[r * n + c];
+        /* gemm(Tran row-major n x n, SinvUh column-major, out row-major, overwrite): out[i][j] = sum_k Tran[i][k] SinvUh[k + j n] */
+        for (I i = 0; i < n; i++)
+            for (I j = 0; j < n; j++) {
+                T sum = 0.0;
+                for (I k = 0; k < n; k++) sum += Tran[i * n + k] * SinvUh[j * n + k];
+                A[i * n + j] = sum;
+            }
+    }
+    free(Tran); free(U); free(V); free(SinvUh); free(S);
 }

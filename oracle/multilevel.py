@@ -25,6 +25,7 @@ def _smoother(spec, core=None):
         return lambda A, x, b: None
     fn = {'jacobi': _rx.jacobi, 'gauss_seidel': _rx.gauss_seidel,
           'gauss_seidel_indexed': _rx.gauss_seidel_indexed, 'bsr_gauss_seidel_indexed': _rx.bsr_gauss_seidel_indexed,
+          'block_jacobi': _rx.block_jacobi, 'block_gauss_seidel': _rx.block_gauss_seidel,
           'polynomial': _rx.polynomial}[name]
     return lambda A, x, b: fn(A, x, b, core=core, **kw)
 

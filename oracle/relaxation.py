@@ -128,6 +128,51 @@ def bsr_gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', co
                     core.bsr_gauss_seidel(A.indptr, A.indices, data, x, b, i, i + dr, dr, bs)
 
 
+def _block_system(A, x, b, blocksize, Dinv):
+    A, x, b = make_system(A, x, b, formats=['csr', 'bsr'])
+    A = A.tobsr(blocksize=(blocksize, blocksize))
+    if Dinv.shape[0] != A.shape[0] // blocksize:
+        raise ValueError('Dinv and A have incompatible dimensions')
+    if Dinv.shape[1] != blocksize or Dinv.shape[2] != blocksize:
+        raise ValueError('Dinv and blocksize are incompatible')
+    return A, x, b, np.ravel(np.ascontiguousarray(Dinv, dtype=np.float64))
+
+
+def block_jacobi(A, x, b, Dinv, blocksize, iterations=1, omega=1.0, core=None):
+    """pyamg/relaxation/relaxation.py:430-492 with the inverses of the diagonal blocks GIVEN (the reference computes
+    them with LAPACK gelss, utils.py:601-690 -> util/linalg.py:568-649)"""
+    core = core or _o.core
+    A, x, b, Tx = _block_system(A, x, b, blocksize, Dinv)
+    nb = A.shape[0] // blocksize
+    temp = np.empty_like(x)
+    om = np.array([omega], dtype=A.dtype)
+    for _ in range(iterations):
+        core.block_jacobi(A.indptr, A.indices, np.ravel(A.data), x, b, Tx, temp, 0, nb, 1, om, blocksize)
+
+
+def block_gauss_seidel(A, x, b, Dinv, blocksize, iterations=1, sweep='forward', indices=None, core=None):
+    """pyamg/relaxation/relaxation.py:495-592 (Dinv given).  `indices`: block rows relaxed in that order instead, one
+    reference call per block row -- the sequential definition of the block-multicolour sweep."""
+    core = core or _o.core
+    A, x, b, Tx = _block_system(A, x, b, blocksize, Dinv)
+    data = np.ravel(A.data)
+    nb = A.shape[0] // blocksize
+    if indices is not None:
+        indices = np.asarray(indices, dtype='intc')
+    fused = getattr(core, 'block_gauss_seidel_indexed', None)
+    for _ in range(iterations):
+        for direction in (('forward', 'backward') if sweep == 'symmetric' else (sweep,)):
+            r0, r1, dr = _sweep_range(direction, nb if indices is None else len(indices))
+            if indices is None:
+                core.block_gauss_seidel(A.indptr, A.indices, data, x, b, Tx, r0, r1, dr, blocksize)
+            elif fused is not None:
+                fused(A.indptr, A.indices, data, x, b, Tx, indices, r0, r1, dr, blocksize)
+            else:
+                for p in range(r0, r1, dr):
+                    i = int(indices[p])
+                    core.block_gauss_seidel(A.indptr, A.indices, data, x, b, Tx, i, i + dr, dr, blocksize)
+
+
 def polynomial(A, x, b, coefficients, iterations=1, core=None):
     """pyamg/relaxation/relaxation.py:593-668 (what 'chebyshev' resolves to, smoothing.py:438-449): numpy / scipy
     expressions exactly as the reference writes them."""

@@ -25,6 +25,7 @@ class LevelDesc(Structure):
         ('Id', p), ('color_ptr_host', POINTER(c_int)), ('K', c_int),
         ('pre_ncoef', c_int), ('post_ncoef', c_int),
         ('pre_coef', c_double * 8), ('post_coef', c_double * 8),
+        ('Dinv', p),
     ]
 
 
@@ -76,6 +77,11 @@ _SIGS = {
     'b200amg_bsr_sub': (c_int, [c_int, c_int, c_int, p, p, p, p, p, p, c_int, c_int, p, p, p, p, p]),
     'b200amg_bsr_slot_map': (c_int, [c_int, p, p, p, p, p, p]),
     'b200amg_bsr_matmat_numeric': (c_int, [c_int, c_int, c_int, c_int, p, p, p, p, p, p, p, p, p, c_longlong, p, p]),
+    'b200amg_block_jacobi': (c_int, [p, p, p, p, p, p, p, c_int, c_int, c_int, c_double, c_int, p]),
+    'b200amg_block_gauss_seidel': (c_int, [p, p, p, p, p, p, c_int, c_int, c_int, c_int, p, POINTER(c_int), c_int, p]),
+    'b200amg_block_diag_inverse': (c_int, [c_int, c_int, p, p, p, p, p]),
+    'b200amg_block_diag_inverse_gj': (c_int, [c_int, c_int, p, p, p, p, p]),
+    'b200amg_pinv_array': (c_int, [p, c_int, c_int, c_int, p]),
     'b200amg_rs_strength': (c_int, [c_int, c_double, p, p, p, c_int, c_int, p, p, p, p, p]),
     'b200amg_csr_not_canonical': (c_int, [c_int, p, p, p, p]),
     'b200amg_rs_direct_interpolation_pass1': (c_int, [c_int, p, p, p, p, p]),
@@ -83,6 +89,7 @@ _SIGS = {
     'b200amg_rs_cf_splitting_host': (c_int, [c_int, p, p, p, p, p]),
     'b200amg_vertex_coloring_mis_host': (c_int, [c_int, p, p, p]),
     'b200amg_standard_aggregation_host': (c_int, [c_int, p, p, p, p]),
+    'b200amg_level_desc_size': (c_int, []),
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),
     'b200amg_vcycle_create': (c_int, [c_int, POINTER(LevelDesc), p, p, c_longlong, POINTER(c_void_p)]),
     'b200amg_vcycle_run': (c_int, [p, p, p, c_int, c_int, p]),

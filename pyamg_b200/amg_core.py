@@ -3,8 +3,8 @@
 device arrays (torch CUDA tensors: int32 indices, float64 values).  Like the SWIG
 INPLACE_ARRAY1 typemaps (amg_core.i:27-92) they refuse wrong dtypes (TypeError) and
 non-contiguous arrays (ValueError) instead of converting, mutate `x` / `temp` in place and
-return None.  Two optional trailing arguments extend gauss_seidel_indexed / bsr_gauss_seidel:
-`color_ptr` (host ints) declares colour groups inside `Id`, enabling the parallel sweep.
+return None.  Two optional trailing arguments extend gauss_seidel_indexed / bsr_gauss_seidel /
+block_gauss_seidel: `color_ptr` (host ints) declares colour groups inside `Id`, enabling the parallel sweep.
 """
 import ctypes
 
@@ -121,3 +121,20 @@ def rs_cf_splitting(n_nodes, Sp, Sj, Tp, Tj, splitting):
                                           splitting.ctypes.data)
     if rc != 0:
         raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+
+
+def block_jacobi(Ap, Aj, Ax, x, b, Tx, temp, row_start, row_stop, row_step, omega, blocksize):
+    """relaxation.h:661-727 (Tx = inverses of the diagonal blocks, [n_brow * bs * bs])"""
+    p = _csr(Ap, Aj, Ax)
+    _lib.call('b200amg_block_jacobi', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              _chk(Tx, torch.float64, 'Tx'), _chk(temp, torch.float64, 'temp'), int(row_start), int(row_stop),
+              int(row_step), _omega(omega), int(blocksize), _stream())
+
+
+def block_gauss_seidel(Ap, Aj, Ax, x, b, Tx, row_start, row_stop, row_step, blocksize, Id=None, color_ptr=None):
+    """relaxation.h:753-806; with (Id, color_ptr): block rows grouped by colour, one parallel launch per colour"""
+    p = _csr(Ap, Aj, Ax)
+    cp, K = _cptr(color_ptr)
+    _lib.call('b200amg_block_gauss_seidel', *p, _chk(x, torch.float64, 'x'), _chk(b, torch.float64, 'b'),
+              _chk(Tx, torch.float64, 'Tx'), int(row_start), int(row_stop), int(row_step), int(blocksize),
+              0 if Id is None else _chk(Id, torch.int32, 'Id'), cp, K, _stream())

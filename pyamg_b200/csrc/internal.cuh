@@ -98,6 +98,18 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
 int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                       const int *Id, int start, int stop, int step, cudaStream_t st);
 
+// block relaxation with stored diagonal-block inverses (block_relax.cu); block_jacobi_pp reads xin, writes xout
+int block_jacobi_pp(int bs, int nb, const int *Ap, const int *Aj, const double *Ax, const double *xin, double *xout,
+                    const double *b, const double *Dinv, double omega, cudaStream_t st);
+int block_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b, const double *Dinv,
+                   const int *Id, int p0, int p1, cudaStream_t st);
+int block_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
+                        const double *Dinv, const int *Id, int start, int stop, int step, cudaStream_t st);
+
+int block_diag_inverse_gj(int n_brow, int bs, const int *Ap, const int *Aj, const double *Ax, double *Dinv, cudaStream_t st);
+// amg_core.pinv_array on the device (pinv.cu, compiled without FMA contraction), n <= 6
+int pinv_array(double *AA, int m, int n, int transA, cudaStream_t st);
+
 int dot(long long n, const double *x, const double *y, double *out, double *work, cudaStream_t st);
 int axpy(long long n, double a, const double *x, double *y, cudaStream_t st);
 int scal(long long n, double a, const double *x, double *y, cudaStream_t st);

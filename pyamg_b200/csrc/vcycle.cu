@@ -204,6 +204,35 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
         }
         return 0;
     }
+    if (kind == 5) {                                   // block Jacobi: ping-pong like kind 1
+        const int nb = d.n / d.bs;
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        for (int it = 0; it < iters; ++it) {
+            B200_TRY(block_jacobi_pp(d.bs, nb, d.Ap, d.Aj, d.Ax, *cur, *spare, b, d.Dinv, omega, st));
+            double *t = *cur; *cur = *spare; *spare = t;
+        }
+        return 0;
+    }
+    if (kind == 6 || kind == 7) {                      // block Gauss-Seidel: colour-ordered / lexicographic
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
+        const int nb = d.n / d.bs, K = d.K;
+        for (int it = 0; it < iters; ++it) {
+            for (int pass = 0; pass < 2; ++pass) {
+                const bool bwd = (pass == 1);
+                if ((sweep == 0 && bwd) || (sweep == 1 && !bwd)) continue;
+                if (kind == 7) {
+                    B200_TRY(block_gs_sequential(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Dinv, nullptr, bwd ? nb - 1 : 0,
+                                                 bwd ? -1 : nb, bwd ? -1 : 1, st));
+                    continue;
+                }
+                for (int q = 0; q < K; ++q) {
+                    const int c = bwd ? K - 1 - q : q;
+                    B200_TRY(block_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Dinv, d.Id, L.color_ptr[c], L.color_ptr[c + 1], st));
+                }
+            }
+        }
+        return 0;
+    }
     return set_err(B200AMG_EINVAL, "smooth: unknown smoother kind");
 }
 
@@ -247,7 +276,7 @@ static int cycle(Engine &E, int k, double *x, const double *b, int kind, bool x_
     // The iterate must end in x.  Jacobi sweeps ping-pong between x and the spare buffer; when the sweeps still to
     // come would leave the result in the spare buffer, the correction is written OUT OF PLACE (other buffer =
     // iterate + P x_c, same bits) -- one more swap, and the D2D copy back to x disappears.
-    const int swaps_to_come = d.post_kind == 1 ? d.post_iters : 0;
+    const int swaps_to_come = (d.post_kind == 1 || d.post_kind == 5) ? d.post_iters : 0;
     if (((cur == x) ? 0 : 1) != (swaps_to_come & 1)) {
         B200_TRY(prolong_add(L, L.xc, cur, spare, st));
         double *t = cur; cur = spare; spare = t;
@@ -307,7 +336,11 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
         }
         L.bc = w; w += al(L.d.nc);
         L.xc = w; w += al(L.d.nc);
-        if (L.d.pre_kind == 2 || L.d.post_kind == 2) {
+        for (int side = 0; side < 2; ++side) {
+            const int kind = side ? L.d.post_kind : L.d.pre_kind;
+            if (kind >= 5 && kind <= 7 && !L.d.Dinv) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: block smoother without Dinv"); }
+        }
+        if (L.d.pre_kind == 2 || L.d.post_kind == 2 || L.d.pre_kind == 6 || L.d.post_kind == 6) {
             if (!L.d.color_ptr_host || !L.d.Id || L.d.K < 0) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: colour ordering missing"); }
             L.color_ptr.assign(L.d.color_ptr_host, L.d.color_ptr_host + L.d.K + 1);
             L.d.color_ptr_host = nullptr;
@@ -466,3 +499,5 @@ extern "C" int b200amg_vcycle_destroy(void *handle)
     delete E;
     return 0;
 }
+
+extern "C" int b200amg_level_desc_size(void) { return (int)sizeof(b200amg_level_desc); }

@@ -28,8 +28,8 @@ def import_hierarchy(levels, presmoother=None, postsmoother=None, coarse_solver=
 
 def _norho(spec):
     """imported specs carry RESOLVED parameters (omega already divided by rho)"""
-    if isinstance(spec, tuple) and spec[0] == 'jacobi':
+    if isinstance(spec, tuple) and spec[0] in ('jacobi', 'block_jacobi'):
         kw = dict(spec[1])
         kw.setdefault('withrho', False)
-        return ('jacobi', kw)
+        return (spec[0], kw)
     return spec

@@ -27,9 +27,10 @@ class _Smoother:
     """resolved smoother of one level: kind, omega, iterations, sweep (+ colour ordering)"""
 
     def __init__(self, kind=0, omega=1.0, iterations=1, sweep='forward', indices=None, color_ptr=None, name=None,
-                 coefficients=None):
+                 coefficients=None, Dinv=None):
         self.kind, self.omega, self.iterations, self.sweep = kind, float(omega), int(iterations), sweep
         self.indices, self.color_ptr, self.name = indices, color_ptr, name
+        self.Dinv = Dinv                              # kinds 5-7: inverses of the diagonal blocks, device [n_brow, bs, bs]
         self.coefficients = None if coefficients is None else [float(c) for c in coefficients]   # kind 4: polynomial
 
 
@@ -186,7 +187,17 @@ class multilevel_solver:
                     setattr(d, side + '_ncoef', len(sm.coefficients))
                     for q, c in enumerate(sm.coefficients):
                         getattr(d, side + '_coef')[q] = c
-            ordered = [s for s in (pre, post) if s.kind == 2]
+            blocked = [s for s in (pre, post) if s.kind in (5, 6, 7)]
+            if blocked:
+                Dinv = blocked[0].Dinv
+                if any(s.Dinv is not Dinv and not torch.equal(s.Dinv, Dinv) for s in blocked[1:]):
+                    raise ValueError('pre- and post-smoother must share one set of diagonal-block inverses per level')
+                if tuple(Dinv.shape) != (A.n_brow, A.blocksize[0], A.blocksize[0]):
+                    raise ValueError('Dinv and A have incompatible dimensions')
+                Dinv = Dinv.contiguous()
+                keep.append(Dinv)
+                d.Dinv = _ptr(Dinv)
+            ordered = [s for s in (pre, post) if s.kind in (2, 6)]
             if ordered:
                 s0 = ordered[0]
                 for s in ordered[1:]:

@@ -104,6 +104,65 @@ def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', color_
         amg_core.gauss_seidel_indexed(A.indptr, A.indices, A.data, x, b, indices, r0, r1, dr, color_ptr)
 
 
+def get_block_diag_inverse(A, blocksize=None):
+    """inverses of the diagonal blocks, [n_brow, bs, bs] on the device (pyamg/util/utils.py:601-690 with
+    inv_flag=True; cached on the matrix like the reference's A.block_D_inv).  Gauss-Jordan per block: equal to the
+    reference's LAPACK result to rounding, zero for a numerically singular block."""
+    bs = A.blocksize[0] if blocksize is None else int(blocksize)
+    if A.blocksize != (bs, bs):
+        raise NotImplementedError('re-blocking on the device is not available: A must be BSR with the requested blocksize')
+    cached = getattr(A, 'block_D_inv', None)
+    if cached is not None and tuple(cached.shape) == (A.n_brow, bs, bs):
+        return cached
+    Dinv = torch.empty((A.n_brow, bs, bs), dtype=torch.float64, device=A.data.device)
+    _lib.call('b200amg_block_diag_inverse', A.n_brow, bs, A.indptr.data_ptr(), A.indices.data_ptr(), A.data.data_ptr(),
+              Dinv.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    A.block_D_inv = Dinv
+    return Dinv
+
+
+def _block_args(A, x, b, blocksize, Dinv):
+    A, x, b = make_system(A, x, b, formats=['csr', 'bsr'])
+    blocksize = int(blocksize)
+    if A.blocksize != (blocksize, blocksize):
+        raise NotImplementedError('re-blocking on the device is not available: A must be BSR with the requested blocksize')
+    if Dinv is None:
+        Dinv = get_block_diag_inverse(A, blocksize)
+    elif Dinv.shape[0] != A.shape[0] // blocksize:
+        raise ValueError('Dinv and A have incompatible dimensions')
+    elif Dinv.shape[1] != blocksize or Dinv.shape[2] != blocksize:
+        raise ValueError('Dinv and blocksize are incompatible')
+    return A, x, b, blocksize, Dinv.contiguous().view(-1)
+
+
+def block_jacobi(A, x, b, Dinv=None, blocksize=1, iterations=1, omega=1.0):
+    """pyamg/relaxation/relaxation.py:430-492"""
+    A, x, b, bs, Tx = _block_args(A, x, b, blocksize, Dinv)
+    nb = A.shape[0] // bs
+    if nb <= 0:
+        return
+    temp = torch.empty_like(x)
+    for _ in range(iterations):
+        amg_core.block_jacobi(A.indptr, A.indices, A.data, x, b, Tx, temp, 0, nb, 1, [omega], bs)
+
+
+def block_gauss_seidel(A, x, b, iterations=1, sweep='forward', blocksize=1, Dinv=None, indices=None, color_ptr=None):
+    """pyamg/relaxation/relaxation.py:495-592.  Without `indices`: the reference's lexicographic sweep (sequential on the
+    device).  With `indices` (block rows grouped by colour) and `color_ptr`: the colours one after the other, the rows
+    of a colour in parallel."""
+    A, x, b, bs, Tx = _block_args(A, x, b, blocksize, Dinv)
+    if indices is not None and not isinstance(indices, torch.Tensor):
+        indices = torch.from_numpy(np.ascontiguousarray(indices, dtype='intc')).to(x.device)
+    if sweep == 'symmetric':
+        for _ in range(iterations):
+            block_gauss_seidel(A, x, b, 1, 'forward', bs, Dinv, indices, color_ptr)
+            block_gauss_seidel(A, x, b, 1, 'backward', bs, Dinv, indices, color_ptr)
+        return
+    r0, r1, dr = _range(sweep, A.shape[0] // bs if indices is None else int(indices.numel()))
+    for _ in range(iterations):
+        amg_core.block_gauss_seidel(A.indptr, A.indices, A.data, x, b, Tx, r0, r1, dr, bs, indices, color_ptr)
+
+
 def polynomial(A, x, b, coefficients, iterations=1):
     """pyamg/relaxation/relaxation.py:593-668: x += p(A)(b - A x) with p given by its coefficients (highest power
     first), Horner form: h = c0 r; h = c_k r + A h.  The reference's "norm(x) == 0 -> residual = b" shortcut gives

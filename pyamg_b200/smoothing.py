@@ -2,7 +2,8 @@
 
 A smoother spec is `name`, `(name, {opts})`, or a per-level list of those -- the same forms the
 reference accepts (smoothing.py:37-57,126-169).  Names with a device kernel:
-jacobi, gauss_seidel, gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev / polynomial, None.
+jacobi, gauss_seidel, gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev / polynomial, block_jacobi,
+block_gauss_seidel, multicolor_block_gauss_seidel, None.
 """
 import numpy as np
 import torch
@@ -21,6 +22,42 @@ def rho_D_inv_A(A):
         dinv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
         A.rho_D_inv = approximate_spectral_radius(A, row_scale=dinv)
     return A.rho_D_inv
+
+
+class _BlockDinvA:
+    """x -> Dinv (A x) without forming the product (smoothing.py:243-247)"""
+
+    def __init__(self, A, Dinv):
+        n = A.n_brow
+        bs = A.blocksize[0]
+        ar = torch.arange(n + 1, dtype=torch.int32, device=A.data.device)
+        self.D = DevMat(ar, ar[:-1].contiguous(), Dinv.contiguous().view(-1), A.shape, (bs, bs), 'bsr', True)
+        self.A = A
+        self.shape = A.shape
+
+    def matvec(self, v):
+        return self.D.matvec(self.A.matvec(v))
+
+
+def rho_block_D_inv_A(A, Dinv):
+    """spectral radius of (block D)^-1 A, cached on the matrix (smoothing.py:203-250)"""
+    if not hasattr(A, 'rho_block_D_inv'):
+        A.rho_block_D_inv = approximate_spectral_radius(_BlockDinvA(A, Dinv))
+    return A.rho_block_D_inv
+
+
+def _block_setup(A, kw):
+    """blocksize / Dinv resolution of setup_block_jacobi / setup_block_gauss_seidel (smoothing.py:366-420)"""
+    Dinv, blocksize = kw.pop('Dinv', None), kw.pop('blocksize', None)
+    if blocksize is None:
+        blocksize = A.blocksize[0] if Dinv is None else int(Dinv.shape[1])
+    if blocksize != 1 and Dinv is None:
+        Dinv = relaxation.get_block_diag_inverse(A, blocksize)
+    if Dinv is not None and not isinstance(Dinv, torch.Tensor):
+        Dinv = torch.from_numpy(np.ascontiguousarray(Dinv, dtype=np.float64)).to(_dev())
+    if blocksize != 1 and A.blocksize != (blocksize, blocksize):
+        raise NotImplementedError('re-blocking on the device is not available: A must be BSR with the requested blocksize')
+    return int(blocksize), Dinv
 
 
 def chebyshev_polynomial_coefficients(a, b, degree):
@@ -79,6 +116,30 @@ def _resolve(spec, lvl):
             if not isinstance(idx, torch.Tensor):
                 idx = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.intc)).to(_dev())
         return _Smoother(2, 1.0, iters, sweep, idx, np.ascontiguousarray(ptr, dtype=np.intc), name=name)
+    if name == 'block_jacobi':
+        bs, Dinv = _block_setup(A, kw)
+        if bs == 1:                                     # block Jacobi is equivalent to normal Jacobi (smoothing.py:377-380)
+            return _resolve(('jacobi', kw), lvl)
+        omega, iters = kw.pop('omega', 1.0), kw.pop('iterations', 1)
+        if kw.pop('withrho', True):
+            omega = omega / rho_block_D_inv_A(A, Dinv)
+        if kw:
+            raise TypeError('block_jacobi: unexpected options %r' % sorted(kw))
+        return _Smoother(5, omega, iters, name=name, Dinv=Dinv)
+    if name in ('block_gauss_seidel', 'multicolor_block_gauss_seidel'):
+        bs, Dinv = _block_setup(A, kw)
+        if bs == 1:
+            return _resolve(('gauss_seidel' if name == 'block_gauss_seidel' else 'multicolor_gauss_seidel', kw), lvl)
+        iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
+        if kw:
+            raise TypeError('%s: unexpected options %r' % (name, sorted(kw)))
+        if name == 'block_gauss_seidel':                # the reference's lexicographic order: sequential on the device
+            return _Smoother(7, 1.0, iters, sweep, name=name, Dinv=Dinv)
+        if not hasattr(lvl, '_mc_order'):
+            idx, ptr = relaxation.color_ordering(relaxation.vertex_coloring(A, 'MIS'))
+            lvl._mc_order = (torch.from_numpy(idx).to(_dev()), ptr)
+        idx, ptr = lvl._mc_order
+        return _Smoother(6, 1.0, iters, sweep, idx, np.ascontiguousarray(ptr, dtype=np.intc), name=name, Dinv=Dinv)
     if name in ('polynomial', 'chebyshev'):
         iters = kw.pop('iterations', 1)
         if name == 'polynomial':
@@ -93,7 +154,8 @@ def _resolve(spec, lvl):
             raise TypeError('%s: unexpected options %r' % (name, sorted(kw)))
         return _Smoother(4, 1.0, iters, name=name, coefficients=np.asarray(coef, dtype=np.float64))
     raise ValueError('smoother %r has no device kernel (available: jacobi, gauss_seidel, '
-                     'gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev, polynomial, None)' % (name,))
+                     'gauss_seidel_indexed, multicolor_gauss_seidel, chebyshev, polynomial, block_jacobi, block_gauss_seidel, '
+                     'multicolor_block_gauss_seidel, None)' % (name,))
 
 
 def change_smoothers(ml, presmoother, postsmoother):

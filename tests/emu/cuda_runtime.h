@@ -2,7 +2,7 @@
 // (pyamg_b200/csrc/*.cu, unchanged) for the HOST, so that thread-per-row / warp-per-row kernels can be checked
 // against scipy in this GPU-less container before they ever see hardware (tests/test_emulated_kernels.py).
 // Every CUDA thread of a block is a real OS thread; __syncthreads / __syncwarp are barriers; blocks run one after
-// the other.  Supports what the setup kernels use: no shuffles, no shared memory, no atomics.  The product never
+// the other.  Supports what the emulated kernels use: barriers and full-warp __shfl_sync; no shared memory, no atomics.  The product never
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
 #include <barrier>
@@ -42,7 +42,8 @@ namespace cuda_emu {
 struct BlockSync {
     std::barrier<> block;
     std::vector<std::unique_ptr<std::barrier<>>> warp;
-    explicit BlockSync(int nthreads) : block(nthreads) {
+    std::vector<unsigned long long> slots;           // one 8-byte exchange slot per thread (warp shuffles)
+    explicit BlockSync(int nthreads) : block(nthreads), slots(((nthreads + 31) / 32) * 32) {
         for (int w = 0; w < (nthreads + 31) / 32; ++w)
             warp.emplace_back(new std::barrier<>(std::min(32, nthreads - 32 * w)));
     }
@@ -76,6 +77,26 @@ void launch(dim3 grid, dim3 block, F body)
 
 inline void __syncthreads() { cuda_emu::cur->block.arrive_and_wait(); }
 inline void __syncwarp(unsigned = 0xffffffffu) { cuda_emu::cur->warp[threadIdx.x / 32]->arrive_and_wait(); }
+
+// full-warp shuffle: every lane of the warp that is still in the kernel must call it (true of the kernels emulated
+// here: lanes leave only at the end)
+template <class T>
+inline T __shfl_sync(unsigned, T v, int src, int width = 32)
+{
+    static_assert(sizeof(T) <= 8, "shuffle payload");
+    cuda_emu::BlockSync *s = cuda_emu::cur;
+    const unsigned tid = threadIdx.x, w = tid / 32, lane = tid % 32;
+    unsigned long long raw = 0;
+    memcpy(&raw, &v, sizeof(T));
+    s->slots[tid] = raw;
+    s->warp[w]->arrive_and_wait();
+    const unsigned from = (lane / width) * width + ((unsigned)src % width);
+    raw = s->slots[w * 32 + from];
+    s->warp[w]->arrive_and_wait();
+    T out;
+    memcpy(&out, &raw, sizeof(T));
+    return out;
+}
 
 #define B200_LAUNCH(kernel, grid, block, smem, stream, ...) \
     cuda_emu::launch(dim3(grid), dim3(block), [&] { kernel(__VA_ARGS__); })

@@ -144,6 +144,40 @@ def sa_elasticity3d(name, nv, improve=True):
           [getattr(l, 'P', None) is not None and l.P.blocksize for l in ml.levels], res[0], res[-1])
 
 
+def sa_elasticity3d_block_smoothers(name, nv):
+    """The reference's DEFAULT smoother on a block problem: symmetric block_gauss_seidel with the inverses of the
+    diagonal blocks from get_block_diag (amg_core.pinv_array for 3x3 / 6x6 blocks), plus a block_jacobi(4/3) run on the
+    same hierarchy.  The inverses and the resolved omega (4/3 / rho_block_D_inv_A) are stored, so that cycles replay
+    with exactly the reference's numbers; candidates as given (improve_candidates=None)."""
+    from pyamg.gallery import linear_elasticity_p1
+    from pyamg.relaxation.smoothing import change_smoothers
+    import scipy.sparse as sp
+    V, E = tet_grid(nv)
+    A, B = linear_elasticity_p1(V, E, format='bsr')
+    free = np.where(V[:, 0] > 0)[0]
+    dof = (3 * free[:, None] + np.arange(3)[None, :]).ravel()
+    A = sp.csr_matrix(A)[dof][:, dof].tobsr(blocksize=(3, 3))
+    B = B[dof]
+    np.random.seed(0)
+    ml = pyamg.smoothed_aggregation_solver(A, B, max_coarse=10, improve_candidates=None)     # default pre/post smoothers
+    b, res, x = run(ml, A.shape[0], 8)
+    specs = []
+    for lvl in ml.levels[:-1]:
+        Dinv = np.array(lvl.A.block_D_inv)
+        sp_ = ('block_gauss_seidel', {'Dinv': Dinv, 'blocksize': int(Dinv.shape[1]), 'sweep': 'symmetric', 'iterations': 1})
+        specs.append((sp_, sp_))
+    extra = {'B': B, 'b': b, 'residuals': res, 'x': x}
+    bj = ('block_jacobi', {'omega': 4.0 / 3.0})
+    change_smoothers(ml, bj, bj)
+    r2 = []
+    x2 = ml.solve(b, tol=1e-30, maxiter=8, residuals=r2)
+    extra.update({'bj_residuals': np.array(r2), 'bj_x': x2})
+    for k, lvl in enumerate(ml.levels[:-1]):
+        extra['bj_omega%d' % k] = (4.0 / 3.0) / lvl.A.rho_block_D_inv
+    hier_io.save(os.path.join(OUT, name), ml.levels, specs, extra)
+    print(name, [(l.A.shape[0], l.A.blocksize) for l in ml.levels], res[0], res[-1], r2[-1])
+
+
 def sa_chebyshev(name, grid, max_coarse):
     """SA hierarchy with the reference's 'chebyshev' smoother (smoothing.py:438-449 -> relaxation.polynomial).  The
     coefficients the reference resolved (from its own random-start spectral-radius estimate) are read back out of the
@@ -208,6 +242,9 @@ def sa_elasticity(name, grid):
 
 
 if __name__ == '__main__':
+    if sys.argv[1:] == ['elasticity3d_block_smoothers']:
+        sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)
+        sys.exit(0)
     if sys.argv[1:] == ['elasticity3d_setup']:           # only the fixture added last (the others are unchanged)
         sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
         sys.exit(0)
@@ -220,3 +257,4 @@ if __name__ == '__main__':
     sa_chebyshev('sa_poisson3d_12_chebyshev.npz', (12, 12, 12), 20)
     sa_elasticity3d('sa_elasticity3d_tets_7.npz', 7)
     sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
+    sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)

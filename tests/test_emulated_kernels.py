@@ -27,19 +27,26 @@ EMU = os.path.join(HERE, 'emu')
 c_int, c_ll, c_dbl, vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_double, ctypes.c_void_p
 
 
-@pytest.fixture(scope='module')
-def emu():
+def build_emu(stem, extra=()):
+    """pyamg_b200/csrc/<stem>.cu (+ extra stems) compiled for the host with the stand-in CUDA header -> ctypes library"""
     if shutil.which('g++') is None:
         pytest.skip('g++ not available')
-    out = os.path.join(EMU, '_build', 'libemu_bsr_setup.so')
-    src = os.path.join(ROOT, 'pyamg_b200', 'csrc', 'bsr_setup.cu')
-    deps = [src, os.path.join(EMU, 'cuda_runtime.h'), os.path.join(EMU, 'emu_globals.cpp'),
-            os.path.join(ROOT, 'pyamg_b200', 'csrc', 'common.cuh'), os.path.join(ROOT, 'include', 'b200amg.h')]
+    out = os.path.join(EMU, '_build', 'libemu_%s.so' % stem)
+    srcs = [os.path.join(ROOT, 'pyamg_b200', 'csrc', st + '.cu') for st in (stem,) + tuple(extra)]
+    src = srcs[0]
+    deps = srcs + [os.path.join(EMU, 'cuda_runtime.h'), os.path.join(EMU, 'emu_globals.cpp'),
+            os.path.join(ROOT, 'pyamg_b200', 'csrc', 'common.cuh'), os.path.join(ROOT, 'pyamg_b200', 'csrc', 'internal.cuh'),
+            os.path.join(ROOT, 'include', 'b200amg.h')]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         os.makedirs(os.path.dirname(out), exist_ok=True)
         subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU,
-                        '-x', 'c++', src, os.path.join(EMU, 'emu_globals.cpp'), '-o', out], check=True)
-    lib = ctypes.CDLL(out)
+                        '-x', 'c++'] + srcs + [os.path.join(EMU, 'emu_globals.cpp'), '-o', out], check=True)
+    return ctypes.CDLL(out)
+
+
+@pytest.fixture(scope='module')
+def emu():
+    lib = build_emu('bsr_setup')
     sigs = {
         'b200amg_bsr_scale_rows': [c_int, c_int, c_int, vp, vp, vp, c_dbl, c_int, vp, vp],
         'b200amg_bsr_gather_blocks': [c_ll, c_int, c_int, vp, vp, vp, c_int, vp],
@@ -310,3 +317,163 @@ def test_block_sa_hierarchy_equals_reference_fixture(emu, golden_dir):
         assert np.array_equal(Bc, ref[k + 1].B)
         cur_A, cur_B = Ac, Bc
     assert same(cur_A, levels[-1].A)                       # the coarsest operator stays in bsr_matmat's first-touch order
+
+
+# ---- block relaxation (csrc/block_relax.cu) against the reference's compiled kernels -----------------------------------
+@pytest.fixture(scope='module')
+def emu_relax():
+    lib = build_emu('pinv', extra=('block_relax',))
+    from pyamg_b200 import _lib
+    for name in ('b200amg_block_jacobi', 'b200amg_block_gauss_seidel', 'b200amg_block_diag_inverse',
+                 'b200amg_block_diag_inverse_gj', 'b200amg_pinv_array'):
+        f = getattr(lib, name)
+        f.restype, f.argtypes = _lib._SIGS[name]
+    return lib
+
+
+def block_problem(nb, bs, seed, diag=True):
+    rng = np.random.RandomState(seed)
+    pat = sp.csr_matrix(sp.random(nb, nb, 0.15, random_state=rng, format='csr') + (sp.identity(nb) if diag else 0))
+    pat = sp.csr_matrix(pat + pat.T)
+    pat.sort_indices()
+    data = rng.randn(len(pat.indices), bs, bs)
+    A = sp.bsr_matrix((data, pat.indices.astype(np.int32), pat.indptr.astype(np.int32)), shape=(nb * bs, nb * bs))
+    return A, rng.randn(nb, bs, bs), rng.randn(nb * bs), rng.randn(nb * bs)
+
+
+CORE = oracle.ref if oracle.ref is not None else oracle.port          # the reference's own block kernels when built
+
+
+@pytest.mark.parametrize('bs', [1, 2, 3, 5, 6, 8])
+def test_block_gauss_seidel_sequential_equals_reference(emu_relax, bs):
+    A, Dinv, b, x0 = block_problem(45, bs, bs)
+    Ap, Aj, Ax, Tx = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy(), np.ravel(Dinv).copy()
+    for r0, r1, dr in ((0, 45, 1), (44, -1, -1), (3, 33, 3), (7, 7, 1)):
+        want, got = x0.copy(), x0.copy()
+        if r0 != r1:
+            CORE.block_gauss_seidel(Ap, Aj, Ax, want, b, Tx, r0, r1, dr, bs)
+        assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), r0, r1, dr, bs, None, None, 0, None) == 0
+        assert np.array_equal(got, want), (bs, r0, r1, dr)
+    # an index list with repeats, walked backwards: one reference call per listed block row
+    Id = i32(np.random.RandomState(1).randint(0, 45, 60))
+    want, got = x0.copy(), x0.copy()
+    for p_ in range(59, -1, -1):
+        CORE.block_gauss_seidel(Ap, Aj, Ax, want, b, Tx, int(Id[p_]), int(Id[p_]) - 1, -1, bs)
+    assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), 59, -1, -1, bs, P(Id), None, 0, None) == 0
+    assert np.array_equal(got, want)
+    assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), 0, 10, -1, bs, None, None, 0, None) != 0
+
+
+@pytest.mark.parametrize('bs', [2, 3, 6])
+def test_block_gauss_seidel_colour_ordered_equals_row_by_row_reference(emu_relax, bs):
+    """the parallel form: block rows grouped by MIS colour of the block graph, one launch per colour, forward and
+    backward, against the reference kernel driven one block row at a time in the same order"""
+    from oracle import relaxation as orx
+    A, Dinv, b, x0 = block_problem(150, bs, 10 + bs)
+    Ap, Aj, Ax, Tx = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy(), np.ravel(Dinv).copy()
+    G = sp.csr_matrix((np.ones(len(Aj)), Aj, Ap), shape=(150, 150))
+    idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(G, oracle.port))
+    idx, ptr = i32(idx), np.ascontiguousarray(ptr, dtype=np.intc)
+    K = len(ptr) - 1
+    assert K >= 3
+    cp = ptr.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+    want, got = x0.copy(), x0.copy()
+    for i in idx:
+        CORE.block_gauss_seidel(Ap, Aj, Ax, want, b, Tx, int(i), int(i) + 1, 1, bs)
+    for i in idx[::-1]:
+        CORE.block_gauss_seidel(Ap, Aj, Ax, want, b, Tx, int(i), int(i) - 1, -1, bs)
+    n = len(idx)
+    assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), 0, n, 1, bs, P(idx), cp, K, None) == 0
+    assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), n - 1, -1, -1, bs, P(idx), cp, K, None) == 0
+    assert np.array_equal(got, want)
+    # a range that cuts a colour is refused
+    assert emu_relax.b200amg_block_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), 0, n - 1, 1, bs, P(idx), cp, K, None) != 0
+
+
+@pytest.mark.parametrize('bs', [1, 2, 3, 6, 7])
+def test_block_jacobi_equals_reference(emu_relax, bs):
+    A, Dinv, b, x0 = block_problem(70, bs, 20 + bs)
+    Ap, Aj, Ax, Tx = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy(), np.ravel(Dinv).copy()
+    for (r0, r1, dr), omega in (((0, 70, 1), 0.7), ((0, 70, 1), 1.0), ((4, 64, 4), 1.3), ((69, -1, -1), 0.5)):
+        want, got = x0.copy(), x0.copy()
+        tw, tg = np.full_like(x0, 7.0), np.full_like(x0, 7.0)
+        CORE.block_jacobi(Ap, Aj, Ax, want, b, Tx, tw, r0, r1, dr, np.array([omega]), bs)
+        assert emu_relax.b200amg_block_jacobi(P(Ap), P(Aj), P(Ax), P(got), P(b), P(Tx), P(tg), r0, r1, dr, omega, bs, None) == 0
+        # partial sweeps read temp entries outside the sweep: both sides see the same caller-filled values
+        assert np.array_equal(got, want) and np.array_equal(tg, tw), (bs, r0, r1, dr)
+
+
+@pytest.mark.parametrize('bs', [1, 2, 3, 6, 8])
+def test_block_diag_inverse_gauss_jordan(emu_relax, bs):
+    """the Gauss-Jordan path (used for 7x7 / 8x8 blocks, where the reference calls LAPACK gelss: no bit contract): to
+    rounding against numpy; no diagonal block or a singular one -> zero block"""
+    rng = np.random.RandomState(bs)
+    nb = 60
+    A, _, _, _ = block_problem(nb, bs, 30 + bs)
+    A = A.copy()
+    for i in range(nb):                                     # SPD-ish diagonal blocks like a stiffness matrix
+        q = A.indptr[i] + int(np.where(A.indices[A.indptr[i]:A.indptr[i + 1]] == i)[0][0])
+        M = rng.randn(bs, bs)
+        A.data[q] = M @ M.T + bs * np.eye(bs)
+    q5 = A.indptr[5] + int(np.where(A.indices[A.indptr[5]:A.indptr[6]] == 5)[0][0])
+    A.data[q5] = 0.0
+    if bs > 1:
+        q9 = A.indptr[9] + int(np.where(A.indices[A.indptr[9]:A.indptr[10]] == 9)[0][0])
+        A.data[q9] = np.ones((bs, bs))                      # rank one
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy()
+    Dinv = np.full(nb * bs * bs, np.nan)
+    assert emu_relax.b200amg_block_diag_inverse_gj(nb, bs, P(Ap), P(Aj), P(Ax), P(Dinv), None) == 0
+    Dinv = Dinv.reshape(nb, bs, bs)
+    for i in range(nb):
+        q = A.indptr[i] + int(np.where(A.indices[A.indptr[i]:A.indptr[i + 1]] == i)[0][0])
+        if i == 5 or (i == 9 and bs > 1):
+            assert np.all(Dinv[i] == 0.0)
+        else:
+            ref = np.linalg.inv(A.data[q])
+            assert np.abs(Dinv[i] - ref).max() <= 1e-12 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize('n', [1, 2, 3, 4, 5, 6])
+def test_pinv_array_equals_reference_kernel(emu_relax, n):
+    """amg_core.pinv_array (one-sided Jacobi SVD): SPD, general, zero and rank-deficient blocks, both storage orders --
+    the bits of the reference's compiled kernel"""
+    rng = np.random.RandomState(n)
+    a = rng.randn(150, n, n)
+    for i in range(0, 150, 4):
+        M = rng.randn(n, n)
+        a[i] = M @ M.T + n * np.eye(n)
+    a[7] = 0.0
+    if n > 1:
+        a[9] = np.ones((n, n))
+        a[11][:, 0] = a[11][:, 1]
+    for trans in ('T', 'F'):
+        want, got = a.copy(), a.copy()
+        CORE.pinv_array(want.ravel(), 150, n, trans)
+        assert emu_relax.b200amg_pinv_array(P(got), 150, n, 1 if trans == 'T' else 0, None) == 0
+        assert np.array_equal(got, want), (n, trans)
+    assert emu_relax.b200amg_pinv_array(P(a), 150, 7, 1, None) != 0
+
+
+@pytest.mark.parametrize('bs', [2, 3, 6])
+def test_block_diag_inverse_equals_reference_get_block_diag(emu_relax, bs):
+    """the Dinv the block smoothers get by default: diagonal blocks (zeros where a block row stores none) through
+    pinv_array(..., 'T') -- pyamg/util/utils.py:655-677"""
+    A, _, _, _ = block_problem(80, bs, 40 + bs)
+    # drop the diagonal block of a few rows
+    keep = np.ones(len(A.indices), bool)
+    for i in (3, 17):
+        q = A.indptr[i] + int(np.where(A.indices[A.indptr[i]:A.indptr[i + 1]] == i)[0][0])
+        keep[q] = False
+    cnt = np.add.reduceat(keep.astype(np.int64), A.indptr[:-1])
+    A2 = sp.bsr_matrix((A.data[keep], A.indices[keep], np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)), shape=A.shape)
+    Ap, Aj, Ax = i32(A2.indptr), i32(A2.indices), np.ravel(A2.data).copy()
+    want = np.zeros((80, bs, bs))
+    for i in range(80):
+        for q in range(Ap[i], Ap[i + 1]):
+            if Aj[q] == i:
+                want[i] = A2.data[q]
+    CORE.pinv_array(want.ravel(), 80, bs, 'T')
+    got = np.full(80 * bs * bs, np.nan)
+    assert emu_relax.b200amg_block_diag_inverse(80, bs, P(Ap), P(Aj), P(Ax), P(got), None) == 0
+    assert np.array_equal(got.reshape(80, bs, bs), want)
+    assert np.all(want[3] == 0.0)
