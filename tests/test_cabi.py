@@ -159,3 +159,10 @@ def test_tet_elasticity_generator_equals_reference_gallery(golden_dir):
     # the operator is symmetric and annihilates the rigid-body modes away from the clamped face
     D = (As - As.T)
     assert abs(D).max() <= 1e-10 * np.abs(Aref.data).max()
+
+
+def test_level_descriptor_mirror_matches_the_compiled_struct():
+    """the ctypes mirror of b200amg_level_desc (pyamg_b200/_lib.py) has the size the library was compiled with"""
+    from pyamg_b200 import _lib
+    assert ctypes.sizeof(_lib.LevelDesc) == _lib.load().b200amg_level_desc_size()
+    assert _lib.LevelDesc.Dinv.offset + 8 == ctypes.sizeof(_lib.LevelDesc)
