@@ -167,6 +167,60 @@ def jacobi_prolongation_smoother(S, T, omega=4.0 / 3.0, degree=1):
     return P, rho
 
 
+def _levelize(spec, max_levels):
+    """levelize_smooth_or_improve_candidates (util/utils.py): one spec for all levels, or a list padded with its last"""
+    if isinstance(spec, list):
+        out = list(spec)
+        while len(out) < max_levels:
+            out.append(out[-1])
+        return out
+    return [spec] * max_levels
+
+
+def improve_B(A, B, spec, core=None):
+    """aggregation.py:311-319: B <- relaxation_as_linear_operator(spec, A, 0) * B, every column relaxed on its own"""
+    from . import relaxation as rx
+    name, kw = spec if isinstance(spec, tuple) else (spec, {})
+    if name is None:
+        return B
+    kw = dict(kw)
+    iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
+    if kw:
+        raise NotImplementedError('oracle.sa: improve_candidates options %r' % sorted(kw))
+    bs = blocksize(A)
+    b0 = np.zeros(A.shape[0], dtype=A.dtype)
+    out = np.empty_like(B)
+    Dinv = None
+    for c in range(B.shape[1]):
+        x = np.array(B[:, c], dtype=A.dtype)
+        if name == 'gauss_seidel' or (name == 'block_gauss_seidel' and bs == 1):
+            rx.gauss_seidel(A, x, b0, iterations=iters, sweep=sweep, core=core)
+        elif name == 'block_gauss_seidel':
+            if Dinv is None:
+                Dinv = block_diag_inverse(A, core)
+            rx.block_gauss_seidel(A, x, b0, Dinv, bs, iterations=iters, sweep=sweep, core=core)
+        else:
+            raise NotImplementedError('oracle.sa: improve_candidates method %r' % (name,))
+        out[:, c] = x
+    return out
+
+
+def block_diag_inverse(A, core=None):
+    """get_block_diag(A, blocksize, inv_flag=True) (util/utils.py:601-690) for blocks smaller than 7: the stored
+    diagonal blocks (zeros where absent) through amg_core.pinv_array(..., 'T')"""
+    core = core or _o.core
+    bs = blocksize(A)
+    if bs >= 7:
+        raise NotImplementedError('oracle.sa: blocks of 7 and more go through LAPACK gelss in the reference')
+    nb = A.shape[0] // bs
+    D = np.zeros((nb, bs, bs), dtype=A.dtype)
+    rows = np.repeat(np.arange(nb), np.diff(A.indptr))
+    on_diag = np.where(A.indices == rows)[0]
+    D[rows[on_diag]] = A.data[on_diag]
+    core.pinv_array(D.ravel(), nb, bs, 'T')
+    return D
+
+
 def blocksize(A):
     return A.blocksize[0] if A.format == 'bsr' else 1
 
@@ -179,10 +233,11 @@ def smoothed_aggregation_hierarchy(A, B=None, theta=0.0, smooth_omega=4.0 / 3.0,
     """aggregation.py:30-290 for symmetry='hermitian', strength=('symmetric',{'theta':theta}),
     aggregate='standard', smooth=('jacobi',{'omega':smooth_omega}); returns a list of
     oracle.multilevel.Level with RESOLVED smoother specs (omega/rho for Jacobi).
-    ``improve_candidates`` must be None (the reference default -- 4 symmetric block-GS sweeps
-    on level 0, aggregation.py:38-41 -- is passed explicitly as None by the parity harness)."""
-    if improve_candidates is not None:
-        raise NotImplementedError('oracle.sa: improve_candidates must be None')
+    ``improve_candidates``: None, or the reference's forms (a spec or a per-level list, aggregation.py:38-41 -- the
+    reference DEFAULT is [('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None]) for the methods
+    gauss_seidel / block_gauss_seidel: B <- relaxation on A B = 0, column by column (aggregation.py:311-319,
+    util/utils.py:1140-1204)."""
+    improve = _levelize(improve_candidates, max_levels)
     A = A.asfptype() if hasattr(A, 'asfptype') else A.astype(np.float64)
     if B is None:
         bs = blocksize(A)
@@ -197,6 +252,7 @@ def smoothed_aggregation_hierarchy(A, B=None, theta=0.0, smooth_omega=4.0 / 3.0,
     while len(levels) < max_levels and levels[-1].A.shape[0] // blocksize(levels[-1].A) > max_coarse:
         lvl = levels[-1]
         A, B = lvl.A, lvl.B
+        B = lvl.B = improve_B(A, B, improve[len(levels) - 1], core)
         C = symmetric_strength_pattern(A, theta, core)
         AggOp, _, _ = standard_aggregation(C, core)
         T, Bc = fit_candidates(AggOp, B, core=core)
@@ -224,4 +280,10 @@ def _resolve(spec, lvl):
     if name == 'gauss_seidel':
         return ('gauss_seidel', {'sweep': kw.pop('sweep', 'forward'),
                                  'iterations': kw.pop('iterations', 1)})
+    if name == 'block_gauss_seidel':               # the reference's SA default (aggregation.py:34-37)
+        sweep, iters = kw.pop('sweep', 'forward'), kw.pop('iterations', 1)
+        bs = blocksize(lvl.A)
+        if bs == 1:                                # smoothing.py:406-408
+            return ('gauss_seidel', {'sweep': sweep, 'iterations': iters})
+        return ('block_gauss_seidel', {'Dinv': block_diag_inverse(lvl.A), 'blocksize': bs, 'sweep': sweep, 'iterations': iters})
     raise ValueError('oracle.sa: unsupported smoother %r' % (name,))

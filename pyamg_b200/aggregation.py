@@ -137,6 +137,43 @@ def jacobi_prolongation_smoother_block(A, T, omega=4.0 / 3.0, degree=1, rho=None
     return P, rho
 
 
+def _levelize_improve(spec, max_levels):
+    """levelize_smooth_or_improve_candidates (pyamg/util/utils.py): one spec for every level, or a list padded with its
+    last entry"""
+    if isinstance(spec, list):
+        out = list(spec)
+        while len(out) < max_levels:
+            out.append(out[-1])
+        return out
+    return [spec] * max_levels
+
+
+def improve_candidates_on_level(A, Bv, K2, spec):
+    """aggregation.py:311-319: B <- relaxation_as_linear_operator(spec, A, 0) * B (util/utils.py:1140-1204): every
+    candidate (column of B) relaxed on A x = 0 on its own.  Methods: gauss_seidel, block_gauss_seidel (what the
+    reference's default asks for) -- lexicographic sweeps, exact and sequential on the device."""
+    from . import relaxation
+    name, kw = _unpack(spec)
+    if name is None:
+        return Bv
+    iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
+    if name not in ('gauss_seidel', 'block_gauss_seidel') or kw:
+        raise NotImplementedError('improve_candidates: gauss_seidel / block_gauss_seidel with sweep and iterations only')
+    n = A.shape[0]
+    bs = A.blocksize[0]
+    b0 = torch.zeros(n, dtype=torch.float64, device=Bv.device)
+    Bm = Bv.view(n, K2)
+    out = torch.empty_like(Bm)
+    for c in range(K2):
+        x = Bm[:, c].contiguous()
+        if name == 'gauss_seidel' or bs == 1:            # block GS with 1 x 1 blocks is plain GS (smoothing.py:406-408)
+            relaxation.gauss_seidel(A, x, b0, iterations=iters, sweep=sweep)
+        else:
+            relaxation.block_gauss_seidel(A, x, b0, iterations=iters, sweep=sweep, blocksize=bs)
+        out[:, c] = x
+    return out.reshape(-1).contiguous()
+
+
 def _scaled(A, v, c=None):
     out = torch.empty_like(A.data)
     _lib.call('b200amg_csr_scale_rows', A.shape[0], _ptr(A.indptr), _ptr(A.data), _ptr(v),
@@ -189,13 +226,14 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     device path; unsupported options raise (no CPU fallback).  Deviations from the reference
     DEFAULTS, both because the reference default is a lexicographic (sequential) block
     Gauss-Seidel: `presmoother/postsmoother` default to Jacobi(4/3) and `improve_candidates`
-    to None.  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
+    to None.  The reference defaults are available by asking for them --
+    improve_candidates=[('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None],
+    presmoother=postsmoother=('block_gauss_seidel', {'sweep': 'symmetric'}) -- exact, but those sweeps are
+    lexicographic, i.e. one row after the other on the device.  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
     tests feed the reference's spectral-radius estimates."""
     if symmetry not in ('hermitian', 'symmetric'):
         raise NotImplementedError('only symmetric / hermitian problems have a device setup path')
-    if improve_candidates is not None and improve_candidates != [None] and improve_candidates != (None, {}):
-        raise NotImplementedError('improve_candidates must be None (the reference default is a sequential '
-                                  'block Gauss-Seidel on B)')
+    improve = _levelize_improve(improve_candidates, max_levels)
     if diagonal_dominance:
         raise NotImplementedError('diagonal_dominance filtering is not available on the device')
     sname, skw = _unpack(strength)
@@ -236,6 +274,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     while len(levels) < max_levels and levels[-1].A.n_brow > max_coarse:
         lvl = levels[-1]
         k = len(levels) - 1
+        lvl.B = improve_candidates_on_level(lvl.A, lvl.B, K2, improve[k])
         if block:
             # the same steps on blocks: aggregation on the block graph AS STORED (first-touch order out of bsr_matmat
             # on coarse levels), then the in-place block sort of get_diagonal

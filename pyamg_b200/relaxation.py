@@ -106,8 +106,9 @@ def gauss_seidel_indexed(A, x, b, indices, iterations=1, sweep='forward', color_
 
 def get_block_diag_inverse(A, blocksize=None):
     """inverses of the diagonal blocks, [n_brow, bs, bs] on the device (pyamg/util/utils.py:601-690 with
-    inv_flag=True; cached on the matrix like the reference's A.block_D_inv).  Gauss-Jordan per block: equal to the
-    reference's LAPACK result to rounding, zero for a numerically singular block."""
+    inv_flag=True; cached on the matrix like the reference's A.block_D_inv).  Blocks up to 6 x 6 go through the device
+    restatement of amg_core.pinv_array like in the reference (its bits, pseudo-inverse of singular blocks included);
+    7 x 7 and 8 x 8 -- LAPACK gelss in the reference -- through Gauss-Jordan (equal to rounding)."""
     bs = A.blocksize[0] if blocksize is None else int(blocksize)
     if A.blocksize != (bs, bs):
         raise NotImplementedError('re-blocking on the device is not available: A must be BSR with the requested blocksize')

@@ -18,7 +18,7 @@ import torch
 
 import hier_io
 from oracle import sa as osa
-from test_emulated_kernels import emu, same  # noqa: F401  (the host-compiled kernel source)
+from test_emulated_kernels import emu, emu_relax, same  # noqa: F401  (the host-compiled kernel sources)
 
 
 def _arr(ptr, n, ctype):
@@ -26,7 +26,7 @@ def _arr(ptr, n, ctype):
 
 
 @pytest.fixture()
-def host_amg(emu, monkeypatch):  # noqa: F811
+def host_amg(emu, emu_relax, monkeypatch):  # noqa: F811
     import pyamg_b200 as amg
     from pyamg_b200 import _lib, aggregation, linalg, multilevel, smoothing, sparse
     DevMat = sparse.DevMat
@@ -38,16 +38,20 @@ def host_amg(emu, monkeypatch):  # noqa: F811
             monkeypatch.setattr(mod, '_stream', lambda: 0)
     emu_names = ('b200amg_bsr_scale_rows', 'b200amg_bsr_gather_blocks', 'b200amg_fit_candidates', 'b200amg_tentative_scatter',
                  'b200amg_bsr_sub', 'b200amg_bsr_slot_map', 'b200amg_bsr_matmat_numeric')
+    relax_names = ('b200amg_block_gauss_seidel', 'b200amg_block_jacobi', 'b200amg_block_diag_inverse', 'b200amg_pinv_array')
     for name in emu_names:                                  # bind exactly the product's signature table
         f = getattr(emu, name)
+        f.restype, f.argtypes = _lib._SIGS[name]
+    for name in relax_names:
+        f = getattr(emu_relax, name)
         f.restype, f.argtypes = _lib._SIGS[name]
     real_call = _lib.call
     seen = set()
 
     def call(name, *args):
         seen.add(name)
-        if name in emu_names:
-            rc = getattr(emu, name)(*args)
+        if name in emu_names or name in relax_names:
+            rc = getattr(emu if name in emu_names else emu_relax, name)(*args)
             assert rc == 0, name
         elif name == 'b200amg_flag_nonneg':
             n, agg, flag, _ = args
@@ -74,6 +78,18 @@ def host_amg(emu, monkeypatch):  # noqa: F811
             real_call(name, *args)                          # host entry points of the real library (aggregation, colouring)
 
     monkeypatch.setattr(_lib, 'call', call)
+
+    from pyamg_b200 import amg_core
+
+    def chk(t, dtype, name):                                # the product's check minus "must be a CUDA tensor"
+        assert isinstance(t, torch.Tensor) and t.dtype == dtype and t.dim() == 1 and t.is_contiguous(), name
+        return t.data_ptr()
+    monkeypatch.setattr(amg_core, '_chk', chk)
+    monkeypatch.setattr(amg_core, '_stream', lambda: 0)
+
+    class _S:
+        cuda_stream = 0
+    monkeypatch.setattr(torch.cuda, 'current_stream', lambda *a, **k: _S())
 
     def scan(v):
         out = torch.zeros(v.numel() + 1, dtype=torch.int32)
@@ -184,3 +200,30 @@ def test_bench_config4_host_pieces(host_amg, golden_dir):
     assert bench.block_table(ml)[0] == [A0.n_brow, A0.nblocks, 3]
     vb = bench.vcycle_bytes(ml, 2)
     assert vb > 4 * bench.bsr_gs_sweep_bytes(A0.n_brow, A0.nblocks, 3) + bench.block_bytes(A0.nblocks, 3, 3)
+
+
+def test_block_path_with_the_reference_default_improve_candidates(host_amg, golden_dir):
+    """improve_candidates = the reference's default (4 symmetric block_gauss_seidel sweeps on A B = 0, inverses of the
+    diagonal blocks by pinv_array): the orchestration + the kernel sources rebuild the hierarchy the REAL reference built
+    with its defaults (tests/golden/sa_elasticity3d_tets_7.npz)"""
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7.npz'))
+    B = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))[1]['B']
+    A = levels[0].A
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    default = [('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None]
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=default)
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=default,
+                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    assert 'b200amg_block_gauss_seidel' in amg._seen_calls and 'b200amg_block_diag_inverse' in amg._seen_calls
+    # block smoother names resolve against the same inverses
+    amg.change_smoothers(ml, ('multicolor_block_gauss_seidel', {'sweep': 'symmetric'}), ('block_jacobi', {'omega': 1.0, 'withrho': False}))
+    pre, post = ml.levels[0].presmoother, ml.levels[0].postsmoother
+    assert (pre.kind, post.kind) == (6, 5) and pre.Dinv is post.Dinv and tuple(pre.Dinv.shape) == (294, 3, 3)
+    assert pre.indices.numel() == 294

@@ -216,3 +216,30 @@ def test_block_smoother_cycles_match_reference_fixture(amg, golden_dir):
     xd = ml.solve(ex['b'], tol=1e-30, maxiter=6, residuals=rd)
     assert np.all(np.abs(np.array(rd) - np.array(ro)) <= RTOL * ro[0])
     assert np.abs(xd - xo).max() <= RTOL * np.abs(xo).max()
+
+
+@pytest.mark.parametrize('name,pre,mc', [('sa_poisson3d_16_default', ('jacobi', {'omega': 4.0 / 3.0}), 30),
+                                         ('sa_elasticity3d_tets_7', ('gauss_seidel', {'sweep': 'symmetric'}), 10)])
+def test_sa_setup_with_the_reference_default_improve_candidates(amg, golden_dir, name, pre, mc):
+    """improve_candidates = the reference's default (4 symmetric lexicographic block_gauss_seidel sweeps on A B = 0):
+    the device setup rebuilds the hierarchies the REAL reference built with ITS defaults, bit for bit (rho fed in)"""
+    levels, ex = hier_io.load(os.path.join(golden_dir, name + '.npz'))
+    B = None
+    if name.startswith('sa_elasticity3d'):
+        B = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_setup.npz'))[1]['B']
+    default = [('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None]
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), B, presmoother=pre, postsmoother=pre, max_coarse=mc,
+                                             improve_candidates=default)
+    rhos = [(l.rho_smooth, getattr(l.A, 'rho_D_inv', None)) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(levels[0].A, B, presmoother=pre, postsmoother=pre, max_coarse=mc,
+                                         improve_candidates=default, rho_override=rhos)
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    res = []
+    x = ml.solve(ex['b'], tol=1e-30, maxiter=len(ex['residuals']) - 1, residuals=res)
+    assert np.all(np.abs(np.array(res) - ex['residuals']) <= RTOL * ex['residuals'][0])
+    assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
