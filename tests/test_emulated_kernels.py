@@ -179,7 +179,7 @@ def emu_fit_candidates(lib, agg, nagg, B, K1, K2, tol=1e-10):
 
 
 def same(M, Rf):
-    return (M.format == Rf.format and M.blocksize == Rf.blocksize and M.shape == Rf.shape
+    return (M.format == Rf.format and getattr(M, 'blocksize', (1, 1)) == getattr(Rf, 'blocksize', (1, 1)) and M.shape == Rf.shape
             and np.array_equal(M.indptr, Rf.indptr) and np.array_equal(M.indices, Rf.indices)
             and np.array_equal(np.ravel(M.data), np.ravel(Rf.data)))
 
