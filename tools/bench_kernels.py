@@ -119,7 +119,15 @@ def main():
         ms = timed(lambda: amg.amg_core.bsr_gauss_seidel(Ab.indptr, Ab.indices, Ab.data, xb, bb, 0, Ab.n_brow, 1, bs, cidx_d, cptr))
         add(8, 'b200amg_bsr_gauss_seidel bs=%d' % bs, 'bsr_gs_color_kernel<%d> x %d colours (one forward sweep)' % (bs, len(cptr) - 1),
             spmv_bytes(Ab) + 8 * nb + 4 * Ab.n_brow, ms, tag + '; block rows by MIS colour of the block graph')
-        del Ab, xb, bb, yb, tb, cidx_d
+        # block smoothers with stored diagonal-block inverses (the reference's SA default): + 8 bs^2 bytes of Dinv per block row
+        Dinv = amg.relaxation.get_block_diag_inverse(Ab).view(-1)
+        dbytes = 8 * bs * bs * Ab.n_brow
+        add(10, 'b200amg_block_jacobi bs=%d' % bs, 'block_jacobi_kernel<%d> + temp copy' % bs, spmv_bytes(Ab) + 8 * nb + dbytes,
+            timed(lambda: amg.amg_core.block_jacobi(Ab.indptr, Ab.indices, Ab.data, xb, bb, Dinv, tb, 0, Ab.n_brow, 1, [0.8], bs)), tag)
+        ms = timed(lambda: amg.amg_core.block_gauss_seidel(Ab.indptr, Ab.indices, Ab.data, xb, bb, Dinv, 0, Ab.n_brow, 1, bs, cidx_d, cptr))
+        add(10, 'b200amg_block_gauss_seidel bs=%d' % bs, 'block_gs_color_kernel<%d> x %d colours (one forward sweep)' % (bs, len(cptr) - 1),
+            spmv_bytes(Ab) + 8 * nb + 4 * Ab.n_brow + dbytes, ms, tag + '; block rows by MIS colour of the block graph')
+        del Ab, xb, bb, yb, tb, cidx_d, Dinv
 
     # ---- norms (row 9) ----------------------------------------------------------------------------------------
     from pyamg_b200 import linalg
