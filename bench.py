@@ -595,6 +595,31 @@ def measure_e2e(R, args):
             'call': 'multilevel_solver.solve(b_host_pinned, maxiter=1) -> x_host (aspreconditioner matvec)'}
 
 
+def measure_solve(R, tol=1e-10, maxiter=400):
+    """solve time (BASELINE metric: "V-cycles/sec & solve time"; SURVEY 8d "time-to-tol=1e-10"): b resident in HBM,
+    x0 = 0, ml.solve(b, tol=1e-10) stand-alone (one residual norm per iteration returns to the host, like the reference)
+    and with the device PCG around the same cycle (accel='cg').  Wall clock around the synchronous public call."""
+    import torch
+    ml = R['ml']
+    bt = torch.from_numpy(R['b']).cuda()
+    out = {'tol': tol, 'call': "multilevel_solver.solve(b_device, tol=1e-10[, accel='cg'])"}
+    for key, kw in (('standalone', {}), ('pcg', {'accel': 'cg'})):
+        try:
+            ml.solve(bt, tol=1e-2, maxiter=2, **kw)                       # warm the code path
+            res = []
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ml.solve(bt, tol=tol, maxiter=maxiter, residuals=res, **kw)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            its = len(res) - 1
+            out[key] = {'iterations': its, 'seconds': round(dt, 5), 'converged': bool(res[-1] <= tol * float(np.linalg.norm(R['b']))),
+                        'ms_per_iteration': round(1e3 * dt / max(its, 1), 4)}
+        except Exception as exc:                                          # noqa: BLE001  (a measurement, not the contract)
+            out[key] = {'error': '%s: %s' % (type(exc).__name__, exc)}
+    return out
+
+
 def measure_roofline(R, reps=5):
     """dominant kernel = csr_pipe_kernel<OP_JACOBI> on level 0 (pre- and post-smoothing sweep: 2 of the
     5 level-0 passes, ~36 % of a cycle).
@@ -867,6 +892,7 @@ def main():
         args.no_cpu_baseline = True
     e2e = measure_e2e(R, args)
     roof = measure_roofline(R) if R['rank'] == 0 else None
+    solve = measure_solve(R) if R['rank'] == 0 and R['world'] == 1 else None
     cpu, parity = (None, None)
     if R['rank'] == 0 and R['world'] == 1 and not args.no_cpu_baseline:
         cpu, parity = cpu_baseline(R, args)
@@ -892,7 +918,7 @@ def main():
                       'setup_s_device': round(R['setup_s'], 2),
                       'unfused_algorithmic_bytes_per_cycle': vb,
                       'cycle_GBs_on_unfused_bytes': round(vb / (R['ms_step'] * 1e-3) / 1e9, 1)},
-           'clocks': R['clocks'], 'e2e': e2e, 'gpu_launches': int(R['launches']), 'roofline': roof}
+           'clocks': R['clocks'], 'e2e': e2e, 'gpu_launches': int(R['launches']), 'roofline': roof, 'solve': solve}
     if cpu is not None:
         out['cpu_baseline'] = cpu
         out['parity_in_run'] = parity
