@@ -227,3 +227,24 @@ def test_block_path_with_the_reference_default_improve_candidates(host_amg, gold
     pre, post = ml.levels[0].presmoother, ml.levels[0].postsmoother
     assert (pre.kind, post.kind) == (6, 5) and pre.Dinv is post.Dinv and tuple(pre.Dinv.shape) == (294, 3, 3)
     assert pre.indices.numel() == 294
+
+
+def test_bench_helpers_on_a_scalar_hierarchy(host_amg, golden_dir):
+    """the helpers bench.py's DEFAULT (config 2) path calls on the solver object -- byte model, level tables, oracle
+    specs -- on a scalar SA hierarchy held in DevMats (the attribute surface they rely on)"""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_poisson3d_12.npz'))
+    ml = host_amg.import_hierarchy(levels)
+    want = 0
+    for l in levels[:-1]:
+        n, nnz, nc = l.A.shape[0], l.A.nnz, l.P.shape[1]
+        want += 3 * (12 * nnz + 4 * n + 24 * n) + (12 * l.R.nnz + 4 * nc + 8 * n + 8 * nc) + (12 * l.P.nnz + 4 * n + 8 * nc + 16 * n)
+    want += 8 * levels[-1].A.shape[0] ** 2
+    assert bench.vcycle_bytes(ml) == want
+    assert bench.block_table(ml) is None
+    assert bench.level_table(ml) == [[l.A.shape[0], l.A.nnz] for l in levels]
+    hl = bench.host_levels(ml)
+    assert hl[0].pre[0] == 'jacobi' and abs(hl[0].pre[1]['omega'] - levels[0].pre[1]['omega']) == 0.0
+    assert bench.block_bytes(ml.levels[0].A.nblocks, *ml.levels[0].A.blocksize) == 12 * levels[0].A.nnz
