@@ -287,6 +287,12 @@ int b200amg_rs_direct_interpolation_pass2(int n_nodes, const int *Ap, const int 
  *      to the reference (arrays are HOST pointers) ------------------------------------------ */
 /* amg_core.vertex_coloring_mis, pyamg/amg_core/graph.h:171-188: returns K, color[i] in [0,K) */
 int b200amg_vertex_coloring_mis_host(int n, const int *Ap_host, const int *Aj_host, int *color_host);
+/* amg_core.vertex_coloring_jones_plassmann / vertex_coloring_LDF (pyamg/amg_core/graph.h:242-335; methods 'JP' and
+ * 'LDF' of pyamg/graph.py:84-125): weights = one random number per vertex (the reference draws sp.rand(N)).
+ * Host arrays; return the number of colours. */
+int b200amg_vertex_coloring_jones_plassmann_host(int n, const int *Ap, const int *Aj, int *color,
+                                                 const double *weights);
+int b200amg_vertex_coloring_ldf_host(int n, const int *Ap, const int *Aj, int *color, const double *weights);
 /* amg_core.standard_aggregation, pyamg/amg_core/smoothed_aggregation.h:121-221: returns the
  * number of aggregates; agg[i] = aggregate of node i or -1; roots[k] = seed node of k */
 int b200amg_standard_aggregation_host(int n, const int *Ap_host, const int *Aj_host, int *agg_host,

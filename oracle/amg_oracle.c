@@ -690,3 +690,84 @@ void orc_pinv_array(T *AA, I m, I n, I transA)
     }
     free(Tran); free(U); free(V); free(SinvUh); free(S);
 }
+
+/* ---- amg_core.vertex_coloring_jones_plassmann / vertex_coloring_LDF, graph.h:242-335, over one sweep of
+ * maximal_independent_set_parallel (:90-160, run serially in index order with in-place state) and
+ * vertex_coloring_first_fit (:200-222).  State in x: -1 uncoloured, -2 excluded this round, >= 0 colour. */
+static I mis_sweep(I n, const I *Ap, const I *Aj, I K, I *x, const T *y)
+{
+    I found = 0;
+    for (I i = 0; i < n; i++) {
+        if (x[i] != -1) continue;
+        const T yi = y[i];
+        I p;
+        for (p = Ap[i]; p < Ap[i + 1]; p++) {
+            const I j = Aj[p];
+            if (x[j] == K) { x[i] = -2; break; }
+            if (x[j] == -1) {
+                if (y[j] > yi) break;
+                if (y[j] == yi && j > i) break;
+            }
+        }
+        if (p == Ap[i + 1]) {
+            for (p = Ap[i]; p < Ap[i + 1]; p++) if (x[Aj[p]] == -1) x[Aj[p]] = -2;
+            found++;
+            x[i] = K;
+        }
+    }
+    return found;
+}
+
+static void first_fit(I n, const I *Ap, const I *Aj, I *x, I K)
+{
+    char *used = (char *)malloc((size_t)K + 1);
+    for (I i = 0; i < n; i++) {
+        if (x[i] != K) continue;
+        for (I c = 0; c <= K; c++) used[c] = 0;
+        for (I p = Ap[i]; p < Ap[i + 1]; p++) {
+            const I j = Aj[p];
+            if (j == i || x[j] < 0) continue;
+            used[x[j]] = 1;
+        }
+        I c = 0;
+        while (c < K && used[c]) c++;
+        x[i] = c;
+    }
+    free(used);
+}
+
+I orc_vertex_coloring_jp(I n, const I *Ap, const I *Aj, I *x, T *z)
+{
+    for (I i = 0; i < n; i++) { x[i] = -1; z[i] += Ap[i + 1] - Ap[i]; }
+    I done = 0, K = 0, best = -1;
+    while (done < n) {
+        done += mis_sweep(n, Ap, Aj, K, x, z);
+        for (I i = 0; i < n; i++) if (x[i] == -2) x[i] = -1;
+        first_fit(n, Ap, Aj, x, K);
+        K++;
+    }
+    for (I i = 0; i < n; i++) if (x[i] > best) best = x[i];
+    return best;
+}
+
+I orc_vertex_coloring_ldf(I n, const I *Ap, const I *Aj, I *x, const T *y)
+{
+    T *w = (T *)malloc(sizeof(T) * (n > 0 ? n : 1));
+    for (I i = 0; i < n; i++) x[i] = -1;
+    I done = 0, K = 0, best = -1;
+    while (done < n) {
+        for (I i = 0; i < n; i++) {
+            if (x[i] != -1) continue;
+            I free_nb = 0;
+            for (I p = Ap[i]; p < Ap[i + 1]; p++) if (x[Aj[p]] == -1 && Aj[p] != i) free_nb++;
+            w[i] = y[i] + free_nb;
+        }
+        done += mis_sweep(n, Ap, Aj, K, x, w);
+        for (I i = 0; i < n; i++) if (x[i] == -2) x[i] = -1;
+        first_fit(n, Ap, Aj, x, K);
+        K++;
+    }
+    for (I i = 0; i < n; i++) if (x[i] > best) best = x[i];
+    free(w);
+    return best;
+}

@@ -88,6 +88,8 @@ _SIGS = {
     'b200amg_rs_direct_interpolation_pass2': (c_int, [c_int, p, p, p, p, p, p, p, p, p, p, p, p]),
     'b200amg_rs_cf_splitting_host': (c_int, [c_int, p, p, p, p, p]),
     'b200amg_vertex_coloring_mis_host': (c_int, [c_int, p, p, p]),
+    'b200amg_vertex_coloring_jones_plassmann_host': (c_int, [c_int, p, p, p, p]),
+    'b200amg_vertex_coloring_ldf_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_standard_aggregation_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_level_desc_size': (c_int, []),
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),

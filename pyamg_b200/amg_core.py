@@ -99,6 +99,31 @@ def vertex_coloring_mis(num_rows, Ap, Aj, x):
     return K
 
 
+def _weighted_coloring(entry, num_rows, Ap, Aj, x, w):
+    Ap = np.ascontiguousarray(Ap, np.intc)
+    Aj = np.ascontiguousarray(Aj, np.intc)
+    w = np.ascontiguousarray(w, np.float64)
+    if x.dtype != np.intc or not x.flags.c_contiguous:
+        raise TypeError('x must be a contiguous int32 numpy array')
+    if w.shape[0] < num_rows:
+        raise ValueError('one weight per vertex expected')
+    lib = _lib.load()
+    K = getattr(lib, entry)(int(num_rows), Ap.ctypes.data, Aj.ctypes.data, x.ctypes.data, w.ctypes.data)
+    if K < 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+    return K
+
+
+def vertex_coloring_jones_plassmann(num_rows, Ap, Aj, x, z):
+    """graph.h:242-287 (host arrays; z = random weights, left unmodified here); returns the number of colours"""
+    return _weighted_coloring('b200amg_vertex_coloring_jones_plassmann_host', num_rows, Ap, Aj, x, z)
+
+
+def vertex_coloring_LDF(num_rows, Ap, Aj, x, y):
+    """graph.h:290-335 (host arrays; y = random weights); returns the number of colours"""
+    return _weighted_coloring('b200amg_vertex_coloring_ldf_host', num_rows, Ap, Aj, x, y)
+
+
 def standard_aggregation(n_row, Ap, Aj, x, y):
     """smoothed_aggregation.h:121-221 (host arrays); returns the number of aggregates."""
     Ap = np.ascontiguousarray(Ap, np.intc)

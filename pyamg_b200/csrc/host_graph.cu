@@ -2,6 +2,7 @@
 // IDENTICAL integer result: greedy MIS colouring (pyamg/amg_core/graph.h:171-188 over
 // :34-61) used to build the multicolour Gauss-Seidel ordering, and the three-pass standard
 // aggregation (pyamg/amg_core/smoothed_aggregation.h:121-221).  Arrays are HOST pointers.
+#include <algorithm>
 #include <vector>
 #include "common.cuh"
 
@@ -29,6 +30,98 @@ extern "C" int b200amg_vertex_coloring_mis_host(int n, const int *Ap, const int 
         ++round;
     }
     return round;   // number of colours
+}
+
+// ---- Jones-Plassmann and largest-degree-first colourings (pyamg/amg_core/graph.h:242-335; pyamg/graph.py:84-125
+// methods 'JP', 'LDF').  Each round: one serial pass of the weight-based independent-set selection over the
+// uncoloured vertices (a vertex joins when no uncoloured neighbour outweighs it, ties to the larger index; its
+// uncoloured neighbours sit the round out), then every vertex picked this round takes the smallest colour no
+// neighbour holds.  Integer results identical to the reference for the same weights.
+namespace {
+struct RoundColouring {
+    int n;
+    const int *Ap, *Aj;
+    int *col;                                   // -1 uncoloured, -2 sitting this round out, >= 0 colour
+    std::vector<char> seen;
+
+    int pick(int round, const double *w)
+    {
+        int picked = 0;
+        for (int i = 0; i < n; ++i) {
+            if (col[i] != -1) continue;
+            bool wins = true;
+            for (int p = Ap[i]; p < Ap[i + 1] && wins; ++p) {
+                const int j = Aj[p];
+                if (col[j] == round) { col[i] = -2; wins = false; }
+                else if (col[j] == -1 && (w[j] > w[i] || (w[j] == w[i] && j > i))) wins = false;
+            }
+            if (!wins) continue;
+            for (int p = Ap[i]; p < Ap[i + 1]; ++p) if (col[Aj[p]] == -1) col[Aj[p]] = -2;
+            col[i] = round;
+            ++picked;
+        }
+        for (int i = 0; i < n; ++i) if (col[i] == -2) col[i] = -1;
+        return picked;
+    }
+
+    void smallest_free_colour(int round)
+    {
+        seen.assign((size_t)round + 1, 0);
+        for (int i = 0; i < n; ++i) {
+            if (col[i] != round) continue;
+            std::fill(seen.begin(), seen.end(), 0);
+            for (int p = Ap[i]; p < Ap[i + 1]; ++p) {
+                const int j = Aj[p];
+                if (j != i && col[j] >= 0) seen[col[j]] = 1;
+            }
+            int c = 0;
+            while (c < round && seen[c]) ++c;
+            col[i] = c;
+        }
+    }
+};
+}  // namespace
+
+// weights[i] = the random number of vertex i (the degree is added inside, like the reference; the caller's array is
+// left untouched).  Returns the number of colours.
+extern "C" int b200amg_vertex_coloring_jones_plassmann_host(int n, const int *Ap, const int *Aj, int *color,
+                                                            const double *weights)
+{
+    if (n < 0) return set_err(B200AMG_EINVAL, "vertex_coloring_jones_plassmann: n < 0");
+    std::vector<double> w(n > 0 ? n : 1);
+    for (int i = 0; i < n; ++i) { color[i] = -1; w[i] = weights[i] + (Ap[i + 1] - Ap[i]); }
+    RoundColouring rc{n, Ap, Aj, color, {}};
+    int done = 0, round = 0, most = -1;
+    while (done < n) {
+        done += rc.pick(round, w.data());
+        rc.smallest_free_colour(round);
+        ++round;
+    }
+    for (int i = 0; i < n; ++i) most = color[i] > most ? color[i] : most;
+    return most + 1;
+}
+
+// weight of an uncoloured vertex in a round = its random number + its uncoloured neighbours (self excluded)
+extern "C" int b200amg_vertex_coloring_ldf_host(int n, const int *Ap, const int *Aj, int *color, const double *weights)
+{
+    if (n < 0) return set_err(B200AMG_EINVAL, "vertex_coloring_LDF: n < 0");
+    std::vector<double> w(n > 0 ? n : 1);
+    for (int i = 0; i < n; ++i) color[i] = -1;
+    RoundColouring rc{n, Ap, Aj, color, {}};
+    int done = 0, round = 0, most = -1;
+    while (done < n) {
+        for (int i = 0; i < n; ++i) {
+            if (color[i] != -1) continue;
+            int open = 0;
+            for (int p = Ap[i]; p < Ap[i + 1]; ++p) open += (color[Aj[p]] == -1 && Aj[p] != i);
+            w[i] = weights[i] + open;
+        }
+        done += rc.pick(round, w.data());
+        rc.smallest_free_colour(round);
+        ++round;
+    }
+    for (int i = 0; i < n; ++i) most = color[i] > most ? color[i] : most;
+    return most + 1;
 }
 
 // agg[i] in [0, n_agg) or -1 (isolated node); roots[k] = seed node of aggregate k.

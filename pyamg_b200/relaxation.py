@@ -185,10 +185,11 @@ def polynomial(A, x, b, coefficients, iterations=1):
 
 
 def vertex_coloring(G, method='MIS'):
-    """pyamg/graph.py:84-125, method 'MIS' only (-> graph.h:171-188); host, setup-time.
-    G: DevMat or scipy matrix (pattern of block rows for BSR)."""
-    if method != 'MIS':
-        raise ValueError('only the MIS colouring is available')
+    """pyamg/graph.py:84-125: 'MIS' (graph.h:171-188), 'JP' (Jones-Plassmann, :242-287), 'LDF' (largest degree first,
+    :290-335); host, setup-time.  'JP' and 'LDF' draw one random weight per vertex from the global numpy RNG like the
+    reference's sp.rand(N).  G: DevMat or scipy matrix (pattern of block rows for BSR)."""
+    if method not in ('MIS', 'JP', 'LDF'):
+        raise ValueError('unknown method (%s)' % method)
     if isinstance(G, DevMat):
         Ap, Aj = G.indptr.cpu().numpy(), G.indices.cpu().numpy()
         n = G.n_brow
@@ -196,7 +197,12 @@ def vertex_coloring(G, method='MIS'):
         Ap, Aj = np.asarray(G.indptr, np.intc), np.asarray(G.indices, np.intc)
         n = len(Ap) - 1
     colors = np.empty(n, dtype=np.intc)
-    amg_core.vertex_coloring_mis(n, Ap, Aj, colors)
+    if method == 'MIS':
+        amg_core.vertex_coloring_mis(n, Ap, Aj, colors)
+    elif method == 'JP':
+        amg_core.vertex_coloring_jones_plassmann(n, Ap, Aj, colors, np.random.rand(n))
+    else:
+        amg_core.vertex_coloring_LDF(n, Ap, Aj, colors, np.random.rand(n))
     return colors
 
 

@@ -105,9 +105,11 @@ def _resolve(spec, lvl):
     if name in ('gauss_seidel_indexed', 'multicolor_gauss_seidel'):
         iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
         if name == 'multicolor_gauss_seidel':
-            if not hasattr(lvl, '_mc_order'):
-                idx, ptr = relaxation.color_ordering(relaxation.vertex_coloring(A, 'MIS'))
+            method = kw.pop('coloring', 'MIS')                      # 'MIS' (default), 'JP', 'LDF': pyamg/graph.py:84-125
+            if getattr(lvl, '_mc_method', method) != method or not hasattr(lvl, '_mc_order'):
+                idx, ptr = relaxation.color_ordering(relaxation.vertex_coloring(A, method))
                 lvl._mc_order = (torch.from_numpy(idx).to(_dev()), ptr)
+                lvl._mc_method = method
             idx, ptr = lvl._mc_order
         else:
             idx, ptr = kw.pop('indices'), kw.pop('color_ptr', None)

@@ -166,3 +166,39 @@ def test_level_descriptor_mirror_matches_the_compiled_struct():
     from pyamg_b200 import _lib
     assert ctypes.sizeof(_lib.LevelDesc) == _lib.load().b200amg_level_desc_size()
     assert _lib.LevelDesc.Dinv.offset + 8 == ctypes.sizeof(_lib.LevelDesc)
+
+
+def test_host_jp_ldf_colourings():
+    """vertex_coloring_jones_plassmann / vertex_coloring_LDF on the host: the reference's known-answer vectors
+    (pyamg/tests/test_graph.py:172-227), equality with the reference's compiled kernels / the C port on random graphs
+    with tied weights and self loops, and validity (no edge inside a colour)"""
+    from pyamg_b200 import amg_core
+    G0 = sp.csr_matrix(np.array([[0, 1, 0, 1, 0], [1, 0, 1, 1, 1], [0, 1, 0, 0, 1], [1, 1, 0, 0, 1], [0, 1, 1, 1, 0]]))
+    G1 = sp.csr_matrix(np.array([[0, 1, 1, 0, 0, 0], [1, 0, 1, 1, 0, 0], [1, 1, 0, 0, 0, 0], [0, 1, 0, 0, 1, 1],
+                                 [0, 0, 0, 1, 0, 1], [0, 0, 0, 1, 1, 0]]))
+    w0, w1 = np.array([0.8, 0.1, 0.9, 0.7, 0.6]), np.array([0.1, 0.2, 0.3, 0.1, 0.2, 0.3])
+    gold = {('vertex_coloring_jones_plassmann', 0): [2, 0, 1, 1, 2], ('vertex_coloring_jones_plassmann', 1): [2, 0, 1, 1, 2, 0],
+            ('vertex_coloring_LDF', 0): [2, 0, 1, 1, 2], ('vertex_coloring_LDF', 1): [2, 0, 1, 2, 1, 0]}
+    cores = [amg_core, oracle.port] + ([oracle.ref] if oracle.ref is not None else [])
+    for (fn, which), want in gold.items():
+        G, w = ((G0, w0), (G1, w1))[which]
+        for core in cores:
+            c = np.empty(G.shape[0], np.intc)
+            getattr(core, fn)(G.shape[0], G.indptr.astype(np.intc), G.indices.astype(np.intc), c, w.copy())
+            assert list(c) == want, (fn, which, core)
+    rng = np.random.RandomState(3)
+    for trial in range(40):
+        n = rng.randint(1, 300)
+        G = sp.random(n, n, rng.uniform(0.01, 0.1), random_state=rng, format='csr')
+        G = sp.csr_matrix(G + G.T + (sp.eye(n) if trial % 2 else 0 * sp.eye(n)))
+        Ap, Aj = G.indptr.astype(np.intc), G.indices.astype(np.intc)
+        w = rng.rand(n)
+        w[::5] = w[0]
+        for fn in ('vertex_coloring_jones_plassmann', 'vertex_coloring_LDF'):
+            a, b = np.empty(n, np.intc), np.empty(n, np.intc)
+            K = getattr(amg_core, fn)(n, Ap, Aj, a, w.copy())
+            getattr(cores[-1], fn)(n, Ap, Aj, b, w.copy())
+            assert np.array_equal(a, b) and K == a.max() + 1
+            rows = np.repeat(np.arange(n), np.diff(Ap))
+            off = rows != Aj
+            assert not np.any(a[rows[off]] == a[Aj[off]])
