@@ -199,6 +199,18 @@ int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, const doubl
                             const int *Bj, const double *Bx, int pass, int *cnt, const int *Cp,
                             int *Cj, double *Cx, void *stream);
 
+/* ---- symmetric strength of connection (csrc/strength.cu): amg_core.symmetric_strength_of_connection,
+ * pyamg/amg_core/smoothed_aggregation.h:48-99, for theta > 0 (theta == 0 keeps A's pattern) ------------- */
+/* one value per block = sum of its squared entries in numpy's sum(axis=1) order (pyamg/strength.py:300-305) */
+int b200amg_block_sqnorm(long long n_blocks, int R, int C, const double *Ax, double *out, void *stream);
+/* diag[i] = |sum of the stored (i, i) entries| (smoothed_aggregation.h:62-71) */
+int b200amg_abs_diag(int n_row, const int *Ap, const int *Aj, const double *Ax, double *diag, void *stream);
+/* strong entries: the diagonal, and a_ij with a_ij^2 >= theta^2 |a_ii| |a_jj|; pass 0 writes cnt[i], pass 1 fills
+ * Sj/Sx at Sp[i] in storage order */
+int b200amg_symmetric_strength(int n_row, double theta, const int *Ap, const int *Aj, const double *Ax,
+                               const double *diag, int pass, int *cnt, const int *Sp, int *Sj, double *Sx,
+                               void *stream);
+
 /* ---- block (BSR) smoothed-aggregation setup (csrc/bsr_setup.cu) -- BASELINE config 4 -------------- */
 /* scipy bsr_scale_rows (pyamg/util/utils.py:133-200): out[blk][r][c] = Ax[blk][r][c] * v[R*i + r], then
  * times the scalar c of pyamg/aggregation/smooth.py:164 when use_c != 0 */

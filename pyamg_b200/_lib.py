@@ -70,6 +70,9 @@ _SIGS = {
     'b200amg_tentative_fill': (c_int, [c_int, p, p, p, p, p, p]),
     'b200amg_csr_sub_sorted': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
     'b200amg_csr_sub_general': (c_int, [c_int, p, p, p, p, p, p, c_int, p, p, p, p, p]),
+    'b200amg_block_sqnorm': (c_int, [c_longlong, c_int, c_int, p, p, p]),
+    'b200amg_abs_diag': (c_int, [c_int, p, p, p, p, p]),
+    'b200amg_symmetric_strength': (c_int, [c_int, c_double, p, p, p, p, c_int, p, p, p, p, p]),
     'b200amg_bsr_scale_rows': (c_int, [c_int, c_int, c_int, p, p, p, c_double, c_int, p, p]),
     'b200amg_bsr_gather_blocks': (c_int, [c_longlong, c_int, c_int, p, p, p, c_int, p]),
     'b200amg_fit_candidates': (c_int, [c_int, c_int, c_int, p, p, p, c_double, p, p, p]),

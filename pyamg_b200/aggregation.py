@@ -41,6 +41,38 @@ def sort_indices(A):
     return DevMat(S.indptr, S.indices, S.data, A.shape, A.blocksize, A.format, True)
 
 
+def symmetric_strength_of_connection(A, theta=0.0):
+    """pyamg/strength.py:213-318 -> the strength PATTERN as a scalar CSR DevMat over the (block) rows of A (all the
+    aggregation reads, aggregate.py:77-85; the values kept are A's / the blocks' squared Frobenius norms, unscaled).
+    theta == 0: every stored entry is strong -- A's own index arrays.  BSR levels (1 x 1 blocks included) are measured
+    by the squared Frobenius norm of their blocks, like the reference (strength.py:300-305)."""
+    if theta < 0:
+        raise ValueError('expected a positive theta')
+    if A.blocksize[0] != A.blocksize[1]:
+        raise ValueError('matrix must have square blocks')
+    if theta == 0:
+        return block_pattern(A)
+    st = _stream()
+    dev = A.data.device
+    n = A.n_brow
+    if A.format == 'csr':
+        vals = A.data
+    else:
+        vals = torch.empty(A.nblocks, dtype=torch.float64, device=dev)
+        _lib.call('b200amg_block_sqnorm', A.nblocks, A.blocksize[0], A.blocksize[1], _ptr(A.data), _ptr(vals), st)
+    diag = torch.empty(max(n, 1), dtype=torch.float64, device=dev)
+    _lib.call('b200amg_abs_diag', n, _ptr(A.indptr), _ptr(A.indices), _ptr(vals), _ptr(diag), st)
+    cnt = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    args = (n, float(theta), _ptr(A.indptr), _ptr(A.indices), _ptr(vals), _ptr(diag))
+    _lib.call('b200amg_symmetric_strength', *args, 0, _ptr(cnt), 0, 0, 0, st)
+    Sp = _scan_i32(cnt[:n])
+    nnz = int(Sp[-1].item())
+    Sj = torch.empty(nnz, dtype=torch.int32, device=dev)
+    Sx = torch.empty(nnz, dtype=torch.float64, device=dev)
+    _lib.call('b200amg_symmetric_strength', *args, 1, 0, _ptr(Sp), _ptr(Sj), _ptr(Sx), st)
+    return DevMat(Sp, Sj, Sx, (n, n), (1, 1), 'csr', A.has_sorted_indices)
+
+
 def standard_aggregation(A):
     """-> (agg int32 device tensor [n], n_agg, roots).  Pattern goes to the host once."""
     n = A.shape[0]
@@ -237,8 +269,11 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     if diagonal_dominance:
         raise NotImplementedError('diagonal_dominance filtering is not available on the device')
     sname, skw = _unpack(strength)
-    if sname not in ('symmetric', None) or skw.get('theta', 0.0) != 0.0:
-        raise NotImplementedError("strength must be 'symmetric' with theta=0 (or None)")
+    if sname not in ('symmetric', None) or set(skw) - {'theta'}:
+        raise NotImplementedError("strength must be ('symmetric', {'theta': t}) or None")
+    theta = float(skw.get('theta', 0.0)) if sname is not None else 0.0
+    if theta < 0:
+        raise ValueError('expected a positive theta')
     if _unpack(aggregate)[0] != 'standard':
         raise NotImplementedError("aggregate must be 'standard'")
     mname, mkw = _unpack(smooth)
@@ -279,7 +314,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
             # the same steps on blocks: aggregation on the block graph AS STORED (first-touch order out of bsr_matmat
             # on coarse levels), then the in-place block sort of get_diagonal
             K1 = lvl.A.blocksize[0]
-            agg, nagg, roots = standard_aggregation(block_pattern(lvl.A))
+            agg, nagg, roots = standard_aggregation(symmetric_strength_of_connection(lvl.A, theta))
             T, Bc = fit_candidates_block(agg, nagg, lvl.B, K1, K2)
             A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
             if mname == 'jacobi':
@@ -300,7 +335,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         # out of csr_matmat on coarse levels; pass 2 of the aggregation picks the FIRST aggregated
         # neighbour in storage order) and only afterwards sorts it in place inside
         # jacobi_prolongation_smoother -> get_diagonal (pyamg/util/utils.py:571)
-        agg, nagg, roots = standard_aggregation(lvl.A)
+        agg, nagg, roots = standard_aggregation(lvl.A if theta == 0 else symmetric_strength_of_connection(lvl.A, theta))
         T, Bc = fit_candidates_scalar(agg, nagg, lvl.B)
         A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
         if mname == 'jacobi':

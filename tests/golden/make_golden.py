@@ -178,6 +178,28 @@ def sa_elasticity3d_block_smoothers(name, nv):
     print(name, [(l.A.shape[0], l.A.blocksize) for l in ml.levels], res[0], res[-1], r2[-1])
 
 
+def sa_theta(name, A, B, theta, max_coarse):
+    """SA with a symmetric strength threshold theta > 0 (entries dropped from the aggregation graph; BSR levels --
+    every coarse level -- measured by the squared Frobenius norm of their blocks, strength.py:300-305), candidates as
+    given, Jacobi(4/3) smoothers"""
+    np.random.seed(0)
+    ml = pyamg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': theta}), presmoother=JAC, postsmoother=JAC,
+                                           max_coarse=max_coarse, improve_candidates=None)
+    b, res, x = run(ml, A.shape[0], 8)
+    extra = {'b': b, 'residuals': res, 'x': x, 'theta': theta}
+    if B is not None:
+        extra['B'] = B
+    hier_io.save(os.path.join(OUT, name), ml.levels, jacobi_specs(ml), extra)
+    print(name, [(l.A.shape[0], l.A.nnz, l.A.format) for l in ml.levels], res[0], res[-1])
+
+
+def sa_theta_fixtures():
+    st = diffusion_stencil_2d(epsilon=0.01, theta=np.pi / 6, type='FE')
+    sa_theta('sa_aniso2d_40_theta005.npz', stencil_grid(st, (40, 40), format='csr'), None, 0.05, 10)
+    A, B = linear_elasticity((16, 16), format='bsr')
+    sa_theta('sa_elasticity2d_16_theta001.npz', A, B, 0.01, 10)
+
+
 def sa_chebyshev(name, grid, max_coarse):
     """SA hierarchy with the reference's 'chebyshev' smoother (smoothing.py:438-449 -> relaxation.polynomial).  The
     coefficients the reference resolved (from its own random-start spectral-radius estimate) are read back out of the
@@ -245,6 +267,9 @@ if __name__ == '__main__':
     if sys.argv[1:] == ['elasticity3d_block_smoothers']:
         sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)
         sys.exit(0)
+    if sys.argv[1:] == ['sa_theta']:
+        sa_theta_fixtures()
+        sys.exit(0)
     if sys.argv[1:] == ['elasticity3d_setup']:           # only the fixture added last (the others are unchanged)
         sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
         sys.exit(0)
@@ -258,3 +283,4 @@ if __name__ == '__main__':
     sa_elasticity3d('sa_elasticity3d_tets_7.npz', 7)
     sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
     sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)
+    sa_theta_fixtures()

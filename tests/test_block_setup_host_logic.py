@@ -18,7 +18,7 @@ import torch
 
 import hier_io
 from oracle import sa as osa
-from test_emulated_kernels import emu, emu_relax, same  # noqa: F401  (the host-compiled kernel sources)
+from test_emulated_kernels import emu, emu_relax, emu_strength, same  # noqa: F401  (the host-compiled kernel sources)
 
 
 def _arr(ptr, n, ctype):
@@ -26,7 +26,7 @@ def _arr(ptr, n, ctype):
 
 
 @pytest.fixture()
-def host_amg(emu, emu_relax, monkeypatch):  # noqa: F811
+def host_amg(emu, emu_relax, emu_strength, monkeypatch):  # noqa: F811
     import pyamg_b200 as amg
     from pyamg_b200 import _lib, aggregation, linalg, multilevel, smoothing, sparse
     DevMat = sparse.DevMat
@@ -45,13 +45,15 @@ def host_amg(emu, emu_relax, monkeypatch):  # noqa: F811
     for name in relax_names:
         f = getattr(emu_relax, name)
         f.restype, f.argtypes = _lib._SIGS[name]
+    strength_names = ('b200amg_block_sqnorm', 'b200amg_abs_diag', 'b200amg_symmetric_strength')
     real_call = _lib.call
     seen = set()
 
     def call(name, *args):
         seen.add(name)
-        if name in emu_names or name in relax_names:
-            rc = getattr(emu if name in emu_names else emu_relax, name)(*args)
+        if name in emu_names or name in relax_names or name in strength_names:
+            lib = emu if name in emu_names else emu_relax if name in relax_names else emu_strength
+            rc = getattr(lib, name)(*args)
             assert rc == 0, name
         elif name == 'b200amg_flag_nonneg':
             n, agg, flag, _ = args
@@ -248,3 +250,28 @@ def test_bench_helpers_on_a_scalar_hierarchy(host_amg, golden_dir):
     hl = bench.host_levels(ml)
     assert hl[0].pre[0] == 'jacobi' and abs(hl[0].pre[1]['omega'] - levels[0].pre[1]['omega']) == 0.0
     assert bench.block_bytes(ml.levels[0].A.nblocks, *ml.levels[0].A.blocksize) == 12 * levels[0].A.nnz
+
+
+def test_block_path_with_a_strength_threshold(host_amg, golden_dir):
+    """strength=('symmetric', {'theta': 0.01}) on a BSR 2x2 problem: block rows measured by the squared Frobenius norm of
+    their blocks, entries below the threshold leave the aggregation graph -- the hierarchy the REAL reference built"""
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity2d_16_theta001.npz'))
+    A, B, theta = levels[0].A, ex['B'], float(ex['theta'])
+    jac = ('jacobi', {'omega': 4.0 / 3.0})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10)
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})      # smoothers are not the subject here (Jacobi needs the device Arnoldi)
+    ml = amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': theta}), presmoother=gs, postsmoother=gs,
+                                         max_coarse=10, rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+    assert len(ml.levels) == len(levels) == 4
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    assert {'b200amg_block_sqnorm', 'b200amg_abs_diag', 'b200amg_symmetric_strength'} <= amg._seen_calls
+    # fewer strong connections than stored blocks on some level: the threshold did something
+    dropped = [l.A.nblocks - amg.aggregation.symmetric_strength_of_connection(l.A, theta).nnz for l in ml.levels[:-1]]
+    assert min(dropped) >= 0 and max(dropped) > 0, dropped
+    with pytest.raises(ValueError):
+        amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': -1.0}))

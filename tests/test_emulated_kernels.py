@@ -477,3 +477,59 @@ def test_block_diag_inverse_equals_reference_get_block_diag(emu_relax, bs):
     assert emu_relax.b200amg_block_diag_inverse(80, bs, P(Ap), P(Aj), P(Ax), P(got), None) == 0
     assert np.array_equal(got.reshape(80, bs, bs), want)
     assert np.all(want[3] == 0.0)
+
+
+# ---- symmetric strength of connection, theta > 0 (csrc/strength.cu) ------------------------------------------------
+@pytest.fixture(scope='module')
+def emu_strength():
+    lib = build_emu('strength')
+    from pyamg_b200 import _lib
+    for name in ('b200amg_block_sqnorm', 'b200amg_abs_diag', 'b200amg_symmetric_strength'):
+        f = getattr(lib, name)
+        f.restype, f.argtypes = _lib._SIGS[name]
+    return lib
+
+
+def emu_symmetric_strength(lib, A, theta):
+    """aggregation.symmetric_strength_of_connection for theta > 0 -> (Sp, Sj)"""
+    if A.format == 'csr':
+        n, vals = A.shape[0], np.ascontiguousarray(A.data, dtype=np.float64)
+    else:
+        R, C = A.blocksize
+        n = A.shape[0] // R
+        data = np.ascontiguousarray(A.data, dtype=np.float64).ravel()
+        vals = np.full(len(A.indices), np.nan)
+        assert lib.b200amg_block_sqnorm(len(A.indices), R, C, P(data), P(vals), None) == 0
+    Ap, Aj = i32(A.indptr), i32(A.indices)
+    diag = np.full(n, np.nan)
+    assert lib.b200amg_abs_diag(n, P(Ap), P(Aj), P(vals), P(diag), None) == 0
+    cnt = np.zeros(n, np.int32)
+    assert lib.b200amg_symmetric_strength(n, theta, P(Ap), P(Aj), P(vals), P(diag), 0, P(cnt), None, None, None, None) == 0
+    Sp = i32(np.concatenate([[0], np.cumsum(cnt)]))
+    Sj, Sx = np.full(Sp[-1], -1, np.int32), np.full(Sp[-1], np.nan)
+    assert lib.b200amg_symmetric_strength(n, theta, P(Ap), P(Aj), P(vals), P(diag), 1, None, P(Sp), P(Sj), P(Sx), None) == 0
+    return Sp, Sj, vals
+
+
+@pytest.mark.parametrize('bs', [0, 1, 2, 3, 6, 8])
+def test_symmetric_strength_equals_reference(emu_strength, bs):
+    """the strength pattern for theta > 0 against oracle/sa.py's restatement of pyamg/strength.py:213-318 (numpy block
+    norms + the reference's compiled amg_core.symmetric_strength_of_connection); bs = 0: a CSR matrix.  Ties included:
+    a constant-coefficient stencil puts many entries exactly ON the threshold."""
+    rng = np.random.RandomState(bs)
+    if bs == 0:
+        T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(12, 12))
+        A = sp.csr_matrix(sp.kron(T, sp.identity(12)) + 0.25 * sp.kron(sp.identity(12), T))
+        A.sort_indices()
+        mats = [A, sp.csr_matrix(A + sp.random(144, 144, 0.05, random_state=rng))]
+    else:
+        mats = [random_bsr(60, 60, bs, bs, 0.15, 70 + bs, unsorted=True) + sp.identity(60 * bs, format='bsr')]
+        mats = [sp.bsr_matrix(m, blocksize=(bs, bs)) for m in mats]
+    for A in mats:
+        for theta in (0.25, 0.5, 0.01):
+            Sp, Sj, vals = emu_symmetric_strength(emu_strength, A, theta)
+            ref = osa.symmetric_strength_pattern(A, theta, core=CORE)
+            assert np.array_equal(Sp, ref.indptr) and np.array_equal(Sj, ref.indices[:ref.indptr[-1]]), (bs, theta)
+            if bs:
+                assert np.array_equal(vals, (A.data * A.data).reshape(-1, bs * bs).sum(axis=1))     # numpy's own summation order
+    assert emu_strength.b200amg_symmetric_strength(4, -0.1, None, None, None, None, 0, None, None, None, None, None) != 0

@@ -243,3 +243,26 @@ def test_sa_setup_with_the_reference_default_improve_candidates(amg, golden_dir,
     x = ml.solve(ex['b'], tol=1e-30, maxiter=len(ex['residuals']) - 1, residuals=res)
     assert np.all(np.abs(np.array(res) - ex['residuals']) <= RTOL * ex['residuals'][0])
     assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
+
+
+@pytest.mark.parametrize('name', ['sa_aniso2d_40_theta005', 'sa_elasticity2d_16_theta001'])
+def test_sa_setup_with_a_strength_threshold(amg, golden_dir, name):
+    """strength=('symmetric', {'theta': t > 0}) (csrc/strength.cu): CSR level 0 + BSR(1,1) coarse levels, and a BSR 2x2
+    problem, against the hierarchies the REAL reference built"""
+    levels, ex = hier_io.load(os.path.join(golden_dir, name + '.npz'))
+    B, theta = ex.get('B'), float(ex['theta'])
+    jac = ('jacobi', {'omega': 4.0 / 3.0})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10)
+    rhos = [(l.rho_smooth, l.A.rho_D_inv) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(levels[0].A, B, strength=('symmetric', {'theta': theta}), presmoother=jac,
+                                         postsmoother=jac, max_coarse=10, rho_override=rhos)
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    res = []
+    x = ml.solve(ex['b'], tol=1e-30, maxiter=len(ex['residuals']) - 1, residuals=res)
+    assert np.all(np.abs(np.array(res) - ex['residuals']) <= RTOL * ex['residuals'][0])
+    assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
