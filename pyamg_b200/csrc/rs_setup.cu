@@ -131,7 +131,7 @@ extern "C" int b200amg_rs_strength(int n_row, double theta, const int *Ap, const
 {
     if (n_row <= 0) return 0;
     if (theta < 0.0 || theta > 1.0) return set_err(B200AMG_EINVAL, "rs_strength: expected theta in [0,1]");
-    rs_strength_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, theta, Ap, Aj, Ax, flags, pass, cnt, Cp, Cj, Cx);
+    B200_LAUNCH(rs_strength_kernel, (n_row + 255) / 256, 256, 0, S(stream), n_row, theta, Ap, Aj, Ax, flags, pass, cnt, Cp, Cj, Cx);
     return check_launch("rs_strength_kernel");
 }
 
@@ -139,7 +139,7 @@ extern "C" int b200amg_csr_not_canonical(int n_row, const int *Ap, const int *Aj
 {
     B200_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), S(stream)));
     if (n_row <= 0) return 0;
-    csr_not_canonical_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, Ap, Aj, flag);
+    B200_LAUNCH(csr_not_canonical_kernel, (n_row + 255) / 256, 256, 0, S(stream), n_row, Ap, Aj, flag);
     return check_launch("csr_not_canonical_kernel");
 }
 
@@ -147,7 +147,7 @@ extern "C" int b200amg_rs_direct_interpolation_pass1(int n_nodes, const int *Sp,
                                                      int *cnt, void *stream)
 {
     if (n_nodes <= 0) return 0;
-    rs_interp_count_kernel<<<(n_nodes + 255) / 256, 256, 0, S(stream)>>>(n_nodes, Sp, Sj, splitting, cnt);
+    B200_LAUNCH(rs_interp_count_kernel, (n_nodes + 255) / 256, 256, 0, S(stream), n_nodes, Sp, Sj, splitting, cnt);
     return check_launch("rs_interp_count_kernel");
 }
 
@@ -156,7 +156,7 @@ extern "C" int b200amg_rs_direct_interpolation_pass2(int n_nodes, const int *Ap,
                                                      const int *cmap, const int *Pp, int *Pj, double *Px, void *stream)
 {
     if (n_nodes <= 0) return 0;
-    rs_interp_fill_kernel<<<(n_nodes + 255) / 256, 256, 0, S(stream)>>>(n_nodes, Ap, Aj, Ax, Sp, Sj, Sx, splitting, cmap,
+    B200_LAUNCH(rs_interp_fill_kernel, (n_nodes + 255) / 256, 256, 0, S(stream), n_nodes, Ap, Aj, Ax, Sp, Sj, Sx, splitting, cmap,
                                                                         Pp, Pj, Px);
     return check_launch("rs_interp_fill_kernel");
 }

@@ -133,7 +133,7 @@ extern "C" int b200amg_csr_scale_rows(int n_row, const int *Ap, const double *Ax
                                       double *out, void *stream)
 {
     if (n_row <= 0) return 0;
-    csr_scale_rows_kernel<<<(n_row + 7) / 8, 256, 0, S(stream)>>>(n_row, Ap, Ax, v, c, use_c, out);
+    B200_LAUNCH(csr_scale_rows_kernel, (n_row + 7) / 8, 256, 0, S(stream), n_row, Ap, Ax, v, c, use_c, out);
     return check_launch("csr_scale_rows_kernel");
 }
 
@@ -141,14 +141,14 @@ extern "C" int b200amg_tentative_scalar(int n_agg, const int *Mp, const int *Mi,
                                         double *node_val, void *stream)
 {
     if (n_agg <= 0) return 0;
-    tentative_scalar_kernel<<<(n_agg + 255) / 256, 256, 0, S(stream)>>>(n_agg, Mp, Mi, Mb, tol, Bc, node_val);
+    B200_LAUNCH(tentative_scalar_kernel, (n_agg + 255) / 256, 256, 0, S(stream), n_agg, Mp, Mi, Mb, tol, Bc, node_val);
     return check_launch("tentative_scalar_kernel");
 }
 
 extern "C" int b200amg_flag_nonneg(int n, const int *agg, int *flag, void *stream)
 {
     if (n <= 0) return 0;
-    flag_nonneg_kernel<<<(n + 255) / 256, 256, 0, S(stream)>>>(n, agg, flag);
+    B200_LAUNCH(flag_nonneg_kernel, (n + 255) / 256, 256, 0, S(stream), n, agg, flag);
     return check_launch("flag_nonneg_kernel");
 }
 
@@ -156,7 +156,7 @@ extern "C" int b200amg_tentative_fill(int n, const int *agg, const double *node_
                                       void *stream)
 {
     if (n <= 0) return 0;
-    tentative_fill_kernel<<<(n + 255) / 256, 256, 0, S(stream)>>>(n, agg, node_val, Tp, Tj, Tx);
+    B200_LAUNCH(tentative_fill_kernel, (n + 255) / 256, 256, 0, S(stream), n, agg, node_val, Tp, Tj, Tx);
     return check_launch("tentative_fill_kernel");
 }
 
@@ -165,7 +165,7 @@ extern "C" int b200amg_csr_sub_sorted(int n_row, const int *Ap, const int *Aj, c
                                       double *Cx, void *stream)
 {
     if (n_row <= 0) return 0;
-    csr_sub_sorted_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
+    B200_LAUNCH(csr_sub_sorted_kernel, (n_row + 255) / 256, 256, 0, S(stream), n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
     return check_launch("csr_sub_sorted_kernel");
 }
 
@@ -174,6 +174,6 @@ extern "C" int b200amg_csr_sub_general(int n_row, const int *Ap, const int *Aj, 
                                        double *Cx, void *stream)
 {
     if (n_row <= 0) return 0;
-    csr_sub_general_kernel<<<(n_row + 255) / 256, 256, 0, S(stream)>>>(n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
+    B200_LAUNCH(csr_sub_general_kernel, (n_row + 255) / 256, 256, 0, S(stream), n_row, Ap, Aj, Ax, Bp, Bj, Bx, pass, cnt, Cp, Cj, Cx);
     return check_launch("csr_sub_general_kernel");
 }

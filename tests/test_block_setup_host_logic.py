@@ -18,7 +18,7 @@ import torch
 
 import hier_io
 from oracle import sa as osa
-from test_emulated_kernels import emu, emu_relax, emu_strength, same  # noqa: F401  (the host-compiled kernel sources)
+from test_emulated_kernels import emu, emu_relax, emu_setup, emu_strength, same  # noqa: F401  (the host-compiled kernel sources)
 
 
 def _arr(ptr, n, ctype):
@@ -26,12 +26,12 @@ def _arr(ptr, n, ctype):
 
 
 @pytest.fixture()
-def host_amg(emu, emu_relax, emu_strength, monkeypatch):  # noqa: F811
+def host_amg(emu, emu_relax, emu_strength, emu_setup, monkeypatch):  # noqa: F811
     import pyamg_b200 as amg
-    from pyamg_b200 import _lib, aggregation, linalg, multilevel, smoothing, sparse
+    from pyamg_b200 import _lib, aggregation, classical, linalg, multilevel, smoothing, sparse
     DevMat = sparse.DevMat
     cpu = torch.device('cpu')
-    for mod in (sparse, aggregation, linalg, multilevel, smoothing):
+    for mod in (sparse, aggregation, classical, linalg, multilevel, smoothing):
         if hasattr(mod, '_dev'):
             monkeypatch.setattr(mod, '_dev', lambda: cpu)
         if hasattr(mod, '_stream'):
@@ -46,36 +46,25 @@ def host_amg(emu, emu_relax, emu_strength, monkeypatch):  # noqa: F811
         f = getattr(emu_relax, name)
         f.restype, f.argtypes = _lib._SIGS[name]
     strength_names = ('b200amg_block_sqnorm', 'b200amg_abs_diag', 'b200amg_symmetric_strength')
+    setup_names = ('b200amg_csr_scale_rows', 'b200amg_tentative_scalar', 'b200amg_flag_nonneg', 'b200amg_tentative_fill',
+                   'b200amg_csr_sub_sorted', 'b200amg_csr_sub_general', 'b200amg_rs_strength', 'b200amg_csr_not_canonical',
+                   'b200amg_rs_direct_interpolation_pass1', 'b200amg_rs_direct_interpolation_pass2')
     real_call = _lib.call
     seen = set()
 
     def call(name, *args):
         seen.add(name)
-        if name in emu_names or name in relax_names or name in strength_names:
-            lib = emu if name in emu_names else emu_relax if name in relax_names else emu_strength
+        if name in emu_names or name in relax_names or name in strength_names or name in setup_names:
+            lib = (emu if name in emu_names else emu_relax if name in relax_names else emu_strength if name in strength_names
+                   else emu_setup)
             rc = getattr(lib, name)(*args)
             assert rc == 0, name
-        elif name == 'b200amg_flag_nonneg':
-            n, agg, flag, _ = args
-            _arr(flag, n, ctypes.c_int)[:] = _arr(agg, n, ctypes.c_int) >= 0
-        elif name == 'b200amg_tentative_fill':
-            n, agg, val, Tp, Tj, Tx, _ = args
-            a, tp = _arr(agg, n, ctypes.c_int), _arr(Tp, n + 1, ctypes.c_int)
-            keep = a >= 0
-            _arr(Tj, int(tp[-1]), ctypes.c_int)[:] = a[keep]
-            _arr(Tx, int(tp[-1]), ctypes.c_double)[:] = _arr(val, n, ctypes.c_double)[keep]
         elif name == 'b200amg_extract_diag':
             nb, bs, Ap, Aj, Ax, d, _ = args
             ap = _arr(Ap, nb + 1, ctypes.c_int)
             M = sp.bsr_matrix((_arr(Ax, int(ap[-1]) * bs * bs, ctypes.c_double).reshape(-1, bs, bs),
                                _arr(Aj, int(ap[-1]), ctypes.c_int), ap), shape=(nb * bs, nb * bs))
             _arr(d, nb * bs, ctypes.c_double)[:] = M.diagonal()
-        elif name == 'b200amg_csr_not_canonical':
-            n, Ap, Aj, flag, _ = args
-            ap = _arr(Ap, n + 1, ctypes.c_int)
-            aj = _arr(Aj, int(ap[-1]), ctypes.c_int)
-            bad = any(np.any(np.diff(aj[ap[i]:ap[i + 1]]) <= 0) for i in range(n))
-            _arr(flag, 1, ctypes.c_int)[0] = int(bad)
         else:
             real_call(name, *args)                          # host entry points of the real library (aggregation, colouring)
 
@@ -121,9 +110,12 @@ def host_amg(emu, emu_relax, emu_strength, monkeypatch):  # noqa: F811
         return DevMat(torch.from_numpy(np.ascontiguousarray(T.indptr, np.int32)), torch.from_numpy(np.ascontiguousarray(T.indices, np.int32)),
                       torch.from_numpy(np.ascontiguousarray(T.data, np.float64)), (A.shape[1], A.shape[0]), (1, 1), A.format, True)
 
-    for mod in (sparse, aggregation):
-        monkeypatch.setattr(mod, 'matmat', matmat)
+    for mod in (sparse, aggregation, classical):
+        if hasattr(mod, 'matmat'):
+            monkeypatch.setattr(mod, 'matmat', matmat)
         monkeypatch.setattr(mod, 'transpose', transpose)
+        if hasattr(mod, '_scan_i32'):
+            monkeypatch.setattr(mod, '_scan_i32', scan)
     amg._seen_calls = seen
     return amg
 
@@ -275,3 +267,39 @@ def test_block_path_with_a_strength_threshold(host_amg, golden_dir):
     assert min(dropped) >= 0 and max(dropped) > 0, dropped
     with pytest.raises(ValueError):
         amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': -1.0}))
+
+
+@pytest.mark.parametrize('name,kw', [('sa_poisson3d_12', {}), ('sa_aniso2d_40_theta005', {'strength': ('symmetric', {'theta': 0.05})})])
+def test_scalar_sa_path_builds_the_reference_hierarchy(host_amg, golden_dir, name, kw):
+    """the scalar smoothed-aggregation setup (pinned on the GPU in round 1: tests/test_gpu_cycle.py) through the same CPU
+    harness -- setup_kernels.cu compiled for the host, SpGEMM / transpose by scipy -- against fixtures from the REAL
+    reference, with and without a strength threshold"""
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, name + '.npz'))
+    jac = ('jacobi', {'omega': 4.0 / 3.0})
+    mc = {'sa_poisson3d_12': 20}.get(name, 10)
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), theta=kw.get('strength', (0, {'theta': 0.0}))[1]['theta'],
+                                             presmoother=jac, postsmoother=jac, max_coarse=mc)
+    rhos = [(l.rho_smooth, l.A.rho_D_inv) for l in ref[:-1]]
+    ml = amg.smoothed_aggregation_solver(levels[0].A, presmoother=jac, postsmoother=jac, max_coarse=mc, rho_override=rhos, **kw)
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+    assert abs(ml.levels[0].presmoother.omega - levels[0].pre[1]['omega']) == 0.0
+
+
+@pytest.mark.parametrize('name', ['rs_poisson2d_40_mcgs', 'rs_aniso_48_mcgs'])
+def test_ruge_stuben_path_builds_the_reference_hierarchy(host_amg, golden_dir, name):
+    """classical Ruge-Stuben setup (pyamg_b200/classical.py; rs_setup.cu compiled for the host, the C/F splitting by the
+    real library's host function) against the fixtures from the REAL reference, unsorted coarse rows included"""
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, name + '.npz'))
+    ml = amg.ruge_stuben_solver(levels[0].A, max_coarse=20, presmoother=None, postsmoother=None)
+    assert len(ml.levels) == len(levels)
+    for k, (m, r) in enumerate(zip(ml.levels, levels)):
+        for nm in ('A', 'P', 'R'):
+            if hasattr(r, nm):
+                assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)

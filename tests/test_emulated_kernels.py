@@ -533,3 +533,16 @@ def test_symmetric_strength_equals_reference(emu_strength, bs):
             if bs:
                 assert np.array_equal(vals, (A.data * A.data).reshape(-1, bs * bs).sum(axis=1))     # numpy's own summation order
     assert emu_strength.b200amg_symmetric_strength(4, -0.1, None, None, None, None, 0, None, None, None, None, None) != 0
+
+
+# ---- the scalar setup kernels (already pinned on the GPU in round 1), compiled for the host for the CPU harness -----
+@pytest.fixture(scope='module')
+def emu_setup():
+    lib = build_emu('setup_kernels', extra=('rs_setup',))
+    from pyamg_b200 import _lib
+    for name in ('b200amg_csr_scale_rows', 'b200amg_tentative_scalar', 'b200amg_flag_nonneg', 'b200amg_tentative_fill',
+                 'b200amg_csr_sub_sorted', 'b200amg_csr_sub_general', 'b200amg_rs_strength', 'b200amg_csr_not_canonical',
+                 'b200amg_rs_direct_interpolation_pass1', 'b200amg_rs_direct_interpolation_pass2'):
+        f = getattr(lib, name)
+        f.restype, f.argtypes = _lib._SIGS[name]
+    return lib
