@@ -2,9 +2,11 @@
 // (pyamg_b200/csrc/*.cu, unchanged) for the HOST, so that thread-per-row / warp-per-row kernels can be checked
 // against scipy in this GPU-less container before they ever see hardware (tests/test_emulated_kernels.py).
 // Every CUDA thread of a block is a real OS thread; __syncthreads / __syncwarp are barriers; blocks run one after
-// the other.  Supports what the emulated kernels use: barriers and full-warp __shfl_sync; no shared memory, no atomics.  The product never
+// the other.  Supports what the emulated kernels use: barriers, full-warp __shfl_sync / __all_sync, __ldg, int4 / double2 loads;
+// dynamic shared memory only as a global array the test provides; no static shared memory, no atomics.  The product never
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
+#include <algorithm>
 #include <barrier>
 #include <cmath>
 #include <cstddef>
@@ -18,11 +20,19 @@ struct uint3emu { unsigned x, y, z; };
 inline thread_local uint3emu threadIdx, blockIdx;
 inline thread_local dim3 blockDim, gridDim;
 
+struct alignas(16) int4 { int x, y, z, w; };
+struct alignas(16) double2 { double x, y; };
+using std::max;
+using std::min;
+
 typedef int cudaError_t;
 typedef void *cudaStream_t;
 enum { cudaSuccess = 0 };
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
+enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount = 16 };
+inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
+inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 2; return cudaSuccess; }   // a 2-SM "device"
 inline cudaError_t cudaMemsetAsync(void *p, int v, size_t n, cudaStream_t) { memset(p, v, n); return cudaSuccess; }
 
 #define __global__
@@ -30,7 +40,8 @@ inline cudaError_t cudaMemsetAsync(void *p, int v, size_t n, cudaStream_t) { mem
 #define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
-#define __align__(n) alignas(n)
+#define __shared__
+#define __align__(n) __attribute__((aligned(n)))
 
 // separately rounded arithmetic: the volatile keeps the compiler from contracting or reassociating
 inline double __dmul_rn(double a, double b) { volatile double r = a * b; return r; }
@@ -97,6 +108,23 @@ inline T __shfl_sync(unsigned, T v, int src, int width = 32)
     memcpy(&out, &raw, sizeof(T));
     return out;
 }
+
+// warp vote over the lanes of the calling thread's warp (all of them still in the kernel)
+inline int __all_sync(unsigned, int pred)
+{
+    cuda_emu::BlockSync *s = cuda_emu::cur;
+    const unsigned tid = threadIdx.x, w = tid / 32;
+    s->slots[tid] = pred ? 1ull : 0ull;
+    s->warp[w]->arrive_and_wait();
+    const unsigned lanes = std::min(32u, blockDim.x - 32 * w);
+    int all = 1;
+    for (unsigned l = 0; l < lanes; ++l) all &= (int)s->slots[w * 32 + l];
+    s->warp[w]->arrive_and_wait();
+    return all;
+}
+template <class T> inline T __ldg(const T *p) { return *p; }
+inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }
+#define B200_PREFETCH_L2(p) ((void)(p))
 
 #define B200_LAUNCH(kernel, grid, block, smem, stream, ...) \
     cuda_emu::launch(dim3(grid), dim3(block), [&] { kernel(__VA_ARGS__); })
