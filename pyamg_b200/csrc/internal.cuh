@@ -48,11 +48,14 @@ struct RowPat {
     unsigned char *codes = nullptr;  // [n]
     RowPatEntry *table = nullptr;    // [npat * 8]
     int npat = 0, n = 0, far = 0;    // far = largest column offset in the table
+    int common_len = 0;              // entries of the typical (middle) row
     bool ok() const { return codes != nullptr; }
 };
 int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const double *Ax, RowPat *out, cudaStream_t st);
 void rowpat_free(RowPat *r);
 int rowpat_op(int op, const RowPat &r, const StreamArgs &a, cudaStream_t st);
+// two rows in flight per thread (rowpat_ilp2.cu; B200AMG_ROWPAT_ILP2=1): -1 = not eligible, else the launch status
+int rowpat_ilp2_op(int op, const RowPat &r, const StreamArgs &a, int common_len, cudaStream_t st);
 
 int rows_per_cta_for(long long nnz, int nrows);
 // persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when

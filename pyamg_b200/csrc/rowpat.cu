@@ -15,6 +15,7 @@
 #include <string.h>
 #include <algorithm>
 #include <vector>
+#include <cstdlib>
 #include "internal.cuh"
 
 namespace b200amg {
@@ -205,7 +206,10 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
             unsigned char mid = 0;
             if (good) good = cudaMemcpy(&mid, codes + n_row / 2, 1, cudaMemcpyDeviceToHost) == cudaSuccess;
             if (good && mid < npat)
+            {
                 for (int q = 0; q < RP_LEN; ++q) out->far = std::max(out->far, ht[(size_t)mid * RP_LEN + q].off);
+                out->common_len = ht[(size_t)mid * RP_LEN].len & 0xff;     // row length of that typical row (rowpat_ilp2.cu)
+            }
         }
         if (good) {
             out->codes = codes;
@@ -471,6 +475,13 @@ int rowpat_op(int op, const RowPat &r, const StreamArgs &a0, cudaStream_t st)
     StreamArgs a = a0;
     if (op == OP_ADD && !a.b) a.b = a.y;              // y += A x: the kernels read the addend through b
     if (a.row_begin != 0 || a.row_end != r.n) return set_err(B200AMG_EINVAL, "rowpat_op: full row range only");
+    // experiment switch (off unless B200AMG_ROWPAT_ILP2=1): the two-rows-in-flight kernel for the ops it has; it
+    // declines (-1) small or unusual operators and the default kernel below runs
+    static const bool ilp2 = [] { const char *e = getenv("B200AMG_ROWPAT_ILP2"); return e && e[0] == '1'; }();
+    if (ilp2) {
+        const int rc = rowpat_ilp2_op(op, r, a, r.common_len, st);
+        if (rc >= 0) return rc;
+    }
     switch (op) {
     case OP_MATVEC: return launch_rowpat<OP_MATVEC>(r, a, st);
     case OP_SPMV_AB: return launch_rowpat<OP_SPMV_AB>(r, a, st);

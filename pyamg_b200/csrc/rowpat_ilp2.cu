@@ -1,11 +1,13 @@
-// PREPARED FOR ROUND 2 -- compiles (nvcc sm_100a, see README.md in this directory), NEVER RUN ON HARDWARE.
+// EXPERIMENT, off by default (B200AMG_ROWPAT_ILP2=1 turns it on; rowpat.cu::rowpat_op): verified bit-identical on the
+// host emulation (tests/test_emulated_kernels.py::test_prepared_rowpat_ilp2_kernel_is_bit_identical), compiles to 79-80
+// registers without spills, NOT YET RUN ON HARDWARE (written after round 1's GPU minutes were spent).
 //
 // Row-pattern sweep with TWO rows in flight per thread.  Evidence (profiles/r01b/rejected/README.md): the default
-// kernel (pyamg_b200/csrc/rowpat.cu) is bound by the ~2400-cycle dependent chain of one step per warp, not by DRAM.
+// kernel (rowpat.cu) is bound by the ~2400-cycle dependent chain of one step per warp, not by DRAM.
 // Here a thread owns rows r and r + 256 of a chunk at the same time: for warps whose 64 rows all have the operator's
 // common row length LEN (the interior stencil) the 2 x LEN gathers are issued back to back before either fold starts;
 // other warps (grid boundaries) take the one-row-at-a-time path.  Arithmetic per row is that of rowpat.cu (same order,
-// same roundings).  Meant to be dropped into pyamg_b200/csrc/ next to rowpat.cu (enable.diff.txt).
+// same roundings).
 #include <algorithm>
 #include "internal.cuh"
 

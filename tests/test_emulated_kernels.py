@@ -548,7 +548,7 @@ def emu_setup():
     return lib
 
 
-# ---- the prepared two-rows-in-flight row-pattern kernel (profiles/r01b/prepared/rowpat_ilp2.cu.txt) -------------------
+# ---- the two-rows-in-flight row-pattern kernel (csrc/rowpat_ilp2.cu, off by default: B200AMG_ROWPAT_ILP2=1) ----------
 def rowpat_layout(A):
     """host construction of the row-pattern layout of csrc/rowpat.cu: per row the number of its (offset, value)
     sequence; table[pattern][8] of (v, off, len | diagonal mask << 8)"""
@@ -576,7 +576,7 @@ def rowpat_layout(A):
 def emu_ilp2():
     if shutil.which('g++') is None:
         pytest.skip('g++ not available')
-    src = os.path.join(ROOT, 'profiles', 'r01b', 'prepared', 'rowpat_ilp2.cu.txt')
+    src = os.path.join(ROOT, 'pyamg_b200', 'csrc', 'rowpat_ilp2.cu')
     out = os.path.join(EMU, '_build', 'libemu_rowpat_ilp2.so')
     deps = [src, os.path.join(EMU, 'cuda_runtime.h'), os.path.join(EMU, 'emu_dyn_smem.cpp'), os.path.join(ROOT, 'pyamg_b200', 'csrc', 'internal.cuh')]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):

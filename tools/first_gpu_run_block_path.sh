@@ -15,6 +15,9 @@ timeout 300 python bench.py --config 4 --grid 40 --steps 10 --warmup 3 > $out/be
 timeout 900 python bench.py --config 4 --steps 20 --warmup 3 > $out/bench_cfg4_128.json 2> $out/bench_cfg4_128.err; echo "cfg4/128 rc=$?" | tee -a $out/summary.txt
 # 4. headline config unchanged?
 timeout 600 python bench.py --steps 20 --warmup 3 > $out/bench_cfg2.json 2> $out/bench_cfg2.err; echo "cfg2 rc=$?" | tee -a $out/summary.txt
+# 4b. the two-rows-in-flight row-pattern kernel (off by default): same bench with the switch on
+B200AMG_ROWPAT_ILP2=1 timeout 600 python bench.py --steps 20 --warmup 3 > $out/bench_cfg2_ilp2.json 2> $out/bench_cfg2_ilp2.err; echo "cfg2 ilp2 rc=$?" | tee -a $out/summary.txt
+B200AMG_ROWPAT_ILP2=1 timeout 600 python -m pytest tests/test_gpu_cycle.py tests/test_gpu_kernels.py -q -x > $out/gpu_suite_ilp2.log 2>&1; echo "gpu suite ilp2 rc=$?" | tee -a $out/summary.txt
 python - <<'PY' | tee -a gpurun_out/block_path/summary.txt
 import json, glob
 for f in sorted(glob.glob('gpurun_out/block_path/bench_*.json')):
