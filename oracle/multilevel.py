@@ -103,6 +103,22 @@ class Solver:
         elif cycle == 'F':
             self._cycle(k + 1, coarse_x, coarse_b, cycle)
             self._cycle(k + 1, coarse_x, coarse_b, 'V')
+        elif cycle == 'AMLI':
+            # multilevel.py:511-537: nAMLI recursive corrections, A-orthogonalised against each other
+            nAMLI = 2
+            Ac = self.levels[k + 1].A
+            p = np.zeros((nAMLI, coarse_b.shape[0]), dtype=coarse_b.dtype)
+            beta = np.zeros((nAMLI, nAMLI), dtype=coarse_b.dtype)
+            for q in range(nAMLI):
+                p[q, :] = 1
+                self._cycle(k + 1, p[q, :].reshape(coarse_b.shape), coarse_b, cycle)
+                for j in range(q):
+                    beta[q, j] = np.inner(p[j, :].conj(), Ac * p[q, :]) / np.inner(p[j, :].conj(), Ac * p[j, :])
+                    p[q, :] -= beta[q, j] * p[j, :]
+                Ap = Ac * p[q, :]
+                alpha = np.inner(p[q, :].conj(), np.ravel(coarse_b)) / np.inner(p[q, :].conj(), Ap)
+                coarse_x += alpha * p[q, :].reshape(coarse_x.shape)
+                coarse_b -= alpha * Ap.reshape(coarse_b.shape)
         else:
             raise TypeError('Unrecognized cycle type (%s)' % cycle)
         x += lvl.P * coarse_x

@@ -231,9 +231,76 @@ class multilevel_solver:
         return float(np.sqrt(self._nrm[0].item()))
 
     def cycle_device(self, cycle='V', use_graph=True):
-        """one cycle on the engine's resident (x, b): x <- cycle(x, b).  Asynchronous."""
+        """one cycle on the engine's resident (x, b): x <- cycle(x, b).  Asynchronous.  V / W / F replay the engine's
+        CUDA graph; 'AMLI' needs inner products between its recursive corrections and is driven from the host
+        (cycle_host)."""
+        if cycle == 'AMLI':
+            self.cycle_host(0, self._x, self._b, 'AMLI')
+            return
         _lib.call('b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], int(use_graph),
                   self._stream.cuda_stream)
+
+    def _apply_smoother(self, sm, A, x, b):
+        """one resolved smoother through the stand-alone entry points (same kernels' arithmetic as the engine)"""
+        from . import relaxation as rx
+        if sm is None or sm.kind == 0:
+            return
+        if sm.kind == 1:
+            rx.jacobi(A, x, b, iterations=sm.iterations, omega=sm.omega)
+        elif sm.kind == 2:
+            rx.gauss_seidel(A, x, b, iterations=sm.iterations, sweep=sm.sweep, indices=sm.indices, color_ptr=sm.color_ptr)
+        elif sm.kind == 3:
+            rx.gauss_seidel(A, x, b, iterations=sm.iterations, sweep=sm.sweep)
+        elif sm.kind == 4:
+            rx.polynomial(A, x, b, sm.coefficients, iterations=sm.iterations)
+        elif sm.kind == 5:
+            rx.block_jacobi(A, x, b, Dinv=sm.Dinv, blocksize=A.blocksize[0], iterations=sm.iterations, omega=sm.omega)
+        elif sm.kind in (6, 7):
+            rx.block_gauss_seidel(A, x, b, iterations=sm.iterations, sweep=sm.sweep, blocksize=A.blocksize[0], Dinv=sm.Dinv,
+                                  indices=sm.indices if sm.kind == 6 else None, color_ptr=sm.color_ptr if sm.kind == 6 else None)
+        else:
+            raise ValueError('unknown smoother kind %r' % (sm.kind,))
+
+    def cycle_host(self, k, x, b, cycle='V'):
+        """multilevel_solver.__solve (pyamg/multilevel.py:473-548) driven from the host, one kernel call per operation,
+        on device vectors x (updated in place) and b: every cycle type of the reference, 'AMLI' included (:511-537: two
+        recursive corrections per level, the second A-orthogonalised against the first, step lengths from inner
+        products that return to the host).  V / W / F give the engine's numbers and serve as its cross-check."""
+        from . import linalg
+        lvl = self.levels[k]
+        A = lvl.A
+        self._apply_smoother(getattr(lvl, 'presmoother', None), A, x, b)
+        r = A.residual(x, b)
+        cb = lvl.R.matvec(r)
+        cx = torch.zeros_like(cb)
+        if k == len(self.levels) - 2:
+            cx.copy_(self.coarse_solver(self.levels[-1].A, cb))
+        elif cycle == 'V':
+            self.cycle_host(k + 1, cx, cb, 'V')
+        elif cycle == 'W':
+            self.cycle_host(k + 1, cx, cb, cycle)
+            self.cycle_host(k + 1, cx, cb, cycle)
+        elif cycle == 'F':
+            self.cycle_host(k + 1, cx, cb, cycle)
+            self.cycle_host(k + 1, cx, cb, 'V')
+        elif cycle == 'AMLI':
+            Ac = self.levels[k + 1].A
+            p = []
+            for q in range(2):                                        # nAMLI = 2
+                pq = torch.ones_like(cb)                              # the reference starts every direction from ones
+                self.cycle_host(k + 1, pq, cb, cycle)
+                for pj in p:
+                    beta = linalg.dot(pj, Ac.matvec(pq)) / linalg.dot(pj, Ac.matvec(pj))
+                    pq.sub_(pj * beta)
+                Ap = Ac.matvec(pq)
+                alpha = linalg.dot(pq, cb) / linalg.dot(pq, Ap)
+                cx.add_(pq * alpha)
+                cb.sub_(Ap * alpha)
+                p.append(pq)
+        else:
+            raise TypeError('Unrecognized cycle type (%s)' % cycle)
+        x.add_(lvl.P.matvec(cx))
+        self._apply_smoother(getattr(lvl, 'postsmoother', None), A, x, b)
 
     def profile_cycle(self, cycle='V'):
         """one un-graphed cycle on the resident (x, b) with a CUDA event after every operation:
@@ -300,9 +367,7 @@ class multilevel_solver:
         stopping test `||r_k|| <= tol * ||b||`, residual history appended to `residuals`,
         `callback(x)` after every cycle.  numpy in -> numpy out, torch CUDA in -> torch CUDA out."""
         cycle = str(cycle).upper()
-        if cycle not in _CYCLE:
-            if cycle == 'AMLI':
-                raise NotImplementedError('AMLI cycles are not available on the device')
+        if cycle not in _CYCLE and cycle != 'AMLI':
             raise TypeError('Unrecognized cycle type (%s)' % cycle)
         if accel is not None:
             from . import krylov

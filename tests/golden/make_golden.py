@@ -200,6 +200,19 @@ def sa_theta_fixtures():
     sa_theta('sa_elasticity2d_16_theta001.npz', A, B, 0.01, 10)
 
 
+def sa_poisson_amli(name, grid, max_coarse):
+    """cycle='AMLI' (multilevel.py:511-537: two A-orthogonalised recursive corrections per level) on the hierarchy and
+    right-hand side of sa_poisson3d_12.npz (same seed, same call order)"""
+    A = poisson(grid, format='csr')
+    np.random.seed(0)
+    ml = pyamg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=max_coarse, improve_candidates=None)
+    b = np.random.rand(A.shape[0])
+    r = []
+    xx = ml.solve(b, tol=1e-30, maxiter=4, residuals=r, cycle='AMLI')
+    np.savez_compressed(os.path.join(OUT, name), residuals=np.array(r), x=xx, b=b)
+    print(name, [l.A.shape[0] for l in ml.levels], r)
+
+
 def sa_chebyshev(name, grid, max_coarse):
     """SA hierarchy with the reference's 'chebyshev' smoother (smoothing.py:438-449 -> relaxation.polynomial).  The
     coefficients the reference resolved (from its own random-start spectral-radius estimate) are read back out of the
@@ -267,6 +280,9 @@ if __name__ == '__main__':
     if sys.argv[1:] == ['elasticity3d_block_smoothers']:
         sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)
         sys.exit(0)
+    if sys.argv[1:] == ['amli']:
+        sa_poisson_amli('sa_poisson3d_12_AMLI.npz', (12, 12, 12), 20)
+        sys.exit(0)
     if sys.argv[1:] == ['sa_theta']:
         sa_theta_fixtures()
         sys.exit(0)
@@ -284,3 +300,4 @@ if __name__ == '__main__':
     sa_elasticity3d('sa_elasticity3d_tets_7_setup.npz', 7, improve=False)
     sa_elasticity3d_block_smoothers('sa_elasticity3d_tets_7_blockgs.npz', 7)
     sa_theta_fixtures()
+    sa_poisson_amli('sa_poisson3d_12_AMLI.npz', (12, 12, 12), 20)

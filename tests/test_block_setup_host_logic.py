@@ -59,6 +59,28 @@ def host_amg(emu, emu_relax, emu_strength, emu_setup, monkeypatch):  # noqa: F81
                    else emu_setup)
             rc = getattr(lib, name)(*args)
             assert rc == 0, name
+        elif name == 'b200amg_bsr_matvec':                  # scipy's own bsr / csr matvec (what the device kernel is pinned to)
+            nbr, nbc, R, C, Ap, Aj, Ax, x, bb, y, mode, _ = args
+            ap = _arr(Ap, nbr + 1, ctypes.c_int)
+            nb_ = int(ap[-1])
+            M = sp.bsr_matrix((_arr(Ax, nb_ * R * C, ctypes.c_double).reshape(-1, R, C), _arr(Aj, nb_, ctypes.c_int), ap),
+                              shape=(nbr * R, nbc * C))
+            if R == 1 and C == 1:
+                M = sp.csr_matrix((_arr(Ax, nb_, ctypes.c_double), _arr(Aj, nb_, ctypes.c_int), ap), shape=(nbr, nbc))
+            Ax_ = M * _arr(x, nbc * C, ctypes.c_double)
+            yv = _arr(y, nbr * R, ctypes.c_double)
+            if mode == 0:
+                yv[:] = Ax_
+            elif mode == 1:
+                yv[:] = _arr(bb, nbr * R, ctypes.c_double) - Ax_
+            else:
+                yv[:] = (_arr(bb, nbr * R, ctypes.c_double) if bb else yv) + Ax_
+        elif name == 'b200amg_dense_matvec':
+            n_, M_, x_, y_, _ = args
+            _arr(y_, n_, ctypes.c_double)[:] = np.dot(_arr(M_, n_ * n_, ctypes.c_double).reshape(n_, n_), _arr(x_, n_, ctypes.c_double))
+        elif name == 'b200amg_dot':
+            n_, x_, y_, out_, _, _ = args
+            _arr(out_, 1, ctypes.c_double)[0] = np.inner(_arr(x_, n_, ctypes.c_double), _arr(y_, n_, ctypes.c_double))
         elif name == 'b200amg_extract_diag':
             nb, bs, Ap, Aj, Ax, d, _ = args
             ap = _arr(Ap, nb + 1, ctypes.c_int)
@@ -303,3 +325,39 @@ def test_ruge_stuben_path_builds_the_reference_hierarchy(host_amg, golden_dir, n
         for nm in ('A', 'P', 'R'):
             if hasattr(r, nm):
                 assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
+
+
+def test_host_driven_cycles_on_a_block_hierarchy(host_amg, golden_dir):
+    """multilevel_solver.cycle_host (the host-driven cycle behind cycle='AMLI'; V / W / F as the engine's cross-check) on
+    the hierarchy the REAL reference built with its default block_gauss_seidel smoothers: V-cycles against the history
+    the reference recorded, W and AMLI against the oracle's restatement (itself pinned to reference fixtures).  Block
+    smoother and pinv kernels from the host-compiled source, SpMV / dense solve / dots by scipy and numpy doubles."""
+    import oracle
+    from oracle import multilevel as oml
+    amg = host_amg
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_elasticity3d_tets_7_blockgs.npz'))
+    bgs = ('block_gauss_seidel', {'sweep': 'symmetric'})
+    ml = amg.import_hierarchy(levels, presmoother=bgs, postsmoother=bgs)
+    for m, r in zip(ml.levels[:-1], levels[:-1]):
+        assert m.presmoother.kind == 7 and np.array_equal(m.presmoother.Dinv.numpy(), r.pre[1]['Dinv'])   # pinv_array bits
+    b = torch.from_numpy(ex['b'].copy())
+    A0 = levels[0].A
+
+    def history(cycle, ncyc):
+        x = torch.zeros_like(b)
+        res = [float(np.sqrt(np.inner(ex['b'], ex['b'])))]
+        for _ in range(ncyc):
+            ml.cycle_host(0, x, b, cycle)
+            r = ex['b'] - A0 * x.numpy()
+            res.append(float(np.sqrt(np.inner(r, r))))
+        return np.array(res), x.numpy()
+    res, x = history('V', len(ex['residuals']) - 1)
+    assert np.array_equal(res, ex['residuals']) and np.array_equal(x, ex['x'])
+    for cyc in ('W', 'AMLI'):
+        ro = []
+        xo = oml.Solver(levels, core=oracle.port).solve(ex['b'], tol=1e-30, maxiter=2, residuals=ro, cycle=cyc)
+        res, x = history(cyc, 2)
+        assert np.all(np.abs(res - np.array(ro)) <= 1e-12 * ro[0]), cyc
+        assert np.abs(x - xo).max() <= 1e-12 * np.abs(xo).max(), cyc
+    with pytest.raises(TypeError):
+        ml.cycle_host(0, torch.zeros_like(b), b, 'Z')

@@ -11,7 +11,6 @@ import ctypes
 import os
 import shutil
 import subprocess
-import sys
 
 import numpy as np
 import pytest

@@ -266,3 +266,22 @@ def test_sa_setup_with_a_strength_threshold(amg, golden_dir, name):
     x = ml.solve(ex['b'], tol=1e-30, maxiter=len(ex['residuals']) - 1, residuals=res)
     assert np.all(np.abs(np.array(res) - ex['residuals']) <= RTOL * ex['residuals'][0])
     assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
+
+
+def test_amli_cycle_and_host_driven_cycles(amg, golden_dir):
+    """cycle='AMLI' (host-driven: multilevel_solver.cycle_host) against the history the REAL reference recorded; the
+    host-driven V / W / F cycles give the graph-replayed engine's numbers"""
+    levels, ex = hier_io.load(os.path.join(golden_dir, 'sa_poisson3d_12.npz'))
+    z = np.load(os.path.join(golden_dir, 'sa_poisson3d_12_AMLI.npz'))
+    ml = amg.import_hierarchy(levels)
+    res = []
+    x = ml.solve(z['b'], tol=1e-30, maxiter=len(z['residuals']) - 1, residuals=res, cycle='AMLI')
+    assert np.all(np.abs(np.array(res) - z['residuals']) <= RTOL * z['residuals'][0])
+    assert np.abs(x - z['x']).max() <= RTOL * np.abs(z['x']).max()
+    b = torch.from_numpy(ex['b']).cuda()
+    for cyc in ('V', 'W', 'F'):
+        xe = ml.solve(b, tol=1e-30, maxiter=3, cycle=cyc)
+        xh = torch.zeros_like(b)
+        for _ in range(3):
+            ml.cycle_host(0, xh, b, cyc)
+        assert float((xe - xh).abs().max()) <= RTOL * float(xe.abs().max()), cyc
