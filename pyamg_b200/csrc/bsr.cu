@@ -208,7 +208,7 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     if (R < 1 || C < 1 || R > 8 || C > 8) return set_err(B200AMG_EINVAL, "bsr_matvec: block shape must be in 1..8");
     const long long n = (long long)n_brow * R;
     if (n <= 0) return 0;
-    bsr_matvec_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
+    B200_LAUNCH(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
     return check_launch("bsr_matvec_kernel");
 }
 
@@ -218,7 +218,7 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
     const long long n = (long long)(nb1 - nb0) * bs;
     if (n <= 0) return 0;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    BS_SWITCH(bs, (bsr_jacobi_kernel<BS><<<grid, 256, 0, st>>>(nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega)));
+    BS_SWITCH(bs, B200_LAUNCH(bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
     return check_launch("bsr_jacobi_kernel");
 }
 
@@ -228,7 +228,7 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     if (p1 <= p0) return 0;
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
-    BS_SWITCH(bs, (bsr_gs_color_kernel<BS><<<grid, 128, 0, st>>>(Ap, Aj, Ax, x, b, Id, p0, p1, backward)));
+    BS_SWITCH(bs, B200_LAUNCH(bsr_gs_color_kernel<BS>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward));
     return check_launch("bsr_gs_color_kernel");
 }
 
@@ -236,7 +236,7 @@ int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, do
                       const int *Id, int start, int stop, int step, cudaStream_t st)
 {
     if (start == stop) return 0;
-    BS_SWITCH(bs, (bsr_gs_sequential_kernel<BS><<<1, 1, 0, st>>>(Ap, Aj, Ax, x, b, Id, start, stop, step)));
+    BS_SWITCH(bs, B200_LAUNCH(bsr_gs_sequential_kernel<BS>, 1, 1, 0, st, Ap, Aj, Ax, x, b, Id, start, stop, step));
     return check_launch("bsr_gs_sequential_kernel");
 }
 

@@ -7,6 +7,7 @@
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
 #include <algorithm>
+#include <atomic>
 #include <barrier>
 #include <cmath>
 #include <cstddef>
@@ -123,6 +124,8 @@ inline int __all_sync(unsigned, int pred)
     return all;
 }
 template <class T> inline T __ldg(const T *p) { return *p; }
+inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }
 #define B200_PREFETCH_L2(p) ((void)(p))
 

@@ -18,7 +18,7 @@ import torch
 
 import hier_io
 from oracle import sa as osa
-from test_emulated_kernels import emu, emu_relax, emu_setup, emu_strength, same  # noqa: F401  (the host-compiled kernel sources)
+from test_emulated_kernels import emu, emu_bsr, emu_relax, emu_setup, emu_strength, same  # noqa: F401  (the host-compiled kernel sources)
 
 
 def _arr(ptr, n, ctype):
@@ -26,7 +26,7 @@ def _arr(ptr, n, ctype):
 
 
 @pytest.fixture()
-def host_amg(emu, emu_relax, emu_strength, emu_setup, monkeypatch):  # noqa: F811
+def host_amg(emu, emu_relax, emu_strength, emu_setup, emu_bsr, monkeypatch):  # noqa: F811
     import pyamg_b200 as amg
     from pyamg_b200 import _lib, aggregation, classical, linalg, multilevel, smoothing, sparse
     DevMat = sparse.DevMat
@@ -59,7 +59,13 @@ def host_amg(emu, emu_relax, emu_strength, emu_setup, monkeypatch):  # noqa: F81
                    else emu_setup)
             rc = getattr(lib, name)(*args)
             assert rc == 0, name
-        elif name == 'b200amg_bsr_matvec':                  # scipy's own bsr / csr matvec (what the device kernel is pinned to)
+        elif name == 'b200amg_bsr_matvec' and (args[2], args[3]) != (1, 1):      # blocks: the kernel source of csrc/bsr.cu
+            nbr, nbc, R, C, Ap, Aj, Ax, x, bb, y, mode, _ = args
+            assert emu_bsr.emu_bsr_matvec(nbr, R, C, Ap, Aj, Ax, x, bb, y, mode) == 0
+        elif name == 'b200amg_bsr_gauss_seidel' and args[8] > 1:
+            Ap, Aj, Ax, x, bb, r0, r1, dr, bs, Id, cp, K, _ = args
+            assert emu_bsr.emu_bsr_gauss_seidel(Ap, Aj, Ax, x, bb, r0, r1, dr, bs, Id, cp, K) == 0
+        elif name == 'b200amg_bsr_matvec':                  # 1 x 1: scipy's csr matvec (what the CSR kernels are pinned to)
             nbr, nbc, R, C, Ap, Aj, Ax, x, bb, y, mode, _ = args
             ap = _arr(Ap, nbr + 1, ctypes.c_int)
             nb_ = int(ap[-1])
@@ -361,3 +367,34 @@ def test_host_driven_cycles_on_a_block_hierarchy(host_amg, golden_dir):
         assert np.abs(x - xo).max() <= 1e-12 * np.abs(xo).max(), cyc
     with pytest.raises(TypeError):
         ml.cycle_host(0, torch.zeros_like(b), b, 'Z')
+
+
+def test_config4_in_miniature_end_to_end(host_amg, golden_dir):
+    """BASELINE config 4 end to end on the kernel SOURCES, without a GPU: generator -> block SA setup with the six
+    rigid-body modes -> symmetric block-multicolour bsr_gauss_seidel V-cycles (host-driven), every block kernel from the
+    host-compiled csrc files -- against the oracle's cycle on the same hierarchy with the same block rows relaxed one by
+    one in the same colour order by the reference row update (what bench.py's parity_in_run does at full size)"""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import oracle
+    from oracle import multilevel as oml
+    amg = host_amg
+    A, B = amg.gallery.linear_elasticity_tets(7, device=torch.device('cpu'))
+    gs = ('gauss_seidel', {'sweep': 'symmetric'})
+    np.random.seed(0)
+    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10)
+    mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=10,
+                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+    rng = np.random.RandomState(1)
+    bh = rng.rand(A.shape[0])
+    levels = bench.host_levels(ml)
+    ro = []
+    xo = oml.Solver(levels, core=oracle.port).solve(bh, tol=1e-30, maxiter=3, residuals=ro)
+    b, x = torch.from_numpy(bh.copy()), torch.zeros(A.shape[0], dtype=torch.float64)
+    for _ in range(3):
+        ml.cycle_host(0, x, b, 'V')
+    assert np.array_equal(x.numpy(), xo)                        # same arithmetic, same order: the bits
+    assert ro[-1] < 0.5 * ro[0]
+    assert {'b200amg_bsr_gauss_seidel', 'b200amg_bsr_matvec', 'b200amg_fit_candidates', 'b200amg_bsr_matmat_numeric'} <= amg._seen_calls

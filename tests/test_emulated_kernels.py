@@ -638,3 +638,64 @@ def test_prepared_rowpat_ilp2_kernel_is_bit_identical(emu_ilp2, grid, common):
     want = x.copy()
     CORE.bsr_jacobi(Ap, Aj, A.data, want, b, temp, 0, n, 1, 1, np.array([0.7]))
     assert np.array_equal(run(OP_JACOBI_BSR1, 0.7), want)
+
+
+# ---- the BSR solve-phase kernels (csrc/bsr.cu; pinned on the GPU in round 1) for the CPU harness -------------------
+@pytest.fixture(scope='module')
+def emu_bsr():
+    if shutil.which('g++') is None:
+        pytest.skip('g++ not available')
+    csrc = os.path.join(ROOT, 'pyamg_b200', 'csrc')
+    srcs = [os.path.join(csrc, 'bsr.cu'), os.path.join(EMU, 'emu_bsr_api.cpp'), os.path.join(EMU, 'emu_globals.cpp')]
+    out = os.path.join(EMU, '_build', 'libemu_bsr.so')
+    deps = srcs + [os.path.join(EMU, 'cuda_runtime.h'), os.path.join(csrc, 'internal.cuh'), os.path.join(csrc, 'common.cuh')]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU, '-I', csrc,
+                        '-x', 'c++'] + srcs + ['-o', out], check=True)
+    lib = ctypes.CDLL(out)
+    lib.emu_bsr_matvec.restype = c_int
+    lib.emu_bsr_matvec.argtypes = [c_int, c_int, c_int, vp, vp, vp, vp, vp, vp, c_int]
+    lib.emu_bsr_jacobi.restype = c_int
+    lib.emu_bsr_jacobi.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_dbl]
+    lib.emu_bsr_gauss_seidel.restype = c_int
+    lib.emu_bsr_gauss_seidel.argtypes = [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, vp, ctypes.POINTER(c_int), c_int]
+    return lib
+
+
+@pytest.mark.parametrize('bs', [2, 3, 6])
+def test_bsr_solve_kernels_equal_reference(emu_bsr, bs):
+    """bsr_matvec (3 modes, rectangular blocks too), bsr_jacobi, bsr_gauss_seidel lexicographic and colour-ordered: the
+    kernel source of csrc/bsr.cu on the host against scipy's bsr_matvec and the reference's compiled kernels"""
+    from oracle import relaxation as orx
+    A, _, b, x0 = block_problem(90, bs, 60 + bs)
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy()
+    n = 90 * bs
+    for mode, want in ((0, A * x0), (1, b - A * x0), (2, b + A * x0)):
+        y = np.full(n, np.nan)
+        assert emu_bsr.emu_bsr_matvec(90, bs, bs, P(Ap), P(Aj), P(Ax), P(x0), P(b), P(y), mode) == 0
+        assert np.array_equal(y, want), mode
+    Rm = random_bsr(50, 70, 3, 6, 0.2, 5)
+    xr = np.random.RandomState(1).rand(70 * 6)
+    y = np.full(150, np.nan)
+    assert emu_bsr.emu_bsr_matvec(50, 3, 6, P(i32(Rm.indptr)), P(i32(Rm.indices)), P(np.ravel(Rm.data).copy()), P(xr), None, P(y), 0) == 0
+    assert np.array_equal(y, Rm * xr)
+    want, tw, got, tg = x0.copy(), np.zeros(n), x0.copy(), np.zeros(n)
+    CORE.bsr_jacobi(Ap, Aj, Ax, want, b, tw, 0, 90, 1, bs, np.array([0.8]))
+    assert emu_bsr.emu_bsr_jacobi(P(Ap), P(Aj), P(Ax), P(got), P(b), P(tg), 0, 90, bs, 0.8) == 0
+    assert np.array_equal(got, want)
+    for r0, r1, dr in ((0, 90, 1), (89, -1, -1)):
+        want, got = x0.copy(), x0.copy()
+        CORE.bsr_gauss_seidel(Ap, Aj, Ax, want, b, r0, r1, dr, bs)
+        assert emu_bsr.emu_bsr_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), r0, r1, dr, bs, None, None, 0) == 0
+        assert np.array_equal(got, want)
+    G = sp.csr_matrix((np.ones(len(Aj)), Aj, Ap), shape=(90, 90))
+    idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(G, oracle.port))
+    idx, ptr = i32(idx), np.ascontiguousarray(ptr, dtype=np.intc)
+    cp = ptr.ctypes.data_as(ctypes.POINTER(c_int))
+    want, got = x0.copy(), x0.copy()
+    oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, 0, 90, 1, bs)
+    oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, 89, -1, -1, bs)
+    assert emu_bsr.emu_bsr_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), 0, 90, 1, bs, P(idx), cp, len(ptr) - 1) == 0
+    assert emu_bsr.emu_bsr_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), 89, -1, -1, bs, P(idx), cp, len(ptr) - 1) == 0
+    assert np.array_equal(got, want)
