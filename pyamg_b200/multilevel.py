@@ -35,13 +35,30 @@ class _Smoother:
 
 
 def coarse_grid_solver(solver):
-    """pyamg/multilevel.py:554-720 for the dense pseudo-inverse solvers ('pinv2' default, 'pinv'):
-    the pseudo-inverse of the (<= max_coarse) coarsest matrix is formed ONCE on the host with
-    LAPACK, exactly as the reference does (sp.linalg.pinv2(A.todense())), and applied on the
-    device every cycle (b200amg_dense_matvec)."""
+    """pyamg/multilevel.py:554-720 for the direct solvers: 'pinv2' (default) / 'pinv' -- the pseudo-inverse of the
+    (<= max_coarse) coarsest matrix is formed ONCE on the host with LAPACK, exactly as the reference does
+    (sp.linalg.pinv2(A.todense())), and applied on the device every cycle (b200amg_dense_matvec) -- and 'lu' /
+    'cholesky' / 'splu', whose factorisation is likewise done once on the host and kept as the explicit inverse (for
+    'splu' of the matrix without its empty rows / columns, zero there, like the reference's Map), so that the per-cycle
+    work is the same dense product; equal to the reference's triangular solves up to rounding (not to the bit)."""
     name, kwargs = solver if isinstance(solver, tuple) else (solver, {})
-    if name not in ('pinv', 'pinv2'):
-        raise ValueError('coarse solver %r is not available on the device (pinv, pinv2)' % (name,))
+    if name not in ('pinv', 'pinv2', 'lu', 'cholesky', 'splu'):
+        raise ValueError('coarse solver %r is not available on the device (pinv, pinv2, lu, cholesky, splu)' % (name,))
+
+    def host_inverse(dense):
+        import scipy.linalg
+        if name in ('pinv', 'pinv2'):
+            return scipy.linalg.pinv(dense, **kwargs)
+        if name == 'lu':
+            return scipy.linalg.lu_solve(scipy.linalg.lu_factor(dense, **kwargs), np.eye(dense.shape[0]))
+        if name == 'cholesky':
+            return scipy.linalg.cho_solve(scipy.linalg.cho_factor(dense, **kwargs), np.eye(dense.shape[0]))
+        keep = np.where(np.abs(dense).sum(axis=0) != 0)[0]          # 'splu': drop empty columns (and the same rows)
+        inv = np.zeros_like(dense)
+        if len(keep):
+            sub = dense[np.ix_(keep, keep)]
+            inv[np.ix_(keep, keep)] = scipy.linalg.lu_solve(scipy.linalg.lu_factor(sub), np.eye(len(keep)))
+        return inv
 
     class generic_solver:
         def __init__(self):
@@ -52,9 +69,8 @@ def coarse_grid_solver(solver):
             if A.nnz == 0:
                 return None
             if self.P is None:
-                import scipy.linalg
                 dense = A.to_scipy().toarray()
-                self.P = torch.from_numpy(np.ascontiguousarray(scipy.linalg.pinv(dense, **kwargs))).to(_dev())
+                self.P = torch.from_numpy(np.ascontiguousarray(host_inverse(dense))).to(_dev())
             return self.P
 
         def __call__(self, A, b):

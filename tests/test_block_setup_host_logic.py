@@ -398,3 +398,27 @@ def test_config4_in_miniature_end_to_end(host_amg, golden_dir):
     assert np.array_equal(x.numpy(), xo)                        # same arithmetic, same order: the bits
     assert ro[-1] < 0.5 * ro[0]
     assert {'b200amg_bsr_gauss_seidel', 'b200amg_bsr_matvec', 'b200amg_fit_candidates', 'b200amg_bsr_matmat_numeric'} <= amg._seen_calls
+
+
+def test_coarse_solver_names(host_amg, golden_dir):
+    """coarse_solver = 'pinv2' (default), 'pinv', 'lu', 'cholesky', 'splu' (multilevel.py:608-650): the inverse formed on
+    the host once; all of them solve the SPD coarse system of the fixture"""
+    amg = host_amg
+    levels, _ = hier_io.load(os.path.join(golden_dir, 'sa_poisson3d_12.npz'))
+    Ac = levels[-1].A
+    rhs = np.random.RandomState(0).rand(Ac.shape[0])
+    want = np.linalg.solve(Ac.toarray(), rhs)
+    for name in ('pinv2', 'pinv', 'lu', 'cholesky', 'splu'):
+        cs = amg.multilevel.coarse_grid_solver(name)
+        x = cs(amg.DevMat.from_scipy(Ac), torch.from_numpy(rhs.copy()))
+        assert np.abs(x.numpy() - want).max() <= 1e-12 * np.abs(want).max(), name
+    with pytest.raises(ValueError):
+        amg.multilevel.coarse_grid_solver('gmres')
+    # 'splu' with an empty row / column: zero there
+    D = Ac.toarray()
+    D[3, :] = 0.0
+    D[:, 3] = 0.0
+    cs = amg.multilevel.coarse_grid_solver('splu')
+    x = cs(amg.DevMat.from_scipy(sp.csr_matrix(D)), torch.from_numpy(rhs.copy())).numpy()
+    keep = np.array([i for i in range(D.shape[0]) if i != 3])
+    assert x[3] == 0.0 and np.allclose(x[keep], np.linalg.solve(D[np.ix_(keep, keep)], rhs[keep]), rtol=1e-11)
