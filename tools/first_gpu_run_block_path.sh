@@ -29,6 +29,8 @@ for f in sorted(glob.glob('gpurun_out/block_path/bench_*.json')):
     except Exception as e:
         print(f, 'unreadable:', e)
 PY
+# 4c. per-entry-point roofline table incl. the block smoothers
+timeout 600 python tools/bench_kernels.py --out $out/kernels_roofline.json > $out/kernels_roofline.log 2>&1; echo "bench_kernels rc=$?" | tee -a $out/summary.txt
 # 5. launch list of the config-4 cycle for profiles/ (only after the plain run above exited)
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/ncu_launches_cfg4.csv \
     python bench.py --config 4 --steps 2 --warmup 1 --no-cpu-baseline > $out/ncu_cfg4.log 2>&1; echo "ncu rc=$?" | tee -a $out/summary.txt
