@@ -309,6 +309,8 @@ int b200amg_vertex_coloring_ldf_host(int n, const int *Ap, const int *Aj, int *c
  * number of aggregates; agg[i] = aggregate of node i or -1; roots[k] = seed node of k */
 int b200amg_standard_aggregation_host(int n, const int *Ap_host, const int *Aj_host, int *agg_host,
                                       int *roots_host);
+/* amg_core.naive_aggregation (smoothed_aggregation.h:244-277, aggregate='naive'); host arrays, returns n_agg */
+int b200amg_naive_aggregation_host(int n, const int *Ap, const int *Aj, int *agg, int *roots);
 /* amg_core.rs_cf_splitting, pyamg/amg_core/ruge_stuben.h:157-297: S (no diagonal) and T = S^T as host CSR;
  * splitting[i] = 1 (C point) or 0 (F point) */
 int b200amg_rs_cf_splitting_host(int n_nodes, const int *Sp_host, const int *Sj_host, const int *Tp_host,

@@ -73,13 +73,15 @@ def symmetric_strength_of_connection(A, theta=0.0):
     return DevMat(Sp, Sj, Sx, (n, n), (1, 1), 'csr', A.has_sorted_indices)
 
 
-def standard_aggregation(A):
-    """-> (agg int32 device tensor [n], n_agg, roots).  Pattern goes to the host once."""
+def standard_aggregation(A, method='standard'):
+    """-> (agg int32 device tensor [n], n_agg, roots).  Pattern goes to the host once.  method: 'standard'
+    (aggregate.py:20-103) or 'naive' (:106-190)."""
     n = A.shape[0]
     Ap, Aj = A.indptr.cpu().numpy(), A.indices.cpu().numpy()
     agg = np.empty(n, dtype=np.intc)
     roots = np.empty(n, dtype=np.intc)
-    nagg = amg_core.standard_aggregation(n, Ap, Aj, agg, roots)
+    fn = amg_core.standard_aggregation if method == 'standard' else amg_core.naive_aggregation
+    nagg = fn(n, Ap, Aj, agg, roots)
     return torch.from_numpy(agg).to(_dev()), nagg, roots[:nagg]
 
 
@@ -274,8 +276,9 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     theta = float(skw.get('theta', 0.0)) if sname is not None else 0.0
     if theta < 0:
         raise ValueError('expected a positive theta')
-    if _unpack(aggregate)[0] != 'standard':
-        raise NotImplementedError("aggregate must be 'standard'")
+    aname = _unpack(aggregate)[0]
+    if aname not in ('standard', 'naive'):
+        raise NotImplementedError("aggregate must be 'standard' or 'naive'")
     mname, mkw = _unpack(smooth)
     if mname not in ('jacobi', None) or set(mkw) - {'omega', 'degree'}:
         raise NotImplementedError("smooth must be ('jacobi', {'omega', 'degree'}) or None")
@@ -314,7 +317,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
             # the same steps on blocks: aggregation on the block graph AS STORED (first-touch order out of bsr_matmat
             # on coarse levels), then the in-place block sort of get_diagonal
             K1 = lvl.A.blocksize[0]
-            agg, nagg, roots = standard_aggregation(symmetric_strength_of_connection(lvl.A, theta))
+            agg, nagg, roots = standard_aggregation(symmetric_strength_of_connection(lvl.A, theta), aname)
             T, Bc = fit_candidates_block(agg, nagg, lvl.B, K1, K2)
             A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
             if mname == 'jacobi':
@@ -335,7 +338,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         # out of csr_matmat on coarse levels; pass 2 of the aggregation picks the FIRST aggregated
         # neighbour in storage order) and only afterwards sorts it in place inside
         # jacobi_prolongation_smoother -> get_diagonal (pyamg/util/utils.py:571)
-        agg, nagg, roots = standard_aggregation(lvl.A if theta == 0 else symmetric_strength_of_connection(lvl.A, theta))
+        agg, nagg, roots = standard_aggregation(lvl.A if theta == 0 else symmetric_strength_of_connection(lvl.A, theta), aname)
         T, Bc = fit_candidates_scalar(agg, nagg, lvl.B)
         A = lvl.A = sort_indices(lvl.A) if mname == 'jacobi' else lvl.A
         if mname == 'jacobi':

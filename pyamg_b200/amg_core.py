@@ -99,6 +99,20 @@ def vertex_coloring_mis(num_rows, Ap, Aj, x):
     return K
 
 
+def naive_aggregation(n_row, Ap, Aj, x, y):
+    """smoothed_aggregation.h:244-277 (host arrays); x receives 0-based aggregate numbers (the reference's are 1-based
+    and its Python wrapper subtracts 1, aggregate.py:174-176); returns the number of aggregates"""
+    Ap = np.ascontiguousarray(Ap, np.intc)
+    Aj = np.ascontiguousarray(Aj, np.intc)
+    if x.dtype != np.intc or y.dtype != np.intc or not x.flags.c_contiguous or not y.flags.c_contiguous:
+        raise TypeError('x, y must be contiguous int32 numpy arrays')
+    lib = _lib.load()
+    k = lib.b200amg_naive_aggregation_host(int(n_row), Ap.ctypes.data, Aj.ctypes.data, x.ctypes.data, y.ctypes.data)
+    if k < 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+    return k
+
+
 def _weighted_coloring(entry, num_rows, Ap, Aj, x, w):
     Ap = np.ascontiguousarray(Ap, np.intc)
     Aj = np.ascontiguousarray(Aj, np.intc)

@@ -250,3 +250,20 @@ extern "C" int b200amg_rs_cf_splitting_host(int n, const int *Sp, const int *Sj,
     }
     return 0;
 }
+
+// amg_core.naive_aggregation (pyamg/amg_core/smoothed_aggregation.h:244-277; aggregate='naive'): in index order, a node
+// not yet taken founds an aggregate with every neighbour not yet taken.  agg[i] in [0, n_agg), roots[k] = founder.
+extern "C" int b200amg_naive_aggregation_host(int n, const int *Ap, const int *Aj, int *agg, int *roots)
+{
+    if (n < 0) return set_err(B200AMG_EINVAL, "naive_aggregation: n < 0");
+    for (int i = 0; i < n; ++i) agg[i] = -1;
+    int nagg = 0;
+    for (int i = 0; i < n; ++i) {
+        if (agg[i] >= 0) continue;
+        agg[i] = nagg;
+        for (int p = Ap[i]; p < Ap[i + 1]; ++p)
+            if (agg[Aj[p]] < 0) agg[Aj[p]] = nagg;
+        roots[nagg++] = i;
+    }
+    return nagg;
+}

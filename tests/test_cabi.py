@@ -202,3 +202,24 @@ def test_host_jp_ldf_colourings():
             rows = np.repeat(np.arange(n), np.diff(Ap))
             off = rows != Aj
             assert not np.any(a[rows[off]] == a[Aj[off]])
+
+
+def test_host_naive_aggregation_equals_reference():
+    """b200amg_naive_aggregation_host (aggregate='naive') against the reference's compiled amg_core.naive_aggregation
+    (1-based there, 0-based here like the reference's Python wrapper makes them) and its docstring example"""
+    from pyamg_b200 import amg_core
+    G = sp.csr_matrix(np.array([[2., -1, 0, 0], [-1, 2, -1, 0], [0, -1, 2, -1], [0, 0, -1, 2]]))
+    a, r = np.empty(4, np.intc), np.empty(4, np.intc)
+    assert amg_core.naive_aggregation(4, G.indptr, G.indices, a, r) == 2 and list(a) == [0, 0, 1, 1] and list(r[:2]) == [0, 2]
+    if oracle.ref is None:
+        pytest.skip('reference kernels not built')
+    rng = np.random.RandomState(0)
+    for t in range(40):
+        n = rng.randint(1, 200)
+        M = sp.random(n, n, rng.uniform(0.01, 0.1), random_state=rng, format='csr')
+        M = sp.csr_matrix(M + M.T + (sp.eye(n) if t % 2 else 0 * sp.eye(n)))
+        Ap, Aj = M.indptr.astype(np.intc), M.indices.astype(np.intc)
+        a, r, a2, r2 = (np.empty(n, np.intc) for _ in range(4))
+        k = amg_core.naive_aggregation(n, Ap, Aj, a, r)
+        k2 = oracle.ref.naive_aggregation(n, Ap, Aj, a2, r2)
+        assert k == k2 and np.array_equal(a, a2 - 1) and np.array_equal(r[:k], r2[:k2])
