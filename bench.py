@@ -696,6 +696,41 @@ def measure_roofline(R, reps=5):
             'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
 
 
+def golden_parity(args):
+    """config 2 pinned to the REAL reference at the benchmark's own size: tests/golden/ref_config2_<grid>.json holds what
+    the reference (imported in the build container, tests/golden/make_ref_config2.py) produced for this exact protocol --
+    level table, both rho(D^-1 A) estimates per level, the residual history of 10 V-cycles, entries of x.  The device
+    setup is re-run with the reference's rho fed in (the one quantity the device estimates to 1e-7 only),
+    consuming the seeded random stream like the reference, and the 10-cycle history is compared."""
+    path = os.path.join(ROOT, 'tests', 'golden', 'ref_config2_%d.json' % args.grid)
+    if args.config != 2 or args.smoother != 'jacobi' or not os.path.exists(path):
+        return None
+    import pyamg_b200 as amg
+    g = json.load(open(path))
+    fh = float.fromhex
+    rho = list(zip([fh(h) for h in g['rho_smooth_hex']], [fh(h) for h in g['rho_relax_hex']]))
+    A = amg.gallery.poisson((args.grid,) * 3)
+    np.random.seed(0)
+    ml = amg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=500, rho_override=rho)
+    b = np.random.rand(A.shape[0])
+    res = []
+    x = ml.solve(b, tol=1e-30, maxiter=len(g['residuals_hex']) - 1, residuals=res)
+    x = np.asarray(x)
+    ref = np.array([fh(h) for h in g['residuals_hex']])
+    res = np.array(res, dtype=np.float64)
+    xp = np.array([fh(h) for h in g['x_pick_hex']])
+    out = {'fixture': 'tests/golden/ref_config2_%d.json (real reference, build container)' % args.grid,
+           'levels_equal': level_table(ml) == g['levels'],
+           'b_identical': float(b.sum()).hex() == g['b_sum_hex'],
+           'cycles': int(len(ref) - 1),
+           'history_vs_reference_max_rel_diff': float(np.max(np.abs(res - ref) / ref)) if len(res) == len(ref) else None,
+           'x_entries_max_rel_diff': float(np.max(np.abs(x[g['x_pick_index']] - xp) / np.abs(xp))),
+           'x_norm_rel_diff': float(abs(np.linalg.norm(x) - fh(g['x_norm_hex'])) / fh(g['x_norm_hex'])),
+           'reference_history_first_last': [float(ref[0]), float(ref[-1])]}
+    del ml
+    return out
+
+
 def cpu_baseline(R, args):
     """reference CPU path (scipy SpMV + the reference's compiled amg_core smoothers when
     oracle/_ref is built, else the C port) on this box's host cores, same hierarchy, same b."""
@@ -799,79 +834,179 @@ def cpu_problem_rs(grid):
     return levels, np.random.rand(A.shape[0])
 
 
+def load_reference_pyamg():
+    """the REAL reference package (pyamg 3.0.2 fork): /root/reference in the build container, else the installed copy
+    under baseline/_ref (oracle/install_ref.py; travels to the GPU box).  oracle/refimport.py is loaded by file path so
+    that nothing else of this repository -- neither pyamg_b200 nor the oracle's C port -- enters the reference process.
+    -> the imported `pyamg` module, or None when neither source exists."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('b200amg_refimport', os.path.join(ROOT, 'oracle', 'refimport.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    if not mod.available():
+        return None, 'no reference package (looked at %s)' % mod.REF_ROOT
+    import warnings
+    warnings.simplefilter('ignore')
+    return mod.import_pyamg(), mod.REF_ROOT
+
+
+def reference_mcgs(pyamg, ml):
+    """symmetric multicolour Gauss-Seidel on every level with the reference's own pieces:
+    pyamg.graph.vertex_coloring(A, 'MIS') -> rows grouped by colour -> relaxation.gauss_seidel_indexed"""
+    from pyamg.graph import vertex_coloring
+    from pyamg.relaxation.relaxation import gauss_seidel_indexed
+    colours = []
+    for lvl in ml.levels[:-1]:
+        c = vertex_coloring(lvl.A.tocsr(), 'MIS')
+        K = int(c.max()) + 1
+        idx = np.concatenate([np.where(c == k)[0] for k in range(K)]).astype('intc')
+
+        def sm(A, x, b, idx=idx):
+            gauss_seidel_indexed(A, x, b, idx, iterations=1, sweep='symmetric')
+        lvl.presmoother = lvl.postsmoother = sm
+        colours.append(K)
+    return colours
+
+
+def reference_problem(pyamg, args):
+    """the workload of `args.config` built by the reference's own public API -> (ml, b, colours per level or None)"""
+    g = args.grid
+    colours = None
+    if args.config == 2:
+        A = pyamg.gallery.poisson((g, g, g), format='csr')
+        np.random.seed(0)
+        ml = pyamg.smoothed_aggregation_solver(A, presmoother=JAC, postsmoother=JAC, max_coarse=500)
+        if args.smoother == 'mcgs':
+            colours = reference_mcgs(pyamg, ml)
+    elif args.config == 3:
+        from pyamg.gallery.diffusion import diffusion_stencil_2d
+        st = diffusion_stencil_2d(epsilon=0.001, theta=np.pi / 8, type='FE')
+        A = pyamg.gallery.stencil_grid(st, (g, g), format='csr')
+        np.random.seed(0)
+        ml = pyamg.ruge_stuben_solver(A, max_coarse=500)
+        colours = reference_mcgs(pyamg, ml)
+    else:
+        # the matrix generator is not on the measured path: the stencil-wise assembly of pyamg_b200.gallery on the CPU
+        # device (the reference's element loop in Python would take hours for 12.3 M tetrahedra); solver = the reference's
+        import torch
+        from pyamg_b200 import gallery
+        A, B = gallery.linear_elasticity_tets(g, device=torch.device('cpu'))
+        A, B = A.to_scipy(), B.numpy()
+        np.random.seed(0)
+        gs = ('gauss_seidel', {'sweep': 'symmetric'})
+        ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=500, improve_candidates=None)
+    b = np.random.rand(ml.levels[0].A.shape[0])
+    return ml, b, colours
+
+
+def scipy_level_tables(levels):
+    lv = [[int(l.A.shape[0]), int(l.A.nnz)] for l in levels]
+    blocks = None
+    if any(getattr(l.A, 'blocksize', (1, 1)) != (1, 1) for l in levels):
+        blocks = [[int(l.A.shape[0] // l.A.blocksize[0]), int(l.A.nnz // (l.A.blocksize[0] * l.A.blocksize[1])), int(l.A.blocksize[0])]
+                  for l in levels]
+    return lv, blocks
+
+
+def workload_config(args, levels, blocks, colours):
+    """the `config` object both arms print: the workload only, so that the two lines carry the SAME object
+    (everything arm-specific -- parallelism, setup time, byte counts -- goes to `detail`)"""
+    nb0, bs0 = (blocks[0][1], blocks[0][2]) if blocks else (levels[0][1], 1)
+    return {'workload': workload_name(args), 'grid': args.grid, 'levels': levels, 'block_levels': blocks,
+            'colours_per_level': colours,
+            'l2': 'inputs larger than L2 (the level-0 operator alone is %.2f GB)' % (1e-9 * block_bytes(nb0, bs0, bs0))}
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the V-cycle (oracle/_ref =
-    its compiled _amg_core + scipy SpMV, glued exactly like pyamg/multilevel.py:473-548), serial,
-    on the box's host cores; same config/metric/unit.  Only the TIMED path matters here: the
-    hierarchy it cycles over is produced by the device setup when a GPU is present (seconds
-    instead of ~200 s of CPU setup; bit-identical to the reference-built one, tests/), else by the
-    CPU restatement oracle/sa.py."""
+    """--impl reference: the reference's OWN stock code path, nothing of this repository's product on it.
+    pyamg (imported through oracle/refimport.py from /root/reference or from the installed copy baseline/_ref) builds the
+    hierarchy with its public constructor and every step is ONE call of its cycle recursion
+    multilevel_solver.__solve(0, x, b, 'V') (pyamg/multilevel.py:473-548) -- scipy SpMV + the reference's compiled
+    amg_core smoothers, serial, on the box's host cores.  No torch.cuda, no pyamg_b200, no libb200amg.so in this process
+    (config 4 alone borrows pyamg_b200.gallery's matrix generator on the CPU device).
+    When no reference package exists the arm falls back to the CPU restatement (oracle/) and says so in `kind`."""
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    import oracle
-    from oracle import multilevel as oml
     budget_s = float(os.environ.get('B200AMG_REF_BUDGET_S', '200'))
-    how = None
-    try:
-        import torch
-        if torch.cuda.is_available():
-            ml, b = build_for(args)
-            levels = host_levels(ml)
-            if args.config == 4:
-                levels = lexicographic(levels)
-            how = 'device setup (pyamg_b200), downloaded to the host'
-            del ml
-            torch.cuda.empty_cache()
-    except Exception as exc:                                           # noqa: BLE001
-        how = None
-        sys.stderr.write('reference arm: device setup unavailable (%s); CPU setup\n' % (exc,))
-    if how is None and args.config == 3:
-        levels, b = cpu_problem_rs(args.grid)
-        how = 'CPU setup (oracle/rs.py)'
-    if how is None and args.config == 4:
-        levels, b = cpu_problem_elasticity(args.grid)
-        how = 'CPU setup (oracle/sa.py on blocks)'
-    if how is None:
-        from oracle import sa
-        import scipy.sparse as sp
-        g = args.grid
-        I = sp.identity(g, format='csr')
-        T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(g, g), format='csr')
-        A = (sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T)).tocsr()
-        A.sort_indices()
-        np.random.seed(0)
-        levels = sa.smoothed_aggregation_hierarchy(A, presmoother=JAC, postsmoother=JAC, max_coarse=500, core=oracle.core)
-        b = np.random.rand(A.shape[0])
-        how = 'CPU setup (oracle/sa.py)'
-    S = oml.Solver(levels, core=oracle.core, wasted_prolongation=True)
-    S.coarse_matrix()
-    x = np.zeros_like(b)
     t0 = time.perf_counter()
-    S._cycle(0, x, b, 'V')
+    pyamg, where = load_reference_pyamg()
+    if pyamg is not None:
+        ml, b, colours = reference_problem(pyamg, args)
+        setup_s = time.perf_counter() - t0
+        levels, blocks = scipy_level_tables(ml.levels)
+        cycle = ml._multilevel_solver__solve              # the reference's private recursion, called as solve() calls it
+        step = lambda x: cycle(0, x, b, 'V')              # noqa: E731
+        kind = 'reference'
+        how = ('stock pyamg %s from %s: %s + multilevel_solver.__solve(0, x, b, "V") per step'
+               % (getattr(pyamg, '__version__', '3.0.2'), where,
+                  {2: 'smoothed_aggregation_solver', 3: 'ruge_stuben_solver + gauss_seidel_indexed over MIS colours',
+                   4: 'smoothed_aggregation_solver(B = rigid-body modes), symmetric lexicographic bsr_gauss_seidel'}[args.config]))
+        n_levels = len(ml.levels)
+        rho = [float(l.A.rho_D_inv) if hasattr(l.A, 'rho_D_inv') else None for l in ml.levels[:-1]]
+    else:
+        sys.stderr.write('reference arm: %s -- CPU restatement (oracle/) instead\n' % where)
+        import oracle
+        from oracle import multilevel as oml
+        if args.config == 3:
+            lv, b = cpu_problem_rs(args.grid)
+        elif args.config == 4:
+            lv, b = cpu_problem_elasticity(args.grid)
+        else:
+            from oracle import sa
+            import scipy.sparse as sp
+            g = args.grid
+            I = sp.identity(g, format='csr')
+            T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(g, g), format='csr')
+            A = (sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T)).tocsr()
+            A.sort_indices()
+            np.random.seed(0)
+            lv = sa.smoothed_aggregation_hierarchy(A, presmoother=JAC, postsmoother=JAC, max_coarse=500, core=oracle.core)
+            b = np.random.rand(A.shape[0])
+        setup_s = time.perf_counter() - t0
+        S = oml.Solver(lv, core=oracle.core, wasted_prolongation=True)
+        S.coarse_matrix()
+        step = lambda x: S._cycle(0, x, b, 'V')           # noqa: E731
+        levels, blocks = scipy_level_tables(lv)
+        colours = None
+        if args.config == 3:
+            # rows ascend inside a colour: colours = descents of the index list + 1
+            colours = [int(np.flatnonzero(np.diff(l.pre[1]['indices']) < 0).size + 1) for l in lv[:-1]]
+        kind = oracle.kind if oracle.kind == 'port' else 'port+reference-kernels'
+        how = 'CPU restatement oracle/ (setup oracle/sa.py|rs.py, cycle oracle/multilevel.py over %s + scipy)' % (
+            'oracle/_ref/_amg_core.so' if oracle.kind == 'reference' else 'the C port')
+        n_levels = len(lv)
+        rho = None
+    x = np.zeros_like(b)
+    hist = [float(np.linalg.norm(b))]                      # x0 = 0: ||b - A x0||
+    t0 = time.perf_counter()
+    step(x)
     t_first = time.perf_counter() - t0
     warm_done = 1
     while warm_done < args.warmup and (warm_done + 1) * t_first < 0.25 * budget_s:
-        S._cycle(0, x, b, 'V')
+        step(x)
         warm_done += 1
     timed = max(1, min(args.steps, int(0.75 * budget_s / max(t_first, 1e-9))))
     t0 = time.perf_counter()
     for _ in range(timed):
-        S._cycle(0, x, b, 'V')
+        step(x)
     sec = (time.perf_counter() - t0) / timed
     val = 1.0 / sec
-    sample = ('%d of the %d requested V(1,1)-cycles timed (%d warm-up), each a full cycle over the %d-level '
-              'hierarchy of the workload (grid %d); hierarchy from: %s' % (timed, args.steps, warm_done, len(levels), args.grid, how))
+    sample = ('%d of the %d requested V(1,1)-cycles timed (%d warm-up), each a full cycle over the %d-level hierarchy of '
+              'the workload (grid %d), x carried from cycle to cycle; %s; serial code, 1 core'
+              % (timed, args.steps, warm_done, n_levels, args.grid, how))
     out = {'impl': 'reference', 'metric': metric_name(args),
            'value': val, 'unit': 'V-cycles/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
            'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
            'dtype': 'f64', 'data': 'synthetic',
-           'config': {'workload': workload_name(args),
-                      'levels': [[int(l.A.shape[0]), int(l.A.nnz)] for l in levels]},
+           'config': workload_config(args, levels, blocks, colours),
            'cpu_baseline': {'value': val, 'unit': 'V-cycles/s', 'cores': 1, 'host_cores': os.cpu_count(),
-                            'kind': oracle.kind, 'sample': sample},
+                            'kind': kind, 'sample': sample},
            'e2e': {'value': val, 'unit': 'V-cycles/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-           'gpu_launches': 0}
+           'gpu_launches': 0,
+           'detail': {'parallelism': '1 host core (the reference is serial)', 'setup_s_reference': round(setup_s, 1),
+                      'timed_steps': timed, 'warmup_done': warm_done, 'rho_D_inv_A': rho,
+                      'modules_loaded': sorted(m for m in sys.modules if m.split('.')[0] in ('torch', 'pyamg_b200', 'oracle'))[:8]}}
     print(json.dumps(out))
 
 
@@ -903,18 +1038,21 @@ def main():
         return
     ml = R['ml']
     vb = vcycle_bytes(ml, 2 if args.smoother == 'mcgs' else 0)
+    golden = None
+    if R['world'] == 1:
+        try:
+            golden = golden_parity(args)
+        except Exception as exc:                                          # noqa: BLE001  (reported, never hidden)
+            golden = {'error': '%s: %s' % (type(exc).__name__, exc)}
     out = {'metric': metric_name(args),
            'value': R['value'], 'unit': 'V-cycles/s', 'n_gpus': R['world'], 'steps': args.steps,
            'warmup': args.warmup, 'ms_per_step': R['ms_step'], 'higher_is_better': True, 'scaling': 'weak',
            'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-           'config': {'workload': workload_name(args),
-                      'levels': level_table(ml), 'parallelism': 'single GPU' if R['world'] == 1 else
+           'config': workload_config(args, level_table(ml), block_table(ml),
+                                     ([int(len(l.presmoother.color_ptr) - 1) for l in ml.levels[:-1]]
+                                      if args.smoother == 'mcgs' else None)),
+           'detail': {'parallelism': 'single GPU' if R['world'] == 1 else
                       'replicas: %d independent solves, one per GPU' % R['world'],
-                      'l2': 'inputs larger than L2 (the level-0 operator alone is %.2f GB)'
-                            % (1e-9 * block_bytes(ml.levels[0].A.nblocks, *ml.levels[0].A.blocksize)),
-                      'block_levels': block_table(ml),
-                      'colours_per_level': ([int(len(l.presmoother.color_ptr) - 1) for l in ml.levels[:-1]]
-                                            if args.smoother == 'mcgs' else None),
                       'setup_s_device': round(R['setup_s'], 2),
                       'unfused_algorithmic_bytes_per_cycle': vb,
                       'cycle_GBs_on_unfused_bytes': round(vb / (R['ms_step'] * 1e-3) / 1e9, 1)},
@@ -922,6 +1060,8 @@ def main():
     if cpu is not None:
         out['cpu_baseline'] = cpu
         out['parity_in_run'] = parity
+    if golden is not None:
+        out['parity_vs_reference_golden'] = golden
     print(json.dumps(out))
 
 

@@ -4,8 +4,9 @@
  and supplying the two build-generated modules; the native module is
 oracle/_ref/_amg_core.so (compiled from the reference sources by oracle/build_ref.sh).
 
-Only usable in the build container (the GPU box has no /root/reference); used by
-tests/golden/make_golden.py to generate fixtures and by tests that are skipped elsewhere.
+Source of the package: /root/reference in the build container, else the installed copy under baseline/_ref
+(oracle/install_ref.py; git-ignored, travels to the GPU box).  Used by tests/golden/make_golden.py to generate
+fixtures, by tests that are skipped where neither exists, and by bench.py --impl reference (the reference arm).
 """
 import builtins
 import importlib
@@ -16,8 +17,27 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get('PYAMG_REF_ROOT', '/root/reference')
 _HERE = os.path.dirname(os.path.abspath(__file__))
+_INSTALLED = os.path.join(os.path.dirname(_HERE), 'baseline', '_ref')      # oracle/install_ref.py (travels to the GPU box)
+
+
+def _ref_root():
+    env = os.environ.get('PYAMG_REF_ROOT')
+    if env:
+        return env
+    if os.path.isdir('/root/reference/pyamg'):
+        return '/root/reference'
+    return _INSTALLED
+
+
+REF_ROOT = _ref_root()
+
+
+def _native():
+    for p in (os.path.join(_HERE, '_ref', '_amg_core.so'), os.path.join(_INSTALLED, '_amg_core.so')):
+        if os.path.exists(p):
+            return p
+    return os.path.join(_HERE, '_ref', '_amg_core.so')
 
 _PATCHES = {
     'aggregation/aggregate.py': [
@@ -28,8 +48,7 @@ _PATCHES = {
 
 
 def available():
-    return os.path.isdir(os.path.join(REF_ROOT, 'pyamg')) and \
-        os.path.exists(os.path.join(_HERE, '_ref', '_amg_core.so'))
+    return os.path.isdir(os.path.join(REF_ROOT, 'pyamg')) and os.path.exists(_native())
 
 
 class _Loader(importlib.abc.SourceLoader):
@@ -68,8 +87,7 @@ class _Finder(importlib.abc.MetaPathFinder):
         if fullname in ('pyamg.__config__', 'pyamg.version'):
             return importlib.machinery.ModuleSpec(fullname, _Generated(fullname))
         if fullname == 'pyamg.amg_core._amg_core':
-            so = os.path.join(_HERE, '_ref', '_amg_core.so')
-            return importlib.util.spec_from_file_location(fullname, so)
+            return importlib.util.spec_from_file_location(fullname, _native())
         rel = fullname.split('.')[1:]
         base = os.path.join(REF_ROOT, 'pyamg', *rel)
         if os.path.isdir(base) and os.path.exists(os.path.join(base, '__init__.py')):
@@ -194,7 +212,7 @@ def import_pyamg():
         _shims()
         sys.meta_path.insert(0, _Finder())
         # amg_core.py falls back to a plain `import _amg_core`
-        spec = importlib.util.spec_from_file_location('_amg_core', os.path.join(_HERE, '_ref', '_amg_core.so'))
+        spec = importlib.util.spec_from_file_location('_amg_core', _native())
         mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(mod)
         sys.modules['_amg_core'] = mod

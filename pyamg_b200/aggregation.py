@@ -164,6 +164,8 @@ def jacobi_prolongation_smoother_block(A, T, omega=4.0 / 3.0, degree=1, rho=None
     dinv = inverse_diagonal(A)
     if rho is None:
         rho = approximate_spectral_radius(_scaled_block(A, dinv))
+    else:
+        np.random.rand(A.shape[1], 1)       # a fed estimate still consumes the start vector's draw (util/linalg.py:367)
     S = _scaled_block(A, dinv, omega / rho)
     P = T
     for _ in range(degree):
@@ -243,6 +245,8 @@ def jacobi_prolongation_smoother(A, T, omega=4.0 / 3.0, degree=1, rho=None):
     dinv = inverse_diagonal(A)
     if rho is None:
         rho = approximate_spectral_radius(_scaled(A, dinv))
+    else:
+        np.random.rand(A.shape[1], 1)       # a fed estimate still consumes the start vector's draw (util/linalg.py:367)
     S = _scaled(A, dinv, omega / rho)
     P = T
     for _ in range(degree):
@@ -264,7 +268,8 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
     improve_candidates=[('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None],
     presmoother=postsmoother=('block_gauss_seidel', {'sweep': 'symmetric'}) -- exact, but those sweeps are
     lexicographic, i.e. one row after the other on the device.  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
-    tests feed the reference's spectral-radius estimates."""
+    tests feed the reference's spectral-radius estimates; a fed estimate still draws (and drops) the start vector the
+    estimate would have drawn, so that a seeded setup leaves the global numpy RNG where the reference leaves it."""
     if symmetry not in ('hermitian', 'symmetric'):
         raise NotImplementedError('only symmetric / hermitian problems have a device setup path')
     improve = _levelize_improve(improve_candidates, max_levels)
@@ -358,6 +363,7 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
         for k, lvl in enumerate(levels[:-1]):
             if k < len(rho_override) and rho_override[k][1] is not None:
                 lvl.A.rho_D_inv = rho_override[k][1]
+                np.random.rand(lvl.A.shape[1], 1)       # keep the seeded random stream where the reference's is
     ml = multilevel_solver(levels, **kwargs)
     change_smoothers(ml, presmoother, postsmoother)
     return ml

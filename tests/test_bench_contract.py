@@ -20,10 +20,39 @@ def test_reference_arm_line(extra):
     d = json.loads(r.stdout.strip().splitlines()[-1])
     assert d['impl'] == 'reference' and d['unit'] == 'V-cycles/s' and d['higher_is_better'] is True
     assert d['value'] > 0 and abs(d['value'] - 1000.0 / d['ms_per_step']) <= 1e-6 * d['value']
-    assert d['cpu_baseline']['kind'] in ('reference', 'port') and d['cpu_baseline']['cores'] == 1
+    assert d['cpu_baseline']['kind'] in ('reference', 'port', 'port+reference-kernels') and d['cpu_baseline']['cores'] == 1
     assert d['cpu_baseline']['value'] == d['value'] and d['e2e']['value'] == d['value']
     assert d['e2e']['h2d_bytes_per_step'] == 0 and d['e2e']['d2h_bytes_per_step'] == 0 and d['gpu_launches'] == 0
     assert d['vs_baseline'] is None and len(d['config']['levels']) >= 2 and 'workload' in d['config']
+    # the `config` object is the workload only -- the same keys the GPU arm prints (bench.workload_config)
+    assert sorted(d['config']) == ['block_levels', 'colours_per_level', 'grid', 'l2', 'levels', 'workload']
+    if d['cpu_baseline']['kind'] == 'reference':
+        # the stock reference drove the run: its package came from /root/reference or the installed copy, and (config 4's
+        # matrix generator aside) nothing of this repository's product or of torch was imported into the process
+        assert 'stock pyamg' in d['cpu_baseline']['sample'] and '__solve' in d['cpu_baseline']['sample']
+        if '--config' not in extra or extra[extra.index('--config') + 1] != '4':
+            assert d['detail']['modules_loaded'] == []
+
+
+def test_reference_arm_runs_from_the_installed_copy(tmp_path):
+    """baseline/_ref (oracle/install_ref.py) is what the GPU box has instead of /root/reference"""
+    if not os.path.isdir(os.path.join(ROOT, 'baseline', '_ref', 'pyamg')):
+        pytest.skip('no installed reference copy (build container only)')
+    env = dict(os.environ, B200AMG_REF_BUDGET_S='5', CUDA_VISIBLE_DEVICES='', PYAMG_REF_ROOT=os.path.join(ROOT, 'baseline', '_ref'))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference', '--steps', '2', '--warmup', '1',
+                        '--grid', '14'], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d['cpu_baseline']['kind'] == 'reference' and 'baseline/_ref' in d['cpu_baseline']['sample']
+
+
+def test_reference_arm_without_any_reference_package_falls_back_to_the_restatement(tmp_path):
+    env = dict(os.environ, B200AMG_REF_BUDGET_S='5', CUDA_VISIBLE_DEVICES='', PYAMG_REF_ROOT=str(tmp_path))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference', '--steps', '2', '--warmup', '1',
+                        '--grid', '14'], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d['cpu_baseline']['kind'] in ('port', 'port+reference-kernels') and d['value'] > 0
 
 
 def test_reference_arm_other_ranks_exit_quietly():
