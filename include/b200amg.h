@@ -92,6 +92,15 @@ int b200amg_bsr_gauss_seidel(const int *Ap, const int *Aj, const double *Ax, dou
 /* out_dev[0] = sum_i x_i*y_i  (deterministic two-stage reduction; work: >= 1024 doubles) */
 int b200amg_dot(long long n, const double *x, const double *y, double *out_dev, double *work,
                 void *stream);
+/* b200amg_dot without any caller-provided or allocated scratch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, serving loops, harnesses that
+ * forbid cudaMalloc).  The partial sums live in a file-scope `static __device__ __align__(256)` array of 1024 doubles
+ * (8 KB, held by every GPU that loads the library until exit); the call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine).  Limit: n <= 268 435 456 (2^28) elements, larger n returns B200AMG_EINVAL with a message.
+ * Same kernels and reduction order as b200amg_dot: the result is bit-identical to it.  All calls on a device share the
+ * array (nothing needs clearing: every cell read is written first by the same call), so calls that OVERLAP on the GPU
+ * (different streams without ordering) race -- serialise them. */
+int b200amg_dot_noalloc(long long n, const double *x, const double *y, double *out_dev, void *stream);
 /* y = a*x + y ; y = x ; x = 0 */
 int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream);
 /* y = a*x */

@@ -51,6 +51,7 @@ _SIGS = {
     'b200amg_halo_push': (c_int, [p, c_int, p, p, p, p, p, c_int, p, p]),
     'b200amg_halo_wait': (c_int, [p, c_int, p, c_longlong, p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
+    'b200amg_dot_noalloc': (c_int, [c_longlong, p, p, p, p]),
     'b200amg_axpy': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scal': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scale_diag': (c_int, [c_longlong, c_double, p, p, p, c_int, p]),

@@ -141,6 +141,11 @@ extern "C" int b200amg_dot(long long n, const double *x, const double *y, double
     return dot(n, x, y, out_dev, work, S(stream));
 }
 
+extern "C" int b200amg_dot_noalloc(long long n, const double *x, const double *y, double *out_dev, void *stream)
+{
+    return dot_noalloc(n, x, y, out_dev, S(stream));
+}
+
 extern "C" int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream)
 {
     return axpy(n, a, x, y, S(stream));

@@ -64,6 +64,42 @@ int dot(long long n, const double *x, const double *y, double *out, double *work
     return check_launch("dot_final_kernel");
 }
 
+// ---- b200amg_dot_noalloc: the same two kernels with the partial sums in a library-owned array -----------------
+// For callers that cannot allocate (CUDA graph capture, serving loops): the DOT_MAX_GRID partial sums live in a
+// file-scope device array (8 KB on every GPU that loads the library, held until exit) instead of a caller-provided
+// `work`.  In HOST code `g_dot_scratch` is only the symbol's host-side stand-in, never a device address: the address
+// the kernels get comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// Nothing has to start at zero (dot_partial_kernel overwrites the `grid` cells dot_final_kernel reads); every call
+// shares the array, so two calls that overlap on the GPU (different streams, no ordering) race.
+constexpr long long DOT_NOALLOC_MAX_N = 1ll << 28;          // 268 435 456 doubles per vector (2 GiB)
+constexpr int DOT_NOALLOC_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_dot_scratch[DOT_MAX_GRID];
+static double *g_dot_scratch_ptr[DOT_NOALLOC_MAX_DEVICES];   // device address of g_dot_scratch, per device ordinal
+
+static int dot_scratch_address(double **out)
+{
+    int dev = -1;
+    B200_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= DOT_NOALLOC_MAX_DEVICES) return set_err(B200AMG_EINVAL, "dot_noalloc: device ordinal out of range");
+    if (!g_dot_scratch_ptr[dev]) {
+        double *ptr = nullptr;
+        B200_CUDA(cudaGetSymbolAddress((void **)&ptr, g_dot_scratch));
+        if (!ptr) return set_err(B200AMG_ESTATE, "dot_noalloc: cudaGetSymbolAddress returned a null address");
+        g_dot_scratch_ptr[dev] = ptr;
+    }
+    *out = g_dot_scratch_ptr[dev];
+    return 0;
+}
+
+int dot_noalloc(long long n, const double *x, const double *y, double *out, cudaStream_t st)
+{
+    if (n > DOT_NOALLOC_MAX_N)
+        return set_err(B200AMG_EINVAL, "b200amg_dot_noalloc: n exceeds the maximum of 268435456 (2^28) elements");
+    double *scratch = nullptr;
+    B200_TRY(dot_scratch_address(&scratch));
+    return dot(n, x, y, out, scratch, st);
+}
+
 __global__ void __launch_bounds__(256) axpy_kernel(long long n, double a, const double *__restrict__ x, double *y)
 {
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;

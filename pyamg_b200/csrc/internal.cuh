@@ -114,6 +114,7 @@ int block_diag_inverse_gj(int n_brow, int bs, const int *Ap, const int *Aj, cons
 int pinv_array(double *AA, int m, int n, int transA, cudaStream_t st);
 
 int dot(long long n, const double *x, const double *y, double *out, double *work, cudaStream_t st);
+int dot_noalloc(long long n, const double *x, const double *y, double *out, cudaStream_t st);   // scratch inside the library
 int axpy(long long n, double a, const double *x, double *y, cudaStream_t st);
 int scal(long long n, double a, const double *x, double *y, cudaStream_t st);
 int extract_diag(int nb, int bs, const int *Ap, const int *Aj, const double *Ax, double *diag, cudaStream_t st);
