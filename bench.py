@@ -894,7 +894,7 @@ def reference_problem(pyamg, args):
         A, B = A.to_scipy(), B.numpy()
         np.random.seed(0)
         gs = ('gauss_seidel', {'sweep': 'symmetric'})
-        ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=500, improve_candidates=None)
+        ml = pyamg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=500)
     b = np.random.rand(ml.levels[0].A.shape[0])
     return ml, b, colours
 

@@ -314,6 +314,13 @@ int b200amg_vertex_coloring_mis_host(int n, const int *Ap_host, const int *Aj_ho
 int b200amg_vertex_coloring_jones_plassmann_host(int n, const int *Ap, const int *Aj, int *color,
                                                  const double *weights);
 int b200amg_vertex_coloring_ldf_host(int n, const int *Ap, const int *Aj, int *color, const double *weights);
+/* Dependency levels ("wavefronts") of the lexicographic sweep of amg_core.gauss_seidel / bsr_gauss_seidel /
+ * block_gauss_seidel (pyamg/amg_core/relaxation.h:33-62, :89-173, :753-806) over the rows (block rows) of the pattern
+ * (Ap, Aj): level[i] = the parallel step at which row i sees exactly the operands of the sequential sweep.  Rows grouped
+ * by level (ascending inside a level) + the level offsets are an (Id, color_ptr_host) pair for
+ * b200amg_gauss_seidel_indexed / b200amg_bsr_gauss_seidel / b200amg_block_gauss_seidel: the lexicographic sweep, forward
+ * or backward, bit for bit, one launch per level instead of one thread.  Host arrays; returns the number of levels. */
+int b200amg_gs_wavefronts_host(int n, const int *Ap_host, const int *Aj_host, int *level_host);
 /* amg_core.standard_aggregation, pyamg/amg_core/smoothed_aggregation.h:121-221: returns the
  * number of aggregates; agg[i] = aggregate of node i or -1; roots[k] = seed node of k */
 int b200amg_standard_aggregation_host(int n, const int *Ap_host, const int *Aj_host, int *agg_host,

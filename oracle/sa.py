@@ -228,13 +228,14 @@ def blocksize(A):
 def smoothed_aggregation_hierarchy(A, B=None, theta=0.0, smooth_omega=4.0 / 3.0,
                                    presmoother=('jacobi', {'omega': 4.0 / 3.0}),
                                    postsmoother=('jacobi', {'omega': 4.0 / 3.0}),
-                                   max_levels=10, max_coarse=500, improve_candidates=None,
+                                   max_levels=10, max_coarse=500,
+                                   improve_candidates=[('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None],
                                    core=None):
     """aggregation.py:30-290 for symmetry='hermitian', strength=('symmetric',{'theta':theta}),
     aggregate='standard', smooth=('jacobi',{'omega':smooth_omega}); returns a list of
     oracle.multilevel.Level with RESOLVED smoother specs (omega/rho for Jacobi).
-    ``improve_candidates``: None, or the reference's forms (a spec or a per-level list, aggregation.py:38-41 -- the
-    reference DEFAULT is [('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None]) for the methods
+    ``improve_candidates``: the reference's default (aggregation.py:38-41), None, or the reference's other forms (a spec
+    or a per-level list) for the methods
     gauss_seidel / block_gauss_seidel: B <- relaxation on A B = 0, column by column (aggregation.py:311-319,
     util/utils.py:1140-1204)."""
     improve = _levelize(improve_candidates, max_levels)

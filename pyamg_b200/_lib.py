@@ -95,6 +95,7 @@ _SIGS = {
     'b200amg_vertex_coloring_jones_plassmann_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_vertex_coloring_ldf_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_naive_aggregation_host': (c_int, [c_int, p, p, p, p]),
+    'b200amg_gs_wavefronts_host': (c_int, [c_int, p, p, p]),
     'b200amg_standard_aggregation_host': (c_int, [c_int, p, p, p, p]),
     'b200amg_level_desc_size': (c_int, []),
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),

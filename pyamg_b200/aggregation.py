@@ -258,16 +258,16 @@ def smoothed_aggregation_solver(A, B=None, BH=None, symmetry='hermitian', streng
                                 aggregate='standard', smooth=('jacobi', {'omega': 4.0 / 3.0}),
                                 presmoother=('jacobi', {'omega': 4.0 / 3.0}),
                                 postsmoother=('jacobi', {'omega': 4.0 / 3.0}),
-                                improve_candidates=None, max_levels=10, max_coarse=500,
+                                improve_candidates=[('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None],
+                                max_levels=10, max_coarse=500,
                                 diagonal_dominance=False, keep=False, rho_override=None, **kwargs):
-    """Same call as the reference's smoothed_aggregation_solver for the options that have a
-    device path; unsupported options raise (no CPU fallback).  Deviations from the reference
-    DEFAULTS, both because the reference default is a lexicographic (sequential) block
-    Gauss-Seidel: `presmoother/postsmoother` default to Jacobi(4/3) and `improve_candidates`
-    to None.  The reference defaults are available by asking for them --
-    improve_candidates=[('block_gauss_seidel', {'sweep': 'symmetric', 'iterations': 4}), None],
-    presmoother=postsmoother=('block_gauss_seidel', {'sweep': 'symmetric'}) -- exact, but those sweeps are
-    lexicographic, i.e. one row after the other on the device.  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
+    """Same call as the reference's smoothed_aggregation_solver (pyamg/aggregation/aggregation.py:28-42) for the options
+    that have a device path; unsupported options raise (no CPU fallback).  `improve_candidates` defaults to the
+    reference's (4 symmetric block Gauss-Seidel sweeps on A B = 0 on the finest level): those sweeps are lexicographic,
+    and run level-parallel over their dependency wavefronts with the reference's bits (relaxation.wavefront_ordering).
+    One deviation from the reference DEFAULTS: `presmoother/postsmoother` default to Jacobi(4/3) instead of the
+    lexicographic block Gauss-Seidel (available by asking for it:
+    presmoother=postsmoother=('block_gauss_seidel', {'sweep': 'symmetric'})).  `rho_override` (list of per-level (rho_smooth, rho_relax) or None) lets the parity
     tests feed the reference's spectral-radius estimates; a fed estimate still draws (and drops) the start vector the
     estimate would have drawn, so that a seeded setup leaves the global numpy RNG where the reference leaves it."""
     if symmetry not in ('hermitian', 'symmetric'):

@@ -99,6 +99,20 @@ def vertex_coloring_mis(num_rows, Ap, Aj, x):
     return K
 
 
+def gs_wavefronts(num_rows, Ap, Aj, level):
+    """dependency levels of the lexicographic Gauss-Seidel sweep over the pattern (host int32 arrays); returns the
+    number of levels.  No reference counterpart: it is what lets relaxation.h:33-62 run in parallel with its bits."""
+    Ap = np.ascontiguousarray(Ap, np.intc)
+    Aj = np.ascontiguousarray(Aj, np.intc)
+    if level.dtype != np.intc or not level.flags.c_contiguous:
+        raise TypeError('level must be a contiguous int32 numpy array')
+    lib = _lib.load()
+    K = lib.b200amg_gs_wavefronts_host(int(num_rows), Ap.ctypes.data, Aj.ctypes.data, level.ctypes.data)
+    if K < 0:
+        raise _lib.B200AmgError(lib.b200amg_last_error().decode())
+    return K
+
+
 def naive_aggregation(n_row, Ap, Aj, x, y):
     """smoothed_aggregation.h:244-277 (host arrays); x receives 0-based aggregate numbers (the reference's are 1-based
     and its Python wrapper subtracts 1, aggregate.py:174-176); returns the number of aggregates"""

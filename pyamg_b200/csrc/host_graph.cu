@@ -267,3 +267,31 @@ extern "C" int b200amg_naive_aggregation_host(int n, const int *Ap, const int *A
     }
     return nagg;
 }
+
+// ---- wavefronts of a lexicographic Gauss-Seidel sweep (amg_core.gauss_seidel / bsr_gauss_seidel / block_gauss_seidel,
+// pyamg/amg_core/relaxation.h:33-62, :89-173, :753-806).  The sequential sweep over rows 0, 1, ..., n-1 relaxes row i
+// with the NEW values of the rows j < i it references and the OLD values of the rows j > i.  level[i] = the earliest
+// parallel step at which row i can run with exactly those operands: after every referenced row j < i (true dependence)
+// and after every row j < i that references i (it must read x_i before i overwrites it).  Rows of one level are then
+// independent of each other; running the levels in ascending order gives the bits of the forward sweep, in descending
+// order those of the backward sweep.  One ascending pass; returns the number of levels.
+extern "C" int b200amg_gs_wavefronts_host(int n, const int *Ap, const int *Aj, int *level)
+{
+    if (n < 0) return set_err(B200AMG_EINVAL, "gs_wavefronts: n < 0");
+    std::vector<int> pending(n > 0 ? n : 1, 0);          // lower bound handed forward by rows that read x_i
+    int nlev = 0;
+    for (int i = 0; i < n; ++i) {
+        int L = pending[i];
+        for (int p = Ap[i]; p < Ap[i + 1]; ++p) {
+            const int j = Aj[p];
+            if (j >= 0 && j < i) L = std::max(L, level[j] + 1);
+        }
+        level[i] = L;
+        for (int p = Ap[i]; p < Ap[i + 1]; ++p) {
+            const int j = Aj[p];
+            if (j > i && j < n) pending[j] = std::max(pending[j], L + 1);
+        }
+        nlev = std::max(nlev, L + 1);
+    }
+    return nlev;
+}

@@ -44,18 +44,27 @@ struct __align__(16) RowPatEntry {
     double v;
     int off, len;                    // column offset (Aj - row); len = entries of the whole pattern
 };
+constexpr int RP_TILE_MAXSEG = 4;    // contiguous x segments a chunk of rows gathers from (rowpat_tile.cu)
+constexpr int RP_TILE_LEN = 8;       // == RP_LEN
 struct RowPat {
     unsigned char *codes = nullptr;  // [n]
     RowPatEntry *table = nullptr;    // [npat * 8]
     int npat = 0, n = 0, far = 0;    // far = largest column offset in the table
     int common_len = 0;              // entries of the typical (middle) row
+    // plan of the TMA-staged sweep (rowpat_tile.cu), made from the typical row's pattern; tile_ok == false: not eligible
+    bool tile_ok = false;
+    int tile_len = 0, nseg = 0, xs_elems = 0;
+    int seg_lo[RP_TILE_MAXSEG] = {0, 0, 0, 0}, seg_len[RP_TILE_MAXSEG] = {0, 0, 0, 0}, seg_base[RP_TILE_MAXSEG] = {0, 0, 0, 0};
+    int sbase[RP_TILE_LEN] = {0, 0, 0, 0, 0, 0, 0, 0};
+    double cval[RP_TILE_LEN] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned short *tmask = nullptr; // [256] device: presence mask of every pattern relative to the typical one
     bool ok() const { return codes != nullptr; }
 };
 int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const double *Ax, RowPat *out, cudaStream_t st);
 void rowpat_free(RowPat *r);
 int rowpat_op(int op, const RowPat &r, const StreamArgs &a, cudaStream_t st);
-// two rows in flight per thread (rowpat_ilp2.cu; B200AMG_ROWPAT_ILP2=1): -1 = not eligible, else the launch status
-int rowpat_ilp2_op(int op, const RowPat &r, const StreamArgs &a, int common_len, cudaStream_t st);
+// TMA-staged sweep (rowpat_tile.cu): -1 = not eligible (rowpat.cu's kernel runs), else the launch status
+int rowpat_tile_op(int op, const RowPat &r, const StreamArgs &a, cudaStream_t st);
 
 int rows_per_cta_for(long long nnz, int nrows);
 // persistent TMA pipeline (csr_pipe.cu): returns 1 when it took the launch (*rc = status), 0 when

@@ -124,10 +124,24 @@ __global__ void __launch_bounds__(256) rowpat_encode_kernel(int n_row, const int
     }
 }
 
+void rowpat_tile_plan(RowPat *r, const std::vector<RowPatEntry> &ht, int common);   // rowpat_tile.cu
+
+// hist[p] = rows with pattern p (the most frequent pattern is the operator's interior stencil)
+__global__ void __launch_bounds__(256) rowpat_hist_kernel(int n, const unsigned char *__restrict__ codes, unsigned *hist)
+{
+    __shared__ unsigned s_h[256];
+    s_h[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) atomicAdd(&s_h[codes[i]], 1u);
+    __syncthreads();
+    if (s_h[threadIdx.x]) atomicAdd(&hist[threadIdx.x], s_h[threadIdx.x]);
+}
+
 void rowpat_free(RowPat *r)
 {
     if (r->codes) cudaFree(r->codes);
     if (r->table) cudaFree(r->table);
+    if (r->tmask) cudaFree(r->tmask);
     *r = RowPat();
 }
 
@@ -208,14 +222,31 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
             if (good && mid < npat)
             {
                 for (int q = 0; q < RP_LEN; ++q) out->far = std::max(out->far, ht[(size_t)mid * RP_LEN + q].off);
-                out->common_len = ht[(size_t)mid * RP_LEN].len & 0xff;     // row length of that typical row (rowpat_ilp2.cu)
+                out->common_len = ht[(size_t)mid * RP_LEN].len & 0xff;     // row length of that typical row
             }
-        }
-        if (good) {
-            out->codes = codes;
-            out->table = table;
-            out->npat = npat;
-            out->n = n_row;
+            if (good) {
+                out->codes = codes;
+                out->table = table;
+                out->npat = npat;
+                out->n = n_row;
+                // segments / masks of the TMA-staged sweep, made from the MOST FREQUENT pattern (the middle row of a
+                // structured grid sits on two faces)
+                unsigned *d_hist = nullptr, h_hist[256];
+                if (cudaMalloc(&d_hist, sizeof(h_hist)) == cudaSuccess) {
+                    cudaMemsetAsync(d_hist, 0, sizeof(h_hist), st);
+                    rowpat_hist_kernel<<<grid, 256, 0, st>>>(n_row, codes, d_hist);
+                    ++g_launches;
+                    if (cudaMemcpyAsync(h_hist, d_hist, sizeof(h_hist), cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                        cudaStreamSynchronize(st) == cudaSuccess) {
+                        int common = 0;
+                        for (int p2 = 1; p2 < npat; ++p2)
+                            if (h_hist[p2] > h_hist[common]) common = p2;
+                        rowpat_tile_plan(out, ht, common);
+                    }
+                    cudaGetLastError();
+                    cudaFree(d_hist);
+                }
+            }
         }
     }
     if (d_known) cudaFree(d_known);
@@ -475,11 +506,10 @@ int rowpat_op(int op, const RowPat &r, const StreamArgs &a0, cudaStream_t st)
     StreamArgs a = a0;
     if (op == OP_ADD && !a.b) a.b = a.y;              // y += A x: the kernels read the addend through b
     if (a.row_begin != 0 || a.row_end != r.n) return set_err(B200AMG_EINVAL, "rowpat_op: full row range only");
-    // experiment switch (off unless B200AMG_ROWPAT_ILP2=1): the two-rows-in-flight kernel for the ops it has; it
-    // declines (-1) small or unusual operators and the default kernel below runs
-    static const bool ilp2 = [] { const char *e = getenv("B200AMG_ROWPAT_ILP2"); return e && e[0] == '1'; }();
-    if (ilp2) {
-        const int rc = rowpat_ilp2_op(op, r, a, r.common_len, st);
+    // the TMA-staged sweep takes the launch when the operator and the vectors qualify (B200AMG_ROWPAT_TILE=0: A/B switch)
+    static const bool tile = [] { const char *e = getenv("B200AMG_ROWPAT_TILE"); return !(e && e[0] == '0'); }();
+    if (tile) {
+        const int rc = rowpat_tile_op(op, r, a, st);
         if (rc >= 0) return rc;
     }
     switch (op) {

@@ -63,9 +63,34 @@ def jacobi(A, x, b, iterations=1, omega=1.0):
             amg_core.bsr_jacobi(A.indptr, A.indices, A.data, x, b, temp, 0, n // R, 1, R, [omega])
 
 
+WAVEFRONT_MIN_ROWS = 1024        # below this a lexicographic sweep stays on one thread block
+WAVEFRONT_MIN_WIDTH = 32         # average rows per dependency level for the level-parallel form to pay
+
+
+def wavefront_ordering(A):
+    """Rows (block rows) of the LEXICOGRAPHIC Gauss-Seidel sweep grouped by dependency level (amg_core.gs_wavefronts),
+    cached on the matrix: -> (indices int32 device tensor, level_ptr host int32) or None when the sweep is too narrow
+    (small or densely coupled matrices: one level per few rows) to beat the sequential kernel.  Feeding the pair to the
+    indexed kernels as a colour ordering runs the reference's sweep order, bit for bit, one launch per level."""
+    cached = getattr(A, '_gs_wavefront', False)
+    if cached is not False:
+        return cached
+    n = A.n_brow
+    out = None
+    if n >= WAVEFRONT_MIN_ROWS:
+        level = np.empty(n, dtype=np.intc)
+        nlev = amg_core.gs_wavefronts(n, A.indptr.cpu().numpy(), A.indices.cpu().numpy(), level)
+        if n >= WAVEFRONT_MIN_WIDTH * nlev:
+            idx, ptr = color_ordering(level)
+            out = (torch.from_numpy(idx).to(A.data.device), ptr)
+    A._gs_wavefront = out
+    return out
+
+
 def gauss_seidel(A, x, b, iterations=1, sweep='forward', indices=None, color_ptr=None):
-    """Lexicographic sweep (sequential on the device) unless a colour ordering
-    (`indices`, `color_ptr` over rows / block rows) is given."""
+    """Lexicographic sweep unless a colour ordering (`indices`, `color_ptr` over rows / block rows) is given.  The
+    lexicographic sweep runs level-parallel over its dependency wavefronts when the matrix is large and sparse enough
+    (wavefront_ordering; same bits), else sequentially on one thread block."""
     A, x, b = make_system(A, x, b, formats=['csr', 'bsr'])
     if A.format == 'csr':
         bs = 1
@@ -74,6 +99,10 @@ def gauss_seidel(A, x, b, iterations=1, sweep='forward', indices=None, color_ptr
         if R != C:
             raise ValueError('BSR blocks must be square')
         bs = R
+    if indices is None and color_ptr is None:
+        wf = wavefront_ordering(A)
+        if wf is not None:
+            indices, color_ptr = wf
     if sweep == 'symmetric':
         for _ in range(iterations):
             gauss_seidel(A, x, b, 1, 'forward', indices, color_ptr)
@@ -154,6 +183,10 @@ def block_gauss_seidel(A, x, b, iterations=1, sweep='forward', blocksize=1, Dinv
     A, x, b, bs, Tx = _block_args(A, x, b, blocksize, Dinv)
     if indices is not None and not isinstance(indices, torch.Tensor):
         indices = torch.from_numpy(np.ascontiguousarray(indices, dtype='intc')).to(x.device)
+    if indices is None and color_ptr is None:
+        wf = wavefront_ordering(A)                      # the lexicographic sweep, level-parallel (same bits)
+        if wf is not None:
+            indices, color_ptr = wf
     if sweep == 'symmetric':
         for _ in range(iterations):
             block_gauss_seidel(A, x, b, 1, 'forward', bs, Dinv, indices, color_ptr)
@@ -210,7 +243,8 @@ def color_ordering(colors):
     """Rows grouped by colour, ascending inside each colour -> (indices int32[n], color_ptr int32[K+1])."""
     colors = np.asarray(colors)
     K = int(colors.max()) + 1 if len(colors) else 0
-    idx = np.argsort(colors, kind='stable').astype(np.intc)
+    key = colors.astype(np.uint16) if 0 < K <= 65536 else colors      # 16-bit keys: numpy's stable sort is a radix sort
+    idx = np.argsort(key, kind='stable').astype(np.intc)
     ptr = np.zeros(K + 1, dtype=np.intc)
     np.cumsum(np.bincount(colors, minlength=K), out=ptr[1:])
     return idx, ptr

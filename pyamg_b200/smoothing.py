@@ -101,7 +101,13 @@ def _resolve(spec, lvl):
             raise TypeError('jacobi: unexpected options %r' % sorted(kw))
         return _Smoother(1, omega, iters, name='jacobi')
     if name == 'gauss_seidel':
-        return _Smoother(3, 1.0, kw.pop('iterations', 1), kw.pop('sweep', 'forward'), name='gauss_seidel')
+        iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
+        if kw:
+            raise TypeError('gauss_seidel: unexpected options %r' % sorted(kw))
+        wf = relaxation.wavefront_ordering(A)           # the lexicographic sweep over its dependency levels: same bits
+        if wf is not None:
+            return _Smoother(2, 1.0, iters, sweep, wf[0], np.ascontiguousarray(wf[1], dtype=np.intc), name='gauss_seidel')
+        return _Smoother(3, 1.0, iters, sweep, name='gauss_seidel')
     if name in ('gauss_seidel_indexed', 'multicolor_gauss_seidel'):
         iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
         if name == 'multicolor_gauss_seidel':
@@ -135,7 +141,10 @@ def _resolve(spec, lvl):
         iters, sweep = kw.pop('iterations', 1), kw.pop('sweep', 'forward')
         if kw:
             raise TypeError('%s: unexpected options %r' % (name, sorted(kw)))
-        if name == 'block_gauss_seidel':                # the reference's lexicographic order: sequential on the device
+        if name == 'block_gauss_seidel':                # the reference's lexicographic order
+            wf = relaxation.wavefront_ordering(A)       # ... level-parallel where the matrix allows it (same bits)
+            if wf is not None:
+                return _Smoother(6, 1.0, iters, sweep, wf[0], np.ascontiguousarray(wf[1], dtype=np.intc), name=name, Dinv=Dinv)
             return _Smoother(7, 1.0, iters, sweep, name=name, Dinv=Dinv)
         if not hasattr(lvl, '_mc_order'):
             idx, ptr = relaxation.color_ordering(relaxation.vertex_coloring(A, 'MIS'))

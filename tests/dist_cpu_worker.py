@@ -107,7 +107,7 @@ def main():
         A = poisson3d(grid); A.sort_indices()
         np.random.seed(5)
         jac = ('jacobi', {'omega': 4.0 / 3.0})
-        host = osa.smoothed_aggregation_hierarchy(A, presmoother=jac, postsmoother=jac, max_coarse=12, core=oracle.port)
+        host = osa.smoothed_aggregation_hierarchy(A, presmoother=jac, postsmoother=jac, max_coarse=12, core=oracle.port, improve_candidates=None)
         b = np.random.rand(A.shape[0])
         levels_desc = []
         for L in host[:-1]:

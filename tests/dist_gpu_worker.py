@@ -24,7 +24,7 @@ def main():
         A = amg.gallery.poisson((grid * world, grid, grid))
         np.random.seed(2)
         jac = ('jacobi', {'omega': 4.0 / 3.0})
-        ml = amg.smoothed_aggregation_solver(A, presmoother=jac, postsmoother=jac, max_coarse=40)
+        ml = amg.smoothed_aggregation_solver(A, presmoother=jac, postsmoother=jac, max_coarse=40, improve_candidates=None)
         b = np.random.rand(A.shape[0])
     S = DistributedSolver.from_ml(ml, agglomerate_below=thresh)
     res = []

@@ -154,9 +154,9 @@ def test_block_path_builds_the_reference_hierarchy(host_amg, golden_dir):
     A, B = levels[0].A, ex['B']
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     rhos = [(l.rho_smooth, None) for l in ref[:-1]]
-    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos, improve_candidates=None)
     assert len(ml.levels) == len(levels) == 3
     for k, (m, r) in enumerate(zip(ml.levels, levels)):
         for nm in ('A', 'P', 'R'):
@@ -175,20 +175,20 @@ def test_block_path_default_candidates_and_argument_checks(host_amg, golden_dir)
     assert A.format == 'bsr' and A.blocksize == (2, 2)
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     rhos = [(l.rho_smooth, None) for l in ref[:-1]]
-    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos, improve_candidates=None)
     assert len(ml.levels) == len(ref)
     for k, (m, r) in enumerate(zip(ml.levels, ref)):
         for nm in ('A', 'P', 'R'):
             if getattr(r, nm, None) is not None:
                 assert same(getattr(m, nm).to_scipy(), getattr(r, nm)), (k, nm)
     with pytest.raises(NotImplementedError):
-        amg.smoothed_aggregation_solver(A, strength=None)
+        amg.smoothed_aggregation_solver(A, strength=None, improve_candidates=None)
     with pytest.raises(NotImplementedError):
-        amg.smoothed_aggregation_solver(sp.csr_matrix(A), np.ones((A.shape[0], 2)))
+        amg.smoothed_aggregation_solver(sp.csr_matrix(A), np.ones((A.shape[0], 2)), improve_candidates=None)
     with pytest.raises(ValueError):
-        amg.smoothed_aggregation_solver(A, np.ones((A.shape[0] + 2, 3)))
+        amg.smoothed_aggregation_solver(A, np.ones((A.shape[0] + 2, 3)), improve_candidates=None)
 
 
 def test_bench_config4_host_pieces(host_amg, golden_dir):
@@ -203,10 +203,10 @@ def test_bench_config4_host_pieces(host_amg, golden_dir):
     A, B = amg.gallery.linear_elasticity_tets(7, device=torch.device('cpu'))
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)             # spectral radii from the oracle's setup: the device Arnoldi needs the GPU's dot / axpy
-    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
     ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=10,
-                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]], improve_candidates=None)
     assert [l.A.blocksize for l in ml.levels] == [(3, 3), (6, 6), (6, 6)]
     sm = ml.levels[0].presmoother
     assert sm.kind == 2 and sm.indices.numel() == ml.levels[0].A.n_brow          # block rows, not scalar rows
@@ -280,10 +280,10 @@ def test_block_path_with_a_strength_threshold(host_amg, golden_dir):
     A, B, theta = levels[0].A, ex['B'], float(ex['theta'])
     jac = ('jacobi', {'omega': 4.0 / 3.0})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10, improve_candidates=None)
     gs = ('gauss_seidel', {'sweep': 'symmetric'})      # smoothers are not the subject here (Jacobi needs the device Arnoldi)
     ml = amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': theta}), presmoother=gs, postsmoother=gs,
-                                         max_coarse=10, rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+                                         max_coarse=10, rho_override=[(l.rho_smooth, None) for l in ref[:-1]], improve_candidates=None)
     assert len(ml.levels) == len(levels) == 4
     for k, (m, r) in enumerate(zip(ml.levels, levels)):
         for nm in ('A', 'P', 'R'):
@@ -294,7 +294,7 @@ def test_block_path_with_a_strength_threshold(host_amg, golden_dir):
     dropped = [l.A.nblocks - amg.aggregation.symmetric_strength_of_connection(l.A, theta).nnz for l in ml.levels[:-1]]
     assert min(dropped) >= 0 and max(dropped) > 0, dropped
     with pytest.raises(ValueError):
-        amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': -1.0}))
+        amg.smoothed_aggregation_solver(A, B, strength=('symmetric', {'theta': -1.0}), improve_candidates=None)
 
 
 @pytest.mark.parametrize('name,kw', [('sa_poisson3d_12', {}), ('sa_aniso2d_40_theta005', {'strength': ('symmetric', {'theta': 0.05})})])
@@ -308,9 +308,9 @@ def test_scalar_sa_path_builds_the_reference_hierarchy(host_amg, golden_dir, nam
     mc = {'sa_poisson3d_12': 20}.get(name, 10)
     np.random.seed(0)
     ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), theta=kw.get('strength', (0, {'theta': 0.0}))[1]['theta'],
-                                             presmoother=jac, postsmoother=jac, max_coarse=mc)
+                                             presmoother=jac, postsmoother=jac, max_coarse=mc, improve_candidates=None)
     rhos = [(l.rho_smooth, l.A.rho_D_inv) for l in ref[:-1]]
-    ml = amg.smoothed_aggregation_solver(levels[0].A, presmoother=jac, postsmoother=jac, max_coarse=mc, rho_override=rhos, **kw)
+    ml = amg.smoothed_aggregation_solver(levels[0].A, presmoother=jac, postsmoother=jac, max_coarse=mc, rho_override=rhos, **kw, improve_candidates=None)
     assert len(ml.levels) == len(levels)
     for k, (m, r) in enumerate(zip(ml.levels, levels)):
         for nm in ('A', 'P', 'R'):
@@ -383,10 +383,10 @@ def test_config4_in_miniature_end_to_end(host_amg, golden_dir):
     A, B = amg.gallery.linear_elasticity_tets(7, device=torch.device('cpu'))
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.to_scipy(), B.numpy(), presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
     ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=10,
-                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]])
+                                         rho_override=[(l.rho_smooth, None) for l in ref[:-1]], improve_candidates=None)
     rng = np.random.RandomState(1)
     bh = rng.rand(A.shape[0])
     levels = bench.host_levels(ml)

@@ -289,7 +289,7 @@ def test_block_sa_hierarchy_equals_reference_fixture(emu, golden_dir):
     A, B = levels[0].A, ex['B']
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     assert len(ref) == len(levels) == 3
     K2 = B.shape[1]
     cur_A, cur_B = A.copy(), B
@@ -545,99 +545,6 @@ def emu_setup():
         f = getattr(lib, name)
         f.restype, f.argtypes = _lib._SIGS[name]
     return lib
-
-
-# ---- the two-rows-in-flight row-pattern kernel (csrc/rowpat_ilp2.cu, off by default: B200AMG_ROWPAT_ILP2=1) ----------
-def rowpat_layout(A):
-    """host construction of the row-pattern layout of csrc/rowpat.cu: per row the number of its (offset, value)
-    sequence; table[pattern][8] of (v, off, len | diagonal mask << 8)"""
-    n = A.shape[0]
-    pats, codes = {}, np.empty(n, np.uint8)
-    table = []
-    for i in range(n):
-        s_, e_ = A.indptr[i], A.indptr[i + 1]
-        key = (tuple(int(j) - i for j in A.indices[s_:e_]), tuple(float(v) for v in A.data[s_:e_]))
-        if key not in pats:
-            assert len(key[0]) <= 8 and len(pats) < 255
-            pats[key] = len(pats)
-            ln = len(key[0])
-            dm = sum((1 << q) for q in range(ln) if key[0][q] == 0)
-            for q in range(8):
-                table.append((key[1][q] if q < ln else 0.0, key[0][q] if q < ln else 0, ln | (dm << 8)))
-        codes[i] = pats[key]
-    tab = np.array(table, dtype=np.dtype([('v', '<f8'), ('off', '<i4'), ('len', '<i4')]))
-    mid = A.indptr[n // 2]
-    far = int(max(A.indices[mid:A.indptr[n // 2 + 1]] - n // 2))
-    return codes, tab, len(pats), far
-
-
-@pytest.fixture(scope='module')
-def emu_ilp2():
-    if shutil.which('g++') is None:
-        pytest.skip('g++ not available')
-    src = os.path.join(ROOT, 'pyamg_b200', 'csrc', 'rowpat_ilp2.cu')
-    out = os.path.join(EMU, '_build', 'libemu_rowpat_ilp2.so')
-    deps = [src, os.path.join(EMU, 'cuda_runtime.h'), os.path.join(EMU, 'emu_dyn_smem.cpp'), os.path.join(ROOT, 'pyamg_b200', 'csrc', 'internal.cuh')]
-    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
-        os.makedirs(os.path.dirname(out), exist_ok=True)
-        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-DB200_TEST_HOOKS',
-                        '-I', EMU, '-I', os.path.join(ROOT, 'pyamg_b200', 'csrc'), '-x', 'c++', src,
-                        os.path.join(EMU, 'emu_globals.cpp'), os.path.join(EMU, 'emu_dyn_smem.cpp'), '-o', out], check=True)
-    lib = ctypes.CDLL(out)
-    lib.b200amg_test_rowpat_ilp2.restype = c_int
-    lib.b200amg_test_rowpat_ilp2.argtypes = [c_int, c_int, c_int, c_int, vp, vp, c_int, vp, vp, vp, c_dbl]
-    return lib
-
-
-def ilp2_fast_warps(lens, common):
-    """(warp, pair) slots of the launch whose 64 rows all have the common length: these take the two-rows-in-flight path"""
-    n = len(lens)
-    fast = 0
-    for base in range(0, n, 512):                              # a pair slot = rows [base, base+256) and [base+256, base+512)
-        for w in range(8):
-            ra = np.arange(base + 32 * w, base + 32 * w + 32)
-            rb = ra + 256
-            if rb[-1] < n and np.all(lens[ra] == common) and np.all(lens[rb] == common):
-                fast += 1
-    return fast
-
-
-@pytest.mark.parametrize('grid,common', [((8, 8, 70), 7), ((13, 12, 11), 7), ((40, 70), 5)])
-def test_prepared_rowpat_ilp2_kernel_is_bit_identical(emu_ilp2, grid, common):
-    """round 2's first kernel candidate, checked before it sees hardware: matvec, residual, Jacobi (CSR and BSR(1,1)
-    association) on Poisson stencils -- interior warps take the two-rows-in-flight path, boundary warps the predicated
-    one -- against scipy's csr_matvec and the reference's compiled jacobi / bsr_jacobi"""
-    T = [sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(g, g)) for g in grid]
-    A = None
-    for d in range(len(grid)):
-        term = None
-        for e in range(len(grid)):
-            f = T[e] if e == d else sp.identity(grid[e])
-            term = f if term is None else sp.kron(term, f)
-        A = term if A is None else A + term
-    A = sp.csr_matrix(A)
-    A.sort_indices()
-    n = A.shape[0]
-    codes, tab, npat, far = rowpat_layout(A)
-    fast = ilp2_fast_warps(np.diff(A.indptr), common)
-    assert (fast > 0) == (grid[-1] >= 64), fast                # the long-line grids exercise the fast path, the small one the other
-    rng = np.random.RandomState(len(grid))
-    x, b = rng.rand(n), rng.rand(n)
-    OP_MATVEC, OP_RESIDUAL, OP_JACOBI, OP_JACOBI_BSR1 = 0, 2, 4, 5
-    Ap, Aj = i32(A.indptr), i32(A.indices)
-
-    def run(op, omega=0.0):
-        y = np.full(n, np.nan)
-        assert emu_ilp2.b200amg_test_rowpat_ilp2(op, n, npat, far, P(codes), tab.ctypes.data, common, P(x), P(b), P(y), omega) == 0
-        return y
-    assert np.array_equal(run(OP_MATVEC), A * x)
-    assert np.array_equal(run(OP_RESIDUAL), b - A * x)
-    want, temp = x.copy(), np.empty(n)
-    CORE.jacobi(Ap, Aj, A.data, want, b, temp, 0, n, 1, np.array([0.7]))
-    assert np.array_equal(run(OP_JACOBI, 0.7), want)
-    want = x.copy()
-    CORE.bsr_jacobi(Ap, Aj, A.data, want, b, temp, 0, n, 1, 1, np.array([0.7]))
-    assert np.array_equal(run(OP_JACOBI_BSR1, 0.7), want)
 
 
 # ---- the BSR solve-phase kernels (csrc/bsr.cu; pinned on the GPU in round 1) for the CPU harness -------------------

@@ -164,6 +164,66 @@ def test_multicolor_gauss_seidel_bit_exact(amg, name, make):
     assert np.array_equal(xd.cpu().numpy(), xo)
 
 
+def nonsymmetric_band(rng, n=6000):
+    """rows reference 2-3 columns within +-40 of the diagonal, pattern NOT symmetric: a row may be read by an earlier
+    row that it does not reference itself (the anti-dependence of the wavefront levels)"""
+    rows = np.repeat(np.arange(n), 3)
+    cols = np.clip(rows + rng.randint(-40, 41, rows.size), 0, n - 1)
+    A = sp.coo_matrix((rng.rand(rows.size) - 0.5, (rows, cols)), shape=(n, n)).tocsr()
+    A = sp.csr_matrix(A + sp.diags(np.full(n, 3.0)))
+    A.sort_indices()
+    return A
+
+
+@pytest.mark.parametrize('name,make', [('poisson3d_17', lambda rng: poisson3d(17)), ('lap2d_90', lambda rng: lap2d(90)),
+                                       ('nonsymmetric_band', nonsymmetric_band)])
+def test_lexicographic_gauss_seidel_over_wavefronts_bit_exact(amg, monkeypatch, name, make):
+    """amg_core.gauss_seidel (relaxation.h:33-62) run level-parallel over the dependency wavefronts of the sweep
+    (relaxation.wavefront_ordering): the bits of the sequential sweep, forward, backward and symmetric"""
+    monkeypatch.setattr(amg.relaxation, 'WAVEFRONT_MIN_WIDTH', 1)
+    rng = np.random.RandomState(8)
+    A = make(rng)
+    n = A.shape[0]
+    x0, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    wf = amg.relaxation.wavefront_ordering(dA)
+    assert wf is not None and int(wf[1][-1]) == n and len(wf[1]) - 1 < n
+    lvl = np.empty(n, dtype=np.intc)
+    lvl[wf[0].cpu().numpy()] = np.repeat(np.arange(len(wf[1]) - 1), np.diff(wf[1]))
+    # definition of a valid schedule: every coupled pair (i, j), i < j, in either direction, has level[i] < level[j]
+    C = sp.coo_matrix(A + A.T)
+    m = C.row < C.col
+    assert np.all(lvl[C.row[m]] < lvl[C.col[m]])
+    for sweep in ('forward', 'backward', 'symmetric'):
+        xo = x0.copy(); orx.gauss_seidel(A, xo, b, iterations=2, sweep=sweep, core=oracle.port)
+        xd = dev(x0.copy())
+        amg.relaxation.gauss_seidel(dA, xd, dev(b), iterations=2, sweep=sweep)
+        assert np.array_equal(xd.cpu().numpy(), xo), sweep
+
+
+@pytest.mark.parametrize('bs', [3, 6])
+def test_lexicographic_block_sweeps_over_wavefronts_bit_exact(amg, bs):
+    """bsr_gauss_seidel (relaxation.h:89-173) and block_gauss_seidel (:753-806) in their lexicographic order through the
+    wavefront schedule of the block graph"""
+    rng = np.random.RandomState(9)
+    G = poisson3d(12)                                                     # 1728 block rows, 34 wavefronts
+    Bk = rng.rand(bs, bs); Bk = Bk @ Bk.T + bs * np.eye(bs)
+    A = sp.kron(G, Bk).tobsr(blocksize=(bs, bs)); A.sort_indices()
+    n = A.shape[0]
+    x0, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)
+    assert amg.relaxation.wavefront_ordering(dA) is not None
+    for sweep in ('forward', 'backward', 'symmetric'):
+        xo = x0.copy(); orx.gauss_seidel(A, xo, b, sweep=sweep, core=oracle.port)
+        xd = dev(x0.copy()); amg.relaxation.gauss_seidel(dA, xd, dev(b), sweep=sweep)
+        assert np.array_equal(xd.cpu().numpy(), xo), sweep
+    Dinv = amg.relaxation.get_block_diag_inverse(dA, bs)
+    xo = x0.copy()
+    orx.block_gauss_seidel(A, xo, b, Dinv=Dinv.cpu().numpy(), blocksize=bs, sweep='symmetric', core=oracle.port)
+    xd = dev(x0.copy()); amg.relaxation.block_gauss_seidel(dA, xd, dev(b), blocksize=bs, sweep='symmetric', Dinv=Dinv)
+    assert np.array_equal(xd.cpu().numpy(), xo)
+
+
 def test_reference_golden_vectors_on_device(amg):
     """pyamg/relaxation/tests/test_relaxation.py:139-188, :291-402 through the device path"""
     rx, D = amg.relaxation, amg.DevMat.from_scipy
@@ -303,7 +363,23 @@ def stencil_many_row_patterns(rng):
     return A
 
 
+def lap2d_periodic(m):
+    """5-point stencil on a torus: the wrap-around rows have column offsets no interior row has, so in the row-pattern
+    layout they are NOT the common pattern with entries missing (per-row global path of the TMA-staged sweep)"""
+    S = sp.diags([np.ones(m - 1), np.ones(m - 1), [1.0], [1.0]], [-1, 1, m - 1, -(m - 1)], shape=(m, m), format='csr')
+    I = sp.eye(m)
+    A = sp.csr_matrix(4.0 * sp.eye(m * m) - sp.kron(S, I) - sp.kron(I, S))
+    A.sort_indices()
+    return A
+
+
+# lap2d_301 / poisson3d_41 / lap1d: odd offsets, an odd number of rows (the last element of a staged segment travels
+# on its own), 5-, 7- and 3-entry common patterns of the TMA-staged row-pattern sweep (csrc/rowpat_tile.cu)
 DICT_CASES = [('lap2d_800', lambda rng: lap2d(800), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('lap2d_301', lambda rng: lap2d(301), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('poisson3d_41', lambda rng: poisson3d(41), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('lap1d_100001', lambda rng: lap1d(100001), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('lap2d_periodic_300', lambda rng: lap2d_periodic(300), {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('few_valued_irregular', few_valued_irregular, {'0': 1, '1': 3, '2': 3, '3': 3}),
               ('stencil_with_oddities', stencil_with_oddities, {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('stencil_many_row_patterns', stencil_many_row_patterns, {'0': 1, '1': 1, '2': 1, '3': 1}),

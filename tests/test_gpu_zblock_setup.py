@@ -90,9 +90,9 @@ def test_block_sa_setup_matches_reference(amg, golden_dir):
     A, B = levels[0].A, ex['B']
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     rhos = [(l.rho_smooth, None) for l in ref[:-1]]
-    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    ml = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos, improve_candidates=None)
     assert len(ml.levels) == len(levels)
     for k, (m, r) in enumerate(zip(ml.levels, levels)):
         for nm in ('A', 'P', 'R'):
@@ -105,7 +105,7 @@ def test_block_sa_setup_matches_reference(amg, golden_dir):
     assert np.abs(x - ex['x']).max() <= RTOL * np.abs(ex['x']).max()
     # own spectral-radius estimate from the same seeded stream: an unconverged Krylov number, 1e-7
     np.random.seed(0)
-    ml2 = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ml2 = amg.smoothed_aggregation_solver(A, B, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     for m, r in zip(ml2.levels[:-1], ref[:-1]):
         assert abs(m.rho_smooth - r.rho_smooth) <= 1e-7 * r.rho_smooth
 
@@ -116,9 +116,9 @@ def test_block_sa_default_candidates_2d(amg, golden_dir):
     A = levels[0].A
     gs = ('gauss_seidel', {'sweep': 'symmetric'})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(A.copy(), None, presmoother=gs, postsmoother=gs, max_coarse=10, improve_candidates=None)
     rhos = [(l.rho_smooth, None) for l in ref[:-1]]
-    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos)
+    ml = amg.smoothed_aggregation_solver(A, presmoother=gs, postsmoother=gs, max_coarse=10, rho_override=rhos, improve_candidates=None)
     assert len(ml.levels) == len(ref)
     for k, (m, r) in enumerate(zip(ml.levels, ref)):
         for nm in ('A', 'P', 'R'):
@@ -249,10 +249,10 @@ def test_sa_setup_with_a_strength_threshold(amg, golden_dir, name):
     B, theta = ex.get('B'), float(ex['theta'])
     jac = ('jacobi', {'omega': 4.0 / 3.0})
     np.random.seed(0)
-    ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10)
+    ref = osa.smoothed_aggregation_hierarchy(levels[0].A.copy(), B, theta=theta, presmoother=jac, postsmoother=jac, max_coarse=10, improve_candidates=None)
     rhos = [(l.rho_smooth, l.A.rho_D_inv) for l in ref[:-1]]
     ml = amg.smoothed_aggregation_solver(levels[0].A, B, strength=('symmetric', {'theta': theta}), presmoother=jac,
-                                         postsmoother=jac, max_coarse=10, rho_override=rhos)
+                                         postsmoother=jac, max_coarse=10, rho_override=rhos, improve_candidates=None)
     assert len(ml.levels) == len(levels)
     for k, (m, r) in enumerate(zip(ml.levels, levels)):
         for nm in ('A', 'P', 'R'):
