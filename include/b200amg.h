@@ -101,6 +101,21 @@ int b200amg_dot(long long n, const double *x, const double *y, double *out_dev, 
  * array (nothing needs clearing: every cell read is written first by the same call), so calls that OVERLAP on the GPU
  * (different streams without ordering) race -- serialise them. */
 int b200amg_dot_noalloc(long long n, const double *x, const double *y, double *out_dev, void *stream);
+/* ---- preconditioned CG with its scalars on the device (pyamg/krylov/_cg.py:109-170; multilevel.py:381-422 accel='cg').
+ * `state`: >= 16 + capacity doubles on the device: [0] rz [1] pAp [2] rz_new [3] alpha [4] beta [5] tol (absolute, in
+ * the preconditioned norm sqrt(<r, z>)) [6] flag [7] iterations done [8] maxiter [9] capacity of the history
+ * [16 + k] sqrt(rz) after iteration k.  The caller writes [0], [5], [7] = 0, [8], [9], [16] and flag = 0, then enqueues
+ * per iteration: Ap = A p; b200amg_dot(Ap, p) -> state + 1; b200amg_pcg_scalars(state, 0); b200amg_pcg_update_xr;
+ * [r = b - A x on the iterations that recompute it]; z = M r; b200amg_dot(r, z) -> state + 2;
+ * b200amg_pcg_scalars(state, 1); b200amg_pcg_update_p.  flag: 0 running, 1 converged, 2 maxiter, -1 / -2 / -3 the
+ * reference's three abort conditions (indefinite matrix, indefinite / singular preconditioner).  After flag != 0
+ * every kernel is a no-op, so iterations may be enqueued ahead of the host's look at the flag. */
+int b200amg_pcg_scalars(double *state, int which, void *stream);
+/* x += alpha p; update_r != 0: r -= alpha Ap (separately rounded, numpy's `x += alpha * p`) */
+int b200amg_pcg_update_xr(long long n, const double *state, const double *p, const double *Ap, double *x, double *r,
+                          int update_r, void *stream);
+/* p = beta p + z */
+int b200amg_pcg_update_p(long long n, const double *state, const double *z, double *p, void *stream);
 /* y = a*x + y ; y = x ; x = 0 */
 int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream);
 /* y = a*x */
@@ -380,6 +395,15 @@ int b200amg_vcycle_create(int nlev, const b200amg_level_desc *levels_host, const
  * graph captured on first use for these (x, b) pointers. */
 int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph,
                        void *stream);
+/* x <- cycle(0, b): one cycle from a zero initial guess = the preconditioner application of
+ * multilevel_solver.aspreconditioner (pyamg/multilevel.py:274-314).  x need not be cleared; the first pre-smoothing
+ * Jacobi sweep from the known-zero guess is the bit-identical diagonal scaling (one pass over A_0 less). */
+int b200amg_vcycle_run_zero(void *handle, double *x, const double *b, int cycle_kind, int use_graph,
+                            void *stream);
+/* y = A_level x (op 0) or y = b - A_level x (op 2) in the layout the engine streams that operator in (A * p and
+ * b - A * x of pyamg/krylov/_cg.py around the cycle) */
+int b200amg_vcycle_apply_op(void *handle, int level, int op, const double *x, const double *b, double *y,
+                           void *stream);
 /* One UN-graphed cycle with a CUDA event after every operation: fills (host arrays, up to
  * max_ops entries) the operation code, its level and its device time in ms, in execution
  * order; *n_ops_host = entries written.  Synchronises the stream.  bench.py uses it for the

@@ -52,6 +52,9 @@ _SIGS = {
     'b200amg_halo_wait': (c_int, [p, c_int, p, c_longlong, p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
     'b200amg_dot_noalloc': (c_int, [c_longlong, p, p, p, p]),
+    'b200amg_pcg_scalars': (c_int, [p, c_int, p]),
+    'b200amg_pcg_update_xr': (c_int, [c_longlong, p, p, p, p, p, c_int, p]),
+    'b200amg_pcg_update_p': (c_int, [c_longlong, p, p, p, p]),
     'b200amg_axpy': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scal': (c_int, [c_longlong, c_double, p, p, p]),
     'b200amg_scale_diag': (c_int, [c_longlong, c_double, p, p, p, c_int, p]),
@@ -101,6 +104,8 @@ _SIGS = {
     'b200amg_vcycle_work_bytes': (c_longlong, [c_int, POINTER(LevelDesc)]),
     'b200amg_vcycle_create': (c_int, [c_int, POINTER(LevelDesc), p, p, c_longlong, POINTER(c_void_p)]),
     'b200amg_vcycle_run': (c_int, [p, p, p, c_int, c_int, p]),
+    'b200amg_vcycle_run_zero': (c_int, [p, p, p, c_int, c_int, p]),
+    'b200amg_vcycle_apply_op': (c_int, [p, c_int, c_int, p, p, p, p]),
     'b200amg_vcycle_profile': (c_int, [p, p, p, c_int, c_int, POINTER(c_int), POINTER(c_int),
                                        POINTER(ctypes.c_float), POINTER(c_int), p]),
     'b200amg_vcycle_residual_norm2': (c_int, [p, p, p, p, p]),

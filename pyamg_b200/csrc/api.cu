@@ -51,7 +51,7 @@ extern "C" int b200amg_bsr_matvec(int n_brow, int n_bcol, int R, int C, const in
         StreamArgs a{Ap, Aj, Ax, x, b, y, nnz_lookup(Ap, n_brow, S(stream)), 0, n_brow, 1.0, 0.0, 0.0};
         return stream_op(mode == 0 ? OP_MATVEC : (mode == 1 ? OP_RESIDUAL : OP_ADD), a, S(stream));
     }
-    return bsr_matvec(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode, S(stream));
+    return bsr_matvec(n_brow, R, C, Ap, Aj, Ax, x, b, y, mode, S(stream), nnz_lookup(Ap, n_brow, S(stream)));
 }
 
 extern "C" int b200amg_jacobi(const int *Ap, const int *Aj, const double *Ax, double *x, const double *b, double *temp,
@@ -128,10 +128,13 @@ extern "C" int b200amg_bsr_gauss_seidel(const int *Ap, const int *Aj, const doub
     int c0, c1;
     const int dir = colour_loop(row_start, row_stop, row_step, color_ptr_host, K, &c0, &c1);
     if (!dir) return set_err(B200AMG_EINVAL, "bsr_gauss_seidel: sweep range must cover whole colours");
+    // schedule hint: blocks per block row over the first cp[K] rows (all rows when Id is a permutation; cached read)
+    const int nrows_hint = color_ptr_host[K];
+    const double bpr = (blocksize > 1 && nrows_hint > 0) ? (double)nnz_lookup(Ap, nrows_hint, S(stream)) / nrows_hint : -1.0;
     for (int c = c0; c != c1; c += dir) {
         const int p0 = color_ptr_host[c], p1 = color_ptr_host[c + 1];
         if (blocksize == 1) B200_TRY(gs_rows(true, Ap, Aj, Ax, x, b, Id, p0, p1, S(stream)));
-        else B200_TRY(bsr_gs_color(blocksize, Ap, Aj, Ax, x, b, Id, p0, p1, dir < 0, S(stream)));
+        else B200_TRY(bsr_gs_color(blocksize, Ap, Aj, Ax, x, b, Id, p0, p1, dir < 0, S(stream), bpr));
     }
     return 0;
 }
@@ -144,6 +147,23 @@ extern "C" int b200amg_dot(long long n, const double *x, const double *y, double
 extern "C" int b200amg_dot_noalloc(long long n, const double *x, const double *y, double *out_dev, void *stream)
 {
     return dot_noalloc(n, x, y, out_dev, S(stream));
+}
+
+extern "C" int b200amg_pcg_scalars(double *state, int which, void *stream)
+{
+    if (!state || which < 0 || which > 1) return set_err(B200AMG_EINVAL, "pcg_scalars: bad arguments");
+    return pcg_scalars(state, which, S(stream));
+}
+
+extern "C" int b200amg_pcg_update_xr(long long n, const double *state, const double *p, const double *Ap, double *x,
+                                     double *r, int update_r, void *stream)
+{
+    return pcg_update_xr(n, state, p, Ap, x, r, update_r, S(stream));
+}
+
+extern "C" int b200amg_pcg_update_p(long long n, const double *state, const double *z, double *p, void *stream)
+{
+    return pcg_update_p(n, state, z, p, S(stream));
 }
 
 extern "C" int b200amg_axpy(long long n, double a, const double *x, double *y, void *stream)

@@ -100,6 +100,81 @@ int dot_noalloc(long long n, const double *x, const double *y, double *out, cuda
     return dot(n, x, y, out, scratch, st);
 }
 
+// ---- preconditioned CG without the host in the loop (pyamg/krylov/_cg.py:109-170) ---------------------------------
+// The iteration's scalars live in a small device array `st` (doubles):
+//   [0] rz  [1] pAp  [2] rz_new  [3] alpha  [4] beta  [5] tol (absolute, preconditioned norm)  [6] flag  [7] iter
+//   [8] maxiter  [9] capacity of hist  [16 + k] hist[k] = sqrt(rz) after iteration k (k = 0: initial)
+// flag: 0 running, 1 converged (normr < tol), 2 maxiter reached, -1 indefinite matrix (pAp < 0), -2 indefinite
+// preconditioner (rz < 0), -3 singular preconditioner (rz == 0 without convergence).  Once flag != 0 every kernel of
+// a later iteration is a no-op, so the host may enqueue iterations ahead and read the flag every few of them.
+constexpr int PCG_HIST0 = 16;
+
+// which == 0: after pAp = <Ap, p>; which == 1: after rz_new = <r, z>
+__global__ void pcg_scalars_kernel(double *st, int which)
+{
+    if (st[6] != 0.0) return;
+    if (which == 0) {
+        if (st[1] < 0.0) { st[6] = -1.0; return; }               // _cg.py:120-122
+        st[3] = st[0] / st[1];                                   // alpha = rz / pAp
+        return;
+    }
+    const double rz_new = st[2];
+    if (rz_new < 0.0) { st[6] = -2.0; return; }                  // _cg.py:135-137
+    st[4] = rz_new / st[0];                                      // beta = rz / rz_old
+    st[0] = rz_new;
+    const int it = (int)st[7] + 1;
+    st[7] = (double)it;
+    const double normr = sqrt(rz_new);
+    if (it < (int)st[9]) st[PCG_HIST0 + it] = normr;
+    if (normr < st[5]) st[6] = 1.0;                              // _cg.py:152-153
+    else if (rz_new == 0.0) st[6] = -3.0;                        // :154-159
+    else if (it >= (int)st[8]) st[6] = 2.0;                      // :161-162
+}
+
+// x += alpha p;  r -= alpha Ap (when update_r != 0: the iterations that do not recompute r = b - A x)
+__global__ void __launch_bounds__(256) pcg_update_xr_kernel(long long n, const double *__restrict__ st,
+                                                            const double *__restrict__ p, const double *__restrict__ Ap,
+                                                            double *x, double *r, int update_r)
+{
+    if (st[6] != 0.0) return;
+    const double alpha = st[3];
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    x[i] = add_rn(x[i], mul_rn(alpha, p[i]));
+    if (update_r) r[i] = sub_rn(r[i], mul_rn(alpha, Ap[i]));
+}
+
+// p = beta p + z
+__global__ void __launch_bounds__(256) pcg_update_p_kernel(long long n, const double *__restrict__ st,
+                                                           const double *__restrict__ z, double *p)
+{
+    if (st[6] != 0.0) return;
+    const double beta = st[4];
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) p[i] = add_rn(mul_rn(p[i], beta), z[i]);
+}
+
+int pcg_scalars(double *st, int which, cudaStream_t s)
+{
+    pcg_scalars_kernel<<<1, 1, 0, s>>>(st, which);
+    return check_launch("pcg_scalars_kernel");
+}
+
+int pcg_update_xr(long long n, const double *st, const double *p, const double *Ap, double *x, double *r, int update_r,
+                  cudaStream_t s)
+{
+    if (n <= 0) return 0;
+    pcg_update_xr_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, st, p, Ap, x, r, update_r);
+    return check_launch("pcg_update_xr_kernel");
+}
+
+int pcg_update_p(long long n, const double *st, const double *z, double *p, cudaStream_t s)
+{
+    if (n <= 0) return 0;
+    pcg_update_p_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, st, z, p);
+    return check_launch("pcg_update_p_kernel");
+}
+
 __global__ void __launch_bounds__(256) axpy_kernel(long long n, double a, const double *__restrict__ x, double *y)
 {
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;

@@ -3,6 +3,7 @@
 // dense block product = linalg.h:359-398 'gemm' started from zero).
 // Arithmetic order is the reference's: per off-diagonal block loc = ((0+a0 x0)+a1 x1)+...,
 // acc -= loc; then the point sweep inside the diagonal block.
+#include <stdlib.h>
 #include "internal.cuh"
 
 namespace b200amg {
@@ -178,6 +179,135 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
     }
 }
 
+// One colour of block rows, ONE WARP per block row: the form for rows with many blocks (coarse elasticity levels:
+// 44-55 blocks of 6 x 6 per row).  The lanes-per-row kernel above walks a row's blocks one after the other, two
+// dependent global loads per block (Aj, then the block and x_j): 0.8 us per block, 40 us per colour launch whatever the
+// colour's size (ncu, profiles/r02).  Here the warp takes 32 / BS blocks of its row per pass -- lane (g, k) forms
+// loc = row k of block g times x_j from zero, exactly the reference's gemm (linalg.h:359-398) -- so one pass costs ONE
+// round of memory latency; then the pass's locs are subtracted from the row sums in STORAGE order (shuffled one by one
+// to the lanes 0..BS-1 that hold acc), which is the order of relaxation.h:139-144: the bits do not change.
+template <int BS, bool backward>
+__global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                                const double *__restrict__ Ax, double *x,
+                                                                const double *__restrict__ b, const int *__restrict__ Id,
+                                                                int p0, int p1)
+{
+    constexpr int G = 32 / BS;                          // blocks per pass
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int p = p0 + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (p >= p1) return;                                // the whole warp leaves together
+    const int i = Id[p];
+    const int g = lane / BS, k = lane - g * BS;
+    const bool lane_ok = g < G;
+    const int lo = Ap[i], hi = Ap[i + 1];
+    double acc = (lane < BS) ? b[(size_t)i * BS + lane] : 0.0;
+    int dptr = -1;
+#pragma unroll 2
+    for (int q0 = lo; q0 < hi; q0 += G) {
+        const int q = q0 + g;
+        const bool have = lane_ok && q < hi;
+        const int j = have ? Aj[q] : -1;
+        const bool isdiag = have && j == i;
+        double loc = 0.0;
+        if (have && !isdiag) {
+            const double *blk = Ax + ((size_t)q * BS + k) * BS;
+            const double *xb = x + (size_t)j * BS;
+#pragma unroll
+            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[c], xb[c]));
+        }
+        const unsigned dg = __ballot_sync(FULL, isdiag);
+        if (dg) dptr = q0 + (31 - __clz(dg)) / BS;      // the last stored diagonal block wins (relaxation.h:121)
+        // blocks that do not exist / the diagonal block hand over +0.0: acc - (+0.0) == acc bit for bit, also for -0.0
+        loc = (have && !isdiag) ? loc : 0.0;
+#pragma unroll
+        for (int gg = 0; gg < G; ++gg) acc = sub_rn(acc, __shfl_sync(FULL, loc, gg * BS + (lane < BS ? lane : 0)));
+    }
+    if (dptr < 0) return;
+    // point sweep inside the diagonal block (relaxation.h:150-163): lane k < BS owns row k of D
+    double xl[BS], Dk[BS];
+#pragma unroll
+    for (int c = 0; c < BS; ++c) {
+        xl[c] = x[(size_t)i * BS + c];
+        Dk[c] = (lane < BS) ? Ax[((size_t)dptr * BS + lane) * BS + c] : 0.0;
+    }
+#pragma unroll
+    for (int kq = 0; kq < BS; ++kq) {
+        const int kk0 = backward ? BS - 1 - kq : kq;
+        double nv = 0.0;
+        bool wrote = false;
+        if (lane == kk0) {
+            double d = 1.0, a = acc;
+#pragma unroll
+            for (int cq = 0; cq < BS; ++cq) {
+                const int kk = backward ? BS - 1 - cq : cq;
+                if (kk == kk0) d = Dk[kk];
+                else a = sub_rn(a, mul_rn(Dk[kk], xl[kk]));
+            }
+            if (d != 0.0) {
+                nv = div_rn(a, d);
+                wrote = true;
+                x[(size_t)i * BS + kk0] = nv;
+            }
+        }
+        const double cur = wrote ? nv : xl[kk0];
+        xl[kk0] = __shfl_sync(FULL, cur, kk0);
+    }
+}
+
+// scipy bsr_matvec with ONE WARP per block row (rows with many blocks: the restrictions of an elasticity hierarchy,
+// 6 x 3 / 6 x 6 blocks, 30-150 blocks per row; the thread-per-scalar-row kernel above walks them one block at a
+// time: 0.5-0.6 ms for 1331 / 27 block rows).  scipy accumulates y[i*R + r] over ALL entries of the scalar row in
+// storage order into one running sum, so only the products are free: lane (g, r) multiplies row r of block g of the
+// pass by x_j (C separately rounded products), then the running sum of scalar row r travels through the groups in
+// block order -- group g adds its C products, hands the sum to group g + 1 by a shuffle -- G shuffles per pass.
+template <int R>
+__global__ void __launch_bounds__(128) bsr_matvec_warp_kernel(int n_brow, int C, const int *__restrict__ Ap,
+                                                              const int *__restrict__ Aj, const double *__restrict__ Ax,
+                                                              const double *__restrict__ x, const double *__restrict__ b,
+                                                              double *y, int mode)
+{
+    constexpr int G = 32 / R;
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (i >= n_brow) return;
+    const int g = lane / R, r = lane - g * R;
+    const bool lane_ok = g < G;
+    const int lo = Ap[i], hi = Ap[i + 1];
+    double carry = 0.0;                                   // running sum of scalar row r after the blocks before this pass
+#pragma unroll 2
+    for (int q0 = lo; q0 < hi; q0 += G) {
+        const int q = q0 + g;
+        const bool have = lane_ok && q < hi;
+        double pr[8];
+        if (have) {
+            const double *blk = Ax + ((size_t)q * R + r) * C;
+            const double *xb = x + (size_t)Aj[q] * C;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                if (c < C) pr[c] = mul_rn(blk[c], xb[c]);
+        }
+        double a = carry;
+#pragma unroll
+        for (int gg = 0; gg < G; ++gg) {
+            if (gg > 0) a = __shfl_sync(FULL, a, (gg - 1) * R + (lane_ok ? r : 0));   // sum after group gg - 1
+            if (g == gg && have) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    if (c < C) a = add_rn(a, pr[c]);
+            }
+        }
+        carry = __shfl_sync(FULL, a, (G - 1) * R + (lane_ok ? r : 0));
+    }
+    if (lane < R) {
+        const size_t row = (size_t)i * R + lane;
+        if (mode == 0) y[row] = carry;
+        else if (mode == 1) y[row] = sub_rn(b[row], carry);
+        else y[row] = add_rn(b ? b[row] : y[row], carry);
+    }
+}
+
 template <int BS>
 __global__ void bsr_gs_sequential_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
                                          const double *__restrict__ Ax, double *x, const double *__restrict__ b,
@@ -202,12 +332,37 @@ __global__ void bsr_gs_sequential_kernel(const int *__restrict__ Ap, const int *
     default: return set_err(B200AMG_EINVAL, "blocksize must be in 1..8");     \
     }
 
+#define R_SWITCH(r, CALL)                                                     \
+    switch (r) {                                                              \
+    case 2: { constexpr int RR = 2; CALL; } break;                            \
+    case 3: { constexpr int RR = 3; CALL; } break;                            \
+    case 4: { constexpr int RR = 4; CALL; } break;                            \
+    case 5: { constexpr int RR = 5; CALL; } break;                            \
+    case 6: { constexpr int RR = 6; CALL; } break;                            \
+    case 7: { constexpr int RR = 7; CALL; } break;                            \
+    default: { constexpr int RR = 8; CALL; } break;                           \
+    }
+
+// B200AMG_BSR_WARP=0 keeps the lanes-per-row / thread-per-row kernels everywhere (A/B switch)
+static bool bsr_warp_kernels()
+{
+    static const bool on = [] { const char *e = getenv("B200AMG_BSR_WARP"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
+// nblocks: stored blocks of the operator (< 0: unknown) -- rows with at least half a pass of blocks on average go to
+// the warp-per-block-row kernel
 int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax, const double *x,
-               const double *b, double *y, int mode, cudaStream_t st)
+               const double *b, double *y, int mode, cudaStream_t st, long long nblocks)
 {
     if (R < 1 || C < 1 || R > 8 || C > 8) return set_err(B200AMG_EINVAL, "bsr_matvec: block shape must be in 1..8");
     const long long n = (long long)n_brow * R;
     if (n <= 0) return 0;
+    if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && 2 * nblocks >= (long long)(32 / R) * n_brow) {
+        const unsigned grid = (unsigned)((n_brow + 3) / 4);
+        R_SWITCH(R, B200_LAUNCH(bsr_matvec_warp_kernel<RR>, grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode));
+        return check_launch("bsr_matvec_warp_kernel");
+    }
     B200_LAUNCH(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
     return check_launch("bsr_matvec_kernel");
 }
@@ -223,9 +378,15 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
 }
 
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
-                 const int *Id, int p0, int p1, bool backward, cudaStream_t st)
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row)
 {
     if (p1 <= p0) return 0;
+    if (bs >= 2 && bsr_warp_kernels() && 2.0 * blocks_per_row >= (double)(32 / bs)) {
+        const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
+        if (backward) { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }
+        else { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }
+        return check_launch("bsr_gs_color_warp_kernel");
+    }
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
     BS_SWITCH(bs, B200_LAUNCH(bsr_gs_color_kernel<BS>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward));

@@ -101,12 +101,13 @@ int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x
 int gs_sequential(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                   const int *Id, int start, int stop, int step, cudaStream_t st);
 
+// nblocks / blocks_per_row (stored blocks; < 0: unknown) pick the schedule: warp per block row for long rows
 int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax, const double *x,
-               const double *b, double *y, int mode, cudaStream_t st);
+               const double *b, double *y, int mode, cudaStream_t st, long long nblocks = -1);
 int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const double *Ax, const double *xin,
                double *xout, const double *b, double omega, cudaStream_t st);
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
-                 const int *Id, int p0, int p1, bool backward, cudaStream_t st);
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row = -1.0);
 int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                       const int *Id, int start, int stop, int step, cudaStream_t st);
 
@@ -124,6 +125,10 @@ int pinv_array(double *AA, int m, int n, int transA, cudaStream_t st);
 
 int dot(long long n, const double *x, const double *y, double *out, double *work, cudaStream_t st);
 int dot_noalloc(long long n, const double *x, const double *y, double *out, cudaStream_t st);   // scratch inside the library
+int pcg_scalars(double *st, int which, cudaStream_t s);
+int pcg_update_xr(long long n, const double *st, const double *p, const double *Ap, double *x, double *r, int update_r,
+                  cudaStream_t s);
+int pcg_update_p(long long n, const double *st, const double *z, double *p, cudaStream_t s);
 int axpy(long long n, double a, const double *x, double *y, cudaStream_t st);
 int scal(long long n, double a, const double *x, double *y, cudaStream_t st);
 int extract_diag(int nb, int bs, const int *Ap, const int *Aj, const double *Ax, double *diag, cudaStream_t st);

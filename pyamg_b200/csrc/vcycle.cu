@@ -26,7 +26,7 @@ struct LevelRt {
 };
 
 struct GraphKey {
-    double *x; const double *b; int kind;
+    double *x; const double *b; int kind;   // kind: cycle kind | 4 when the cycle starts from a zero guess
     cudaGraphExec_t exec;
     long long launches;   // kernel nodes in the graph (for b200amg_launch_count)
 };
@@ -90,7 +90,7 @@ static int apply_A(const LevelRt &L, int op_scalar, int bsr_mode, const double *
         if (L.sA.ok()) return sell_op(op_scalar, L.sA, a, st);
         return stream_op(op_scalar, a, st);
     }
-    return bsr_matvec(d.n / d.bs, d.bs, d.bs, d.Ap, d.Aj, d.Ax, x, b, y, bsr_mode, st);
+    return bsr_matvec(d.n / d.bs, d.bs, d.bs, d.Ap, d.Aj, d.Ax, x, b, y, bsr_mode, st, L.nzA);
 }
 
 static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_t st)
@@ -102,7 +102,7 @@ static int restrict_r(const LevelRt &L, const double *r, double *bc, cudaStream_
         if (L.sR.ok()) return sell_op(OP_MATVEC, L.sR, a, st);
         return stream_op(OP_MATVEC, a, st);
     }
-    return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st);
+    return bsr_matvec(d.nc / d.p_bc, d.p_bc, d.p_br, d.Rp, d.Rj, d.Rx, r, nullptr, bc, 0, st, L.nzR);
 }
 
 // x_out = x_in + P x_c (x_in == nullptr: in place)
@@ -115,7 +115,7 @@ static int prolong_add(const LevelRt &L, const double *xc, const double *x_in, d
         if (L.sP.ok()) return sell_op(OP_ADD, L.sP, a, st);
         return stream_op(OP_ADD, a, st);
     }
-    return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, x_in, x, 2, st);
+    return bsr_matvec(d.n / d.p_br, d.p_br, d.p_bc, d.Pp, d.Pj, d.Px, xc, x_in, x, 2, st, L.nzP);
 }
 
 // one smoothing stage; *cur is the buffer holding the iterate (x or the spare), swapped by Jacobi
@@ -163,7 +163,8 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
                     else if (d.bs == 1)
                         B200_TRY(gs_rows(d.flavor != 0, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
                     else
-                        B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st));
+                        B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st,
+                                              (double)L.nzA / (double)(d.n / d.bs)));
                 }
             }
         }
@@ -402,15 +403,13 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
     return 0;
 }
 
-extern "C" int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph, void *stream)
+static int run_cycle(Engine *E, double *x, const double *b, int cycle_kind, int use_graph, bool from_zero, cudaStream_t st)
 {
-    Engine *E = reinterpret_cast<Engine *>(handle);
-    if (!E || cycle_kind < 0 || cycle_kind > 2) return set_err(B200AMG_EINVAL, "vcycle_run: bad arguments");
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     B200_TRY(ensure_diag(*E, st));
-    if (!use_graph || st == nullptr) return cycle(*E, 0, x, b, cycle_kind, false, st);
+    if (!use_graph || st == nullptr) return cycle(*E, 0, x, b, cycle_kind, from_zero, st);
+    const int key_kind = cycle_kind | (from_zero ? 4 : 0);
     for (auto &g : E->graphs)
-        if (g.x == x && g.b == b && g.kind == cycle_kind) {
+        if (g.x == x && g.b == b && g.kind == key_kind) {
             B200_CUDA(cudaGraphLaunch(g.exec, st));
             g_launches += g.launches;
             return 0;
@@ -418,17 +417,46 @@ extern "C" int b200amg_vcycle_run(void *handle, double *x, const double *b, int 
     cudaGraph_t graph;
     const long long before = g_launches;
     B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    int rc = cycle(*E, 0, x, b, cycle_kind, false, st);
+    int rc = cycle(*E, 0, x, b, cycle_kind, from_zero, st);
     cudaError_t ce = cudaStreamEndCapture(st, &graph);
     if (rc) return rc;
     if (ce != cudaSuccess) return set_err((int)ce, "vcycle_run: stream capture failed");
-    GraphKey key{x, b, cycle_kind, nullptr, g_launches - before};
+    GraphKey key{x, b, key_kind, nullptr, g_launches - before};
     B200_CUDA(cudaGraphInstantiate(&key.exec, graph, 0));
     B200_CUDA(cudaGraphDestroy(graph));
-    if (E->graphs.size() >= 8) { cudaGraphExecDestroy(E->graphs.front().exec); E->graphs.erase(E->graphs.begin()); }
+    if (E->graphs.size() >= 12) { cudaGraphExecDestroy(E->graphs.front().exec); E->graphs.erase(E->graphs.begin()); }
     E->graphs.push_back(key);
     B200_CUDA(cudaGraphLaunch(key.exec, st));
     return 0;
+}
+
+extern "C" int b200amg_vcycle_run(void *handle, double *x, const double *b, int cycle_kind, int use_graph, void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || cycle_kind < 0 || cycle_kind > 2) return set_err(B200AMG_EINVAL, "vcycle_run: bad arguments");
+    return run_cycle(E, x, b, cycle_kind, use_graph, false, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// x <- cycle(0, b): the preconditioner application (multilevel.py:274-314 calls solve(b, x0 = zeros, maxiter = 1)).
+// x need not be cleared by the caller; the first pre-smoothing sweep from the known-zero guess is the bit-identical
+// diagonal scaling / a memset, like on the coarse levels of every cycle -- one pass over A_0 less than b200amg_vcycle_run
+extern "C" int b200amg_vcycle_run_zero(void *handle, double *x, const double *b, int cycle_kind, int use_graph, void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || cycle_kind < 0 || cycle_kind > 2) return set_err(B200AMG_EINVAL, "vcycle_run_zero: bad arguments");
+    return run_cycle(E, x, b, cycle_kind, use_graph, true, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// y = A_level x (op 0) or y = b - A_level x (op 2) in the layout the engine streams that operator in: what a Krylov
+// method around the cycle needs (pyamg/krylov/_cg.py: A*p, b - A*x) without a second copy of A in plain CSR traffic
+extern "C" int b200amg_vcycle_apply_op(void *handle, int level, int op, const double *x, const double *b, double *y,
+                                      void *stream)
+{
+    Engine *E = reinterpret_cast<Engine *>(handle);
+    if (!E || level < 0 || level >= (int)E->lev.size() || (op != 0 && op != 2))
+        return set_err(B200AMG_EINVAL, "vcycle_apply_op: bad arguments");
+    return apply_A(E->lev[level], op == 0 ? OP_MATVEC : OP_RESIDUAL, op == 0 ? 0 : 1, x, b, y,
+                   reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_kind, int max_ops,

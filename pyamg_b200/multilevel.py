@@ -217,7 +217,11 @@ class multilevel_solver:
             if ordered:
                 s0 = ordered[0]
                 for s in ordered[1:]:
-                    if s.indices is not s0.indices and not np.array_equal(np.asarray(s.color_ptr), np.asarray(s0.color_ptr)):
+                    if s.indices is not s0.indices and not (
+                            np.array_equal(np.asarray(s.color_ptr), np.asarray(s0.color_ptr)) and
+                            (torch.equal(s.indices, s0.indices) if isinstance(s.indices, torch.Tensor) and isinstance(s0.indices, torch.Tensor)
+                             else np.array_equal(np.asarray(s.indices.cpu() if isinstance(s.indices, torch.Tensor) else s.indices),
+                                                 np.asarray(s0.indices.cpu() if isinstance(s0.indices, torch.Tensor) else s0.indices)))):
                         raise ValueError('pre- and post-smoother must share one colour ordering per level')
                 Id = s0.indices
                 if not isinstance(Id, torch.Tensor):
@@ -246,15 +250,18 @@ class multilevel_solver:
                   self._stream.cuda_stream)
         return float(np.sqrt(self._nrm[0].item()))
 
-    def cycle_device(self, cycle='V', use_graph=True):
+    def cycle_device(self, cycle='V', use_graph=True, from_zero=False):
         """one cycle on the engine's resident (x, b): x <- cycle(x, b).  Asynchronous.  V / W / F replay the engine's
         CUDA graph; 'AMLI' needs inner products between its recursive corrections and is driven from the host
-        (cycle_host)."""
+        (cycle_host).  from_zero: x is known to be zero (and need not be cleared): the first pre-smoothing sweep
+        collapses to its bit-identical shortcut (b200amg_vcycle_run_zero)."""
         if cycle == 'AMLI':
+            if from_zero:
+                self._x.zero_()
             self.cycle_host(0, self._x, self._b, 'AMLI')
             return
-        _lib.call('b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b), _CYCLE[cycle], int(use_graph),
-                  self._stream.cuda_stream)
+        _lib.call('b200amg_vcycle_run_zero' if from_zero else 'b200amg_vcycle_run', self._engine, _ptr(self._x), _ptr(self._b),
+                  _CYCLE[cycle], int(use_graph), self._stream.cuda_stream)
 
     def _apply_smoother(self, sm, A, x, b):
         """one resolved smoother through the stand-alone entry points (same kernels' arithmetic as the engine)"""
@@ -378,10 +385,13 @@ class multilevel_solver:
         return LinearOperator(shape, matvec, dtype=np.float64)
 
     def solve(self, b, x0=None, tol=1e-5, maxiter=100, cycle='V', accel=None, callback=None, residuals=None,
-              return_residuals=False, _norms=True):
+              return_residuals=False, _norms=True, _alias_out=False):
         """Same contract as the reference's solve (multilevel.py:316-471): relative-residual
         stopping test `||r_k|| <= tol * ||b||`, residual history appended to `residuals`,
-        `callback(x)` after every cycle.  numpy in -> numpy out, torch CUDA in -> torch CUDA out."""
+        `callback(x)` after every cycle.  numpy in -> numpy out, torch CUDA in -> torch CUDA out, torch CPU (pinned) in
+        -> torch CPU out (a fresh tensor; `_alias_out=True` hands out the solver's persistent pinned buffer instead,
+        which the next call overwrites).  `_norms=False` skips the residual norms (fixed `maxiter` cycles): what
+        aspreconditioner's matvec needs."""
         cycle = str(cycle).upper()
         if cycle not in _CYCLE and cycle != 'AMLI':
             raise TypeError('Unrecognized cycle type (%s)' % cycle)
@@ -402,9 +412,10 @@ class multilevel_solver:
             if bt.numel() != n:
                 raise ValueError('b has invalid dimensions')
             self._b.copy_(bt.reshape(-1), non_blocking=True)
-            if x0 is None:
-                self._x.zero_()
-            else:
+            zero_guess = x0 is None
+            if zero_guess and _norms:
+                self._x.zero_()                       # the residual norm before the first cycle reads x
+            elif not zero_guess:
                 xt = x0 if isinstance(x0, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.ravel(x0), np.float64))
                 self._x.copy_(xt.reshape(-1), non_blocking=True)
             if residuals is None:
@@ -419,20 +430,22 @@ class multilevel_solver:
                     tol = tol * normb
                 residuals.append(self._residual_norm())
                 while len(residuals) <= maxiter and residuals[-1] > tol:
-                    self.cycle_device(cycle)
+                    self.cycle_device(cycle, from_zero=zero_guess and len(residuals) == 1)
                     residuals.append(self._residual_norm())
                     if callback is not None:
                         callback(self._x.cpu().numpy() if as_numpy else self._x)
             else:
-                for _ in range(maxiter):
-                    self.cycle_device(cycle)
+                if maxiter == 0 and zero_guess:
+                    self._x.zero_()
+                for k in range(maxiter):
+                    self.cycle_device(cycle, from_zero=zero_guess and k == 0)
             if host_tensor:
                 # host tensor in -> host tensor out through a persistent pinned buffer (one D2H copy)
                 if getattr(self, '_xhost', None) is None:
                     self._xhost = torch.empty(n, dtype=torch.float64, pin_memory=True)
                 self._xhost.copy_(self._x, non_blocking=True)
                 self._stream.synchronize()
-                out = self._xhost
+                out = self._xhost if _alias_out else self._xhost.clone()
             else:
                 out = self._x.cpu().numpy() if as_numpy else self._x.clone()
         cur.wait_stream(self._stream)
@@ -441,6 +454,70 @@ class multilevel_solver:
         if return_residuals:
             return out, residuals
         return out
+
+    def solve_many(self, bs, maxiter=1, cycle='V', out=None):
+        """x_k = `maxiter` cycles from a zero initial guess for EVERY right-hand side of `bs` (host vectors: pinned
+        torch CPU tensors for full overlap, numpy arrays accepted) -- the multiple-right-hand-side form of
+        `aspreconditioner().matvec` / `solve(b, maxiter=k)` without residual norms.  Three streams pipeline the work of
+        consecutive right-hand sides: while the cycle of b_k runs, b_{k+1} crosses PCIe host->device and x_{k-1}
+        device->host (full duplex), over two device buffer pairs.  Every x_k is the same bits as
+        solve(b_k, maxiter=maxiter, _norms=False).  -> list of host tensors (`out`: preallocated pinned tensors to fill;
+        default: fresh pinned tensors)."""
+        cycle = str(cycle).upper()
+        if cycle not in _CYCLE:
+            raise TypeError('solve_many: cycle must be V, W or F (got %s)' % cycle)
+        if len(self.levels) == 1:
+            raise NotImplementedError('solve_many needs a multilevel hierarchy')
+        if self._engine is None:
+            self._build_engine()
+        n = self.levels[0].A.shape[0]
+        dev = self._x.device
+        if getattr(self, '_pipe', None) is None:
+            self._pipe = {'x': [self._x, torch.zeros_like(self._x)], 'b': [self._b, torch.zeros_like(self._b)],
+                          'h2d': torch.cuda.Stream(device=dev), 'd2h': torch.cuda.Stream(device=dev)}
+        P = self._pipe
+        comp, h2d, d2h = self._stream, P['h2d'], P['d2h']
+        cur = torch.cuda.current_stream()
+        for s_ in (comp, h2d, d2h):
+            s_.wait_stream(cur)
+        b_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        x_ready = [None, None]
+        x_copied = [None, None]
+        outs = []
+        for k, bk in enumerate(bs):
+            slot = k & 1
+            bt = bk if isinstance(bk, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.ravel(bk), np.float64))
+            if bt.numel() != n:
+                raise ValueError('b has invalid dimensions')
+            xo = out[k] if out is not None else torch.empty(n, dtype=torch.float64, pin_memory=True)
+            xd, bd = P['x'][slot], P['b'][slot]
+            if x_ready[slot] is not None:
+                h2d.wait_event(x_ready[slot])             # the cycle two right-hand sides ago has finished reading b
+            with torch.cuda.stream(h2d):
+                bd.copy_(bt.reshape(-1), non_blocking=True)
+                b_ready[slot].record(h2d)
+            comp.wait_event(b_ready[slot])
+            if x_copied[slot] is not None:
+                comp.wait_event(x_copied[slot])           # ... and its x has left for the host
+            with torch.cuda.stream(comp):
+                for it in range(maxiter):
+                    _lib.call('b200amg_vcycle_run_zero' if it == 0 else 'b200amg_vcycle_run', self._engine, _ptr(xd), _ptr(bd),
+                              _CYCLE[cycle], 1, comp.cuda_stream)
+                if maxiter == 0:
+                    xd.zero_()
+                x_ready[slot] = torch.cuda.Event()
+                x_ready[slot].record(comp)
+            d2h.wait_event(x_ready[slot])
+            with torch.cuda.stream(d2h):
+                xo.copy_(xd, non_blocking=True)
+                x_copied[slot] = torch.cuda.Event()
+                x_copied[slot].record(d2h)
+            b_ready[slot] = torch.cuda.Event()
+            outs.append(xo)
+        d2h.synchronize()
+        comp.synchronize()
+        cur.wait_stream(comp)
+        return outs
 
     def _keep_dotwork(self):
         if not hasattr(self, '_dotwork'):

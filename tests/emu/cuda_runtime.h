@@ -2,7 +2,7 @@
 // (pyamg_b200/csrc/*.cu, unchanged) for the HOST, so that thread-per-row / warp-per-row kernels can be checked
 // against scipy in this GPU-less container before they ever see hardware (tests/test_emulated_kernels.py).
 // Every CUDA thread of a block is a real OS thread; __syncthreads / __syncwarp are barriers; blocks run one after
-// the other.  Supports what the emulated kernels use: barriers, full-warp __shfl_sync / __all_sync, __ldg, int4 / double2 loads;
+// the other.  Supports what the emulated kernels use: barriers, full-warp __shfl_sync / __all_sync / __ballot_sync, __ldg, int4 / double2 loads;
 // dynamic shared memory only as a global array the test provides; no static shared memory, no atomics.  The product never
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
@@ -122,6 +122,18 @@ inline int __all_sync(unsigned, int pred)
     for (unsigned l = 0; l < lanes; ++l) all &= (int)s->slots[w * 32 + l];
     s->warp[w]->arrive_and_wait();
     return all;
+}
+inline unsigned __ballot_sync(unsigned, int pred)
+{
+    cuda_emu::BlockSync *s = cuda_emu::cur;
+    const unsigned tid = threadIdx.x, w = tid / 32;
+    s->slots[tid] = pred ? 1ull : 0ull;
+    s->warp[w]->arrive_and_wait();
+    const unsigned lanes = std::min(32u, blockDim.x - 32 * w);
+    unsigned m = 0;
+    for (unsigned l = 0; l < lanes; ++l) m |= (unsigned)s->slots[w * 32 + l] << l;
+    s->warp[w]->arrive_and_wait();
+    return m;
 }
 template <class T> inline T __ldg(const T *p) { return *p; }
 inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }

@@ -563,10 +563,14 @@ def emu_bsr():
     lib = ctypes.CDLL(out)
     lib.emu_bsr_matvec.restype = c_int
     lib.emu_bsr_matvec.argtypes = [c_int, c_int, c_int, vp, vp, vp, vp, vp, vp, c_int]
+    lib.emu_bsr_matvec_warp.restype = c_int
+    lib.emu_bsr_matvec_warp.argtypes = [c_int, c_int, c_int, vp, vp, vp, vp, vp, vp, c_int]
     lib.emu_bsr_jacobi.restype = c_int
     lib.emu_bsr_jacobi.argtypes = [vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_dbl]
     lib.emu_bsr_gauss_seidel.restype = c_int
     lib.emu_bsr_gauss_seidel.argtypes = [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, vp, ctypes.POINTER(c_int), c_int]
+    lib.emu_bsr_gauss_seidel_warp.restype = c_int
+    lib.emu_bsr_gauss_seidel_warp.argtypes = [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, vp, ctypes.POINTER(c_int), c_int]
     return lib
 
 
@@ -606,3 +610,19 @@ def test_bsr_solve_kernels_equal_reference(emu_bsr, bs):
     assert emu_bsr.emu_bsr_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), 0, 90, 1, bs, P(idx), cp, len(ptr) - 1) == 0
     assert emu_bsr.emu_bsr_gauss_seidel(P(Ap), P(Aj), P(Ax), P(got), P(b), 89, -1, -1, bs, P(idx), cp, len(ptr) - 1) == 0
     assert np.array_equal(got, want)
+    # the warp-per-block-row schedules (long rows in the product): same bits
+    got = x0.copy()
+    assert emu_bsr.emu_bsr_gauss_seidel_warp(P(Ap), P(Aj), P(Ax), P(got), P(b), 0, 90, 1, bs, P(idx), cp, len(ptr) - 1) == 0
+    assert emu_bsr.emu_bsr_gauss_seidel_warp(P(Ap), P(Aj), P(Ax), P(got), P(b), 89, -1, -1, bs, P(idx), cp, len(ptr) - 1) == 0
+    assert np.array_equal(got, want)
+    for mode, wantv in ((0, A * x0), (1, b - A * x0), (2, b + A * x0)):
+        y = np.full(n, np.nan)
+        assert emu_bsr.emu_bsr_matvec_warp(90, bs, bs, P(Ap), P(Aj), P(Ax), P(x0), P(b), P(y), mode) == 0
+        assert np.array_equal(y, wantv), mode
+    for (nr, nc, R, C) in ((50, 70, 3, 6), (40, 90, 6, 3), (7, 300, 6, 6)):
+        Rm = random_bsr(nr, nc, R, C, 0.3, 5)
+        xr = np.random.RandomState(1).rand(nc * C)
+        y = np.full(nr * R, np.nan)
+        assert emu_bsr.emu_bsr_matvec_warp(nr, R, C, P(i32(Rm.indptr)), P(i32(Rm.indices)), P(np.ravel(Rm.data).copy()), P(xr),
+                                           None, P(y), 0) == 0
+        assert np.array_equal(y, Rm * xr), (R, C)
