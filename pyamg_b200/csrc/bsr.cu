@@ -134,15 +134,32 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
     if (active) {
         acc = b[(size_t)i * BS + k];
         const int hi = Ap[i + 1];
-        for (int q = Ap[i]; q < hi; ++q) {
-            const int j = Aj[q];
-            if (j == i) { dptr = q; continue; }
-            const double *blk = Ax + ((size_t)q * BS + k) * BS;
-            const double *xb = x + (size_t)j * BS;
-            double loc = 0.0;
+        // U blocks in flight: their column numbers first, then every block row / x_j operand, then the folds in
+        // storage order -- one round of memory latency per U blocks instead of two per block
+        constexpr int U = BS <= 4 ? 4 : 2;
+        for (int q = Ap[i]; q < hi; q += U) {
+            int j[U];
+            double bl[U][BS], xv[U][BS];
 #pragma unroll
-            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[c], xb[c]));
-            acc = sub_rn(acc, loc);
+            for (int u = 0; u < U; ++u) j[u] = (q + u < hi) ? Aj[q + u] : -1;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (j[u] >= 0 && j[u] != i) {
+                    const double *blk = Ax + ((size_t)(q + u) * BS + k) * BS;
+                    const double *xb = x + (size_t)j[u] * BS;
+#pragma unroll
+                    for (int c = 0; c < BS; ++c) { bl[u][c] = blk[c]; xv[u][c] = xb[c]; }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (j[u] < 0) continue;
+                if (j[u] == i) { dptr = q + u; continue; }
+                double loc = 0.0;
+#pragma unroll
+                for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(bl[u][c], xv[u][c]));
+                acc = sub_rn(acc, loc);
+            }
         }
     }
     const bool has_diag = active && dptr >= 0;
@@ -358,7 +375,9 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     if (R < 1 || C < 1 || R > 8 || C > 8) return set_err(B200AMG_EINVAL, "bsr_matvec: block shape must be in 1..8");
     const long long n = (long long)n_brow * R;
     if (n <= 0) return 0;
-    if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && 2 * nblocks >= (long long)(32 / R) * n_brow) {
+    // warp per block row only where thread-per-scalar-row cannot fill the machine (few rows) and the rows are long
+    // (measured on BASELINE config 4, profiles/r02: 1 331 x 6 rows 0.54 -> 0.13 ms; 2.08 M x 3 rows 0.53 -> 2.3 ms)
+    if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && n < kSMs * 1024 && nblocks >= 2ll * (32 / R) * n_brow) {
         const unsigned grid = (unsigned)((n_brow + 3) / 4);
         R_SWITCH(R, B200_LAUNCH(bsr_matvec_warp_kernel<RR>, grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode));
         return check_launch("bsr_matvec_warp_kernel");
@@ -381,7 +400,9 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
                  const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row)
 {
     if (p1 <= p0) return 0;
-    if (bs >= 2 && bsr_warp_kernels() && 2.0 * blocks_per_row >= (double)(32 / bs)) {
+    // warp per block row where the colour is too small for lanes-per-row to fill the machine and the rows are long
+    // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
+    if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
         if (backward) { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }
         else { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }

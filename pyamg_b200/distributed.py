@@ -137,8 +137,8 @@ class DistributedSolver:
             return sub
         return cls(describe(ml), coarse, **kw)
 
-    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=100000, backend=None, device=None,
-                 halo='auto'):
+    def __init__(self, levels, coarse_factory, group=None, agglomerate_below=None, backend=None, device=None,
+                 halo='auto', min_rows_per_rank=16384):
         self.group = group
         self.rank, self.G = dist.get_rank(group), dist.get_world_size(group)
         self.be = backend if backend is not None else DeviceBackend()
@@ -152,8 +152,12 @@ class DistributedSolver:
         if self.rank == 0:
             nlev = len(levels) + 1
             ka = nlev - 1
+            # a level stays partitioned while every rank keeps a slab worth launching kernels for: the threshold
+            # scales with the number of ranks (at 2 GPUs the 89 k-row level 2 of 2 x 256^3 stays partitioned instead
+            # of making rank 0 run it alone while rank 1 idles); `agglomerate_below` overrides it with a global size
+            limit = agglomerate_below if agglomerate_below is not None else min_rows_per_rank * self.G
             for k in range(1, nlev - 1):
-                if levels[k]['n'] < agglomerate_below:
+                if levels[k]['n'] < limit:
                     ka = k
                     break
             info = [{q: levels[k][q] for q in ('n', 'nc', 'flavor', 'pre', 'post')} for k in range(ka)]
@@ -351,8 +355,8 @@ class DistributedSolver:
 
     def exchange(self, plan, v):
         """refresh v[n_own : n_own + n_halo] from the owners (v = [owned | halo])"""
-        if self.G == 1 or (self._p2p is None and plan.n_halo == 0 and plan.send_idx.numel() == 0):
-            return
+        if self.G == 1:
+            return                                        # (a rank with nothing to send or receive still joins the collective)
         self._mark('compute')
         if self._p2p is not None:
             ent = self._p2p['plans'][id(plan)]
@@ -487,6 +491,34 @@ class DistributedSolver:
             dist.all_to_all_single(dst[:L.n_own], s, output_split_sizes=[L.n_own] + [0] * (self.G - 1),
                                    input_split_sizes=sizes if self.rank == 0 else [0] * self.G, group=self.group)
 
+    def load_local(self, b_slab, x0_slab=None):
+        """every rank loads ITS OWN slab of b (and x0, default 0) -- a host (pinned) or device vector of n_own entries --
+        through its own PCIe link: the distributed form of solve(b_host); no collective, asynchronous"""
+        L = self.levels[0]
+        L.b[:L.n_own].copy_(torch.as_tensor(b_slab).reshape(-1), non_blocking=True)
+        if x0_slab is None:
+            L.x[:L.n_own].zero_()
+        else:
+            L.x[:L.n_own].copy_(torch.as_tensor(x0_slab).reshape(-1), non_blocking=True)
+
+    def store_local(self, out):
+        """this rank's slab of x -> `out` (host pinned or device vector of n_own entries); asynchronous"""
+        L = self.levels[0]
+        out.copy_(L.x[:L.n_own], non_blocking=True)
+        return out
+
+    def slab(self):
+        """(first row, one past the last row) of this rank's slab of the finest level"""
+        sp = self.levels[0].split
+        return int(sp[self.rank]), int(sp[self.rank + 1])
+
+    def check_halo(self):
+        """raise if a peer-memory halo wait timed out since the last check (a stalled peer would otherwise give
+        silently wrong iterates); one small D2H read per call site"""
+        n = self.halo_errors()
+        if n:
+            raise RuntimeError('distributed cycle: %d halo wait(s) timed out -- a peer rank stalled; the iterate is not valid' % n)
+
     def gather_x(self):
         L = self.levels[0]
         sp = L.split
@@ -525,5 +557,6 @@ class DistributedSolver:
             res.append(self.residual_norm())
         if residuals is not None:
             residuals[:] = res
+        self.check_halo()
         x = self.gather_x()
         return x

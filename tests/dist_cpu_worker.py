@@ -126,7 +126,20 @@ def main():
         ok = bool(np.array_equal(x.numpy(), xr)) and np.allclose(res, ref_res, rtol=1e-12, atol=0)
         print('partitioned levels', len(S.levels), 'of', S.nlev, 'exchanges', S.exchanges, 'bit-identical x', np.array_equal(x.numpy(), xr),
               'res', res[-1], ref_res[-1], flush=True)
-    flag = torch.tensor([1 if ok else 0])
+    # slab-local entry points: every rank loads its own slab of b and reads its own slab of x (no gather through rank 0)
+    S.load(b)
+    lo, hi = S.slab()
+    b_loc = S.levels[0].b[:hi - lo].clone()
+    S.load_local(b_loc)
+    for _ in range(cycles):
+        S.cycle()
+    x_loc = S.store_local(torch.empty(hi - lo, dtype=torch.float64))
+    xg = S.gather_x()
+    S.check_halo()
+    ok_loc = torch.tensor([1])
+    if rank == 0:
+        ok_loc[0] = int(np.array_equal(xg.numpy(), xr) and np.array_equal(x_loc.numpy(), xr[lo:hi]))
+    flag = torch.tensor([1 if ok and int(ok_loc.item()) == 1 else 0])
     dist.broadcast(flag, 0)
     dist.destroy_process_group()
     sys.exit(0 if int(flag.item()) == 1 else 1)
