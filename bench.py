@@ -42,6 +42,7 @@ def parse():
                     help='grid points per dimension (default: 256 for config 2, 4000 for config 3, 128 for config 4)')
     ap.add_argument('--cpu-cycles', type=int, default=3, help='V-cycles of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extras', action='store_true', help='config 2: skip the extra measurements (plain CSR layouts, RAP, config 3)')
     ap.add_argument('--smoother', default='jacobi', choices=['jacobi', 'mcgs'],
                     help='jacobi: the BASELINE headline config; mcgs: same hierarchy with symmetric multicolour Gauss-Seidel '
                          '(gauss_seidel_indexed over MIS colours) pre/post -- an extra, non-headline measurement')
@@ -718,6 +719,145 @@ def measure_roofline(R, reps=5):
             'ungraphed_cycle_ms': round(tot, 4), 'op_ms': share}
 
 
+def measure_extras(R, args):
+    """driver-visible breadth inside the ONE bench line (config 2 only; the headline keys are untouched):
+    plain_csr -- the same cycle with the engine's coded layouts switched off (B200AMG_VALUE_DICT=0): what an operator
+                 that is NOT a constant-coefficient stencil gets (CSR streamed as stored);
+    rap       -- the Galerkin product R*A*P of level 0 on the device (time, ratio to 2 x products and to the
+                 bytes of R, A, RA, P, out) with scipy's (R*A)*P on one host core beside it;
+    config3   -- BASELINE configs[2] (RS + symmetric multicolour Gauss-Seidel, 4000^2) as value / roofline / parity."""
+    import torch
+    import pyamg_b200 as amg
+    from pyamg_b200 import sparse
+    ml = R['ml']
+    out = {}
+    peak, _ = measured_peak()
+
+    def timed_cycles(m, k):
+        st = m._stream
+        for _ in range(3):
+            m.cycle_device('V')
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(k):
+            m.cycle_device('V')
+        e1.record(st)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / k
+
+    def op_ms(m, reps=3):
+        m.profile_cycle('V')
+        acc = {}
+        for _ in range(reps):
+            for op, lev, ms in m.profile_cycle('V'):
+                acc.setdefault('%s@L%d' % (op, lev), []).append(ms)
+        return {k: float(np.mean(v)) for k, v in acc.items()}
+
+    # ---- plain CSR -----------------------------------------------------------------------------------------------
+    try:
+        old = os.environ.get('B200AMG_VALUE_DICT')
+        os.environ['B200AMG_VALUE_DICT'] = '0'
+        ml._destroy_engine()
+        ml.solve(R['b'], maxiter=0, _norms=False)
+        ms = timed_cycles(ml, args.steps)
+        ops = op_ms(ml)
+        A0 = ml.levels[0].A
+        tj = 0.5 * (ops['presmooth@L0'] + ops['postsmooth@L0'])
+        nB = jacobi_bytes(A0.shape[0], A0.nnz)
+        out['plain_csr'] = {'value': 1000.0 / ms, 'unit': 'V-cycles/s', 'ms_per_step': ms,
+                            'layouts_level0': {k: LAYOUT_NAME.get(v, str(v)) for k, v in ml.layouts()[0].items()},
+                            'jacobi_L0': {'kernel': 'csr_pipe_kernel<OP_JACOBI> (persistent TMA pipeline over CSR)',
+                                          'ms_per_launch': round(tj, 4), 'algorithmic_bytes_per_launch': nB,
+                                          'achieved_GBs': round(nB / (tj * 1e-3) / 1e9, 1), 'frac': round(nB / (tj * 1e-3) / 1e9 / peak, 4)},
+                            'residual_L0_frac': round(jacobi_bytes(A0.shape[0], A0.nnz) / (ops['residual@L0'] * 1e-3) / 1e9 / peak, 4),
+                            'how': 'same hierarchy, engine rebuilt with B200AMG_VALUE_DICT=0 (no row-pattern / value-code layouts)'}
+    except Exception as exc:                                              # noqa: BLE001
+        out['plain_csr'] = {'error': '%s: %s' % (type(exc).__name__, exc)}
+    finally:
+        if old is None:
+            os.environ.pop('B200AMG_VALUE_DICT', None)
+        else:
+            os.environ['B200AMG_VALUE_DICT'] = old
+        ml._destroy_engine()
+        ml.solve(R['b'], maxiter=0, _norms=False)
+
+    # ---- Galerkin product of level 0 -------------------------------------------------------------------------------
+    try:
+        L0 = ml.levels[0]
+        Rm, Am, Pm = L0.R, L0.A, L0.P
+        rowlen = lambda M: (M.indptr[1:] - M.indptr[:-1]).to(torch.int64)   # noqa: E731
+        best = None
+        for _ in range(2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            RA = sparse.matmat(Rm, Am, True)
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            Ac = sparse.matmat(RA, Pm, True)
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            if best is None or t2 - t0 < best[0]:
+                best = (t2 - t0, t1 - t0, t2 - t1)
+            prod1 = int(rowlen(Am)[Rm.indices.long()].sum().item())
+            prod2 = int(rowlen(Pm)[RA.indices.long()].sum().item())
+            nnz_RA, nnz_out = int(RA.nnz), int(Ac.nnz)
+            del RA, Ac
+        byt = 12 * (Rm.nnz + Am.nnz + 2 * nnz_RA + Pm.nnz + nnz_out) + 4 * (Rm.shape[0] * 3 + Am.shape[0] + Pm.shape[0])
+        rap = {'level': 0, 'device_s': round(best[0], 4), 'device_s_RA': round(best[1], 4), 'device_s_RAP': round(best[2], 4),
+               'products': [prod1, prod2], 'flops_2x_products': 2 * (prod1 + prod2),
+               'GFLOPs': round(2 * (prod1 + prod2) / best[0] / 1e9, 1),
+               'bytes_R_A_RA_P_out': byt, 'GBs_on_those_bytes': round(byt / best[0] / 1e9, 1),
+               'nnz': {'R': int(Rm.nnz), 'A': int(Am.nnz), 'RA': nnz_RA, 'P': int(Pm.nnz), 'out': nnz_out},
+               'call': 'pyamg_b200.sparse.matmat(matmat(R, A), P) in scipy output order (wall clock, synchronised, best of 2)'}
+        if not args.no_cpu_baseline:
+            Rs, As, Ps = Rm.to_scipy().tocsr(), Am.to_scipy().tocsr(), Pm.to_scipy().tocsr()
+            t0 = time.perf_counter()
+            _ = (Rs * As) * Ps
+            rap['scipy_host_s'] = round(time.perf_counter() - t0, 2)
+            rap['scipy_call'] = '(R * A) * P with scipy.sparse on 1 host core (pyamg/aggregation/aggregation.py:429), once'
+            del Rs, As, Ps, _
+        out['rap'] = rap
+    except Exception as exc:                                              # noqa: BLE001
+        out['rap'] = {'error': '%s: %s' % (type(exc).__name__, exc)}
+
+    # ---- config 3 --------------------------------------------------------------------------------------------------
+    try:
+        import argparse
+        a3 = argparse.Namespace(**vars(args))
+        a3.config, a3.grid, a3.smoother = 3, 4000, 'mcgs'
+        t0 = time.perf_counter()
+        m3, b3 = build_problem_rs(a3.grid)
+        torch.cuda.synchronize()
+        setup3 = time.perf_counter() - t0
+        m3.solve(b3, maxiter=0, _norms=False)
+        ms3 = timed_cycles(m3, args.steps)
+        ops3 = op_ms(m3)
+        A0 = m3.levels[0].A
+        sm0 = m3.levels[0].presmoother
+        K = int(len(sm0.color_ptr) - 1)
+        t_s = 0.25 * (ops3['presmooth@L0'] + ops3['postsmooth@L0'])        # one of the two sweeps of a symmetric step
+        nB = gs_sweep_bytes(A0.shape[0], A0.nnz)
+        c3 = {'workload': workload_name(a3), 'value': 1000.0 / ms3, 'unit': 'V-cycles/s', 'ms_per_step': ms3,
+              'levels': level_table(m3), 'colours_per_level': [int(len(l.presmoother.color_ptr) - 1) for l in m3.levels[:-1]],
+              'setup_s_device': round(setup3, 2),
+              'roofline': {'kernel': 'sell_gs_kernel level 0: one colour-ordered sweep = %d launches' % K,
+                           'ms_per_sweep': round(t_s, 4), 'algorithmic_bytes_per_sweep': nB,
+                           'achieved_GBs': round(nB / (t_s * 1e-3) / 1e9, 1), 'frac': round(nB / (t_s * 1e-3) / 1e9 / peak, 4)}}
+        if not args.no_cpu_baseline:
+            lv = host_levels(m3)
+            sec, kind, x_cpu = cpu_cycles_timed(lv, b3, 1, warm=1)
+            x_gpu = m3.solve(b3, maxiter=2, _norms=False)
+            c3['cpu_baseline'] = {'value': 1.0 / sec, 'unit': 'V-cycles/s', 'cores': 1, 'kind': kind,
+                                  'sample': '1 V(1,1)-cycle after 1 warm-up cycle on the same hierarchy'}
+            c3['bit_identical_x_after_2_cycles'] = bool(np.array_equal(x_gpu, x_cpu))
+        out['config3'] = c3
+        del m3
+    except Exception as exc:                                              # noqa: BLE001
+        out['config3'] = {'error': '%s: %s' % (type(exc).__name__, exc)}
+    return out
+
+
 def golden_parity(args):
     """config 2 pinned to the REAL reference at the benchmark's own size: tests/golden/ref_config2_<grid>.json holds what
     the reference (imported in the build container, tests/golden/make_ref_config2.py) produced for this exact protocol --
@@ -1061,6 +1201,9 @@ def main():
     ml = R['ml']
     vb = vcycle_bytes(ml, 2 if args.smoother == 'mcgs' else 0)
     golden = None
+    extra = None
+    if R['world'] == 1 and args.config == 2 and args.smoother == 'jacobi' and not args.no_extras:
+        extra = measure_extras(R, args)
     if R['world'] == 1:
         try:
             golden = golden_parity(args)
@@ -1084,6 +1227,8 @@ def main():
         out['parity_in_run'] = parity
     if golden is not None:
         out['parity_vs_reference_golden'] = golden
+    if extra is not None:
+        out['extra'] = extra
     print(json.dumps(out))
 
 
