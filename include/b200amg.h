@@ -163,6 +163,12 @@ int b200amg_halo_push(const double *v, int n_send, const int *send_idx, const in
                       const unsigned long long *sig_ptrs, int n_nbr, unsigned *state, void *stream);
 int b200amg_halo_wait(const unsigned long long *flag_ptrs, int n_nbr, unsigned *state,
                       long long max_spins, void *stream);
+/* push + wait as ONE kernel node (the last CTA of the push signals the neighbours, then waits for theirs): what the
+ * distributed cycle launches per halo refresh; push_state / wait_state as for the two separate calls. */
+int b200amg_halo_exchange(const double *v, int n_send, const int *send_idx, const int *dst_rank,
+                          const long long *dst_off, const unsigned long long *bases,
+                          const unsigned long long *sig_ptrs, const unsigned long long *flag_ptrs, int n_nbr,
+                          unsigned *push_state, unsigned *wait_state, long long max_spins, void *stream);
 
 /* ---- setup-phase: Galerkin product and transpose (scipy csr_matmat / csr_tocsc;
  *      pyamg/aggregation/aggregation.py:429, pyamg/classical/classical.py:174,187) -------- */
@@ -380,6 +386,10 @@ typedef struct b200amg_level_desc {
      * color_ptr as for kind 2), 7 lexicographic block_gauss_seidel (sequential on the device, exact):
      * pyamg/amg_core/relaxation.h:661-806 with the inverses of the diagonal blocks, [n / bs][bs][bs] */
     const double *Dinv;
+    /* kind 2 on a BSR(1 x 1) level: nonzero = CSR arithmetic x_i = (b_i - sum) / a_ii -- the reference's
+     * gauss_seidel_indexed converts its matrix to CSR first (relaxation.py:713) -- zero = the arithmetic of the level's
+     * format (bsr_gauss_seidel for BSR: what the lexicographic gauss_seidel dispatches to, relaxation.py:351-354) */
+    int gs_csr;
 } b200amg_level_desc;
 /* sizeof(b200amg_level_desc) as compiled: lets a binding check its mirror of the struct */
 int b200amg_level_desc_size(void);

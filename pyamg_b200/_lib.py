@@ -26,6 +26,7 @@ class LevelDesc(Structure):
         ('pre_ncoef', c_int), ('post_ncoef', c_int),
         ('pre_coef', c_double * 8), ('post_coef', c_double * 8),
         ('Dinv', p),
+        ('gs_csr', c_int),
     ]
 
 
@@ -50,6 +51,7 @@ _SIGS = {
     'b200amg_op_destroy': (c_int, [p]),
     'b200amg_halo_push': (c_int, [p, c_int, p, p, p, p, p, c_int, p, p]),
     'b200amg_halo_wait': (c_int, [p, c_int, p, c_longlong, p]),
+    'b200amg_halo_exchange': (c_int, [p, c_int, p, p, p, p, p, p, c_int, p, p, c_longlong, p]),
     'b200amg_dot': (c_int, [c_longlong, p, p, p, p, p]),
     'b200amg_dot_noalloc': (c_int, [c_longlong, p, p, p, p]),
     'b200amg_pcg_scalars': (c_int, [p, c_int, p]),

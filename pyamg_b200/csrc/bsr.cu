@@ -117,7 +117,7 @@ __device__ __forceinline__ void bsr_gs_block_row(int i, const int *__restrict__ 
 // sweep is sequential in k, so step kq is done by the lane that owns row k and its result is handed to the
 // group by a shuffle before the next step -- the order and the bits of bsr_gs_block_row, with BS times the
 // threads in flight (thread-per-block-row reached 0.41-0.53 of HBM peak, profiles/r01b/kernels_roofline.json).
-template <int BS>
+template <int BS, bool PERM>
 __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                            const double *__restrict__ Ax, double *x,
                                                            const double *__restrict__ b, const int *__restrict__ Id,
@@ -133,11 +133,12 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
     long long dptr = -1;
     if (active) {
         acc = b[(size_t)i * BS + k];
-        const int hi = Ap[i + 1];
+        const int rp = PERM ? p : i;                    // PERM: (Ap, Aj, Ax) is the colour-grouped copy, row = position
+        const int hi = Ap[rp + 1];
         // U blocks in flight: their column numbers first, then every block row / x_j operand, then the folds in
         // storage order -- one round of memory latency per U blocks instead of two per block
         constexpr int U = BS <= 4 ? 4 : 2;
-        for (int q = Ap[i]; q < hi; q += U) {
+        for (int q = Ap[rp]; q < hi; q += U) {
             int j[U];
             double bl[U][BS], xv[U][BS];
 #pragma unroll
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
 // loc = row k of block g times x_j from zero, exactly the reference's gemm (linalg.h:359-398) -- so one pass costs ONE
 // round of memory latency; then the pass's locs are subtracted from the row sums in STORAGE order (shuffled one by one
 // to the lanes 0..BS-1 that hold acc), which is the order of relaxation.h:139-144: the bits do not change.
-template <int BS, bool backward>
+template <int BS, bool backward, bool PERM>
 __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                                 const double *__restrict__ Ax, double *x,
                                                                 const double *__restrict__ b, const int *__restrict__ Id,
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
     const int i = Id[p];
     const int g = lane / BS, k = lane - g * BS;
     const bool lane_ok = g < G;
-    const int lo = Ap[i], hi = Ap[i + 1];
+    const int lo = Ap[PERM ? p : i], hi = Ap[(PERM ? p : i) + 1];
     double acc = (lane < BS) ? b[(size_t)i * BS + lane] : 0.0;
     int dptr = -1;
 #pragma unroll 2
@@ -396,21 +397,25 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
     return check_launch("bsr_jacobi_kernel");
 }
 
+// perm != 0: (Ap, Aj, Ax) is a colour-grouped copy of the operator -- its row p is block row Id[p] (bsr_color_build)
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
-                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row)
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row, bool perm)
 {
     if (p1 <= p0) return 0;
     // warp per block row where the colour is too small for lanes-per-row to fill the machine and the rows are long
     // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
-        if (backward) { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }
-        else { R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1)); }
+#define GS_WARP(BW, PM) R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, BW, PM>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1))
+        if (backward) { if (perm) { GS_WARP(true, true); } else { GS_WARP(true, false); } }
+        else { if (perm) { GS_WARP(false, true); } else { GS_WARP(false, false); } }
+#undef GS_WARP
         return check_launch("bsr_gs_color_warp_kernel");
     }
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
-    BS_SWITCH(bs, B200_LAUNCH(bsr_gs_color_kernel<BS>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward));
+    if (perm) { BS_SWITCH(bs, B200_LAUNCH((bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    else { BS_SWITCH(bs, B200_LAUNCH((bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
     return check_launch("bsr_gs_color_kernel");
 }
 

@@ -80,9 +80,70 @@ __global__ void __launch_bounds__(32) halo_wait_kernel(const unsigned long long 
     if (i == 0) state[0] = e;
 }
 
+// push and wait in ONE kernel node: the CTAs scatter and fence as in halo_push_kernel; the last CTA to arrive raises
+// this rank's epoch on the neighbours and then ALSO waits for theirs (lane i spins on neighbour i's flag cell), so the
+// kernel retires when the halo of this rank is complete.  The push never depends on a peer, so two ranks running this
+// kernel cannot block each other.  One launch per refresh instead of two (13 refreshes per distributed cycle).
+__global__ void __launch_bounds__(256) halo_exchange_kernel(const double *__restrict__ v, int n_send,
+                                                            const int *__restrict__ send_idx,
+                                                            const int *__restrict__ dst_rank,
+                                                            const long long *__restrict__ dst_off,
+                                                            const unsigned long long *__restrict__ bases,
+                                                            const unsigned long long *__restrict__ sig_ptrs,
+                                                            const unsigned long long *__restrict__ flag_ptrs, int n_nbr,
+                                                            unsigned *push_state, unsigned *wait_state, long long max_spins)
+{
+    __shared__ int s_last;
+    const int j = blockIdx.x * 256 + threadIdx.x;
+    if (j < n_send) {
+        double *dst = reinterpret_cast<double *>(bases[dst_rank[j]]) + dst_off[j];
+        *dst = v[send_idx[j]];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned prev = atomicAdd(&push_state[1], 1u);
+        s_last = (prev == gridDim.x - 1);
+        if (s_last) {
+            push_state[1] = 0;
+            const unsigned e = push_state[0] + 1;
+            push_state[0] = e;
+            __threadfence_system();
+            for (int i = 0; i < n_nbr; ++i) st_release_sys_u32(reinterpret_cast<unsigned *>(sig_ptrs[i]), e);
+        }
+    }
+    __syncthreads();
+    if (!s_last || threadIdx.x >= 32) return;
+    const unsigned e = wait_state[0] + 1;
+    const int i = threadIdx.x;
+    if (i < n_nbr) {
+        const unsigned *f = reinterpret_cast<const unsigned *>(flag_ptrs[i]);
+        long long spins = 0;
+        while ((int)(ld_acquire_sys_u32(f) - e) < 0) {
+            if (++spins > max_spins) { atomicExch(&wait_state[1], 1u); break; }
+            __nanosleep(20);
+        }
+    }
+    __syncwarp();
+    if (i == 0) wait_state[0] = e;
+}
+
 }  // namespace b200amg
 
 using namespace b200amg;
+
+extern "C" int b200amg_halo_exchange(const double *v, int n_send, const int *send_idx, const int *dst_rank,
+                                     const long long *dst_off, const unsigned long long *bases,
+                                     const unsigned long long *sig_ptrs, const unsigned long long *flag_ptrs, int n_nbr,
+                                     unsigned *push_state, unsigned *wait_state, long long max_spins, void *stream)
+{
+    if (n_send < 0 || n_nbr < 0 || n_nbr > 32) return set_err(B200AMG_EINVAL, "halo_exchange: bad sizes (0..32 neighbours)");
+    const int grid = n_send > 0 ? (n_send + 255) / 256 : 1;
+    halo_exchange_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(v, n_send, send_idx, dst_rank, dst_off, bases,
+                                                                                   sig_ptrs, flag_ptrs, n_nbr, push_state,
+                                                                                   wait_state, max_spins);
+    return check_launch("halo_exchange_kernel");
+}
 
 extern "C" int b200amg_halo_push(const double *v, int n_send, const int *send_idx, const int *dst_rank,
                                  const long long *dst_off, const unsigned long long *bases,

@@ -50,6 +50,7 @@ struct RowPat {
     unsigned char *codes = nullptr;  // [n]
     RowPatEntry *table = nullptr;    // [npat * 8]
     int npat = 0, n = 0, far = 0;    // far = largest column offset in the table
+    int xlen = 0;                    // entries of x the operator may reference (> n on a row slab with halo columns)
     int common_len = 0;              // entries of the typical (middle) row
     // plan of the TMA-staged sweep (rowpat_tile.cu), made from the typical row's pattern; tile_ok == false: not eligible
     bool tile_ok = false;
@@ -107,7 +108,17 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
 int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const double *Ax, const double *xin,
                double *xout, const double *b, double omega, cudaStream_t st);
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
-                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row = -1.0);
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row = -1.0,
+                 bool perm = false);
+// colour-grouped copy of a BSR operator for colour-ordered block Gauss-Seidel (row p = block row Id[p]); rp == nullptr: none
+struct BsrColor {
+    int *rp = nullptr, *cj = nullptr;
+    double *cx = nullptr;
+    bool ok() const { return rp != nullptr; }
+};
+int bsr_color_build(int nb, int bs, long long nblocks, const int *Ap, const int *Aj, const double *Ax, const int *Id,
+                    BsrColor *out, cudaStream_t st);
+void bsr_color_free(BsrColor *c);
 int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                       const int *Id, int start, int stop, int step, cudaStream_t st);
 

@@ -121,6 +121,9 @@ __global__ void __launch_bounds__(256) rowpat_encode_kernel(int n_row, const int
         }
         if (good) codes[row] = (unsigned char)p;
         else flags[2] = 1;
+        int mc = -1;                                        // flags[3] = largest column referenced (x has more entries
+        for (int k = s; k < e; ++k) mc = max(mc, Aj[k]);    // than the operator has rows on a row slab with halo columns)
+        if (mc > flags[3]) atomicMax(&flags[3], mc);
     }
 }
 
@@ -229,6 +232,7 @@ int rowpat_build(int n_row, long long nnz, const int *Ap, const int *Aj, const d
                 out->table = table;
                 out->npat = npat;
                 out->n = n_row;
+                out->xlen = std::max(n_row, flags[3] + 1);
                 // segments / masks of the TMA-staged sweep, made from the MOST FREQUENT pattern (the middle row of a
                 // structured grid sits on two faces)
                 unsigned *d_hist = nullptr, h_hist[256];

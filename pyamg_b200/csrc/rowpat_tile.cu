@@ -49,6 +49,7 @@ constexpr int TT_SMEM_LIMIT = 227 * 1024 / TT_RESIDENT - 1024;
 
 struct TileArgs {
     int n, nseg;
+    int xlen;                                                         // entries of x (>= n: halo columns of a row slab)
     int seg_lo[TT_MAXSEG], seg_len[TT_MAXSEG], seg_base[TT_MAXSEG];   // elements; lo relative to the chunk's first row
     int xs_elems;                                                     // doubles of x per stage
     int sbase[RP_TILE_LEN];                                           // x of entry q for chunk row i: xs[sbase[q] + i]
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
             for (int s = 0; s < TT_MAXSEG; ++s) {
                 const long long g0 = r0 + a.seg_lo[s], g1 = g0 + a.seg_len[s];
                 c0[s] = g0 < 0 ? 0 : g0;
-                c1[s] = s < a.nseg ? (g1 < a.n ? g1 : (long long)a.n) : c0[s];
+                c1[s] = s < a.nseg ? (g1 < a.xlen ? g1 : (long long)a.xlen) : c0[s];
                 if (c1[s] > c0[s]) bytes += (uint32_t)((c1[s] - c0[s]) & ~1ll) * 8u;
             }
             const int nb = (int)(a.n - r0 < TT_CH ? a.n - r0 : TT_CH);          // rows of this chunk
@@ -308,6 +309,7 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     }
     TileArgs a;
     a.n = r.n;
+    a.xlen = r.xlen;
     a.nseg = r.nseg;
     for (int i = 0; i < TT_MAXSEG; ++i) { a.seg_lo[i] = r.seg_lo[i]; a.seg_len[i] = r.seg_len[i]; a.seg_base[i] = r.seg_base[i]; }
     a.xs_elems = r.xs_elems;

@@ -20,6 +20,7 @@ struct LevelRt {
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
+    BsrColor bGS;                             // the same for a block operator (bsr.cu)
     RowPat rpA;                               // one byte per row of a stencil operator (rowpat.cu)
     ValueDict dA, dP, dR;                     // 8-bit value codes of operators with <= 256 distinct values
     std::vector<int> color_ptr;
@@ -53,6 +54,7 @@ static void free_level(LevelRt &L)
     sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
     dict_free(&L.dA); dict_free(&L.dP); dict_free(&L.dR);
     rowpat_free(&L.rpA);
+    bsr_color_free(&L.bGS);
 }
 
 // B200AMG_VALUE_DICT=0 switches the value dictionary off (A/B measurements)
@@ -159,9 +161,12 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
                     const int c = bwd ? K - 1 - q : q;
                     const int p0 = L.color_ptr[c], p1 = L.color_ptr[c + 1];
                     if (d.bs == 1 && L.sGS.ok())
-                        B200_TRY(sell_gs_color(d.flavor != 0, L.sGS, d.Id, p0, p1, *cur, b, st));
+                        B200_TRY(sell_gs_color(d.flavor != 0 && !d.gs_csr, L.sGS, d.Id, p0, p1, *cur, b, st));
                     else if (d.bs == 1)
-                        B200_TRY(gs_rows(d.flavor != 0, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
+                        B200_TRY(gs_rows(d.flavor != 0 && !d.gs_csr, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
+                    else if (L.bGS.ok())
+                        B200_TRY(bsr_gs_color(d.bs, L.bGS.rp, L.bGS.cj, L.bGS.cx, *cur, b, d.Id, p0, p1, bwd, st,
+                                              (double)L.nzA / (double)(d.n / d.bs), true));
                     else
                         B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st,
                                               (double)L.nzA / (double)(d.n / d.bs)));
@@ -389,6 +394,12 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
         if (!src && L.d.bs == 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 &&
             L.color_ptr[0] == 0 && L.color_ptr[L.d.K] == L.d.n && L.d.n >= 128)
             src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sGS, nullptr, L.d.Id);
+        // ... and the block form: rows of a colour contiguous (B200AMG_BSR_COLOR_COPY=0: A/B switch)
+        if (!src && L.d.bs > 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 && L.color_ptr[0] == 0 &&
+            L.color_ptr[L.d.K] == L.d.n / L.d.bs && L.d.n / L.d.bs >= 200000) {   // large levels only: no gain on small ones (run 7)
+            const char *ev = getenv("B200AMG_BSR_COLOR_COPY");
+            if (!(ev && ev[0] == '0')) src = bsr_color_build(L.d.n / L.d.bs, L.d.bs, nzA, L.d.Ap, L.d.Aj, L.d.Ax, L.d.Id, &L.bGS, nullptr);
+        }
         if (src) {
             free_level(L);
             for (auto &Lp : E->lev) free_level(Lp);

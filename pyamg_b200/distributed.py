@@ -73,6 +73,19 @@ class DeviceBackend:
         self._lib.call('b200amg_scale_diag', diag.numel(), float(omega), b.data_ptr(), diag.data_ptr(), x.data_ptr(),
                        int(flavor), self.stream())
 
+    def gs_color(self, op, x, b, Id, p0, p1, flavor):
+        """rows Id[p0:p1] (one colour of the GLOBAL colouring, local numbering) relaxed in parallel, x in place:
+        amg_core.gauss_seidel_indexed / bsr_gauss_seidel(bs = 1) arithmetic (relaxation.h:394-426, :89-173)"""
+        if p1 <= p0:
+            return
+        cp = (ctypes.c_int * 2)(int(p0), int(p1))
+        if flavor:
+            self._lib.call('b200amg_bsr_gauss_seidel', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
+                           b.data_ptr(), int(p0), int(p1), 1, 1, Id.data_ptr(), cp, 1, self.stream())
+        else:
+            self._lib.call('b200amg_gauss_seidel_indexed', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
+                           b.data_ptr(), Id.data_ptr(), int(p0), int(p1), 1, cp, 1, self.stream())
+
     def dot(self, x, y, n):
         if not hasattr(self, '_dw'):
             self._dw = torch.empty(1024, dtype=torch.float64, device=self.device)
@@ -109,10 +122,15 @@ def describe(ml):
                 raise NotImplementedError('distributed cycle: scalar (1x1 block) levels only')
         pre, post = L.presmoother, L.postsmoother
         for sm in (pre, post):
-            if sm.kind not in (0, 1):
-                raise NotImplementedError('distributed cycle: Jacobi / None smoothers only')
+            if sm.kind not in (0, 1, 2):
+                raise NotImplementedError('distributed cycle: Jacobi, colour-ordered Gauss-Seidel or None smoothers only')
         d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
-             'pre': (pre.kind, pre.omega, pre.iterations), 'post': (post.kind, post.omega, post.iterations)}
+             'pre': (pre.kind, pre.omega, pre.iterations, pre.sweep), 'post': (post.kind, post.omega, post.iterations, post.sweep)}
+        ordered = [sm for sm in (pre, post) if sm.kind == 2]
+        if ordered:                                     # one GLOBAL colour ordering per level (multilevel._build_engine checks it)
+            d['Id'] = ordered[0].indices
+            d['color_ptr'] = [int(v) for v in ordered[0].color_ptr]
+            d['gs_csr'] = int(ordered[0].name in ('gauss_seidel_indexed', 'multicolor_gauss_seidel'))
         for nm in ('A', 'P', 'R'):
             M = getattr(L, nm)
             d[nm] = (M.indptr, M.indices, M.data)
@@ -145,6 +163,8 @@ class DistributedSolver:
         self.device = device if device is not None else self.be.device
         self.exchanges = 0
         self.halo_mode = halo
+        import os
+        self._fused_halo = os.environ.get('B200AMG_HALO_FUSED', '1') != '0'    # one kernel node per refresh (A/B switch)
         self._p2p = None
         self._graph = None
         self._prof = None
@@ -161,6 +181,9 @@ class DistributedSolver:
                     ka = k
                     break
             info = [{q: levels[k][q] for q in ('n', 'nc', 'flavor', 'pre', 'post')} for k in range(ka)]
+            for k in range(ka):
+                info[k]['K'] = len(levels[k]['color_ptr']) - 1 if 'color_ptr' in levels[k] else 0
+                info[k]['gs_csr'] = int(levels[k].get('gs_csr', 1))
             meta[0] = {'ka': ka, 'nlev': nlev, 'levels': info}
         dist.broadcast_object_list(meta, src=0, group=group)
         meta = meta[0]
@@ -214,6 +237,26 @@ class DistributedSolver:
             setattr(L, nm, self.be.make_op(ip, ix, dx, ip.numel() - 1))
             setattr(L, 'plan' + nm, plan)
         L.diag = L.A.diagonal()
+        # colour-ordered Gauss-Seidel: the GLOBAL colouring cut by slab -- every rank keeps, colour by colour, the rows of
+        # its slab in local numbering (ascending inside a colour like the global list), so a colour step relaxes the
+        # same rows with the same operands as the single-GPU sweep once the halo is fresh
+        L.Id, L.cptr = None, None
+        if info.get('K', 0) > 0:
+            parts = [None] * G
+            if rank == 0:
+                Id = torch.as_tensor(src['Id']).to(torch.int64).cpu()
+                cp = src['color_ptr']
+                for p in range(G):
+                    segs, ptr = [], [0]
+                    for c in range(len(cp) - 1):
+                        seg = Id[cp[c]:cp[c + 1]]
+                        seg = seg[(seg >= sp[p]) & (seg < sp[p + 1])] - sp[p]
+                        segs.append(seg)
+                        ptr.append(ptr[-1] + int(seg.numel()))
+                    parts[p] = (torch.cat(segs).to(torch.int32) if segs else torch.zeros(0, dtype=torch.int32), ptr)
+            got = [None]
+            dist.scatter_object_list(got, parts if rank == 0 else None, src=0, group=self.group)
+            L.Id, L.cptr = got[0][0].to(dev).contiguous(), got[0][1]
         return L
 
     def _alloc(self):
@@ -361,10 +404,16 @@ class DistributedSolver:
         if self._p2p is not None:
             ent = self._p2p['plans'][id(plan)]
             lib, st, nn = self.be._lib, self.be.stream(), len(self._p2p['nbr'])
-            lib.call('b200amg_halo_push', v.data_ptr(), ent['n_send'], ent['send_idx'].data_ptr(), ent['dst_rank'].data_ptr(),
-                     ent['dst_off'].data_ptr(), ent['bases'][v.data_ptr()].data_ptr(), ent['sig'].data_ptr(), nn,
-                     ent['push_state'].data_ptr(), st)
-            lib.call('b200amg_halo_wait', ent['flg'].data_ptr(), nn, ent['wait_state'].data_ptr(), 1 << 24, st)
+            if self._fused_halo:
+                lib.call('b200amg_halo_exchange', v.data_ptr(), ent['n_send'], ent['send_idx'].data_ptr(),
+                         ent['dst_rank'].data_ptr(), ent['dst_off'].data_ptr(), ent['bases'][v.data_ptr()].data_ptr(),
+                         ent['sig'].data_ptr(), ent['flg'].data_ptr(), nn, ent['push_state'].data_ptr(),
+                         ent['wait_state'].data_ptr(), 1 << 24, st)
+            else:
+                lib.call('b200amg_halo_push', v.data_ptr(), ent['n_send'], ent['send_idx'].data_ptr(), ent['dst_rank'].data_ptr(),
+                         ent['dst_off'].data_ptr(), ent['bases'][v.data_ptr()].data_ptr(), ent['sig'].data_ptr(), nn,
+                         ent['push_state'].data_ptr(), st)
+                lib.call('b200amg_halo_wait', ent['flg'].data_ptr(), nn, ent['wait_state'].data_ptr(), 1 << 24, st)
             self.exchanges += 1
             self._mark('exchange')
             return
@@ -391,10 +440,26 @@ class DistributedSolver:
 
     # ---- the cycle (multilevel.py:473-548 on slabs) ----------------------------------------------
     def _smooth(self, L, spec, x, xs, b, x_is_zero):
-        kind, omega, iters = spec
+        kind, omega, iters = spec[:3]
         if kind == 0 or iters == 0:
             if x_is_zero:
                 x[:L.n_own].zero_()
+            return x, xs
+        if kind == 2:
+            # colour-ordered Gauss-Seidel over the GLOBAL colours (relaxation.h:394-426 semantics): one halo refresh
+            # per colour, then this rank's rows of the colour in parallel; bit-identical to the single-GPU sweep
+            sweep = spec[3] if len(spec) > 3 else 'forward'
+            if x_is_zero:
+                x[:L.n_own].zero_()
+            K = len(L.cptr) - 1
+            for _ in range(iters):
+                for backward in (False, True):
+                    if (sweep == 'forward' and backward) or (sweep == 'backward' and not backward):
+                        continue
+                    for q in range(K):
+                        c = K - 1 - q if backward else q
+                        self.exchange(L.planA, x)
+                        self.be.gs_color(L.A, x, b, L.Id, L.cptr[c], L.cptr[c + 1], L.info['flavor'] and not L.info.get('gs_csr', 1))
             return x, xs
         op = OP_JACOBI_BSR1 if L.info['flavor'] else OP_JACOBI
         for it in range(iters):

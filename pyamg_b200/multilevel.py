@@ -229,6 +229,9 @@ class multilevel_solver:
                 cp = np.ascontiguousarray(s0.color_ptr, dtype=np.intc)
                 keep += [Id, cp]
                 d.Id, d.K = _ptr(Id), len(cp) - 1
+                # gauss_seidel_indexed (and the multicolour construct over it) works on the CSR form of the matrix in
+                # the reference (relaxation.py:713); the lexicographic gauss_seidel keeps the level's format
+                d.gs_csr = int(s0.name in ('gauss_seidel_indexed', 'multicolor_gauss_seidel'))
                 d.color_ptr_host = cp.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
         lib = _lib.load()
         nbytes = lib.b200amg_vcycle_work_bytes(nlev, descs)

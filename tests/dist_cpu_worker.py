@@ -74,6 +74,18 @@ class CpuBackend:
             v = (omega * bn) / dn if flavor else omega * (bn / dn)
         x.numpy()[:n] = np.where(dn != 0, v, 0.0)
 
+    def gs_color(self, op, x, b, Id, p0, p1, flavor):
+        if p1 <= p0:
+            return
+        xn, bn = x.numpy(), np.ascontiguousarray(b.numpy()[:op.n])
+        idx = np.ascontiguousarray(Id.numpy(), dtype=np.intc)
+        xc = np.ascontiguousarray(xn)
+        if flavor:
+            oracle.port.bsr_gauss_seidel_indexed(op.ip, op.ix, op.dx, xc, bn, idx, int(p0), int(p1), 1, 1)
+        else:
+            oracle.port.gauss_seidel_indexed(op.ip, op.ix, op.dx, xc, bn, idx, int(p0), int(p1), 1)
+        xn[:] = xc
+
     def dot(self, x, y, n):
         return torch.tensor([float(np.dot(x.numpy()[:n], y.numpy()[:n]))], dtype=torch.float64)
 
@@ -99,6 +111,7 @@ def t3(M):
 
 def main():
     grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    mcgs = len(sys.argv) > 4 and sys.argv[4] == 'mcgs'
     dist.init_process_group('gloo')
     rank = dist.get_rank()
     D = _load('distributed')
@@ -114,6 +127,12 @@ def main():
             d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
                  'pre': (1, L.pre[1]['omega'], 1), 'post': (1, L.post[1]['omega'], 1),
                  'A': t3(L.A), 'P': t3(L.P), 'R': t3(L.R)}
+            if mcgs:        # symmetric multicolour Gauss-Seidel over the MIS colours of the GLOBAL matrix graph
+                from oracle import relaxation as orx
+                idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(sp.csr_matrix(L.A), oracle.port))
+                L.pre = L.post = ('gauss_seidel_indexed', {'indices': idx, 'sweep': 'symmetric', 'iterations': 1})
+                d['pre'] = d['post'] = (2, 1.0, 1, 'symmetric')
+                d['Id'], d['color_ptr'] = torch.from_numpy(np.ascontiguousarray(idx, np.int32)), [int(v) for v in ptr]
             levels_desc.append(d)
         coarse = lambda ka: CoarseOracle(host[ka:])
     S = D.DistributedSolver(levels_desc, coarse, agglomerate_below=thresh, backend=CpuBackend())

@@ -13,6 +13,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    mcgs = len(sys.argv) > 4 and sys.argv[4] == 'mcgs'
     local = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local)
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
@@ -26,6 +27,9 @@ def main():
         jac = ('jacobi', {'omega': 4.0 / 3.0})
         ml = amg.smoothed_aggregation_solver(A, presmoother=jac, postsmoother=jac, max_coarse=40, improve_candidates=None)
         b = np.random.rand(A.shape[0])
+        if mcgs:            # symmetric multicolour Gauss-Seidel over GLOBAL MIS colours on every level
+            mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+            amg.change_smoothers(ml, mc, mc)
     S = DistributedSolver.from_ml(ml, agglomerate_below=thresh)
     res = []
     x = S.solve(b, tol=1e-30, maxiter=cycles, residuals=res)
@@ -37,6 +41,22 @@ def main():
         ok = same and np.allclose(res, ref, rtol=1e-12, atol=0)
         print('world', world, 'partitioned levels', len(S.levels), 'of', S.nlev, 'exchanges', S.exchanges,
               'bit-identical x', same, 'res', res[-1], ref[-1], flush=True)
+    # slab-local I/O: every rank loads its own slab of b / stores its own slab of x through pinned host memory
+    S.load(b)
+    lo, hi = S.slab()
+    b_loc = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    b_loc.copy_(S.levels[0].b[:hi - lo])
+    torch.cuda.synchronize()
+    S.load_local(b_loc)
+    for _ in range(cycles):
+        S.cycle()
+    x_loc = S.store_local(torch.empty(hi - lo, dtype=torch.float64).pin_memory())
+    torch.cuda.synchronize()
+    S.check_halo()
+    xg = S.gather_x()
+    if rank == 0:
+        ok = ok and bool(torch.equal(xg, xr)) and bool(torch.equal(x_loc, xr[lo:hi].cpu()))
+        print('slab-local x bit-identical', bool(torch.equal(x_loc, xr[lo:hi].cpu())), flush=True)
     flag = torch.tensor([1 if ok else 0], device='cuda')
     dist.broadcast(flag, 0)
     dist.destroy_process_group()

@@ -10,11 +10,11 @@ import pytest
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def run(world, grid, thresh, cycles, port):
+def run(world, grid, thresh, cycles, port, *extra):
     env = dict(os.environ, MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), OMP_NUM_THREADS='1')
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
            '--master-addr', '127.0.0.1', '--master-port', str(port), os.path.join(HERE, 'dist_cpu_worker.py'),
-           str(grid), str(thresh), str(cycles)]
+           str(grid), str(thresh), str(cycles)] + list(extra)
     return subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
 
 
@@ -30,3 +30,12 @@ def test_partitioned_cycle_equals_global(world, grid, thresh):
     assert 'bit-identical x True' in r.stdout
     if (grid, thresh) == (14, 5):
         assert 'partitioned levels 3 of 4' in r.stdout
+
+
+@pytest.mark.parametrize('world,grid,thresh', [(2, 10, 50), (3, 9, 30)])
+def test_partitioned_multicolour_gauss_seidel_equals_global(world, grid, thresh):
+    """colour-ordered Gauss-Seidel with GLOBAL colours on the partitioned levels (one halo refresh per
+    colour): bit-identical to the single-process sweep"""
+    r = run(world, grid, thresh, 3, 29600 + world * 10 + grid, 'mcgs')
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert 'bit-identical x True' in r.stdout
