@@ -625,3 +625,28 @@ class DistributedSolver:
         self.check_halo()
         x = self.gather_x()
         return x
+
+
+class _Participant:
+    """What a rank WITHOUT the hierarchy holds in place of the multilevel_solver: its solve() joins the collective
+    that rank 0 enters through `ml.solve(b, distributed=True)`, with the same keyword arguments."""
+
+    def __init__(self, **kw):
+        self._kw, self._S = kw, None
+
+    def solver(self):
+        if self._S is None:
+            self._S = DistributedSolver.from_ml(None, **self._kw)
+        return self._S
+
+    def solve(self, b=None, x0=None, tol=1e-5, maxiter=100, cycle='V', residuals=None, **ignored):
+        if str(cycle).upper() != 'V':
+            raise NotImplementedError('distributed solve: V-cycles only')
+        return self.solver().solve(None, None, tol=tol, maxiter=maxiter, residuals=residuals)
+
+
+def participant(**kw):
+    """the stand-in for `ml` on the ranks that do not hold the hierarchy (rank != 0):
+        ml = b200.smoothed_aggregation_solver(A, ...) if rank == 0 else b200.distributed.participant()
+        x = ml.solve(b if rank == 0 else None, tol=1e-8, distributed=True)       # collective; x on rank 0"""
+    return _Participant(**kw)

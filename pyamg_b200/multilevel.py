@@ -387,17 +387,36 @@ class multilevel_solver:
             return self.solve(b, maxiter=1, cycle=cycle, tol=1e-12, _norms=False)
         return LinearOperator(shape, matvec, dtype=np.float64)
 
+    def distributed_solver(self, **kw):
+        """the row-partitioned solver over the ranks of torch.distributed for this hierarchy (collective; cached):
+        the other ranks hold pyamg_b200.distributed.participant() in place of this object"""
+        if getattr(self, '_dist', None) is None:
+            from .distributed import DistributedSolver
+            self._dist = DistributedSolver.from_ml(self, **kw)
+        return self._dist
+
     def solve(self, b, x0=None, tol=1e-5, maxiter=100, cycle='V', accel=None, callback=None, residuals=None,
-              return_residuals=False, _norms=True, _alias_out=False):
+              return_residuals=False, _norms=True, _alias_out=False, distributed=False):
         """Same contract as the reference's solve (multilevel.py:316-471): relative-residual
         stopping test `||r_k|| <= tol * ||b||`, residual history appended to `residuals`,
         `callback(x)` after every cycle.  numpy in -> numpy out, torch CUDA in -> torch CUDA out, torch CPU (pinned) in
         -> torch CPU out (a fresh tensor; `_alias_out=True` hands out the solver's persistent pinned buffer instead,
         which the next call overwrites).  `_norms=False` skips the residual norms (fixed `maxiter` cycles): what
-        aspreconditioner's matvec needs."""
+        aspreconditioner's matvec needs.  `distributed=True` (one process per GPU, torch.distributed initialised): the
+        same call on the row-partitioned hierarchy; collective -- the other ranks call
+        pyamg_b200.distributed.participant().solve(distributed=True); x comes back on this rank."""
         cycle = str(cycle).upper()
         if cycle not in _CYCLE and cycle != 'AMLI':
             raise TypeError('Unrecognized cycle type (%s)' % cycle)
+        if distributed:
+            # one process per GPU (torch.distributed initialised): the fine levels are cut into row slabs over the
+            # ranks, halos refreshed over NVLink, coarse levels agglomerated here (distributed.py); same stopping rule
+            if cycle != 'V' or accel is not None or callback is not None:
+                raise NotImplementedError('distributed solve: plain V-cycles (no accel / callback)')
+            res = [] if residuals is None else residuals
+            x = self.distributed_solver().solve(b, x0, tol=tol, maxiter=maxiter, residuals=res)
+            out = x if isinstance(b, torch.Tensor) else x.cpu().numpy().reshape(np.shape(b))
+            return (out, res) if return_residuals else out
         if accel is not None:
             from . import krylov
             return krylov.accelerated_solve(self, accel, b, x0, tol, maxiter, cycle, callback, residuals)

@@ -30,9 +30,20 @@ def main():
         if mcgs:            # symmetric multicolour Gauss-Seidel over GLOBAL MIS colours on every level
             mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
             amg.change_smoothers(ml, mc, mc)
-    S = DistributedSolver.from_ml(ml, agglomerate_below=thresh)
+    # the public call: rank 0 holds the hierarchy, the others a participant; solve(distributed=True) is collective
+    from pyamg_b200.distributed import participant
     res = []
-    x = S.solve(b, tol=1e-30, maxiter=cycles, residuals=res)
+    if rank == 0:
+        x = ml.solve(torch.from_numpy(b).cuda(), tol=1e-30, maxiter=cycles, residuals=res, distributed=True)
+        S = ml.distributed_solver()
+    else:
+        me = participant()
+        x = me.solve(tol=1e-30, maxiter=cycles, residuals=res, distributed=True)
+        S = me.solver()
+    assert isinstance(S, DistributedSolver)
+    if thresh != 200:                                     # explicit agglomeration threshold: a second solver
+        S = DistributedSolver.from_ml(ml, agglomerate_below=thresh)
+        x = S.solve(b, tol=1e-30, maxiter=cycles, residuals=res)
     ok = True
     if rank == 0:
         ref = []
