@@ -521,7 +521,9 @@ def run_distributed(args):
         peak, how = measured_peak()
         ach = nB / (t_j * 1e-3) / 1e9
         val = world * 1000.0 / ms_step
-        out = {'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1)' % args.grid,
+        gd = grid_dims(args.grid, world)
+        out = {'metric': 'V-cycles/sec, 3D Poisson %d^3 SA (Jacobi 4/3), V(1,1) [x %d row slabs of %d^3: global problem %dx%dx%d, '
+                         'value = n_gpus x distributed V-cycles/s]' % (args.grid, world, args.grid, gd[0], gd[1], gd[2]),
                'value': val, 'unit': 'V-cycles/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
                'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
                'dtype': 'f64', 'data': 'synthetic',

@@ -44,7 +44,7 @@ struct __align__(16) RowPatEntry {
     double v;
     int off, len;                    // column offset (Aj - row); len = entries of the whole pattern
 };
-constexpr int RP_TILE_MAXSEG = 4;    // contiguous x segments a chunk of rows gathers from (rowpat_tile.cu)
+constexpr int RP_TILE_MAXSEG = 8;    // contiguous x segments a chunk of rows gathers from (rowpat_tile.cu)
 constexpr int RP_TILE_LEN = 8;       // == RP_LEN
 struct RowPat {
     unsigned char *codes = nullptr;  // [n]
@@ -54,8 +54,8 @@ struct RowPat {
     int common_len = 0;              // entries of the typical (middle) row
     // plan of the TMA-staged sweep (rowpat_tile.cu), made from the typical row's pattern; tile_ok == false: not eligible
     bool tile_ok = false;
-    int tile_len = 0, nseg = 0, xs_elems = 0;
-    int seg_lo[RP_TILE_MAXSEG] = {0, 0, 0, 0}, seg_len[RP_TILE_MAXSEG] = {0, 0, 0, 0}, seg_base[RP_TILE_MAXSEG] = {0, 0, 0, 0};
+    int tile_len = 0, nseg = 0, xs_elems = 0, tile_stages = 0;
+    int seg_lo[RP_TILE_MAXSEG] = {}, seg_len[RP_TILE_MAXSEG] = {}, seg_base[RP_TILE_MAXSEG] = {};
     int sbase[RP_TILE_LEN] = {0, 0, 0, 0, 0, 0, 0, 0};
     double cval[RP_TILE_LEN] = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned short *tmask = nullptr; // [256] device: presence mask of every pattern relative to the typical one
@@ -82,6 +82,7 @@ struct Sell {
     unsigned char *cc = nullptr;     // [padded]   8-bit value codes into dict[256]
     double *dict = nullptr;
     int *row_len = nullptr;          // [n]
+    int max_w = 0;                   // widest slice (slots per row); 0 = not measured (large operators)
     bool ok() const { return cj != nullptr; }
 };
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,

@@ -27,7 +27,7 @@
 #define TT_CHUNK 1024
 #endif
 #ifndef TT_STAGES
-#define TT_STAGES 3
+#define TT_STAGES 4          // most ring stages the plan may use; it takes as many (>= 2) as fit the CTA's shared memory
 #endif
 #ifndef TT_RESIDENT
 #define TT_RESIDENT 2
@@ -39,7 +39,7 @@
 namespace b200amg {
 
 constexpr int TT_CH = TT_CHUNK;
-constexpr int TT_ST = TT_STAGES;
+constexpr int TT_MAX_ST = TT_STAGES;
 constexpr int TT_CONS = TT_CONSUMERS;           // consumer threads
 constexpr int TT_TPB = TT_CONS + 32;            // + producer warp
 constexpr int TT_RPT = TT_CH / TT_CONS;         // rows per consumer thread and chunk
@@ -49,6 +49,7 @@ constexpr int TT_SMEM_LIMIT = 227 * 1024 / TT_RESIDENT - 1024;
 
 struct TileArgs {
     int n, nseg;
+    int nst;                                                          // ring stages (2..TT_MAX_ST)
     int xlen;                                                         // entries of x (>= n: halo columns of a row slab)
     int seg_lo[TT_MAXSEG], seg_len[TT_MAXSEG], seg_base[TT_MAXSEG];   // elements; lo relative to the chunk's first row
     int xs_elems;                                                     // doubles of x per stage
@@ -102,7 +103,8 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
     constexpr int QD = LEN / 2;                                  // the diagonal sits in the middle of the common pattern
     extern __shared__ __align__(128) unsigned char tt_smem[];
-    // stage s: [x: xs_elems doubles][b: CH doubles][codes: CH bytes]; then mask[256], full[ST], empty[ST]
+    // stage s: [x: xs_elems doubles][b: CH doubles][codes: CH bytes]; then mask[256], full[nst], empty[nst]
+    const int TT_ST = a.nst;
     const int stage_bytes = (a.xs_elems + (NEED_B ? TT_CH : 0)) * 8 + TT_CH;
     unsigned short *s_mask = reinterpret_cast<unsigned short *>(tt_smem + (size_t)TT_ST * stage_bytes);
     uint64_t *full = reinterpret_cast<uint64_t *>(tt_smem + (size_t)TT_ST * stage_bytes + 512);
@@ -260,7 +262,11 @@ void rowpat_tile_plan(RowPat *r, const std::vector<RowPatEntry> &ht, int common)
     }
     r->nseg = nseg;
     r->xs_elems = base;
-    if ((long long)TT_ST * ((long long)(base + TT_CH) * 8 + TT_CH) + 512 + 2 * TT_ST * 8 > TT_SMEM_LIMIT) return;
+    // as many ring stages as fit (3 for the 7-point stencil on 256-point grid lines, 2 on 512-point lines)
+    int nst = TT_MAX_ST;
+    while (nst >= 2 && (long long)nst * ((long long)(base + TT_CH) * 8 + TT_CH) + 512 + 2 * nst * 8 > TT_SMEM_LIMIT) --nst;
+    if (nst < 2) return;
+    r->tile_stages = nst;
     for (int q = 0; q < L; ++q) {
         r->sbase[q] = r->seg_base[seg_of[q]] + (off[q] - r->seg_lo[seg_of[q]]);
         r->cval[q] = val[q];
@@ -301,7 +307,7 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
         B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     }
     constexpr bool NEED_B = (OP == OP_RESIDUAL || OP >= OP_JACOBI);
-    const int smem = TT_ST * ((r.xs_elems + (NEED_B ? TT_CH : 0)) * 8 + TT_CH) + 512 + 2 * TT_ST * 8;
+    const int smem = r.tile_stages * ((r.xs_elems + (NEED_B ? TT_CH : 0)) * 8 + TT_CH) + 512 + 2 * r.tile_stages * 8;
     static bool attr_set = false;
     if (!attr_set) {
         B200_CUDA(cudaFuncSetAttribute(rowpat_tile_kernel<OP, LEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_LIMIT));
@@ -309,6 +315,7 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     }
     TileArgs a;
     a.n = r.n;
+    a.nst = r.tile_stages;
     a.xlen = r.xlen;
     a.nseg = r.nseg;
     for (int i = 0; i < TT_MAXSEG; ++i) { a.seg_lo[i] = r.seg_lo[i]; a.seg_len[i] = r.seg_len[i]; a.seg_base[i] = r.seg_base[i]; }

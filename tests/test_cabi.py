@@ -223,3 +223,39 @@ def test_host_naive_aggregation_equals_reference():
         k = amg_core.naive_aggregation(n, Ap, Aj, a, r)
         k2 = oracle.ref.naive_aggregation(n, Ap, Aj, a2, r2)
         assert k == k2 and np.array_equal(a, a2 - 1) and np.array_equal(r[:k], r2[:k2])
+
+
+def test_gs_wavefronts_host_gives_the_sequential_sweep():
+    """b200amg_gs_wavefronts_host: rows grouped by level, levels in ascending (descending) order with the rows of a
+    level updated TOGETHER from the values before the level, reproduce the lexicographic forward (backward)
+    Gauss-Seidel sweep of the reference kernel bit for bit -- symmetric and non-symmetric patterns, empty rows"""
+    from pyamg_b200 import amg_core
+    rng = np.random.RandomState(8)
+    n = 700
+    rows = np.repeat(np.arange(n), 3)
+    cols = np.clip(rows + rng.randint(-25, 26, rows.size), 0, n - 1)
+    N = sp.coo_matrix((rng.rand(rows.size) - 0.5, (rows, cols)), shape=(n, n)).tocsr()
+    N = sp.csr_matrix(N + sp.diags(np.full(n, 3.0)))
+    from helpers_mats import poisson3d
+    for A in (N, sp.csr_matrix(poisson3d(7))):
+        A.sort_indices()
+        m = A.shape[0]
+        lvl = np.empty(m, np.intc)
+        K = amg_core.gs_wavefronts(m, A.indptr.astype(np.intc), A.indices.astype(np.intc), lvl)
+        assert lvl.min() == 0 and lvl.max() == K - 1
+        C = sp.coo_matrix(A + A.T)
+        lt = C.row < C.col
+        assert np.all(lvl[C.row[lt]] < lvl[C.col[lt]])
+        x0, b = rng.rand(m), rng.rand(m)
+        for sweep, order in (('forward', range(K)), ('backward', range(K - 1, -1, -1))):
+            want = x0.copy()
+            orx.gauss_seidel(A, want, b, sweep=sweep, core=oracle.port)
+            x = x0.copy()
+            for L in order:
+                new = x.copy()
+                for i in np.where(lvl == L)[0]:
+                    one = x.copy()
+                    orx.gauss_seidel_indexed(A, one, b, np.array([i], dtype=np.intc), core=oracle.port)
+                    new[i] = one[i]
+                x = new
+            assert np.array_equal(x, want), sweep

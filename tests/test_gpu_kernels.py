@@ -363,6 +363,16 @@ def stencil_many_row_patterns(rng):
     return A
 
 
+def poisson3d_box(nx, ny, nz):
+    """7-point Laplacian on an nx x ny x nz box, x fastest: column offsets +-1, +-nx, +-nx*ny"""
+    Tx, Ty, Tz = lap1d(nx), lap1d(ny), lap1d(nz)
+    Ix, Iy, Iz = sp.eye(nx), sp.eye(ny), sp.eye(nz)
+    A = sp.kron(sp.kron(Iz, Iy), Tx) + sp.kron(sp.kron(Iz, Ty), Ix) + sp.kron(sp.kron(Tz, Iy), Ix)
+    A = sp.csr_matrix(A)
+    A.sort_indices()
+    return A
+
+
 def lap2d_periodic(m):
     """5-point stencil on a torus: the wrap-around rows have column offsets no interior row has, so in the row-pattern
     layout they are NOT the common pattern with entries missing (per-row global path of the TMA-staged sweep)"""
@@ -380,6 +390,10 @@ DICT_CASES = [('lap2d_800', lambda rng: lap2d(800), {'0': 1, '1': 3, '2': 4, '3'
               ('poisson3d_41', lambda rng: poisson3d(41), {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('lap1d_100001', lambda rng: lap1d(100001), {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('lap2d_periodic_300', lambda rng: lap2d_periodic(300), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              # grid lines of 600 points: the merged middle segment is wide, the stage ring drops to 2 stages (the 512^3
+              # problem of 8 GPUs); lines of 1100 points: five separate segments
+              ('poisson3d_600x5x5', lambda rng: poisson3d_box(600, 5, 5), {'0': 1, '1': 3, '2': 4, '3': 5}),
+              ('poisson3d_1100x5x4', lambda rng: poisson3d_box(1100, 5, 4), {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('few_valued_irregular', few_valued_irregular, {'0': 1, '1': 3, '2': 3, '3': 3}),
               ('stencil_with_oddities', stencil_with_oddities, {'0': 1, '1': 3, '2': 4, '3': 5}),
               ('stencil_many_row_patterns', stencil_many_row_patterns, {'0': 1, '1': 1, '2': 1, '3': 1}),
