@@ -82,7 +82,6 @@ struct Sell {
     unsigned char *cc = nullptr;     // [padded]   8-bit value codes into dict[256]
     double *dict = nullptr;
     int *row_len = nullptr;          // [n]
-    int max_w = 0;                   // widest slice (slots per row); 0 = not measured (large operators)
     bool ok() const { return cj != nullptr; }
 };
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,

@@ -122,35 +122,33 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
     if (t >= TT_CONS) {
         // ---------------- producer: one lane feeds the stage ring ----------------
         if (t != TT_CONS) return;
+        int st = 0, round = 0;                              // ring slot and how often it has been filled
         for (int k = 0; k < my_chunks; ++k) {
-            const int st = k % TT_ST;
-            if (k >= TT_ST) mbar_wait(&empty[st], ((k / TT_ST) - 1) & 1);
+            if (round > 0) mbar_wait(&empty[st], (round - 1) & 1);
             const long long r0 = (long long)((int)blockIdx.x + k * (int)gridDim.x) * TT_CH;
             unsigned char *sb = tt_smem + (size_t)st * stage_bytes;
             double *xs = reinterpret_cast<double *>(sb);
             uint64_t *bar = &full[st];
-            // clipped ranges first (the byte count must be announced before the copies complete)
-            long long c0[TT_MAXSEG], c1[TT_MAXSEG];
+            // the byte count must be announced before the copies can complete: clipped ranges twice (cheap, nseg <= 8)
             uint32_t bytes = 0;
-#pragma unroll
-            for (int s = 0; s < TT_MAXSEG; ++s) {
+            for (int s = 0; s < a.nseg; ++s) {
                 const long long g0 = r0 + a.seg_lo[s], g1 = g0 + a.seg_len[s];
-                c0[s] = g0 < 0 ? 0 : g0;
-                c1[s] = s < a.nseg ? (g1 < a.xlen ? g1 : (long long)a.xlen) : c0[s];
-                if (c1[s] > c0[s]) bytes += (uint32_t)((c1[s] - c0[s]) & ~1ll) * 8u;
+                const long long c0 = g0 < 0 ? 0 : g0, c1 = g1 < a.xlen ? g1 : (long long)a.xlen;
+                if (c1 > c0) bytes += (uint32_t)((c1 - c0) & ~1ll) * 8u;
             }
             const int nb = (int)(a.n - r0 < TT_CH ? a.n - r0 : TT_CH);          // rows of this chunk
             if (NEED_B) bytes += (uint32_t)(nb & ~1) * 8u;
             const uint32_t code_bytes = (uint32_t)((nb + 15) & ~15);             // the code array is padded by 64 bytes
             bytes += code_bytes;
             mbar_arrive_expect_tx(bar, bytes);
-#pragma unroll
-            for (int s = 0; s < TT_MAXSEG; ++s) {
-                if (c1[s] <= c0[s]) continue;
-                double *dst = xs + a.seg_base[s] + (c0[s] - (r0 + a.seg_lo[s]));
-                const long long cnt = c1[s] - c0[s], even = cnt & ~1ll;
-                if (even) bulk_g2s(dst, a.x + c0[s], (uint32_t)even * 8u, bar);
-                if (cnt & 1) cp_async_8(dst + even, a.x + c0[s] + even);         // odd n: the last element on its own
+            for (int s = 0; s < a.nseg; ++s) {
+                const long long g0 = r0 + a.seg_lo[s], g1 = g0 + a.seg_len[s];
+                const long long c0 = g0 < 0 ? 0 : g0, c1 = g1 < a.xlen ? g1 : (long long)a.xlen;
+                if (c1 <= c0) continue;
+                double *dst = xs + a.seg_base[s] + (c0 - g0);
+                const long long cnt = c1 - c0, even = cnt & ~1ll;
+                if (even) bulk_g2s(dst, a.x + c0, (uint32_t)even * 8u, bar);
+                if (cnt & 1) cp_async_8(dst + even, a.x + c0 + even);            // odd length: the last element on its own
             }
             if (NEED_B) {
                 double *bs = xs + a.xs_elems;
@@ -159,6 +157,7 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
             }
             bulk_g2s(sb + (size_t)(a.xs_elems + (NEED_B ? TT_CH : 0)) * 8, a.codes + r0, code_bytes, bar);
             mbar_arrive_after_cp_async(bar);
+            if (++st == TT_ST) { st = 0; ++round; }
         }
         return;
     }
@@ -166,14 +165,14 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
     // ---------------- consumers: thread t owns rows t, t + TT_CONS, ... of every chunk ----------------
     const double diag = a.val[QD];
     const double one_m_omega = sub_rn(1.0, a.omega);
-    for (int k = 0; k < my_chunks; ++k) {
-        const int st = k % TT_ST;
+    int st = 0, round = 0;
+    for (int k = 0; k < my_chunks; ++k, st = (st + 1 == TT_ST ? 0 : st + 1), round += (st == 0)) {
         const int r0 = ((int)blockIdx.x + k * (int)gridDim.x) * TT_CH;
         const unsigned char *sb = tt_smem + (size_t)st * stage_bytes;
         const double *xs = reinterpret_cast<const double *>(sb);
         const double *bs = xs + a.xs_elems;
         const unsigned char *cs = sb + (size_t)(a.xs_elems + (NEED_B ? TT_CH : 0)) * 8;
-        mbar_wait(&full[st], (k / TT_ST) & 1);
+        mbar_wait(&full[st], round & 1);
         double xv[TT_RPT][LEN], bi[TT_RPT];
         unsigned m[TT_RPT];
         int code[TT_RPT];

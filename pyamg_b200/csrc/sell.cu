@@ -12,10 +12,7 @@
 // does it (scipy csr_matvec / amg_core jacobi, pyamg/amg_core/relaxation.h:201-239): the bits
 // are those of the CSR kernels.  Cost: the copy (engine-owned, built once per level) and
 // 19-23 % padding traffic; no shared memory, no barriers, 8 independent loads in flight per lane.
-#include <stdlib.h>
-#include <algorithm>
 #include <type_traits>
-#include <vector>
 #include "internal.cuh"
 #include "setup.cuh"
 
@@ -24,8 +21,6 @@ namespace b200amg {
 constexpr int SELL_C = 32;
 constexpr int SELL_TPB = 256;
 constexpr int SELL_U = 8;
-constexpr int SELL_WIDE_MAX_ROWS = 200000;   // below this a thread-per-row grid cannot fill the machine
-constexpr int SELL_WIDE_MIN_W = 40, SELL_WIDE_MAX_W = 420;
 
 bool sell_wanted(long long nnz, int nrows)
 {
@@ -122,17 +117,6 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         if (e == cudaSuccess) {
             sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc);
             rc = check_launch("sell_fill_kernel");
-        }
-    }
-    // operators with few rows: the widest slice decides whether the slice-per-CTA kernel applies (sell_wide_kernel)
-    if (e == cudaSuccess && !rc && s.cj && n < SELL_WIDE_MAX_ROWS) {
-        std::vector<long long> hw(ns);
-        if (cudaMemcpy(hw.data(), width, sizeof(long long) * ns, cudaMemcpyDeviceToHost) == cudaSuccess) {
-            long long m = 0;
-            for (long long v : hw) m = std::max(m, v);
-            s.max_w = (int)(m / SELL_C);
-        } else {
-            cudaGetLastError();
         }
     }
     if (width) cudaFree(width);
@@ -266,92 +250,6 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     }
 }
 
-// ---- operators with FEW, LONG rows (restriction of level 1: 44 629 rows x 240 slots; the level-2 operator) ----------
-// Thread-per-row leaves the machine empty there: 1 395 warps on 148 SMs, each walking 240 dependent rounds of 8 slots
-// (ncu, profiles/r02: 93 us at 13 % occupancy, 1.9 TB/s).  Here ONE CTA takes one slice of 32 rows: its 8 warps deal the
-// slots among them (warp q: slots q, q + 8, ...; lane = row, so index / value loads stay coalesced and the x gathers
-// of neighbouring rows stay neighbours), turn them into separately rounded products in shared memory, and after one
-// barrier lane r of warp 0 folds row r's products in STORAGE order -- the same ordered sum as the thread-per-row
-// kernel, 8 times the loads in flight.  Padding slots and the smoothers' diagonal slot hold +0.0: acc + (+0.0) == acc
-// bit for bit (acc starts at +0.0 / b_i and cannot become -0.0 by adding +0.0 ... see rowpat.cu), so the fold runs the
-// full slice width without tests.
-template <int OP>
-__global__ void __launch_bounds__(SELL_TPB) sell_wide_kernel(const int n, const long long *__restrict__ slice_off,
-                                                             const int *__restrict__ cj, const double *__restrict__ cv,
-                                                             const int *__restrict__ row_len, const StreamArgs a)
-{
-    constexpr bool SMOOTH = (OP >= OP_JACOBI);
-    constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
-    constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
-    extern __shared__ double sw_prod[];                       // [32][stride], stride odd: conflict-free row walks
-    __shared__ int s_diagk[SELL_C];
-    const int slice = blockIdx.x, lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
-    const long long off = slice_off[slice];
-    const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
-    const int stride = w | 1;
-    const int row = slice * SELL_C + lane;
-    const bool live = row < n;
-    const int len = live ? row_len[row] : 0;
-    if (threadIdx.x < SELL_C) s_diagk[threadIdx.x] = -1;
-    if (SMOOTH) __syncthreads();
-    const double *__restrict__ xg = a.x;
-    const int *pj = cj + off + lane;
-    const double *pv = cv + off + lane;
-    constexpr int NW = SELL_TPB / 32;
-    for (int k0 = wq; k0 < w; k0 += NW * SELL_U) {
-        int c[SELL_U];
-        double v[SELL_U], xv[SELL_U];
-#pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            const int k = k0 + u * NW;
-            const bool in = k < len;
-            c[u] = in ? __ldcs(pj + (long long)k * SELL_C) : -1;
-            v[u] = in ? __ldcs(pv + (long long)k * SELL_C) : 0.0;
-        }
-#pragma unroll
-        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
-#pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            const int k = k0 + u * NW;
-            if (k < w) {
-                double pr = 0.0;
-                if (c[u] >= 0) {
-                    if (SMOOTH && c[u] == row) atomicMax(&s_diagk[lane], k);      // last stored diagonal wins
-                    else pr = mul_rn(v[u], xv[u]);
-                }
-                sw_prod[lane * stride + k] = pr;
-            }
-        }
-    }
-    __syncthreads();
-    if (wq != 0 || !live) return;
-    double bi = 0.0, xi = 0.0, yi = 0.0;
-    if (NEED_B) bi = __ldg(a.b + row);
-    if (SMOOTH) xi = __ldg(xg + row);
-    if (OP == OP_ADD) yi = a.b[row];
-    double acc = BSRF ? bi : 0.0;
-    const double *pr = sw_prod + lane * stride;
-#pragma unroll 8
-    for (int k = 0; k < w; ++k) acc = BSRF ? sub_rn(acc, pr[k]) : add_rn(acc, pr[k]);
-    double diag = 0.0;
-    if (SMOOTH && s_diagk[lane] >= 0) diag = pv[(long long)s_diagk[lane] * SELL_C];
-    double *y = a.y;
-    if (OP == OP_MATVEC) {
-        y[row] = acc;
-    } else if (OP == OP_RESIDUAL) {
-        y[row] = sub_rn(bi, acc);
-    } else if (OP == OP_ADD) {
-        y[row] = add_rn(yi, acc);
-    } else if (OP == OP_JACOBI) {
-        y[row] = (diag != 0.0)
-                     ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), mul_rn(a.omega, div_rn(sub_rn(bi, acc), diag)))
-                     : xi;
-    } else if (OP == OP_JACOBI_BSR1) {
-        y[row] = (diag != 0.0) ? add_rn(mul_rn(sub_rn(1.0, a.omega), xi), div_rn(mul_rn(a.omega, acc), diag)) : xi;
-    }
-}
-
-
 // ---- colour-ordered Gauss-Seidel on a colour-grouped SELL copy -----------------------------------
 // amg_core.gauss_seidel_indexed (relaxation.h:394-426) / bsr_gauss_seidel with bs = 1 (:89-173) for the
 // positions [p0, p1) of the index list `Id` = ONE colour: rows of a colour never read each other, so the
@@ -414,23 +312,6 @@ template <int OP>
 static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
-    // few long rows: one CTA per slice.  EXPERIMENT (B200AMG_SELL_WIDE=1; default off): the first hardware run
-    // (profiles/r02/rejected/sell_wide_kernel.cu.txt) was slower at ONE resident CTA per SM -- the driver's default
-    // shared-memory carve-out; this version asks for the maximum carve-out so that 3 (w = 240) to 8 CTAs fit
-    static const bool wide = [] { const char *e = getenv("B200AMG_SELL_WIDE"); return e && e[0] == '1'; }();
-    if (wide && OP != OP_SPMV_AB && !s.cc && s.n < SELL_WIDE_MAX_ROWS && s.max_w >= SELL_WIDE_MIN_W && s.max_w <= SELL_WIDE_MAX_W) {
-        const int smem = (int)sizeof(double) * SELL_C * (s.max_w | 1);
-        static bool attr_set = false;
-        if (!attr_set) {
-            B200_CUDA(cudaFuncSetAttribute(sell_wide_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)sizeof(double) * SELL_C * (SELL_WIDE_MAX_W | 1)));
-            B200_CUDA(cudaFuncSetAttribute(sell_wide_kernel<OP>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                           cudaSharedmemCarveoutMaxShared));
-            attr_set = true;
-        }
-        sell_wide_kernel<OP><<<(s.n + SELL_C - 1) / SELL_C, SELL_TPB, smem, st>>>(s.n, s.slice_off, s.cj, s.cv, s.row_len, a);
-        return check_launch("sell_wide_kernel");
-    }
     if (s.cc)
         sell_kernel<OP, false, true><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cc, s.dict, s.row_len, a);
     else if (s.n < 400000)
