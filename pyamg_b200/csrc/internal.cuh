@@ -99,6 +99,9 @@ long long nnz_lookup(const int *Ap, int n_row, cudaStream_t st);
 int stream_op(int op, const StreamArgs &a, cudaStream_t st);
 int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
             const int *Id, int p0, int p1, cudaStream_t st);
+// a whole colour-ordered smoothing step of a small level in ONE launch (small_level.cu): -1 = not eligible
+int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *Ap, const int *Aj, const double *Ax, const int *Id,
+                 const int *cptr_dev, int K, double *x, const double *b, int iters, int sweep, bool x_is_zero, cudaStream_t st);
 int gs_sequential(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                   const int *Id, int start, int stop, int step, cudaStream_t st);
 

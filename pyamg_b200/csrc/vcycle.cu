@@ -24,6 +24,7 @@ struct LevelRt {
     RowPat rpA;                               // one byte per row of a stencil operator (rowpat.cu)
     ValueDict dA, dP, dR;                     // 8-bit value codes of operators with <= 256 distinct values
     std::vector<int> color_ptr;
+    int *cptr_dev = nullptr;                  // the same offsets on the device (small_level.cu)
 };
 
 struct GraphKey {
@@ -55,6 +56,8 @@ static void free_level(LevelRt &L)
     dict_free(&L.dA); dict_free(&L.dP); dict_free(&L.dR);
     rowpat_free(&L.rpA);
     bsr_color_free(&L.bGS);
+    if (L.cptr_dev) cudaFree(L.cptr_dev);
+    L.cptr_dev = nullptr;
 }
 
 // B200AMG_VALUE_DICT=0 switches the value dictionary off (A/B measurements)
@@ -151,8 +154,13 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
         return 0;
     }
     if (kind == 2) {                                   // colour-ordered Gauss-Seidel (indexed)
-        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
         const int K = d.K;
+        {   // small level: the whole step in one launch, iterate in shared memory (same colour order, same bits)
+            const int rc = gs_level_cta(d.bs, d.flavor != 0 && !d.gs_csr, d.n, L.nzA * d.bs * d.bs, d.Ap, d.Aj, d.Ax, d.Id,
+                                        L.cptr_dev, K, *cur, b, iters, sweep, x_is_zero, st);
+            if (rc >= 0) return rc;
+        }
+        if (x_is_zero) B200_CUDA(cudaMemsetAsync(*cur, 0, sizeof(double) * d.n, st));
         for (int it = 0; it < iters; ++it) {
             for (int pass = 0; pass < 2; ++pass) {
                 const bool bwd = (pass == 1);
@@ -350,6 +358,12 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             if (!L.d.color_ptr_host || !L.d.Id || L.d.K < 0) { delete E; return set_err(B200AMG_EINVAL, "vcycle_create: colour ordering missing"); }
             L.color_ptr.assign(L.d.color_ptr_host, L.d.color_ptr_host + L.d.K + 1);
             L.d.color_ptr_host = nullptr;
+            if (cudaMalloc(&L.cptr_dev, sizeof(int) * (L.d.K + 1)) != cudaSuccess ||
+                cudaMemcpy(L.cptr_dev, L.color_ptr.data(), sizeof(int) * (L.d.K + 1), cudaMemcpyHostToDevice) != cudaSuccess) {
+                cudaGetLastError();
+                if (L.cptr_dev) cudaFree(L.cptr_dev);
+                L.cptr_dev = nullptr;                    // the per-colour launches do not need it
+            }
         }
         // nonzero counts (one small D2H read per matrix, at create time only) size the CTAs
         auto last = [](const int *p, int n, int *out) {
