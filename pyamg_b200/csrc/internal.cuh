@@ -53,7 +53,7 @@ struct RowPat {
     int xlen = 0;                    // entries of x the operator may reference (> n on a row slab with halo columns)
     int common_len = 0;              // entries of the typical (middle) row
     // plan of the TMA-staged sweep (rowpat_tile.cu), made from the typical row's pattern; tile_ok == false: not eligible
-    bool tile_ok = false, tile_wide = false;   // tile_wide: 512 consumers, one CTA per SM, deep ring (large stages)
+    bool tile_ok = false;
     int tile_len = 0, nseg = 0, xs_elems = 0, tile_stages = 0;
     int seg_lo[RP_TILE_MAXSEG] = {}, seg_len[RP_TILE_MAXSEG] = {}, seg_base[RP_TILE_MAXSEG] = {};
     int sbase[RP_TILE_LEN] = {0, 0, 0, 0, 0, 0, 0, 0};

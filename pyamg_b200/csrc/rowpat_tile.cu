@@ -39,14 +39,13 @@
 namespace b200amg {
 
 constexpr int TT_CH = TT_CHUNK;
-constexpr int TT_MAX_ST = 6;
-// two launch shapes: 256 consumers, 2 CTAs per SM, up to 112 KB of stages each (the default: 3 stages for the 7-point
-// stencil on 256-point grid lines, 2 on 512-point lines) and, when not even 2 stages fit twice (grid lines of 1000+
-// points), 512 consumers, ONE CTA per SM with the whole 226 KB for its ring
-constexpr int TT_CONS_A = TT_CONSUMERS, TT_CONS_B = 512;
+constexpr int TT_MAX_ST = TT_STAGES;
+constexpr int TT_CONS = TT_CONSUMERS;           // consumer threads
+constexpr int TT_TPB = TT_CONS + 32;            // + producer warp
+constexpr int TT_RPT = TT_CH / TT_CONS;         // rows per consumer thread and chunk
 constexpr int TT_MAXSEG = RP_TILE_MAXSEG;
 constexpr unsigned TT_NOT_SUBSET = 0x100u;
-constexpr int TT_SMEM_LIMIT_A = 227 * 1024 / TT_RESIDENT - 1024, TT_SMEM_LIMIT_B = 226 * 1024;
+constexpr int TT_SMEM_LIMIT = 227 * 1024 / TT_RESIDENT - 1024;
 
 struct TileArgs {
     int n, nseg;
@@ -96,12 +95,9 @@ __device__ __noinline__ void tile_generic_row(const TileArgs &a, int row, int co
     }
 }
 
-template <int OP, int LEN, int TT_CONS>
-__global__ void __launch_bounds__(TT_CONS + 32, TT_CONS == TT_CONS_A ? TT_RESIDENT : 1)
-    rowpat_tile_kernel(const __grid_constant__ TileArgs a)
+template <int OP, int LEN>
+__global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const __grid_constant__ TileArgs a)
 {
-    constexpr int TT_TPB = TT_CONS + 32;            // + producer warp
-    constexpr int TT_RPT = TT_CH / TT_CONS;         // rows per consumer thread and chunk
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
@@ -265,20 +261,11 @@ void rowpat_tile_plan(RowPat *r, const std::vector<RowPatEntry> &ht, int common)
     }
     r->nseg = nseg;
     r->xs_elems = base;
-    // as many ring stages as fit (3 for the 7-point stencil on 256-point grid lines, 2 on 512-point lines)
-    auto stages_within = [&](long long limit) {
-        int nst = TT_MAX_ST;
-        while (nst >= 1 && (long long)nst * ((long long)(base + TT_CH) * 8 + TT_CH) + 512 + 2 * nst * 8 > limit) --nst;
-        return nst;
-    };
-    int nst = std::min(stages_within(TT_SMEM_LIMIT_A), 4);
-    r->tile_wide = false;
-    // measured at 512^3 on one B200 (profiles/r02/run14_summary.txt): 2 CTAs x 2 stages 0.729 ms per Jacobi sweep, the
-    // one-CTA shape with 5 stages 0.863 ms -- so the wide shape is only the fallback when not even 2 stages fit twice
-    if (nst < 2) {                                                     // huge stages: one CTA per SM, deep ring
-        nst = stages_within(TT_SMEM_LIMIT_B);
-        r->tile_wide = true;
-    }
+    // as many ring stages as fit (3 for the 7-point stencil on 256-point grid lines, 2 on 512-point lines).  A second
+    // launch shape for large stages -- 512 consumers, one CTA per SM, 5 stages -- was measured at 512^3 and is slower
+    // (0.863 vs 0.729 ms per Jacobi sweep, profiles/r02/run14_summary.txt): not kept
+    int nst = TT_MAX_ST;
+    while (nst >= 2 && (long long)nst * ((long long)(base + TT_CH) * 8 + TT_CH) + 512 + 2 * nst * 8 > TT_SMEM_LIMIT) --nst;
     if (nst < 2) return;
     r->tile_stages = nst;
     for (int q = 0; q < L; ++q) {
@@ -311,7 +298,7 @@ void rowpat_tile_plan(RowPat *r, const std::vector<RowPatEntry> &ht, int common)
     r->tile_ok = true;
 }
 
-template <int OP, int LEN, int CONS>
+template <int OP, int LEN>
 static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
 {
     static int sms = 0;
@@ -321,12 +308,10 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
         B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     }
     constexpr bool NEED_B = (OP == OP_RESIDUAL || OP >= OP_JACOBI);
-    constexpr bool WIDE = CONS != TT_CONS_A;
     const int smem = r.tile_stages * ((r.xs_elems + (NEED_B ? TT_CH : 0)) * 8 + TT_CH) + 512 + 2 * r.tile_stages * 8;
     static bool attr_set = false;
     if (!attr_set) {
-        B200_CUDA(cudaFuncSetAttribute(rowpat_tile_kernel<OP, LEN, CONS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       WIDE ? TT_SMEM_LIMIT_B : TT_SMEM_LIMIT_A));
+        B200_CUDA(cudaFuncSetAttribute(rowpat_tile_kernel<OP, LEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_LIMIT));
         attr_set = true;
     }
     TileArgs a;
@@ -343,26 +328,18 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     a.x = s.x; a.b = s.b; a.y = s.y;
     a.omega = s.omega;
     const int n_chunks = (r.n + TT_CH - 1) / TT_CH;
-    const int grid = std::min(n_chunks, sms * (WIDE ? 1 : TT_RESIDENT));
-    rowpat_tile_kernel<OP, LEN, CONS><<<grid, CONS + 32, smem, st>>>(a);
+    const int grid = std::min(n_chunks, sms * TT_RESIDENT);
+    rowpat_tile_kernel<OP, LEN><<<grid, TT_TPB, smem, st>>>(a);
     return check_launch("rowpat_tile_kernel");
 }
 
 template <int OP>
 static int launch_tile_len(const RowPat &r, const StreamArgs &s, cudaStream_t st)
 {
-    if (r.tile_wide) {
-        switch (r.tile_len) {
-        case 3: return launch_tile<OP, 3, TT_CONS_B>(r, s, st);
-        case 5: return launch_tile<OP, 5, TT_CONS_B>(r, s, st);
-        case 7: return launch_tile<OP, 7, TT_CONS_B>(r, s, st);
-        }
-        return -1;
-    }
     switch (r.tile_len) {
-    case 3: return launch_tile<OP, 3, TT_CONS_A>(r, s, st);
-    case 5: return launch_tile<OP, 5, TT_CONS_A>(r, s, st);
-    case 7: return launch_tile<OP, 7, TT_CONS_A>(r, s, st);
+    case 3: return launch_tile<OP, 3>(r, s, st);
+    case 5: return launch_tile<OP, 5>(r, s, st);
+    case 7: return launch_tile<OP, 7>(r, s, st);
     }
     return -1;
 }
