@@ -113,9 +113,10 @@ def measured_peak():
     return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-ENTRY_BYTES = {1: 12, 2: 12, 3: 5, 4: 1, 5: 0, 6: 5}   # bytes per stored entry by engine layout (b200amg_vcycle_layout)
+ENTRY_BYTES = {1: 12, 2: 12, 3: 5, 4: 1, 5: 0, 6: 5, 7: 10}   # bytes per stored entry by engine layout (b200amg_vcycle_layout)
 LAYOUT_NAME = {1: 'CSR (int32 column + fp64 value)', 2: 'sliced-ELL copy', 3: 'CSR + 8-bit value codes',
-               4: 'CSR rows + 8-bit (offset, value) pattern codes', 5: 'one row-pattern byte per row', 6: 'sliced-ELL copy with 8-bit value codes'}
+               4: 'CSR rows + 8-bit (offset, value) pattern codes', 5: 'one row-pattern byte per row', 6: 'sliced-ELL copy with 8-bit value codes',
+               7: 'sliced-ELL copy with 16-bit column steps'}
 
 
 def matrix_bytes(n, nnz, layout=1):
@@ -1221,6 +1222,7 @@ def main():
            'detail': {'parallelism': 'single GPU' if R['world'] == 1 else
                       'replicas: %d independent solves, one per GPU' % R['world'],
                       'setup_s_device': round(R['setup_s'], 2),
+                      'engine_layouts': [{k: LAYOUT_NAME.get(v, str(v)) for k, v in L.items()} for L in ml.layouts()],
                       'unfused_algorithmic_bytes_per_cycle': vb,
                       'cycle_GBs_on_unfused_bytes': round(vb / (R['ms_step'] * 1e-3) / 1e9, 1)},
            'clocks': R['clocks'], 'e2e': e2e, 'gpu_launches': int(R['launches']), 'roofline': roof, 'solve': solve}

@@ -147,7 +147,8 @@ int b200amg_op_apply(void *handle, int op, const double *x, const double *b, dou
 int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL, 3 CSR + 8-bit value codes, 4 CSR rows + 8-bit
                                            * (column offset, value) pattern codes, 5 one row-pattern
                                            * byte per row (stencil operators), 6 sliced-ELL with
-                                           * 8-bit value codes */
+                                           * 8-bit value codes, 7 sliced-ELL with 16-bit column
+                                           * steps (sorted rows, >= 400 000 rows) */
 int b200amg_op_destroy(void *handle);
 
 /* ---- multi-GPU halo refresh over NVLink peer memory (pyamg_b200/distributed.py) -------
@@ -428,8 +429,9 @@ int b200amg_vcycle_apply_op(void *handle, int level, int op, const double *x, co
 int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_kind, int max_ops,
                            int *op_code_host, int *op_level_host, float *op_ms_host,
                            int *n_ops_host, void *stream);
-/* layout the engine streams an operator of `level` in (which: 0 A, 1 P, 2 R): the b200amg_op_layout codes,
- * 0 for block operators.  Informational: every layout gives the same bits. */
+/* layout the engine streams an operator of `level` in (which: 0 A, 1 P, 2 R, 3 the colour-grouped copy of A that
+ * colour-ordered Gauss-Seidel sweeps): the b200amg_op_layout codes, 0 for block operators / no such copy.
+ * Informational: every layout gives the same bits. */
 int b200amg_vcycle_layout(void *handle, int level, int which);
 /* rnorm2_dev[0] = ||b - A0 x||^2 on the finest level (residual_norm of multilevel.py:450,461) */
 int b200amg_vcycle_residual_norm2(void *handle, const double *x, const double *b,

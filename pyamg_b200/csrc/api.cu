@@ -260,7 +260,7 @@ extern "C" int b200amg_op_layout(void *handle)
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
     if (!h) return 0;
     if (h->rp.ok()) return 5;
-    if (h->sell.ok()) return h->sell.cc ? 6 : 2;
+    if (h->sell.ok()) return h->sell.cc ? 6 : (h->sell.cd ? 7 : 2);
     return h->vd.ok() ? (h->vd.offs ? 4 : 3) : 1;
 }
 

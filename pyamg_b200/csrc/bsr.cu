@@ -204,11 +204,16 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
 // loc = row k of block g times x_j from zero, exactly the reference's gemm (linalg.h:359-398) -- so one pass costs ONE
 // round of memory latency; then the pass's locs are subtracted from the row sums in STORAGE order (shuffled one by one
 // to the lanes 0..BS-1 that hold acc), which is the order of relaxation.h:139-144: the bits do not change.
-template <int BS, bool backward, bool PERM>
+// NB passes form a BATCH: the column indices of the whole batch are requested together, then all its block rows and
+// x_j, and only then the ordered subtraction runs -- two rounds of memory latency per NB * (32 / BS) blocks instead of
+// per 32 / BS (a 55-block row of 6 x 6 blocks: 6 rounds instead of 22; these launches are one wave of warps, so rounds
+// of latency are all their run time).  `zero` is 0 at run time: the `tie` words keep the compiler from sinking each load
+// next to its use (sell.cu has the story).
+template <int BS, bool backward, bool PERM, int NB>
 __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                                 const double *__restrict__ Ax, double *x,
                                                                 const double *__restrict__ b, const int *__restrict__ Id,
-                                                                int p0, int p1)
+                                                                int p0, int p1, int zero)
 {
     constexpr int G = 32 / BS;                          // blocks per pass
     constexpr unsigned FULL = 0xffffffffu;
@@ -221,25 +226,54 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
     const int lo = Ap[PERM ? p : i], hi = Ap[(PERM ? p : i) + 1];
     double acc = (lane < BS) ? b[(size_t)i * BS + lane] : 0.0;
     int dptr = -1;
-#pragma unroll 2
-    for (int q0 = lo; q0 < hi; q0 += G) {
-        const int q = q0 + g;
-        const bool have = lane_ok && q < hi;
-        const int j = have ? Aj[q] : -1;
-        const bool isdiag = have && j == i;
-        double loc = 0.0;
-        if (have && !isdiag) {
-            const double *blk = Ax + ((size_t)q * BS + k) * BS;
-            const double *xb = x + (size_t)j * BS;
+    for (int q0 = lo; q0 < hi; q0 += G * NB) {
+        int j[NB];
 #pragma unroll
-            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(blk[c], xb[c]));
+        for (int t = 0; t < NB; ++t) {
+            const int q = q0 + t * G + g;
+            j[t] = (lane_ok && q < hi) ? Aj[q] : -1;
         }
-        const unsigned dg = __ballot_sync(FULL, isdiag);
-        if (dg) dptr = q0 + (31 - __clz(dg)) / BS;      // the last stored diagonal block wins (relaxation.h:121)
-        // blocks that do not exist / the diagonal block hand over +0.0: acc - (+0.0) == acc bit for bit, also for -0.0
-        loc = (have && !isdiag) ? loc : 0.0;
+        int tie = 0;
+        if (NB > 1) {
 #pragma unroll
-        for (int gg = 0; gg < G; ++gg) acc = sub_rn(acc, __shfl_sync(FULL, loc, gg * BS + (lane < BS ? lane : 0)));
+            for (int t = 0; t < NB; ++t) tie |= j[t];
+            tie &= zero;
+        }
+        double bl[NB][BS], xv[NB][BS];
+#pragma unroll
+        for (int t = 0; t < NB; ++t) {
+            const int q = q0 + t * G + g;
+            const bool use = j[t] >= 0 && j[t] != i;
+            const double *blk = Ax + ((size_t)q * BS + k) * BS + (t == 0 ? tie : 0);
+            const double *xb = x + (size_t)(use ? j[t] : 0) * BS;
+#pragma unroll
+            for (int c = 0; c < BS; ++c) {
+                bl[t][c] = use ? blk[c] : 0.0;
+                xv[t][c] = use ? xb[c] : 0.0;
+            }
+        }
+        if (NB > 1) {
+#pragma unroll
+            for (int t = 0; t < NB; ++t)
+#pragma unroll
+                for (int c = 0; c < BS; ++c) tie |= __double2loint(bl[t][c]) | __double2loint(xv[t][c]);
+            tie &= zero;
+        }
+#pragma unroll
+        for (int t = 0; t < NB; ++t) {
+            if (q0 + t * G >= hi) break;                // warp-uniform
+            const bool have = (t == 0 ? j[t] + tie : j[t]) >= 0;
+            const bool isdiag = have && j[t] == i;
+            double loc = 0.0;
+#pragma unroll
+            for (int c = 0; c < BS; ++c) loc = add_rn(loc, mul_rn(bl[t][c], xv[t][c]));
+            const unsigned dg = __ballot_sync(FULL, isdiag);
+            if (dg) dptr = q0 + t * G + (31 - __clz(dg)) / BS;      // the last stored diagonal block wins (relaxation.h:121)
+            // blocks that do not exist / the diagonal block hand over +0.0: acc - (+0.0) == acc bit for bit, also for -0.0
+            loc = (have && !isdiag) ? loc : 0.0;
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg) acc = sub_rn(acc, __shfl_sync(FULL, loc, gg * BS + (lane < BS ? lane : 0)));
+        }
     }
     if (dptr < 0) return;
     // point sweep inside the diagonal block (relaxation.h:150-163): lane k < BS owns row k of D
@@ -279,11 +313,12 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
 // storage order into one running sum, so only the products are free: lane (g, r) multiplies row r of block g of the
 // pass by x_j (C separately rounded products), then the running sum of scalar row r travels through the groups in
 // block order -- group g adds its C products, hands the sum to group g + 1 by a shuffle -- G shuffles per pass.
-template <int R>
+// NB passes per batch, their loads requested together (see bsr_gs_color_warp_kernel).
+template <int R, int NB>
 __global__ void __launch_bounds__(128) bsr_matvec_warp_kernel(int n_brow, int C, const int *__restrict__ Ap,
                                                               const int *__restrict__ Aj, const double *__restrict__ Ax,
                                                               const double *__restrict__ x, const double *__restrict__ b,
-                                                              double *y, int mode)
+                                                              double *y, int mode, int zero)
 {
     constexpr int G = 32 / R;
     constexpr unsigned FULL = 0xffffffffu;
@@ -294,29 +329,58 @@ __global__ void __launch_bounds__(128) bsr_matvec_warp_kernel(int n_brow, int C,
     const bool lane_ok = g < G;
     const int lo = Ap[i], hi = Ap[i + 1];
     double carry = 0.0;                                   // running sum of scalar row r after the blocks before this pass
-#pragma unroll 2
-    for (int q0 = lo; q0 < hi; q0 += G) {
-        const int q = q0 + g;
-        const bool have = lane_ok && q < hi;
-        double pr[8];
-        if (have) {
-            const double *blk = Ax + ((size_t)q * R + r) * C;
-            const double *xb = x + (size_t)Aj[q] * C;
+    for (int q0 = lo; q0 < hi; q0 += G * NB) {
+        int j[NB];
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-                if (c < C) pr[c] = mul_rn(blk[c], xb[c]);
+        for (int t = 0; t < NB; ++t) {
+            const int q = q0 + t * G + g;
+            j[t] = (lane_ok && q < hi) ? Aj[q] : -1;
         }
-        double a = carry;
+        int tie = 0;
+        if (NB > 1) {
 #pragma unroll
-        for (int gg = 0; gg < G; ++gg) {
-            if (gg > 0) a = __shfl_sync(FULL, a, (gg - 1) * R + (lane_ok ? r : 0));   // sum after group gg - 1
-            if (g == gg && have) {
+            for (int t = 0; t < NB; ++t) tie |= j[t];
+            tie &= zero;
+        }
+        double pr[NB][8];
 #pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    if (c < C) a = add_rn(a, pr[c]);
+        for (int t = 0; t < NB; ++t) {
+            const int q = q0 + t * G + g;
+            const bool have = j[t] >= 0;
+            const double *blk = Ax + ((size_t)q * R + r) * C + (t == 0 ? tie : 0);
+            const double *xb = x + (size_t)(have ? j[t] : 0) * C;
+            double bl[8], xv[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                bl[c] = (have && c < C) ? blk[c] : 0.0;
+                xv[c] = (have && c < C) ? xb[c] : 0.0;
             }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) pr[t][c] = mul_rn(bl[c], xv[c]);
         }
-        carry = __shfl_sync(FULL, a, (G - 1) * R + (lane_ok ? r : 0));
+        if (NB > 1) {
+#pragma unroll
+            for (int t = 0; t < NB; ++t)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) tie |= __double2loint(pr[t][c]);
+            tie &= zero;
+        }
+#pragma unroll
+        for (int t = 0; t < NB; ++t) {
+            if (q0 + t * G >= hi) break;                  // warp-uniform
+            const bool have = (t == 0 ? j[t] + tie : j[t]) >= 0;
+            double a = carry;
+#pragma unroll
+            for (int gg = 0; gg < G; ++gg) {
+                if (gg > 0) a = __shfl_sync(FULL, a, (gg - 1) * R + (lane_ok ? r : 0));   // sum after group gg - 1
+                if (g == gg && have) {
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        if (c < C) a = add_rn(a, pr[t][c]);
+                }
+            }
+            carry = __shfl_sync(FULL, a, (G - 1) * R + (lane_ok ? r : 0));
+        }
     }
     if (lane < R) {
         const size_t row = (size_t)i * R + lane;
@@ -368,6 +432,13 @@ static bool bsr_warp_kernels()
     return on;
 }
 
+// B200AMG_BSR_WARP_BATCH=0: one pass per round of loads, as in the first version (A/B switch)
+static bool bsr_warp_batch()
+{
+    static const bool on = [] { const char *e = getenv("B200AMG_BSR_WARP_BATCH"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 // nblocks: stored blocks of the operator (< 0: unknown) -- rows with at least half a pass of blocks on average go to
 // the warp-per-block-row kernel
 int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax, const double *x,
@@ -380,7 +451,8 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     // (measured on BASELINE config 4, profiles/r02: 1 331 x 6 rows 0.54 -> 0.13 ms; 2.08 M x 3 rows 0.53 -> 2.3 ms)
     if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && n < kSMs * 1024 && nblocks >= 2ll * (32 / R) * n_brow) {
         const unsigned grid = (unsigned)((n_brow + 3) / 4);
-        R_SWITCH(R, B200_LAUNCH(bsr_matvec_warp_kernel<RR>, grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode));
+        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH((bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        else { R_SWITCH(R, B200_LAUNCH((bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
         return check_launch("bsr_matvec_warp_kernel");
     }
     B200_LAUNCH(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
@@ -406,9 +478,14 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
-#define GS_WARP(BW, PM) R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, BW, PM>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1))
-        if (backward) { if (perm) { GS_WARP(true, true); } else { GS_WARP(true, false); } }
-        else { if (perm) { GS_WARP(false, true); } else { GS_WARP(false, false); } }
+#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
+        if (bsr_warp_batch()) {
+            if (backward) { if (perm) { GS_WARP(true, true, 4); } else { GS_WARP(true, false, 4); } }
+            else { if (perm) { GS_WARP(false, true, 4); } else { GS_WARP(false, false, 4); } }
+        } else {
+            if (backward) { if (perm) { GS_WARP(true, true, 1); } else { GS_WARP(true, false, 1); } }
+            else { if (perm) { GS_WARP(false, true, 1); } else { GS_WARP(false, false, 1); } }
+        }
 #undef GS_WARP
         return check_launch("bsr_gs_color_warp_kernel");
     }

@@ -77,12 +77,14 @@ struct Sell {
     int n = 0;                       // rows
     long long padded = 0;            // stored slots (32 * sum of slice widths)
     long long *slice_off = nullptr;  // [n_slices + 1] slot offset of every slice
-    int *cj = nullptr;               // [padded]
+    int *cj = nullptr;               // [padded]   32-bit columns, or
+    unsigned short *cd = nullptr;    // [padded]   16-bit column steps: column of slot k = first[row] + cd[0..k] (sorted rows)
+    int *first = nullptr;            // [n]        first stored column of every row (with cd)
     double *cv = nullptr;            // [padded]   (fp64 values) or
     unsigned char *cc = nullptr;     // [padded]   8-bit value codes into dict[256]
     double *dict = nullptr;
     int *row_len = nullptr;          // [n]
-    bool ok() const { return cj != nullptr; }
+    bool ok() const { return cj != nullptr || cd != nullptr; }
 };
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
                const int *perm = nullptr, const unsigned char *codes = nullptr, const double *dict = nullptr);

@@ -21,6 +21,7 @@ namespace b200amg {
 constexpr int SELL_C = 32;
 constexpr int SELL_TPB = 256;
 constexpr int SELL_U = 8;
+constexpr int SELL_BIG_ROWS = 400000;      // below: too few warps to fill the SMs, the latency-hiding forms run
 
 bool sell_wanted(long long nnz, int nrows)
 {
@@ -51,7 +52,8 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__rest
                                                         const double *__restrict__ Ax, const int *__restrict__ perm,
                                                         const long long *__restrict__ slice_off, int *__restrict__ cj,
                                                         double *__restrict__ cv, const unsigned char *__restrict__ codes,
-                                                        unsigned char *__restrict__ cc)
+                                                        unsigned char *__restrict__ cc, unsigned short *__restrict__ cd,
+                                                        int *__restrict__ first)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     const int slice = row >> 5, lane = threadIdx.x & 31;
@@ -64,18 +66,37 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__rest
         lo = Ap[src];
         len = Ap[src + 1] - lo;
     }
+    if (cd && row < n) first[row] = len > 0 ? Aj[lo] : 0;
     for (int k = 0; k < w; ++k) {
         const bool in = k < len;
-        cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
+        if (cd) cd[off + (long long)k * SELL_C + lane] = (in && k > 0) ? (unsigned short)(Aj[lo + k] - Aj[lo + k - 1]) : (unsigned short)0;
+        else cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
         if (cc) cc[off + (long long)k * SELL_C + lane] = in ? codes[lo + k] : (unsigned char)0;
         else cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
     }
+}
+
+// 16-bit column steps need rows stored by ascending column with steps below 65 536 (flag[0] = 1 otherwise)
+__global__ void __launch_bounds__(256) sell_steps_check_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                               int *__restrict__ flag)
+{
+    const int row = blockIdx.x * 256 + threadIdx.x;
+    if (row >= n) return;
+    bool bad = false;
+    const int hi = Ap[row + 1];
+    for (int k = Ap[row] + 1; k < hi; ++k) {
+        const long long step = (long long)Aj[k] - Aj[k - 1];
+        bad |= step < 0 || step > 65535;
+    }
+    if (bad) flag[0] = 1;
 }
 
 void sell_free(Sell *s)
 {
     if (s->slice_off) cudaFree(s->slice_off);
     if (s->cj) cudaFree(s->cj);
+    if (s->cd) cudaFree(s->cd);
+    if (s->first) cudaFree(s->first);
     if (s->cv) cudaFree(s->cv);
     if (s->cc) cudaFree(s->cc);
     if (s->dict) cudaFree(s->dict);
@@ -87,6 +108,10 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
                const int *perm, const unsigned char *codes, const double *dict)
 {
     const bool coded = codes != nullptr && dict != nullptr;     // 8-bit value codes instead of fp64 values
+    // 16-bit column steps (10 instead of 12 bytes per slot) where bytes are what the pass costs: big uncoded operators
+    // (B200AMG_SELL_COL16: 0 never, 2 for every size -- tests; read per build)
+    const char *env = getenv("B200AMG_SELL_COL16");
+    bool steps = !(env && env[0] == '0') && !coded && (n >= SELL_BIG_ROWS || (env && env[0] == '2'));
     *out = Sell();
     if (n <= 0) return 0;
     const int ns = (n + SELL_C - 1) / SELL_C;
@@ -102,26 +127,43 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, perm, width, s.row_len);
         rc = check_launch("sell_width_kernel");
         if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
-        if (!rc) {
+        int *flag = reinterpret_cast<int *>(width);            // width is consumed by the scan: reuse its first word
+        if (!rc && steps) {
+            e = cudaMemsetAsync(flag, 0, sizeof(int), st);
+            if (e == cudaSuccess) {
+                sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, flag);
+                rc = check_launch("sell_steps_check_kernel");
+            }
+        }
+        if (!rc && e == cudaSuccess) {
+            int bad = 0;
             e = cudaMemcpyAsync(&s.padded, s.slice_off + ns, sizeof(long long), cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess && steps) e = cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (bad) steps = false;
         }
     }
     // refuse pathological padding (one long row per slice): the CSR kernels handle those
     if (e == cudaSuccess && !rc && s.padded > 0 && s.padded <= 2 * nnz + 64 * SELL_C) {
-        e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
+        if (steps) {
+            e = cudaMalloc(&s.cd, sizeof(unsigned short) * (size_t)s.padded + 64);
+            if (e == cudaSuccess) e = cudaMalloc(&s.first, sizeof(int) * (size_t)n);
+        } else {
+            e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
+        }
         if (e == cudaSuccess && !coded) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
         if (e == cudaSuccess && coded) e = cudaMalloc(&s.cc, (size_t)s.padded + 64);
         if (e == cudaSuccess && coded) e = cudaMalloc(&s.dict, sizeof(double) * 256);
         if (e == cudaSuccess && coded) e = cudaMemcpyAsync(s.dict, dict, sizeof(double) * 256, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess) {
-            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc);
+            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc, s.cd,
+                                                              s.first);
             rc = check_launch("sell_fill_kernel");
         }
     }
     if (width) cudaFree(width);
     if (scratch) cudaFree(scratch);
-    if (e != cudaSuccess || rc || !s.cj || !(s.cv || s.cc)) {
+    if (e != cudaSuccess || rc || !(s.cj || s.cd) || !(s.cv || s.cc)) {
         sell_free(&s);
         if (e != cudaSuccess) {
             cudaGetLastError();
@@ -134,20 +176,27 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
 }
 
 // ---- apply ----------------------------------------------------------------------------------
-// PIPE: prefetch the next round's slots (100 registers, 2 CTAs/SM) -- pays when the matrix has too few
-// rows to fill the SMs with warps anyway; large matrices run the plain form (64 registers, 4 CTAs/SM)
-// CODED: the value slots hold 8-bit codes into a table of <= 256 doubles (dict.cu) -- 5 bytes per slot instead of 12
-template <int OP, bool PIPE, bool CODED>
+// PIPE: prefetch the next round's slots (2 CTAs/SM at U = 8) -- pays when the matrix has too few rows to fill the
+// SMs with warps anyway (a warp is then a chain of w / U dependent memory latencies); large matrices run the plain
+// form (64 registers, 4 CTAs/SM).  U: slots per lane per round.
+// FMT 0: 32-bit columns + fp64 values (12 bytes per slot)
+// FMT 1: the value slots hold 8-bit codes into a table of <= 256 doubles (dict.cu) -- 5 bytes per slot
+// FMT 2: 16-bit column STEPS + fp64 values (10 bytes per slot): column = first[row] + running sum of the steps
+template <int OP, int U, bool PIPE, int FMT, bool TIE = false>
 __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long long *__restrict__ slice_off,
-                                                        const int *__restrict__ cj, const void *__restrict__ cvals,
-                                                        const double *__restrict__ dict,
+                                                        const void *__restrict__ cols, const void *__restrict__ cvals,
+                                                        const double *__restrict__ dict, const int *__restrict__ first,
                                                         const int *__restrict__ row_len, const StreamArgs a)
 {
+    constexpr bool CODED = (FMT == 1), STEPS = (FMT == 2);
+    static_assert(!(PIPE && FMT != 0), "the prefetching form keeps 32-bit columns and fp64 values");
     using V = typename std::conditional<CODED, unsigned char, double>::type;
+    using J = typename std::conditional<STEPS, unsigned short, int>::type;
     const V *__restrict__ cv = reinterpret_cast<const V *>(cvals);
+    const J *__restrict__ cj = reinterpret_cast<const J *>(cols);
     __shared__ double s_dict[CODED ? 256 : 1];
     if (CODED) {
-        s_dict[threadIdx.x] = dict[threadIdx.x];               // SELL_TPB == 256
+        s_dict[threadIdx.x] = dict[threadIdx.x];               // coded launches use SELL_TPB == 256 threads
         __syncthreads();
     }
     auto value = [&](V raw) -> double {
@@ -157,7 +206,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     constexpr bool SMOOTH = (OP >= OP_JACOBI);
     constexpr bool BSRF = (OP == OP_JACOBI_BSR1);
     constexpr bool NEED_B = (OP == OP_RESIDUAL || SMOOTH);
-    const int row = blockIdx.x * SELL_TPB + threadIdx.x;
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
     const int slice = row >> 5, lane = threadIdx.x & 31;
     if (slice >= (n + SELL_C - 1) / SELL_C) return;            // whole warp
     const long long off = slice_off[slice];
@@ -166,64 +215,94 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     const int len = live ? row_len[row] : 0;
     const double *__restrict__ xg = a.x;
     double bi = 0.0, xi = 0.0, yi = 0.0;
+    int run = 0;                                               // STEPS: column of the last slot walked
     if (live) {
         if (NEED_B) bi = __ldg(a.b + row);
         if (SMOOTH) xi = __ldg(xg + row);
         if (OP == OP_ADD) yi = a.b[row];
+        if (STEPS) run = __ldg(first + row);
     }
     double acc = BSRF ? bi : 0.0, diag = 0.0;
-    const int *pj = cj + off + lane;
+    const J *pj = cj + off + lane;
     const V *pv = cv + off + lane;
-    if (PIPE) {
+    if constexpr (PIPE) {
     // software pipeline: the (index, value) slots of round r+1 are requested before round r's x
     // gathers are consumed, so a round costs one memory latency, not two
-    int c[SELL_U], cn[SELL_U];
-    double v[SELL_U], vn[SELL_U], xv[SELL_U];
+    int c[U], cn[U];
+    double v[U], vn[U], xv[U];
 #pragma unroll
-    for (int u = 0; u < SELL_U; ++u) {
+    for (int u = 0; u < U; ++u) {
         const bool in = u < len;
-        c[u] = in ? __ldcs(pj + (long long)u * SELL_C) : -1;
+        c[u] = in ? (int)__ldcs(pj + (long long)u * SELL_C) : -1;
         v[u] = in ? value(__ldcs(pv + (long long)u * SELL_C)) : 0.0;
     }
-    for (int k0 = 0; k0 < w; k0 += SELL_U) {
+    for (int k0 = 0; k0 < w; k0 += U) {
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
+        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            const int k = k0 + SELL_U + u;
+        for (int u = 0; u < U; ++u) {
+            const int k = k0 + U + u;
             const bool in = k < len;
-            cn[u] = in ? __ldcs(pj + (long long)k * SELL_C) : -1;
+            cn[u] = in ? (int)__ldcs(pj + (long long)k * SELL_C) : -1;
             vn[u] = in ? value(__ldcs(pv + (long long)k * SELL_C)) : 0.0;
         }
+        // ptxas otherwise sinks every load next to its use to save registers (3-7 gathers in flight, the prefetch
+        // AFTER the fold: a round then costs four latencies).  Making the first fold step wait for a word that depends
+        // on every load of the round forces all of them to be issued first; `tie` is 0 at run time (row_begin == 0:
+        // sell_op takes full row ranges only), which the compiler cannot know.
+        int tie = 0;
+        if (TIE) {
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            if (c[u] >= 0) {
+            for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]) | cn[u] | __double2loint(vn[u]);
+            tie &= a.row_begin;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
                 const double pr = mul_rn(v[u], xv[u]);
                 if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
             }
         }
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
+        for (int u = 0; u < U; ++u) {
             c[u] = cn[u];
             v[u] = vn[u];
         }
     }
     } else {
-    for (int k0 = 0; k0 < w; k0 += SELL_U) {
-        int c[SELL_U];
-        double v[SELL_U], xv[SELL_U];
+    for (int k0 = 0; k0 < w; k0 += U) {
+        int c[U];
+        J raw[U];
+        double v[U], xv[U];
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
+        for (int u = 0; u < U; ++u) {
             const bool in = k0 + u < len;
-            c[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : -1;
+            raw[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : (J)0;
             v[u] = in ? value(__ldcs(pv + (long long)(k0 + u) * SELL_C)) : 0.0;
         }
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
+        for (int u = 0; u < U; ++u) {
+            const bool in = k0 + u < len;
+            if (STEPS) run += (int)raw[u];                              // padding slots hold step 0
+            c[u] = in ? (STEPS ? run : (int)raw[u]) : -1;
+        }
+        int tie = 0;
+        if (TIE) {                                                      // all slot loads issued before the first gather
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            if (c[u] >= 0) {
+            for (int u = 0; u < U; ++u) tie |= (int)raw[u] | (CODED ? 0 : __double2loint((double)v[u]));
+            tie &= a.row_begin;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u] + (u == 0 ? tie : 0)) : 0.0;
+        if (TIE) {                                                      // all gathers issued before the fold
+#pragma unroll
+            for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]);
+            tie &= a.row_begin;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
                 const double pr = mul_rn(v[u], xv[u]);
                 if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
@@ -255,13 +334,21 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
 // positions [p0, p1) of the index list `Id` = ONE colour: rows of a colour never read each other, so the
 // parallel update equals the sequential sweep bit for bit.  Slot row r of the copy holds matrix row Id[r]
 // (columns keep the original numbering); x is updated in place.
-template <bool BSRF>
+// U slots per lane per round; `zero` is 0 at run time and ties every round's loads together (see sell_kernel): a
+// colour of a coarse level is a few thousand rows -- one wave of warps whose run time is the number of dependent
+// memory latencies in a row walk (2 per round), so short rows want ONE round.
+// STEPS: 16-bit column steps instead of 32-bit columns (Sell::cd / first)
+template <bool BSRF, int U, bool STEPS>
 __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const int p1, const long long *__restrict__ slice_off,
-                                                           const int *__restrict__ cj, const double *__restrict__ cv,
+                                                           const void *__restrict__ cols, const double *__restrict__ cv,
+                                                           const int *__restrict__ first,
                                                            const int *__restrict__ row_len, const int *__restrict__ Id,
-                                                           double *x, const double *__restrict__ b)
+                                                           double *x, const double *__restrict__ b, const int zero)
 {
-    const int r = (p0 & ~31) + blockIdx.x * SELL_TPB + threadIdx.x;          // slot row (slices may straddle colours)
+    constexpr bool TIE = U > 8;
+    using J = typename std::conditional<STEPS, unsigned short, int>::type;
+    const J *__restrict__ cj = reinterpret_cast<const J *>(cols);
+    const int r = (p0 & ~31) + blockIdx.x * blockDim.x + threadIdx.x;       // slot row (slices may straddle colours)
     const int slice = r >> 5, lane = threadIdx.x & 31;
     if ((slice << 5) >= p1) return;                                         // whole warp
     const bool live = r >= p0 && r < p1;
@@ -271,22 +358,40 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     const int row = live ? Id[r] : -1;
     const double bi = live ? b[row] : 0.0;
     double acc = BSRF ? bi : 0.0, diag = 0.0;
-    const int *pj = cj + off + lane;
+    const J *pj = cj + off + lane;
     const double *pv = cv + off + lane;
-    for (int k0 = 0; k0 < w; k0 += SELL_U) {
-        int c[SELL_U];
-        double v[SELL_U], xv[SELL_U];
+    int run = (STEPS && live) ? first[r] : 0;
+    for (int k0 = 0; k0 < w; k0 += U) {
+        int c[U];
+        J raw[U];
+        double v[U], xv[U];
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
+        for (int u = 0; u < U; ++u) {
             const bool in = k0 + u < len;
-            c[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : -1;
+            raw[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : (J)0;
             v[u] = in ? __ldcs(pv + (long long)(k0 + u) * SELL_C) : 0.0;
         }
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) xv[u] = (c[u] >= 0) ? x[c[u]] : 0.0;
+        for (int u = 0; u < U; ++u) {
+            if (STEPS) run += (int)raw[u];
+            c[u] = (k0 + u < len) ? (STEPS ? run : (int)raw[u]) : -1;
+        }
+        int tie = 0;
+        if (TIE) {
 #pragma unroll
-        for (int u = 0; u < SELL_U; ++u) {
-            if (c[u] >= 0) {
+            for (int u = 0; u < U; ++u) tie |= (int)raw[u] | __double2loint(v[u]);
+            tie &= zero;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? x[c[u] + (u == 0 ? tie : 0)] : 0.0;
+        if (TIE) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]);
+            tie &= zero;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
                 if (c[u] == row) diag = v[u];
                 else {
                     const double pr = mul_rn(v[u], xv[u]);
@@ -298,26 +403,71 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     if (live && diag != 0.0) x[row] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(bi, acc), diag);
 }
 
+template <bool BSRF>
+static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st)
+{
+    // B200AMG_SELL_GS_U: 8 / 16 / 32 for every colour (A/B); default by the size of the colour
+    static const int forced = [] { const char *e = getenv("B200AMG_SELL_GS_U"); return e ? atoi(e) : 0; }();
+    const int rows = p1 - (p0 & ~31);
+    const int U = forced ? forced : (rows < 64 * 1024 ? 32 : (rows < 512 * 1024 ? 16 : 8));
+    const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
+#define SELL_GS_LAUNCH(UU, TPB)                                                                                                   \
+    do {                                                                                                                          \
+        if (s.cd) sell_gs_kernel<BSRF, UU, true><<<(rows + TPB - 1) / TPB, TPB, 0, st>>>(p0, p1, s.slice_off, cols, s.cv, s.first, \
+                                                                                         s.row_len, Id, x, b, 0);                 \
+        else sell_gs_kernel<BSRF, UU, false><<<(rows + TPB - 1) / TPB, TPB, 0, st>>>(p0, p1, s.slice_off, cols, s.cv, nullptr,     \
+                                                                                     s.row_len, Id, x, b, 0);                     \
+    } while (0)
+    if (U == 32) SELL_GS_LAUNCH(32, 64);
+    else if (U == 16) SELL_GS_LAUNCH(16, 128);
+    else SELL_GS_LAUNCH(8, SELL_TPB);
+#undef SELL_GS_LAUNCH
+    return check_launch("sell_gs_kernel");
+}
+
 int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st)
 {
     if (p1 <= p0) return 0;
-    const int first = p0 & ~31;
-    const int grid = (p1 - first + SELL_TPB - 1) / SELL_TPB;
-    if (bsrf) sell_gs_kernel<true><<<grid, SELL_TPB, 0, st>>>(p0, p1, s.slice_off, s.cj, s.cv, s.row_len, Id, x, b);
-    else sell_gs_kernel<false><<<grid, SELL_TPB, 0, st>>>(p0, p1, s.slice_off, s.cj, s.cv, s.row_len, Id, x, b);
-    return check_launch("sell_gs_kernel");
+    return bsrf ? launch_sell_gs<true>(s, Id, p0, p1, x, b, st) : launch_sell_gs<false>(s, Id, p0, p1, x, b, st);
+}
+
+// few-row operators (< SELL_BIG_ROWS): 0 = U 8 prefetching as the compiler schedules it (round 1), 1 = U 8 prefetching
+// with all loads of a round forced in flight, 2 = U 16 likewise, 3 = U 32 two-phase likewise
+static int sell_small_mode()
+{
+    static const int m = [] { const char *e = getenv("B200AMG_SELL_SMALL"); return e ? atoi(e) : 2; }();
+    return m;
+}
+static int sell_small_tpb()
+{
+    static const int t = [] {
+        const char *e = getenv("B200AMG_SELL_SMALL_TPB");
+        const int v = e ? atoi(e) : 64;
+        return (v == 32 || v == 64 || v == 128 || v == 256) ? v : 64;
+    }();
+    return t;
 }
 
 template <int OP>
 static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
-    if (s.cc)
-        sell_kernel<OP, false, true><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cc, s.dict, s.row_len, a);
-    else if (s.n < 400000)
-        sell_kernel<OP, true, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, s.row_len, a);
-    else
-        sell_kernel<OP, false, false><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, s.row_len, a);
+    if (s.cc) {
+        sell_kernel<OP, SELL_U, false, 1><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
+    } else if (s.cd) {
+        sell_kernel<OP, SELL_U, false, 2><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
+    } else if (s.n < SELL_BIG_ROWS) {
+        // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: deeper rounds, and
+        // small blocks so that the few warps spread over all SMs
+        const int mode = sell_small_mode(), tpb = mode == 0 ? SELL_TPB : sell_small_tpb();
+        const int g = (s.n + tpb - 1) / tpb;
+        if (mode == 1) sell_kernel<OP, 8, true, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        else if (mode == 2) sell_kernel<OP, 16, true, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        else if (mode == 3) sell_kernel<OP, 32, false, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        else sell_kernel<OP, SELL_U, true, 0><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+    } else {
+        sell_kernel<OP, SELL_U, false, 0><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+    }
     return check_launch("sell_kernel");
 }
 

@@ -11,41 +11,97 @@
 
 namespace b200amg {
 
-constexpr int SL_TPB = 1024;
+constexpr int SL_TPB = 1024;        // block form
+constexpr int SL_TPB1 = 256;        // scalar form: few threads, many registers -- a colour of such a level is <= ~300 rows
+constexpr int SL_U = 16;            // operator entries of the NEXT colour's row held in registers while this colour folds
 
-// dirs: bit q = direction of pass q (0 forward: colours 0..K-1, 1 backward), npass passes in all
+// dirs: bit q = direction of pass q (0 forward: colours 0..K-1, 1 backward), npass passes in all.
+// A phase (one colour of one pass) used to cost Id -> Ap -> (Aj, Ax) -> fold = 4-6 dependent L2 latencies (~3 us; 26
+// phases per symmetric step).  The operator does not change, only x does: each thread requests the row it will relax in
+// the NEXT phase -- index, bounds, b, the first SL_U (column, value) pairs -- BEFORE it folds the current one, so after
+// the block barrier only shared-memory reads of x and the ordered fold remain on the critical path.
 template <bool BSRF>
-__global__ void __launch_bounds__(SL_TPB, 1) gs_level_cta_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
-                                                                 const double *__restrict__ Ax, const int *__restrict__ Id,
-                                                                 const int *__restrict__ cptr, int K, double *x,
-                                                                 const double *__restrict__ b, int npass, unsigned dirs,
-                                                                 int x_is_zero)
+__global__ void __launch_bounds__(SL_TPB1, 1) gs_level_cta_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                                  const double *__restrict__ Ax, const int *__restrict__ Id,
+                                                                  const int *__restrict__ cptr, int K, double *x,
+                                                                  const double *__restrict__ b, int npass, unsigned dirs,
+                                                                  int x_is_zero)
 {
     extern __shared__ double sl_x[];
-    for (int i = threadIdx.x; i < n; i += SL_TPB) sl_x[i] = x_is_zero ? 0.0 : x[i];
-    __syncthreads();
-    for (int q = 0; q < npass; ++q) {
-        const bool bwd = (dirs >> q) & 1u;
-        for (int cq = 0; cq < K; ++cq) {
-            const int c = bwd ? K - 1 - cq : cq;
-            const int p1 = cptr[c + 1];
-            for (int p = cptr[c] + (int)threadIdx.x; p < p1; p += SL_TPB) {
-                const int i = Id[p];
-                double acc = BSRF ? b[i] : 0.0, diag = 0.0;
-                const int hi = Ap[i + 1];
+    const int tid = threadIdx.x;
+    const int nphase = npass * K;
+    auto colour_of = [&](int ph) {
+        const int q = ph / K, cq = ph - q * K;
+        return ((dirs >> q) & 1u) ? K - 1 - cq : cq;
+    };
+    // one row walk from global memory (rows beyond the first of a colour, and the tail of rows longer than SL_U)
+    auto walk = [&](int i, int k, int hi, double &acc, double &diag) {
 #pragma unroll 4
-                for (int k = Ap[i]; k < hi; ++k) {
-                    const int j = Aj[k];
-                    const double v = Ax[k];
-                    if (j == i) diag = v;
-                    else acc = BSRF ? sub_rn(acc, mul_rn(v, sl_x[j])) : add_rn(acc, mul_rn(v, sl_x[j]));
-                }
-                if (diag != 0.0) sl_x[i] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(b[i], acc), diag);
-            }
-            __syncthreads();
+        for (; k < hi; ++k) {
+            const int j = Aj[k];
+            const double v = Ax[k];
+            if (j == i) diag = v;
+            else acc = BSRF ? sub_rn(acc, mul_rn(v, sl_x[j])) : add_rn(acc, mul_rn(v, sl_x[j]));
         }
+    };
+    int ci = -1, clo = 0, chi = 0, cc[SL_U];        // current phase's first row of this thread
+    double cb = 0.0, cv[SL_U];
+    auto request = [&](int ph, int &ri, int &rlo, int &rhi, double &rb, int (&rc)[SL_U], double (&rv)[SL_U]) {
+        ri = -1;
+        rlo = rhi = 0;
+        rb = 0.0;
+        if (ph < nphase) {
+            const int c = colour_of(ph);
+            const int p = cptr[c] + tid;
+            if (p < cptr[c + 1]) {
+                ri = Id[p];
+                rlo = Ap[ri];
+                rhi = Ap[ri + 1];
+                rb = b[ri];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SL_U; ++u) {
+            const bool in = rlo + u < rhi;
+            rc[u] = in ? Aj[rlo + u] : -1;
+            rv[u] = in ? Ax[rlo + u] : 0.0;
+        }
+    };
+    request(0, ci, clo, chi, cb, cc, cv);
+    for (int i = tid; i < n; i += SL_TPB1) sl_x[i] = x_is_zero ? 0.0 : x[i];
+    __syncthreads();
+    for (int ph = 0; ph < nphase; ++ph) {
+        int ni, nlo, nhi, nc[SL_U];
+        double nb, nv[SL_U];
+        request(ph + 1, ni, nlo, nhi, nb, nc, nv);
+        __syncwarp();                                   // the requests are issued before the fold below touches x
+        if (ci >= 0) {
+            double acc = BSRF ? cb : 0.0, diag = 0.0;
+#pragma unroll
+            for (int u = 0; u < SL_U; ++u) {
+                if (cc[u] >= 0) {
+                    if (cc[u] == ci) diag = cv[u];
+                    else acc = BSRF ? sub_rn(acc, mul_rn(cv[u], sl_x[cc[u]])) : add_rn(acc, mul_rn(cv[u], sl_x[cc[u]]));
+                }
+            }
+            walk(ci, clo + SL_U, chi, acc, diag);
+            if (diag != 0.0) sl_x[ci] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(cb, acc), diag);
+            // colours wider than the block: the remaining rows of this thread, straight from memory
+            const int c = colour_of(ph);
+            const int p1 = cptr[c + 1];
+            for (int p = cptr[c] + tid + SL_TPB1; p < p1; p += SL_TPB1) {
+                const int i = Id[p];
+                double a2 = BSRF ? b[i] : 0.0, d2 = 0.0;
+                walk(i, Ap[i], Ap[i + 1], a2, d2);
+                if (d2 != 0.0) sl_x[i] = BSRF ? div_rn(a2, d2) : div_rn(sub_rn(b[i], a2), d2);
+            }
+        }
+        __syncthreads();
+        ci = ni; clo = nlo; chi = nhi; cb = nb;
+#pragma unroll
+        for (int u = 0; u < SL_U; ++u) { cc[u] = nc[u]; cv[u] = nv[u]; }
     }
-    for (int i = threadIdx.x; i < n; i += SL_TPB) x[i] = sl_x[i];
+    for (int i = tid; i < n; i += SL_TPB1) x[i] = sl_x[i];
 }
 
 // block form: one warp per block row of the colour (the arithmetic of bsr_gs_color_warp_kernel), 32 rows in flight
@@ -156,6 +212,20 @@ static unsigned pass_dirs(int iters, int sweep, int *npass)
 // 55 6x6 blocks (2.6 M values) 0.84 -> 1.3 ms.  Hence the limit on stored values.
 constexpr long long SL_MAX_VALUES = 40000;
 
+// host emulation (tests/emu) has no function attributes: the shared-memory opt-in is a device matter
+#ifdef B200_HOST_EMULATION
+#define SL_OPT_IN(kernel) ((void)0)
+#else
+#define SL_OPT_IN(kernel)                                                                                                  \
+    do {                                                                                                                   \
+        static bool set = false;                                                                                           \
+        if (!set) {                                                                                                        \
+            B200_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * SL_MAX_N)); \
+            set = true;                                                                                                    \
+        }                                                                                                                  \
+    } while (0)
+#endif
+
 int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *Ap, const int *Aj, const double *Ax, const int *Id,
                  const int *cptr_dev, int K, double *x, const double *b, int iters, int sweep, bool x_is_zero, cudaStream_t st)
 {
@@ -165,26 +235,21 @@ int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *A
     int npass = 0;
     const unsigned dirs = pass_dirs(iters, sweep, &npass);
     const int smem = (int)sizeof(double) * n;
+    const int zi = x_is_zero ? 1 : 0;
     if (bs == 1) {
-        static bool set1 = false;
-        if (!set1) {
-            B200_CUDA(cudaFuncSetAttribute(gs_level_cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * SL_MAX_N));
-            B200_CUDA(cudaFuncSetAttribute(gs_level_cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * SL_MAX_N));
-            set1 = true;
+        if (bsrf) {
+            SL_OPT_IN(gs_level_cta_kernel<true>);
+            B200_LAUNCH(gs_level_cta_kernel<true>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
+        } else {
+            SL_OPT_IN(gs_level_cta_kernel<false>);
+            B200_LAUNCH(gs_level_cta_kernel<false>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
         }
-        if (bsrf) gs_level_cta_kernel<true><<<1, SL_TPB, smem, st>>>(n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, x_is_zero);
-        else gs_level_cta_kernel<false><<<1, SL_TPB, smem, st>>>(n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, x_is_zero);
         return check_launch("gs_level_cta_kernel");
     }
-#define SL_BSR(BSV)                                                                                                        \
-    case BSV: {                                                                                                            \
-        static bool setb = false;                                                                                          \
-        if (!setb) {                                                                                                       \
-            B200_CUDA(cudaFuncSetAttribute(bsr_gs_level_cta_kernel<BSV>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                                           (int)sizeof(double) * SL_MAX_N));                                               \
-            setb = true;                                                                                                   \
-        }                                                                                                                  \
-        bsr_gs_level_cta_kernel<BSV><<<1, SL_TPB, smem, st>>>(n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, x_is_zero); \
+#define SL_BSR(BSV)                                                                                                          \
+    case BSV: {                                                                                                              \
+        SL_OPT_IN(bsr_gs_level_cta_kernel<BSV>);                                                                             \
+        B200_LAUNCH(bsr_gs_level_cta_kernel<BSV>, 1, SL_TPB, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi); \
     } break;
     switch (bs) {
         SL_BSR(2) SL_BSR(3) SL_BSR(4) SL_BSR(5) SL_BSR(6) SL_BSR(7) SL_BSR(8)

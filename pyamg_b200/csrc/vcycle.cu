@@ -528,18 +528,20 @@ extern "C" int b200amg_vcycle_residual_norm2(void *handle, const double *x, cons
 
 // layout the engine streams an operator in: 1 CSR as given, 2 sliced-ELL copy, 3 CSR + 8-bit value codes,
 // 4 CSR row pointers + 8-bit (offset, value) pattern codes, 5 one row-pattern byte per row,
-// 6 sliced-ELL copy with 8-bit value codes;
-// 0 = block operator / no such level
+// 6 sliced-ELL copy with 8-bit value codes, 7 sliced-ELL copy with 16-bit column steps;
+// 0 = block operator / no such level.  which = 3: the colour-grouped copy of A that colour-ordered Gauss-Seidel
+// sweeps (2 or 7; 0 when the level has none)
 extern "C" int b200amg_vcycle_layout(void *handle, int level, int which)
 {
     Engine *E = reinterpret_cast<Engine *>(handle);
-    if (!E || level < 0 || level >= (int)E->lev.size() || which < 0 || which > 2) return 0;
+    if (!E || level < 0 || level >= (int)E->lev.size() || which < 0 || which > 3) return 0;
     const LevelRt &L = E->lev[level];
+    if (which == 3) return L.sGS.ok() ? (L.sGS.cd ? 7 : 2) : 0;
     if (which == 0 ? L.d.bs != 1 : (L.d.p_br != 1 || L.d.p_bc != 1)) return 0;
     const Sell &s = which == 0 ? L.sA : which == 1 ? L.sP : L.sR;
     const ValueDict &d = which == 0 ? L.dA : which == 1 ? L.dP : L.dR;
     if (which == 0 && L.rpA.ok()) return 5;
-    if (s.ok()) return s.cc ? 6 : 2;
+    if (s.ok()) return s.cc ? 6 : (s.cd ? 7 : 2);
     return d.ok() ? (d.offs ? 4 : 3) : 1;
 }
 

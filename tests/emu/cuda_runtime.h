@@ -6,6 +6,8 @@
 // dynamic shared memory only as a global array the test provides; no static shared memory, no atomics.  The product never
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
+#define B200_HOST_EMULATION 1
+#include <cstdlib>
 #include <algorithm>
 #include <atomic>
 #include <barrier>
@@ -139,6 +141,7 @@ template <class T> inline T __ldg(const T *p) { return *p; }
 inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }
+inline int __double2loint(double d) { unsigned long long r; memcpy(&r, &d, 8); return (int)(unsigned)(r & 0xffffffffull); }
 #define B200_PREFETCH_L2(p) ((void)(p))
 
 #define B200_LAUNCH(kernel, grid, block, smem, stream, ...) \

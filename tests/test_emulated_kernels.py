@@ -626,3 +626,111 @@ def test_bsr_solve_kernels_equal_reference(emu_bsr, bs):
         assert emu_bsr.emu_bsr_matvec_warp(nr, R, C, P(i32(Rm.indptr)), P(i32(Rm.indices)), P(np.ravel(Rm.data).copy()), P(xr),
                                            None, P(y), 0) == 0
         assert np.array_equal(y, Rm * xr), (R, C)
+
+
+# ---- whole smoothing steps of small levels in one launch (csrc/small_level.cu) -------------------------------------------
+@pytest.fixture(scope='module')
+def emu_small():
+    if shutil.which('g++') is None:
+        pytest.skip('g++ not available')
+    csrc = os.path.join(ROOT, 'pyamg_b200', 'csrc')
+    srcs = [os.path.join(csrc, 'small_level.cu'), os.path.join(EMU, 'emu_small_level.cpp'), os.path.join(EMU, 'emu_globals.cpp')]
+    out = os.path.join(EMU, '_build', 'libemu_small.so')
+    deps = srcs + [os.path.join(EMU, 'cuda_runtime.h'), os.path.join(csrc, 'internal.cuh'), os.path.join(csrc, 'common.cuh')]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU, '-I', csrc,
+                        '-x', 'c++'] + srcs + ['-o', out], check=True)
+    lib = ctypes.CDLL(out)
+    lib.emu_gs_level_cta.restype = c_int
+    lib.emu_gs_level_cta.argtypes = [c_int, c_int, c_int, ctypes.c_longlong, vp, vp, vp, vp, vp, c_int, vp, vp, c_int, c_int, c_int]
+    return lib
+
+
+@pytest.mark.parametrize('n,per_row,sweep,iters,zero', [(700, 9, 2, 1, False), (300, 25, 0, 2, True), (1500, 5, 1, 1, False),
+                                                        (40, 3, 2, 3, False)])
+@pytest.mark.parametrize('bsrf', [False, True])
+def test_small_level_step_scalar(emu_small, n, per_row, sweep, iters, zero, bsrf):
+    """gs_level_cta_kernel (iterate in shared memory, the NEXT colour's row requested before the current one is folded;
+    rows longer than the 16 prefetched entries and colours wider than the 256 threads included) against the oracle's
+    sequential gauss_seidel_indexed / bsr_gauss_seidel_indexed(blocksize 1) sweeps over the same MIS colour ordering"""
+    from oracle import relaxation as orx
+    rng = np.random.RandomState(n + per_row)
+    rows = np.repeat(np.arange(n), per_row)
+    cols = (rows + rng.randint(-4 * per_row, 4 * per_row, rows.size)) % n
+    A = sp.csr_matrix((rng.rand(rows.size) - 0.4, (rows, cols)), shape=(n, n))
+    A = sp.csr_matrix(A + A.T + sp.diags(rng.rand(n) + 2.0 * per_row))
+    A.sort_indices()
+    if n == 700:                                    # a row without a diagonal entry is left alone, like the reference
+        A = A.tolil(); A[5, 5] = 0.0; A = sp.csr_matrix(A); A.eliminate_zeros()
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), A.data.copy()
+    idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(A, oracle.port))
+    idx, ptr = i32(idx), i32(ptr)
+    K = len(ptr) - 1
+    if n == 1500:
+        assert np.max(np.diff(ptr)) > 256           # a colour wider than the block
+    if per_row == 25:
+        assert np.max(np.diff(Ap)) > 16             # rows longer than the prefetch depth
+    b, x0 = rng.rand(n), (np.zeros(n) if zero else rng.rand(n))
+    want = x0.copy()
+    for _ in range(iters):
+        for (r0, r1, dr) in (((0, n, 1),) if sweep == 0 else ((n - 1, -1, -1),) if sweep == 1 else ((0, n, 1), (n - 1, -1, -1))):
+            if bsrf:
+                oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, r0, r1, dr, 1)
+            else:
+                oracle.port.gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, r0, r1, dr)
+    got = np.full(n, np.nan) if zero else x0.copy()
+    assert emu_small.emu_gs_level_cta(1, int(bsrf), n, len(Ax), P(Ap), P(Aj), P(Ax), P(idx), P(ptr), K, P(got), P(b), iters, sweep,
+                                      int(zero)) == 0
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize('bs,sweep', [(2, 2), (3, 0), (6, 1)])
+def test_small_level_step_block(emu_small, bs, sweep):
+    """bsr_gs_level_cta_kernel against the oracle's bsr_gauss_seidel_indexed sweeps"""
+    from oracle import relaxation as orx
+    nb = 60
+    A, _, b, x0 = block_problem(nb, bs, 40 + bs)
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy()
+    G = sp.csr_matrix((np.ones(len(Aj)), Aj, Ap), shape=(nb, nb))
+    idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(G, oracle.port))
+    idx, ptr = i32(idx), i32(ptr)
+    want = x0.copy()
+    for (r0, r1, dr) in (((0, nb, 1),) if sweep == 0 else ((nb - 1, -1, -1),) if sweep == 1 else ((0, nb, 1), (nb - 1, -1, -1))):
+        oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, r0, r1, dr, bs)
+    got = x0.copy()
+    assert emu_small.emu_gs_level_cta(bs, 1, nb * bs, len(Ax), P(Ap), P(Aj), P(Ax), P(idx), P(ptr), len(ptr) - 1, P(got), P(b), 1,
+                                      sweep, 0) == 0
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize('bs,nb,density', [(2, 300, 0.6), (3, 200, 0.6), (6, 80, 0.7)])
+def test_bsr_warp_gauss_seidel_long_rows(emu_bsr, bs, nb, density):
+    """the batched warp-per-block-row sweep on rows that need SEVERAL batches (4 or 8 passes of 32 / bs blocks each) and a
+    ragged last one, against the reference's bsr_gauss_seidel_indexed on the same colour ordering"""
+    from oracle import relaxation as orx
+    rng = np.random.RandomState(bs)
+    pat = sp.csr_matrix(sp.random(nb, nb, density, random_state=rng, format='csr') + sp.identity(nb))
+    pat = sp.csr_matrix(pat + pat.T)
+    pat.sort_indices()
+    assert np.max(np.diff(pat.indptr)) > (32 // bs) * (8 if bs <= 3 else 4)
+    data = 0.01 * rng.randn(len(pat.indices), bs, bs)
+    rows_of = np.repeat(np.arange(nb), np.diff(pat.indptr))
+    data[rows_of == pat.indices] += 3.0 * np.eye(bs)        # diagonally dominant: the sweeps stay finite
+    A = sp.bsr_matrix((data, pat.indices.astype(np.int32), pat.indptr.astype(np.int32)), shape=(nb * bs, nb * bs))
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ravel(A.data).copy()
+    b, x0 = rng.randn(nb * bs), rng.randn(nb * bs)
+    # any partition into "colours" is a valid index list for the indexed sweep; rows of a dense pattern all conflict, so
+    # the parallel kernel is only the sequential sweep if every colour is ONE row
+    idx = i32(rng.permutation(nb))
+    ptr = np.ascontiguousarray(np.arange(nb + 1), dtype=np.intc)
+    cp = ptr.ctypes.data_as(ctypes.POINTER(c_int))
+    want, got = x0.copy(), x0.copy()
+    oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, 0, nb, 1, bs)
+    oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, nb - 1, -1, -1, bs)
+    assert emu_bsr.emu_bsr_gauss_seidel_warp(P(Ap), P(Aj), P(Ax), P(got), P(b), 0, nb, 1, bs, P(idx), cp, nb) == 0
+    assert emu_bsr.emu_bsr_gauss_seidel_warp(P(Ap), P(Aj), P(Ax), P(got), P(b), nb - 1, -1, -1, bs, P(idx), cp, nb) == 0
+    assert np.all(np.isfinite(want)) and np.array_equal(got, want)
+    y = np.full(nb * bs, np.nan)
+    assert emu_bsr.emu_bsr_matvec_warp(nb, bs, bs, P(Ap), P(Aj), P(Ax), P(x0), P(b), P(y), 1) == 0
+    assert np.array_equal(y, b - A * x0)

@@ -476,3 +476,50 @@ def test_sliced_ell_layout_bit_exact(amg, name, n, per_row, few_values):
     xo = x.copy(); orx.jacobi(Ab, xo, b, iterations=1, omega=0.7, core=oracle.port)
     assert np.array_equal(run(5, np.zeros(n)), xo)
     amg._lib.load().b200amg_op_destroy(h)
+
+
+@pytest.mark.parametrize('name,n,per_row,span,sort,expect', [('steps_fit', 40000, 31, 90, True, 7), ('long_rows', 9000, 240, 700, True, 7),
+                                                             ('step_too_wide', 300000, 20, 140000, True, 2),
+                                                             ('unsorted_rows', 40000, 31, 90, False, 2)])
+def test_sliced_ell_16bit_column_steps(amg, monkeypatch, name, n, per_row, span, sort, expect):
+    """layout 7: columns stored as 16-bit steps from the previous stored column (10 bytes per slot).  Needs rows
+    stored by ascending column with steps < 65 536; anything else keeps 32-bit columns.  Same bits either way."""
+    monkeypatch.setenv('B200AMG_SELL_COL16', '2')           # the engine uses it from 400 000 rows; here for every size
+    rng = np.random.RandomState(12)
+    rows = np.repeat(np.arange(n), per_row)
+    cols = (rows + rng.randint(-span, span, rows.size)) % n
+    A = sp.csr_matrix((rng.rand(rows.size) - 0.3, (rows, cols)), shape=(n, n))      # duplicates summed: ragged rows
+    A = sp.csr_matrix(A + sp.diags(rng.rand(n) + 1.0)); A.sort_indices()
+    if name == 'steps_fit':
+        A = sp.csr_matrix(A)
+        A.data[A.indptr[7]:A.indptr[8]] = 0.0; A.eliminate_zeros()                  # an empty row
+    if not sort:            # reverse the storage order of every 5th row
+        for i in range(0, n, 5):
+            lo, hi = A.indptr[i], A.indptr[i + 1]
+            A.indices[lo:hi] = A.indices[lo:hi][::-1].copy(); A.data[lo:hi] = A.data[lo:hi][::-1].copy()
+        A.has_sorted_indices = False
+    x, b = rng.rand(n), rng.rand(n)
+    dA = amg.DevMat.from_scipy(A)                           # storage order kept as given
+    P = lambda t: t.data_ptr()
+    import ctypes
+    h = ctypes.c_void_p()
+    amg._lib.call('b200amg_op_create', n, P(dA.indptr), P(dA.indices), P(dA.data), 2, ctypes.byref(h), 0)
+    try:
+        assert amg._lib.load().b200amg_op_layout(h) == expect
+
+        def run(op, y0):
+            y = dev(y0)
+            dx, db = dev(x), dev(b)
+            amg._lib.call('b200amg_op_apply', h, op, P(dx), P(db), P(y), 0.7, 0)
+            torch.cuda.synchronize()
+            return y.cpu().numpy()
+        core = oracle.port
+        Ax = np.zeros(n); core.csr_matvec(n, n, A.indptr, A.indices, A.data, x, Ax)
+        assert np.array_equal(run(0, np.zeros(n)), Ax)
+        assert np.array_equal(run(2, np.zeros(n)), b - Ax)
+        assert np.array_equal(run(3, b), b + Ax)
+        xo = x.copy(); tmp = np.empty(n)
+        core.jacobi(A.indptr, A.indices, A.data, xo, b, tmp, 0, n, 1, np.array([0.7]))
+        assert np.array_equal(run(4, np.zeros(n)), xo)
+    finally:
+        amg._lib.call('b200amg_op_destroy', h)
