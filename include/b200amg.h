@@ -144,6 +144,12 @@ int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax,
                       void **handle_out, void *stream);
 int b200amg_op_apply(void *handle, int op, const double *x, const double *b, double *y, double omega,
                      void *stream);
+/* The same handle over a BLOCK operator (n_brow block rows of R x C row-major blocks, 1..8): b200amg_op_apply then
+ * runs scipy's bsr_matvec arithmetic (MATVEC / RESIDUAL / ADD; `_sparsetools/bsr.h` bsr_matvec) or, for square
+ * blocks, one amg_core.bsr_jacobi sweep from x to y (pyamg/amg_core/relaxation.h:267-360; both JACOBI op codes).
+ * Used for the block levels of the row-partitioned multi-GPU cycle; b200amg_op_layout returns 0. */
+int b200amg_bsr_op_create(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax,
+                          void **handle_out, void *stream);
 int b200amg_op_layout(void *handle);     /* 1 CSR, 2 sliced-ELL, 3 CSR + 8-bit value codes, 4 CSR rows + 8-bit
                                            * (column offset, value) pattern codes, 5 one row-pattern
                                            * byte per row (stencil operators), 6 sliced-ELL with

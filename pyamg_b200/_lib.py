@@ -47,6 +47,7 @@ _SIGS = {
     'b200amg_op_create': (c_int, [c_int, p, p, p, c_int, POINTER(c_void_p), p]),
     'b200amg_op_apply': (c_int, [p, c_int, p, p, p, c_double, p]),
     'b200amg_op_layout': (c_int, [p]),
+    'b200amg_bsr_op_create': (c_int, [c_int, c_int, c_int, p, p, p, POINTER(c_void_p), p]),
     'b200amg_vcycle_layout': (c_int, [p, c_int, c_int]),
     'b200amg_op_destroy': (c_int, [p]),
     'b200amg_halo_push': (c_int, [p, c_int, p, p, p, p, p, c_int, p, p]),

@@ -203,7 +203,23 @@ struct OpHandle {
     Sell sell;
     ValueDict vd;
     RowPat rp;
+    int R = 1, C = 1;                // block shape (b200amg_bsr_op_create); n_row counts BLOCK rows then
 };
+
+// Block operator behind the same handle: n_brow block rows of R x C blocks (row-major), nnz = stored blocks.  The
+// row-partitioned multi-GPU cycle applies local block operators to [owned | halo] vectors through b200amg_op_apply
+// (MATVEC / RESIDUAL / ADD: scipy bsr_matvec arithmetic; JACOBI and JACOBI_BSR1: amg_core.bsr_jacobi from x to y).
+extern "C" int b200amg_bsr_op_create(int n_brow, int R, int C, const int *Ap, const int *Aj, const double *Ax,
+                                     void **handle_out, void *stream)
+{
+    if (n_brow < 0 || !handle_out || R < 1 || C < 1 || R > 8 || C > 8) return set_err(B200AMG_EINVAL, "bsr_op_create: bad arguments");
+    OpHandle *h = new OpHandle{n_brow, -1, Ap, Aj, Ax, Sell(), ValueDict(), RowPat()};
+    h->R = R;
+    h->C = C;
+    h->nnz = n_brow > 0 ? nnz_lookup(Ap, n_brow, S(stream)) : 0;
+    *handle_out = h;
+    return 0;
+}
 
 extern "C" int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
                                  void **handle_out, void *stream)
@@ -248,6 +264,16 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
     if (!h || op < 0 || op > OP_JACOBI_BSR1 || op == OP_SPMV_AB) return set_err(B200AMG_EINVAL, "op_apply: bad arguments");
     if (h->n_row == 0) return 0;
+    if (h->R != 1 || h->C != 1) {
+        switch (op) {
+        case OP_MATVEC: return bsr_matvec(h->n_row, h->R, h->C, h->Ap, h->Aj, h->Ax, x, nullptr, y, 0, S(stream), h->nnz);
+        case OP_RESIDUAL: return bsr_matvec(h->n_row, h->R, h->C, h->Ap, h->Aj, h->Ax, x, b, y, 1, S(stream), h->nnz);
+        case OP_ADD: return bsr_matvec(h->n_row, h->R, h->C, h->Ap, h->Aj, h->Ax, x, b, y, 2, S(stream), h->nnz);
+        default:
+            if (h->R != h->C) return set_err(B200AMG_EINVAL, "op_apply: Jacobi needs square blocks");
+            return bsr_jacobi(h->R, 0, h->n_row, h->Ap, h->Aj, h->Ax, x, y, b, omega, S(stream));
+        }
+    }
     StreamArgs a{h->Ap, h->Aj, h->Ax, x, b, y, h->nnz, 0, h->n_row, 1.0, 0.0, omega};
     h->vd.apply(a);
     if (h->rp.ok()) return rowpat_op(op, h->rp, a, S(stream));
@@ -258,7 +284,7 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
 extern "C" int b200amg_op_layout(void *handle)
 {
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
-    if (!h) return 0;
+    if (!h || h->R != 1 || h->C != 1) return 0;
     if (h->rp.ok()) return 5;
     if (h->sell.ok()) return h->sell.cc ? 6 : (h->sell.cd ? 7 : 2);
     return h->vd.ok() ? (h->vd.offs ? 4 : 3) : 1;

@@ -479,7 +479,9 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
 #define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
-        if (bsr_warp_batch()) {
+        // batches pay while the colour is a fraction of a wave (config 4, run 15: level 2, 48 rows per colour, 0.76 -> 0.56 ms
+        // per step; level 1, 6 600 rows per colour, 0.65 -> 0.79 ms: the 128 registers cost resident warps there)
+        if (bsr_warp_batch() && p1 - p0 <= kSMs * 8) {
             if (backward) { if (perm) { GS_WARP(true, true, 4); } else { GS_WARP(true, false, 4); } }
             else { if (perm) { GS_WARP(false, true, 4); } else { GS_WARP(false, false, 4); } }
         } else {

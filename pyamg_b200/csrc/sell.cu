@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
 {
     constexpr bool CODED = (FMT == 1), STEPS = (FMT == 2);
     static_assert(!(PIPE && FMT != 0), "the prefetching form keeps 32-bit columns and fp64 values");
+    static_assert(PIPE || !TIE, "only the prefetching form ties its loads");
     using V = typename std::conditional<CODED, unsigned char, double>::type;
     using J = typename std::conditional<STEPS, unsigned short, int>::type;
     const V *__restrict__ cv = reinterpret_cast<const V *>(cvals);
@@ -287,22 +288,11 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
             if (STEPS) run += (int)raw[u];                              // padding slots hold step 0
             c[u] = in ? (STEPS ? run : (int)raw[u]) : -1;
         }
-        int tie = 0;
-        if (TIE) {                                                      // all slot loads issued before the first gather
 #pragma unroll
-            for (int u = 0; u < U; ++u) tie |= (int)raw[u] | (CODED ? 0 : __double2loint((double)v[u]));
-            tie &= a.row_begin;
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u] + (u == 0 ? tie : 0)) : 0.0;
-        if (TIE) {                                                      // all gathers issued before the fold
-#pragma unroll
-            for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]);
-            tie &= a.row_begin;
-        }
+        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
+            if (c[u] >= 0) {
                 const double pr = mul_rn(v[u], xv[u]);
                 if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
@@ -406,10 +396,11 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
 template <bool BSRF>
 static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st)
 {
-    // B200AMG_SELL_GS_U: 8 / 16 / 32 for every colour (A/B); default by the size of the colour
+    // B200AMG_SELL_GS_U: 8 / 32 for every colour (A/B); default by the size of the colour
     static const int forced = [] { const char *e = getenv("B200AMG_SELL_GS_U"); return e ? atoi(e) : 0; }();
     const int rows = p1 - (p0 & ~31);
-    const int U = forced ? forced : (rows < 64 * 1024 ? 32 : (rows < 512 * 1024 ? 16 : 8));
+    // config 3 (run 15): colours below 64 k rows 3-7 % faster with one 32-slot round; 121 k rows: 16 slots SLOWER than 8
+    const int U = forced ? forced : (rows < 64 * 1024 ? 32 : 8);
     const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
 #define SELL_GS_LAUNCH(UU, TPB)                                                                                                   \
     do {                                                                                                                          \
@@ -419,7 +410,6 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
                                                                                      s.row_len, Id, x, b, 0);                     \
     } while (0)
     if (U == 32) SELL_GS_LAUNCH(32, 64);
-    else if (U == 16) SELL_GS_LAUNCH(16, 128);
     else SELL_GS_LAUNCH(8, SELL_TPB);
 #undef SELL_GS_LAUNCH
     return check_launch("sell_gs_kernel");
@@ -431,21 +421,11 @@ int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, doubl
     return bsrf ? launch_sell_gs<true>(s, Id, p0, p1, x, b, st) : launch_sell_gs<false>(s, Id, p0, p1, x, b, st);
 }
 
-// few-row operators (< SELL_BIG_ROWS): 0 = U 8 prefetching as the compiler schedules it (round 1), 1 = U 8 prefetching
-// with all loads of a round forced in flight, 2 = U 16 likewise, 3 = U 32 two-phase likewise
-static int sell_small_mode()
+// few-row operators (< SELL_BIG_ROWS).  B200AMG_SELL_SMALL=0: the round-1 form for every op (A/B switch)
+static bool sell_small_deep()
 {
-    static const int m = [] { const char *e = getenv("B200AMG_SELL_SMALL"); return e ? atoi(e) : 2; }();
-    return m;
-}
-static int sell_small_tpb()
-{
-    static const int t = [] {
-        const char *e = getenv("B200AMG_SELL_SMALL_TPB");
-        const int v = e ? atoi(e) : 64;
-        return (v == 32 || v == 64 || v == 128 || v == 256) ? v : 64;
-    }();
-    return t;
+    static const bool on = [] { const char *e = getenv("B200AMG_SELL_SMALL"); return !(e && e[0] == '0'); }();
+    return on;
 }
 
 template <int OP>
@@ -457,14 +437,16 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
     } else if (s.cd) {
         sell_kernel<OP, SELL_U, false, 2><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
     } else if (s.n < SELL_BIG_ROWS) {
-        // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: deeper rounds, and
-        // small blocks so that the few warps spread over all SMs
-        const int mode = sell_small_mode(), tpb = mode == 0 ? SELL_TPB : sell_small_tpb();
-        const int g = (s.n + tpb - 1) / tpb;
-        if (mode == 1) sell_kernel<OP, 8, true, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
-        else if (mode == 2) sell_kernel<OP, 16, true, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
-        else if (mode == 3) sell_kernel<OP, 32, false, 0, true><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
-        else sell_kernel<OP, SELL_U, true, 0><<<g, tpb, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: 16 slots per round,
+        // all forced in flight, and 64-thread blocks so that the few warps spread over all SMs.  Measured on config 2
+        // (profiles/r02/run15_summary.txt): restriction of level 1 (44 629 rows x 240) 0.088 -> 0.047 ms, level-2
+        // residual 0.021 -> 0.017 ms; 8 slots tied 0.052, 32 slots in two phases 0.064, 256-thread blocks 0.064.  The
+        // smoothing ops already kept their loads together (the diagonal test splits the basic block) and are fastest
+        // as they were (0.021 vs 0.028 ms).
+        if (OP < OP_JACOBI && sell_small_deep())
+            sell_kernel<OP, 16, true, 0, true><<<(s.n + 63) / 64, 64, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        else
+            sell_kernel<OP, SELL_U, true, 0><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     } else {
         sell_kernel<OP, SELL_U, false, 0><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     }

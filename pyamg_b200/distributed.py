@@ -40,11 +40,17 @@ class DeviceBackend:
         return torch.cuda.current_stream().cuda_stream
 
     class Op:
-        def __init__(self, be, ip, ix, dx, n_row):
-            self.be, self.ip, self.ix, self.dx, self.n_row = be, ip, ix, dx, int(n_row)
+        """n_row rows (BLOCK rows of R x C blocks when R * C > 1) of a local operator"""
+
+        def __init__(self, be, ip, ix, dx, n_row, R=1, C=1):
+            self.be, self.ip, self.ix, self.dx, self.n_row, self.R, self.C = be, ip, ix, dx, int(n_row), int(R), int(C)
             self.h = ctypes.c_void_p()
-            be._lib.call('b200amg_op_create', self.n_row, ip.data_ptr(), ix.data_ptr(), dx.data_ptr(), 0,
-                         ctypes.byref(self.h), be.stream())
+            if self.R * self.C > 1:
+                be._lib.call('b200amg_bsr_op_create', self.n_row, self.R, self.C, ip.data_ptr(), ix.data_ptr(), dx.data_ptr(),
+                             ctypes.byref(self.h), be.stream())
+            else:
+                be._lib.call('b200amg_op_create', self.n_row, ip.data_ptr(), ix.data_ptr(), dx.data_ptr(), 0,
+                             ctypes.byref(self.h), be.stream())
 
         def apply(self, op, x, b, y, omega=0.0):
             self.be._lib.call('b200amg_op_apply', self.h, op, x.data_ptr(), 0 if b is None else b.data_ptr(),
@@ -55,8 +61,8 @@ class DeviceBackend:
             return int(self.be._lib.load().b200amg_op_layout(self.h))
 
         def diagonal(self):
-            d = torch.empty(self.n_row, dtype=torch.float64, device=self.dx.device)
-            self.be._lib.call('b200amg_extract_diag', self.n_row, 1, self.ip.data_ptr(), self.ix.data_ptr(),
+            d = torch.empty(self.n_row * self.R, dtype=torch.float64, device=self.dx.device)
+            self.be._lib.call('b200amg_extract_diag', self.n_row, self.R, self.ip.data_ptr(), self.ix.data_ptr(),
                               self.dx.data_ptr(), d.data_ptr(), self.be.stream())
             return d
 
@@ -66,8 +72,8 @@ class DeviceBackend:
             except Exception:
                 pass
 
-    def make_op(self, ip, ix, dx, n_row):
-        return DeviceBackend.Op(self, ip, ix, dx, n_row)
+    def make_op(self, ip, ix, dx, n_row, R=1, C=1):
+        return DeviceBackend.Op(self, ip, ix, dx, n_row, R, C)
 
     def scale_diag(self, omega, b, diag, x, flavor):
         self._lib.call('b200amg_scale_diag', diag.numel(), float(omega), b.data_ptr(), diag.data_ptr(), x.data_ptr(),
@@ -79,9 +85,9 @@ class DeviceBackend:
         if p1 <= p0:
             return
         cp = (ctypes.c_int * 2)(int(p0), int(p1))
-        if flavor:
+        if flavor or op.R > 1:                  # block rows: amg_core.bsr_gauss_seidel over the listed BLOCK rows
             self._lib.call('b200amg_bsr_gauss_seidel', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
-                           b.data_ptr(), int(p0), int(p1), 1, 1, Id.data_ptr(), cp, 1, self.stream())
+                           b.data_ptr(), int(p0), int(p1), 1, op.R, Id.data_ptr(), cp, 1, self.stream())
         else:
             self._lib.call('b200amg_gauss_seidel_indexed', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
                            b.data_ptr(), Id.data_ptr(), int(p0), int(p1), 1, cp, 1, self.stream())
@@ -117,14 +123,15 @@ def describe(ml):
     the raw CSR arrays of A, P, R (torch tensors), sizes, arithmetic flavor and resolved smoothers"""
     out = []
     for L in ml.levels[:-1]:
-        for nm in ('A', 'P', 'R'):
-            if not getattr(L, nm).is_scalar:
-                raise NotImplementedError('distributed cycle: scalar (1x1 block) levels only')
+        if L.A.blocksize[0] != L.A.blocksize[1] or L.P.blocksize[0] != L.A.blocksize[0] or L.R.blocksize[1] != L.A.blocksize[0] \
+                or L.R.blocksize[0] != L.P.blocksize[1]:
+            raise NotImplementedError('distributed cycle: block shapes of A, P, R do not chain')
         pre, post = L.presmoother, L.postsmoother
         for sm in (pre, post):
             if sm.kind not in (0, 1, 2):
                 raise NotImplementedError('distributed cycle: Jacobi, colour-ordered Gauss-Seidel or None smoothers only')
         d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
+             'bs': int(L.A.blocksize[0]), 'bsc': int(L.P.blocksize[1]),     # unknowns per block row: this level / the next
              'pre': (pre.kind, pre.omega, pre.iterations, pre.sweep), 'post': (post.kind, post.omega, post.iterations, post.sweep)}
         ordered = [sm for sm in (pre, post) if sm.kind == 2]
         if ordered:                                     # one GLOBAL colour ordering per level (multilevel._build_engine checks it)
@@ -180,7 +187,8 @@ class DistributedSolver:
                 if levels[k]['n'] < limit:
                     ka = k
                     break
-            info = [{q: levels[k][q] for q in ('n', 'nc', 'flavor', 'pre', 'post')} for k in range(ka)]
+            info = [{q: levels[k].get(q, 1) if q in ('bs', 'bsc') else levels[k][q] for q in ('n', 'nc', 'flavor', 'pre', 'post', 'bs', 'bsc')}
+                    for k in range(ka)]
             for k in range(ka):
                 info[k]['K'] = len(levels[k]['color_ptr']) - 1 if 'color_ptr' in levels[k] else 0
                 info[k]['gs_csr'] = int(levels[k].get('gs_csr', 1))
@@ -202,25 +210,29 @@ class DistributedSolver:
     def _distribute_level(self, k, info, src):
         G, rank, dev = self.G, self.rank, self.device
         n, nc = info['n'], info['nc']
-        sp, spc = part.split_points(n, G), part.split_points(nc, G)
+        # block levels are cut between BLOCK rows (a block row is relaxed as a unit); vectors, halo plans and every
+        # size below count scalars.  The coarse split of level k is the fine split of level k + 1 (bsc_k == bs_{k+1}).
+        bs, bsc = info.get('bs', 1), info.get('bsc', 1)
+        spb, spcb = part.split_points(n // bs, G), part.split_points(nc // bsc, G)
+        sp, spc = [v * bs for v in spb], [v * bsc for v in spcb]
         L = _Level()
         L.info, L.split, L.csplit = info, sp, spc
         L.n_own, L.nc_own = sp[rank + 1] - sp[rank], spc[rank + 1] - spc[rank]
-        shapes = {'A': (sp, sp), 'P': (sp, spc), 'R': (spc, sp)}
+        shapes = {'A': (spb, spb, bs, bs), 'P': (spb, spcb, bs, bsc), 'R': (spcb, spb, bsc, bs)}
         for nm in ('A', 'P', 'R'):
-            rs, cs = shapes[nm]
+            rs, cs, bR, bC = shapes[nm]
             header = [None]
             if rank == 0:
                 Mp, Mj, Mx = src[nm]
-                halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1])[3] for p in range(G)]
+                halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC)[3] for p in range(G)]
                 plans = part.build_plans(halos, cs)
                 header[0] = [pl.pack() for pl in plans]
             dist.broadcast_object_list(header, src=0, group=self.group)
-            plan = part.HaloPlan.unpack(header[0][rank]).to(dev)
+            plan = part.HaloPlan.unpack(header[0][rank]).expanded(bC).to(dev)
             if rank == 0:
                 mine = None
                 for p in range(G):
-                    ip, ix, dx, _ = part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1])
+                    ip, ix, dx, _ = part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC)
                     if p == 0:
                         mine = (ip, ix, dx)
                     else:
@@ -233,8 +245,9 @@ class DistributedSolver:
                 sizes = torch.empty(2, dtype=torch.int64, device=dev)
                 dist.recv(sizes, 0, group=self.group)
                 n_ip, n_ix = [int(v) for v in sizes.tolist()]
-                ip, ix, dx = _recv_tensors([(n_ip, torch.int32), (n_ix, torch.int32), (n_ix, torch.float64)], 0, dev, self.group)
-            setattr(L, nm, self.be.make_op(ip, ix, dx, ip.numel() - 1))
+                ip, ix, dx = _recv_tensors([(n_ip, torch.int32), (n_ix, torch.int32), (n_ix * bR * bC, torch.float64)], 0, dev,
+                                           self.group)
+            setattr(L, nm, self.be.make_op(ip, ix, dx, ip.numel() - 1, bR, bC))
             setattr(L, 'plan' + nm, plan)
         L.diag = L.A.diagonal()
         # colour-ordered Gauss-Seidel: the GLOBAL colouring cut by slab -- every rank keeps, colour by colour, the rows of
@@ -249,8 +262,8 @@ class DistributedSolver:
                 for p in range(G):
                     segs, ptr = [], [0]
                     for c in range(len(cp) - 1):
-                        seg = Id[cp[c]:cp[c + 1]]
-                        seg = seg[(seg >= sp[p]) & (seg < sp[p + 1])] - sp[p]
+                        seg = Id[cp[c]:cp[c + 1]]                   # (block) rows of this colour
+                        seg = seg[(seg >= spb[p]) & (seg < spb[p + 1])] - spb[p]
                         segs.append(seg)
                         ptr.append(ptr[-1] + int(seg.numel()))
                     parts[p] = (torch.cat(segs).to(torch.int32) if segs else torch.zeros(0, dtype=torch.int32), ptr)

@@ -29,9 +29,10 @@ def owner_counts(sorted_cols, split):
     return (pos[1:] - pos[:-1]).tolist()
 
 
-def localize(indptr, indices, data, row0, row1, col0, col1):
-    """Rows [row0, row1) of a CSR/BSR(1x1) matrix with columns renumbered for the rank owning the
-    column range [col0, col1).  -> (indptr int32, indices int32, data, halo_cols int64 ascending)"""
+def localize(indptr, indices, data, row0, row1, col0, col1, blockvals=1):
+    """Rows [row0, row1) of a CSR/BSR matrix with columns renumbered for the rank owning the
+    column range [col0, col1).  -> (indptr int32, indices int32, data, halo_cols int64 ascending).
+    For a BSR operator rows / columns count BLOCKS and every stored block carries `blockvals` = R * C values."""
     s, e = int(indptr[row0]), int(indptr[row1])
     ip = (indptr[row0:row1 + 1] - indptr[row0]).to(torch.int32).contiguous()
     cols = indices[s:e].to(torch.int64)
@@ -41,7 +42,7 @@ def localize(indptr, indices, data, row0, row1, col0, col1):
     loc[own] = cols[own] - col0
     if halo_cols.numel():
         loc[~own] = (col1 - col0) + torch.searchsorted(halo_cols, cols[~own])
-    return ip, loc.to(torch.int32).contiguous(), data[s:e].contiguous().clone(), halo_cols
+    return ip, loc.to(torch.int32).contiguous(), data[s * blockvals:e * blockvals].contiguous().clone(), halo_cols
 
 
 class HaloPlan:
@@ -56,6 +57,16 @@ class HaloPlan:
     def to(self, device):
         self.send_idx = self.send_idx.to(device)
         return self
+
+    def expanded(self, bs):
+        """the plan of the SCALAR vector space when this plan counts blocks of bs unknowns: block q is the scalars
+        q * bs .. q * bs + bs - 1, in the owned part and in the halo alike"""
+        if bs == 1:
+            return self
+        k = torch.arange(bs, dtype=torch.int64, device=self.send_idx.device)
+        idx = (self.send_idx.to(torch.int64)[:, None] * bs + k[None, :]).reshape(-1)
+        return HaloPlan(self.n_own * bs, self.n_halo * bs, idx, [c * bs for c in self.send_counts],
+                        [c * bs for c in self.recv_counts])
 
     def pack(self):
         return {'n_own': self.n_own, 'n_halo': self.n_halo, 'send_idx': self.send_idx.cpu(),

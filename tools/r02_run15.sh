@@ -11,19 +11,19 @@ tail -5 $out/gpu_suite.log | cut -c1-300 >> $sum
 run() { # name, bench args, env...
   name=$1; shift
   args=$1; shift
-  env "$@" timeout 900 python bench.py $args --steps 20 --warmup 3 --no-cpu-baseline --no-extras > $out/bench_$name.json 2> $out/bench_$name.err; echo "$name rc=$?" | tee -a $sum
+  env "$@" timeout 900 python bench.py $args --steps 20 --warmup 3 --no-extras > $out/bench_$name.json 2> $out/bench_$name.err; echo "$name rc=$?" | tee -a $sum
 }
-run cfg2_default "" X=1
-run cfg2_small0_round1 "" B200AMG_SELL_SMALL=0
-run cfg2_small1_u8_tied "" B200AMG_SELL_SMALL=1
-run cfg2_small3_u32_tied "" B200AMG_SELL_SMALL=3
-run cfg2_small2_tpb256 "" B200AMG_SELL_SMALL_TPB=256
-run cfg2_col16_off "" B200AMG_SELL_COL16=0
+run cfg2_default "--no-cpu-baseline" X=1
+run cfg2_small0_round1 "--no-cpu-baseline" B200AMG_SELL_SMALL=0
+run cfg2_small1_u8_tied "--no-cpu-baseline" B200AMG_SELL_SMALL=1
+run cfg2_small3_u32_tied "--no-cpu-baseline" B200AMG_SELL_SMALL=3
+run cfg2_small2_tpb256 "--no-cpu-baseline" B200AMG_SELL_SMALL_TPB=256
+run cfg2_col16_off "--no-cpu-baseline" B200AMG_SELL_COL16=0
 run cfg3_default "--config 3" X=1
-run cfg3_gs_u8 "--config 3" B200AMG_SELL_GS_U=8
-run cfg3_col16_off "--config 3" B200AMG_SELL_COL16=0
+run cfg3_gs_u8 "--config 3 --no-cpu-baseline" B200AMG_SELL_GS_U=8
+run cfg3_col16_off "--config 3 --no-cpu-baseline" B200AMG_SELL_COL16=0
 run cfg4_default "--config 4" X=1
-run cfg4_batch_off "--config 4" B200AMG_BSR_WARP_BATCH=0
+run cfg4_batch_off "--config 4 --no-cpu-baseline" B200AMG_BSR_WARP_BATCH=0
 python - <<'PY' | tee -a gpurun_out/r02n/summary.txt
 import json, glob
 for f in sorted(glob.glob('gpurun_out/r02n/bench_*.json')):
@@ -35,7 +35,7 @@ for f in sorted(glob.glob('gpurun_out/r02n/bench_*.json')):
         ops = r['op_ms']
         if 'cfg2' in f:
             ops = {k: v for k, v in ops.items() if 'L0' not in k or 'restrict' in k}
-        print(f.split('/')[-1], round(d['value'], 2), 'ms', round(d['ms_per_step'], 4), 'frac', r.get('frac'), 'golden', g.get('history_vs_reference_max_rel_diff'), ops)
+        print(f.split('/')[-1], round(d['value'], 2), 'parity', (d.get('parity_in_run') or {}).get('max_rel_diff_x_vs_cpu_reference'), 'ms', round(d['ms_per_step'], 4), 'frac', r.get('frac'), 'golden', g.get('history_vs_reference_max_rel_diff'), ops)
         if 'default' in f:
             print('   layouts', lay)
     except Exception as e:
