@@ -79,15 +79,17 @@ class DeviceBackend:
         self._lib.call('b200amg_scale_diag', diag.numel(), float(omega), b.data_ptr(), diag.data_ptr(), x.data_ptr(),
                        int(flavor), self.stream())
 
-    def gs_color(self, op, x, b, Id, p0, p1, flavor):
+    def gs_color(self, op, x, b, Id, p0, p1, flavor, backward=False):
         """rows Id[p0:p1] (one colour of the GLOBAL colouring, local numbering) relaxed in parallel, x in place:
-        amg_core.gauss_seidel_indexed / bsr_gauss_seidel(bs = 1) arithmetic (relaxation.h:394-426, :89-173)"""
+        amg_core.gauss_seidel_indexed / bsr_gauss_seidel arithmetic (relaxation.h:394-426, :89-173).  `backward` matters
+        for block rows only: the point sweep inside the diagonal block runs in the direction of the pass (:150-163)"""
         if p1 <= p0:
             return
         cp = (ctypes.c_int * 2)(int(p0), int(p1))
         if flavor or op.R > 1:                  # block rows: amg_core.bsr_gauss_seidel over the listed BLOCK rows
+            r0, r1, dr = (int(p1) - 1, int(p0) - 1, -1) if backward else (int(p0), int(p1), 1)
             self._lib.call('b200amg_bsr_gauss_seidel', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
-                           b.data_ptr(), int(p0), int(p1), 1, op.R, Id.data_ptr(), cp, 1, self.stream())
+                           b.data_ptr(), r0, r1, dr, op.R, Id.data_ptr(), cp, 1, self.stream())
         else:
             self._lib.call('b200amg_gauss_seidel_indexed', op.ip.data_ptr(), op.ix.data_ptr(), op.dx.data_ptr(), x.data_ptr(),
                            b.data_ptr(), Id.data_ptr(), int(p0), int(p1), 1, cp, 1, self.stream())
@@ -472,7 +474,7 @@ class DistributedSolver:
                     for q in range(K):
                         c = K - 1 - q if backward else q
                         self.exchange(L.planA, x)
-                        self.be.gs_color(L.A, x, b, L.Id, L.cptr[c], L.cptr[c + 1], L.info['flavor'] and not L.info.get('gs_csr', 1))
+                        self.be.gs_color(L.A, x, b, L.Id, L.cptr[c], L.cptr[c + 1], L.info['flavor'] and not L.info.get('gs_csr', 1), backward)
             return x, xs
         op = OP_JACOBI_BSR1 if L.info['flavor'] else OP_JACOBI
         for it in range(iters):

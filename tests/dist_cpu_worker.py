@@ -27,11 +27,29 @@ def _load(name):
 
 
 class CpuOp:
-    def __init__(self, ip, ix, dx, n_row):
+    def __init__(self, ip, ix, dx, n_row, R=1, C=1):
         self.ip, self.ix, self.dx, self.n = ip.numpy(), ix.numpy(), dx.numpy(), int(n_row)
         self.ncol = int(self.ix.max()) + 1 if self.ix.size else 0
+        self.R, self.C = int(R), int(C)
+
+    def _apply_block(self, op, x, b, y, omega):
+        """block rows: scipy bsr_matvec / amg_core.bsr_jacobi (the oracle's restatements)"""
+        xn, yn = x.numpy(), y.numpy()
+        nb, R, C = self.n, self.R, self.C
+        n = nb * R
+        if op in (0, 2, 3):
+            t = np.zeros(n)
+            oracle.port.bsr_matvec(nb, self.ncol, R, C, self.ip, self.ix, self.dx, np.ascontiguousarray(xn), t)
+            yn[:n] = t if op == 0 else (b.numpy()[:n] - t if op == 2 else yn[:n] + t)
+        else:
+            xc, temp = xn.copy(), xn.copy()
+            oracle.port.bsr_jacobi(self.ip, self.ix, self.dx, xc, np.ascontiguousarray(b.numpy()[:n]), temp, 0, nb, 1, R,
+                                   np.array([omega]))
+            yn[:n] = xc[:n]
 
     def apply(self, op, x, b, y, omega=0.0):
+        if self.R * self.C > 1:
+            return self._apply_block(op, x, b, y, omega)
         xn, yn = x.numpy(), y.numpy()
         n = self.n
         if op in (0, 2, 3):
@@ -53,19 +71,21 @@ class CpuOp:
             yn[:n] = xc[:n]
 
     def diagonal(self):
-        d = np.zeros(self.n)
+        R = self.R
+        d = np.zeros(self.n * R)
+        blocks = self.dx.reshape(-1, R, self.C)
         for i in range(self.n):
             for k in range(self.ip[i], self.ip[i + 1]):
                 if self.ix[k] == i:
-                    d[i] = self.dx[k]
+                    d[i * R:(i + 1) * R] = np.diag(blocks[k])
         return torch.from_numpy(d)
 
 
 class CpuBackend:
     device = torch.device('cpu')
 
-    def make_op(self, ip, ix, dx, n_row):
-        return CpuOp(ip, ix, dx, n_row)
+    def make_op(self, ip, ix, dx, n_row, R=1, C=1):
+        return CpuOp(ip, ix, dx, n_row, R, C)
 
     def scale_diag(self, omega, b, diag, x, flavor):
         n = diag.numel()
@@ -74,14 +94,15 @@ class CpuBackend:
             v = (omega * bn) / dn if flavor else omega * (bn / dn)
         x.numpy()[:n] = np.where(dn != 0, v, 0.0)
 
-    def gs_color(self, op, x, b, Id, p0, p1, flavor):
+    def gs_color(self, op, x, b, Id, p0, p1, flavor, backward=False):
         if p1 <= p0:
             return
-        xn, bn = x.numpy(), np.ascontiguousarray(b.numpy()[:op.n])
+        xn, bn = x.numpy(), np.ascontiguousarray(b.numpy()[:op.n * op.R])
         idx = np.ascontiguousarray(Id.numpy(), dtype=np.intc)
         xc = np.ascontiguousarray(xn)
-        if flavor:
-            oracle.port.bsr_gauss_seidel_indexed(op.ip, op.ix, op.dx, xc, bn, idx, int(p0), int(p1), 1, 1)
+        if flavor or op.R > 1:
+            r0, r1, dr = (int(p1) - 1, int(p0) - 1, -1) if backward else (int(p0), int(p1), 1)
+            oracle.port.bsr_gauss_seidel_indexed(op.ip, op.ix, op.dx, xc, bn, idx, r0, r1, dr, op.R)
         else:
             oracle.port.gauss_seidel_indexed(op.ip, op.ix, op.dx, xc, bn, idx, int(p0), int(p1), 1)
         xn[:] = xc
@@ -111,7 +132,8 @@ def t3(M):
 
 def main():
     grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
-    mcgs = len(sys.argv) > 4 and sys.argv[4] == 'mcgs'
+    mcgs = len(sys.argv) > 4 and sys.argv[4] in ('mcgs', 'bsr_mcgs')
+    block = len(sys.argv) > 4 and sys.argv[4] in ('bsr_jacobi', 'bsr_mcgs')
     dist.init_process_group('gloo')
     rank = dist.get_rank()
     D = _load('distributed')
@@ -120,14 +142,36 @@ def main():
         A = poisson3d(grid); A.sort_indices()
         np.random.seed(5)
         jac = ('jacobi', {'omega': 4.0 / 3.0})
-        host = osa.smoothed_aggregation_hierarchy(A, presmoother=jac, postsmoother=jac, max_coarse=12, core=oracle.port, improve_candidates=None)
+        if block:
+            # a vector problem: 3 unknowns per grid point (BSR 3x3), 6 candidates -> coarse levels with 6 x 6 blocks,
+            # P with 3 x 6 / 6 x 6 blocks (the block shapes of the elasticity hierarchy of BASELINE config 4)
+            rng = np.random.RandomState(3)
+            M = rng.rand(3, 3); M = M @ M.T + 3 * np.eye(3)
+            A = sp.bsr_matrix(sp.kron(A, M), blocksize=(3, 3)); A.sort_indices()
+            B = np.hstack([np.kron(np.ones((A.shape[0] // 3, 1)), np.eye(3)), rng.rand(A.shape[0], 3)])
+            jac = ('jacobi', {'omega': 0.9, 'withrho': False})
+            host = osa.smoothed_aggregation_hierarchy(A, B, presmoother=jac, postsmoother=jac, max_coarse=6, core=oracle.port,
+                                                      improve_candidates=None)
+        else:
+            host = osa.smoothed_aggregation_hierarchy(A, presmoother=jac, postsmoother=jac, max_coarse=12, core=oracle.port,
+                                                      improve_candidates=None)
         b = np.random.rand(A.shape[0])
         levels_desc = []
         for L in host[:-1]:
             d = {'n': L.A.shape[0], 'nc': L.P.shape[1], 'flavor': 0 if L.A.format == 'csr' else 1,
                  'pre': (1, L.pre[1]['omega'], 1), 'post': (1, L.post[1]['omega'], 1),
                  'A': t3(L.A), 'P': t3(L.P), 'R': t3(L.R)}
-            if mcgs:        # symmetric multicolour Gauss-Seidel over the MIS colours of the GLOBAL matrix graph
+            if block:
+                d['bs'], d['bsc'] = int(L.A.blocksize[0]), int(L.P.blocksize[1])
+                assert L.P.blocksize[0] == d['bs'] and L.R.blocksize == (d['bsc'], d['bs'])
+            if mcgs and block:      # block rows relaxed colour by colour (MIS colours of the BLOCK graph): bsr_gauss_seidel
+                from oracle import relaxation as orx
+                G = sp.csr_matrix((np.ones(len(L.A.indices)), L.A.indices, L.A.indptr), shape=(d['n'] // d['bs'],) * 2)
+                idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(G, oracle.port))
+                L.pre = L.post = ('bsr_gauss_seidel_indexed', {'indices': idx, 'sweep': 'symmetric', 'iterations': 1})
+                d['pre'] = d['post'] = (2, 1.0, 1, 'symmetric')
+                d['Id'], d['color_ptr'], d['gs_csr'] = torch.from_numpy(np.ascontiguousarray(idx, np.int32)), [int(v) for v in ptr], 0
+            elif mcgs:        # symmetric multicolour Gauss-Seidel over the MIS colours of the GLOBAL matrix graph
                 from oracle import relaxation as orx
                 idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(sp.csr_matrix(L.A), oracle.port))
                 L.pre = L.post = ('gauss_seidel_indexed', {'indices': idx, 'sweep': 'symmetric', 'iterations': 1})

@@ -14,6 +14,7 @@ sys.path.insert(0, ROOT)
 def main():
     grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
     mcgs = len(sys.argv) > 4 and sys.argv[4] == 'mcgs'
+    block = len(sys.argv) > 4 and sys.argv[4] == 'bsr'
     local = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local)
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
@@ -21,7 +22,15 @@ def main():
     import pyamg_b200 as amg
     from pyamg_b200.distributed import DistributedSolver
     ml, b = None, None
-    if rank == 0:
+    if rank == 0 and block:
+        # P1 elasticity on grid^3 vertices: BSR 3 x 3 on the finest level, 6 x 6 below (6 rigid-body modes), symmetric
+        # colour-ordered block Gauss-Seidel -- the hierarchy shape of BASELINE config 4
+        A, B = amg.gallery.linear_elasticity_tets(grid)
+        np.random.seed(2)
+        mc = ('multicolor_gauss_seidel', {'sweep': 'symmetric'})
+        ml = amg.smoothed_aggregation_solver(A, B, presmoother=mc, postsmoother=mc, max_coarse=10)
+        b = np.random.rand(A.shape[0])
+    elif rank == 0:
         A = amg.gallery.poisson((grid * world, grid, grid))
         np.random.seed(2)
         jac = ('jacobi', {'omega': 4.0 / 3.0})

@@ -39,3 +39,13 @@ def test_partitioned_multicolour_gauss_seidel_equals_global(world, grid, thresh)
     r = run(world, grid, thresh, 3, 29600 + world * 10 + grid, 'mcgs')
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert 'bit-identical x True' in r.stdout
+
+
+@pytest.mark.parametrize('world,grid,thresh,mode', [(2, 8, 100, 'bsr_jacobi'), (2, 8, 100, 'bsr_mcgs'), (3, 7, 100, 'bsr_mcgs')])
+def test_partitioned_block_levels_equal_global(world, grid, thresh, mode):
+    """BSR levels (3 x 3 blocks on the finest level, 6 x 6 below, 3 x 6 / 6 x 6 transfer blocks) cut between block rows:
+    bsr_matvec / bsr_jacobi / block-row colour-ordered bsr_gauss_seidel on slabs, bit-identical to the single-process cycle"""
+    r = run(world, grid, thresh, 3, 29700 + world * 10 + grid + (5 if mode == 'bsr_mcgs' else 0), mode)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert 'bit-identical x True' in r.stdout
+    assert 'partitioned levels 2 of 3' in r.stdout

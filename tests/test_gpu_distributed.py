@@ -12,12 +12,13 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize('grid,thresh,extra', [(24, 200, []), (16, 10 ** 9, []), (24, 200, ['mcgs'])])
+@pytest.mark.parametrize('grid,thresh,extra', [(24, 200, []), (16, 10 ** 9, []), (24, 200, ['mcgs']),
+                                               (14, 100, ['bsr'])])      # block levels (3 x 3, 6 x 6) cut between block rows
 def test_partitioned_cycle_on_device(grid, thresh, extra):
     if not torch.cuda.is_available():
         pytest.skip('needs a CUDA device')
     world = min(2, torch.cuda.device_count())
-    port = 29700 + grid + 50 * len(extra)
+    port = 29700 + grid + 50 * len(extra) + (7 if extra == ['bsr'] else 0)
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
            '--master-addr', '127.0.0.1', '--master-port', str(port), os.path.join(HERE, 'dist_gpu_worker.py'),
            str(grid), str(thresh), '4'] + extra
