@@ -338,6 +338,15 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     constexpr bool TIE = U > 8;
     using J = typename std::conditional<STEPS, unsigned short, int>::type;
     const J *__restrict__ cj = reinterpret_cast<const J *>(cols);
+    // Programmatic dependent launch: the NEXT colour's kernel may start as soon as every block of this one has, and
+    // everything up to cudaGridDependencySynchronize() below -- which waits for the previous kernel to finish and its
+    // writes to be visible -- reads only what no kernel of the cycle writes (the operator, the index list).  A colour of
+    // a coarse level is launch latency plus a chain of dependent loads; this takes the launch and the operator part
+    // of the chain off the critical path.  Launched without the attribute both calls do nothing.  Only the one-round
+    // form for small colours (U == 32) is launched that way; it reads x around L1 (ld.cg): blocks of two kernels can
+    // share an SM now, and a line of x the earlier kernel pulled into L1 must not serve the later one.
+    constexpr bool PDL = (U == 32);
+    if (PDL) cudaTriggerProgrammaticLaunchCompletion();
     const int r = (p0 & ~31) + blockIdx.x * blockDim.x + threadIdx.x;       // slot row (slices may straddle colours)
     const int slice = r >> 5, lane = threadIdx.x & 31;
     if ((slice << 5) >= p1) return;                                         // whole warp
@@ -346,11 +355,10 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
     const int len = live ? row_len[r] : 0;
     const int row = live ? Id[r] : -1;
-    const double bi = live ? b[row] : 0.0;
-    double acc = BSRF ? bi : 0.0, diag = 0.0;
     const J *pj = cj + off + lane;
     const double *pv = cv + off + lane;
     int run = (STEPS && live) ? first[r] : 0;
+    double bi = 0.0, acc = 0.0, diag = 0.0;
     for (int k0 = 0; k0 < w; k0 += U) {
         int c[U];
         J raw[U];
@@ -372,8 +380,16 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
             for (int u = 0; u < U; ++u) tie |= (int)raw[u] | __double2loint(v[u]);
             tie &= zero;
         }
+        if (k0 == 0) {
+            if (PDL) cudaGridDependencySynchronize();                       // x and b are final from here on
+            bi = live ? (PDL ? __ldcg(b + row) : b[row]) : 0.0;
+            acc = BSRF ? bi : 0.0;
+        }
 #pragma unroll
-        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? x[c[u] + (u == 0 ? tie : 0)] : 0.0;
+        for (int u = 0; u < U; ++u) {
+            const double *px = x + c[u] + (u == 0 ? tie : 0);
+            xv[u] = (c[u] >= 0) ? (PDL ? __ldcg(px) : *px) : 0.0;
+        }
         if (TIE) {
 #pragma unroll
             for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]);
@@ -390,6 +406,10 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
             }
         }
     }
+    if (w == 0) {                                                           // a slice of empty rows
+        if (PDL) cudaGridDependencySynchronize();
+        bi = live ? b[row] : 0.0;
+    }
     if (live && diag != 0.0) x[row] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(bi, acc), diag);
 }
 
@@ -402,15 +422,32 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
     // config 3 (run 15): colours below 64 k rows 3-7 % faster with one 32-slot round; 121 k rows: 16 slots SLOWER than 8
     const int U = forced ? forced : (rows < 64 * 1024 ? 32 : 8);
     const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
+    // B200AMG_PDL=0: plain stream order (A/B switch)
+    static const bool pdl = [] { const char *e = getenv("B200AMG_PDL"); return !(e && e[0] == '0'); }();
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const int *firstp = s.cd ? s.first : nullptr;
 #define SELL_GS_LAUNCH(UU, TPB)                                                                                                   \
     do {                                                                                                                          \
-        if (s.cd) sell_gs_kernel<BSRF, UU, true><<<(rows + TPB - 1) / TPB, TPB, 0, st>>>(p0, p1, s.slice_off, cols, s.cv, s.first, \
-                                                                                         s.row_len, Id, x, b, 0);                 \
-        else sell_gs_kernel<BSRF, UU, false><<<(rows + TPB - 1) / TPB, TPB, 0, st>>>(p0, p1, s.slice_off, cols, s.cv, nullptr,     \
-                                                                                     s.row_len, Id, x, b, 0);                     \
+        cfg.gridDim = dim3((unsigned)((rows + TPB - 1) / TPB));                                                                   \
+        cfg.blockDim = dim3(TPB);                                                                                                 \
+        cudaError_t e = s.cd ? cudaLaunchKernelEx(&cfg, sell_gs_kernel<BSRF, UU, true>, p0, p1, (const long long *)s.slice_off,   \
+                                                  cols, (const double *)s.cv, firstp, (const int *)s.row_len, Id, x, b, 0)       \
+                             : cudaLaunchKernelEx(&cfg, sell_gs_kernel<BSRF, UU, false>, p0, p1, (const long long *)s.slice_off,  \
+                                                  cols, (const double *)s.cv, firstp, (const int *)s.row_len, Id, x, b, 0);      \
+        if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                            \
     } while (0)
-    if (U == 32) SELL_GS_LAUNCH(32, 64);
-    else SELL_GS_LAUNCH(8, SELL_TPB);
+    if (U == 32) {
+        SELL_GS_LAUNCH(32, 64);
+    } else {
+        cfg.numAttrs = 0;
+        SELL_GS_LAUNCH(8, SELL_TPB);
+    }
 #undef SELL_GS_LAUNCH
     return check_launch("sell_gs_kernel");
 }
