@@ -27,6 +27,7 @@ __device__ __forceinline__ double block_sum(double v)
 __global__ void __launch_bounds__(DOT_TPB) dot_partial_kernel(long long n, const double *__restrict__ x,
                                                               const double *__restrict__ y, double *__restrict__ part)
 {
+    pdl_enter();
     double s = 0.0;
     const long long stride = (long long)gridDim.x * DOT_TPB;
     long long i = (long long)blockIdx.x * DOT_TPB + threadIdx.x;
@@ -47,6 +48,7 @@ __global__ void __launch_bounds__(DOT_TPB) dot_partial_kernel(long long n, const
 
 __global__ void __launch_bounds__(DOT_TPB) dot_final_kernel(int m, const double *__restrict__ part, double *out)
 {
+    pdl_enter();
     double s = 0.0;
     for (int i = threadIdx.x; i < m; i += DOT_TPB) s += part[i];
     s = block_sum(s);
@@ -58,9 +60,9 @@ int dot(long long n, const double *x, const double *y, double *out, double *work
     if (n < 0) return set_err(B200AMG_EINVAL, "dot: n < 0");
     long long want = (n / 2 + DOT_TPB - 1) / DOT_TPB;
     int grid = (int)(want < 1 ? 1 : (want > DOT_MAX_GRID ? DOT_MAX_GRID : want));
-    dot_partial_kernel<<<grid, DOT_TPB, 0, st>>>(n, x, y, work);
+    B200_LAUNCH_PDL(dot_partial_kernel, grid, DOT_TPB, 0, st, n, x, y, work);
     B200_TRY(check_launch("dot_partial_kernel"));
-    dot_final_kernel<<<1, DOT_TPB, 0, st>>>(grid, work, out);
+    B200_LAUNCH_PDL(dot_final_kernel, 1, DOT_TPB, 0, st, grid, work, out);
     return check_launch("dot_final_kernel");
 }
 
@@ -112,6 +114,7 @@ constexpr int PCG_HIST0 = 16;
 // which == 0: after pAp = <Ap, p>; which == 1: after rz_new = <r, z>
 __global__ void pcg_scalars_kernel(double *st, int which)
 {
+    pdl_enter();
     if (st[6] != 0.0) return;
     if (which == 0) {
         if (st[1] < 0.0) { st[6] = -1.0; return; }               // _cg.py:120-122
@@ -136,6 +139,7 @@ __global__ void __launch_bounds__(256) pcg_update_xr_kernel(long long n, const d
                                                             const double *__restrict__ p, const double *__restrict__ Ap,
                                                             double *x, double *r, int update_r)
 {
+    pdl_enter();
     if (st[6] != 0.0) return;
     const double alpha = st[3];
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
@@ -148,6 +152,7 @@ __global__ void __launch_bounds__(256) pcg_update_xr_kernel(long long n, const d
 __global__ void __launch_bounds__(256) pcg_update_p_kernel(long long n, const double *__restrict__ st,
                                                            const double *__restrict__ z, double *p)
 {
+    pdl_enter();
     if (st[6] != 0.0) return;
     const double beta = st[4];
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
@@ -156,7 +161,7 @@ __global__ void __launch_bounds__(256) pcg_update_p_kernel(long long n, const do
 
 int pcg_scalars(double *st, int which, cudaStream_t s)
 {
-    pcg_scalars_kernel<<<1, 1, 0, s>>>(st, which);
+    B200_LAUNCH_PDL(pcg_scalars_kernel, 1, 1, 0, s, st, which);
     return check_launch("pcg_scalars_kernel");
 }
 
@@ -164,14 +169,14 @@ int pcg_update_xr(long long n, const double *st, const double *p, const double *
                   cudaStream_t s)
 {
     if (n <= 0) return 0;
-    pcg_update_xr_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, st, p, Ap, x, r, update_r);
+    B200_LAUNCH_PDL(pcg_update_xr_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, p, Ap, x, r, update_r);
     return check_launch("pcg_update_xr_kernel");
 }
 
 int pcg_update_p(long long n, const double *st, const double *z, double *p, cudaStream_t s)
 {
     if (n <= 0) return 0;
-    pcg_update_p_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, st, z, p);
+    B200_LAUNCH_PDL(pcg_update_p_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, z, p);
     return check_launch("pcg_update_p_kernel");
 }
 
@@ -231,6 +236,7 @@ int extract_diag(int nb, int bs, const int *Ap, const int *Aj, const double *Ax,
 __global__ void __launch_bounds__(256) scale_diag_kernel(long long n, double omega, const double *__restrict__ b,
                                                          const double *__restrict__ d, double *__restrict__ x, int bsrf)
 {
+    pdl_enter();
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
     const double di = d[i];
@@ -242,7 +248,7 @@ __global__ void __launch_bounds__(256) scale_diag_kernel(long long n, double ome
 int scale_diag(long long n, double omega, const double *b, const double *d, double *x, int bsrf, cudaStream_t st)
 {
     if (n <= 0) return 0;
-    scale_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, omega, b, d, x, bsrf);
+    B200_LAUNCH_PDL(scale_diag_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n, omega, b, d, x, bsrf);
     return check_launch("scale_diag_kernel");
 }
 
@@ -250,6 +256,7 @@ int scale_diag(long long n, double omega, const double *b, const double *d, doub
 __global__ void __launch_bounds__(256) dense_matvec_kernel(int n, const double *__restrict__ M,
                                                            const double *__restrict__ x, double *__restrict__ y)
 {
+    pdl_enter();
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= n) return;
     const double *m = M + (size_t)row * n;
@@ -263,7 +270,7 @@ __global__ void __launch_bounds__(256) dense_matvec_kernel(int n, const double *
 int dense_matvec(int n, const double *M, const double *x, double *y, cudaStream_t st)
 {
     if (n <= 0) return 0;
-    dense_matvec_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, M, x, y);
+    B200_LAUNCH_PDL(dense_matvec_kernel, (n + 7) / 8, 256, 0, st, n, M, x, y);
     return check_launch("dense_matvec_kernel");
 }
 

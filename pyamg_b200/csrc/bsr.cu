@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(256) bsr_matvec_kernel(int n_brow, int R, int 
                                                          const double *__restrict__ x, const double *__restrict__ b,
                                                          double *y, int mode)
 {
+    pdl_enter();
     const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= (long long)n_brow * R) return;
     const int i = (int)(g / R), r = (int)(g - (long long)i * R);
@@ -36,6 +37,7 @@ __global__ void __launch_bounds__(256) bsr_jacobi_kernel(int nb0, int nb1, const
                                                          const double *__restrict__ xin, double *__restrict__ xout,
                                                          const double *__restrict__ b, double omega)
 {
+    pdl_enter();
     const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= (long long)(nb1 - nb0) * BS) return;
     const int i = nb0 + (int)(g / BS), k = (int)(g % BS);
@@ -123,6 +125,7 @@ __global__ void __launch_bounds__(128) bsr_gs_color_kernel(const int *__restrict
                                                            const double *__restrict__ b, const int *__restrict__ Id,
                                                            int p0, int p1, bool backward)
 {
+    pdl_enter();
     constexpr int RPW = 32 / BS;                        // block rows per warp
     const int lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int g = lane / BS, k = lane - g * BS;
@@ -215,6 +218,7 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
                                                                 const double *__restrict__ b, const int *__restrict__ Id,
                                                                 int p0, int p1, int zero)
 {
+    pdl_enter();
     constexpr int G = 32 / BS;                          // blocks per pass
     constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -320,6 +324,7 @@ __global__ void __launch_bounds__(128) bsr_matvec_warp_kernel(int n_brow, int C,
                                                               const double *__restrict__ x, const double *__restrict__ b,
                                                               double *y, int mode, int zero)
 {
+    pdl_enter();
     constexpr int G = 32 / R;
     constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -395,6 +400,7 @@ __global__ void bsr_gs_sequential_kernel(const int *__restrict__ Ap, const int *
                                          const double *__restrict__ Ax, double *x, const double *__restrict__ b,
                                          const int *Id, int start, int stop, int step)
 {
+    pdl_enter();
     for (int p = start; p != stop; p += step) {
         bsr_gs_block_row<BS>(Id ? Id[p] : p, Ap, Aj, Ax, x, b, step < 0);
         __threadfence_block();
@@ -451,11 +457,11 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     // (measured on BASELINE config 4, profiles/r02: 1 331 x 6 rows 0.54 -> 0.13 ms; 2.08 M x 3 rows 0.53 -> 2.3 ms)
     if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && n < kSMs * 1024 && nblocks >= 2ll * (32 / R) * n_brow) {
         const unsigned grid = (unsigned)((n_brow + 3) / 4);
-        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH((bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
-        else { R_SWITCH(R, B200_LAUNCH((bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH_PDL((bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        else { R_SWITCH(R, B200_LAUNCH_PDL((bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
         return check_launch("bsr_matvec_warp_kernel");
     }
-    B200_LAUNCH(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
+    B200_LAUNCH_PDL(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
     return check_launch("bsr_matvec_kernel");
 }
 
@@ -465,7 +471,7 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
     const long long n = (long long)(nb1 - nb0) * bs;
     if (n <= 0) return 0;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    BS_SWITCH(bs, B200_LAUNCH(bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
+    BS_SWITCH(bs, B200_LAUNCH_PDL(bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
     return check_launch("bsr_jacobi_kernel");
 }
 
@@ -478,7 +484,7 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
-#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH((bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
+#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
         // batches pay while the colour is a fraction of a wave (config 4, run 15: level 2, 48 rows per colour, 0.76 -> 0.56 ms
         // per step; level 1, 6 600 rows per colour, 0.65 -> 0.79 ms: the 128 registers cost resident warps there)
         if (bsr_warp_batch() && p1 - p0 <= kSMs * 8) {
@@ -493,8 +499,8 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     }
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
-    if (perm) { BS_SWITCH(bs, B200_LAUNCH((bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
-    else { BS_SWITCH(bs, B200_LAUNCH((bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    if (perm) { BS_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    else { BS_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
     return check_launch("bsr_gs_color_kernel");
 }
 
@@ -502,7 +508,7 @@ int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, do
                       const int *Id, int start, int stop, int step, cudaStream_t st)
 {
     if (start == stop) return 0;
-    BS_SWITCH(bs, B200_LAUNCH(bsr_gs_sequential_kernel<BS>, 1, 1, 0, st, Ap, Aj, Ax, x, b, Id, start, stop, step));
+    BS_SWITCH(bs, B200_LAUNCH_PDL(bsr_gs_sequential_kernel<BS>, 1, 1, 0, st, Ap, Aj, Ax, x, b, Id, start, stop, step));
     return check_launch("bsr_gs_sequential_kernel");
 }
 

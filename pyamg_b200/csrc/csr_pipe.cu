@@ -89,14 +89,16 @@ __global__ void __launch_bounds__(P_TPB, P_CTAS_PER_SM) csr_pipe_kernel(const St
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
     const int t = threadIdx.x;
+    pdl_trigger();
     if (t == 0) {
         for (int i = 0; i < NP; ++i) { mbar_init(&S.ptr_full[i], 2); mbar_init(&S.ptr_empty[i], P_CWARPS); }
         for (int i = 0; i < ND; ++i) { mbar_init(&S.data_full[i], 2); mbar_init(&S.data_empty[i], P_CWARPS); }
         mbar_fence_init();
     }
-    if (MODE == 1 && t < 256) S.dict[t] = a.dict[t];
+    if (MODE == 1 && t < 256) S.dict[t] = a.dict[t];           // (engine-owned tables: complete before any launch)
     if (MODE == 2 && t < 256) S.pat[t] = PatEntry{a.dict[t], a.offs[t], 0};
     __syncthreads();
+    pdl_wait();                 // set-up overlaps the previous kernel of the stream; the operator and the vectors wait for it
 
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int *__restrict__ Ap = a.Ap;
@@ -328,7 +330,7 @@ static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
     const int nrows = a.row_end - a.row_begin;
     const int num_tiles = (nrows + rpt - 1) / rpt;
     const int grid = min(num_tiles, g_sms * P_CTAS_PER_SM);
-    csr_pipe_kernel<OP, MODE><<<grid, P_TPB, sizeof(Smem), st>>>(a, rpt, num_tiles);
+    B200_LAUNCH_PDL((csr_pipe_kernel<OP, MODE>), grid, P_TPB, sizeof(Smem), st, a, rpt, num_tiles);
     return check_launch("csr_pipe_kernel");
 }
 

@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(TPB) csr_stream_kernel(const StreamArgs a, con
     __shared__ __align__(16) int s_c[CHUNK];
 
     const int t = threadIdx.x;
+    pdl_enter();
     const int rpb = rows_per_cta;
     const int r0 = a.row_begin + blockIdx.x * rpb;
     const int nr = min(rpb, a.row_end - r0);
@@ -173,9 +174,9 @@ static int launch_stream(const StreamArgs &a0, cudaStream_t st)
     const int rpb = rows_per_cta_for(a.nnz, nrows);
     const int grid = (nrows + rpb - 1) / rpb;
     if (aligned16(a.Aj) && aligned16(a.Ax))
-        csr_stream_kernel<OP, true><<<grid, TPB, 0, st>>>(a, rpb);
+        B200_LAUNCH_PDL((csr_stream_kernel<OP, true>), grid, TPB, 0, st, a, rpb);
     else
-        csr_stream_kernel<OP, false><<<grid, TPB, 0, st>>>(a, rpb);
+        B200_LAUNCH_PDL((csr_stream_kernel<OP, false>), grid, TPB, 0, st, a, rpb);
     return check_launch("csr_stream_kernel");
 }
 
@@ -206,6 +207,7 @@ __global__ void __launch_bounds__(128) gs_rows_kernel(const int *__restrict__ Ap
                                                       const double *__restrict__ b,
                                                       const int *__restrict__ Id, int p0, int p1)
 {
+    pdl_enter();
     const int p = p0 + blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= p1) return;
     const int i = Id[p];
@@ -291,8 +293,8 @@ int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x
 {
     if (p1 <= p0) return 0;
     const int grid = (p1 - p0 + 127) / 128;
-    if (bsrf) gs_rows_kernel<true><<<grid, 128, 0, st>>>(Ap, Aj, Ax, x, b, Id, p0, p1);
-    else gs_rows_kernel<false><<<grid, 128, 0, st>>>(Ap, Aj, Ax, x, b, Id, p0, p1);
+    if (bsrf) B200_LAUNCH_PDL(gs_rows_kernel<true>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
+    else B200_LAUNCH_PDL(gs_rows_kernel<false>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
     return check_launch("gs_rows_kernel");
 }
 

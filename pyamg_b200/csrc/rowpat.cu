@@ -386,13 +386,15 @@ __global__ void __launch_bounds__(RP_TPB, RP_CTAS_PER_SM) rowpat_kernel(const Ro
     int *s_off = reinterpret_cast<int *>(rp_smem);
     double *s_val = reinterpret_cast<double *>(rp_smem + (size_t)a.npat * RP_LEN * sizeof(int));
     int *s_meta = reinterpret_cast<int *>(rp_smem + (size_t)a.npat * RP_LEN * (sizeof(int) + sizeof(double)));
-    for (int i = threadIdx.x; i < a.npat * RP_LEN; i += RP_TPB) {
+    pdl_trigger();
+    for (int i = threadIdx.x; i < a.npat * RP_LEN; i += RP_TPB) {     // (engine-owned table: complete before any launch)
         const RowPatEntry en = a.table[i];
         s_off[i] = en.off;
         s_val[i] = en.v;
         if ((i & (RP_LEN - 1)) == 0) s_meta[i / RP_LEN] = en.len;
     }
     __syncthreads();
+    pdl_wait();
     const double *__restrict__ xg = a.x;
     const int n_chunks = (a.n + RP_CHUNK - 1) / RP_CHUNK;
     // A CTA's steps: step k covers rows [r0, r0 + 256) of chunk blockIdx.x + (k / SPC) * gridDim.x.
@@ -501,7 +503,7 @@ static int launch_rowpat(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     const int n_chunks = (r.n + RP_CHUNK - 1) / RP_CHUNK;
     const int grid = std::min(n_chunks, sms * RP_CTAS_PER_SM);
     RowPatArgs a{r.n, r.npat, r.far, r.codes, r.table, s.x, s.b, s.y, s.alpha, s.beta, s.omega};
-    rowpat_kernel<OP><<<grid, RP_TPB, ((sizeof(int) + sizeof(double)) * RP_LEN + sizeof(int)) * r.npat + 16, st>>>(a);
+    B200_LAUNCH_PDL(rowpat_kernel<OP>, grid, RP_TPB, ((sizeof(int) + sizeof(double)) * RP_LEN + sizeof(int)) * r.npat + 16, st, a);
     return check_launch("rowpat_kernel");
 }
 

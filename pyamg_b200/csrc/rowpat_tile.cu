@@ -110,12 +110,14 @@ __global__ void __launch_bounds__(TT_TPB, TT_RESIDENT) rowpat_tile_kernel(const 
     uint64_t *full = reinterpret_cast<uint64_t *>(tt_smem + (size_t)TT_ST * stage_bytes + 512);
     uint64_t *empty = full + TT_ST;
     const int t = threadIdx.x;
+    pdl_trigger();
     if (t == 0) {
         for (int s = 0; s < TT_ST; ++s) { mbar_init(&full[s], 2); mbar_init(&empty[s], TT_CONS / 32); }
         mbar_fence_init();
     }
     for (int i = t; i < 256; i += TT_TPB) s_mask[i] = a.mask[i];
     __syncthreads();
+    pdl_wait();                 // barriers and masks are set up while the previous kernel drains; x and b wait for it
     const int n_chunks = (a.n + TT_CH - 1) / TT_CH;
     const int my_chunks = (n_chunks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -329,7 +331,7 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     a.omega = s.omega;
     const int n_chunks = (r.n + TT_CH - 1) / TT_CH;
     const int grid = std::min(n_chunks, sms * TT_RESIDENT);
-    rowpat_tile_kernel<OP, LEN><<<grid, TT_TPB, smem, st>>>(a);
+    B200_LAUNCH_PDL((rowpat_tile_kernel<OP, LEN>), grid, TT_TPB, smem, st, a);
     return check_launch("rowpat_tile_kernel");
 }
 

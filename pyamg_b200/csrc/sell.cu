@@ -159,6 +159,9 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
             sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc, s.cd,
                                                               s.first);
             rc = check_launch("sell_fill_kernel");
+            // the apply kernels request slots of this copy BEFORE they wait for their predecessor in the stream
+            // (programmatic dependent launch): the copy must be complete when the build returns
+            if (!rc) e = cudaStreamSynchronize(st);
         }
     }
     if (width) cudaFree(width);
@@ -196,6 +199,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     const V *__restrict__ cv = reinterpret_cast<const V *>(cvals);
     const J *__restrict__ cj = reinterpret_cast<const J *>(cols);
     __shared__ double s_dict[CODED ? 256 : 1];
+    pdl_trigger();
     if (CODED) {
         s_dict[threadIdx.x] = dict[threadIdx.x];               // coded launches use SELL_TPB == 256 threads
         __syncthreads();
@@ -216,14 +220,16 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     const int len = live ? row_len[row] : 0;
     const double *__restrict__ xg = a.x;
     double bi = 0.0, xi = 0.0, yi = 0.0;
-    int run = 0;                                               // STEPS: column of the last slot walked
-    if (live) {
-        if (NEED_B) bi = __ldg(a.b + row);
-        if (SMOOTH) xi = __ldg(xg + row);
-        if (OP == OP_ADD) yi = a.b[row];
-        if (STEPS) run = __ldg(first + row);
-    }
-    double acc = BSRF ? bi : 0.0, diag = 0.0;
+    int run = (STEPS && live) ? __ldg(first + row) : 0;        // STEPS: column of the last slot walked
+    // x, b, y may be what the previous kernel of the stream wrote: nothing of them is read before pdl_wait()
+    auto load_vectors = [&] {
+        if (live) {
+            if (NEED_B) bi = __ldg(a.b + row);
+            if (SMOOTH) xi = __ldg(xg + row);
+            if (OP == OP_ADD) yi = a.b[row];
+        }
+    };
+    double acc = 0.0, diag = 0.0;
     const J *pj = cj + off + lane;
     const V *pv = cv + off + lane;
     if constexpr (PIPE) {
@@ -237,6 +243,9 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
         c[u] = in ? (int)__ldcs(pj + (long long)u * SELL_C) : -1;
         v[u] = in ? value(__ldcs(pv + (long long)u * SELL_C)) : 0.0;
     }
+    pdl_wait();                                                 // the first round of slots is already on its way
+    load_vectors();
+    acc = BSRF ? bi : 0.0;
     for (int k0 = 0; k0 < w; k0 += U) {
 #pragma unroll
         for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
@@ -272,6 +281,9 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
         }
     }
     } else {
+    pdl_wait();
+    load_vectors();
+    acc = BSRF ? bi : 0.0;
     for (int k0 = 0; k0 < w; k0 += U) {
         int c[U];
         J raw[U];
@@ -346,7 +358,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     // form for small colours (U == 32) is launched that way; it reads x around L1 (ld.cg): blocks of two kernels can
     // share an SM now, and a line of x the earlier kernel pulled into L1 must not serve the later one.
     constexpr bool PDL = (U == 32);
-    if (PDL) cudaTriggerProgrammaticLaunchCompletion();
+    if (PDL) pdl_trigger();
     const int r = (p0 & ~31) + blockIdx.x * blockDim.x + threadIdx.x;       // slot row (slices may straddle colours)
     const int slice = r >> 5, lane = threadIdx.x & 31;
     if ((slice << 5) >= p1) return;                                         // whole warp
@@ -381,7 +393,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
             tie &= zero;
         }
         if (k0 == 0) {
-            if (PDL) cudaGridDependencySynchronize();                       // x and b are final from here on
+            if (PDL) pdl_wait();                                            // x and b are final from here on
             bi = live ? (PDL ? __ldcg(b + row) : b[row]) : 0.0;
             acc = BSRF ? bi : 0.0;
         }
@@ -407,7 +419,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
         }
     }
     if (w == 0) {                                                           // a slice of empty rows
-        if (PDL) cudaGridDependencySynchronize();
+        if (PDL) pdl_wait();
         bi = live ? b[row] : 0.0;
     }
     if (live && diag != 0.0) x[row] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(bi, acc), diag);
@@ -470,9 +482,9 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
     if (s.cc) {
-        sell_kernel<OP, SELL_U, false, 1><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
     } else if (s.cd) {
-        sell_kernel<OP, SELL_U, false, 2><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
+        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
     } else if (s.n < SELL_BIG_ROWS) {
         // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: 16 slots per round,
         // all forced in flight, and 64-thread blocks so that the few warps spread over all SMs.  Measured on config 2
@@ -481,11 +493,11 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
         // smoothing ops already kept their loads together (the diagonal test splits the basic block) and are fastest
         // as they were (0.021 vs 0.028 ms).
         if (OP < OP_JACOBI && sell_small_deep())
-            sell_kernel<OP, 16, true, 0, true><<<(s.n + 63) / 64, 64, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL((sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
         else
-            sell_kernel<OP, SELL_U, true, 0><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     } else {
-        sell_kernel<OP, SELL_U, false, 0><<<grid, SELL_TPB, 0, st>>>(s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     }
     return check_launch("sell_kernel");
 }
