@@ -457,11 +457,11 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     // (measured on BASELINE config 4, profiles/r02: 1 331 x 6 rows 0.54 -> 0.13 ms; 2.08 M x 3 rows 0.53 -> 2.3 ms)
     if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && n < kSMs * 1024 && nblocks >= 2ll * (32 / R) * n_brow) {
         const unsigned grid = (unsigned)((n_brow + 3) / 4);
-        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH_PDL((bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
-        else { R_SWITCH(R, B200_LAUNCH_PDL((bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH_PDL(true, (bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        else { R_SWITCH(R, B200_LAUNCH_PDL(true, (bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
         return check_launch("bsr_matvec_warp_kernel");
     }
-    B200_LAUNCH_PDL(bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
+    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
     return check_launch("bsr_matvec_kernel");
 }
 
@@ -471,7 +471,7 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
     const long long n = (long long)(nb1 - nb0) * bs;
     if (n <= 0) return 0;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    BS_SWITCH(bs, B200_LAUNCH_PDL(bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
+    BS_SWITCH(bs, B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
     return check_launch("bsr_jacobi_kernel");
 }
 
@@ -484,7 +484,7 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
-#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
+#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH_PDL(true, (bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
         // batches pay while the colour is a fraction of a wave (config 4, run 15: level 2, 48 rows per colour, 0.76 -> 0.56 ms
         // per step; level 1, 6 600 rows per colour, 0.65 -> 0.79 ms: the 128 registers cost resident warps there)
         if (bsr_warp_batch() && p1 - p0 <= kSMs * 8) {
@@ -499,8 +499,8 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     }
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
-    if (perm) { BS_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
-    else { BS_SWITCH(bs, B200_LAUNCH_PDL((bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    if (perm) { BS_SWITCH(bs, B200_LAUNCH_PDL((long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    else { BS_SWITCH(bs, B200_LAUNCH_PDL((long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
     return check_launch("bsr_gs_color_kernel");
 }
 
@@ -508,7 +508,7 @@ int bsr_gs_sequential(int bs, const int *Ap, const int *Aj, const double *Ax, do
                       const int *Id, int start, int stop, int step, cudaStream_t st)
 {
     if (start == stop) return 0;
-    BS_SWITCH(bs, B200_LAUNCH_PDL(bsr_gs_sequential_kernel<BS>, 1, 1, 0, st, Ap, Aj, Ax, x, b, Id, start, stop, step));
+    BS_SWITCH(bs, B200_LAUNCH_PDL(false, bsr_gs_sequential_kernel<BS>, 1, 1, 0, st, Ap, Aj, Ax, x, b, Id, start, stop, step));
     return check_launch("bsr_gs_sequential_kernel");
 }
 

@@ -50,29 +50,43 @@ __device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(
 __device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
 
 // ---- programmatic dependent launch (PDL) -----------------------------------------------------------------------
-// A cycle is a chain of 30-400 dependent kernels; between two of them the GPU otherwise idles for the launch
-// (2-3 us) plus the first dependent loads of the next kernel.  A kernel launched through launch_pdl() may be
-// scheduled while its predecessor in the stream still runs; it calls pdl_enter() BEFORE its first access to anything
-// an earlier kernel of the stream may have written (griddepcontrol.wait: returns when the predecessor has finished
-// and its writes are visible) -- whatever it does before that (barrier setup, loads of operator data that no kernel
-// of the cycle writes) overlaps the predecessor.  pdl_enter() also lets the NEXT kernel be scheduled early
-// (griddepcontrol.launch_dependents).  Launched the ordinary way both instructions do nothing.  B200AMG_PDL=0 turns
-// the launch attribute off (A/B switch).  Works under stream capture (programmatic graph edges).
+// A cycle is a chain of 30-400 dependent kernels; on the coarse levels a kernel is a few microseconds of work behind
+// 2-3 us of launch latency and a chain of dependent first loads.  A kernel launched through launch_pdl(early = true)
+// may be scheduled while its predecessor in the stream still runs; it calls pdl_wait() BEFORE its first access to
+// anything an earlier kernel of the stream may have written (griddepcontrol.wait: returns when the predecessor has
+// finished and flushed its writes) -- whatever it does before that (barrier set-up, loads from engine-owned operator
+// copies, which are complete before any launch) overlaps the predecessor.  pdl_trigger() at the top of a kernel lets
+// ITS successor be scheduled (griddepcontrol.launch_dependents).  Launched the ordinary way both do nothing.
+//
+// One thing an early start takes away: a kernel normally begins with an L1 that holds nothing of its predecessor's
+// era; blocks of two kernels sharing an SM means lines the predecessor pulled in (x, say, before another SM updated
+// it) are still there after the wait -- measured: wrong iterates from the first cycle on a 1 728-row problem.  So the
+// wait is followed by a gpu-scope fence, which the compiler turns into MEMBAR + CCTL.IVALL (L1 invalidate).  Only
+// small grids are launched early (that is where launch latency matters) and only small grids pay the fence:
+// both sides use the same bound on gridDim.x.  B200AMG_PDL=0 turns the attribute off (A/B switch); =2 also launches
+// the big persistent kernels early.  Works under stream capture (programmatic graph edges).
+constexpr unsigned PDL_MAX_GRID = 2048;
+constexpr long long PDL_SMALL_ROWS = 400000;      // launches over fewer rows are taken to be latency-bound
 #ifdef B200_HOST_EMULATION
 inline void pdl_enter() {}
 inline void pdl_trigger() {}
 inline void pdl_wait() {}
 #else
 __device__ __forceinline__ void pdl_trigger() { cudaTriggerProgrammaticLaunchCompletion(); }
-__device__ __forceinline__ void pdl_wait() { cudaGridDependencySynchronize(); }
-__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
-inline bool pdl_enabled()
+__device__ __forceinline__ void pdl_wait()
 {
-    static const bool on = [] { const char *e = getenv("B200AMG_PDL"); return !(e && e[0] == '0'); }();
-    return on;
+    cudaGridDependencySynchronize();
+    if (gridDim.x <= PDL_MAX_GRID) asm volatile("fence.acq_rel.gpu;" ::: "memory");
 }
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+inline int pdl_level()
+{
+    static const int lv = [] { const char *e = getenv("B200AMG_PDL"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }();
+    return lv;
+}
+// early: the caller's judgement that the launch is latency-bound (few rows); level 2 ignores it
 template <class... P, class... A>
-inline cudaError_t launch_pdl(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A &&...args)
+inline cudaError_t launch_pdl(bool early, void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A &&...args)
 {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -83,7 +97,8 @@ inline cudaError_t launch_pdl(void (*kernel)(P...), dim3 grid, dim3 block, size_
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    const int lv = pdl_level();
+    cfg.numAttrs = (grid.x <= PDL_MAX_GRID && grid.y == 1 && grid.z == 1 && (lv == 2 || (lv == 1 && early))) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<A &&>(args)...);
 }
 #endif
@@ -94,8 +109,8 @@ inline cudaError_t launch_pdl(void (*kernel)(P...), dim3 grid, dim3 block, size_
 #endif
 // ... and the same for kernels that call pdl_enter() / pdl_wait() (see above)
 #ifndef B200_LAUNCH_PDL
-#define B200_LAUNCH_PDL(kernel, grid, block, smem, stream, ...) \
-    (void)b200amg::launch_pdl(kernel, dim3(grid), dim3(block), (size_t)(smem), (stream), __VA_ARGS__)
+#define B200_LAUNCH_PDL(early, kernel, grid, block, smem, stream, ...) \
+    (void)b200amg::launch_pdl((early), kernel, dim3(grid), dim3(block), (size_t)(smem), (stream), __VA_ARGS__)
 #endif
 
 constexpr int kSMs = 148;  // B200

@@ -350,15 +350,11 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     constexpr bool TIE = U > 8;
     using J = typename std::conditional<STEPS, unsigned short, int>::type;
     const J *__restrict__ cj = reinterpret_cast<const J *>(cols);
-    // Programmatic dependent launch: the NEXT colour's kernel may start as soon as every block of this one has, and
-    // everything up to cudaGridDependencySynchronize() below -- which waits for the previous kernel to finish and its
-    // writes to be visible -- reads only what no kernel of the cycle writes (the operator, the index list).  A colour of
-    // a coarse level is launch latency plus a chain of dependent loads; this takes the launch and the operator part
-    // of the chain off the critical path.  Launched without the attribute both calls do nothing.  Only the one-round
-    // form for small colours (U == 32) is launched that way; it reads x around L1 (ld.cg): blocks of two kernels can
-    // share an SM now, and a line of x the earlier kernel pulled into L1 must not serve the later one.
-    constexpr bool PDL = (U == 32);
-    if (PDL) pdl_trigger();
+    // Programmatic dependent launch (common.cuh): the NEXT colour's kernel may start as soon as every block of this one
+    // has, and everything up to pdl_wait() below reads only what no kernel of the cycle writes (the colour-grouped copy
+    // of the operator, the index list).  A colour of a coarse level is launch latency plus a chain of dependent loads;
+    // this takes the launch and the operator part of the chain off the critical path.
+    pdl_trigger();
     const int r = (p0 & ~31) + blockIdx.x * blockDim.x + threadIdx.x;       // slot row (slices may straddle colours)
     const int slice = r >> 5, lane = threadIdx.x & 31;
     if ((slice << 5) >= p1) return;                                         // whole warp
@@ -393,15 +389,12 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
             tie &= zero;
         }
         if (k0 == 0) {
-            if (PDL) pdl_wait();                                            // x and b are final from here on
-            bi = live ? (PDL ? __ldcg(b + row) : b[row]) : 0.0;
+            pdl_wait();                                                     // x and b are final from here on
+            bi = live ? b[row] : 0.0;
             acc = BSRF ? bi : 0.0;
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const double *px = x + c[u] + (u == 0 ? tie : 0);
-            xv[u] = (c[u] >= 0) ? (PDL ? __ldcg(px) : *px) : 0.0;
-        }
+        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? x[c[u] + (u == 0 ? tie : 0)] : 0.0;
         if (TIE) {
 #pragma unroll
             for (int u = 0; u < U; ++u) tie |= __double2loint(xv[u]);
@@ -419,7 +412,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
         }
     }
     if (w == 0) {                                                           // a slice of empty rows
-        if (PDL) pdl_wait();
+        pdl_wait();
         bi = live ? b[row] : 0.0;
     }
     if (live && diag != 0.0) x[row] = BSRF ? div_rn(acc, diag) : div_rn(sub_rn(bi, acc), diag);
@@ -434,32 +427,20 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
     // config 3 (run 15): colours below 64 k rows 3-7 % faster with one 32-slot round; 121 k rows: 16 slots SLOWER than 8
     const int U = forced ? forced : (rows < 64 * 1024 ? 32 : 8);
     const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
-    // B200AMG_PDL=0: plain stream order (A/B switch)
-    static const bool pdl = [] { const char *e = getenv("B200AMG_PDL"); return !(e && e[0] == '0'); }();
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cudaLaunchConfig_t cfg = {};
-    cfg.stream = st;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
     const int *firstp = s.cd ? s.first : nullptr;
-#define SELL_GS_LAUNCH(UU, TPB)                                                                                                   \
+#define SELL_GS_LAUNCH(EARLY, UU, TPB)                                                                                            \
     do {                                                                                                                          \
-        cfg.gridDim = dim3((unsigned)((rows + TPB - 1) / TPB));                                                                   \
-        cfg.blockDim = dim3(TPB);                                                                                                 \
-        cudaError_t e = s.cd ? cudaLaunchKernelEx(&cfg, sell_gs_kernel<BSRF, UU, true>, p0, p1, (const long long *)s.slice_off,   \
-                                                  cols, (const double *)s.cv, firstp, (const int *)s.row_len, Id, x, b, 0)       \
-                             : cudaLaunchKernelEx(&cfg, sell_gs_kernel<BSRF, UU, false>, p0, p1, (const long long *)s.slice_off,  \
-                                                  cols, (const double *)s.cv, firstp, (const int *)s.row_len, Id, x, b, 0);      \
+        const dim3 g((unsigned)((rows + TPB - 1) / TPB)), blk(TPB);                                                               \
+        cudaError_t e = s.cd ? launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, true>, g, blk, 0, st, p0, p1,                           \
+                                          (const long long *)s.slice_off, cols, (const double *)s.cv, firstp,                    \
+                                          (const int *)s.row_len, Id, x, b, 0)                                                    \
+                             : launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, false>, g, blk, 0, st, p0, p1,                          \
+                                          (const long long *)s.slice_off, cols, (const double *)s.cv, firstp,                    \
+                                          (const int *)s.row_len, Id, x, b, 0);                                                   \
         if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                            \
     } while (0)
-    if (U == 32) {
-        SELL_GS_LAUNCH(32, 64);
-    } else {
-        cfg.numAttrs = 0;
-        SELL_GS_LAUNCH(8, SELL_TPB);
-    }
+    if (U == 32) SELL_GS_LAUNCH(true, 32, 64);
+    else SELL_GS_LAUNCH(false, 8, SELL_TPB);
 #undef SELL_GS_LAUNCH
     return check_launch("sell_gs_kernel");
 }
@@ -482,9 +463,9 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
     if (s.cc) {
-        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
     } else if (s.cd) {
-        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
+        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
     } else if (s.n < SELL_BIG_ROWS) {
         // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: 16 slots per round,
         // all forced in flight, and 64-thread blocks so that the few warps spread over all SMs.  Measured on config 2
@@ -493,11 +474,11 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
         // smoothing ops already kept their loads together (the diagonal test splits the basic block) and are fastest
         // as they were (0.021 vs 0.028 ms).
         if (OP < OP_JACOBI && sell_small_deep())
-            B200_LAUNCH_PDL((sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(true, (sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
         else
-            B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(true, (sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     } else {
-        B200_LAUNCH_PDL((sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     }
     return check_launch("sell_kernel");
 }

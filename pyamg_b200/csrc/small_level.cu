@@ -241,17 +241,17 @@ int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *A
     if (bs == 1) {
         if (bsrf) {
             SL_OPT_IN(gs_level_cta_kernel<true>);
-            B200_LAUNCH_PDL(gs_level_cta_kernel<true>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
+            B200_LAUNCH_PDL(true, gs_level_cta_kernel<true>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
         } else {
             SL_OPT_IN(gs_level_cta_kernel<false>);
-            B200_LAUNCH_PDL(gs_level_cta_kernel<false>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
+            B200_LAUNCH_PDL(true, gs_level_cta_kernel<false>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
         }
         return check_launch("gs_level_cta_kernel");
     }
 #define SL_BSR(BSV)                                                                                                          \
     case BSV: {                                                                                                              \
         SL_OPT_IN(bsr_gs_level_cta_kernel<BSV>);                                                                             \
-        B200_LAUNCH_PDL(bsr_gs_level_cta_kernel<BSV>, 1, SL_TPB, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi); \
+        B200_LAUNCH_PDL(true, bsr_gs_level_cta_kernel<BSV>, 1, SL_TPB, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi); \
     } break;
     switch (bs) {
         SL_BSR(2) SL_BSR(3) SL_BSR(4) SL_BSR(5) SL_BSR(6) SL_BSR(7) SL_BSR(8)

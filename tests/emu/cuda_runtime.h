@@ -146,5 +146,5 @@ inline int __double2loint(double d) { unsigned long long r; memcpy(&r, &d, 8); r
 
 #define B200_LAUNCH(kernel, grid, block, smem, stream, ...) \
     cuda_emu::launch(dim3(grid), dim3(block), [&] { kernel(__VA_ARGS__); })
-#define B200_LAUNCH_PDL(kernel, grid, block, smem, stream, ...) \
+#define B200_LAUNCH_PDL(early, kernel, grid, block, smem, stream, ...) \
     cuda_emu::launch(dim3(grid), dim3(block), [&] { kernel(__VA_ARGS__); })
