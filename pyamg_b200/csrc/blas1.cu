@@ -60,9 +60,9 @@ int dot(long long n, const double *x, const double *y, double *out, double *work
     if (n < 0) return set_err(B200AMG_EINVAL, "dot: n < 0");
     long long want = (n / 2 + DOT_TPB - 1) / DOT_TPB;
     int grid = (int)(want < 1 ? 1 : (want > DOT_MAX_GRID ? DOT_MAX_GRID : want));
-    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, dot_partial_kernel, grid, DOT_TPB, 0, st, n, x, y, work);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, dot_partial_kernel, grid, DOT_TPB, 0, st, n, x, y, work);
     B200_TRY(check_launch("dot_partial_kernel"));
-    B200_LAUNCH_PDL(true, dot_final_kernel, 1, DOT_TPB, 0, st, grid, work, out);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER), dot_final_kernel, 1, DOT_TPB, 0, st, grid, work, out);
     return check_launch("dot_final_kernel");
 }
 
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) pcg_update_p_kernel(long long n, const do
 
 int pcg_scalars(double *st, int which, cudaStream_t s)
 {
-    B200_LAUNCH_PDL(true, pcg_scalars_kernel, 1, 1, 0, s, st, which);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER), pcg_scalars_kernel, 1, 1, 0, s, st, which);
     return check_launch("pcg_scalars_kernel");
 }
 
@@ -169,14 +169,14 @@ int pcg_update_xr(long long n, const double *st, const double *p, const double *
                   cudaStream_t s)
 {
     if (n <= 0) return 0;
-    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, pcg_update_xr_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, p, Ap, x, r, update_r);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, pcg_update_xr_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, p, Ap, x, r, update_r);
     return check_launch("pcg_update_xr_kernel");
 }
 
 int pcg_update_p(long long n, const double *st, const double *z, double *p, cudaStream_t s)
 {
     if (n <= 0) return 0;
-    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, pcg_update_p_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, z, p);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, pcg_update_p_kernel, (unsigned)((n + 255) / 256), 256, 0, s, n, st, z, p);
     return check_launch("pcg_update_p_kernel");
 }
 
@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(256) scale_diag_kernel(long long n, double ome
 int scale_diag(long long n, double omega, const double *b, const double *d, double *x, int bsrf, cudaStream_t st)
 {
     if (n <= 0) return 0;
-    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, scale_diag_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n, omega, b, d, x, bsrf);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, scale_diag_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n, omega, b, d, x, bsrf);
     return check_launch("scale_diag_kernel");
 }
 
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(256) dense_matvec_kernel(int n, const double *
 int dense_matvec(int n, const double *M, const double *x, double *y, cudaStream_t st)
 {
     if (n <= 0) return 0;
-    B200_LAUNCH_PDL(true, dense_matvec_kernel, (n + 7) / 8, 256, 0, st, n, M, x, y);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER), dense_matvec_kernel, (n + 7) / 8, 256, 0, st, n, M, x, y);
     return check_launch("dense_matvec_kernel");
 }
 

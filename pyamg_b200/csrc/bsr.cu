@@ -218,17 +218,20 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
                                                                 const double *__restrict__ b, const int *__restrict__ Id,
                                                                 int p0, int p1, int zero)
 {
-    pdl_enter();
+    // the operator (index list, row bounds, block columns, blocks) is read BEFORE the dependency wait: the engine passes
+    // hierarchy arrays that no kernel of the cycle writes, and launches early only then (bsr_gs_color: static_op)
+    pdl_trigger();
     constexpr int G = 32 / BS;                          // blocks per pass
     constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int p = p0 + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (p >= p1) return;                                // the whole warp leaves together
+    if (p >= p1) { pdl_wait(); return; }                // the whole warp leaves together
     const int i = Id[p];
     const int g = lane / BS, k = lane - g * BS;
     const bool lane_ok = g < G;
     const int lo = Ap[PERM ? p : i], hi = Ap[(PERM ? p : i) + 1];
-    double acc = (lane < BS) ? b[(size_t)i * BS + lane] : 0.0;
+    double acc = 0.0;
+    bool waited = false;
     int dptr = -1;
     for (int q0 = lo; q0 < hi; q0 += G * NB) {
         int j[NB];
@@ -249,12 +252,20 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
             const int q = q0 + t * G + g;
             const bool use = j[t] >= 0 && j[t] != i;
             const double *blk = Ax + ((size_t)q * BS + k) * BS + (t == 0 ? tie : 0);
+#pragma unroll
+            for (int c = 0; c < BS; ++c) bl[t][c] = use ? blk[c] : 0.0;
+        }
+        if (!waited) {                                  // warp-uniform: x and b are final from here on
+            pdl_wait();
+            acc = (lane < BS) ? b[(size_t)i * BS + lane] : 0.0;
+            waited = true;
+        }
+#pragma unroll
+        for (int t = 0; t < NB; ++t) {
+            const bool use = j[t] >= 0 && j[t] != i;
             const double *xb = x + (size_t)(use ? j[t] : 0) * BS;
 #pragma unroll
-            for (int c = 0; c < BS; ++c) {
-                bl[t][c] = use ? blk[c] : 0.0;
-                xv[t][c] = use ? xb[c] : 0.0;
-            }
+            for (int c = 0; c < BS; ++c) xv[t][c] = use ? xb[c] : 0.0;
         }
         if (NB > 1) {
 #pragma unroll
@@ -279,6 +290,7 @@ __global__ void __launch_bounds__(128) bsr_gs_color_warp_kernel(const int *__res
             for (int gg = 0; gg < G; ++gg) acc = sub_rn(acc, __shfl_sync(FULL, loc, gg * BS + (lane < BS ? lane : 0)));
         }
     }
+    if (!waited) pdl_wait();                            // a row without blocks
     if (dptr < 0) return;
     // point sweep inside the diagonal block (relaxation.h:150-163): lane k < BS owns row k of D
     double xl[BS], Dk[BS];
@@ -457,11 +469,11 @@ int bsr_matvec(int n_brow, int R, int C, const int *Ap, const int *Aj, const dou
     // (measured on BASELINE config 4, profiles/r02: 1 331 x 6 rows 0.54 -> 0.13 ms; 2.08 M x 3 rows 0.53 -> 2.3 ms)
     if (R >= 2 && nblocks >= 0 && bsr_warp_kernels() && n < kSMs * 1024 && nblocks >= 2ll * (32 / R) * n_brow) {
         const unsigned grid = (unsigned)((n_brow + 3) / 4);
-        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH_PDL(true, (bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
-        else { R_SWITCH(R, B200_LAUNCH_PDL(true, (bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        if (bsr_warp_batch()) { R_SWITCH(R, B200_LAUNCH_PDL(pdl_class(PDL_OTHER), (bsr_matvec_warp_kernel<RR, 4>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
+        else { R_SWITCH(R, B200_LAUNCH_PDL(pdl_class(PDL_OTHER), (bsr_matvec_warp_kernel<RR, 1>), grid, 128, 0, st, n_brow, C, Ap, Aj, Ax, x, b, y, mode, 0)); }
         return check_launch("bsr_matvec_warp_kernel");
     }
-    B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, bsr_matvec_kernel, (unsigned)((n + 255) / 256), 256, 0, st, n_brow, R, C, Ap, Aj, Ax, x, b, y, mode);
     return check_launch("bsr_matvec_kernel");
 }
 
@@ -471,20 +483,20 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
     const long long n = (long long)(nb1 - nb0) * bs;
     if (n <= 0) return 0;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    BS_SWITCH(bs, B200_LAUNCH_PDL(n < PDL_SMALL_ROWS, bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
+    BS_SWITCH(bs, B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && n < PDL_SMALL_ROWS, bsr_jacobi_kernel<BS>, grid, 256, 0, st, nb0, nb1, Ap, Aj, Ax, xin, xout, b, omega));
     return check_launch("bsr_jacobi_kernel");
 }
 
 // perm != 0: (Ap, Aj, Ax) is a colour-grouped copy of the operator -- its row p is block row Id[p] (bsr_color_build)
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
-                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row, bool perm)
+                 const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row, bool perm, bool static_op)
 {
     if (p1 <= p0) return 0;
     // warp per block row where the colour is too small for lanes-per-row to fill the machine and the rows are long
     // (config 4: level 1, 6 600 rows of 44 blocks per colour, 43 -> 27 us per launch; level 0, 260 k rows of 15: slower)
     if (bs >= 2 && bsr_warp_kernels() && (long long)(p1 - p0) * bs < kSMs * 1024 && blocks_per_row >= 2.0 * (32 / bs)) {
         const unsigned grid = (unsigned)((p1 - p0 + 3) / 4);       // 4 warps = 4 block rows per CTA
-#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH_PDL(true, (bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
+#define GS_WARP(BW, PM, NBV) R_SWITCH(bs, B200_LAUNCH_PDL(pdl_class(PDL_SWEEP) && static_op, (bsr_gs_color_warp_kernel<RR, BW, PM, (NBV > 1 && RR <= 3) ? 2 * NBV : NBV>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, 0))
         // batches pay while the colour is a fraction of a wave (config 4, run 15: level 2, 48 rows per colour, 0.76 -> 0.56 ms
         // per step; level 1, 6 600 rows per colour, 0.65 -> 0.79 ms: the 128 registers cost resident warps there)
         if (bsr_warp_batch() && p1 - p0 <= kSMs * 8) {
@@ -499,8 +511,8 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
     }
     const int rows_per_cta = (32 / bs) * 4;             // 4 warps, 32 / bs block rows each
     const unsigned grid = (unsigned)((p1 - p0 + rows_per_cta - 1) / rows_per_cta);
-    if (perm) { BS_SWITCH(bs, B200_LAUNCH_PDL((long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
-    else { BS_SWITCH(bs, B200_LAUNCH_PDL((long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    if (perm) { BS_SWITCH(bs, B200_LAUNCH_PDL(pdl_class(PDL_SWEEP) && (long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, true>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
+    else { BS_SWITCH(bs, B200_LAUNCH_PDL(pdl_class(PDL_SWEEP) && (long long)(p1 - p0) * bs < PDL_SMALL_ROWS, (bsr_gs_color_kernel<BS, false>), grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1, backward)); }
     return check_launch("bsr_gs_color_kernel");
 }
 

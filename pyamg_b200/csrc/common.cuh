@@ -76,13 +76,27 @@ __device__ __forceinline__ void pdl_trigger() { cudaTriggerProgrammaticLaunchCom
 __device__ __forceinline__ void pdl_wait()
 {
     cudaGridDependencySynchronize();
-    if (gridDim.x <= PDL_MAX_GRID) asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    if (gridDim.x <= PDL_MAX_GRID) {                  // (call sites are warp-uniform; the invalidate is SM-wide)
+        if ((threadIdx.x & 31) == 0) asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        __syncwarp();
+    }
 }
 __device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
 inline int pdl_level()
 {
     static const int lv = [] { const char *e = getenv("B200AMG_PDL"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }();
     return lv;
+}
+// Kernel classes (B200AMG_PDL_CLASSES bit mask): 1 colour sweeps, 2 few-row sliced-ELL forms, 4 everything else.
+// Only the colour sweeps launch early by default -- measured under graph replay (profiles/r02/run20_pdl_classes_summary.txt):
+// config 3 (300 colour launches per cycle, operator loads before the wait) 6.10 -> 5.40 ms with class 1 alone; config 2
+// (35 kernels of 5-190 us) 0.979 ms without, 0.994 with class 2, 1.001 with class 4, 1.019 with both: where the wait sits
+// at the top of a kernel there is nothing to overlap and the fence is pure cost.
+constexpr int PDL_SWEEP = 1, PDL_SELL = 2, PDL_OTHER = 4;
+inline bool pdl_class(int bit)
+{
+    static const int mask = [] { const char *e = getenv("B200AMG_PDL_CLASSES"); return e ? atoi(e) : PDL_SWEEP; }();
+    return (mask & bit) != 0;
 }
 // early: the caller's judgement that the launch is latency-bound (few rows); level 2 ignores it
 template <class... P, class... A>

@@ -330,7 +330,7 @@ static int launch_pipe(const StreamArgs &a, int rpt, cudaStream_t st)
     const int nrows = a.row_end - a.row_begin;
     const int num_tiles = (nrows + rpt - 1) / rpt;
     const int grid = min(num_tiles, g_sms * P_CTAS_PER_SM);
-    B200_LAUNCH_PDL((long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_pipe_kernel<OP, MODE>), grid, P_TPB, sizeof(Smem), st, a, rpt, num_tiles);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && (long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_pipe_kernel<OP, MODE>), grid, P_TPB, sizeof(Smem), st, a, rpt, num_tiles);
     return check_launch("csr_pipe_kernel");
 }
 

@@ -174,9 +174,9 @@ static int launch_stream(const StreamArgs &a0, cudaStream_t st)
     const int rpb = rows_per_cta_for(a.nnz, nrows);
     const int grid = (nrows + rpb - 1) / rpb;
     if (aligned16(a.Aj) && aligned16(a.Ax))
-        B200_LAUNCH_PDL((long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_stream_kernel<OP, true>), grid, TPB, 0, st, a, rpb);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && (long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_stream_kernel<OP, true>), grid, TPB, 0, st, a, rpb);
     else
-        B200_LAUNCH_PDL((long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_stream_kernel<OP, false>), grid, TPB, 0, st, a, rpb);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && (long long)(a.row_end - a.row_begin) < PDL_SMALL_ROWS, (csr_stream_kernel<OP, false>), grid, TPB, 0, st, a, rpb);
     return check_launch("csr_stream_kernel");
 }
 
@@ -293,8 +293,8 @@ int gs_rows(bool bsrf, const int *Ap, const int *Aj, const double *Ax, double *x
 {
     if (p1 <= p0) return 0;
     const int grid = (p1 - p0 + 127) / 128;
-    if (bsrf) B200_LAUNCH_PDL(p1 - p0 < 64 * 1024, gs_rows_kernel<true>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
-    else B200_LAUNCH_PDL(p1 - p0 < 64 * 1024, gs_rows_kernel<false>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
+    if (bsrf) B200_LAUNCH_PDL(pdl_class(PDL_SWEEP) && p1 - p0 < 64 * 1024, gs_rows_kernel<true>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
+    else B200_LAUNCH_PDL(pdl_class(PDL_SWEEP) && p1 - p0 < 64 * 1024, gs_rows_kernel<false>, grid, 128, 0, st, Ap, Aj, Ax, x, b, Id, p0, p1);
     return check_launch("gs_rows_kernel");
 }
 

@@ -114,7 +114,7 @@ int bsr_jacobi(int bs, int nb0, int nb1, const int *Ap, const int *Aj, const dou
                double *xout, const double *b, double omega, cudaStream_t st);
 int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double *x, const double *b,
                  const int *Id, int p0, int p1, bool backward, cudaStream_t st, double blocks_per_row = -1.0,
-                 bool perm = false);
+                 bool perm = false, bool static_op = false);    // static_op: no kernel in flight writes (Ap, Aj, Ax, Id)
 // colour-grouped copy of a BSR operator for colour-ordered block Gauss-Seidel (row p = block row Id[p]); rp == nullptr: none
 struct BsrColor {
     int *rp = nullptr, *cj = nullptr;

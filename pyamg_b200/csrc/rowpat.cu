@@ -503,7 +503,7 @@ static int launch_rowpat(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     const int n_chunks = (r.n + RP_CHUNK - 1) / RP_CHUNK;
     const int grid = std::min(n_chunks, sms * RP_CTAS_PER_SM);
     RowPatArgs a{r.n, r.npat, r.far, r.codes, r.table, s.x, s.b, s.y, s.alpha, s.beta, s.omega};
-    B200_LAUNCH_PDL((long long)r.n < PDL_SMALL_ROWS, rowpat_kernel<OP>, grid, RP_TPB, ((sizeof(int) + sizeof(double)) * RP_LEN + sizeof(int)) * r.npat + 16, st, a);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && (long long)r.n < PDL_SMALL_ROWS, rowpat_kernel<OP>, grid, RP_TPB, ((sizeof(int) + sizeof(double)) * RP_LEN + sizeof(int)) * r.npat + 16, st, a);
     return check_launch("rowpat_kernel");
 }
 

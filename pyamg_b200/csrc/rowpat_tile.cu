@@ -331,7 +331,7 @@ static int launch_tile(const RowPat &r, const StreamArgs &s, cudaStream_t st)
     a.omega = s.omega;
     const int n_chunks = (r.n + TT_CH - 1) / TT_CH;
     const int grid = std::min(n_chunks, sms * TT_RESIDENT);
-    B200_LAUNCH_PDL((long long)a.n < PDL_SMALL_ROWS, (rowpat_tile_kernel<OP, LEN>), grid, TT_TPB, smem, st, a);
+    B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && (long long)a.n < PDL_SMALL_ROWS, (rowpat_tile_kernel<OP, LEN>), grid, TT_TPB, smem, st, a);
     return check_launch("rowpat_tile_kernel");
 }
 

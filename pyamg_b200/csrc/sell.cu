@@ -439,7 +439,7 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
                                           (const int *)s.row_len, Id, x, b, 0);                                                   \
         if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                            \
     } while (0)
-    if (U == 32) SELL_GS_LAUNCH(true, 32, 64);
+    if (U == 32) SELL_GS_LAUNCH(pdl_class(PDL_SWEEP), 32, 64);
     else SELL_GS_LAUNCH(false, 8, SELL_TPB);
 #undef SELL_GS_LAUNCH
     return check_launch("sell_gs_kernel");
@@ -463,9 +463,9 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
     if (s.cc) {
-        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
     } else if (s.cd) {
-        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
     } else if (s.n < SELL_BIG_ROWS) {
         // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: 16 slots per round,
         // all forced in flight, and 64-thread blocks so that the few warps spread over all SMs.  Measured on config 2
@@ -474,11 +474,11 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
         // smoothing ops already kept their loads together (the diagonal test splits the basic block) and are fastest
         // as they were (0.021 vs 0.028 ms).
         if (OP < OP_JACOBI && sell_small_deep())
-            B200_LAUNCH_PDL(true, (sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
         else
-            B200_LAUNCH_PDL(true, (sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     } else {
-        B200_LAUNCH_PDL(s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
     }
     return check_launch("sell_kernel");
 }

@@ -231,8 +231,14 @@ constexpr long long SL_MAX_VALUES = 40000;
 int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *Ap, const int *Aj, const double *Ax, const int *Id,
                  const int *cptr_dev, int K, double *x, const double *b, int iters, int sweep, bool x_is_zero, cudaStream_t st)
 {
-    static const bool on = [] { const char *e = getenv("B200AMG_SMALL_LEVEL"); return !(e && e[0] == '0'); }();
-    if (!on || !cptr_dev || n > SL_MAX_N || n <= 0 || K <= 0 || iters <= 0 || iters > 15) return -1;
+    // B200AMG_SMALL_LEVEL: 0 never, 1 block levels only (default), 2 scalar levels too.  Since the per-colour launches
+    // of small colours start early (programmatic dependent launch, operator loads before the wait: ~3 us per colour) they
+    // beat the one-block scalar form (~4 us per colour phase): config 3 level 7, 0.104 -> 0.084 ms per step
+    // (profiles/r02/run19_summary.txt).
+    const char *env = getenv("B200AMG_SMALL_LEVEL");         // (read per call: tests switch it)
+    const int mode = (env && env[0] >= '0' && env[0] <= '2') ? env[0] - '0' : 1;
+    if (mode == 0 || (mode == 1 && bs == 1)) return -1;
+    if (!cptr_dev || n > SL_MAX_N || n <= 0 || K <= 0 || iters <= 0 || iters > 15) return -1;
     if (stored_values < 0 || stored_values > SL_MAX_VALUES) return -1;
     int npass = 0;
     const unsigned dirs = pass_dirs(iters, sweep, &npass);
@@ -241,17 +247,17 @@ int gs_level_cta(int bs, bool bsrf, int n, long long stored_values, const int *A
     if (bs == 1) {
         if (bsrf) {
             SL_OPT_IN(gs_level_cta_kernel<true>);
-            B200_LAUNCH_PDL(true, gs_level_cta_kernel<true>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
+            B200_LAUNCH_PDL(pdl_class(PDL_SWEEP), gs_level_cta_kernel<true>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
         } else {
             SL_OPT_IN(gs_level_cta_kernel<false>);
-            B200_LAUNCH_PDL(true, gs_level_cta_kernel<false>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
+            B200_LAUNCH_PDL(pdl_class(PDL_SWEEP), gs_level_cta_kernel<false>, 1, SL_TPB1, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi);
         }
         return check_launch("gs_level_cta_kernel");
     }
 #define SL_BSR(BSV)                                                                                                          \
     case BSV: {                                                                                                              \
         SL_OPT_IN(bsr_gs_level_cta_kernel<BSV>);                                                                             \
-        B200_LAUNCH_PDL(true, bsr_gs_level_cta_kernel<BSV>, 1, SL_TPB, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi); \
+        B200_LAUNCH_PDL(pdl_class(PDL_SWEEP), bsr_gs_level_cta_kernel<BSV>, 1, SL_TPB, smem, st, n, Ap, Aj, Ax, Id, cptr_dev, K, x, b, npass, dirs, zi); \
     } break;
     switch (bs) {
         SL_BSR(2) SL_BSR(3) SL_BSR(4) SL_BSR(5) SL_BSR(6) SL_BSR(7) SL_BSR(8)

@@ -174,10 +174,10 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
                         B200_TRY(gs_rows(d.flavor != 0 && !d.gs_csr, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, st));
                     else if (L.bGS.ok())
                         B200_TRY(bsr_gs_color(d.bs, L.bGS.rp, L.bGS.cj, L.bGS.cx, *cur, b, d.Id, p0, p1, bwd, st,
-                                              (double)L.nzA / (double)(d.n / d.bs), true));
+                                              (double)L.nzA / (double)(d.n / d.bs), true, true));
                     else
                         B200_TRY(bsr_gs_color(d.bs, d.Ap, d.Aj, d.Ax, *cur, b, d.Id, p0, p1, bwd, st,
-                                              (double)L.nzA / (double)(d.n / d.bs)));
+                                              (double)L.nzA / (double)(d.n / d.bs), false, true));
                 }
             }
         }

@@ -650,11 +650,12 @@ def emu_small():
 @pytest.mark.parametrize('n,per_row,sweep,iters,zero', [(700, 9, 2, 1, False), (300, 25, 0, 2, True), (1500, 5, 1, 1, False),
                                                         (40, 3, 2, 3, False)])
 @pytest.mark.parametrize('bsrf', [False, True])
-def test_small_level_step_scalar(emu_small, n, per_row, sweep, iters, zero, bsrf):
+def test_small_level_step_scalar(emu_small, monkeypatch, n, per_row, sweep, iters, zero, bsrf):
     """gs_level_cta_kernel (iterate in shared memory, the NEXT colour's row requested before the current one is folded;
     rows longer than the 16 prefetched entries and colours wider than the 256 threads included) against the oracle's
     sequential gauss_seidel_indexed / bsr_gauss_seidel_indexed(blocksize 1) sweeps over the same MIS colour ordering"""
     from oracle import relaxation as orx
+    monkeypatch.setenv('B200AMG_SMALL_LEVEL', '2')          # the scalar form is opt-in (per-colour launches are faster on a B200)
     rng = np.random.RandomState(n + per_row)
     rows = np.repeat(np.arange(n), per_row)
     cols = (rows + rng.randint(-4 * per_row, 4 * per_row, rows.size)) % n
