@@ -32,14 +32,27 @@ bool sell_wanted(long long nnz, int nrows)
 
 // ---- build ----------------------------------------------------------------------------------
 // perm (nullable): slot row r holds the matrix row perm[r] (colour-grouped copies for Gauss-Seidel)
-__global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ perm,
-                                                         long long *__restrict__ width, int *__restrict__ row_len)
+// 16-bit column steps: a step of s columns is stored as s / 65535 ESCAPE slots (0xFFFF: "65 535 columns on, no entry")
+// followed by the entry's slot with s % 65535 -- a row that reaches across a grid plane of 65 536 points costs a slot
+constexpr int SELL_ESC = 0xFFFF;
+__device__ __forceinline__ int sell_row_escapes(const int *__restrict__ Aj, int lo, int hi)
+{
+    int e = 0;
+    for (int k = lo + 1; k < hi; ++k) e += (Aj[k] - Aj[k - 1]) / SELL_ESC;
+    return e;
+}
+
+// Aj != nullptr: 16-bit steps, a row's slots = entries + escapes
+__global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
+                                                         const int *__restrict__ perm, long long *__restrict__ width,
+                                                         int *__restrict__ row_len)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     int len = 0;
     if (row < n) {
         const int src = perm ? perm[row] : row;
         len = Ap[src + 1] - Ap[src];
+        if (Aj) len += sell_row_escapes(Aj, Ap[src], Ap[src + 1]);
         row_len[row] = len;
     }
     int m = len;
@@ -66,29 +79,52 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__rest
         lo = Ap[src];
         len = Ap[src + 1] - lo;
     }
-    if (cd && row < n) first[row] = len > 0 ? Aj[lo] : 0;
+    if (cd) {                                           // 16-bit steps (never with value codes)
+        if (row < n) first[row] = len > 0 ? Aj[lo] : 0;
+        int slot = 0;
+        for (int k = 0; k < len; ++k) {
+            const int step = k > 0 ? Aj[lo + k] - Aj[lo + k - 1] : 0;
+            for (int e = step / SELL_ESC; e > 0; --e, ++slot) {
+                cd[off + (long long)slot * SELL_C + lane] = (unsigned short)SELL_ESC;
+                cv[off + (long long)slot * SELL_C + lane] = 0.0;
+            }
+            cd[off + (long long)slot * SELL_C + lane] = (unsigned short)(step % SELL_ESC);
+            cv[off + (long long)slot * SELL_C + lane] = Ax[lo + k];
+            ++slot;
+        }
+        for (; slot < w; ++slot) {
+            cd[off + (long long)slot * SELL_C + lane] = 0;
+            cv[off + (long long)slot * SELL_C + lane] = 0.0;
+        }
+        return;
+    }
     for (int k = 0; k < w; ++k) {
         const bool in = k < len;
-        if (cd) cd[off + (long long)k * SELL_C + lane] = (in && k > 0) ? (unsigned short)(Aj[lo + k] - Aj[lo + k - 1]) : (unsigned short)0;
-        else cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
+        cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
         if (cc) cc[off + (long long)k * SELL_C + lane] = in ? codes[lo + k] : (unsigned char)0;
         else cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
     }
 }
 
-// 16-bit column steps need rows stored by ascending column with steps below 65 536 (flag[0] = 1 otherwise)
+// 16-bit column steps need rows stored by ascending column (flag[0] = 1 otherwise); flag[1] += escape slots needed
 __global__ void __launch_bounds__(256) sell_steps_check_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                                int *__restrict__ flag)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
-    if (row >= n) return;
     bool bad = false;
-    const int hi = Ap[row + 1];
-    for (int k = Ap[row] + 1; k < hi; ++k) {
-        const long long step = (long long)Aj[k] - Aj[k - 1];
-        bad |= step < 0 || step > 65535;
+    int esc = 0;
+    if (row < n) {
+        const int hi = Ap[row + 1];
+        for (int k = Ap[row] + 1; k < hi; ++k) {
+            const int step = Aj[k] - Aj[k - 1];
+            bad |= step < 0;
+            esc += step > 0 ? step / SELL_ESC : 0;
+        }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) esc += __shfl_xor_sync(0xffffffffu, esc, o);
     if (bad) flag[0] = 1;
+    if ((threadIdx.x & 31) == 0 && esc > 0) atomicAdd(flag + 1, min(esc, 1 << 20));
 }
 
 void sell_free(Sell *s)
@@ -123,24 +159,27 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
     if (e == cudaSuccess) e = cudaMalloc(&s.slice_off, sizeof(long long) * (ns + 1));
     if (e == cudaSuccess) e = cudaMalloc(&s.row_len, sizeof(int) * (size_t)n);
     int rc = 0;
-    if (e == cudaSuccess) {
-        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, perm, width, s.row_len);
+    if (e == cudaSuccess && steps) {
+        // sorted rows, and escape slots for steps >= 65 535 a small fraction of the entries (a 512-point-wide grid
+        // would need four per plane crossing: 32-bit columns are cheaper then)
+        int *flag = reinterpret_cast<int *>(width);
+        int got[2] = {0, 0};
+        e = cudaMemsetAsync(flag, 0, 2 * sizeof(int), st);
+        if (e == cudaSuccess) {
+            sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, flag);
+            rc = check_launch("sell_steps_check_kernel");
+        }
+        if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(got, flag, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (got[0] || (long long)got[1] * 32 > nnz) steps = false;
+    }
+    if (e == cudaSuccess && !rc) {
+        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, steps ? Aj : nullptr, perm, width, s.row_len);
         rc = check_launch("sell_width_kernel");
         if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
-        int *flag = reinterpret_cast<int *>(width);            // width is consumed by the scan: reuse its first word
-        if (!rc && steps) {
-            e = cudaMemsetAsync(flag, 0, sizeof(int), st);
-            if (e == cudaSuccess) {
-                sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, flag);
-                rc = check_launch("sell_steps_check_kernel");
-            }
-        }
-        if (!rc && e == cudaSuccess) {
-            int bad = 0;
+        if (!rc) {
             e = cudaMemcpyAsync(&s.padded, s.slice_off + ns, sizeof(long long), cudaMemcpyDeviceToHost, st);
-            if (e == cudaSuccess && steps) e = cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-            if (bad) steps = false;
         }
     }
     // refuse pathological padding (one long row per slice): the CSR kernels handle those
@@ -297,8 +336,9 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const bool in = k0 + u < len;
+            const bool esc = STEPS && (int)raw[u] == SELL_ESC;         // "65 535 columns on, no entry"
             if (STEPS) run += (int)raw[u];                              // padding slots hold step 0
-            c[u] = in ? (STEPS ? run : (int)raw[u]) : -1;
+            c[u] = (in && !esc) ? (STEPS ? run : (int)raw[u]) : -1;
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
@@ -379,8 +419,9 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
+            const bool esc = STEPS && (int)raw[u] == SELL_ESC;
             if (STEPS) run += (int)raw[u];
-            c[u] = (k0 + u < len) ? (STEPS ? run : (int)raw[u]) : -1;
+            c[u] = (k0 + u < len && !esc) ? (STEPS ? run : (int)raw[u]) : -1;
         }
         int tie = 0;
         if (TIE) {

@@ -479,11 +479,13 @@ def test_sliced_ell_layout_bit_exact(amg, name, n, per_row, few_values):
 
 
 @pytest.mark.parametrize('name,n,per_row,span,sort,expect', [('steps_fit', 40000, 31, 90, True, 7), ('long_rows', 9000, 240, 700, True, 7),
-                                                             ('step_too_wide', 300000, 20, 140000, True, 2),
+                                                             ('some_wide_steps', 300000, 40, 140000, True, 7),
+                                                             ('mostly_wide_steps', 300000, 4, 150000, True, 2),
                                                              ('unsorted_rows', 40000, 31, 90, False, 2)])
 def test_sliced_ell_16bit_column_steps(amg, monkeypatch, name, n, per_row, span, sort, expect):
     """layout 7: columns stored as 16-bit steps from the previous stored column (10 bytes per slot).  Needs rows
-    stored by ascending column with steps < 65 536; anything else keeps 32-bit columns.  Same bits either way."""
+    stored by ascending column; a step of 65 535 columns or more takes escape slots ("65 535 on, no entry"), and when
+    those would exceed 1/32 of the entries the copy keeps 32-bit columns.  Same bits either way."""
     monkeypatch.setenv('B200AMG_SELL_COL16', '2')           # the engine uses it from 400 000 rows; here for every size
     rng = np.random.RandomState(12)
     rows = np.repeat(np.arange(n), per_row)
@@ -498,6 +500,9 @@ def test_sliced_ell_16bit_column_steps(amg, monkeypatch, name, n, per_row, span,
             lo, hi = A.indptr[i], A.indptr[i + 1]
             A.indices[lo:hi] = A.indices[lo:hi][::-1].copy(); A.data[lo:hi] = A.data[lo:hi][::-1].copy()
         A.has_sorted_indices = False
+    if name == 'some_wide_steps':       # rows of 40 columns within +-140 000: a few steps per hundred rows need an escape
+        st = np.diff(A.indices.astype(np.int64))
+        assert 0 < np.count_nonzero(st >= 65535) * 32 < A.nnz
     x, b = rng.rand(n), rng.rand(n)
     dA = amg.DevMat.from_scipy(A)                           # storage order kept as given
     P = lambda t: t.data_ptr()
