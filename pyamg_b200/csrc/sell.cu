@@ -35,6 +35,7 @@ bool sell_wanted(long long nnz, int nrows)
 // 16-bit column steps: a step of s columns is stored as s / 65535 ESCAPE slots (0xFFFF: "65 535 columns on, no entry")
 // followed by the entry's slot with s % 65535 -- a row that reaches across a grid plane of 65 536 points costs a slot
 constexpr int SELL_ESC = 0xFFFF;
+constexpr int SELL_HAS_ESC = (int)0x80000000;      // flag in row_len: this row holds escape slots
 __device__ __forceinline__ int sell_row_escapes(const int *__restrict__ Aj, int lo, int hi)
 {
     int e = 0;
@@ -52,8 +53,9 @@ __global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__res
     if (row < n) {
         const int src = perm ? perm[row] : row;
         len = Ap[src + 1] - Ap[src];
-        if (Aj) len += sell_row_escapes(Aj, Ap[src], Ap[src + 1]);
-        row_len[row] = len;
+        const int esc = Aj ? sell_row_escapes(Aj, Ap[src], Ap[src + 1]) : 0;
+        len += esc;
+        row_len[row] = esc ? (len | SELL_HAS_ESC) : len;        // the apply kernels take the escape-aware path per slice
     }
     int m = len;
 #pragma unroll
@@ -256,7 +258,11 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     const long long off = slice_off[slice];
     const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
     const bool live = row < n;
-    const int len = live ? row_len[row] : 0;
+    const int len_raw = live ? row_len[row] : 0;
+    const int len = len_raw & ~SELL_HAS_ESC;
+    // escape slots are rare (rows that cross a grid plane of >= 65 535 points): slices without any take a loop that
+    // does not test for them (the test costs the level-1 Jacobi sweep of config 2 a quarter of its speed)
+    const bool slice_esc = STEPS && __any_sync(0xffffffffu, len_raw < 0);
     const double *__restrict__ xg = a.x;
     double bi = 0.0, xi = 0.0, yi = 0.0;
     int run = (STEPS && live) ? __ldg(first + row) : 0;        // STEPS: column of the last slot walked
@@ -323,34 +329,39 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
     pdl_wait();
     load_vectors();
     acc = BSRF ? bi : 0.0;
-    for (int k0 = 0; k0 < w; k0 += U) {
-        int c[U];
-        J raw[U];
-        double v[U], xv[U];
+    auto rounds = [&](auto esc_tag) {
+        constexpr bool ESC = decltype(esc_tag)::value;
+        for (int k0 = 0; k0 < w; k0 += U) {
+            int c[U];
+            J raw[U];
+            double v[U], xv[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const bool in = k0 + u < len;
-            raw[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : (J)0;
-            v[u] = in ? value(__ldcs(pv + (long long)(k0 + u) * SELL_C)) : 0.0;
-        }
+            for (int u = 0; u < U; ++u) {
+                const bool in = k0 + u < len;
+                raw[u] = in ? __ldcs(pj + (long long)(k0 + u) * SELL_C) : (J)0;
+                v[u] = in ? value(__ldcs(pv + (long long)(k0 + u) * SELL_C)) : 0.0;
+            }
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const bool in = k0 + u < len;
-            const bool esc = STEPS && (int)raw[u] == SELL_ESC;         // "65 535 columns on, no entry"
-            if (STEPS) run += (int)raw[u];                              // padding slots hold step 0
-            c[u] = (in && !esc) ? (STEPS ? run : (int)raw[u]) : -1;
-        }
+            for (int u = 0; u < U; ++u) {
+                const bool in = k0 + u < len;
+                const bool esc = ESC && (int)raw[u] == SELL_ESC;        // "65 535 columns on, no entry"
+                if (STEPS) run += (int)raw[u];                          // padding slots hold step 0
+                c[u] = (in && !esc) ? (STEPS ? run : (int)raw[u]) : -1;
+            }
 #pragma unroll
-        for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
+            for (int u = 0; u < U; ++u) xv[u] = (c[u] >= 0) ? __ldg(xg + c[u]) : 0.0;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (c[u] >= 0) {
-                const double pr = mul_rn(v[u], xv[u]);
-                if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
-                else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+            for (int u = 0; u < U; ++u) {
+                if (c[u] >= 0) {
+                    const double pr = mul_rn(v[u], xv[u]);
+                    if (SMOOTH && c[u] == row) diag = v[u];             // last stored diagonal wins
+                    else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
+                }
             }
         }
-    }
+    };
+    if (STEPS && slice_esc) rounds(std::true_type{});
+    else rounds(std::false_type{});
     }
     if (!live) return;
     double *y = a.y;
@@ -401,7 +412,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     const bool live = r >= p0 && r < p1;
     const long long off = slice_off[slice];
     const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
-    const int len = live ? row_len[r] : 0;
+    const int len = live ? (row_len[r] & ~SELL_HAS_ESC) : 0;
     const int row = live ? Id[r] : -1;
     const J *pj = cj + off + lane;
     const double *pv = cv + off + lane;
@@ -419,6 +430,8 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
+            // (tested per slot here: a per-slice switch like sell_kernel's made THIS kernel slower -- config 3 level 0,
+            // 1.02 -> 1.21 ms per step, profiles/r02/run22_summary.txt)
             const bool esc = STEPS && (int)raw[u] == SELL_ESC;
             if (STEPS) run += (int)raw[u];
             c[u] = (k0 + u < len && !esc) ? (STEPS ? run : (int)raw[u]) : -1;
