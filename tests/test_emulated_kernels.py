@@ -705,7 +705,7 @@ def test_small_level_step_block(emu_small, bs, sweep):
     assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize('bs,nb,density', [(2, 300, 0.6), (3, 200, 0.6), (6, 80, 0.7)])
+@pytest.mark.parametrize('bs,nb,density', [(2, 190, 0.7), (3, 130, 0.7), (6, 80, 0.7)])
 def test_bsr_warp_gauss_seidel_long_rows(emu_bsr, bs, nb, density):
     """the batched warp-per-block-row sweep on rows that need SEVERAL batches (4 or 8 passes of 32 / bs blocks each) and a
     ragged last one, against the reference's bsr_gauss_seidel_indexed on the same colour ordering"""
