@@ -436,7 +436,8 @@ int b200amg_vcycle_profile(void *handle, double *x, const double *b, int cycle_k
                            int *op_code_host, int *op_level_host, float *op_ms_host,
                            int *n_ops_host, void *stream);
 /* layout the engine streams an operator of `level` in (which: 0 A, 1 P, 2 R, 3 the colour-grouped copy of A that
- * colour-ordered Gauss-Seidel sweeps): the b200amg_op_layout codes, 0 for block operators / no such copy.
+ * colour-ordered Gauss-Seidel sweeps, 4 the diagonal-free copy of A that the Jacobi sweeps of a level of >= 400 000
+ * rows stream): the b200amg_op_layout codes, 0 for block operators / no such copy.
  * Informational: every layout gives the same bits. */
 int b200amg_vcycle_layout(void *handle, int level, int which);
 /* rnorm2_dev[0] = ||b - A0 x||^2 on the finest level (residual_norm of multilevel.py:450,461) */

@@ -80,6 +80,8 @@ struct Sell {
     int *cj = nullptr;               // [padded]   32-bit columns, or
     unsigned short *cd = nullptr;    // [padded]   16-bit column steps: column of slot k = first[row] + cd[0..k] (sorted rows)
     int *first = nullptr;            // [n]        first stored column of every row (with cd)
+    double *dg = nullptr;            // [n]        copies for smoothers: the diagonal entries are NOT among the slots,
+                                     //            dg[slot row] = the last stored one (0.0: none)
     double *cv = nullptr;            // [padded]   (fp64 values) or
     unsigned char *cc = nullptr;     // [padded]   8-bit value codes into dict[256]
     double *dict = nullptr;
@@ -87,7 +89,8 @@ struct Sell {
     bool ok() const { return cj != nullptr || cd != nullptr; }
 };
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
-               const int *perm = nullptr, const unsigned char *codes = nullptr, const double *dict = nullptr);
+               const int *perm = nullptr, const unsigned char *codes = nullptr, const double *dict = nullptr,
+               bool drop_diag = false);
 // one colour [p0, p1) of a colour-grouped copy (slot row r = matrix row Id[r]); x updated in place
 int sell_gs_color(bool bsrf, const Sell &s, const int *Id, int p0, int p1, double *x, const double *b, cudaStream_t st);
 void sell_free(Sell *s);

@@ -36,25 +36,37 @@ bool sell_wanted(long long nnz, int nrows)
 // followed by the entry's slot with s % 65535 -- a row that reaches across a grid plane of 65 536 points costs a slot
 constexpr int SELL_ESC = 0xFFFF;
 constexpr int SELL_HAS_ESC = (int)0x80000000;      // flag in row_len: this row holds escape slots
-__device__ __forceinline__ int sell_row_escapes(const int *__restrict__ Aj, int lo, int hi)
+// kept entries of matrix row src -- all of them, or all but the diagonal ones (drop: copies made for a smoother, which
+// never adds the diagonal entry to the row sum; the others keep their order) -- and the escape slots that 16-bit steps
+// need between consecutive kept entries
+__device__ __forceinline__ void sell_row_shape(const int *__restrict__ Ap, const int *__restrict__ Aj, int src, bool drop,
+                                               bool steps, int &kept, int &esc)
 {
-    int e = 0;
-    for (int k = lo + 1; k < hi; ++k) e += (Aj[k] - Aj[k - 1]) / SELL_ESC;
-    return e;
+    const int lo = Ap[src], hi = Ap[src + 1];
+    kept = hi - lo;
+    esc = 0;
+    if (!drop && !steps) return;
+    kept = 0;
+    int prev = 0;
+    for (int k = lo; k < hi; ++k) {
+        const int j = Aj[k];
+        if (drop && j == src) continue;
+        if (steps && kept > 0 && j > prev) esc += (j - prev) / SELL_ESC;
+        prev = j;
+        ++kept;
+    }
 }
 
-// Aj != nullptr: 16-bit steps, a row's slots = entries + escapes
 __global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
-                                                         const int *__restrict__ perm, long long *__restrict__ width,
-                                                         int *__restrict__ row_len)
+                                                         const int *__restrict__ perm, bool drop, bool steps,
+                                                         long long *__restrict__ width, int *__restrict__ row_len)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     int len = 0;
     if (row < n) {
-        const int src = perm ? perm[row] : row;
-        len = Ap[src + 1] - Ap[src];
-        const int esc = Aj ? sell_row_escapes(Aj, Ap[src], Ap[src + 1]) : 0;
-        len += esc;
+        int kept, esc;
+        sell_row_shape(Ap, Aj, perm ? perm[row] : row, drop, steps, kept, esc);
+        len = kept + esc;
         row_len[row] = esc ? (len | SELL_HAS_ESC) : len;        // the apply kernels take the escape-aware path per slice
     }
     int m = len;
@@ -63,65 +75,72 @@ __global__ void __launch_bounds__(256) sell_width_kernel(int n, const int *__res
     if ((threadIdx.x & 31) == 0 && (row >> 5) < (n + SELL_C - 1) / SELL_C) width[row >> 5] = (long long)m * SELL_C;
 }
 
+// dg != nullptr: diagonal entries are left out of the slots, dg[slot row] = the LAST stored one (0.0: none) -- what
+// the reference's sweeps use as the diagonal (relaxation.h:201-239, :394-426)
 __global__ void __launch_bounds__(256) sell_fill_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
                                                         const double *__restrict__ Ax, const int *__restrict__ perm,
                                                         const long long *__restrict__ slice_off, int *__restrict__ cj,
                                                         double *__restrict__ cv, const unsigned char *__restrict__ codes,
                                                         unsigned char *__restrict__ cc, unsigned short *__restrict__ cd,
-                                                        int *__restrict__ first)
+                                                        int *__restrict__ first, double *__restrict__ dg)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     const int slice = row >> 5, lane = threadIdx.x & 31;
     if (slice >= (n + SELL_C - 1) / SELL_C) return;
     const long long off = slice_off[slice];
     const int w = (int)((slice_off[slice + 1] - off) / SELL_C);
-    int lo = 0, len = 0;
+    int lo = 0, len = 0, src = -1;
     if (row < n) {
-        const int src = perm ? perm[row] : row;
+        src = perm ? perm[row] : row;
         lo = Ap[src];
         len = Ap[src + 1] - lo;
     }
-    if (cd) {                                           // 16-bit steps (never with value codes)
-        if (row < n) first[row] = len > 0 ? Aj[lo] : 0;
-        int slot = 0;
-        for (int k = 0; k < len; ++k) {
-            const int step = k > 0 ? Aj[lo + k] - Aj[lo + k - 1] : 0;
+    int slot = 0, prev = 0;
+    double diag = 0.0;
+    for (int k = 0; k < len; ++k) {
+        const int j = Aj[lo + k];
+        if (dg && j == src) {
+            diag = Ax[lo + k];
+            continue;
+        }
+        if (cd) {                                       // 16-bit steps (never with value codes)
+            const int step = (slot > 0 && j > prev) ? j - prev : 0;
+            if (slot == 0) first[row] = j;
             for (int e = step / SELL_ESC; e > 0; --e, ++slot) {
                 cd[off + (long long)slot * SELL_C + lane] = (unsigned short)SELL_ESC;
                 cv[off + (long long)slot * SELL_C + lane] = 0.0;
             }
             cd[off + (long long)slot * SELL_C + lane] = (unsigned short)(step % SELL_ESC);
-            cv[off + (long long)slot * SELL_C + lane] = Ax[lo + k];
-            ++slot;
+        } else {
+            cj[off + (long long)slot * SELL_C + lane] = j;
         }
-        for (; slot < w; ++slot) {
-            cd[off + (long long)slot * SELL_C + lane] = 0;
-            cv[off + (long long)slot * SELL_C + lane] = 0.0;
-        }
-        return;
+        if (cc) cc[off + (long long)slot * SELL_C + lane] = codes[lo + k];
+        else cv[off + (long long)slot * SELL_C + lane] = Ax[lo + k];
+        prev = j;
+        ++slot;
     }
-    for (int k = 0; k < w; ++k) {
-        const bool in = k < len;
-        cj[off + (long long)k * SELL_C + lane] = in ? Aj[lo + k] : 0;
-        if (cc) cc[off + (long long)k * SELL_C + lane] = in ? codes[lo + k] : (unsigned char)0;
-        else cv[off + (long long)k * SELL_C + lane] = in ? Ax[lo + k] : 0.0;
+    if (cd && row < n && slot == 0) first[row] = 0;
+    for (; slot < w; ++slot) {
+        if (cd) cd[off + (long long)slot * SELL_C + lane] = 0;
+        else cj[off + (long long)slot * SELL_C + lane] = 0;
+        if (cc) cc[off + (long long)slot * SELL_C + lane] = 0;
+        else cv[off + (long long)slot * SELL_C + lane] = 0.0;
     }
+    if (dg && row < n) dg[row] = diag;
 }
 
 // 16-bit column steps need rows stored by ascending column (flag[0] = 1 otherwise); flag[1] += escape slots needed
 __global__ void __launch_bounds__(256) sell_steps_check_kernel(int n, const int *__restrict__ Ap, const int *__restrict__ Aj,
-                                                               int *__restrict__ flag)
+                                                               bool drop, int *__restrict__ flag)
 {
     const int row = blockIdx.x * 256 + threadIdx.x;
     bool bad = false;
     int esc = 0;
     if (row < n) {
         const int hi = Ap[row + 1];
-        for (int k = Ap[row] + 1; k < hi; ++k) {
-            const int step = Aj[k] - Aj[k - 1];
-            bad |= step < 0;
-            esc += step > 0 ? step / SELL_ESC : 0;
-        }
+        for (int k = Ap[row] + 1; k < hi; ++k) bad |= Aj[k] < Aj[k - 1];
+        int kept;
+        sell_row_shape(Ap, Aj, row, drop, true, kept, esc);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) esc += __shfl_xor_sync(0xffffffffu, esc, o);
@@ -135,6 +154,7 @@ void sell_free(Sell *s)
     if (s->cj) cudaFree(s->cj);
     if (s->cd) cudaFree(s->cd);
     if (s->first) cudaFree(s->first);
+    if (s->dg) cudaFree(s->dg);
     if (s->cv) cudaFree(s->cv);
     if (s->cc) cudaFree(s->cc);
     if (s->dict) cudaFree(s->dict);
@@ -143,7 +163,7 @@ void sell_free(Sell *s)
 }
 
 int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double *Ax, Sell *out, cudaStream_t st,
-               const int *perm, const unsigned char *codes, const double *dict)
+               const int *perm, const unsigned char *codes, const double *dict, bool drop_diag)
 {
     const bool coded = codes != nullptr && dict != nullptr;     // 8-bit value codes instead of fp64 values
     // 16-bit column steps (10 instead of 12 bytes per slot) where bytes are what the pass costs: big uncoded operators
@@ -168,7 +188,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         int got[2] = {0, 0};
         e = cudaMemsetAsync(flag, 0, 2 * sizeof(int), st);
         if (e == cudaSuccess) {
-            sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, flag);
+            sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, drop_diag, flag);
             rc = check_launch("sell_steps_check_kernel");
         }
         if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(got, flag, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
@@ -176,7 +196,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         if (got[0] || (long long)got[1] * 32 > nnz) steps = false;
     }
     if (e == cudaSuccess && !rc) {
-        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, steps ? Aj : nullptr, perm, width, s.row_len);
+        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, perm, drop_diag, steps, width, s.row_len);
         rc = check_launch("sell_width_kernel");
         if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
         if (!rc) {
@@ -192,13 +212,14 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         } else {
             e = cudaMalloc(&s.cj, sizeof(int) * (size_t)s.padded);
         }
+        if (e == cudaSuccess && drop_diag) e = cudaMalloc(&s.dg, sizeof(double) * (size_t)n);
         if (e == cudaSuccess && !coded) e = cudaMalloc(&s.cv, sizeof(double) * (size_t)s.padded);
         if (e == cudaSuccess && coded) e = cudaMalloc(&s.cc, (size_t)s.padded + 64);
         if (e == cudaSuccess && coded) e = cudaMalloc(&s.dict, sizeof(double) * 256);
         if (e == cudaSuccess && coded) e = cudaMemcpyAsync(s.dict, dict, sizeof(double) * 256, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess) {
             sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc, s.cd,
-                                                              s.first);
+                                                              s.first, s.dg);
             rc = check_launch("sell_fill_kernel");
             // the apply kernels request slots of this copy BEFORE they wait for their predecessor in the stream
             // (programmatic dependent launch): the copy must be complete when the build returns
@@ -226,12 +247,15 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
 // FMT 0: 32-bit columns + fp64 values (12 bytes per slot)
 // FMT 1: the value slots hold 8-bit codes into a table of <= 256 doubles (dict.cu) -- 5 bytes per slot
 // FMT 2: 16-bit column STEPS + fp64 values (10 bytes per slot): column = first[row] + running sum of the steps
-template <int OP, int U, bool PIPE, int FMT, bool TIE = false>
+// DF: a copy made for smoothing (Sell::dg): no diagonal entries among the slots, the diagonal comes from dg[row]
+template <int OP, int U, bool PIPE, int FMT, bool TIE = false, bool DF = false>
 __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long long *__restrict__ slice_off,
                                                         const void *__restrict__ cols, const void *__restrict__ cvals,
                                                         const double *__restrict__ dict, const int *__restrict__ first,
-                                                        const int *__restrict__ row_len, const StreamArgs a)
+                                                        const int *__restrict__ row_len, const double *__restrict__ dg,
+                                                        const StreamArgs a)
 {
+    static_assert(!DF || OP >= OP_JACOBI, "diagonal-free copies serve the smoothing ops only");
     constexpr bool CODED = (FMT == 1), STEPS = (FMT == 2);
     static_assert(!(PIPE && FMT != 0), "the prefetching form keeps 32-bit columns and fp64 values");
     static_assert(PIPE || !TIE, "only the prefetching form ties its loads");
@@ -274,7 +298,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
             if (OP == OP_ADD) yi = a.b[row];
         }
     };
-    double acc = 0.0, diag = 0.0;
+    double acc = 0.0, diag = (DF && live) ? __ldg(dg + row) : 0.0;
     const J *pj = cj + off + lane;
     const V *pv = cv + off + lane;
     if constexpr (PIPE) {
@@ -315,7 +339,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
         for (int u = 0; u < U; ++u) {
             if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
                 const double pr = mul_rn(v[u], xv[u]);
-                if (SMOOTH && c[u] == row) diag = v[u];                 // last stored diagonal wins
+                if (!DF && SMOOTH && c[u] == row) diag = v[u];          // last stored diagonal wins
                 else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
             }
         }
@@ -354,7 +378,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
             for (int u = 0; u < U; ++u) {
                 if (c[u] >= 0) {
                     const double pr = mul_rn(v[u], xv[u]);
-                    if (SMOOTH && c[u] == row) diag = v[u];             // last stored diagonal wins
+                    if (!DF && SMOOTH && c[u] == row) diag = v[u];      // last stored diagonal wins
                     else acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
                 }
             }
@@ -391,11 +415,13 @@ __global__ void __launch_bounds__(SELL_TPB) sell_kernel(const int n, const long 
 // colour of a coarse level is a few thousand rows -- one wave of warps whose run time is the number of dependent
 // memory latencies in a row walk (2 per round), so short rows want ONE round.
 // STEPS: 16-bit column steps instead of 32-bit columns (Sell::cd / first)
-template <bool BSRF, int U, bool STEPS>
+// DF: the copy holds no diagonal entries, dg[slot row] is the diagonal (sell_build drop_diag)
+template <bool BSRF, int U, bool STEPS, bool DF>
 __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const int p1, const long long *__restrict__ slice_off,
                                                            const void *__restrict__ cols, const double *__restrict__ cv,
                                                            const int *__restrict__ first,
                                                            const int *__restrict__ row_len, const int *__restrict__ Id,
+                                                           const double *__restrict__ dg,
                                                            double *x, const double *__restrict__ b, const int zero)
 {
     constexpr bool TIE = U > 8;
@@ -417,7 +443,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
     const J *pj = cj + off + lane;
     const double *pv = cv + off + lane;
     int run = (STEPS && live) ? first[r] : 0;
-    double bi = 0.0, acc = 0.0, diag = 0.0;
+    double bi = 0.0, acc = 0.0, diag = (DF && live) ? dg[r] : 0.0;
     for (int k0 = 0; k0 < w; k0 += U) {
         int c[U];
         J raw[U];
@@ -457,7 +483,7 @@ __global__ void __launch_bounds__(SELL_TPB) sell_gs_kernel(const int p0, const i
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if ((u == 0 ? c[u] + tie : c[u]) >= 0) {
-                if (c[u] == row) diag = v[u];
+                if (!DF && c[u] == row) diag = v[u];
                 else {
                     const double pr = mul_rn(v[u], xv[u]);
                     acc = BSRF ? sub_rn(acc, pr) : add_rn(acc, pr);
@@ -482,20 +508,20 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
     const int U = forced ? forced : (rows < 64 * 1024 ? 32 : 8);
     const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
     const int *firstp = s.cd ? s.first : nullptr;
-#define SELL_GS_LAUNCH(EARLY, UU, TPB)                                                                                            \
-    do {                                                                                                                          \
-        const dim3 g((unsigned)((rows + TPB - 1) / TPB)), blk(TPB);                                                               \
-        cudaError_t e = s.cd ? launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, true>, g, blk, 0, st, p0, p1,                           \
-                                          (const long long *)s.slice_off, cols, (const double *)s.cv, firstp,                    \
-                                          (const int *)s.row_len, Id, x, b, 0)                                                    \
-                             : launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, false>, g, blk, 0, st, p0, p1,                          \
-                                          (const long long *)s.slice_off, cols, (const double *)s.cv, firstp,                    \
-                                          (const int *)s.row_len, Id, x, b, 0);                                                   \
-        if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                            \
+#define SELL_GS_ONE(EARLY, UU, TPB, ST, DFV)                                                                                     \
+    launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, ST, DFV>, g, blk, 0, st, p0, p1, (const long long *)s.slice_off, cols,          \
+               (const double *)s.cv, firstp, (const int *)s.row_len, Id, (const double *)s.dg, x, b, 0)
+#define SELL_GS_LAUNCH(EARLY, UU, TPB)                                                                                           \
+    do {                                                                                                                         \
+        const dim3 g((unsigned)((rows + TPB - 1) / TPB)), blk(TPB);                                                              \
+        cudaError_t e = s.cd ? (s.dg ? SELL_GS_ONE(EARLY, UU, TPB, true, true) : SELL_GS_ONE(EARLY, UU, TPB, true, false))       \
+                             : (s.dg ? SELL_GS_ONE(EARLY, UU, TPB, false, true) : SELL_GS_ONE(EARLY, UU, TPB, false, false));    \
+        if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                           \
     } while (0)
     if (U == 32) SELL_GS_LAUNCH(pdl_class(PDL_SWEEP), 32, 64);
     else SELL_GS_LAUNCH(false, 8, SELL_TPB);
 #undef SELL_GS_LAUNCH
+#undef SELL_GS_ONE
     return check_launch("sell_gs_kernel");
 }
 
@@ -516,10 +542,25 @@ template <int OP>
 static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
 {
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
+    const double *nodg = nullptr;
+    if (s.dg) {
+        // a copy without diagonal entries: smoothing ops only, big operators only (the engine builds it next to the
+        // full copy for levels of >= SELL_BIG_ROWS rows)
+        if constexpr (OP >= OP_JACOBI) {
+            if (s.cc || s.n < SELL_BIG_ROWS) return set_err(B200AMG_ESTATE, "sell_op: diagonal-free copy of a small or coded operator");
+            if (s.cd)
+                B200_LAUNCH_PDL(false, (sell_kernel<OP, SELL_U, false, 2, false, true>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, s.dg, a);
+            else
+                B200_LAUNCH_PDL(false, (sell_kernel<OP, SELL_U, false, 0, false, true>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, s.dg, a);
+            return check_launch("sell_kernel");
+        } else {
+            return set_err(B200AMG_ESTATE, "sell_op: a diagonal-free copy serves the smoothing ops only");
+        }
+    }
     if (s.cc) {
-        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 1>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cc, s.dict, nullptr, s.row_len, nodg, a);
     } else if (s.cd) {
-        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 2>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, nodg, a);
     } else if (s.n < SELL_BIG_ROWS) {
         // a warp is a chain of w / U dependent latencies and there are too few warps to hide it: 16 slots per round,
         // all forced in flight, and 64-thread blocks so that the few warps spread over all SMs.  Measured on config 2
@@ -528,11 +569,11 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
         // smoothing ops already kept their loads together (the diagonal test splits the basic block) and are fastest
         // as they were (0.021 vs 0.028 ms).
         if (OP < OP_JACOBI && sell_small_deep())
-            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, 16, true, 0, true>), (s.n + 63) / 64, 64, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, nodg, a);
         else
-            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+            B200_LAUNCH_PDL(pdl_class(PDL_SELL), (sell_kernel<OP, SELL_U, true, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, nodg, a);
     } else {
-        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, a);
+        B200_LAUNCH_PDL(pdl_class(PDL_OTHER) && s.n < PDL_SMALL_ROWS, (sell_kernel<OP, SELL_U, false, 0>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cj, s.cv, nullptr, nullptr, s.row_len, nodg, a);
     }
     return check_launch("sell_kernel");
 }

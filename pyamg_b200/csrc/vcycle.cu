@@ -13,6 +13,12 @@
 
 namespace b200amg {
 
+static bool diag_free_copies()
+{
+    const char *e = getenv("B200AMG_SELL_DIAGFREE");       // read per engine build (tests switch it)
+    return !(e && e[0] == '0');
+}
+
 struct LevelRt {
     b200amg_level_desc d;
     double *r, *bc, *xc, *tmp, *diag;
@@ -20,6 +26,7 @@ struct LevelRt {
     long long nzA = -1, nzP = -1, nzR = -1;   // stored entries (tile sizing of the stream kernels)
     Sell sA, sR, sP;                          // engine-owned sliced-ELL copies of long-row operators
     Sell sGS;                                 // colour-grouped copy of A for colour-ordered Gauss-Seidel
+    Sell sJ;                                  // copy of A WITHOUT its diagonal entries for the Jacobi sweeps of a big level
     BsrColor bGS;                             // the same for a block operator (bsr.cu)
     RowPat rpA;                               // one byte per row of a stencil operator (rowpat.cu)
     ValueDict dA, dP, dR;                     // 8-bit value codes of operators with <= 256 distinct values
@@ -52,7 +59,7 @@ struct Engine {
 
 static void free_level(LevelRt &L)
 {
-    sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS);
+    sell_free(&L.sA); sell_free(&L.sR); sell_free(&L.sP); sell_free(&L.sGS); sell_free(&L.sJ);
     dict_free(&L.dA); dict_free(&L.dP); dict_free(&L.dR);
     rowpat_free(&L.rpA);
     bsr_color_free(&L.bGS);
@@ -143,6 +150,7 @@ static int smooth(const LevelRt &L, bool post, int kind, double omega, int iters
                 StreamArgs a{d.Ap, d.Aj, d.Ax, *cur, b, *spare, L.nzA, 0, d.n, 1.0, 0.0, omega};
                 L.dA.apply(a);
                 if (L.rpA.ok()) B200_TRY(rowpat_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.rpA, a, st));
+                else if (L.sJ.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sJ, a, st));
                 else if (L.sA.ok()) B200_TRY(sell_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, L.sA, a, st));
                 else B200_TRY(stream_op(d.flavor ? OP_JACOBI_BSR1 : OP_JACOBI, a, st));
             } else {
@@ -388,6 +396,11 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
             return rc;
         };
         if (L.d.bs == 1 && sell_wanted(nzA, L.d.n)) src = sell_with_codes(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sA);
+        // Jacobi on a big uncoded level: a second copy without the diagonal entries (the sweep never adds them to the row
+        // sum; the others keep their order: same bits).  The loop loses the per-slot diagonal test and with it half of its
+        // registers -- the smoothing pass then streams like the residual pass.  B200AMG_SELL_DIAGFREE=0: A/B switch.
+        if (!src && L.sA.ok() && !L.sA.cc && L.d.n >= 400000 && (L.d.pre_kind == 1 || L.d.post_kind == 1) && diag_free_copies())
+            src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sJ, nullptr, nullptr, nullptr, nullptr, true);
         if (!src && L.d.p_br == 1 && L.d.p_bc == 1) {
             if (sell_wanted(nzR, L.d.nc)) src = sell_with_codes(L.d.nc, nzR, L.d.Rp, L.d.Rj, L.d.Rx, &L.sR);
             if (!src && sell_wanted(nzP, L.d.n)) src = sell_with_codes(L.d.n, nzP, L.d.Pp, L.d.Pj, L.d.Px, &L.sP);
@@ -407,7 +420,7 @@ extern "C" int b200amg_vcycle_create(int nlev, const b200amg_level_desc *Ld, con
         // colour-ordered Gauss-Seidel: colour-grouped SELL copy of A when the index list is a permutation
         if (!src && L.d.bs == 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 &&
             L.color_ptr[0] == 0 && L.color_ptr[L.d.K] == L.d.n && L.d.n >= 128)
-            src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sGS, nullptr, L.d.Id);
+            src = sell_build(L.d.n, nzA, L.d.Ap, L.d.Aj, L.d.Ax, &L.sGS, nullptr, L.d.Id, nullptr, nullptr, diag_free_copies());
         // ... and the block form: rows of a colour contiguous (B200AMG_BSR_COLOR_COPY=0: A/B switch)
         if (!src && L.d.bs > 1 && (L.d.pre_kind == 2 || L.d.post_kind == 2) && L.d.K > 0 && L.color_ptr[0] == 0 &&
             L.color_ptr[L.d.K] == L.d.n / L.d.bs && L.d.n / L.d.bs >= 200000) {   // large levels only: no gain on small ones (run 7)
@@ -530,13 +543,14 @@ extern "C" int b200amg_vcycle_residual_norm2(void *handle, const double *x, cons
 // 4 CSR row pointers + 8-bit (offset, value) pattern codes, 5 one row-pattern byte per row,
 // 6 sliced-ELL copy with 8-bit value codes, 7 sliced-ELL copy with 16-bit column steps;
 // 0 = block operator / no such level.  which = 3: the colour-grouped copy of A that colour-ordered Gauss-Seidel
-// sweeps (2 or 7; 0 when the level has none)
+// sweeps (2 or 7; 0 when the level has none); which = 4: the diagonal-free copy of A for the Jacobi sweeps of a big level
 extern "C" int b200amg_vcycle_layout(void *handle, int level, int which)
 {
     Engine *E = reinterpret_cast<Engine *>(handle);
-    if (!E || level < 0 || level >= (int)E->lev.size() || which < 0 || which > 3) return 0;
+    if (!E || level < 0 || level >= (int)E->lev.size() || which < 0 || which > 4) return 0;
     const LevelRt &L = E->lev[level];
     if (which == 3) return L.sGS.ok() ? (L.sGS.cd ? 7 : 2) : 0;
+    if (which == 4) return L.sJ.ok() ? (L.sJ.cd ? 7 : 2) : 0;      // the diagonal-free copy the Jacobi sweeps of a big level stream
     if (which == 0 ? L.d.bs != 1 : (L.d.p_br != 1 || L.d.p_bc != 1)) return 0;
     const Sell &s = which == 0 ? L.sA : which == 1 ? L.sP : L.sR;
     const ValueDict &d = which == 0 ? L.dA : which == 1 ? L.dP : L.dR;

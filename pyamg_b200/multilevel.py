@@ -343,11 +343,11 @@ class multilevel_solver:
         """[{'A': code, 'P': code, 'R': code, 'GS': code} per level below the coarsest]: how the engine streams each
         operator (1 CSR, 2 sliced-ELL, 3 CSR + value codes, 4 CSR rows + pattern codes, 5 row-pattern bytes, 6 sliced-ELL
         + value codes, 7 sliced-ELL + 16-bit column steps, 0 block operator); GS: the colour-grouped copy of A that
-        colour-ordered Gauss-Seidel sweeps (0: none)"""
+        colour-ordered Gauss-Seidel sweeps, J: the diagonal-free copy of A for the Jacobi sweeps of a big level (0: none)"""
         if self._engine is None:
             self._build_engine()
         f = _lib.load().b200amg_vcycle_layout
-        return [{k: int(f(self._engine, lev, w)) for w, k in enumerate(('A', 'P', 'R', 'GS'))} for lev in range(len(self.levels) - 1)]
+        return [{k: int(f(self._engine, lev, w)) for w, k in enumerate(('A', 'P', 'R', 'GS', 'J'))} for lev in range(len(self.levels) - 1)]
 
     def cycle_from_zero(self, b_dev, cycle='V'):
         """x = one cycle from a zero guess for a DEVICE right-hand side: no norms, no host sync, the
