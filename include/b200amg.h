@@ -140,6 +140,8 @@ int b200amg_dense_matvec(int n, const double *M, const double *x, double *y, voi
  *                                                    5  y = jacobi(x)    out of place, amg_core.bsr_jacobi(bs=1) arithmetic
  * Results are bit-identical across layouts.  Used by the row-partitioned multi-GPU cycle
  * (pyamg_b200/distributed.py), where every rank applies LOCAL operators to [owned | halo] vectors. */
+/* (The first Jacobi sweep through a handle over >= 400 000 long rows builds a second copy without the diagonal
+ * entries -- it allocates and synchronises once, never during stream capture; B200AMG_SELL_DIAGFREE=0 disables it.) */
 int b200amg_op_create(int n_row, const int *Ap, const int *Aj, const double *Ax, int layout,
                       void **handle_out, void *stream);
 int b200amg_op_apply(void *handle, int op, const double *x, const double *b, double *y, double omega,

@@ -204,6 +204,8 @@ struct OpHandle {
     ValueDict vd;
     RowPat rp;
     int R = 1, C = 1;                // block shape (b200amg_bsr_op_create); n_row counts BLOCK rows then
+    Sell sellJ;                      // diagonal-free copy for Jacobi on a big long-row operator, built at the first such call
+    bool triedJ = false;
 };
 
 // Block operator behind the same handle: n_brow block rows of R x C blocks (row-major), nnz = stored blocks.  The
@@ -277,6 +279,22 @@ extern "C" int b200amg_op_apply(void *handle, int op, const double *x, const dou
     StreamArgs a{h->Ap, h->Aj, h->Ax, x, b, y, h->nnz, 0, h->n_row, 1.0, 0.0, omega};
     h->vd.apply(a);
     if (h->rp.ok()) return rowpat_op(op, h->rp, a, S(stream));
+    if (h->sell.ok() && op >= OP_JACOBI && !h->sell.cc && h->n_row >= 400000) {
+        // the Jacobi sweeps of a big long-row operator stream a copy without the diagonal entries (vcycle.cu has the
+        // story); built at the first such call outside stream capture (the build allocates and synchronises)
+        if (!h->triedJ) {
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            const char *ev = getenv("B200AMG_SELL_DIAGFREE");
+            if (cudaStreamIsCapturing(S(stream), &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) {
+                h->triedJ = true;
+                if (!(ev && ev[0] == '0')) {
+                    const int rc = sell_build(h->n_row, h->nnz, h->Ap, h->Aj, h->Ax, &h->sellJ, S(stream), nullptr, nullptr, nullptr, true);
+                    if (rc) return rc;
+                }
+            }
+        }
+        if (h->sellJ.ok()) return sell_op(op, h->sellJ, a, S(stream));
+    }
     if (h->sell.ok()) return sell_op(op, h->sell, a, S(stream));
     return stream_op(op, a, S(stream));
 }
@@ -295,6 +313,7 @@ extern "C" int b200amg_op_destroy(void *handle)
     OpHandle *h = reinterpret_cast<OpHandle *>(handle);
     if (!h) return 0;
     sell_free(&h->sell);
+    sell_free(&h->sellJ);
     dict_free(&h->vd);
     rowpat_free(&h->rp);
     delete h;
