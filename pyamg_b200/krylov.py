@@ -14,7 +14,9 @@ from . import _lib
 from .sparse import _ptr
 
 _HIST0 = 16
+_HIST_MAX = 1 << 20
 RECOMPUTE_R = 8
+_ITERATION_GRAPHS = __import__('os').environ.get('B200AMG_PCG_GRAPH', '1') != '0'     # A/B switch
 
 
 def cg(ml, b, x0=None, tol=1e-5, maxiter=None, cycle='V', callback=None, residuals=None, check_every=4):
@@ -42,31 +44,35 @@ def cg(ml, b, x0=None, tol=1e-5, maxiter=None, cycle='V', callback=None, residua
     st.wait_stream(cur)
     with torch.cuda.stream(st):
         s = st.cuda_stream
-        bt = (torch.from_numpy(np.ascontiguousarray(np.ravel(b), np.float64)).to(dev) if as_numpy
-              else b.reshape(-1).to(dev))
-        if bt.numel() != n:
+        # every vector, the right-hand side and the state array live on the solver: the preconditioner's CUDA graph is
+        # keyed by the (z, r) addresses, and one ITERATION is replayed as a CUDA graph of its own (below)
+        # history slots: fixed (the iteration graphs hold the state array's address); a run of more than a million
+        # iterations keeps iterating, its residual list stops growing there
+        cap = min(int(maxiter) + 2, _HIST_MAX)
+        pc = getattr(ml, '_pcg', None)
+        if pc is None or pc['n'] != n:
+            pc = ml._pcg = {'n': n, 'vec': tuple(torch.empty(n, dtype=torch.float64, device=dev) for _ in range(6)),
+                            'state': torch.zeros(_HIST0 + _HIST_MAX, dtype=torch.float64, device=dev), 'graphs': {}}
+        r, z, Ap, p, x, bt = pc['vec']
+        state = pc['state']
+        state.zero_()
+        if (np.size(b) if as_numpy else b.numel()) != n:
             raise ValueError('b has invalid dimensions')
+        bt.copy_(torch.from_numpy(np.ascontiguousarray(np.ravel(b), np.float64)) if as_numpy else b.reshape(-1), non_blocking=True)
         if x0 is None:
-            x = torch.zeros_like(bt)
+            x.zero_()
         elif isinstance(x0, torch.Tensor):
-            x = x0.reshape(-1).to(dev).clone()
+            x.copy_(x0.reshape(-1))
         else:
-            x = torch.from_numpy(np.array(np.ravel(x0), np.float64)).to(dev)
-        # work vectors are kept on the solver: the preconditioner's CUDA graph is keyed by the (z, r) addresses
-        vec = getattr(ml, '_pcg_vecs', None)
-        if vec is None or vec[0].numel() != n:
-            vec = ml._pcg_vecs = tuple(torch.empty(n, dtype=torch.float64, device=dev) for _ in range(4))
-        r, z, Ap, p = vec
-        cap = int(maxiter) + 2
-        state = torch.zeros(_HIST0 + cap, dtype=torch.float64, device=dev)
+            x.copy_(torch.from_numpy(np.array(np.ravel(x0), np.float64)))
         work = ml._keep_dotwork()
         E = ml._engine
 
         def apply_A(op, xin, bin_, out):
             _lib.call('b200amg_vcycle_apply_op', E, 0, op, _ptr(xin), _ptr(bin_) if bin_ is not None else 0, _ptr(out), s)
 
-        def precondition(rin, zout):
-            _lib.call('b200amg_vcycle_run_zero', E, _ptr(zout), _ptr(rin), cyc, 1, s)
+        def precondition(rin, zout, graph=1):
+            _lib.call('b200amg_vcycle_run_zero', E, _ptr(zout), _ptr(rin), cyc, graph, s)
 
         def dot_to(u, v, slot):
             _lib.call('b200amg_dot', n, _ptr(u), _ptr(v), _ptr(state) + 8 * slot, work, s)
@@ -84,7 +90,7 @@ def cg(ml, b, x0=None, tol=1e-5, maxiter=None, cycle='V', callback=None, residua
             residuals[:] = [normr]
         if normb == 0.0:
             normb = 1.0
-        out = lambda: (x.cpu().numpy().reshape(np.shape(b)) if as_numpy else x)   # noqa: E731
+        out = lambda: (x.cpu().numpy().reshape(np.shape(b)) if as_numpy else x.clone())   # noqa: E731
         if normr < tol * normb:
             cur.wait_stream(st)
             return out(), 0
@@ -93,18 +99,39 @@ def cg(ml, b, x0=None, tol=1e-5, maxiter=None, cycle='V', callback=None, residua
         init[0], init[5], init[8], init[9], init[_HIST0] = rz, tol_abs, float(maxiter), float(cap), normr
         state[:_HIST0 + 1].copy_(init.to(dev))
 
-        def enqueue(it):
+        def body(recompute, graph):
             apply_A(0, p, None, Ap)
             dot_to(Ap, p, 1)
             _lib.call('b200amg_pcg_scalars', _ptr(state), 0, s)
-            recompute = not (it % RECOMPUTE_R and it > 0)
             _lib.call('b200amg_pcg_update_xr', n, _ptr(state), _ptr(p), _ptr(Ap), _ptr(x), _ptr(r), 0 if recompute else 1, s)
             if recompute:
                 apply_A(2, x, bt, r)
-            precondition(r, z)
+            precondition(r, z, graph)
             dot_to(r, z, 2)
             _lib.call('b200amg_pcg_scalars', _ptr(state), 1, s)
             _lib.call('b200amg_pcg_update_p', n, _ptr(state), _ptr(z), _ptr(p), s)
+
+        def iteration_graph(recompute):
+            """one whole iteration (about 40 kernels with the cycle) as ONE CUDA graph: a replay costs one launch
+            instead of ten Python-driven ones plus a nested graph launch"""
+            key = (getattr(E, 'value', E), cyc, bool(recompute))       # (a rebuilt engine gets graphs of its own)
+            g = pc['graphs'].get(key)
+            if g is None:
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):    # capture records, it does not execute: no state is touched
+                    body(recompute, 0)                  # the cycle's kernels go straight into this capture
+                pc['graphs'][key] = g
+            return g
+
+        use_graphs = _ITERATION_GRAPHS
+
+        def enqueue(it):
+            recompute = not (it % RECOMPUTE_R and it > 0)
+            if use_graphs:
+                iteration_graph(recompute).replay()
+            else:
+                body(recompute, 1)
 
         step = 1 if callback is not None else max(1, int(check_every))
         enq, seen, flag = 0, 0, 0.0
