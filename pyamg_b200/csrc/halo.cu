@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(32) halo_wait_kernel(const unsigned long long 
 // this rank's epoch on the neighbours and then ALSO waits for theirs (lane i spins on neighbour i's flag cell), so the
 // kernel retires when the halo of this rank is complete.  The push never depends on a peer, so two ranks running this
 // kernel cannot block each other.  One launch per refresh instead of two (13 refreshes per distributed cycle).
+constexpr int HALO_EPT = 4;      // plan entries per thread
 __global__ void __launch_bounds__(256) halo_exchange_kernel(const double *__restrict__ v, int n_send,
                                                             const int *__restrict__ send_idx,
                                                             const int *__restrict__ dst_rank,
@@ -94,11 +95,26 @@ __global__ void __launch_bounds__(256) halo_exchange_kernel(const double *__rest
                                                             unsigned *push_state, unsigned *wait_state, long long max_spins)
 {
     __shared__ int s_last;
-    const int j = blockIdx.x * 256 + threadIdx.x;
-    if (j < n_send) {
-        double *dst = reinterpret_cast<double *>(bases[dst_rank[j]]) + dst_off[j];
-        *dst = v[send_idx[j]];
+    // The refresh sits between two slab kernels 13 times per cycle: it is launched early (programmatic dependent launch,
+    // common.cuh) and resolves its part of the PLAN -- source index, peer base, destination offset: set-up data no
+    // kernel writes -- while the kernel that produces v still runs; only the payload waits for it.
+    pdl_trigger();
+    double *dst[HALO_EPT];
+    int src[HALO_EPT];
+#pragma unroll
+    for (int q = 0; q < HALO_EPT; ++q) {
+        const int j = (blockIdx.x * HALO_EPT + q) * 256 + threadIdx.x;
+        src[q] = -1;
+        dst[q] = nullptr;
+        if (j < n_send) {
+            src[q] = send_idx[j];
+            dst[q] = reinterpret_cast<double *>(bases[dst_rank[j]]) + dst_off[j];
+        }
     }
+    pdl_wait();
+#pragma unroll
+    for (int q = 0; q < HALO_EPT; ++q)
+        if (src[q] >= 0) *dst[q] = v[src[q]];
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
@@ -138,10 +154,13 @@ extern "C" int b200amg_halo_exchange(const double *v, int n_send, const int *sen
                                      unsigned *push_state, unsigned *wait_state, long long max_spins, void *stream)
 {
     if (n_send < 0 || n_nbr < 0 || n_nbr > 32) return set_err(B200AMG_EINVAL, "halo_exchange: bad sizes (0..32 neighbours)");
-    const int grid = n_send > 0 ? (n_send + 255) / 256 : 1;
-    halo_exchange_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(v, n_send, send_idx, dst_rank, dst_off, bases,
-                                                                                   sig_ptrs, flag_ptrs, n_nbr, push_state,
-                                                                                   wait_state, max_spins);
+    const int per_cta = 256 * HALO_EPT;
+    const int grid = n_send > 0 ? (n_send + per_cta - 1) / per_cta : 1;
+    static const bool early = [] { const char *e = getenv("B200AMG_HALO_PDL"); return !(e && e[0] == '0'); }();     // A/B switch
+    const cudaError_t ce = launch_pdl(early, halo_exchange_kernel, dim3(grid), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream),
+                                      v, n_send, send_idx, dst_rank, dst_off, bases, sig_ptrs, flag_ptrs, n_nbr, push_state,
+                                      wait_state, max_spins);
+    if (ce != cudaSuccess) return set_err((int)ce, "halo_exchange_kernel: launch failed");
     return check_launch("halo_exchange_kernel");
 }
 
