@@ -156,7 +156,9 @@ extern "C" int b200amg_halo_exchange(const double *v, int n_send, const int *sen
     if (n_send < 0 || n_nbr < 0 || n_nbr > 32) return set_err(B200AMG_EINVAL, "halo_exchange: bad sizes (0..32 neighbours)");
     const int per_cta = 256 * HALO_EPT;
     const int grid = n_send > 0 ? (n_send + per_cta - 1) / per_cta : 1;
-    static const bool early = [] { const char *e = getenv("B200AMG_HALO_PDL"); return !(e && e[0] == '0'); }();     // A/B switch
+    // B200AMG_HALO_PDL=1 launches the refresh early.  Off by default: measured on 2 B200 it changes nothing inside a cycle
+    // (1.325 vs 1.322 ms) and little back to back (8-11 vs 11-13 us per refresh, tools/halo_microbench.py)
+    static const bool early = [] { const char *e = getenv("B200AMG_HALO_PDL"); return e && e[0] == '1'; }();
     const cudaError_t ce = launch_pdl(early, halo_exchange_kernel, dim3(grid), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream),
                                       v, n_send, send_idx, dst_rank, dst_off, bases, sig_ptrs, flag_ptrs, n_nbr, push_state,
                                       wait_state, max_spins);

@@ -3,8 +3,10 @@
 Preconditioned CG runs on the device WITHOUT the host in the loop: alpha, beta, the curvature checks and the stopping
 test are computed by device kernels from device scalars (b200amg_pcg_*), A p and b - A x run on the engine's layout of
 the finest operator (b200amg_vcycle_apply_op), the preconditioner is one cycle from a zero guess
-(b200amg_vcycle_run_zero, a CUDA-graph replay).  The host enqueues `check_every` iterations ahead and then reads one
-small state array; after convergence the already-enqueued iterations are no-ops, so x is the iterate the reference
+(b200amg_vcycle_run_zero).  One whole ITERATION -- A p, both dots, the scalar kernels, the vector updates and the
+cycle's ~35 kernels -- is captured once as a CUDA graph over vectors and a state array that live on the solver, and
+replayed (B200AMG_PCG_GRAPH=0: ten Python-driven launches per iteration instead).  The host enqueues `check_every`
+iterations ahead and then reads one small state array; after convergence the already-enqueued iterations are no-ops, so x is the iterate the reference
 returns.  Semantics follow _cg.py:109-170: preconditioned norm sqrt(<r, z>), tolerance scaled by the initial one, r
 recomputed as b - A x every 8th iteration, abort on pAp < 0 / rz < 0 / rz == 0."""
 import numpy as np
