@@ -229,6 +229,14 @@ class DistributedSolver:
                 halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC)[3] for p in range(G)]
                 plans = part.build_plans(halos, cs)
                 header[0] = [pl.pack() for pl in plans]
+                if nm == 'P':
+                    # what every rank's x_c looks like, [owned | halo], as indices into the GLOBAL coarse vector (scalars):
+                    # when this is the last partitioned level, rank 0 holds all of x_c after the coarse solve and ships
+                    # slab AND halo in one scatter -- one halo refresh per cycle less
+                    k = torch.arange(bC, dtype=torch.int64, device=halos[0].device)
+                    L.xc_layout = [torch.cat([torch.arange(spc[p], spc[p + 1], dtype=torch.int64, device=halos[p].device),
+                                              (halos[p].to(torch.int64)[:, None] * bC + k[None, :]).reshape(-1)])
+                                   for p in range(G)]
             dist.broadcast_object_list(header, src=0, group=self.group)
             plan = part.HaloPlan.unpack(header[0][rank]).expanded(bC).to(dev)
             if rank == 0:
@@ -447,11 +455,20 @@ class DistributedSolver:
                                input_split_sizes=[L.nc_own] + [0] * (self.G - 1), group=self.group)
 
     def _scatter_coarse(self, L, xc_global):
-        spc = L.csplit
-        sizes = [spc[p + 1] - spc[p] for p in range(self.G)]
-        src = xc_global if self.rank == 0 else torch.empty(0, dtype=torch.float64, device=self.device)
-        dist.all_to_all_single(L.xc[:L.nc_own], src, output_split_sizes=[L.nc_own] + [0] * (self.G - 1),
-                               input_split_sizes=sizes if self.rank == 0 else [0] * self.G, group=self.group)
+        """x_c of the agglomerated levels back to the slabs -- owned part AND halo of every rank ([owned | halo] is the
+        layout of L.xc), so the prolongation needs no refresh of x_c after it"""
+        mine = L.nc_own + L.planP.n_halo
+        if self.rank == 0:
+            if not hasattr(self, '_scat'):
+                idx = torch.cat(L.xc_layout).to(self.device)
+                self._scat = (idx, [int(t.numel()) for t in L.xc_layout],
+                              torch.empty(max(int(idx.numel()), 1), dtype=torch.float64, device=self.device))
+            idx, sizes, buf = self._scat
+            src = torch.index_select(xc_global, 0, idx, out=buf[:idx.numel()])
+        else:
+            sizes, src = [0] * self.G, torch.empty(0, dtype=torch.float64, device=self.device)
+        dist.all_to_all_single(L.xc[:mine], src, output_split_sizes=[mine] + [0] * (self.G - 1),
+                               input_split_sizes=sizes, group=self.group)
 
     # ---- the cycle (multilevel.py:473-548 on slabs) ----------------------------------------------
     def _smooth(self, L, spec, x, xs, b, x_is_zero):
@@ -495,6 +512,7 @@ class DistributedSolver:
         self.exchange(L.planR, L.r)
         L.R.apply(OP_MATVEC, L.r, None, L.bc)
         xc = L.xc
+        scattered_with_halo = False
         if k + 1 < len(self.levels):
             xc, _ = self._cycle(k + 1, L.xc, L.bc, True)          # the iterate may end in the child's spare buffer
         else:
@@ -504,8 +522,10 @@ class DistributedSolver:
             xg = self.coarse.cycle_from_zero(self.cb) if self.rank == 0 else None
             self._mark('coarse_rank0')
             self._scatter_coarse(L, xg)
+            scattered_with_halo = True
             self._mark('scatter')
-        self.exchange(L.planP, xc)
+        if not scattered_with_halo:
+            self.exchange(L.planP, xc)
         L.P.apply(OP_ADD, xc, None, x)
         x, xs = self._smooth(L, L.info['post'], x, xs, b, False)
         return x, xs
