@@ -174,6 +174,7 @@ class DistributedSolver:
         self.halo_mode = halo
         import os
         self._fused_halo = os.environ.get('B200AMG_HALO_FUSED', '1') != '0'    # one kernel node per refresh (A/B switch)
+        self._local_halo_prolong = os.environ.get('B200AMG_HALO_PROLONG', '1') != '0'   # halo of x corrected locally (A/B switch)
         self._p2p = None
         self._graph = None
         self._prof = None
@@ -226,7 +227,12 @@ class DistributedSolver:
             header = [None]
             if rank == 0:
                 Mp, Mj, Mx = src[nm]
-                halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC)[3] for p in range(G)]
+                # P also ships its rows for every rank's A-halo points (extra): after x += P x_c the halo of x is
+                # corrected locally with the same row arithmetic -- the refresh of x before post-smoothing goes away
+                extra = halosA if (nm == 'P' and self._local_halo_prolong) else [None] * G
+                halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC, extra[p])[3] for p in range(G)]
+                if nm == 'A':
+                    halosA = halos
                 plans = part.build_plans(halos, cs)
                 header[0] = [pl.pack() for pl in plans]
                 if nm == 'P':
@@ -239,26 +245,35 @@ class DistributedSolver:
                                    for p in range(G)]
             dist.broadcast_object_list(header, src=0, group=self.group)
             plan = part.HaloPlan.unpack(header[0][rank]).expanded(bC).to(dev)
+            with_halo_rows = nm == 'P' and self._local_halo_prolong
             if rank == 0:
                 mine = None
                 for p in range(G):
-                    ip, ix, dx, _ = part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC)
+                    got = part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC, extra[p])
+                    ops = [got[:3]] + ([got[4]] if with_halo_rows else [])
                     if p == 0:
-                        mine = (ip, ix, dx)
+                        mine = ops
                     else:
-                        sizes = torch.tensor([ip.numel(), ix.numel()], dtype=torch.int64, device=dev)
-                        dist.send(sizes, p, group=self.group)
-                        _send_tensors((ip, ix, dx), p, self.group)
-                    del ip, ix, dx
-                ip, ix, dx = mine
+                        for (ip, ix, dx) in ops:
+                            sizes = torch.tensor([ip.numel(), ix.numel()], dtype=torch.int64, device=dev)
+                            dist.send(sizes, p, group=self.group)
+                            _send_tensors((ip, ix, dx), p, self.group)
+                    del got, ops
+                ops = mine
             else:
-                sizes = torch.empty(2, dtype=torch.int64, device=dev)
-                dist.recv(sizes, 0, group=self.group)
-                n_ip, n_ix = [int(v) for v in sizes.tolist()]
-                ip, ix, dx = _recv_tensors([(n_ip, torch.int32), (n_ix, torch.int32), (n_ix * bR * bC, torch.float64)], 0, dev,
-                                           self.group)
+                ops = []
+                for _ in range(2 if with_halo_rows else 1):
+                    sizes = torch.empty(2, dtype=torch.int64, device=dev)
+                    dist.recv(sizes, 0, group=self.group)
+                    n_ip, n_ix = [int(v) for v in sizes.tolist()]
+                    ops.append(_recv_tensors([(n_ip, torch.int32), (n_ix, torch.int32), (n_ix * bR * bC, torch.float64)], 0, dev,
+                                             self.group))
+            ip, ix, dx = ops[0]
             setattr(L, nm, self.be.make_op(ip, ix, dx, ip.numel() - 1, bR, bC))
             setattr(L, 'plan' + nm, plan)
+            if with_halo_rows:
+                ip, ix, dx = ops[1]
+                L.Ph = self.be.make_op(ip, ix, dx, ip.numel() - 1, bR, bC) if ip.numel() > 1 else None
         L.diag = L.A.diagonal()
         # colour-ordered Gauss-Seidel: the GLOBAL colouring cut by slab -- every rank keeps, colour by colour, the rows of
         # its slab in local numbering (ascending inside a colour like the global list), so a colour step relaxes the
@@ -471,7 +486,7 @@ class DistributedSolver:
                                input_split_sizes=sizes, group=self.group)
 
     # ---- the cycle (multilevel.py:473-548 on slabs) ----------------------------------------------
-    def _smooth(self, L, spec, x, xs, b, x_is_zero):
+    def _smooth(self, L, spec, x, xs, b, x_is_zero, halo_fresh=False):
         kind, omega, iters = spec[:3]
         if kind == 0 or iters == 0:
             if x_is_zero:
@@ -490,7 +505,10 @@ class DistributedSolver:
                         continue
                     for q in range(K):
                         c = K - 1 - q if backward else q
-                        self.exchange(L.planA, x)
+                        if halo_fresh:
+                            halo_fresh = False                    # (the caller has just made the halo of x current)
+                        else:
+                            self.exchange(L.planA, x)
                         self.be.gs_color(L.A, x, b, L.Id, L.cptr[c], L.cptr[c + 1], L.info['flavor'] and not L.info.get('gs_csr', 1), backward)
             return x, xs
         op = OP_JACOBI_BSR1 if L.info['flavor'] else OP_JACOBI
@@ -498,7 +516,10 @@ class DistributedSolver:
             if it == 0 and x_is_zero:
                 self.be.scale_diag(omega, b, L.diag, x, L.info['flavor'])     # bit-identical zero-guess sweep
                 continue
-            self.exchange(L.planA, x)
+            if halo_fresh and it == 0:
+                pass                                              # (the caller has just made the halo of x current)
+            else:
+                self.exchange(L.planA, x)
             L.A.apply(op, x, b, xs, omega)
             x, xs = xs, x
         return x, xs
@@ -527,7 +548,14 @@ class DistributedSolver:
         if not scattered_with_halo:
             self.exchange(L.planP, xc)
         L.P.apply(OP_ADD, xc, None, x)
-        x, xs = self._smooth(L, L.info['post'], x, xs, b, False)
+        fresh = False
+        if self._local_halo_prolong:
+            # the halo of x was refreshed before the residual and nothing has touched x since: the correction of the halo
+            # points is P's rows for them times the same x_c -- what their owners compute, bit for bit
+            if getattr(L, 'Ph', None) is not None:
+                L.Ph.apply(OP_ADD, xc, None, x[L.n_own:])
+            fresh = True
+        x, xs = self._smooth(L, L.info['post'], x, xs, b, False, halo_fresh=fresh)
         return x, xs
 
     def _cycle_eager(self):

@@ -29,20 +29,49 @@ def owner_counts(sorted_cols, split):
     return (pos[1:] - pos[:-1]).tolist()
 
 
-def localize(indptr, indices, data, row0, row1, col0, col1, blockvals=1):
+def gather_rows(indptr, indices, data, rows, blockvals=1):
+    """the rows `rows` (int64 tensor of row numbers, any order) of a CSR/BSR matrix, entries in stored order
+    -> (indptr int64 starting at 0, GLOBAL column indices int64, data)"""
+    rows = rows.to(torch.int64)
+    ptr = indptr.to(torch.int64)
+    starts, lens = ptr[rows], ptr[rows + 1] - ptr[rows]
+    ip = torch.zeros(rows.numel() + 1, dtype=torch.int64, device=indptr.device)
+    if rows.numel():
+        ip[1:] = torch.cumsum(lens, 0)
+    total = int(ip[-1])
+    pos = torch.arange(total, dtype=torch.int64, device=indptr.device)
+    src = pos - torch.repeat_interleave(ip[:-1], lens) + torch.repeat_interleave(starts, lens)
+    vals = data.reshape(-1, blockvals)[src].reshape(-1) if total else data[:0]
+    return ip, indices.to(torch.int64)[src], vals.contiguous().clone()
+
+
+def localize(indptr, indices, data, row0, row1, col0, col1, blockvals=1, extra_rows=None):
     """Rows [row0, row1) of a CSR/BSR matrix with columns renumbered for the rank owning the
     column range [col0, col1).  -> (indptr int32, indices int32, data, halo_cols int64 ascending).
-    For a BSR operator rows / columns count BLOCKS and every stored block carries `blockvals` = R * C values."""
+    For a BSR operator rows / columns count BLOCKS and every stored block carries `blockvals` = R * C values.
+    extra_rows (int64 tensor of row numbers outside the slab): ALSO return those rows as a second operator
+    (indptr, indices, data) in the SAME column numbering -- its columns join the halo list."""
     s, e = int(indptr[row0]), int(indptr[row1])
     ip = (indptr[row0:row1 + 1] - indptr[row0]).to(torch.int32).contiguous()
     cols = indices[s:e].to(torch.int64)
     own = (cols >= col0) & (cols < col1)
-    halo_cols = torch.unique(cols[~own])                       # sorted ascending
-    loc = torch.empty_like(cols)
-    loc[own] = cols[own] - col0
-    if halo_cols.numel():
-        loc[~own] = (col1 - col0) + torch.searchsorted(halo_cols, cols[~own])
-    return ip, loc.to(torch.int32).contiguous(), data[s * blockvals:e * blockvals].contiguous().clone(), halo_cols
+    far = cols[~own]
+    if extra_rows is not None:
+        ip2, cols2, dx2 = gather_rows(indptr, indices, data, extra_rows, blockvals)
+        own2 = (cols2 >= col0) & (cols2 < col1)
+        far = torch.cat([far, cols2[~own2]])
+    halo_cols = torch.unique(far)                              # sorted ascending
+
+    def renumber(c, o):
+        loc = torch.empty_like(c)
+        loc[o] = c[o] - col0
+        if halo_cols.numel():
+            loc[~o] = (col1 - col0) + torch.searchsorted(halo_cols, c[~o])
+        return loc.to(torch.int32).contiguous()
+    out = (ip, renumber(cols, own), data[s * blockvals:e * blockvals].contiguous().clone(), halo_cols)
+    if extra_rows is not None:
+        out = out + ((ip2.to(torch.int32).contiguous(), renumber(cols2, own2), dx2),)
+    return out
 
 
 class HaloPlan:
