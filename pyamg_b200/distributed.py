@@ -222,6 +222,14 @@ class DistributedSolver:
         L.info, L.split, L.csplit = info, sp, spc
         L.n_own, L.nc_own = sp[rank + 1] - sp[rank], spc[rank + 1] - spc[rank]
         shapes = {'A': (spb, spb, bs, bs), 'P': (spb, spcb, bs, bsc), 'R': (spcb, spb, bsc, bs)}
+        # Correcting the halo of x locally after prolongation (instead of refreshing it) is safe only when the post-smoother
+        # does not refresh x IN PLACE: a neighbour that runs ahead would push its next colour's values into this rank's
+        # halo while this rank's own correction (a read-modify-write of the same entries) is still to come.  An
+        # out-of-place sweep (Jacobi: reads x, writes the other buffer; the next push goes to THAT buffer) cannot collide:
+        # every later push into this buffer's halo is ordered behind an exchange this rank takes part in after its
+        # correction.  (The peer-memory protocol has no "halo consumed" signal: it relies on consecutive refreshes
+        # alternating between buffers.)  Without post-smoothing nobody reads the halo of x: nothing to do.
+        local_halo = L.local_halo = bool(self._local_halo_prolong and info['post'][0] == 1 and info['post'][2] >= 1)
         for nm in ('A', 'P', 'R'):
             rs, cs, bR, bC = shapes[nm]
             header = [None]
@@ -229,7 +237,7 @@ class DistributedSolver:
                 Mp, Mj, Mx = src[nm]
                 # P also ships its rows for every rank's A-halo points (extra): after x += P x_c the halo of x is
                 # corrected locally with the same row arithmetic -- the refresh of x before post-smoothing goes away
-                extra = halosA if (nm == 'P' and self._local_halo_prolong) else [None] * G
+                extra = halosA if (nm == 'P' and local_halo) else [None] * G
                 halos = [part.localize(Mp, Mj, Mx, rs[p], rs[p + 1], cs[p], cs[p + 1], bR * bC, extra[p])[3] for p in range(G)]
                 if nm == 'A':
                     halosA = halos
@@ -245,7 +253,7 @@ class DistributedSolver:
                                    for p in range(G)]
             dist.broadcast_object_list(header, src=0, group=self.group)
             plan = part.HaloPlan.unpack(header[0][rank]).expanded(bC).to(dev)
-            with_halo_rows = nm == 'P' and self._local_halo_prolong
+            with_halo_rows = nm == 'P' and local_halo
             if rank == 0:
                 mine = None
                 for p in range(G):
@@ -549,7 +557,7 @@ class DistributedSolver:
             self.exchange(L.planP, xc)
         L.P.apply(OP_ADD, xc, None, x)
         fresh = False
-        if self._local_halo_prolong:
+        if L.local_halo:
             # the halo of x was refreshed before the residual and nothing has touched x since: the correction of the halo
             # points is P's rows for them times the same x_c -- what their owners compute, bit for bit
             if getattr(L, 'Ph', None) is not None:
