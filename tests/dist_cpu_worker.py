@@ -131,10 +131,23 @@ def t3(M):
 
 
 def main():
-    grid, thresh, cycles = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
-    mcgs = len(sys.argv) > 4 and sys.argv[4] in ('mcgs', 'bsr_mcgs')
-    block = len(sys.argv) > 4 and sys.argv[4] in ('bsr_jacobi', 'bsr_mcgs')
+    """argv: one or more scenarios "grid:thresh:cycles[:mode]" run one after the other in the same process group (a
+    torchrun start costs more than a scenario); exit code 0 only if every scenario is bit-identical"""
     dist.init_process_group('gloo')
+    bad = 0
+    for spec in sys.argv[1:]:
+        f = spec.split(':')
+        ok = scenario(int(f[0]), int(f[1]), int(f[2]), f[3] if len(f) > 3 else '')
+        if dist.get_rank() == 0:
+            print('scenario', spec, 'ok' if ok else 'FAILED', flush=True)
+        bad += 0 if ok else 1
+    dist.destroy_process_group()
+    sys.exit(0 if bad == 0 else 1)
+
+
+def scenario(grid, thresh, cycles, mode):
+    mcgs = mode in ('mcgs', 'bsr_mcgs')
+    block = mode in ('bsr_jacobi', 'bsr_mcgs')
     rank = dist.get_rank()
     D = _load('distributed')
     levels_desc, coarse, host, b = None, None, None, None
@@ -204,8 +217,7 @@ def main():
         ok_loc[0] = int(np.array_equal(xg.numpy(), xr) and np.array_equal(x_loc.numpy(), xr[lo:hi]))
     flag = torch.tensor([1 if ok and int(ok_loc.item()) == 1 else 0])
     dist.broadcast(flag, 0)
-    dist.destroy_process_group()
-    sys.exit(0 if int(flag.item()) == 1 else 1)
+    return int(flag.item()) == 1
 
 
 if __name__ == '__main__':
