@@ -11,7 +11,12 @@
 // values.  Rows keep their storage order, so every row sum is folded exactly as the reference
 // does it (scipy csr_matvec / amg_core jacobi, pyamg/amg_core/relaxation.h:201-239): the bits
 // are those of the CSR kernels.  Cost: the copy (engine-owned, built once per level) and
-// 19-23 % padding traffic; no shared memory, no barriers, 8 independent loads in flight per lane.
+// 7-10 % padding traffic (ncu, profiles/r02); no shared memory, no barriers.
+//
+// Round 2 added, all as exact re-encodings of the same ordered sums: 16-bit column steps with escape slots for big
+// sorted copies (10 instead of 12 bytes per slot), copies WITHOUT the diagonal entries for the smoothers (the sweep never
+// adds them; no per-slot diagonal test), few-row forms whose loads of a round are forced in flight (ptxas otherwise
+// sinks each load next to its use), and the early launch of the small colour sweeps (common.cuh).
 #include <type_traits>
 #include "internal.cuh"
 #include "setup.cuh"
