@@ -450,11 +450,12 @@ static bool bsr_warp_kernels()
     return on;
 }
 
-// B200AMG_BSR_WARP_BATCH=0: one pass per round of loads, as in the first version (A/B switch)
-static bool bsr_warp_batch()
+// B200AMG_BSR_WARP_BATCH (A/B switch): 0 one pass per round of loads, as in the first version; 2 batches only for
+// sub-wave colours; 1 (default) batches of two passes for the larger colours as well
+static int bsr_warp_batch()
 {
-    static const bool on = [] { const char *e = getenv("B200AMG_BSR_WARP_BATCH"); return !(e && e[0] == '0'); }();
-    return on;
+    static const int mode = [] { const char *e = getenv("B200AMG_BSR_WARP_BATCH"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }();
+    return mode;
 }
 
 // nblocks: stored blocks of the operator (< 0: unknown) -- rows with at least half a pass of blocks on average go to
@@ -502,6 +503,11 @@ int bsr_gs_color(int bs, const int *Ap, const int *Aj, const double *Ax, double 
         if (bsr_warp_batch() && p1 - p0 <= kSMs * 8) {
             if (backward) { if (perm) { GS_WARP(true, true, 4); } else { GS_WARP(true, false, 4); } }
             else { if (perm) { GS_WARP(false, true, 4); } else { GS_WARP(false, false, 4); } }
+        } else if (bsr_warp_batch() == 1) {
+            // a full wave of warps: batches of two passes (about 80 registers) halve the rounds of latency per row
+            // without giving up as many resident warps as batches of four
+            if (backward) { if (perm) { GS_WARP(true, true, 2); } else { GS_WARP(true, false, 2); } }
+            else { if (perm) { GS_WARP(false, true, 2); } else { GS_WARP(false, false, 2); } }
         } else {
             if (backward) { if (perm) { GS_WARP(true, true, 1); } else { GS_WARP(true, false, 1); } }
             else { if (perm) { GS_WARP(false, true, 1); } else { GS_WARP(false, false, 1); } }
