@@ -450,11 +450,13 @@ static bool bsr_warp_kernels()
     return on;
 }
 
-// B200AMG_BSR_WARP_BATCH (A/B switch): 0 one pass per round of loads, as in the first version; 2 batches only for
-// sub-wave colours; 1 (default) batches of two passes for the larger colours as well
+// B200AMG_BSR_WARP_BATCH (A/B switch): 0 one pass per round of loads, as in the first version; 2 (default) batches only
+// for sub-wave colours; 1 batches of two passes for the larger colours as well -- measured SLOWER on config 4 level 1
+// (6 600 rows per colour: 0.674 vs 0.610 ms per smoothing step, profiles/r02/run35_summary.txt): 70 registers instead
+// of 50 cost more resident warps than the halved rounds of latency give back
 static int bsr_warp_batch()
 {
-    static const int mode = [] { const char *e = getenv("B200AMG_BSR_WARP_BATCH"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }();
+    static const int mode = [] { const char *e = getenv("B200AMG_BSR_WARP_BATCH"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2; }();
     return mode;
 }
 
