@@ -193,7 +193,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         int got[2] = {0, 0};
         e = cudaMemsetAsync(flag, 0, 2 * sizeof(int), st);
         if (e == cudaSuccess) {
-            sell_steps_check_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, drop_diag, flag);
+            B200_LAUNCH(sell_steps_check_kernel, (n + 255) / 256, 256, 0, st, n, Ap, Aj, drop_diag, flag);
             rc = check_launch("sell_steps_check_kernel");
         }
         if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(got, flag, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
@@ -201,7 +201,7 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         if (got[0] || (long long)got[1] * 32 > nnz) steps = false;
     }
     if (e == cudaSuccess && !rc) {
-        sell_width_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, perm, drop_diag, steps, width, s.row_len);
+        B200_LAUNCH(sell_width_kernel, (n + 255) / 256, 256, 0, st, n, Ap, Aj, perm, drop_diag, steps, width, s.row_len);
         rc = check_launch("sell_width_kernel");
         if (!rc) rc = exclusive_scan<long long, long long>(ns, width, s.slice_off, scratch, st);
         if (!rc) {
@@ -223,8 +223,8 @@ int sell_build(int n, long long nnz, const int *Ap, const int *Aj, const double 
         if (e == cudaSuccess && coded) e = cudaMalloc(&s.dict, sizeof(double) * 256);
         if (e == cudaSuccess && coded) e = cudaMemcpyAsync(s.dict, dict, sizeof(double) * 256, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess) {
-            sell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc, s.cd,
-                                                              s.first, s.dg);
+            B200_LAUNCH(sell_fill_kernel, (n + 255) / 256, 256, 0, st, n, Ap, Aj, Ax, perm, s.slice_off, s.cj, s.cv, codes, s.cc,
+                        s.cd, s.first, s.dg);
             rc = check_launch("sell_fill_kernel");
             // the apply kernels request slots of this copy BEFORE they wait for their predecessor in the stream
             // (programmatic dependent launch): the copy must be complete when the build returns
@@ -514,14 +514,13 @@ static int launch_sell_gs(const Sell &s, const int *Id, int p0, int p1, double *
     const void *cols = s.cd ? (const void *)s.cd : (const void *)s.cj;
     const int *firstp = s.cd ? s.first : nullptr;
 #define SELL_GS_ONE(EARLY, UU, TPB, ST, DFV)                                                                                     \
-    launch_pdl(EARLY, sell_gs_kernel<BSRF, UU, ST, DFV>, g, blk, 0, st, p0, p1, (const long long *)s.slice_off, cols,          \
-               (const double *)s.cv, firstp, (const int *)s.row_len, Id, (const double *)s.dg, x, b, 0)
+    B200_LAUNCH_PDL(EARLY, (sell_gs_kernel<BSRF, UU, ST, DFV>), (unsigned)((rows + TPB - 1) / TPB), TPB, 0, st, p0, p1,          \
+                    (const long long *)s.slice_off, cols, (const double *)s.cv, firstp, (const int *)s.row_len, Id,             \
+                    (const double *)s.dg, x, b, 0)
 #define SELL_GS_LAUNCH(EARLY, UU, TPB)                                                                                           \
     do {                                                                                                                         \
-        const dim3 g((unsigned)((rows + TPB - 1) / TPB)), blk(TPB);                                                              \
-        cudaError_t e = s.cd ? (s.dg ? SELL_GS_ONE(EARLY, UU, TPB, true, true) : SELL_GS_ONE(EARLY, UU, TPB, true, false))       \
-                             : (s.dg ? SELL_GS_ONE(EARLY, UU, TPB, false, true) : SELL_GS_ONE(EARLY, UU, TPB, false, false));    \
-        if (e != cudaSuccess) return set_err((int)e, "sell_gs_kernel: launch failed");                                           \
+        if (s.cd) { if (s.dg) SELL_GS_ONE(EARLY, UU, TPB, true, true); else SELL_GS_ONE(EARLY, UU, TPB, true, false); }          \
+        else { if (s.dg) SELL_GS_ONE(EARLY, UU, TPB, false, true); else SELL_GS_ONE(EARLY, UU, TPB, false, false); }             \
     } while (0)
     if (U == 32) SELL_GS_LAUNCH(pdl_class(PDL_SWEEP), 32, 64);
     else SELL_GS_LAUNCH(false, 8, SELL_TPB);
@@ -549,10 +548,10 @@ static int launch_sell(const Sell &s, const StreamArgs &a, cudaStream_t st)
     const int grid = (s.n + SELL_TPB - 1) / SELL_TPB;
     const double *nodg = nullptr;
     if (s.dg) {
-        // a copy without diagonal entries: smoothing ops only, big operators only (the engine builds it next to the
-        // full copy for levels of >= SELL_BIG_ROWS rows)
+        // a copy without diagonal entries: smoothing ops only (the engine builds it next to the full copy for levels of
+        // >= SELL_BIG_ROWS rows; any size works)
         if constexpr (OP >= OP_JACOBI) {
-            if (s.cc || s.n < SELL_BIG_ROWS) return set_err(B200AMG_ESTATE, "sell_op: diagonal-free copy of a small or coded operator");
+            if (s.cc) return set_err(B200AMG_ESTATE, "sell_op: diagonal-free copy of a coded operator");
             if (s.cd)
                 B200_LAUNCH_PDL(false, (sell_kernel<OP, SELL_U, false, 2, false, true>), grid, SELL_TPB, 0, st, s.n, s.slice_off, s.cd, s.cv, nullptr, s.first, s.row_len, s.dg, a);
             else

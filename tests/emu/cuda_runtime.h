@@ -2,7 +2,8 @@
 // (pyamg_b200/csrc/*.cu, unchanged) for the HOST, so that thread-per-row / warp-per-row kernels can be checked
 // against scipy in this GPU-less container before they ever see hardware (tests/test_emulated_kernels.py).
 // Every CUDA thread of a block is a real OS thread; __syncthreads / __syncwarp are barriers; blocks run one after
-// the other.  Supports what the emulated kernels use: barriers, full-warp __shfl_sync / __all_sync / __ballot_sync, __ldg, int4 / double2 loads;
+// the other.  Supports what the emulated kernels use: barriers, full-warp __shfl_sync / __shfl_xor_sync / __all_sync / __any_sync /
+// __ballot_sync, __ldg / __ldcs / __ldcg, int atomicAdd, cudaMalloc / cudaFree / cudaMemcpyAsync as host calls, int4 / double2 loads;
 // dynamic shared memory only as a global array the test provides; no static shared memory, no atomics.  The product never
 // loads anything built from this header (pyamg_b200 needs CUDA tensors and raises without a device).
 #pragma once
@@ -37,6 +38,12 @@ enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount = 16 };
 inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
 inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 2; return cudaSuccess; }   // a 2-SM "device"
 inline cudaError_t cudaMemsetAsync(void *p, int v, size_t n, cudaStream_t) { memset(p, v, n); return cudaSuccess; }
+// "device" memory is host memory here (layout builders such as sell_build allocate their copies)
+template <class T> inline cudaError_t cudaMalloc(T **p, size_t n) { *p = static_cast<T *>(malloc(n ? n : 1)); return *p ? cudaSuccess : 2; }
+inline cudaError_t cudaFree(void *p) { free(p); return cudaSuccess; }
+enum cudaMemcpyKind { cudaMemcpyHostToHost, cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice };
+inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind, cudaStream_t) { memcpy(d, s, n); return cudaSuccess; }
+inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 
 #define __global__
 #define __device__
@@ -138,6 +145,15 @@ inline unsigned __ballot_sync(unsigned, int pred)
     return m;
 }
 template <class T> inline T __ldg(const T *p) { return *p; }
+template <class T> inline T __ldcs(const T *p) { return *p; }
+template <class T> inline T __ldcg(const T *p) { return *p; }
+template <class T>
+inline T __shfl_xor_sync(unsigned m, T v, int lane_mask, int width = 32)
+{
+    return __shfl_sync(m, v, (int)((threadIdx.x % 32) ^ (unsigned)lane_mask), width);
+}
+inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0u; }
+inline int atomicAdd(int *p, int v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
 inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }

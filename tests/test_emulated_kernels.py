@@ -735,3 +735,119 @@ def test_bsr_warp_gauss_seidel_long_rows(emu_bsr, bs, nb, density):
     y = np.full(nb * bs, np.nan)
     assert emu_bsr.emu_bsr_matvec_warp(nb, bs, bs, P(Ap), P(Aj), P(Ax), P(x0), P(b), P(y), 1) == 0
     assert np.array_equal(y, b - A * x0)
+
+
+# ---- the sliced-ELL layout (csrc/sell.cu): copies with 32-bit columns / 16-bit column steps / without diagonal entries ---
+@pytest.fixture(scope='module')
+def emu_sell():
+    if shutil.which('g++') is None:
+        pytest.skip('g++ not available')
+    csrc = os.path.join(ROOT, 'pyamg_b200', 'csrc')
+    srcs = [os.path.join(csrc, 'sell.cu'), os.path.join(EMU, 'emu_sell_api.cpp'), os.path.join(EMU, 'emu_globals.cpp')]
+    out = os.path.join(EMU, '_build', 'libemu_sell.so')
+    deps = srcs + [os.path.join(EMU, 'cuda_runtime.h'), os.path.join(csrc, 'internal.cuh'), os.path.join(csrc, 'common.cuh'),
+                   os.path.join(csrc, 'setup.cuh')]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU, '-I', csrc,
+                        '-x', 'c++'] + srcs + ['-o', out], check=True)
+    lib = ctypes.CDLL(out)
+    ip = ctypes.POINTER(c_int)
+    lib.emu_sell_apply.restype = c_int
+    lib.emu_sell_apply.argtypes = [c_int, ctypes.c_longlong, vp, vp, vp, c_int, c_int, vp, vp, vp, c_dbl, ip, ip]
+    lib.emu_sell_gs.restype = c_int
+    lib.emu_sell_gs.argtypes = [c_int, ctypes.c_longlong, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, vp, vp, ip]
+    return lib
+
+
+def _long_row_matrix(n, ncols, per_row, span, seed, square_diag=True):
+    rng = np.random.RandomState(seed)
+    rows = np.repeat(np.arange(n), per_row)
+    cols = (rows * (ncols // n) + rng.randint(-span, span, rows.size)) % ncols
+    A = sp.csr_matrix((rng.rand(rows.size) - 0.3, (rows, cols)), shape=(n, ncols))       # duplicates summed: ragged rows
+    if square_diag:
+        A = sp.csr_matrix(A + sp.diags(rng.rand(n) + 1.0 + per_row))
+    A.sort_indices()
+    return A, rng
+
+
+@pytest.mark.parametrize('steps', [False, True])
+@pytest.mark.parametrize('drop_diag', [False, True])
+def test_sliced_ell_ops_on_the_host(emu_sell, monkeypatch, steps, drop_diag):
+    """sell_build + sell_kernel compiled for the host: y = A x, b - A x, y + A x and both Jacobi forms from copies with
+    32-bit columns or 16-bit column steps, with or without the diagonal entries, against scipy's csr_matvec and the
+    reference's jacobi / bsr_jacobi loops (oracle port): same bits.  Rows without a diagonal entry, a row that holds ONLY
+    its diagonal and an empty row included."""
+    monkeypatch.setenv('B200AMG_SELL_COL16', '2' if steps else '0')
+    n = 900
+    A, rng = _long_row_matrix(n, n, 40, 120, 5 + steps)
+    A = A.tolil()
+    A[11, 11] = 0.0                                         # no diagonal entry
+    A[12, :] = 0.0; A[12, 12] = 3.0                         # only the diagonal
+    A[13, :] = 0.0                                          # empty row
+    A = sp.csr_matrix(A); A.eliminate_zeros(); A.sort_indices()
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), A.data.copy()
+    x, b = rng.rand(n), rng.rand(n)
+    lay, esc = c_int(0), c_int(0)
+    core = oracle.port
+    Axv = np.zeros(n); core.csr_matvec(n, n, Ap, Aj, Ax, x, Axv)
+    ops = ([] if drop_diag else [(0, np.zeros(n), Axv), (2, np.zeros(n), b - Axv), (3, b.copy(), b + Axv)])
+    xo = x.copy(); core.jacobi(Ap, Aj, Ax, xo, b, np.empty(n), 0, n, 1, np.array([0.7]))
+    xb = x.copy(); core.bsr_jacobi(Ap, Aj, Ax, xb, b, np.empty(n), 0, n, 1, 1, np.array([0.7]))
+    ops += [(4, np.zeros(n), xo), (5, np.zeros(n), xb)]
+    for op, y0, want in ops:
+        y = y0.copy()
+        bb = y if op == 3 else b
+        assert emu_sell.emu_sell_apply(n, len(Ax), P(Ap), P(Aj), P(Ax), int(drop_diag), op, P(x), P(bb), P(y), 0.7,
+                                       ctypes.byref(lay), ctypes.byref(esc)) == 0
+        assert lay.value == (7 if steps else 2)
+        assert np.array_equal(y, want), op
+
+
+def test_sliced_ell_escape_slots_on_the_host(emu_sell, monkeypatch):
+    """16-bit column steps of 65 535 columns or more take escape slots: a 300 x 200 000 operator with 14 entries per row
+    (a few steps that wide per hundred rows) keeps layout 7 and the bits of csr_matvec; with 4 entries per row most steps
+    are that wide and the copy keeps 32-bit columns"""
+    monkeypatch.setenv('B200AMG_SELL_COL16', '2')
+    lay, esc = c_int(0), c_int(0)
+    for per_row, want_layout in ((14, 7), (4, 2)):
+        A, rng = _long_row_matrix(300, 200000, per_row, 100000, 9, square_diag=False)
+        Ap, Aj, Ax = i32(A.indptr), i32(A.indices), A.data.copy()
+        st = np.diff(A.indices.astype(np.int64))
+        inside = np.ones(len(st), bool); inside[A.indptr[1:-1] - 1] = False
+        assert np.count_nonzero(st[inside] >= 65535) > 0
+        x = rng.rand(200000)
+        want = np.zeros(300); oracle.port.csr_matvec(300, 200000, Ap, Aj, Ax, x, want)
+        y = np.full(300, np.nan)
+        assert emu_sell.emu_sell_apply(300, len(Ax), P(Ap), P(Aj), P(Ax), 0, 0, P(x), None, P(y), 0.0, ctypes.byref(lay),
+                                       ctypes.byref(esc)) == 0
+        assert lay.value == want_layout and (esc.value > 0) == (want_layout == 7)
+        assert np.array_equal(y, want)
+
+
+@pytest.mark.parametrize('bsrf', [False, True])
+@pytest.mark.parametrize('steps,drop_diag', [(False, False), (True, True), (False, True)])
+def test_sliced_ell_colour_sweeps_on_the_host(emu_sell, monkeypatch, bsrf, steps, drop_diag):
+    """sell_gs_kernel on a colour-grouped copy (32-slot rounds with tied loads, with / without diagonal entries among the
+    slots, 32-bit columns / 16-bit steps) against the reference's sequential gauss_seidel_indexed / bsr_gauss_seidel over
+    the same MIS colour ordering, forward then backward"""
+    from oracle import relaxation as orx
+    monkeypatch.setenv('B200AMG_SELL_COL16', '2' if steps else '0')
+    n = 700
+    A, rng = _long_row_matrix(n, n, 9, 40, 21)
+    A = sp.csr_matrix(A + A.T); A.sort_indices()
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), A.data.copy()
+    idx, ptr = orx.color_ordering(orx.vertex_coloring_mis(A, oracle.port))
+    idx, ptr = i32(idx), i32(ptr)
+    b, x0 = rng.rand(n), rng.rand(n)
+    want = x0.copy()
+    for (r0, r1, dr) in ((0, n, 1), (n - 1, -1, -1)):
+        if bsrf:
+            oracle.port.bsr_gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, r0, r1, dr, 1)
+        else:
+            oracle.port.gauss_seidel_indexed(Ap, Aj, Ax, want, b, idx, r0, r1, dr)
+    got, lay = x0.copy(), c_int(0)
+    assert emu_sell.emu_sell_gs(n, len(Ax), P(Ap), P(Aj), P(Ax), P(idx), P(ptr), len(ptr) - 1, int(bsrf), int(drop_diag), 2,
+                                P(got), P(b), ctypes.byref(lay)) == 0
+    assert lay.value == (7 if steps else 2)
+    assert np.array_equal(got, want)
