@@ -299,19 +299,28 @@ extern "C" int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, c
     B200_TRY(bin_rows(n_row, ub, lim, perm, work, off, st));
 #define ARGS(b) perm + off[b], off[b + 1] - off[b], Ap, Aj, Ax, Bp, Bj, Bx, ubp
     int n;
-    if ((n = off[1] - off[0]) > 0) {
+    // rows of up to 512 (2048) products in scipy's order can go without a sort (spgemm_hash.cu, B200AMG_SPGEMM_HASH)
+    const int hash_mode = so ? spgemm_hash_mode() : 0;
+    bool hashed[4] = {false, false, false, false};
+    for (int b = 0; b < 4 && hash_mode > 0; ++b) {
+        if ((n = off[b + 1] - off[b]) <= 0) continue;
+        const int took = spgemm_hash_bin(b, hash_mode, ARGS(b), Tj, Tx, cnt, st);
+        if (took < 0) return took;
+        hashed[b] = took > 0;
+    }
+    if (!hashed[0] && (n = off[1] - off[0]) > 0) {
         spgemm_warp_kernel<32, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(0), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_warp_kernel<32>"));
     }
-    if ((n = off[2] - off[1]) > 0) {
+    if (!hashed[1] && (n = off[2] - off[1]) > 0) {
         spgemm_warp_kernel<128, 8><<<(n + 7) / 8, 256, 0, st>>>(ARGS(1), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_warp_kernel<128>"));
     }
-    if ((n = off[3] - off[2]) > 0) {
+    if (!hashed[2] && (n = off[3] - off[2]) > 0) {
         spgemm_cta_kernel<512><<<n, 128, 512 * 16, st>>>(ARGS(2), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<512>"));
     }
-    if ((n = off[4] - off[3]) > 0) {
+    if (!hashed[3] && (n = off[4] - off[3]) > 0) {
         spgemm_cta_kernel<2048><<<n, 256, 2048 * 16, st>>>(ARGS(3), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<2048>"));
     }

@@ -153,7 +153,34 @@ inline T __shfl_xor_sync(unsigned m, T v, int lane_mask, int width = 32)
     return __shfl_sync(m, v, (int)((threadIdx.x % 32) ^ (unsigned)lane_mask), width);
 }
 inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0u; }
+template <class T>
+inline T __shfl_up_sync(unsigned m, T v, unsigned delta, int width = 32)
+{
+    const unsigned lane = threadIdx.x % 32;
+    const T got = __shfl_sync(m, v, (int)(lane >= delta ? lane - delta : lane), width);
+    return lane % (unsigned)width >= delta ? got : v;
+}
+// lanes of the calling thread's warp that hold the same 32-bit value
+inline unsigned __match_any_sync(unsigned, int v)
+{
+    cuda_emu::BlockSync *s = cuda_emu::cur;
+    const unsigned tid = threadIdx.x, w = tid / 32;
+    s->slots[tid] = (unsigned long long)(unsigned)v;
+    s->warp[w]->arrive_and_wait();
+    const unsigned lanes = std::min(32u, blockDim.x - 32 * w);
+    unsigned m = 0;
+    for (unsigned l = 0; l < lanes; ++l) m |= (unsigned)(s->slots[w * 32 + l] == (unsigned long long)(unsigned)v) << l;
+    s->warp[w]->arrive_and_wait();
+    return m;
+}
+inline int __popc(unsigned v) { return __builtin_popcount(v); }
+inline int __ffs(int v) { return __builtin_ffs(v); }
 inline int atomicAdd(int *p, int v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+inline int atomicCAS(int *p, int expected, int desired)
+{
+    __atomic_compare_exchange_n(p, &expected, desired, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+    return expected;                                         // (the value found, like the device's)
+}
 inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }

@@ -851,3 +851,111 @@ def test_sliced_ell_colour_sweeps_on_the_host(emu_sell, monkeypatch, bsrf, steps
                                 P(got), P(b), ctypes.byref(lay)) == 0
     assert lay.value == (7 if steps else 2)
     assert np.array_equal(got, want)
+
+
+# ---- Galerkin-product rows without a sort (csrc/spgemm_hash.cu) --------------------------------------------------------
+@pytest.fixture(scope='module')
+def emu_spgemm():
+    if shutil.which('g++') is None:
+        pytest.skip('g++ not available')
+    csrc = os.path.join(ROOT, 'pyamg_b200', 'csrc')
+    srcs = [os.path.join(csrc, 'spgemm_hash.cu'), os.path.join(EMU, 'emu_spgemm_api.cpp'), os.path.join(EMU, 'emu_globals.cpp')]
+    out = os.path.join(EMU, '_build', 'libemu_spgemm.so')
+    deps = srcs + [os.path.join(EMU, 'cuda_runtime.h'), os.path.join(csrc, 'internal.cuh'), os.path.join(csrc, 'common.cuh'),
+                   os.path.join(csrc, 'setup.cuh')]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run(['g++', '-std=c++20', '-O1', '-ffp-contract=off', '-fPIC', '-shared', '-pthread', '-I', EMU, '-I', csrc,
+                        '-x', 'c++'] + srcs + ['-o', out], check=True)
+    lib = ctypes.CDLL(out)
+    lib.emu_spgemm_hash_bin.restype = c_int
+    lib.emu_spgemm_hash_bin.argtypes = [c_int, c_int, vp, c_int] + [vp] * 10
+    return lib
+
+
+def _sort_free_product(lib, A, B, mode):
+    """C = A B through spgemm_hash_bin the way b200amg_spgemm_numeric drives it: rows binned by their number of products
+    (32 / 128 / 512 / 2048), one call per bin.  -> (indptr, indices, data) in the kernel's output order, bins it took"""
+    Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ascontiguousarray(A.data, np.float64)
+    Bp, Bj, Bx = i32(B.indptr), i32(B.indices), np.ascontiguousarray(B.data, np.float64)
+    n = A.shape[0]
+    blen = np.diff(Bp).astype(np.int64)
+    ub = np.array([blen[Aj[Ap[i]:Ap[i + 1]]].sum() for i in range(n)], dtype=np.int64)
+    ubp = np.concatenate([[0], np.cumsum(ub)]).astype(np.int64)
+    Tj = np.full(max(int(ubp[-1]), 1), -7, dtype=np.int32)
+    Tx = np.full(max(int(ubp[-1]), 1), np.nan)
+    cnt = np.zeros(max(n, 1), dtype=np.int32)
+    limits = [0, 32, 128, 512, 2048]
+    took = []
+    cnt[:n][ub > limits[-1]] = -1                               # rows beyond the last bin stay with the sorting kernels
+    for b in range(4):
+        rows = i32(np.nonzero((ub > limits[b]) & (ub <= limits[b + 1]))[0][::-1])        # (any order inside a bin)
+        if rows.size == 0:
+            continue
+        rc = lib.emu_spgemm_hash_bin(b, mode, P(rows), rows.size, P(Ap), P(Aj), P(Ax), P(Bp), P(Bj), P(Bx), P(ubp), P(Tj), P(Tx),
+                                     P(cnt))
+        assert rc in (0, 1)
+        if rc == 1:
+            took.append(b)
+        else:
+            cnt[rows] = -1
+    return ubp, Tj, Tx, cnt, took
+
+
+@pytest.mark.parametrize('case', ['stencil_RA', 'random_wide', 'cancelling', 'unsorted_operands', 'up_to_2048'])
+def test_sort_free_galerkin_rows_on_the_host(emu_spgemm, case):
+    """every row of C = A B equals scipy's csr_matmat row: the same columns IN THE SAME (reverse first touch) ORDER, the
+    same bits, exact zeros dropped -- for tentative-prolongator-like operands, wide random rows (probe chains, groups of
+    equal columns inside a 32-product step), sums that cancel to 0.0, operands with unsorted rows and duplicate entries"""
+    rng = np.random.RandomState(5)
+    mode = 1
+    if case == 'stencil_RA':
+        d1 = lambda k: sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(k, k))           # noqa: E731
+        eye = sp.identity
+        A = sp.csr_matrix(sp.kron(sp.kron(d1(12), eye(11)), eye(10)) + sp.kron(sp.kron(eye(12), d1(11)), eye(10))
+                          + sp.kron(sp.kron(eye(12), eye(11)), d1(10)))
+        A.sort_indices()
+        agg = (np.arange(A.shape[0]) // 27).astype(np.int32)
+        T = sp.csr_matrix((rng.rand(A.shape[0]) + 0.5, (np.arange(A.shape[0]), agg)))
+        L, R_ = sp.csr_matrix(T.T), A
+        L.sort_indices()
+    elif case == 'random_wide':
+        L = sp.random(60, 300, 0.12, random_state=rng, format='csr')
+        R_ = sp.random(300, 90, 0.08, random_state=rng, format='csr')
+    elif case == 'cancelling':
+        # rows whose products cancel exactly: column j gets +v and -v (dropped, scipy drops it too), and -0.0 sums
+        L = sp.csr_matrix(np.array([[1.0, 1.0, 0.0], [2.0, 0.0, 3.0], [0.0, 0.0, 0.0], [1.0, -1.0, 1.0]]))
+        R_ = sp.csr_matrix(np.array([[4.0, -2.5, 0.0, 1.0], [-4.0, 2.5, 7.0, 0.0], [0.0, 5.0, 0.0, -1.0]]))
+    elif case == 'unsorted_operands':
+        L = sp.random(50, 80, 0.3, random_state=rng, format='csr')
+        R_ = sp.random(80, 70, 0.2, random_state=rng, format='csr')
+        for M in (L, R_):                                                  # shuffle every row's storage order
+            for i in range(M.shape[0]):
+                s, e = M.indptr[i], M.indptr[i + 1]
+                q = rng.permutation(e - s)
+                M.indices[s:e], M.data[s:e] = M.indices[s:e][q], M.data[s:e][q]
+        # duplicate entries inside rows of the left operand (non-canonical CSR)
+        L = sp.csr_matrix((np.concatenate([L.data, L.data[:40]]), np.concatenate([L.indices, L.indices[:40]]),
+                           np.concatenate([L.indptr[:-1], [L.indptr[-1] + 40]])), shape=L.shape)
+    else:
+        mode = 2
+        L = sp.random(12, 400, 0.3, random_state=rng, format='csr')
+        R_ = sp.random(400, 1500, 0.01, random_state=rng, format='csr')
+    ubp, Tj, Tx, cnt, took = _sort_free_product(emu_spgemm, L, R_, mode)
+    import scipy.sparse._sparsetools as st
+    n, nc = L.shape[0], R_.shape[1]
+    cap = st.csr_matmat_maxnnz(n, nc, i32(L.indptr), i32(L.indices), i32(R_.indptr), i32(R_.indices))
+    Cp, Cj, Cx = np.zeros(n + 1, np.int32), np.zeros(max(cap, 1), np.int32), np.zeros(max(cap, 1))
+    st.csr_matmat(n, nc, i32(L.indptr), i32(L.indices), np.ascontiguousarray(L.data, np.float64), i32(R_.indptr), i32(R_.indices),
+                  np.ascontiguousarray(R_.data, np.float64), Cp, Cj, Cx)
+    assert took and (mode == 1 or 3 in took)
+    checked = 0
+    for i in range(n):
+        if cnt[i] < 0:
+            continue
+        o = int(ubp[i])
+        assert cnt[i] == Cp[i + 1] - Cp[i], i
+        assert np.array_equal(Tj[o:o + cnt[i]], Cj[Cp[i]:Cp[i + 1]]), i
+        assert np.array_equal(Tx[o:o + cnt[i]], Cx[Cp[i]:Cp[i + 1]]), i
+        checked += 1
+    assert checked >= n - 2 or case == 'up_to_2048'
