@@ -299,10 +299,10 @@ extern "C" int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, c
     B200_TRY(bin_rows(n_row, ub, lim, perm, work, off, st));
 #define ARGS(b) perm + off[b], off[b + 1] - off[b], Ap, Aj, Ax, Bp, Bj, Bx, ubp
     int n;
-    // rows of up to 512 (2048) products in scipy's order can go without a sort (spgemm_hash.cu, B200AMG_SPGEMM_HASH)
+    // rows of up to 512 (2048, 8192) products in scipy's order can go without a sort (spgemm_hash.cu, B200AMG_SPGEMM_HASH)
     const int hash_mode = so ? spgemm_hash_mode() : 0;
-    bool hashed[4] = {false, false, false, false};
-    for (int b = 0; b < 4 && hash_mode > 0; ++b) {
+    bool hashed[5] = {false, false, false, false, false};
+    for (int b = 0; b < 5 && hash_mode > 0; ++b) {
         if ((n = off[b + 1] - off[b]) <= 0) continue;
         const int took = spgemm_hash_bin(b, hash_mode, ARGS(b), Tj, Tx, cnt, st);
         if (took < 0) return took;
@@ -324,7 +324,7 @@ extern "C" int b200amg_spgemm_numeric(int n_row, const int *Ap, const int *Aj, c
         spgemm_cta_kernel<2048><<<n, 256, 2048 * 16, st>>>(ARGS(3), Tj, Tx, cnt, so);
         B200_TRY(check_launch("spgemm_cta_kernel<2048>"));
     }
-    if ((n = off[5] - off[4]) > 0) {
+    if (!hashed[4] && (n = off[5] - off[4]) > 0) {
         static bool attr_set = false;
         if (!attr_set) {
             B200_CUDA(cudaFuncSetAttribute(spgemm_cta_kernel<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 16));

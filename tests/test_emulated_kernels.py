@@ -875,7 +875,7 @@ def emu_spgemm():
 
 def _sort_free_product(lib, A, B, mode):
     """C = A B through spgemm_hash_bin the way b200amg_spgemm_numeric drives it: rows binned by their number of products
-    (32 / 128 / 512 / 2048), one call per bin.  -> (indptr, indices, data) in the kernel's output order, bins it took"""
+    (32 / 128 / 512 / 2048 / 8192), one call per bin.  -> (indptr, indices, data) in the kernel's output order, bins it took"""
     Ap, Aj, Ax = i32(A.indptr), i32(A.indices), np.ascontiguousarray(A.data, np.float64)
     Bp, Bj, Bx = i32(B.indptr), i32(B.indices), np.ascontiguousarray(B.data, np.float64)
     n = A.shape[0]
@@ -885,10 +885,10 @@ def _sort_free_product(lib, A, B, mode):
     Tj = np.full(max(int(ubp[-1]), 1), -7, dtype=np.int32)
     Tx = np.full(max(int(ubp[-1]), 1), np.nan)
     cnt = np.zeros(max(n, 1), dtype=np.int32)
-    limits = [0, 32, 128, 512, 2048]
+    limits = [0, 32, 128, 512, 2048, 8192]
     took = []
     cnt[:n][ub > limits[-1]] = -1                               # rows beyond the last bin stay with the sorting kernels
-    for b in range(4):
+    for b in range(5):
         rows = i32(np.nonzero((ub > limits[b]) & (ub <= limits[b + 1]))[0][::-1])        # (any order inside a bin)
         if rows.size == 0:
             continue
@@ -902,7 +902,8 @@ def _sort_free_product(lib, A, B, mode):
     return ubp, Tj, Tx, cnt, took
 
 
-@pytest.mark.parametrize('case', ['stencil_RA', 'random_wide', 'cancelling', 'unsorted_operands', 'up_to_2048'])
+@pytest.mark.parametrize('case', ['stencil_RA', 'random_wide', 'cancelling', 'unsorted_operands', 'up_to_2048', 'up_to_8192',
+                                  'full_table'])
 def test_sort_free_galerkin_rows_on_the_host(emu_spgemm, case):
     """every row of C = A B equals scipy's csr_matmat row: the same columns IN THE SAME (reverse first touch) ORDER, the
     same bits, exact zeros dropped -- for tentative-prolongator-like operands, wide random rows (probe chains, groups of
@@ -937,10 +938,23 @@ def test_sort_free_galerkin_rows_on_the_host(emu_spgemm, case):
         # duplicate entries inside rows of the left operand (non-canonical CSR)
         L = sp.csr_matrix((np.concatenate([L.data, L.data[:40]]), np.concatenate([L.indices, L.indices[:40]]),
                            np.concatenate([L.indptr[:-1], [L.indptr[-1] + 40]])), shape=L.shape)
-    else:
+    elif case == 'up_to_2048':
         mode = 2
         L = sp.random(12, 400, 0.3, random_state=rng, format='csr')
         R_ = sp.random(400, 1500, 0.01, random_state=rng, format='csr')
+    elif case == 'up_to_8192':
+        # products staged in the row's global scratch (mode 3): rows of 600 .. 8000 products, few and many distinct columns
+        mode = 3
+        L = sp.vstack([sp.random(6, 500, 0.25, random_state=rng, format='csr'), sp.random(6, 500, 0.6, random_state=rng, format='csr'),
+                       sp.random(3, 500, 0.02, random_state=rng, format='csr'), sp.random(5, 500, 0.09, random_state=rng, format='csr')]).tocsr()
+        R_ = sp.hstack([sp.random(500, 300, 0.06, random_state=rng, format='csr'),
+                        sp.random(500, 6000, 0.001, random_state=rng, format='csr')]).tocsr()
+        L.data -= 0.5
+    else:
+        # a row whose 8192 products all have different columns: the 8192-slot table fills to the last slot
+        mode = 3
+        L = sp.csr_matrix(np.ones((1, 2)))
+        R_ = sp.csr_matrix((rng.rand(8192) + 0.1, (np.repeat([0, 1], 4096), rng.permutation(20000)[:8192])), shape=(2, 20000))
     ubp, Tj, Tx, cnt, took = _sort_free_product(emu_spgemm, L, R_, mode)
     import scipy.sparse._sparsetools as st
     n, nc = L.shape[0], R_.shape[1]
@@ -948,7 +962,7 @@ def test_sort_free_galerkin_rows_on_the_host(emu_spgemm, case):
     Cp, Cj, Cx = np.zeros(n + 1, np.int32), np.zeros(max(cap, 1), np.int32), np.zeros(max(cap, 1))
     st.csr_matmat(n, nc, i32(L.indptr), i32(L.indices), np.ascontiguousarray(L.data, np.float64), i32(R_.indptr), i32(R_.indices),
                   np.ascontiguousarray(R_.data, np.float64), Cp, Cj, Cx)
-    assert took and (mode == 1 or 3 in took)
+    assert took and (mode == 1 or 3 in took or 4 in took) and (case != 'up_to_8192' or (3 in took and 4 in took))
     checked = 0
     for i in range(n):
         if cnt[i] < 0:
@@ -958,4 +972,4 @@ def test_sort_free_galerkin_rows_on_the_host(emu_spgemm, case):
         assert np.array_equal(Tj[o:o + cnt[i]], Cj[Cp[i]:Cp[i + 1]]), i
         assert np.array_equal(Tx[o:o + cnt[i]], Cx[Cp[i]:Cp[i + 1]]), i
         checked += 1
-    assert checked >= n - 2 or case == 'up_to_2048'
+    assert checked >= n - 2 or case in ('up_to_2048', 'up_to_8192')

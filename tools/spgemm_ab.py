@@ -1,5 +1,5 @@
 """A/B of the Galerkin product R A P on the device: the sorting rows (B200AMG_SPGEMM_HASH=0) against the sort-free
-rows (=1: rows of up to 512 products, =2: up to 2048) on the levels of the config-2 hierarchy.  Every mode's result
+rows (=1: rows of up to 512 products, =3: up to 8192, the longer ones staged in global memory) on the levels of the config-2 hierarchy.  Every mode's result
 (indptr, indices in scipy's order, values) must equal mode 0's to the bit.  Prints one JSON line.
     python tools/spgemm_ab.py [--grid 256]"""
 import argparse
@@ -9,10 +9,14 @@ import sys
 import time
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..'))
+import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 import pyamg_b200 as amg  # noqa: E402
 from pyamg_b200 import sparse  # noqa: E402
+
+
+MODES = ('0', '1', '3')
 
 
 def main():
@@ -24,11 +28,12 @@ def main():
     A = amg.gallery.poisson((args.grid,) * 3)
     setup = {}
     ml = None
-    for mode in ('0', '1'):
+    for mode in ('1', '0', '3'):                       # (the first build also pays the process warm-up)
         os.environ['B200AMG_SPGEMM_HASH'] = mode
         del ml
         torch.cuda.synchronize()
         t0 = time.perf_counter()
+        np.random.seed(0)
         ml = amg.smoothed_aggregation_solver(A, max_coarse=500)
         torch.cuda.synchronize()
         setup[mode] = round(time.perf_counter() - t0, 3)
@@ -37,7 +42,7 @@ def main():
         Rm, Am, Pm = L.R, L.A, L.P
         rec = {'level': k, 'rows_R': int(Rm.shape[0]), 'nnz_R': int(Rm.nnz), 'nnz_A': int(Am.nnz)}
         want = None
-        for mode in ('0', '1', '2'):
+        for mode in MODES:
             os.environ['B200AMG_SPGEMM_HASH'] = mode
             best = None
             for _ in range(2):
