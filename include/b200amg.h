@@ -190,7 +190,7 @@ int b200amg_halo_exchange(const double *v, int n_send, const int *send_idx, cons
  *  3. b200amg_spgemm_numeric: every row into the scratch Tj/Tx (both sized
  *     ubp[n_row]) at offset ubp[i], cnt[i] = kept entries.  Tk (u64[ubp[n_row]]) is only
  *     needed when some row has more than 8192 products (else NULL).  work: n_row + 128 ints.
- *     Synchronises the stream once (row binning).  Rows of up to 512 products in scipy's order are
+ *     Synchronises the stream once (row binning).  Rows of up to 8192 products in scipy's order are
  *     accumulated without a sort (spgemm_hash.cu; B200AMG_SPGEMM_HASH=0 switches that off), every other
  *     row by expand-sort-compress; the results are the same to the bit.
  *  4. b200amg_exclusive_scan_i32(cnt) -> Cp[n_row+1];
